@@ -1,0 +1,105 @@
+"""ctypes binding of libcfd_b200.so (include/cfd_b200.h).  There is no CPU fallback: a missing library or a
+missing GPU raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libcfd_b200.so")
+
+CFD_EQ_COUNT = 8
+FAMILY_CAVITY, FAMILY_GENERAL, FAMILY_TEACH = 0, 1, 2
+ORDER_REDBLACK, ORDER_SEQUENTIAL = 0, 1
+
+FIELDS = ("u", "v", "p", "pp", "vis", "den", "t", "cp", "ae", "aw", "an", "as", "ap", "su", "sp", "du", "dv")
+FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
+GEOMS = ("x", "xu", "sew", "sewu", "y", "yv", "sns", "snsv",
+         "xdif", "xcvi", "xcvip", "fx", "fxm",
+         "ydif", "ycvr", "ycvrs", "arx", "arxj", "arxjp", "r", "rmn", "sx", "sxmn", "fv", "fvp", "fy", "fym")
+GEOM_ID = {n: i for i, n in enumerate(GEOMS)}
+
+
+class CfdConfig(C.Structure):
+    _fields_ = [("family", C.c_int), ("ni", C.c_int), ("nj", C.c_int), ("iadv", C.c_int), ("order", C.c_int),
+                ("nswp", C.c_int * CFD_EQ_COUNT), ("urf", C.c_double * CFD_EQ_COUNT),
+                ("ipref", C.c_int), ("jpref", C.c_int), ("device", C.c_int), ("tdma_m", C.c_int),
+                ("goff", C.c_int), ("ni_global", C.c_int), ("halo_w", C.c_int), ("halo_e", C.c_int),
+                ("sew_nim1", C.c_double)]
+
+
+class CfdHeatConfig(C.Structure):
+    _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("k", C.c_double), ("rho", C.c_double), ("cp", C.c_double),
+                ("xa", C.c_double), ("xb", C.c_double), ("ya", C.c_double), ("yb", C.c_double),
+                ("tleft", C.c_double), ("tright", C.c_double), ("tbottom", C.c_double), ("ttop", C.c_double),
+                ("dt", C.c_double), ("qthr", C.c_double), ("qval", C.c_double),
+                ("device", C.c_int), ("j_goff", C.c_int), ("ny_global", C.c_int),
+                ("halo_s", C.c_int), ("halo_n", C.c_int)]
+
+
+class CfdError(RuntimeError):
+    pass
+
+
+# every symbol include/cfd_b200.h declares: name -> (restype, argtypes)
+_vp, _dp, _ip = C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)
+SYMBOLS = {
+    "cfd_create": (C.c_int, [C.POINTER(_vp), C.POINTER(CfdConfig)]),
+    "cfd_destroy": (C.c_int, [_vp]),
+    "cfd_strerror": (C.c_char_p, [C.c_int]),
+    "cfd_last_error": (C.c_char_p, []),
+    "cfd_set_stream": (C.c_int, [_vp, _vp]),
+    "cfd_synchronize": (C.c_int, [_vp]),
+    "cfd_set_geometry": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_probe": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _dp]),
+    "cfd_field_device_view": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
+    "cfd_layout_info": (C.c_int, [_vp, _ip, _ip, _ip]),
+    "cfd_calcu": (C.c_int, [_vp, _dp]),
+    "cfd_calcv": (C.c_int, [_vp, _dp]),
+    "cfd_calcp": (C.c_int, [_vp, _dp]),
+    "cfd_lisolv": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
+    "cfd_iterate": (C.c_int, [_vp, C.c_int, _dp]),
+    "cfd_assemble_u": (C.c_int, [_vp]),
+    "cfd_assemble_v": (C.c_int, [_vp]),
+    "cfd_assemble_p": (C.c_int, [_vp]),
+    "cfd_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "cfd_correct": (C.c_int, [_vp, _vp]),
+    "cfd_residuals": (C.c_int, [_vp, _dp]),
+    "cfd_residual_device_ptr": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "cfd_heat_create": (C.c_int, [C.POINTER(_vp), C.POINTER(CfdHeatConfig)]),
+    "cfd_heat_destroy": (C.c_int, [_vp]),
+    "cfd_heat_set_stream": (C.c_int, [_vp, _vp]),
+    "cfd_heat_upload": (C.c_int, [_vp, _vp, C.c_int]),
+    "cfd_heat_download": (C.c_int, [_vp, _vp, C.c_int]),
+    "cfd_heat2d_step": (C.c_int, [_vp, C.c_int]),
+    "cfd_heat2d_step_exact": (C.c_int, [_vp, C.c_int]),
+    "cfd_heat2d_implicit_step": (C.c_int, [_vp, C.c_int]),
+    "cfd_heat_device_view": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
+    "cfd_heat_synchronize": (C.c_int, [_vp]),
+    "cfd_version": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen the CUDA library; raises if it has not been built (python __graft_entry__.py build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise CfdError(f"{LIB_PATH} is missing: build it with `make -C cfd_b200/csrc` "
+                           "(there is no CPU fallback)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        lib = load()
+        raise CfdError(f"{lib.cfd_strerror(rc).decode()}: {lib.cfd_last_error().decode()}")

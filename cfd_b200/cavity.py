@@ -1,0 +1,250 @@
+"""Host-side mirror of `program cavity_fvm` (lid-driven-cavity-2d/fvm-simple/cavity_fvm.f90) over the C ABI.
+
+The names are the reference's: module variables of vars_mod (cavity_fvm.f90:22-41) become attributes, and
+calcu / calcv / calcp / lisolv keep their meaning (cavity_fvm.f90:92-355, 49-82) -- but the arrays live on the
+GPU, and the host only sees them through `upload` / `download` (the reference driver touches them between
+calls at cavity_fvm.f90:534-538 and 559-607).  Everything numeric runs in libcfd_b200.so; nothing here
+computes a field on the CPU, and a missing library or GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import CfdConfig, FIELD_ID, GEOM_ID, check
+
+
+def setgrid(nicv: int, njcv: int, xstart: float, xend: float, ystart: float, yend: float):
+    """setgrid (cavity_fvm.f90:366-414): uniform, cell-centred, backward-staggered grid.  Host logic (O(ni+nj))."""
+    ni, nj = nicv + 2, njcv + 2
+    x, xu, sew, sewu = (np.zeros(ni) for _ in range(4))
+    y, yv, sns, snsv = (np.zeros(nj) for _ in range(4))
+    xu[0] = xstart
+    xu[1] = xstart
+    dx = (xend - xstart) / nicv
+    for i in range(2, ni):
+        xu[i] = xu[i - 1] + dx
+    x[0] = xu[1]
+    for i in range(1, ni - 1):
+        x[i] = 0.5 * (xu[i] + xu[i + 1])
+        sew[i] = xu[i + 1] - xu[i]
+    x[ni - 1] = xu[ni - 1]
+    for i in range(2, ni - 1):
+        sewu[i] = x[i] - x[i - 1]
+    yv[0] = ystart
+    yv[1] = ystart
+    dy = (yend - ystart) / njcv
+    for j in range(2, nj):
+        yv[j] = yv[j - 1] + dy
+    y[0] = yv[1]
+    for j in range(1, nj - 1):
+        y[j] = 0.5 * (yv[j] + yv[j + 1])
+        sns[j] = yv[j + 1] - yv[j]
+    y[nj - 1] = yv[nj - 1]
+    for j in range(2, nj - 1):
+        snsv[j] = y[j] - y[j - 1]
+    return dict(x=x, xu=xu, sew=sew, sewu=sewu, y=y, yv=yv, sns=sns, snsv=snsv)
+
+
+class CavityFVM:
+    """One GPU context for the cavity family.  Indices are 1-based like the Fortran wherever they are arguments."""
+
+    def __init__(self, nicv=10, njcv=10, *, iadv=3, order="redblack", urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3),
+                 ipref=None, jpref=None, device=-1, tdma_m=0,
+                 ni_local=None, goff=0, halo_w=0, halo_e=0, sew_nim1=0.0):
+        self.lib = _lib.load()
+        self.nicv, self.njcv = nicv, njcv
+        self.ni_global, self.nj = nicv + 2, njcv + 2
+        self.ni = ni_local if ni_local is not None else self.ni_global
+        self.nim1, self.njm1 = self.ni_global - 1, self.nj - 1
+        self.iadv = iadv
+        self.urfu, self.urfv, self.urfp = urf
+        self.nswpu, self.nswpv, self.nswpp = nswp
+        self.ipref = ipref if ipref is not None else self.ni_global // 2      # cavity_fvm.f90:549-550
+        self.jpref = jpref if jpref is not None else self.nj // 2
+        self.imon, self.jmon = self.ipref, self.jpref
+        self.goff = goff
+        cfg = CfdConfig()
+        cfg.family = _lib.FAMILY_CAVITY
+        cfg.ni, cfg.nj = self.ni, self.nj
+        cfg.iadv = iadv
+        cfg.order = _lib.ORDER_SEQUENTIAL if order in ("sequential", "seq", 1) else _lib.ORDER_REDBLACK
+        for k in range(3):
+            cfg.nswp[k] = nswp[k]
+            cfg.urf[k] = urf[k]
+        cfg.ipref, cfg.jpref = self.ipref, self.jpref
+        cfg.device = device
+        cfg.tdma_m = tdma_m
+        cfg.goff = goff
+        cfg.ni_global = self.ni_global if (ni_local is not None) else 0
+        cfg.halo_w, cfg.halo_e = halo_w, halo_e
+        cfg.sew_nim1 = sew_nim1
+        self._cfg = cfg
+        self._h = C.c_void_p()
+        check(self.lib.cfd_create(C.byref(self._h), C.byref(cfg)))
+        self.resoru = self.resorv = self.resorm = 0.0
+
+    # -- life cycle ---------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self.lib.cfd_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def layout(self):
+        m, t, ld = C.c_int(), C.c_int(), C.c_int()
+        check(self.lib.cfd_layout_info(self._h, C.byref(m), C.byref(t), C.byref(ld)))
+        return dict(M=m.value, T=t.value, LD=ld.value)
+
+    def set_stream(self, cuda_stream: int):
+        check(self.lib.cfd_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def synchronize(self):
+        check(self.lib.cfd_synchronize(self._h))
+
+    # -- data movement ------------------------------------------------------------------------------
+    def set_geometry(self, **arrays):
+        for name, a in arrays.items():
+            a = np.ascontiguousarray(a, dtype=np.float64)
+            check(self.lib.cfd_set_geometry(self._h, GEOM_ID[name], a.ctypes.data_as(C.c_void_p), a.size))
+
+    def setgrid(self, xstart=0.0, xend=1.0, ystart=0.0, yend=1.0):
+        """call setgrid(...) of the reference driver (cavity_fvm.f90:532); single-GPU contexts only."""
+        g = setgrid(self.nicv, self.njcv, xstart, xend, ystart, yend)
+        for k, v in g.items():
+            setattr(self, k, v)
+        self.set_geometry(**g)
+        return g
+
+    def upload(self, name: str, a: np.ndarray):
+        a = np.asfortranarray(a, dtype=np.float64)
+        assert a.shape == (self.ni, self.nj), (a.shape, self.ni, self.nj)
+        check(self.lib.cfd_upload(self._h, FIELD_ID[name], a.ctypes.data_as(C.c_void_p), a.shape[0]))
+
+    def upload_ptr(self, name: str, ptr: int, ld: int):
+        check(self.lib.cfd_upload(self._h, FIELD_ID[name], C.c_void_p(ptr), ld))
+
+    def download_ptr(self, name: str, ptr: int, ld: int):
+        check(self.lib.cfd_download(self._h, FIELD_ID[name], C.c_void_p(ptr), ld))
+
+    def download(self, name: str) -> np.ndarray:
+        a = np.zeros((self.ni, self.nj), order="F")
+        check(self.lib.cfd_download(self._h, FIELD_ID[name], a.ctypes.data_as(C.c_void_p), a.shape[0]))
+        return a
+
+    def probe(self, name: str, i: int, j: int) -> float:
+        v = C.c_double()
+        check(self.lib.cfd_probe(self._h, FIELD_ID[name], i, j, C.byref(v)))
+        return v.value
+
+    def device_view(self, name: str):
+        base, stride, n = C.c_void_p(), C.c_longlong(), C.c_int()
+        check(self.lib.cfd_field_device_view(self._h, FIELD_ID[name], C.byref(base), C.byref(stride), C.byref(n)))
+        return base.value, stride.value, n.value
+
+    # -- the reference's subroutines ----------------------------------------------------------------
+    def calcu(self) -> float:
+        r = C.c_double()
+        check(self.lib.cfd_calcu(self._h, C.byref(r)))
+        self.resoru = r.value
+        return r.value
+
+    def calcv(self) -> float:
+        r = C.c_double()
+        check(self.lib.cfd_calcv(self._h, C.byref(r)))
+        self.resorv = r.value
+        return r.value
+
+    def calcp(self) -> float:
+        r = C.c_double()
+        check(self.lib.cfd_calcp(self._h, C.byref(r)))
+        self.resorm = r.value
+        return r.value
+
+    def lisolv(self, istart: int, jstart: int, phi: str):
+        check(self.lib.cfd_lisolv(self._h, istart, jstart, FIELD_ID[phi]))
+
+    def iterate(self, n: int = 1):
+        res = (C.c_double * 8)()
+        check(self.lib.cfd_iterate(self._h, n, res))
+        self.resoru, self.resorv, self.resorm = res[0], res[1], res[2]
+        return self.resoru, self.resorv, self.resorm
+
+    def iterate_async(self, n: int = 1):
+        check(self.lib.cfd_iterate(self._h, n, None))
+
+    def residuals(self):
+        res = (C.c_double * 8)()
+        check(self.lib.cfd_residuals(self._h, res))
+        return tuple(res)
+
+    # -- stage-level calls (multi-GPU driver) -------------------------------------------------------
+    def assemble_u(self):
+        check(self.lib.cfd_assemble_u(self._h))
+
+    def assemble_v(self):
+        check(self.lib.cfd_assemble_v(self._h))
+
+    def assemble_p(self):
+        check(self.lib.cfd_assemble_p(self._h))
+
+    def sweep(self, istart, jstart, phi, colour, first=False):
+        check(self.lib.cfd_sweep(self._h, istart, jstart, FIELD_ID[phi], colour, 1 if first else 0))
+
+    def correct(self, ppref_device_ptr: int | None = None):
+        check(self.lib.cfd_correct(self._h, C.c_void_p(ppref_device_ptr) if ppref_device_ptr else None))
+
+    def residual_device_ptr(self) -> int:
+        p = C.c_void_p()
+        check(self.lib.cfd_residual_device_ptr(self._h, C.byref(p)))
+        return p.value
+
+    # -- the literals of the reference driver ----------------------------------------------------------
+    def init_lid_driven(self, reynolds=100.0, utop=1.0, rho=1000.0, xlim=(0.0, 1.0), ylim=(0.0, 1.0)):
+        """cavity_fvm.f90:527-538: grid, fluid properties, lid velocity (single-GPU contexts)."""
+        self.setgrid(xlim[0], xlim[1], ylim[0], ylim[1])
+        den = np.full((self.ni, self.nj), rho, order="F")
+        vis = np.asfortranarray(den * utop * (xlim[1] - xlim[0]) / reynolds)
+        u = np.zeros((self.ni, self.nj), order="F")
+        u[1:, self.nj - 1] = utop
+        self.upload("den", den)
+        self.upload("vis", vis)
+        self.upload("u", u)
+
+    def run(self, maxit=90000, tol=1.0e-10, check_every=1):
+        """The outer loop cavity_fvm.f90:553-566.  check_every>1 tests the stop rule every that many passes."""
+        it = 0
+        while it < maxit:
+            n = min(check_every, maxit - it)
+            ru, rv, rm = self.iterate(n)
+            it += n
+            if max(ru, rv, rm) < tol:
+                break
+        return it
+
+
+def centred_vel(u: np.ndarray, v: np.ndarray):
+    """centred_vel (cavity_fvm.f90:416-430) on downloaded fields -- post-processing, host side."""
+    ni, nj = u.shape
+    uc, vc = np.zeros_like(u), np.zeros_like(v)
+    uc[0, :] = u[1, :]
+    uc[ni - 1, :] = u[ni - 1, :]
+    vc[:, 0] = v[:, 1]
+    vc[:, nj - 1] = v[:, nj - 1]
+    uc[1:ni - 1, :] = 0.5 * (u[1:ni - 1, :] + u[2:ni, :])
+    vc[:, 1:nj - 1] = 0.5 * (v[:, 1:nj - 1] + v[:, 2:nj])
+    return uc, vc

@@ -1,0 +1,409 @@
+// api.cu -- the extern "C" surface of libcfd_b200.so for the SIMPLE families (include/cfd_b200.h):
+// context life cycle, host<->device layout conversion, and the composition of the stage kernels into the
+// reference's subroutines calcu / calcv / calcp / lisolv and the outer-loop body.
+#include <cstdarg>
+#include "common.cuh"
+
+using namespace cfd;
+
+static thread_local char g_err[1024] = "";
+void cfd_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* cfd_last_error(void) { return g_err; }
+extern "C" const char* cfd_version(void) { return "cfd_b200 0.1 (sm_100a, fp64)"; }
+extern "C" const char* cfd_strerror(int s) {
+  switch (s) {
+    case CFD_OK: return "ok";
+    case CFD_ERR_INVALID: return "invalid argument";
+    case CFD_ERR_CUDA: return "CUDA runtime error";
+    case CFD_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+    case CFD_ERR_UNSUPPORTED: return "unsupported in this build";
+    case CFD_ERR_NOMEM: return "out of device memory";
+    default: return "unknown status";
+  }
+}
+
+// ---- layout conversion kernels -----------------------------------------------------------------------
+namespace cfd {
+// column-major image A(ni,nj) (i fastest)  ->  line layout.  One 32x32 tile of (i0, t) per block and k.
+__global__ void __launch_bounds__(256) k_to_line(const Layout L, const double* __restrict__ src, double* __restrict__ dst) {
+  __shared__ double tile[32][33];
+  const int k = blockIdx.z, ib = blockIdx.x * 32, tb = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int t = tb + r, i0 = ib + threadIdx.x, j0 = t * L.M + k;
+    tile[r][threadIdx.x] = (t < L.T && i0 < L.ni && j0 < L.nj) ? src[(size_t)j0 * L.ni + i0] : 0.0;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int i0 = ib + r, t = tb + threadIdx.x, j0 = t * L.M + k;
+    if (t < L.T && i0 < L.ni && j0 < L.nj) dst[(size_t)i0 * L.LD + (size_t)k * L.T + t] = tile[threadIdx.x][r];
+  }
+}
+__global__ void __launch_bounds__(256) k_from_line(const Layout L, const double* __restrict__ src, double* __restrict__ dst) {
+  __shared__ double tile[32][33];
+  const int k = blockIdx.z, ib = blockIdx.x * 32, tb = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int i0 = ib + r, t = tb + threadIdx.x, j0 = t * L.M + k;
+    tile[r][threadIdx.x] = (t < L.T && i0 < L.ni && j0 < L.nj) ? src[(size_t)i0 * L.LD + (size_t)k * L.T + t] : 0.0;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int t = tb + r, i0 = ib + threadIdx.x, j0 = t * L.M + k;
+    if (t < L.T && i0 < L.ni && j0 < L.nj) dst[(size_t)j0 * L.ni + i0] = tile[threadIdx.x][r];
+  }
+}
+}  // namespace cfd
+
+int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst) {
+  dim3 block(32, 8), grid((c->L.ni + 31) / 32, (c->L.T + 31) / 32, c->L.M);
+  k_to_line<<<grid, block, 0, c->stream>>>(c->L, colmajor, dst);
+  CFD_CUDA(cudaGetLastError());
+  return CFD_OK;
+}
+int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor) {
+  dim3 block(32, 8), grid((c->L.ni + 31) / 32, (c->L.T + 31) / 32, c->L.M);
+  k_from_line<<<grid, block, 0, c->stream>>>(c->L, src, colmajor);
+  CFD_CUDA(cudaGetLastError());
+  return CFD_OK;
+}
+
+// ---- layout choice -------------------------------------------------------------------------------------
+// T threads per line (multiple of 32, <= 1024), M nodes per thread (<= CFD_MAX_M), T*M >= nj.  Among the
+// (M,T) pairs whose line-solver instantiation keeps its chunk in registers (ptxas: no spills) take the least
+// padding, ties to the larger M (less parallel-cyclic-reduction work per node); if none fits, least padding.
+static bool fits_registers(int m, int t) { return t <= 384 || (t <= 640 && m <= 9) || m <= 5; }
+
+static int choose_layout(int ni, int nj, int want_m, Layout* L) {
+  long best = -1;
+  int bm = 0, bt = 0;
+  for (int pass = 0; pass < 2 && best < 0; ++pass) {
+    for (int m = CFD_MAX_M; m >= 1; --m) {
+      if (want_m > 0 && m != want_m) continue;
+      int t = ((nj + m - 1) / m + 31) / 32 * 32;
+      if (t > 1024) continue;
+      if (pass == 0 && !fits_registers(m, t)) continue;
+      long ld = (long)t * m;
+      if (best < 0 || ld < best) {
+        best = ld;
+        bm = m;
+        bt = t;
+      }
+    }
+  }
+  if (best < 0) return CFD_ERR_UNSUPPORTED;
+  L->ni = ni;
+  L->nj = nj;
+  L->M = bm;
+  L->T = bt;
+  L->LD = (int)best;
+  return CFD_OK;
+}
+
+static const int kCavityFields[] = {CFD_U,  CFD_V,  CFD_P,  CFD_PP, CFD_VIS, CFD_DEN, CFD_AE,
+                                    CFD_AW, CFD_AN, CFD_AS, CFD_AP, CFD_SU,  CFD_DU,  CFD_DV};
+
+static bool geom_is_j(int id) {
+  switch (id) {
+    case CFD_G_X: case CFD_G_XU: case CFD_G_SEW: case CFD_G_SEWU:
+    case CFD_G_XDIF: case CFD_G_XCVI: case CFD_G_XCVIP: case CFD_G_FX: case CFD_G_FXM:
+      return false;
+    default:
+      return true;
+  }
+}
+
+extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
+  CFD_REQUIRE(out && cfg, "null argument");
+  *out = nullptr;
+  CFD_REQUIRE(cfg->ni >= 4 && cfg->nj >= 4, "ni, nj must be >= 4 (two boundary nodes + two cells)");
+  CFD_REQUIRE(cfg->family == CFD_FAMILY_CAVITY, "only CFD_FAMILY_CAVITY contexts are created here");
+  CFD_REQUIRE(cfg->iadv >= 1 && cfg->iadv <= 3, "iadv must be 1 (CDS), 2 (UDS) or 3 (hybrid)");
+  CFD_REQUIRE(cfg->order == CFD_ORDER_REDBLACK || cfg->order == CFD_ORDER_SEQUENTIAL, "bad order");
+  CFD_REQUIRE(cfg->halo_w >= 0 && cfg->halo_e >= 0 && cfg->halo_w + cfg->halo_e < cfg->ni, "bad halo widths");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cfd_set_error("no CUDA device visible; libcfd_b200 has no CPU fallback");
+    return CFD_ERR_NO_DEVICE;
+  }
+  int dev = cfg->device;
+  if (dev < 0) CFD_CUDA(cudaGetDevice(&dev));
+  CFD_REQUIRE(dev < ndev, "device ordinal out of range");
+  CFD_CUDA(cudaSetDevice(dev));
+
+  cfd_ctx* c = new cfd_ctx();
+  c->cfg = *cfg;
+  c->device = dev;
+  c->stream = 0;
+  for (auto& f : c->field) f = nullptr;
+  for (auto& g : c->geom) g = nullptr;
+  c->stage = nullptr;
+  c->partial = nullptr;
+  c->res_dev = nullptr;
+  c->seq_scratch = nullptr;
+  int want_m = cfg->tdma_m;
+  if (want_m == 0) {
+    const char* e = getenv("CFD_B200_TDMA_M");
+    if (e) want_m = atoi(e);
+  }
+  if (choose_layout(cfg->ni, cfg->nj, want_m, &c->L) != CFD_OK) {
+    delete c;
+    cfd_set_error("nj=%d too long for the line layout (max %d)", cfg->nj, 1024 * CFD_MAX_M);
+    return CFD_ERR_UNSUPPORTED;
+  }
+  const size_t fbytes = (size_t)c->L.ni * c->L.LD * sizeof(double);
+  for (int f : kCavityFields) {
+    if (cudaMalloc(&c->field[f], fbytes) != cudaSuccess) {
+      cfd_set_error("cudaMalloc of %zu bytes for field %d failed", fbytes, f);
+      cfd_destroy(c);
+      return CFD_ERR_NOMEM;
+    }
+    CFD_CUDA(cudaMemset(c->field[f], 0, fbytes));
+  }
+  for (int g = 0; g < CFD_GEOM_COUNT; ++g) {
+    const size_t n = geom_is_j(g) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
+    c->geom_host[g].assign(geom_is_j(g) ? c->L.nj : c->L.ni, 0.0);
+    CFD_CUDA(cudaMalloc(&c->geom[g], n * sizeof(double)));
+    CFD_CUDA(cudaMemset(c->geom[g], 0, n * sizeof(double)));
+  }
+  c->max_partials = ((c->L.T + 31) / 32) * ((c->L.ni + 7) / 8);
+  CFD_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
+  CFD_CUDA(cudaMalloc(&c->res_dev, 8 * sizeof(double)));
+  CFD_CUDA(cudaMemset(c->res_dev, 0, 8 * sizeof(double)));
+  *out = c;
+  return CFD_OK;
+}
+
+extern "C" int cfd_destroy(cfd_ctx* c) {
+  if (!c) return CFD_OK;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (auto& f : c->field) if (f) cudaFree(f);
+  for (auto& g : c->geom) if (g) cudaFree(g);
+  if (c->stage) cudaFree(c->stage);
+  if (c->partial) cudaFree(c->partial);
+  if (c->res_dev) cudaFree(c->res_dev);
+  if (c->seq_scratch) cudaFree(c->seq_scratch);
+  delete c;
+  return CFD_OK;
+}
+
+extern "C" int cfd_set_stream(cfd_ctx* c, void* s) {
+  CFD_REQUIRE(c, "null context");
+  c->stream = (cudaStream_t)s;
+  return CFD_OK;
+}
+
+extern "C" int cfd_synchronize(cfd_ctx* c) {
+  CFD_REQUIRE(c, "null context");
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+extern "C" int cfd_set_geometry(cfd_ctx* c, int id, const double* host, int n) {
+  CFD_REQUIRE(c && host, "null argument");
+  CFD_REQUIRE(id >= 0 && id < CFD_GEOM_COUNT, "bad geometry id");
+  const bool isj = geom_is_j(id);
+  CFD_REQUIRE(n == (isj ? c->L.nj : c->L.ni), "geometry array length must be nj (y-arrays) or ni (x-arrays)");
+  CFD_CUDA(cudaSetDevice(c->device));
+  c->geom_host[id].assign(host, host + n);
+  if (!isj) {
+    CFD_CUDA(cudaMemcpyAsync(c->geom[id], host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CFD_CUDA(cudaStreamSynchronize(c->stream));
+  } else {
+    std::vector<double> tmp((size_t)c->L.LD, 0.0);
+    for (int j0 = 0; j0 < n; ++j0) tmp[lpos(j0, c->L.M, c->L.T)] = host[j0];
+    CFD_CUDA(cudaMemcpyAsync(c->geom[id], tmp.data(), tmp.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CFD_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  return CFD_OK;
+}
+
+static int ensure_stage(cfd_ctx* c) {
+  if (!c->stage) {
+    if (cudaMalloc(&c->stage, (size_t)c->L.ni * c->L.nj * sizeof(double)) != cudaSuccess) {
+      cfd_set_error("cudaMalloc of the upload/download staging buffer failed");
+      return CFD_ERR_NOMEM;
+    }
+  }
+  return CFD_OK;
+}
+
+static int check_field(const cfd_ctx* c, int field) {
+  if (field < 0 || field >= CFD_FIELD_COUNT || !c->field[field]) {
+    cfd_set_error("field id %d is not allocated in this context", field);
+    return CFD_ERR_INVALID;
+  }
+  return CFD_OK;
+}
+
+extern "C" int cfd_upload(cfd_ctx* c, int field, const double* host, int ld) {
+  CFD_REQUIRE(c && host, "null argument");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(ld >= c->L.ni, "ld < ni");
+  CFD_CUDA(cudaSetDevice(c->device));
+  if ((rc = ensure_stage(c))) return rc;
+  CFD_CUDA(cudaMemcpy2DAsync(c->stage, (size_t)c->L.ni * sizeof(double), host, (size_t)ld * sizeof(double),
+                             (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyHostToDevice, c->stream));
+  if ((rc = cfd_launch_to_line_layout(c, c->stage, c->field[field]))) return rc;
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+extern "C" int cfd_download(cfd_ctx* c, int field, double* host, int ld) {
+  CFD_REQUIRE(c && host, "null argument");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(ld >= c->L.ni, "ld < ni");
+  CFD_CUDA(cudaSetDevice(c->device));
+  if ((rc = ensure_stage(c))) return rc;
+  if ((rc = cfd_launch_from_line_layout(c, c->field[field], c->stage))) return rc;
+  CFD_CUDA(cudaMemcpy2DAsync(host, (size_t)ld * sizeof(double), c->stage, (size_t)c->L.ni * sizeof(double),
+                             (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyDeviceToHost, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+extern "C" int cfd_probe(cfd_ctx* c, int field, int i, int j, double* value) {
+  CFD_REQUIRE(c && value, "null argument");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(i >= 1 && i <= c->L.ni && j >= 1 && j <= c->L.nj, "probe index out of range");
+  const double* src = c->field[field] + (size_t)(i - 1) * c->L.LD + lpos(j - 1, c->L.M, c->L.T);
+  CFD_CUDA(cudaMemcpyAsync(value, src, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+extern "C" int cfd_field_device_view(cfd_ctx* c, int field, void** base, long long* line_stride, int* nlines) {
+  CFD_REQUIRE(c, "null context");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  if (base) *base = c->field[field];
+  if (line_stride) *line_stride = c->L.LD;
+  if (nlines) *nlines = c->L.ni;
+  return CFD_OK;
+}
+
+extern "C" int cfd_layout_info(cfd_ctx* c, int* m, int* t, int* ld) {
+  CFD_REQUIRE(c, "null context");
+  if (m) *m = c->L.M;
+  if (t) *t = c->L.T;
+  if (ld) *ld = c->L.LD;
+  return CFD_OK;
+}
+
+// ---- stage entry points ----------------------------------------------------------------------------------
+extern "C" int cfd_assemble_u(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return cfd_launch_assemble_u(c); }
+extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return cfd_launch_assemble_v(c); }
+extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return cfd_launch_assemble_p(c); }
+extern "C" int cfd_correct(cfd_ctx* c, const double* ppref) { CFD_REQUIRE(c, "null context"); return cfd_launch_correct(c, ppref); }
+
+extern "C" int cfd_sweep(cfd_ctx* c, int istart, int jstart, int field, int colour, int first) {
+  CFD_REQUIRE(c, "null context");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(istart >= 2 && jstart >= 2 && jstart <= c->L.nj - 1, "istart/jstart out of range");
+  if (colour < 0) return cfd_launch_sweep_seq(c, istart, jstart, c->field[field], first);
+  CFD_REQUIRE(colour <= 1, "colour must be 0, 1 or negative (sequential)");
+  return cfd_launch_sweep_rb(c, istart, jstart, c->field[field], colour, first);
+}
+
+static int full_sweep(cfd_ctx* c, int istart, int jstart, int field, int first) {
+  int rc;
+  if (c->cfg.order == CFD_ORDER_SEQUENTIAL) return cfd_launch_sweep_seq(c, istart, jstart, c->field[field], first);
+  if ((rc = cfd_launch_sweep_rb(c, istart, jstart, c->field[field], 0, first))) return rc;
+  return cfd_launch_sweep_rb(c, istart, jstart, c->field[field], 1, first);
+}
+
+extern "C" int cfd_lisolv(cfd_ctx* c, int istart, int jstart, int field) {
+  CFD_REQUIRE(c, "null context");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(istart >= 2 && jstart >= 2 && jstart <= c->L.nj - 1, "istart/jstart out of range");
+  CFD_CUDA(cudaSetDevice(c->device));
+  if ((rc = full_sweep(c, istart, jstart, field, 0))) return rc;
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+static int read_res(cfd_ctx* c, int eq, double* out) {
+  if (!out) return CFD_OK;
+  CFD_CUDA(cudaMemcpyAsync(out, c->res_dev + eq, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+static int stage_u(cfd_ctx* c) {
+  int rc;
+  if ((rc = cfd_launch_assemble_u(c))) return rc;
+  for (int n = 0; n < c->cfg.nswp[CFD_EQ_U]; ++n)
+    if ((rc = full_sweep(c, 3, 2, CFD_U, 0))) return rc;
+  return CFD_OK;
+}
+static int stage_v(cfd_ctx* c) {
+  int rc;
+  if ((rc = cfd_launch_assemble_v(c))) return rc;
+  for (int n = 0; n < c->cfg.nswp[CFD_EQ_V]; ++n)
+    if ((rc = full_sweep(c, 2, 3, CFD_V, 0))) return rc;
+  return CFD_OK;
+}
+static int stage_p(cfd_ctx* c) {
+  int rc;
+  if ((rc = cfd_launch_assemble_p(c))) return rc;
+  if (c->cfg.nswp[CFD_EQ_P] == 0) {   // pp(:,:) = 0 with no sweep to fold it into
+    CFD_CUDA(cudaMemsetAsync(c->field[CFD_PP], 0, (size_t)c->L.ni * c->L.LD * sizeof(double), c->stream));
+  }
+  for (int n = 0; n < c->cfg.nswp[CFD_EQ_P]; ++n)
+    if ((rc = full_sweep(c, 2, 2, CFD_PP, n == 0))) return rc;
+  return cfd_launch_correct(c, nullptr);
+}
+
+extern "C" int cfd_calcu(cfd_ctx* c, double* resoru) {
+  CFD_REQUIRE(c, "null context");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc = stage_u(c);
+  return rc ? rc : read_res(c, CFD_EQ_U, resoru);
+}
+extern "C" int cfd_calcv(cfd_ctx* c, double* resorv) {
+  CFD_REQUIRE(c, "null context");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc = stage_v(c);
+  return rc ? rc : read_res(c, CFD_EQ_V, resorv);
+}
+extern "C" int cfd_calcp(cfd_ctx* c, double* resorm) {
+  CFD_REQUIRE(c, "null context");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc = stage_p(c);
+  return rc ? rc : read_res(c, CFD_EQ_P, resorm);
+}
+
+extern "C" int cfd_iterate(cfd_ctx* c, int n, double res[8]) {
+  CFD_REQUIRE(c && n >= 0, "bad argument");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc;
+  for (int it = 0; it < n; ++it) {
+    if ((rc = stage_u(c))) return rc;
+    if ((rc = stage_v(c))) return rc;
+    if ((rc = stage_p(c))) return rc;
+  }
+  return res ? cfd_residuals(c, res) : CFD_OK;
+}
+
+extern "C" int cfd_residuals(cfd_ctx* c, double res[8]) {
+  CFD_REQUIRE(c && res, "null argument");
+  CFD_CUDA(cudaMemcpyAsync(res, c->res_dev, 8 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+extern "C" int cfd_residual_device_ptr(cfd_ctx* c, void** ptr) {
+  CFD_REQUIRE(c && ptr, "null argument");
+  *ptr = c->res_dev;
+  return CFD_OK;
+}

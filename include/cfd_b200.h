@@ -1,0 +1,180 @@
+/*
+ * cfd_b200.h -- C ABI of libcfd_b200.so: the B200 (sm_100a) implementation of the data-parallel hot path of
+ * brli3/CFD (staggered-grid FVM SIMPLE outer iteration + 5-point FD heat stencils).
+ *
+ * The reference is serial Fortran 90 with no FFI surface: its hot routines take no arguments and talk through
+ * module-global allocatable arrays.  Each entry point below therefore names the reference
+ * routine (path:line under the reference tree) whose work it replaces; the Fortran iso_c_binding interface a
+ * maintainer would add is in INTEGRATION.md.  Plain C types only: pointers, ints, doubles.  Every function
+ * returns CFD_OK (0) or a negative cfd_status; no exceptions, no host callbacks, one thread per context.
+ *
+ * Host arrays are the reference's own: real(dp) A(ld,nj), column-major, 1-based, A(i,j) at a[(i-1)+(j-1)*ld].
+ * All (i,j) arguments are 1-based like the Fortran.  Device storage is private to the context (a line-major,
+ * chunk-interleaved layout); the only way data crosses is cfd_upload / cfd_download.
+ */
+#ifndef CFD_B200_H
+#define CFD_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cfd_ctx cfd_ctx;
+
+typedef enum cfd_status {
+  CFD_OK = 0,
+  CFD_ERR_INVALID = -1,      /* bad argument / size / id */
+  CFD_ERR_CUDA = -2,         /* a CUDA runtime call failed; cfd_last_error() has the text */
+  CFD_ERR_NO_DEVICE = -3,    /* no CUDA device: there is NO CPU fallback */
+  CFD_ERR_UNSUPPORTED = -4,  /* valid request outside what this build implements */
+  CFD_ERR_NOMEM = -5
+} cfd_status;
+
+/* Which reference program family the context mirrors. */
+typedef enum cfd_family {
+  CFD_FAMILY_CAVITY = 0,   /* lid-driven-cavity-2d/fvm-simple/cavity_fvm.f90 (uniform staggered grid)       */
+  CFD_FAMILY_GENERAL = 1,  /* buoyancy-driven-cavity-2d/buoyancy_cav.f90 + cylinder-heat-conduction-2d vars/serv */
+  CFD_FAMILY_TEACH = 2     /* backward-step-flow-2d/calc.f90 + promod.f90 + general.f90                       */
+} cfd_family;
+
+/* Line ordering of the TDMA sweeps (lisolv, cavity_fvm.f90:62). */
+typedef enum cfd_order {
+  CFD_ORDER_REDBLACK = 0,  /* two colour passes over the S-N lines (north_star's variant; same fixed point)  */
+  CFD_ORDER_SEQUENTIAL = 1 /* the reference's W->E line Gauss-Seidel, bit-comparable debug mode (small grids) */
+} cfd_order;
+
+/* 2-D fields, module vars_mod (cavity_fvm.f90:22-41) / vars (cylin_cond.f90:42-71). */
+typedef enum cfd_field {
+  CFD_U = 0, CFD_V, CFD_P, CFD_PP, CFD_VIS /* = gam */, CFD_DEN, CFD_T, CFD_CP,
+  CFD_AE, CFD_AW, CFD_AN, CFD_AS, CFD_AP, CFD_SU, CFD_SP, CFD_DU, CFD_DV,
+  CFD_FIELD_COUNT
+} cfd_field;
+
+/* 1-D geometry arrays set by setgrid (cavity_fvm.f90:366-414) / grid (buoyancy_cav.f90:28-120). */
+typedef enum cfd_geom {
+  CFD_G_X = 0, CFD_G_XU, CFD_G_SEW, CFD_G_SEWU,          /* length ni */
+  CFD_G_Y, CFD_G_YV, CFD_G_SNS, CFD_G_SNSV,              /* length nj */
+  /* general family extras (cylin_cond.f90:57-61) */
+  CFD_G_XDIF, CFD_G_XCVI, CFD_G_XCVIP, CFD_G_FX, CFD_G_FXM,                         /* length ni */
+  CFD_G_YDIF, CFD_G_YCVR, CFD_G_YCVRS, CFD_G_ARX, CFD_G_ARXJ, CFD_G_ARXJP,
+  CFD_G_R, CFD_G_RMN, CFD_G_SX, CFD_G_SXMN, CFD_G_FV, CFD_G_FVP, CFD_G_FY, CFD_G_FYM, /* length nj */
+  CFD_GEOM_COUNT
+} cfd_geom;
+
+/* Equation slots for urf[] / nswp[] / residuals: nq of module vars (cylin_cond.f90:47). */
+enum { CFD_EQ_U = 0, CFD_EQ_V = 1, CFD_EQ_P = 2, CFD_EQ_T = 3, CFD_EQ_COUNT = 8 };
+
+/*
+ * The literals `program cavity_fvm` sets before its loop (cavity_fvm.f90:519-552), as one struct.
+ * Slab fields (goff, ni_global, halo_w, halo_e) describe an i-slab of a larger grid for multi-GPU runs
+ * (one context per rank); a single-GPU context leaves them 0.
+ */
+typedef struct cfd_config {
+  int family;              /* cfd_family */
+  int ni, nj;              /* local array extents INCLUDING boundary nodes (and halo lines, for a slab) */
+  int iadv;                /* 1 CDS, 2 UDS, 3 hybrid (cavity_fvm.f90:30); 4 power law (general family) */
+  int order;               /* cfd_order */
+  int nswp[CFD_EQ_COUNT];  /* nswpu, nswpv, nswpp, (nsweep(4)) ... */
+  double urf[CFD_EQ_COUNT];/* urfu, urfv, urfp, ... */
+  int ipref, jpref;        /* 1-based GLOBAL indices of the pressure reference cell (cavity_fvm.f90:549-550) */
+  int device;              /* CUDA device ordinal; -1 = the calling thread's current device */
+  int tdma_m;              /* elements per thread in the line solver, 0 = choose */
+  /* slab description */
+  int goff;                /* global i of local line 1, minus 1 */
+  int ni_global;           /* 0 = ni */
+  int halo_w, halo_e;      /* halo lines at the west / east end of the local arrays (0 at a physical wall) */
+  double sew_nim1;         /* value of sew(nim1) of the GLOBAL grid for the stale-scalar quirk of calcv
+                              (cavity_fvm.f90:283); 0 = read it from the local geometry */
+} cfd_config;
+
+/* ---- life cycle ------------------------------------------------------------------------------------- */
+/* replaces array_alloc / array_dealloc (cavity_fvm.f90:432-505): fields are zero-initialised on the device */
+int cfd_create(cfd_ctx** out, const cfd_config* cfg);
+int cfd_destroy(cfd_ctx* ctx);
+const char* cfd_strerror(int status);
+const char* cfd_last_error(void);
+/* Kernels of this context are launched on `cuda_stream` (a cudaStream_t passed as void*); default: stream 0. */
+int cfd_set_stream(cfd_ctx* ctx, void* cuda_stream);
+int cfd_synchronize(cfd_ctx* ctx);
+
+/* ---- data movement (the only host<->device traffic) ------------------------------------------------- */
+/* geometry of setgrid (cavity_fvm.f90:366-414): n doubles, n == ni or nj by id */
+int cfd_set_geometry(cfd_ctx* ctx, int geom_id, const double* host, int n);
+/* field A(ld,nj) host -> device / device -> host; replaces direct access to the module arrays by the driver
+   (initial values cavity_fvm.f90:534-538, output 590-607) */
+int cfd_upload(cfd_ctx* ctx, int field, const double* host, int ld);
+int cfd_download(cfd_ctx* ctx, int field, double* host, int ld);
+/* monitor-point read u(imon,jmon) etc. (cavity_fvm.f90:559-563); LOCAL 1-based indices */
+int cfd_probe(cfd_ctx* ctx, int field, int i, int j, double* value);
+/* raw device view for peer/NCCL halo exchange: base pointer of `field`, doubles per line, number of lines.
+   Line i (local, 1-based) is the contiguous range base[(i-1)*line_stride .. +line_stride). */
+int cfd_field_device_view(cfd_ctx* ctx, int field, void** base, long long* line_stride, int* nlines);
+
+/* diagnostic: the device line layout chosen for this context (nodes per thread, threads per line, padded
+   line length); no counterpart in the reference */
+int cfd_layout_info(cfd_ctx* ctx, int* m, int* t, int* ld);
+
+/* ---- the hot path: one call per reference subroutine -------------------------------------------------- */
+/* calcu (cavity_fvm.f90:92-192): assemble + nswpu line sweeps of u; *resoru receives the residual sum */
+int cfd_calcu(cfd_ctx* ctx, double* resoru);
+/* calcv (cavity_fvm.f90:194-291) */
+int cfd_calcv(cfd_ctx* ctx, double* resorv);
+/* calcp (cavity_fvm.f90:293-355): p' assembly, pp=0, nswpp sweeps, correction of p,u,v */
+int cfd_calcp(cfd_ctx* ctx, double* resorm);
+/* lisolv(istart,jstart,ni,nj,phi) (cavity_fvm.f90:49-82): ONE sweep over the current coefficients */
+int cfd_lisolv(cfd_ctx* ctx, int istart, int jstart, int field);
+/* n passes of the loop body cavity_fvm.f90:554-557 without returning to the host; res[0..2] = resoru,resorv,
+   resorm of the LAST pass (res[3..7] reserved for T, k, eps ...) */
+int cfd_iterate(cfd_ctx* ctx, int n, double res[8]);
+
+/* ---- stage-level entry points (what cfd_calc* are made of; used by the multi-GPU driver, which exchanges
+        halo lines between them).  None of them synchronises or touches the host. ------------------------ */
+int cfd_assemble_u(cfd_ctx* ctx);                       /* cavity_fvm.f90:104-187 */
+int cfd_assemble_v(cfd_ctx* ctx);                       /* cavity_fvm.f90:205-285 */
+int cfd_assemble_p(cfd_ctx* ctx);                       /* cavity_fvm.f90:301-342 */
+/* half sweep over the lines of one colour (0/1), or a full sequential sweep if colour < 0;
+   first != 0 treats phi as zero where the reference has just executed pp(:,:)=0 (cavity_fvm.f90:342) */
+int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first);
+int cfd_correct(cfd_ctx* ctx, const double* ppref_device); /* cavity_fvm.f90:346-354; NULL = pp(ipref,jpref) */
+/* finish the deterministic residual reduction and copy res[0..7] to the host (synchronises) */
+int cfd_residuals(cfd_ctx* ctx, double res[8]);
+/* device address of the 8 packed residual sums (for an NCCL all-reduce) */
+int cfd_residual_device_ptr(cfd_ctx* ctx, void** ptr);
+
+/* ---- explicit / implicit 5-point heat conduction (finite-difference-method/heat-conduction/) ---------- */
+typedef struct cfd_heat_config {
+  int nx, ny;                    /* nodes including the Dirichlet edges */
+  double k, rho, cp;             /* fdm1d_explicit_heat_cond.f90:46 */
+  double xa, xb, ya, yb;
+  double tleft, tright, tbottom, ttop;
+  double dt;
+  double qthr, qval;             /* QDOT (fdm1d_explicit_heat_cond.f90:76-88): qval where x < qthr else 0 */
+  int device;
+  int j_goff, ny_global;         /* j-slab of a larger grid (rows), 0 = whole grid */
+  int halo_s, halo_n;
+} cfd_heat_config;
+typedef struct cfd_heat cfd_heat;
+int cfd_heat_create(cfd_heat** out, const cfd_heat_config* cfg);
+int cfd_heat_destroy(cfd_heat* h);
+int cfd_heat_set_stream(cfd_heat* h, void* cuda_stream);
+int cfd_heat_upload(cfd_heat* h, const double* host, int ld);      /* T(ld,ny) column-major */
+int cfd_heat_download(cfd_heat* h, double* host, int ld);
+/* nsteps passes of the update loop fdm1d_explicit_heat_cond.f90:130-139 with the 5-point operator of
+   fdm2d_steady_heat_cond.f90:171-188 (constant conductivity) */
+int cfd_heat2d_step(cfd_heat* h, int nsteps);
+/* same update evaluated in the restatement's exact operation order with IEEE divides (bit-comparable with
+   oracle/heat_oracle.c; slower -- for parity debugging) */
+int cfd_heat2d_step_exact(cfd_heat* h, int nsteps);
+/* nsteps implicit-Euler steps, locally one-dimensional: the tridiagonal assembly of
+   implicit-time/fdm1d_explicit_heat_cond.f90:122-143 along x then y, batched Thomas (thomas, :147-184) */
+int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps);
+int cfd_heat_device_view(cfd_heat* h, void** cur, long long* row_stride, int* nrows);
+int cfd_heat_synchronize(cfd_heat* h);
+
+/* library/build identification */
+const char* cfd_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CFD_B200_H */

@@ -1,0 +1,191 @@
+"""ctypes front-end to the CPU oracle (oracle/*.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs.  The product package (cfd_b200/) never imports this module.
+
+The oracle restates /root/reference/lid-driven-cavity-2d/fvm-simple/cavity_fvm.f90 and the heat-conduction
+stencils (see the headers of cavity_oracle.c / heat_oracle.c for the file:line map).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_BUILD = os.path.join(_HERE, "_build")
+_dp = C.POINTER(C.c_double)
+
+
+def build(force: bool = False) -> None:
+    """Compile the two oracle libraries with the committed Makefile (gcc only)."""
+    need = force or not all(
+        os.path.exists(os.path.join(_BUILD, n)) for n in ("liboracle.so", "liboracle_fast.so"))
+    if not need:
+        srcs = [os.path.join(_HERE, f) for f in ("cavity_oracle.c", "heat_oracle.c", "general_oracle.c",
+                                                 "teach_oracle.c", "fdcavity_oracle.c", "Makefile")]
+        newest = max(os.path.getmtime(s) for s in srcs if os.path.exists(s))
+        need = newest > min(os.path.getmtime(os.path.join(_BUILD, n))
+                            for n in ("liboracle.so", "liboracle_fast.so"))
+    if need:
+        subprocess.run(["make", "-C", _HERE, "-s", "-B"], check=True)
+
+
+class _CavityStruct(C.Structure):
+    _fields_ = ([("ni", C.c_int), ("nj", C.c_int), ("iadv", C.c_int),
+                 ("nswpu", C.c_int), ("nswpv", C.c_int), ("nswpp", C.c_int),
+                 ("ipref", C.c_int), ("jpref", C.c_int), ("order", C.c_int),
+                 ("urfu", C.c_double), ("urfv", C.c_double), ("urfp", C.c_double),
+                 ("resoru", C.c_double), ("resorv", C.c_double), ("resorm", C.c_double)]
+                + [(n, _dp) for n in ("x", "y", "xu", "yv", "sew", "sns", "sewu", "snsv",
+                                      "u", "v", "p", "pp", "vis", "den",
+                                      "ae", "aw", "an", "as_", "ap", "su", "sp", "du", "dv")])
+
+
+_libs: dict = {}
+
+
+def lib(fast: bool = False) -> C.CDLL:
+    key = "fast" if fast else "ref"
+    if key not in _libs:
+        build()
+        path = os.path.join(_BUILD, "liboracle_fast.so" if fast else "liboracle.so")
+        L = C.CDLL(path)
+        L.orc_cavity_run.restype = C.c_int
+        L.orc_cavity_run.argtypes = [C.POINTER(_CavityStruct), C.c_int, C.c_double, C.c_int, C.c_int, _dp]
+        L.orc_setgrid.argtypes = [C.c_int, C.c_int] + [C.c_double] * 4 + [_dp] * 8
+        L.orc_lisolv.argtypes = [C.POINTER(_CavityStruct), C.c_int, C.c_int, _dp]
+        for n in ("orc_calcu", "orc_calcv", "orc_calcp", "orc_assemble_u", "orc_assemble_v",
+                  "orc_assemble_p", "orc_correct"):
+            getattr(L, n).argtypes = [C.POINTER(_CavityStruct)]
+            getattr(L, n).restype = None
+        L.orc_centred_vel.argtypes = [C.c_int, C.c_int, _dp, _dp, _dp, _dp]
+        L.orc_corner_p.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp]
+        L.orc_heat2d_ftcs.argtypes = [C.c_double] * 14 + [_dp, _dp, C.c_int, C.c_int, C.c_int]
+        L.orc_heat2d_ftcs.restype = None
+        L.orc_heat2d_lod.argtypes = [C.c_double] * 14 + [_dp, C.c_int, C.c_int, C.c_int]
+        L.orc_heat2d_lod.restype = None
+        L.orc_heat1d_explicit.argtypes = ([C.c_double] * 7 + [_dp] + [C.c_double] * 4 + [_dp, _dp, C.c_int, C.c_int])
+        L.orc_heat1d_explicit.restype = C.c_int
+        L.orc_heat1d_implicit.argtypes = L.orc_heat1d_explicit.argtypes
+        L.orc_heat1d_implicit.restype = C.c_int
+        L.orc_thomas.argtypes = [_dp] * 5 + [C.c_int]
+        L.orc_thomas.restype = None
+        L.orc_heat2d_coeffs.argtypes = [_dp] * 4 + [C.c_double] * 2 + [_dp] * 5 + [C.c_int, C.c_int]
+        L.orc_heat2d_coeffs.restype = None
+        _libs[key] = L
+    return _libs[key]
+
+
+def _p(a: np.ndarray):
+    assert a.dtype == np.float64 and a.flags["F_CONTIGUOUS"] or a.ndim == 1
+    return a.ctypes.data_as(_dp)
+
+
+QTHR_REF = float(np.float32(0.1))   # the reference compares x with the default-real literal 0.1
+
+
+class Cavity:
+    """State of `program cavity_fvm` (cavity_fvm.f90:509-552): fields as (ni,nj) Fortran-ordered arrays."""
+
+    FIELDS = ("u", "v", "p", "pp", "vis", "den", "ae", "aw", "an", "as_", "ap", "su", "sp", "du", "dv")
+    GEOM_I = ("x", "xu", "sew", "sewu")
+    GEOM_J = ("y", "yv", "sns", "snsv")
+
+    def __init__(self, nicv=10, njcv=10, reynolds=100.0, iadv=3, order=0, fast=False,
+                 urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3), utop=1.0, rho=1000.0,
+                 xlim=(0.0, 1.0), ylim=(0.0, 1.0)):
+        self.L = lib(fast)
+        self.ni, self.nj = nicv + 2, njcv + 2
+        ni, nj = self.ni, self.nj
+        for n in self.GEOM_I:
+            setattr(self, n, np.zeros(ni))
+        for n in self.GEOM_J:
+            setattr(self, n, np.zeros(nj))
+        for n in self.FIELDS:
+            setattr(self, n, np.zeros((ni, nj), order="F"))
+        self.L.orc_setgrid(nicv, njcv, xlim[0], xlim[1], ylim[0], ylim[1],
+                           _p(self.x), _p(self.y), _p(self.xu), _p(self.yv),
+                           _p(self.sew), _p(self.sns), _p(self.sewu), _p(self.snsv))
+        # cavity_fvm.f90:534-538
+        self.den[:, :] = rho
+        self.vis[:, :] = self.den * utop * (xlim[1] - xlim[0]) / reynolds
+        self.u[1:, nj - 1] = utop
+        self.ipref, self.jpref = ni // 2, nj // 2          # cavity_fvm.f90:549-552 (1-based)
+        self.imon, self.jmon = self.ipref, self.jpref
+        self.s = _CavityStruct(ni=ni, nj=nj, iadv=iadv, nswpu=nswp[0], nswpv=nswp[1], nswpp=nswp[2],
+                               ipref=self.ipref, jpref=self.jpref, order=order,
+                               urfu=urf[0], urfv=urf[1], urfp=urf[2])
+        for n in self.GEOM_I + self.GEOM_J + self.FIELDS:
+            setattr(self.s, n, _p(getattr(self, n)))
+
+    def run(self, maxit=90000, tol=1.0e-10, history=False):
+        hist = np.zeros((maxit, 5)) if history else None
+        n = self.L.orc_cavity_run(C.byref(self.s), maxit, tol, self.imon, self.jmon,
+                                  hist.ctypes.data_as(_dp) if history else None)
+        return (n, hist[:n]) if history else n
+
+    def calcu(self):
+        self.L.orc_calcu(C.byref(self.s)); return self.s.resoru
+
+    def calcv(self):
+        self.L.orc_calcv(C.byref(self.s)); return self.s.resorv
+
+    def calcp(self):
+        self.L.orc_calcp(C.byref(self.s)); return self.s.resorm
+
+    def assemble_u(self):
+        self.L.orc_assemble_u(C.byref(self.s)); return self.s.resoru
+
+    def assemble_v(self):
+        self.L.orc_assemble_v(C.byref(self.s)); return self.s.resorv
+
+    def assemble_p(self):
+        self.L.orc_assemble_p(C.byref(self.s)); return self.s.resorm
+
+    def correct(self):
+        self.L.orc_correct(C.byref(self.s))
+
+    def lisolv(self, istart, jstart, phi):
+        self.L.orc_lisolv(C.byref(self.s), istart, jstart, _p(phi))
+
+    def centred_vel(self):
+        uc = np.zeros_like(self.u); vc = np.zeros_like(self.v)
+        self.L.orc_centred_vel(self.ni, self.nj, _p(self.u), _p(self.v), _p(uc), _p(vc))
+        return uc, vc
+
+    @property
+    def residuals(self):
+        return self.s.resoru, self.s.resorv, self.s.resorm
+
+
+def heat2d_ftcs(tc, nsteps, k=5.0, rho=1.0, cp=1.0, lim=(0.0, 1.0, 0.0, 1.0), tbc=(0.0, 0.0, 0.0, 0.0),
+                dt=None, fo=0.2, qthr=QTHR_REF, qval=1.0e3, fast=False):
+    """nsteps FTCS steps on tc (nx,ny) Fortran-ordered; returns the new field (tc is not modified)."""
+    tc = np.array(tc, dtype=np.float64, order="F", copy=True)
+    nx, ny = tc.shape
+    dx = (lim[1] - lim[0]) / (nx - 1)
+    if dt is None:
+        dt = fo * dx * dx / (k / rho / cp)
+    t = np.zeros_like(tc, order="F")
+    lib(fast).orc_heat2d_ftcs(k, rho, cp, lim[0], lim[1], lim[2], lim[3], tbc[0], tbc[1], tbc[2], tbc[3],
+                              dt, qthr, qval, _p(tc), _p(t), nx, ny, nsteps)
+    return tc
+
+
+def heat2d_lod(tc, nsteps, k=5.0, rho=1.0, cp=1.0, lim=(0.0, 1.0, 0.0, 1.0), tbc=(0.0, 0.0, 0.0, 0.0),
+               dt=1.0e-4, qthr=QTHR_REF, qval=1.0e3, fast=False):
+    tc = np.array(tc, dtype=np.float64, order="F", copy=True)
+    nx, ny = tc.shape
+    lib(fast).orc_heat2d_lod(k, rho, cp, lim[0], lim[1], lim[2], lim[3], tbc[0], tbc[1], tbc[2], tbc[3],
+                             dt, qthr, qval, _p(tc), nx, ny, nsteps)
+    return tc
+
+
+def thomas(a, b, c, d):
+    a, b, c, d = (np.ascontiguousarray(v, dtype=np.float64) for v in (a, b, c, d))
+    x = np.zeros_like(d)
+    lib().orc_thomas(_p(a), _p(b), _p(c), _p(d), _p(x), len(d))
+    return x

@@ -1,0 +1,238 @@
+"""Parity of the CUDA cavity path (through the C ABI) with the CPU oracle.  Bit-exact in sequential-order
+mode (fields; residual sums to 1e-12 because the reduction order differs), 1e-8 relative L-inf on converged
+fields in red/black mode (north_star's bar; observed ~1e-13)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def linf_rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def make_pair(cfd, oracle, nicv, njcv, re=100.0, iadv=3, order="sequential", **kw):
+    o = oracle.Cavity(nicv, njcv, re, iadv=iadv, order=0 if order == "sequential" else 1, **kw)
+    g = cfd.CavityFVM(nicv, njcv, iadv=iadv, order=order, **kw)
+    g.init_lid_driven(reynolds=re)
+    return o, g
+
+
+def randomise(o, g, seed):
+    """Give both sides the same non-trivial fields (smooth + noise), keeping den, vis positive."""
+    rng = np.random.default_rng(seed)
+    ni, nj = o.ni, o.nj
+    for name, scale, base in (("u", 0.3, 0.0), ("v", 0.3, 0.0), ("p", 5.0, 0.0), ("den", 50.0, 1000.0), ("vis", 2.0, 10.0)):
+        a = getattr(o, name)
+        a[:, :] = base + scale * (rng.random((ni, nj)) - 0.5)
+        g.upload(name, a)
+
+
+@pytest.mark.parametrize("shape", [(3, 3), (10, 10), (7, 31), (64, 64), (128, 32), (33, 130), (400, 17)])
+def test_upload_download_roundtrip(cfd, shape):
+    g = cfd.CavityFVM(*shape)
+    rng = np.random.default_rng(1)
+    a = np.asfortranarray(rng.random((g.ni, g.nj)))
+    g.upload("p", a)
+    assert np.array_equal(g.download("p"), a)
+    assert g.probe("p", 2, 3) == a[1, 2]
+    assert g.probe("p", g.ni, g.nj) == a[-1, -1]
+    # leading dimension larger than ni (backward-step allocates (it,jt) >= (ni,nj), control.f90:22-25)
+    big = np.zeros((g.ni + 5, g.nj), order="F")
+    big[: g.ni, :] = a
+    g.upload_ptr("u", big.ctypes.data, g.ni + 5)
+    assert np.array_equal(g.download("u"), a)
+    g.close()
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (64, 64), (128, 32), (33, 130), (3, 3), (200, 257)])
+@pytest.mark.parametrize("iadv", [1, 2, 3])
+def test_assembly_bitwise(cfd, oracle, shape, iadv):
+    o, g = make_pair(cfd, oracle, *shape, iadv=iadv)
+    randomise(o, g, 7 + iadv)
+    # u
+    ru_o = o.assemble_u()
+    g.assemble_u()
+    for n, on in (("ae", "ae"), ("aw", "aw"), ("an", "an"), ("as", "as_"), ("ap", "ap"), ("su", "su"), ("du", "du")):
+        assert np.array_equal(g.download(n), getattr(o, on)), ("u", n)
+    assert abs(g.residuals()[0] - ru_o) <= 1e-12 * abs(ru_o)
+    # v
+    rv_o = o.assemble_v()
+    g.assemble_v()
+    for n, on in (("ae", "ae"), ("aw", "aw"), ("an", "an"), ("as", "as_"), ("ap", "ap"), ("su", "su"), ("dv", "dv")):
+        assert np.array_equal(g.download(n), getattr(o, on)), ("v", n)
+    assert abs(g.residuals()[1] - rv_o) <= 1e-12 * abs(rv_o)
+    # p'
+    rm_o = o.assemble_p()
+    g.assemble_p()
+    for n, on in (("ae", "ae"), ("aw", "aw"), ("an", "an"), ("as", "as_"), ("ap", "ap"), ("su", "su")):
+        assert np.array_equal(g.download(n), getattr(o, on)), ("p", n)
+    assert abs(g.residuals()[2] - rm_o) <= 1e-12 * abs(rm_o)
+    g.close()
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (40, 24), (24, 300)])
+def test_lisolv_sequential_bitwise(cfd, oracle, shape):
+    o, g = make_pair(cfd, oracle, *shape)
+    randomise(o, g, 3)
+    o.assemble_u()
+    g.assemble_u()
+    o.lisolv(3, 2, o.u)
+    g.lisolv(3, 2, "u")
+    assert np.array_equal(g.download("u"), o.u)
+    o.assemble_v()
+    g.assemble_v()
+    o.lisolv(2, 3, o.v)
+    g.lisolv(2, 3, "v")
+    assert np.array_equal(g.download("v"), o.v)
+    g.close()
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (40, 24), (24, 300), (130, 1030), (64, 4096)])
+def test_lisolv_redblack_matches_oracle_redblack(cfd, oracle, shape):
+    o, g = make_pair(cfd, oracle, *shape, order="redblack")
+    randomise(o, g, 5)
+    o.assemble_u()
+    g.assemble_u()
+    o.lisolv(3, 2, o.u)
+    g.lisolv(3, 2, "u")
+    assert linf_rel(g.download("u"), o.u) < 1e-11
+    o.assemble_v()
+    g.assemble_v()
+    o.lisolv(2, 3, o.v)
+    g.lisolv(2, 3, "v")
+    assert linf_rel(g.download("v"), o.v) < 1e-11
+    g.close()
+
+
+@pytest.mark.parametrize("m", [1, 2, 3, 5, 8, 13, 16])
+def test_lisolv_redblack_every_chunk_size(cfd, oracle, m):
+    o = oracle.Cavity(20, 150, 100.0, order=1)
+    g = cfd.CavityFVM(20, 150, order="redblack", tdma_m=m)
+    g.init_lid_driven()
+    assert g.layout["M"] == m
+    randomise(o, g, 11)
+    o.assemble_u()
+    g.assemble_u()
+    o.lisolv(3, 2, o.u)
+    g.lisolv(3, 2, "u")
+    assert linf_rel(g.download("u"), o.u) < 1e-11
+    g.close()
+
+
+def test_default_case_sequential_is_bitwise(cfd, oracle):
+    """BASELINE.json config 1: 10x10 CV, Re=100, to the literal stop rule -> 232 iterations."""
+    o, g = make_pair(cfd, oracle, 10, 10)
+    n_o, hist = o.run(history=True)
+    res = []
+    n_g = 0
+    for it in range(1, 1000):
+        res.append((g.calcu(), g.calcv(), g.calcp()))
+        n_g = it
+        if it in (1, 2, 3, 10, 100):
+            assert g.probe("u", g.imon, g.jmon) == hist[it - 1][3]
+            assert g.probe("v", g.imon, g.jmon) == hist[it - 1][4]
+        if max(res[-1]) < 1e-10:
+            break
+    assert n_g == n_o == 232
+    for name in ("u", "v", "p", "pp"):
+        assert np.array_equal(g.download(name), getattr(o, name)), name
+    r = np.array(res)
+    assert np.all(np.abs(r - hist[:, :3]) <= 1e-9 * np.abs(hist[:, :3]) + 1e-22)
+    g.close()
+
+
+def test_cv32_sequential_count_and_fields(cfd, oracle):
+    o, g = make_pair(cfd, oracle, 32, 32)
+    assert o.run() == 2093
+    assert g.run() == 2093
+    for name in ("u", "v", "p"):
+        assert np.array_equal(g.download(name), getattr(o, name)), name
+    g.close()
+
+
+@pytest.mark.parametrize("cv,re,its_rb", [(10, 100.0, 232), (32, 100.0, 2081)])
+def test_redblack_converges_to_reference_solution(cfd, oracle, cv, re, its_rb):
+    o = oracle.Cavity(cv, cv, re)           # the reference's sequential order
+    o.run()
+    g = cfd.CavityFVM(cv, cv, order="redblack")
+    g.init_lid_driven(reynolds=re)
+    n = g.run()
+    assert abs(n - its_rb) <= 2            # stop test sits on a rounding-level residual sum
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-8, name
+    g.close()
+
+
+@pytest.mark.slow
+def test_cv64_redblack_vs_reference(cfd, oracle):
+    o = oracle.Cavity(64, 64, 100.0, fast=True)
+    o.run()
+    g = cfd.CavityFVM(64, 64, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    n = g.run(check_every=2)
+    assert abs(n - 8214) <= 4
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-8, name
+    g.close()
+
+
+def test_trajectory_512_sequential_bitwise(cfd, oracle):
+    """Fixed-length trajectory at a grid the CPU cannot converge in test time."""
+    o, g = make_pair(cfd, oracle, 512, 512, re=1000.0)
+    n = 4
+    o.run(maxit=n, tol=0.0)
+    res = g.iterate(n)
+    for name in ("u", "v", "p"):
+        assert np.array_equal(g.download(name), getattr(o, name)), name
+    for a, b in zip(res, o.residuals):
+        assert abs(a - b) <= 1e-11 * abs(b)
+    g.close()
+
+
+def test_trajectory_1024_redblack(cfd, oracle):
+    o = oracle.Cavity(1024, 1024, 1000.0, order=1, fast=True)
+    g = cfd.CavityFVM(1024, 1024, order="redblack")
+    g.init_lid_driven(reynolds=1000.0)
+    n = 3
+    o.run(maxit=n, tol=0.0)
+    res = g.iterate(n)
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-9, name
+    for a, b in zip(res, o.residuals):
+        assert abs(a - b) <= 1e-9 * abs(b)
+    g.close()
+
+
+def test_full_size_4096_properties(cfd):
+    """BASELINE.json config 3 size: no CPU answer exists at this size, so check size-independent properties:
+    finite fields, untouched boundaries, p(ipref,jpref) pinned at 0, mass residual falling, and that the
+    C-ABI subroutine path (calcu+calcv+calcp) and cfd_iterate give the same bits."""
+    g = cfd.CavityFVM(4096, 4096, order="redblack")
+    g.init_lid_driven(reynolds=1000.0)
+    r1 = g.iterate(1)
+    r5 = g.iterate(4)
+    u = g.download("u")
+    assert np.isfinite(u).all()
+    assert np.all(u[1:, -1] == 1.0) and np.all(u[:, 0] == 0.0) and np.all(u[0, :] == 0.0)
+    assert g.probe("p", g.ipref, g.jpref) == 0.0
+    assert np.isfinite(r5).all() and r5[2] < r1[2] * 10
+    h = cfd.CavityFVM(4096, 4096, order="redblack")
+    h.init_lid_driven(reynolds=1000.0)
+    for _ in range(5):
+        h.calcu(); h.calcv(); h.calcp()
+    assert np.array_equal(h.download("u"), u)
+    g.close(); h.close()
+
+
+def test_error_paths(cfd):
+    with pytest.raises(cfd.CfdError):
+        cfd.CavityFVM(1, 1)
+    g = cfd.CavityFVM(8, 8)
+    with pytest.raises(cfd.CfdError):
+        g.probe("u", 0, 1)
+    with pytest.raises(cfd.CfdError):
+        g.probe("t", 1, 1)          # field not allocated for this family
+    with pytest.raises(cfd.CfdError):
+        g.lisolv(1, 2, "u")
+    g.close()

@@ -1,0 +1,70 @@
+"""Parity of the CUDA FTCS path with the CPU oracle: bit-exact in `exact` mode, 1e-12 relative per step in the
+production (pre-multiplied, FMA) mode -- the tolerance BASELINE.json:north_star states for explicit FD fields."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def noise(nx, ny, seed=20260001):
+    return np.asfortranarray(np.random.default_rng(seed).random((nx, ny)))
+
+
+@pytest.mark.parametrize("shape", [(3, 3), (5, 4), (66, 34), (130, 257), (1026, 1026)])
+def test_ftcs_exact_mode_bitwise(cfd, oracle, shape):
+    nx, ny = shape
+    t0 = noise(nx, ny)
+    h = cfd.Heat2D(nx, ny, tleft=1.0, tright=2.0, tbottom=3.0, ttop=4.0)
+    h.upload(t0)
+    h.step(3, exact=True)
+    want = oracle.heat2d_ftcs(t0, 3, dt=h.dt, tbc=(1.0, 2.0, 3.0, 4.0))
+    assert np.array_equal(h.download(), want)
+    h.close()
+
+
+@pytest.mark.parametrize("shape", [(66, 34), (1026, 1026), (2050, 514)])
+def test_ftcs_fast_mode_1e12_per_step(cfd, oracle, shape):
+    nx, ny = shape
+    t0 = noise(nx, ny)
+    h = cfd.Heat2D(nx, ny)
+    h.upload(t0)
+    cur = t0
+    for _ in range(4):                 # per-step comparison, restarting the oracle from the GPU state
+        h.step(1)
+        want = oracle.heat2d_ftcs(cur, 1, dt=h.dt)
+        got = h.download()
+        assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+        cur = got
+    h.close()
+
+
+def test_ftcs_reference_setup_source_and_bc(cfd, oracle):
+    """SURVEY 8d input 2 at reduced size: T0 = 0, q = 1e3 where x < 0.1, Dirichlet 0, Fo = 0.2, 100 steps."""
+    nx = ny = 258
+    t0 = np.zeros((nx, ny), order="F")
+    h = cfd.Heat2D(nx, ny)
+    h.upload(t0)
+    h.step(100)
+    want = oracle.heat2d_ftcs(t0, 100, dt=h.dt)
+    got = h.download()
+    assert np.abs(got - want).max() <= 1e-11 * np.abs(want).max()
+    assert got[:, 0].max() == 0.0 and got[0, :].max() == 0.0
+    assert got[2, ny // 2] > 0.0 and got[nx // 2, ny // 2] >= 0.0
+    h.close()
+
+
+def test_ftcs_full_size_eigenmode(cfd):
+    """BASELINE.json config 2 size (16384^2): analytic decay of a discrete eigenmode, 10 steps."""
+    n = 16384
+    x = np.linspace(0.0, 1.0, n)
+    s = np.sin(np.pi * x)
+    s[0] = s[-1] = 0.0
+    t0 = np.asfortranarray(s[:, None] * s[None, :])
+    h = cfd.Heat2D(n, n, qval=0.0)
+    h.upload(t0)
+    h.step(10)
+    got = h.download()
+    dx = 1.0 / (n - 1)
+    lam = 1.0 - 8 * (5.0 * h.dt / dx**2) * np.sin(np.pi * dx / 2) ** 2
+    assert np.abs(got - lam**10 * t0).max() < 1e-12
+    h.close()
