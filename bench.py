@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark of BASELINE.json on B200: SIMPLE outer iterations of the lid-driven cavity
+(Re=1000, 4096^2 control volumes per GPU, red/black line TDMA), reported as cell-updates/s (GLUPS) and
+iterations/s, with the HBM roofline of the dominant kernel and a CPU baseline beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat]
+
+A "step" is one pass of the hot path: calcu + calcv + calcp (cavity_fvm.f90:554-557) over the whole grid.
+For N>1 launch with torch.distributed.run (one rank per GPU); the grid is slab-decomposed along i (weak scaling:
+4096 columns per GPU).  Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+NICV = NJCV = 4096          # BASELINE.json configs[2]
+REYNOLDS = 1000.0
+BYTES_PER_CELL_ITER = 928   # 116 doubles / cell / outer iteration (stored-coefficient algorithm)
+SWEEP_BYTES_PER_CELL = 64   # one TDMA sweep: an,as,ae,aw,ap,su,phi read + phi written
+HEAT_N = 16384              # BASELINE.json configs[1]
+HEAT_BYTES_PER_CELL = 16
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+def cpu_baseline_cavity(budget_s=20.0, nicv=NICV, njcv=NJCV):
+    """The oracle (C restatement, -O3 -march=native, 1 thread like the serial reference) on a bounded sample:
+    whole SIMPLE iterations of the same 4096^2 case until ~budget_s seconds have passed (at least 2)."""
+    from oracle import oracle as orc
+    c = orc.Cavity(nicv, njcv, REYNOLDS, fast=True)
+    c.run(maxit=1, tol=0.0)                       # warm-up iteration (page faults, caches)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        c.run(maxit=1, tol=0.0)
+        n += 1
+        dt = time.perf_counter() - t0
+        if (dt > budget_s and n >= 2) or n >= 50:
+            break
+    glups = nicv * njcv * n / dt / 1e9
+    return {"value": glups, "unit": "GLUPS", "iters_per_s": n / dt, "cores": 1, "kind": "port",
+            "host_cores_available": os.cpu_count(),
+            "sample": f"{n} SIMPLE iterations of the same {nicv}x{njcv} Re={REYNOLDS:g} case after 1 warm-up, "
+                      f"{dt:.1f} s, oracle/cavity_oracle.c gcc -O3 -march=native, 1 thread (the reference is serial; "
+                      "no Fortran compiler on the box, so the reference's own build is unavailable)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (sequential line order) timed on the host cores.  The
+    reference is serial Fortran and cannot be compiled here (no Fortran compiler), so the C restatement in
+    oracle/ stands in ("port").  One step = one SIMPLE iteration; the grid is the full 4096^2 case when the
+    whole run fits a few minutes, else a 1024^2 sample of it (cell-updates/s is the comparable unit)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as orc
+    K, W = args.steps, args.warmup
+    full = (K + W) * 6.5 <= 200.0
+    n = NICV if full else 1024
+    c = orc.Cavity(n, n, REYNOLDS, fast=True)
+    for _ in range(W):
+        c.run(maxit=1, tol=0.0)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        c.run(maxit=1, tol=0.0)
+    dt = time.perf_counter() - t0
+    glups = n * n * K / dt / 1e9
+    sample = (f"{K} SIMPLE iterations on {'the full' if full else 'a'} {n}x{n} grid (Re={REYNOLDS:g}, hybrid, nswp 3/3/3), "
+              "sequential line order, oracle/cavity_oracle.c gcc -O3 -march=native, 1 thread: the reference is a serial "
+              "program and its Fortran sources cannot be built on this box (no Fortran compiler)")
+    out = {"impl": "reference", "metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS",
+           "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": dt / K * 1e3, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "iters_per_s_4096": glups * 1e9 / (NICV * NJCV),
+           "config": {"workload": f"lid-driven cavity FVM SIMPLE Re=1000 {NICV}x{NJCV} CV per GPU (BASELINE.json configs[2])",
+                      "grid_timed": f"{n}x{n}", "order": "sequential (reference)"},
+           "cpu_baseline": {"value": glups, "unit": "GLUPS", "cores": 1, "kind": "port", "sample": sample,
+                            "host_cores_available": os.cpu_count()},
+           "e2e": {"value": glups, "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import cfd_b200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    K, W = args.steps, args.warmup
+    hbm_peak, peak_src = peaks()
+    stream = torch.cuda.Stream()
+
+    if world == 1:
+        solver = cfd_b200.CavityFVM(NICV, NJCV, order="redblack", device=local)
+        solver.set_stream(stream.cuda_stream)
+        solver.init_lid_driven(reynolds=REYNOLDS)
+        step = solver.iterate_async
+        sync_res = solver.residuals
+        ctx0 = solver
+        cells_total = NICV * NJCV
+        par = "single GPU"
+    else:
+        from cfd_b200.dist import SlabCavity
+        solver = SlabCavity(NICV * world, NJCV, reynolds=REYNOLDS, stream=stream)
+        step = solver.iterate_async
+        sync_res = solver.residuals
+        ctx0 = solver.ctx
+        cells_total = NICV * world * NJCV
+        par = f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals"
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            step(1)
+        barrier()
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        l0 = ctx0.launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(K):
+            step(1)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = ctx0.launches - l0
+        clocks = sampler.stop() if rank == 0 else None
+        res = sync_res()
+    if world > 1:
+        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    glups = cells_total * K / (ms * 1e-3) / 1e9
+
+    out = {"metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K,
+           "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic",
+           "iters_per_s": K / (ms * 1e-3),
+           "config": {"workload": f"lid-driven cavity FVM SIMPLE Re=1000, {NICV}x{NJCV} CV per GPU, hybrid scheme, "
+                                  "urf .5/.5/.8, nswp 3/3/3, red/black line TDMA (BASELINE.json configs[2])",
+                      "global_grid": f"{NICV * world}x{NJCV}", "parallelism": par,
+                      "l2": "inputs larger than L2 (1.9 GB of live fields per GPU vs 126 MB L2); no explicit flush",
+                      "line_layout": ctx0.layout},
+           "residuals_last": list(res[:3]), "gpu_launches": int(launches)}
+
+    # ---- roofline of the dominant kernel (the red/black line solver), timed live with CUDA events ---------
+    if rank == 0 or world > 1:
+        pass
+    if world == 1:
+        with torch.cuda.stream(stream):
+            evs = []
+            nprof = 3
+            for _ in range(nprof):
+                solver.assemble_u()
+                for sw in range(3):
+                    for col in (0, 1):
+                        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        a.record(stream)
+                        solver.sweep(3, 2, "u", col)
+                        b.record(stream)
+                        evs.append((a, b))
+                solver.iterate_async(1)
+            torch.cuda.synchronize()
+        t_launch = sum(a.elapsed_time(b) for a, b in evs) / len(evs) * 1e-3
+        cells_launch = (NICV - 1) / 2.0 * NJCV          # u-lines i=3..ni-1, half of them per colour pass
+        achieved = SWEEP_BYTES_PER_CELL * cells_launch / t_launch / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("k_tdma_rb", {}).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        out["roofline"] = {"bound": "hbm", "kernel": "k_tdma_rb (one colour pass of a line sweep)",
+                           "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                           "peak_source": peak_src, "traffic": traffic, "launch_ms": t_launch * 1e3,
+                           "algorithmic_bytes_per_launch": SWEEP_BYTES_PER_CELL * cells_launch,
+                           "whole_iteration": {"algorithmic_bytes_per_cell": BYTES_PER_CELL_ITER,
+                                               "achieved": BYTES_PER_CELL_ITER * glups, "frac": BYTES_PER_CELL_ITER * glups / hbm_peak,
+                                               "frac_of_nominal_8TBs": BYTES_PER_CELL_ITER * glups / 8000.0}}
+
+        # ---- e2e: the drop-in call sequence with HOST arrays (pinned), copies inside the timed region --------
+        ni, nj = solver.ni, solver.nj
+        host = {n: torch.empty((nj, ni), dtype=torch.float64, pin_memory=True) for n in ("u", "v", "p")}
+        for n in host:
+            solver.download_ptr(n, host[n].data_ptr(), ni)
+        Ke = max(3, min(K, 10))
+        torch.cuda.synchronize()
+        with torch.cuda.stream(stream):
+            for it in range(1 + Ke):
+                if it == 1:
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                for n in host:
+                    solver.upload_ptr(n, host[n].data_ptr(), ni)
+                ru, rv, rm = solver.calcu(), solver.calcv(), solver.calcp()
+                for n in host:
+                    solver.download_ptr(n, host[n].data_ptr(), ni)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+        fb = ni * nj * 8
+        out["e2e"] = {"value": NICV * NJCV * Ke / dt / 1e9, "unit": "GLUPS", "h2d_bytes_per_step": 3 * fb,
+                      "d2h_bytes_per_step": 3 * fb + 24, "steps": Ke, "ms_per_step": dt / Ke * 1e3,
+                      "what": "per step: cfd_upload(u,v,p) from pinned host arrays, cfd_calcu, cfd_calcv, cfd_calcp "
+                              "(each returns its residual to the host), cfd_download(u,v,p)"}
+    else:
+        out["e2e"] = solver.e2e(max(3, min(K, 10)))
+        out["roofline"] = None
+
+    out["clocks"] = clocks
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline_cavity(args.cpu_budget)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -56,6 +56,7 @@ SYMBOLS = {
     "cfd_probe": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _dp]),
     "cfd_field_device_view": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
     "cfd_layout_info": (C.c_int, [_vp, _ip, _ip, _ip]),
+    "cfd_launch_count": (C.c_longlong, [_vp]),
     "cfd_calcu": (C.c_int, [_vp, _dp]),
     "cfd_calcv": (C.c_int, [_vp, _dp]),
     "cfd_calcp": (C.c_int, [_vp, _dp]),

@@ -110,6 +110,10 @@ class CavityFVM:
         check(self.lib.cfd_layout_info(self._h, C.byref(m), C.byref(t), C.byref(ld)))
         return dict(M=m.value, T=t.value, LD=ld.value)
 
+    @property
+    def launches(self) -> int:
+        return int(self.lib.cfd_launch_count(self._h))
+
     def set_stream(self, cuda_stream: int):
         check(self.lib.cfd_set_stream(self._h, C.c_void_p(cuda_stream)))
 

@@ -31,7 +31,8 @@ extern "C" const char* cfd_strerror(int s) {
 // ---- layout conversion kernels -----------------------------------------------------------------------
 namespace cfd {
 // column-major image A(ni,nj) (i fastest)  ->  line layout.  One 32x32 tile of (i0, t) per block and k.
-__global__ void __launch_bounds__(256) k_to_line(const Layout L, const double* __restrict__ src, double* __restrict__ dst) {
+__global__ void __launch_bounds__(256) k_to_line(const Layout L, const double* __restrict__ src, double* __restrict__ dst,
+                                                 long long SL, int SK) {
   __shared__ double tile[32][33];
   const int k = blockIdx.z, ib = blockIdx.x * 32, tb = blockIdx.y * 32;
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
@@ -41,15 +42,16 @@ __global__ void __launch_bounds__(256) k_to_line(const Layout L, const double* _
   __syncthreads();
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     const int i0 = ib + r, t = tb + threadIdx.x, j0 = t * L.M + k;
-    if (t < L.T && i0 < L.ni && j0 < L.nj) dst[(size_t)i0 * L.LD + (size_t)k * L.T + t] = tile[threadIdx.x][r];
+    if (t < L.T && i0 < L.ni && j0 < L.nj) dst[(size_t)i0 * SL + (size_t)k * SK + t] = tile[threadIdx.x][r];
   }
 }
-__global__ void __launch_bounds__(256) k_from_line(const Layout L, const double* __restrict__ src, double* __restrict__ dst) {
+__global__ void __launch_bounds__(256) k_from_line(const Layout L, const double* __restrict__ src, double* __restrict__ dst,
+                                                   long long SL, int SK) {
   __shared__ double tile[32][33];
   const int k = blockIdx.z, ib = blockIdx.x * 32, tb = blockIdx.y * 32;
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     const int i0 = ib + r, t = tb + threadIdx.x, j0 = t * L.M + k;
-    tile[r][threadIdx.x] = (t < L.T && i0 < L.ni && j0 < L.nj) ? src[(size_t)i0 * L.LD + (size_t)k * L.T + t] : 0.0;
+    tile[r][threadIdx.x] = (t < L.T && i0 < L.ni && j0 < L.nj) ? src[(size_t)i0 * SL + (size_t)k * SK + t] : 0.0;
   }
   __syncthreads();
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
@@ -59,15 +61,19 @@ __global__ void __launch_bounds__(256) k_from_line(const Layout L, const double*
 }
 }  // namespace cfd
 
-int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst) {
+int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst, int field) {
   dim3 block(32, 8), grid((c->L.ni + 31) / 32, (c->L.T + 31) / 32, c->L.M);
-  k_to_line<<<grid, block, 0, c->stream>>>(c->L, colmajor, dst);
+  const bool cf = cfd_is_coef_field(field);
+  k_to_line<<<grid, block, 0, c->stream>>>(c->L, colmajor, dst, cf ? c->L.cSL : (long long)c->L.LD, cf ? c->L.cSK : c->L.T);
+  ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
 }
-int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor) {
+int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor, int field) {
   dim3 block(32, 8), grid((c->L.ni + 31) / 32, (c->L.T + 31) / 32, c->L.M);
-  k_from_line<<<grid, block, 0, c->stream>>>(c->L, src, colmajor);
+  const bool cf = cfd_is_coef_field(field);
+  k_from_line<<<grid, block, 0, c->stream>>>(c->L, src, colmajor, cf ? c->L.cSL : (long long)c->L.LD, cf ? c->L.cSK : c->L.T);
+  ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
 }
@@ -101,11 +107,14 @@ static int choose_layout(int ni, int nj, int want_m, Layout* L) {
   L->M = bm;
   L->T = bt;
   L->LD = (int)best;
+  L->cSL = 6LL * L->LD;
+  L->cSK = 6 * L->T;
   return CFD_OK;
 }
 
-static const int kCavityFields[] = {CFD_U,  CFD_V,  CFD_P,  CFD_PP, CFD_VIS, CFD_DEN, CFD_AE,
-                                    CFD_AW, CFD_AN, CFD_AS, CFD_AP, CFD_SU,  CFD_DU,  CFD_DV};
+static const int kCavityFields[] = {CFD_U, CFD_V, CFD_P, CFD_PP, CFD_VIS, CFD_DEN, CFD_DU, CFD_DV};
+// order of the six arrays inside the interleaved coefficient block (Layout::cSL/cSK)
+static const int kCoefOrder[6] = {CFD_AN, CFD_AS, CFD_AP, CFD_AE, CFD_AW, CFD_SU};
 
 static bool geom_is_j(int id) {
   switch (id) {
@@ -142,9 +151,12 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   for (auto& f : c->field) f = nullptr;
   for (auto& g : c->geom) g = nullptr;
   c->stage = nullptr;
+  c->coef = nullptr;
   c->partial = nullptr;
   c->res_dev = nullptr;
   c->seq_scratch = nullptr;
+  c->launches = 0;
+  for (auto& g : c->gfast) g = nullptr;
   int want_m = cfg->tdma_m;
   if (want_m == 0) {
     const char* e = getenv("CFD_B200_TDMA_M");
@@ -164,13 +176,29 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     }
     CFD_CUDA(cudaMemset(c->field[f], 0, fbytes));
   }
+  if (cudaMalloc(&c->coef, 6 * fbytes) != cudaSuccess) {
+    cfd_set_error("cudaMalloc of %zu bytes for the coefficient block failed", 6 * fbytes);
+    cfd_destroy(c);
+    return CFD_ERR_NOMEM;
+  }
+  CFD_CUDA(cudaMemset(c->coef, 0, 6 * fbytes));
+  for (int a = 0; a < 6; ++a) c->field[kCoefOrder[a]] = c->coef + (size_t)a * c->L.T;
   for (int g = 0; g < CFD_GEOM_COUNT; ++g) {
     const size_t n = geom_is_j(g) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
     c->geom_host[g].assign(geom_is_j(g) ? c->L.nj : c->L.ni, 0.0);
     CFD_CUDA(cudaMalloc(&c->geom[g], n * sizeof(double)));
     CFD_CUDA(cudaMemset(c->geom[g], 0, n * sizeof(double)));
   }
-  c->max_partials = ((c->L.T + 31) / 32) * ((c->L.ni + 7) / 8);
+  for (int g = 0; g < 8; ++g) {
+    const size_t n = (g >= 4) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
+    CFD_CUDA(cudaMalloc(&c->gfast[g], n * sizeof(double)));
+    CFD_CUDA(cudaMemset(c->gfast[g], 0, n * sizeof(double)));
+  }
+  {
+    const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
+    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0);
+  }
+  c->max_partials = ((c->L.T + 31) / 32) * ((c->L.ni + 3) / 4);
   CFD_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
   CFD_CUDA(cudaMalloc(&c->res_dev, 8 * sizeof(double)));
   CFD_CUDA(cudaMemset(c->res_dev, 0, 8 * sizeof(double)));
@@ -182,8 +210,11 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   if (!c) return CFD_OK;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  for (int a = 0; a < 6; ++a) c->field[kCoefOrder[a]] = nullptr;
+  if (c->coef) cudaFree(c->coef);
   for (auto& f : c->field) if (f) cudaFree(f);
   for (auto& g : c->geom) if (g) cudaFree(g);
+  for (auto& g : c->gfast) if (g) cudaFree(g);
   if (c->stage) cudaFree(c->stage);
   if (c->partial) cudaFree(c->partial);
   if (c->res_dev) cudaFree(c->res_dev);
@@ -220,6 +251,42 @@ extern "C" int cfd_set_geometry(cfd_ctx* c, int id, const double* host, int n) {
     CFD_CUDA(cudaMemcpyAsync(c->geom[id], tmp.data(), tmp.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CFD_CUDA(cudaStreamSynchronize(c->stream));
   }
+  if (id <= CFD_G_SNSV) return cfd_update_fast_geometry(c);
+  return CFD_OK;
+}
+
+// Recompute the reciprocal geometry of the production assembly kernels from the host copies.
+int cfd_update_fast_geometry(cfd_ctx* c) {
+  const int ni = c->L.ni, nj = c->L.nj;
+  auto inv = [](double d) { return d != 0.0 ? 1.0 / d : 0.0; };
+  const std::vector<double>&x = c->geom_host[CFD_G_X], &xu = c->geom_host[CFD_G_XU], &sew = c->geom_host[CFD_G_SEW],
+                     &sewu = c->geom_host[CFD_G_SEWU], &y = c->geom_host[CFD_G_Y], &yv = c->geom_host[CFD_G_YV],
+                     &sns = c->geom_host[CFD_G_SNS], &snsv = c->geom_host[CFD_G_SNSV];
+  std::vector<double> bi[4], bj[4];
+  for (auto& v : bi) v.assign((size_t)ni + 2, 0.0);
+  for (auto& v : bj) v.assign((size_t)c->L.LD, 0.0);
+  for (int i = 0; i < ni; ++i) {
+    if (i + 1 < ni) {
+      bi[0][i] = inv(xu[i + 1] - xu[i]);
+      bi[1][i] = inv(x[i + 1] - x[i]);
+    }
+    bi[2][i] = inv(sew[i]);
+    bi[3][i] = inv(sewu[i]);
+  }
+  for (int j = 0; j < nj; ++j) {
+    const int q = lpos(j, c->L.M, c->L.T);
+    if (j + 1 < nj) {
+      bj[0][q] = inv(y[j + 1] - y[j]);
+      bj[1][q] = inv(yv[j + 1] - yv[j]);
+    }
+    bj[2][q] = inv(sns[j]);
+    bj[3][q] = inv(snsv[j]);
+  }
+  for (int g = 0; g < 4; ++g) {
+    CFD_CUDA(cudaMemcpyAsync(c->gfast[g], bi[g].data(), bi[g].size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CFD_CUDA(cudaMemcpyAsync(c->gfast[4 + g], bj[g].data(), bj[g].size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  }
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
   return CFD_OK;
 }
 
@@ -250,7 +317,7 @@ extern "C" int cfd_upload(cfd_ctx* c, int field, const double* host, int ld) {
   if ((rc = ensure_stage(c))) return rc;
   CFD_CUDA(cudaMemcpy2DAsync(c->stage, (size_t)c->L.ni * sizeof(double), host, (size_t)ld * sizeof(double),
                              (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyHostToDevice, c->stream));
-  if ((rc = cfd_launch_to_line_layout(c, c->stage, c->field[field]))) return rc;
+  if ((rc = cfd_launch_to_line_layout(c, c->stage, c->field[field], field))) return rc;
   CFD_CUDA(cudaStreamSynchronize(c->stream));
   return CFD_OK;
 }
@@ -262,7 +329,7 @@ extern "C" int cfd_download(cfd_ctx* c, int field, double* host, int ld) {
   CFD_REQUIRE(ld >= c->L.ni, "ld < ni");
   CFD_CUDA(cudaSetDevice(c->device));
   if ((rc = ensure_stage(c))) return rc;
-  if ((rc = cfd_launch_from_line_layout(c, c->field[field], c->stage))) return rc;
+  if ((rc = cfd_launch_from_line_layout(c, c->field[field], c->stage, field))) return rc;
   CFD_CUDA(cudaMemcpy2DAsync(host, (size_t)ld * sizeof(double), c->stage, (size_t)c->L.ni * sizeof(double),
                              (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyDeviceToHost, c->stream));
   CFD_CUDA(cudaStreamSynchronize(c->stream));
@@ -285,10 +352,12 @@ extern "C" int cfd_field_device_view(cfd_ctx* c, int field, void** base, long lo
   int rc = check_field(c, field);
   if (rc) return rc;
   if (base) *base = c->field[field];
-  if (line_stride) *line_stride = c->L.LD;
+  if (line_stride) *line_stride = cfd_is_coef_field(field) ? c->L.cSL : (long long)c->L.LD;
   if (nlines) *nlines = c->L.ni;
   return CFD_OK;
 }
+
+extern "C" long long cfd_launch_count(cfd_ctx* c) { return c ? c->launches : -1; }
 
 extern "C" int cfd_layout_info(cfd_ctx* c, int* m, int* t, int* ld) {
   CFD_REQUIRE(c, "null context");

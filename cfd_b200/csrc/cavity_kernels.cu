@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(256) k_assemble_u(const CavParams P) {
     const double* pW = P.p + (long long)(i0 - 1) * LD;
     const double* pC = pW + LD;
     const long long out = (long long)i0 * LD;
+    const long long cout = (long long)i0 * P.L.cSL;
     // i-geometry (1-based i = i0+1): sewu(i), xu(i+1)-xu(i), xu(i)-xu(i-1), sew(i), sew(i-1)
     const double sewu_i = __ldg(P.sewu + i0);
     const double dxe = __ldg(P.xu + i0 + 1) - __ldg(P.xu + i0);
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(256) k_assemble_u(const CavParams P) {
       lc.fetch(wvC, vC, k);
       if (j0 >= P.jlo && j0 <= P.jhi) {
         const int q = lc.pos(k);
+        const int cq = k * P.L.cSK + t;
         const double u_w = __ldg(uW + q), u_e = __ldg(uE + q);
         const double den_ww = __ldg(dWW + q), den_e = __ldg(dE + q);
         const double p_w = __ldg(pW + q), p_c = __ldg(pC + q);
@@ -173,12 +175,12 @@ __global__ void __launch_bounds__(256) k_assemble_u(const CavParams P) {
         racc += fabs(resor);
         AP = AP / urfu;
         SU = SU + (1 - urfu) * AP * wu.c;
-        P.ae[out + q] = AE;
-        P.aw[out + q] = AW;
-        P.an[out + q] = AN;
-        P.as[out + q] = AS;
-        P.ap[out + q] = AP;
-        P.su[out + q] = SU;
+        P.ae[cout + cq] = AE;
+        P.aw[cout + cq] = AW;
+        P.an[cout + cq] = AN;
+        P.as[cout + cq] = AS;
+        P.ap[cout + cq] = AP;
+        P.su[cout + cq] = SU;
         P.dout[out + q] = 0.5 * (stale + stale) / AP;
       }
       LineCursor::shift(wu);
@@ -218,6 +220,7 @@ __global__ void __launch_bounds__(256) k_assemble_v(const CavParams P) {
     const double* sE = sC + LD;
     const double* pC = P.p + (long long)i0 * LD;
     const long long out = (long long)i0 * LD;
+    const long long cout = (long long)i0 * P.L.cSL;
     // i-geometry (i = i0+1): sew(i), x(i+1)-x(i), x(i)-x(i-1)
     const double sew_i = __ldg(P.sew + i0);
     const double dxe = __ldg(P.x + i0 + 1) - __ldg(P.x + i0);
@@ -256,6 +259,7 @@ __global__ void __launch_bounds__(256) k_assemble_v(const CavParams P) {
       lc.fetch(wsns, P.snsL, k);
       if (j0 >= P.jlo && j0 <= P.jhi) {
         const int q = lc.pos(k);
+        const int cq = k * P.L.cSK + t;
         const double v_w = __ldg(vW + q), v_e = __ldg(vE + q);
         const double snsv_j = __ldg(P.snsvL + q);
         const double areae = snsv_j, areaw = snsv_j, arean = sew_i, areas = sew_i;
@@ -296,12 +300,12 @@ __global__ void __launch_bounds__(256) k_assemble_v(const CavParams P) {
         racc += fabs(resor);
         AP = AP / urfv;
         SU = SU + (1.0 - urfv) * AP * wv.c;
-        P.ae[out + q] = AE;
-        P.aw[out + q] = AW;
-        P.an[out + q] = AN;
-        P.as[out + q] = AS;
-        P.ap[out + q] = AP;
-        P.su[out + q] = SU;
+        P.ae[cout + cq] = AE;
+        P.aw[cout + cq] = AW;
+        P.an[cout + cq] = AN;
+        P.as[cout + cq] = AS;
+        P.ap[cout + cq] = AP;
+        P.su[cout + cq] = SU;
         P.dout[out + q] = 0.5 * (stale + stale) / AP;
       }
       den_mm = wdC.m;
@@ -343,6 +347,7 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
     const double* duE = duC + LD;
     const double* dvC = P.dv_in + (long long)i0 * LD;
     const long long out = (long long)i0 * LD;
+    const long long cout = (long long)i0 * P.L.cSL;
     const double sew_i = __ldg(P.sew + i0);
     Win3 wd, wv, wdv;
     lc.init(wd, dC);
@@ -355,6 +360,7 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
       lc.fetch(wdv, dvC, k);
       if (j0 >= P.jlo && j0 <= P.jhi) {
         const int q = lc.pos(k);
+        const int cq = k * P.L.cSK + t;
         const double den_w = __ldg(dW + q), den_e = __ldg(dE + q);
         const double u_c = __ldg(uC + q), u_e = __ldg(uE + q);
         const double du_c = __ldg(duC + q), du_e = __ldg(duE + q);
@@ -372,12 +378,12 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
         const double ce = ge * areae, cw = gw * areaw, cn = gn * arean, cs = gs * areas;
         const double smp = ce - cw + cn - cs;
         racc += fabs(smp);
-        P.ae[out + q] = AE;
-        P.aw[out + q] = AW;
-        P.an[out + q] = AN;
-        P.as[out + q] = AS;
-        P.ap[out + q] = AE + AW + AN + AS - 0.0;
-        P.su[out + q] = -smp;
+        P.ae[cout + cq] = AE;
+        P.aw[cout + cq] = AW;
+        P.an[cout + cq] = AN;
+        P.as[cout + cq] = AS;
+        P.ap[cout + cq] = AE + AW + AN + AS - 0.0;
+        P.su[cout + cq] = -smp;
       }
       LineCursor::shift(wd);
       LineCursor::shift(wv);
@@ -482,23 +488,38 @@ static void fill_common(const cfd_ctx* c, CavParams& P) {
 
 static const int BX = 32, BY = 8;
 
-template <typename K>
-static int launch_assemble(cfd_ctx* c, K kernel, CavParams& P, int eq) {
+// which: 0 = u, 1 = v, 2 = p'
+static int launch_assemble(cfd_ctx* c, int which, CavParams& P, int eq) {
   const int nlines = P.ib - P.ia + 1;
   if (nlines <= 0) {   // a slab that owns none of this equation's lines still publishes a zero residual
-    cudaMemsetAsync(c->res_dev + eq, 0, sizeof(double), c->stream);
+    CFD_CUDA(cudaMemsetAsync(c->res_dev + eq, 0, sizeof(double), c->stream));
     return CFD_OK;
   }
-  dim3 block(BX, BY), grid((c->L.T + BX - 1) / BX, (nlines + BY - 1) / BY);
+  const bool fast = !c->exact_assembly && which < 2;
+  const int by = fast ? 4 : BY;
+  dim3 block(BX, by), grid((c->L.T + BX - 1) / BX, (nlines + by - 1) / by);
   const int nblocks = grid.x * grid.y;
   if (nblocks > c->max_partials) {
     cfd_set_error("residual partial buffer too small (%d > %d)", nblocks, c->max_partials);
     return CFD_ERR_INVALID;
   }
   P.partial = c->partial + (size_t)eq * c->max_partials;
-  kernel<<<grid, block, 0, c->stream>>>(P);
-  CFD_CUDA(cudaGetLastError());
+  if (fast) {
+    int rc = cfd_launch_assemble_fast(c, which, P, grid, block);
+    if (rc) return rc;
+  } else {
+    if (which == 0) {
+      k_assemble_u<<<grid, block, 0, c->stream>>>(P);
+    } else if (which == 1) {
+      k_assemble_v<<<grid, block, 0, c->stream>>>(P);
+    } else {
+      k_assemble_p<<<grid, block, 0, c->stream>>>(P);
+    }
+    ++c->launches;
+    CFD_CUDA(cudaGetLastError());
+  }
   k_reduce_partials<<<1, 1024, 0, c->stream>>>(P.partial, nblocks, c->res_dev + eq);
+  ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
 }
@@ -513,7 +534,7 @@ int cfd_launch_assemble_u(cfd_ctx* c) {
   P.urf = c->cfg.urf[CFD_EQ_U];
   P.stale_area = c->geom_host[CFD_G_SNS][c->L.nj - 2];   // sns(njm1)
   P.dout = c->field[CFD_DU];
-  return launch_assemble(c, k_assemble_u, P, CFD_EQ_U);
+  return launch_assemble(c, 0, P, CFD_EQ_U);
 }
 
 int cfd_launch_assemble_v(cfd_ctx* c) {
@@ -530,7 +551,7 @@ int cfd_launch_assemble_v(cfd_ctx* c) {
     P.stale_area = c->geom_host[CFD_G_SEW][NI - 2 - c->cfg.goff];   // sew(nim1)
   }
   P.dout = c->field[CFD_DV];
-  return launch_assemble(c, k_assemble_v, P, CFD_EQ_V);
+  return launch_assemble(c, 1, P, CFD_EQ_V);
 }
 
 int cfd_launch_assemble_p(cfd_ctx* c) {
@@ -541,7 +562,7 @@ int cfd_launch_assemble_p(cfd_ctx* c) {
   P.jlo = 1;
   P.jhi = c->L.nj - 2;
   P.dout = nullptr;
-  return launch_assemble(c, k_assemble_p, P, CFD_EQ_P);
+  return launch_assemble(c, 2, P, CFD_EQ_P);
 }
 
 int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev) {
@@ -573,12 +594,14 @@ int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev) {
   const int nlines = P.ib - P.ia + 1;
   dim3 block(BX, BY), grid((c->L.T + BX - 1) / BX, (nlines + BY - 1) / BY);
   k_correct<<<grid, block, 0, c->stream>>>(P);
+  ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
 }
 
 int cfd_launch_reduce_partials(cfd_ctx* c, int eq, int nblocks) {
   k_reduce_partials<<<1, 1024, 0, c->stream>>>(c->partial + (size_t)eq * c->max_partials, nblocks, c->res_dev + eq);
+  ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
 }

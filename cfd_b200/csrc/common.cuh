@@ -25,6 +25,11 @@ struct Layout {
   int ni, nj;   // logical extents (lines, nodes per line)
   int M, T;     // nodes per thread, threads per line (T multiple of 32)
   int LD;       // T*M >= nj
+  // The six coefficient arrays of one equation (an, as, ap, ae, aw, su -- in that order) are interleaved so that
+  // the line solver can fetch "node k of every thread, all six arrays" of a line as ONE contiguous 6*T block:
+  //   coefficient a, line i0, node (k,t)  at  coef + i0*cSL + k*cSK + a*T + t,   cSL = 6*LD, cSK = 6*T.
+  long long cSL;
+  int cSK;
 };
 
 __host__ __device__ __forceinline__ int lpos(int j0, int M, int T) { return (j0 % M) * T + (j0 / M); }
@@ -45,6 +50,19 @@ struct CavParams {
   const double *x, *xu, *sew, *sewu;
   const double *yL, *yvL, *snsL, *snsvL;
   double* partial;       // one residual partial per block
+};
+
+// Reciprocals of the 1-D geometry for the production assembly kernels (cavity_fast_kernels.cu); 0 where the
+// denominator is 0 (never read there).  by-i arrays natural order, by-j arrays in line layout.
+struct FastGeom {
+  const double *rdxu;    // 1/(xu(i+1)-xu(i))
+  const double *rdx;     // 1/(x(i+1)-x(i))
+  const double *rsew;    // 1/sew(i)
+  const double *rsewu;   // 1/sewu(i)
+  const double *rdyL;    // 1/(y(j+1)-y(j))
+  const double *rdyvL;   // 1/(yv(j+1)-yv(j))
+  const double *rsnsL;   // 1/sns(j)
+  const double *rsnsvL;  // 1/snsv(j)
 };
 
 struct SweepParams {
@@ -85,7 +103,9 @@ struct cfd_ctx {
   cfd::Layout L;
   int device;
   cudaStream_t stream;
-  double* field[CFD_FIELD_COUNT];   // line layout, ni*LD doubles each (allocated on demand by family)
+  double* field[CFD_FIELD_COUNT];   // line layout, ni*LD doubles each (allocated on demand by family);
+                                    // AN,AS,AP,AE,AW,SU point into `coef` (interleaved, see Layout)
+  double* coef;                     // 6*ni*LD doubles
   double* geom[CFD_GEOM_COUNT];     // by-i: natural (ni doubles); by-j: line layout (LD doubles)
   std::vector<double> geom_host[CFD_GEOM_COUNT];
   double* stage;                    // ni*nj staging buffer for upload/download (column-major image)
@@ -93,7 +113,9 @@ struct cfd_ctx {
   int max_partials;
   double* res_dev;                  // 8 packed residual sums
   double* seq_scratch;              // sequential-order debug sweep: forward-elimination arrays
-  int resid_pending[CFD_EQ_COUNT];  // number of partials waiting to be folded per equation
+  double* gfast[8];                 // FastGeom arrays (device)
+  bool exact_assembly;              // bit-exact assembly kernels (sequential-order mode, or CFD_B200_EXACT_ASSEMBLY=1)
+  long long launches;               // kernels launched by this context so far (cfd_launch_count)
 };
 
 // kernels / launchers implemented across the .cu files (all asynchronous on ctx->stream)
@@ -103,6 +125,11 @@ int cfd_launch_assemble_p(cfd_ctx* c);
 int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev);
 int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first);
 int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int first);
-int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst);
-int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor);
+int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst, int field);
+int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor, int field);
+static inline bool cfd_is_coef_field(int f) {
+  return f == CFD_AE || f == CFD_AW || f == CFD_AN || f == CFD_AS || f == CFD_AP || f == CFD_SU;
+}
 int cfd_launch_reduce_partials(cfd_ctx* c, int eq, int nblocks);
+int cfd_launch_assemble_fast(cfd_ctx* c, int which, cfd::CavParams& P, dim3 grid, dim3 block);
+int cfd_update_fast_geometry(cfd_ctx* c);

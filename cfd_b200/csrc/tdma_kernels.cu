@@ -21,143 +21,381 @@ namespace cfd {
 // reciprocal for the red/black solver (not bit-matched to the reference by construction)
 __device__ __forceinline__ double rcp(double x) { return 1.0 / x; }
 
+// Ask the memory system to pull `bytes` (multiple of 16) starting at `p` (16-byte aligned) into L2.  One
+// instruction per array line: the next line of this block streams from HBM while the current one is solved.
+__device__ __forceinline__ void l2_prefetch(const void* p, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
+// Persistent: gridDim.x blocks (about one per SM, register-limited) walk over the lines of one colour.
 template <int M, int BMAX>
 __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
   extern __shared__ double sh[];
   const int T = P.L.T;
   const long long LD = P.L.LD;
   const int t = threadIdx.x, ly = threadIdx.y, LPB = blockDim.y;
-  const int line = blockIdx.x * LPB + ly;
-  const bool valid = line < P.nlines;
-  const int i0 = P.i_first + (valid ? line : 0) * P.i_step;
   const int nth = LPB * T;
   // shared arrays: two PCR buffers of (l,u,r)
   double* bufA = sh;
   double* bufB = sh + 3 * nth;
   const int sidx = ly * T + t;
-
-  const long long o = (long long)i0 * LD;
-  const double* an = P.an + o;
-  const double* as = P.as + o;
-  const double* ap = P.ap + o;
-  const double* ae = P.ae + o;
-  const double* aw = P.aw + o;
-  const double* su = P.su + o;
-  double* phi = P.phi + o;
-  const double* phiE = phi + LD;
-  const double* phiW = phi - LD;
   const bool zeroE = P.first && (P.first_colour == 0 || P.i_step == 1);
   const bool zeroW = P.first && (P.first_colour == 0) && P.i_step != 1;
-
-  double ca[M], cc[M], cf[M];
   const int j0base = t * M;
-  // ---- load + forward elimination inside the chunk (spike cf couples to the previous chunk's last node)
-  {
-    double a[M], b[M], d[M];
-#pragma unroll
-    for (int k = 0; k < M; ++k) {
-      const int j0 = j0base + k, q = k * T + t;
-      const bool act = valid && j0 >= P.jlo && j0 <= P.jhi;
-      if (act) {
-        a[k] = __ldg(an + q);
-        b[k] = __ldg(as + q);
-        d[k] = __ldg(ap + q);
-        const double e = zeroE ? 0.0 : phiE[q];
-        const double w = zeroW ? 0.0 : phiW[q];
-        cc[k] = fma(__ldg(ae + q), e, fma(__ldg(aw + q), w, __ldg(su + q)));
-      } else {
-        a[k] = 0.0;
-        b[k] = 0.0;
-        d[k] = 1.0;
-        cc[k] = (valid && j0 < P.L.nj && !(P.first)) ? phi[q] : 0.0;
+  const unsigned line_bytes = (unsigned)(LD * sizeof(double));
+
+  for (int base = blockIdx.x * LPB; base < P.nlines; base += gridDim.x * LPB) {
+    const int line = base + ly;
+    const bool valid = line < P.nlines;
+    const int i0 = P.i_first + (valid ? line : 0) * P.i_step;
+    const long long o = (long long)i0 * LD;
+    // ---- L2 prefetch of the line this thread group will solve next
+    {
+      const int nline = line + gridDim.x * LPB;
+      if (nline < P.nlines && t < 8) {
+        const long long ni0 = P.i_first + nline * P.i_step;
+        const double* src = t < 6 ? P.an + ni0 * P.L.cSL + (long long)t * LD
+                                  : (t == 6 ? P.phi + (ni0 + 1) * LD : P.phi + (ni0 - 1) * LD);
+        if (!(P.first && t >= 6 && (zeroE || zeroW))) l2_prefetch(src, line_bytes);
       }
     }
+    const long long oc = (long long)i0 * P.L.cSL;
+    const double* an = P.an + oc;
+    const double* as = P.as + oc;
+    const double* ap = P.ap + oc;
+    const double* ae = P.ae + oc;
+    const double* aw = P.aw + oc;
+    const double* su = P.su + oc;
+    double* phi = P.phi + o;
+    const double* phiE = phi + LD;
+    const double* phiW = phi - LD;
+
+    double ca[M], cc[M], cf[M];
+    // ---- load + forward elimination inside the chunk (spike cf couples to the previous chunk's last node)
     {
-      const double inv = rcp(d[0]);
-      ca[0] = a[0] * inv;
-      cc[0] = cc[0] * inv;
-      cf[0] = b[0] * inv;
-    }
+      double a[M], b[M], d[M];
 #pragma unroll
-    for (int k = 1; k < M; ++k) {
-      const double inv = rcp(fma(-b[k], ca[k - 1], d[k]));
-      ca[k] = a[k] * inv;
-      cc[k] = fma(b[k], cc[k - 1], cc[k]) * inv;
-      cf[k] = b[k] * cf[k - 1] * inv;
-    }
-  }
-  // ---- backward elimination onto the chunk's last node: x_k = cc_k + cf_k*x_prev + ca_k*x_last  (k < M-1)
+      for (int k = 0; k < M; ++k) {
+        const int j0 = j0base + k, q = k * T + t;
+        const bool act = valid && j0 >= P.jlo && j0 <= P.jhi;
+        if (act) {
+          const int cq = k * P.L.cSK + t;
+          a[k] = __ldg(an + cq);
+          b[k] = __ldg(as + cq);
+          d[k] = __ldg(ap + cq);
+          const double e = zeroE ? 0.0 : __ldg(phiE + q);
+          const double w = zeroW ? 0.0 : __ldg(phiW + q);
+          cc[k] = fma(__ldg(ae + cq), e, fma(__ldg(aw + cq), w, __ldg(su + cq)));
+        } else {
+          a[k] = 0.0;
+          b[k] = 0.0;
+          d[k] = 1.0;
+          cc[k] = (valid && j0 < P.L.nj && !(P.first)) ? __ldg(phi + q) : 0.0;
+        }
+      }
+      {
+        const double inv = rcp(d[0]);
+        ca[0] = a[0] * inv;
+        cc[0] = cc[0] * inv;
+        cf[0] = b[0] * inv;
+      }
 #pragma unroll
-  for (int k = M - 3; k >= 0; --k) {
-    cc[k] = fma(ca[k], cc[k + 1], cc[k]);
-    cf[k] = fma(ca[k], cf[k + 1], cf[k]);
-    ca[k] = ca[k] * ca[k + 1];
-  }
-  // ---- reduced system over chunk-last nodes: x_t = l*x_{t-1} + u*x_{t+1} + r
-  double l, u, r;
-  if (M == 1) {
-    l = cf[0];
-    u = ca[0];
-    r = cc[0];
-  } else {
-    bufB[sidx] = cc[0];
-    bufB[nth + sidx] = cf[0];
-    bufB[2 * nth + sidx] = ca[0];
+      for (int k = 1; k < M; ++k) {
+        const double inv = rcp(fma(-b[k], ca[k - 1], d[k]));
+        ca[k] = a[k] * inv;
+        cc[k] = fma(b[k], cc[k - 1], cc[k]) * inv;
+        cf[k] = b[k] * cf[k - 1] * inv;
+      }
+    }
+    // ---- backward elimination onto the chunk's last node: x_k = cc_k + cf_k*x_prev + ca_k*x_last  (k < M-1)
+#pragma unroll
+    for (int k = M - 3; k >= 0; --k) {
+      cc[k] = fma(ca[k], cc[k + 1], cc[k]);
+      cf[k] = fma(ca[k], cf[k + 1], cf[k]);
+      ca[k] = ca[k] * ca[k + 1];
+    }
+    // ---- reduced system over chunk-last nodes: x_t = l*x_{t-1} + u*x_{t+1} + r
+    double l, u, r;
+    if (M == 1) {
+      l = cf[0];
+      u = ca[0];
+      r = cc[0];
+    } else {
+      bufB[sidx] = cc[0];
+      bufB[nth + sidx] = cf[0];
+      bufB[2 * nth + sidx] = ca[0];
+      __syncthreads();
+      double ncc = 0.0, ncf = 0.0, ng = 0.0;
+      if (t + 1 < T) {
+        ncc = bufB[sidx + 1];
+        ncf = bufB[nth + sidx + 1];
+        ng = bufB[2 * nth + sidx + 1];
+      }
+      const double inv = rcp(fma(-ca[M - 1], ncf, 1.0));
+      l = cf[M - 1] * inv;
+      u = ca[M - 1] * ng * inv;
+      r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
+    }
+    double* cur = bufA;
+    double* nxt = bufB;
+    cur[sidx] = l;
+    cur[nth + sidx] = u;
+    cur[2 * nth + sidx] = r;
     __syncthreads();
-    double ncc = 0.0, ncf = 0.0, ng = 0.0;
-    if (t + 1 < T) {
-      ncc = bufB[sidx + 1];
-      ncf = bufB[nth + sidx + 1];
-      ng = bufB[2 * nth + sidx + 1];
+    // ---- parallel cyclic reduction
+    for (int s = 1; s < T; s <<= 1) {
+      double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
+      if (t - s >= 0) {
+        lm = cur[sidx - s];
+        um = cur[nth + sidx - s];
+        rm = cur[2 * nth + sidx - s];
+      }
+      if (t + s < T) {
+        lp = cur[sidx + s];
+        up = cur[nth + sidx + s];
+        rp = cur[2 * nth + sidx + s];
+      }
+      const double inv = rcp(fma(-l, um, fma(-u, lp, 1.0)));
+      r = fma(l, rm, fma(u, rp, r)) * inv;
+      l = l * lm * inv;
+      u = u * up * inv;
+      nxt[sidx] = l;
+      nxt[nth + sidx] = u;
+      nxt[2 * nth + sidx] = r;
+      __syncthreads();
+      double* tmp = cur;
+      cur = nxt;
+      nxt = tmp;
     }
-    const double inv = rcp(fma(-ca[M - 1], ncf, 1.0));
-    l = cf[M - 1] * inv;
-    u = ca[M - 1] * ng * inv;
-    r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
+    const double xe = r;
+    const double xp = (t > 0) ? cur[2 * nth + sidx - 1] : 0.0;
+    // ---- back-substitute and store
+    if (valid) {
+#pragma unroll
+      for (int k = 0; k < M; ++k) {
+        const int j0 = j0base + k, q = k * T + t;
+        if (j0 >= P.jlo && j0 <= P.jhi) {
+          const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
+          phi[q] = xk;
+        }
+      }
+    }
+    __syncthreads();   // the shared buffers are reused by the next line
   }
-  double* cur = bufA;
-  double* nxt = bufB;
-  cur[sidx] = l;
-  cur[nth + sidx] = u;
-  cur[2 * nth + sidx] = r;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// TMA-staged line solver (production path for long lines).
+//
+// Same algorithm as k_tdma_rb, but the operands never pass through load registers: an extra producer warp
+// streams the line as M "slices" (node k of every thread: one contiguous 6*T block of the interleaved
+// coefficients plus the two neighbour-phi slices) into a shared-memory ring with cp.async.bulk (TMA) and
+// mbarriers, running ahead of the T consumer threads by up to S slices -- also across line boundaries, so HBM
+// keeps streaming while the consumers are in the backward / cyclic-reduction / store phases of the previous
+// line.  One persistent block per SM.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_1d(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void consumer_sync(int nthreads) {
+  asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+}
+
+template <int M, int BMAX>
+__global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const int S) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int T = P.L.T;
+  const long long LD = P.L.LD;
+  const int tid = threadIdx.x;
+  // carve shared memory: [ring S*8*T doubles][pcr 6*T doubles][full S][empty S]
+  double* ring = reinterpret_cast<double*>(smem_raw);
+  double* bufA = ring + (size_t)S * 8 * T;
+  double* bufB = bufA + 3 * T;
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(bufB + 3 * T);
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S);
+  const int ncw = T / 32;   // consumer warps
+  const bool zeroE = P.first && (P.first_colour == 0 || P.i_step == 1);
+  const bool zeroW = P.first && (P.first_colour == 0) && P.i_step != 1;
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, ncw);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
   __syncthreads();
-  // ---- parallel cyclic reduction
-  for (int s = 1; s < T; s <<= 1) {
-    double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
-    if (t - s >= 0) {
-      lm = cur[sidx - s];
-      um = cur[nth + sidx - s];
-      rm = cur[2 * nth + sidx - s];
+
+  if (tid >= T) {
+    // ---------------- producer warp: one elected thread issues the bulk copies -------------------------
+    if (tid == T) {
+      const unsigned slice_bytes = (unsigned)(T * sizeof(double));
+      const unsigned tx = slice_bytes * (6u + (zeroE ? 0u : 1u) + (zeroW ? 0u : 1u));
+      unsigned it = 0;
+      for (int line = blockIdx.x; line < P.nlines; line += gridDim.x) {
+        const long long i0 = P.i_first + (long long)line * P.i_step;
+        const double* csrc = P.an + i0 * P.L.cSL;       // an is array 0 of the interleaved block
+        const double* esrc = P.phi + (i0 + 1) * LD;
+        const double* wsrc = P.phi + (i0 - 1) * LD;
+        for (int k = 0; k < M; ++k, ++it) {
+          const unsigned s = it % (unsigned)S, ph = (it / (unsigned)S) & 1u;
+          mbar_wait(empty0 + 8 * s, ph ^ 1u);
+          const unsigned fb = full0 + 8 * s;
+          const unsigned dst = smem_u32(ring + (size_t)s * 8 * T);
+          mbar_expect_tx(fb, tx);
+          tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, 6 * slice_bytes, fb);
+          if (!zeroE) tma_load_1d(dst + 6 * slice_bytes, esrc + (size_t)k * T, slice_bytes, fb);
+          if (!zeroW) tma_load_1d(dst + 7 * slice_bytes, wsrc + (size_t)k * T, slice_bytes, fb);
+        }
+      }
     }
-    if (t + s < T) {
-      lp = cur[sidx + s];
-      up = cur[nth + sidx + s];
-      rp = cur[2 * nth + sidx + s];
-    }
-    const double inv = rcp(fma(-l, um, fma(-u, lp, 1.0)));
-    r = fma(l, rm, fma(u, rp, r)) * inv;
-    l = l * lm * inv;
-    u = u * up * inv;
-    nxt[sidx] = l;
-    nxt[nth + sidx] = u;
-    nxt[2 * nth + sidx] = r;
-    __syncthreads();
-    double* tmp = cur;
-    cur = nxt;
-    nxt = tmp;
+    return;
   }
-  const double xe = r;
-  const double xp = (t > 0) ? cur[2 * nth + sidx - 1] : 0.0;
-  // ---- back-substitute and store
-  if (valid) {
+
+  // ---------------- consumers ---------------------------------------------------------------------------
+  const int t = tid, lane = tid & 31;
+  const int j0base = t * M;
+  const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.L.nj - 1, M, T);
+  unsigned it = 0;
+  double bS = 0.0, bN = 0.0;   // Dirichlet end values phi(i, jstart-1), phi(i, nj) of the current line
+  if (!P.first && (int)blockIdx.x < P.nlines) {
+    const double* ph = P.phi + (P.i_first + (long long)blockIdx.x * P.i_step) * LD;
+    bS = __ldg(ph + q_s);
+    bN = __ldg(ph + q_n);
+  }
+  for (int line = blockIdx.x; line < P.nlines; line += gridDim.x) {
+    const long long i0 = P.i_first + (long long)line * P.i_step;
+    double* phi = P.phi + i0 * LD;
+    // end values of the NEXT line, fetched a whole line ahead
+    double bS_next = 0.0, bN_next = 0.0;
+    if (!P.first && line + (int)gridDim.x < P.nlines) {
+      const double* ph = phi + (long long)gridDim.x * P.i_step * LD;
+      bS_next = __ldg(ph + q_s);
+      bN_next = __ldg(ph + q_n);
+    }
+    double ca[M], cc[M], cf[M];
+#pragma unroll
+    for (int k = 0; k < M; ++k, ++it) {
+      const unsigned s = it % (unsigned)S, ph = (it / (unsigned)S) & 1u;
+      mbar_wait(full0 + 8 * s, ph);
+      const double* sl = ring + (size_t)s * 8 * T + t;
+      double a = sl[0], b = sl[T], d = sl[2 * T];
+      double c = sl[5 * T];
+      if (!zeroW) c = fma(sl[4 * T], sl[7 * T], c);
+      if (!zeroE) c = fma(sl[3 * T], sl[6 * T], c);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      const int j0 = j0base + k;
+      if (!(j0 >= P.jlo && j0 <= P.jhi)) {
+        a = 0.0;
+        b = 0.0;
+        d = 1.0;
+        c = (j0 == P.jlo - 1) ? bS : ((j0 == P.L.nj - 1) ? bN : 0.0);
+      }
+      if (k == 0) {
+        const double inv = rcp(d);
+        ca[0] = a * inv;
+        cc[0] = c * inv;
+        cf[0] = b * inv;
+      } else {
+        const double inv = rcp(fma(-b, ca[k > 0 ? k - 1 : 0], d));
+        ca[k] = a * inv;
+        cc[k] = fma(b, cc[k > 0 ? k - 1 : 0], c) * inv;
+        cf[k] = b * cf[k > 0 ? k - 1 : 0] * inv;
+      }
+    }
+#pragma unroll
+    for (int k = M - 3; k >= 0; --k) {
+      cc[k] = fma(ca[k], cc[k + 1], cc[k]);
+      cf[k] = fma(ca[k], cf[k + 1], cf[k]);
+      ca[k] = ca[k] * ca[k + 1];
+    }
+    double l, u, r;
+    if (M == 1) {
+      l = cf[0];
+      u = ca[0];
+      r = cc[0];
+    } else {
+      bufB[t] = cc[0];
+      bufB[T + t] = cf[0];
+      bufB[2 * T + t] = ca[0];
+      consumer_sync(T);
+      double ncc = 0.0, ncf = 0.0, ng = 0.0;
+      if (t + 1 < T) {
+        ncc = bufB[t + 1];
+        ncf = bufB[T + t + 1];
+        ng = bufB[2 * T + t + 1];
+      }
+      const double inv = rcp(fma(-ca[M - 1], ncf, 1.0));
+      l = cf[M - 1] * inv;
+      u = ca[M - 1] * ng * inv;
+      r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
+    }
+    double* cur = bufA;
+    double* nxt = bufB;
+    cur[t] = l;
+    cur[T + t] = u;
+    cur[2 * T + t] = r;
+    consumer_sync(T);
+    for (int sft = 1; sft < T; sft <<= 1) {
+      double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
+      if (t - sft >= 0) {
+        lm = cur[t - sft];
+        um = cur[T + t - sft];
+        rm = cur[2 * T + t - sft];
+      }
+      if (t + sft < T) {
+        lp = cur[t + sft];
+        up = cur[T + t + sft];
+        rp = cur[2 * T + t + sft];
+      }
+      const double inv = rcp(fma(-l, um, fma(-u, lp, 1.0)));
+      r = fma(l, rm, fma(u, rp, r)) * inv;
+      l = l * lm * inv;
+      u = u * up * inv;
+      nxt[t] = l;
+      nxt[T + t] = u;
+      nxt[2 * T + t] = r;
+      consumer_sync(T);
+      double* tmp = cur;
+      cur = nxt;
+      nxt = tmp;
+    }
+    const double xe = r;
+    const double xp = (t > 0) ? cur[2 * T + t - 1] : 0.0;
 #pragma unroll
     for (int k = 0; k < M; ++k) {
-      const int j0 = j0base + k, q = k * T + t;
+      const int j0 = j0base + k;
       if (j0 >= P.jlo && j0 <= P.jhi) {
         const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
-        phi[q] = xk;
+        phi[k * T + t] = xk;
       }
     }
+    bS = bS_next;
+    bN = bN_next;
+    consumer_sync(T);   // PCR buffers are reused by the next line
   }
 }
 
@@ -191,10 +429,11 @@ __global__ void __launch_bounds__(1024, 1) k_tdma_seq(const SeqParams P) {
       if (j0 >= P.jlo && j0 <= P.jhi) {
         const double e = P.first ? 0.0 : phiC[LD + q];
         const double w = phiC[q - LD];
-        sa[j0] = P.an[o + q];
-        sb[j0] = P.as[o + q];
-        sd[j0] = P.ap[o + q];
-        sc[j0] = __dadd_rn(__dadd_rn(__dmul_rn(P.ae[o + q], e), __dmul_rn(P.aw[o + q], w)), P.su[o + q]);
+        const long long cq = (long long)i0 * P.L.cSL + (long long)(j0 % M) * P.L.cSK + (j0 / M);
+        sa[j0] = P.an[cq];
+        sb[j0] = P.as[cq];
+        sd[j0] = P.ap[cq];
+        sc[j0] = __dadd_rn(__dadd_rn(__dmul_rn(P.ae[cq], e), __dmul_rn(P.aw[cq], w)), P.su[cq]);
       }
     }
     __syncthreads();
@@ -222,14 +461,38 @@ __global__ void __launch_bounds__(1024, 1) k_tdma_seq(const SeqParams P) {
 
 // ---- launch tables -------------------------------------------------------------------------------------
 template <int M>
+static int launch_tma_m(cfd_ctx* c, const SweepParams& P, int nblocks, int S, size_t smem) {
+  const int nthreads = P.L.T + 32;
+  cudaError_t e = cudaSuccess;
+  if (nthreads <= 352) {
+    e = cudaFuncSetAttribute(k_tdma_tma<M, 352>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_tdma_tma<M, 352><<<nblocks, nthreads, smem, c->stream>>>(P, S);
+  } else if (nthreads <= 672) {
+    e = cudaFuncSetAttribute(k_tdma_tma<M, 672>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_tdma_tma<M, 672><<<nblocks, nthreads, smem, c->stream>>>(P, S);
+  } else {
+    e = cudaFuncSetAttribute(k_tdma_tma<M, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_tdma_tma<M, 1024><<<nblocks, nthreads, smem, c->stream>>>(P, S);
+  }
+  ++c->launches;
+  return e == cudaSuccess ? CFD_OK : CFD_ERR_CUDA;
+}
+
+template <int M>
 static int launch_rb_m(cfd_ctx* c, const SweepParams& P, int nblocks, dim3 block, size_t smem) {
   const int nthreads = block.x * block.y;
-  if (nthreads <= 384) {
+  if (nthreads <= 320) {
+    k_tdma_rb<M, 320><<<nblocks, block, smem, c->stream>>>(P);
+    ++c->launches;
+  } else if (nthreads <= 384) {
     k_tdma_rb<M, 384><<<nblocks, block, smem, c->stream>>>(P);
+    ++c->launches;
   } else if (nthreads <= 640) {
     k_tdma_rb<M, 640><<<nblocks, block, smem, c->stream>>>(P);
+    ++c->launches;
   } else {
     k_tdma_rb<M, 1024><<<nblocks, block, smem, c->stream>>>(P);
+    ++c->launches;
   }
   return CFD_OK;
 }
@@ -264,10 +527,53 @@ int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int col
   P.su = c->field[CFD_SU];
   P.phi = phi;
   const int T = c->L.T;
+  static int num_sms = 0;
+  if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device));
+  static int use_tma = -1;
+  if (use_tma < 0) {
+    const char* e = getenv("CFD_B200_TDMA_TMA");
+    use_tma = e ? atoi(e) : 1;
+  }
+  if (use_tma && T >= 128 && T + 32 <= 1024) {
+    // TMA-staged persistent kernel: ring of S slices (8*T doubles each), S a power of two
+    const size_t stage = (size_t)8 * T * sizeof(double), pcr = (size_t)6 * T * sizeof(double);
+    int S = 16;
+    const char* es = getenv("CFD_B200_TDMA_STAGES");
+    if (es && atoi(es) > 0) S = atoi(es);
+    while (S > 1 && S * stage + pcr + 2 * S * 8 > 200 * 1024) S >>= 1;
+    const size_t smem = S * stage + pcr + 2 * (size_t)S * 8;
+    const int nblocks = P.nlines < num_sms ? P.nlines : num_sms;
+    int rc = CFD_OK;
+    switch (c->L.M) {
+#define CFD_CASE(m) \
+  case m:           \
+    rc = launch_tma_m<m>(c, P, nblocks, S, smem); \
+    break;
+      CFD_CASE(1) CFD_CASE(2) CFD_CASE(3) CFD_CASE(4) CFD_CASE(5) CFD_CASE(6) CFD_CASE(7) CFD_CASE(8)
+      CFD_CASE(9) CFD_CASE(10) CFD_CASE(11) CFD_CASE(12) CFD_CASE(13) CFD_CASE(14) CFD_CASE(15) CFD_CASE(16)
+#undef CFD_CASE
+      default:
+        cfd_set_error("unsupported M=%d", c->L.M);
+        return CFD_ERR_INVALID;
+    }
+    if (rc) {
+      cfd_set_error("k_tdma_tma: cudaFuncSetAttribute(%zu bytes of shared memory) failed", smem);
+      return rc;
+    }
+    CFD_CUDA(cudaGetLastError());
+    return CFD_OK;
+  }
   int lpb = 256 / T;
   if (lpb < 1) lpb = 1;
   dim3 block(T, lpb);
-  const int nblocks = (P.nlines + lpb - 1) / lpb;
+  int nblocks = (P.nlines + lpb - 1) / lpb;
+  {
+    // persistent grid: one block per SM (the chunk arrays leave room for only one), each walking over lines
+    int per_sm = (T * lpb <= 256) ? 2 : 1;
+    const char* e = getenv("CFD_B200_TDMA_BLOCKS_PER_SM");
+    if (e && atoi(e) > 0) per_sm = atoi(e);
+    if (nblocks > num_sms * per_sm) nblocks = num_sms * per_sm;
+  }
   const size_t smem = (size_t)6 * lpb * T * sizeof(double);
   switch (c->L.M) {
 #define CFD_CASE(m) \
@@ -316,6 +622,7 @@ int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int fi
     attr_set = true;
   }
   k_tdma_seq<<<1, 1024, smem, c->stream>>>(P);
+  ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
 }

@@ -113,6 +113,8 @@ int cfd_field_device_view(cfd_ctx* ctx, int field, void** base, long long* line_
 /* diagnostic: the device line layout chosen for this context (nodes per thread, threads per line, padded
    line length); no counterpart in the reference */
 int cfd_layout_info(cfd_ctx* ctx, int* m, int* t, int* ld);
+/* diagnostic: number of CUDA kernels this context has launched since cfd_create (bench.py's gpu_launches) */
+long long cfd_launch_count(cfd_ctx* ctx);
 
 /* ---- the hot path: one call per reference subroutine -------------------------------------------------- */
 /* calcu (cavity_fvm.f90:92-192): assemble + nswpu line sweeps of u; *resoru receives the residual sum */

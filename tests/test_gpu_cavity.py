@@ -71,6 +71,31 @@ def test_assembly_bitwise(cfd, oracle, shape, iadv):
     g.close()
 
 
+@pytest.mark.parametrize("shape", [(10, 10), (64, 64), (33, 130), (3, 3), (200, 257)])
+@pytest.mark.parametrize("iadv", [1, 2, 3])
+def test_production_assembly_matches_oracle(cfd, oracle, shape, iadv):
+    """Red/black mode uses the reciprocal/FMA assembly kernels: coefficients agree to rounding (1e-13 of the
+    largest entry), not bitwise."""
+    o, g = make_pair(cfd, oracle, *shape, iadv=iadv, order="redblack")
+    randomise(o, g, 17 + iadv)
+
+    def close(n, on):
+        a, b = g.download(n), getattr(o, on)
+        assert np.abs(a - b).max() <= 1e-13 * max(np.abs(b).max(), 1e-300), (n, np.abs(a - b).max())
+
+    ru_o = o.assemble_u()
+    g.assemble_u()
+    for n, on in (("ae", "ae"), ("aw", "aw"), ("an", "an"), ("as", "as_"), ("ap", "ap"), ("su", "su"), ("du", "du")):
+        close(n, on)
+    assert abs(g.residuals()[0] - ru_o) <= 1e-11 * abs(ru_o)
+    rv_o = o.assemble_v()
+    g.assemble_v()
+    for n, on in (("ae", "ae"), ("aw", "aw"), ("an", "an"), ("as", "as_"), ("ap", "ap"), ("su", "su"), ("dv", "dv")):
+        close(n, on)
+    assert abs(g.residuals()[1] - rv_o) <= 1e-11 * abs(rv_o)
+    g.close()
+
+
 @pytest.mark.parametrize("shape", [(10, 10), (40, 24), (24, 300)])
 def test_lisolv_sequential_bitwise(cfd, oracle, shape):
     o, g = make_pair(cfd, oracle, *shape)
@@ -223,6 +248,21 @@ def test_full_size_4096_properties(cfd):
         h.calcu(); h.calcv(); h.calcp()
     assert np.array_equal(h.download("u"), u)
     g.close(); h.close()
+
+
+@pytest.mark.slow
+def test_full_size_4096_two_iterations_vs_oracle(cfd, oracle):
+    """The same two outer iterations on the CPU oracle (red/black order) at the full 4096^2 size."""
+    o = oracle.Cavity(4096, 4096, 1000.0, order=1, fast=True)
+    o.run(maxit=2, tol=0.0)
+    g = cfd.CavityFVM(4096, 4096, order="redblack")
+    g.init_lid_driven(reynolds=1000.0)
+    res = g.iterate(2)
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-9, name
+    for a, b in zip(res, o.residuals):
+        assert abs(a - b) <= 1e-9 * abs(b)
+    g.close()
 
 
 def test_error_paths(cfd):
