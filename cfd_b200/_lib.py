@@ -53,6 +53,7 @@ SYMBOLS = {
     "cfd_set_geometry": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_upload_noalloc": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_probe": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _dp]),
     "cfd_field_device_view": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
     "cfd_layout_info": (C.c_int, [_vp, _ip, _ip, _ip]),

@@ -139,6 +139,13 @@ class CavityFVM:
         assert a.shape == (self.ni, self.nj), (a.shape, self.ni, self.nj)
         check(self.lib.cfd_upload(self._h, FIELD_ID[name], a.ctypes.data_as(C.c_void_p), a.shape[0]))
 
+    def upload_noalloc(self, name: str, a: np.ndarray):
+        """cfd_upload_noalloc: same effect as `upload`, staged in the library's built-in 32 MiB device buffer
+        (no cudaMalloc at run time); grids up to ni*nj = 4 194 304 nodes."""
+        a = np.asfortranarray(a, dtype=np.float64)
+        assert a.shape == (self.ni, self.nj), (a.shape, self.ni, self.nj)
+        check(self.lib.cfd_upload_noalloc(self._h, FIELD_ID[name], a.ctypes.data_as(C.c_void_p), a.shape[0]))
+
     def upload_ptr(self, name: str, ptr: int, ld: int):
         check(self.lib.cfd_upload(self._h, FIELD_ID[name], C.c_void_p(ptr), ld))
 

@@ -322,6 +322,47 @@ extern "C" int cfd_upload(cfd_ctx* c, int field, const double* host, int ld) {
   return CFD_OK;
 }
 
+// ---- upload for callers that must not allocate ----------------------------------------------------------
+// cfd_upload() stages the host image in a device buffer that it cudaMalloc's on its first call.  Some hosts of
+// this library cannot tolerate that: a driver that has already handed all free HBM to its own pool (an
+// OpenACC / CUDA-Fortran runtime arena, an MPS client at its memory limit) gets an out-of-memory error from any
+// later cudaMalloc, and a time-stepping loop that re-uploads boundary data every iteration (the `boundary()` /
+// `gamsor()` hooks of buoyancy_cav.f90) must not hit cudaMalloc's device-wide synchronisation in the middle of
+// the loop.  For them the staging area below is part of the library image itself: it exists on every GPU that
+// loads libcfd_b200.so, from load until the process exits, and nothing is allocated or freed at run time.
+#define CFD_NOALLOC_MAX_DOUBLES (4u * 1024u * 1024u) /* 32 MiB: grids up to ni*nj = 4 194 304 nodes (2048 x 2048) */
+static __device__ __align__(256) double g_noalloc_stage[CFD_NOALLOC_MAX_DOUBLES];
+// Device addresses of g_noalloc_stage, one per device ordinal.  In host code the symbol itself is only a
+// stand-in; the address a kernel or a memcpy may use comes from cudaGetSymbolAddress with that device current.
+static double* g_noalloc_addr[64] = {nullptr};
+
+extern "C" int cfd_upload_noalloc(cfd_ctx* c, int field, const double* host, int ld) {
+  CFD_REQUIRE(c && host, "null argument");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(ld >= c->L.ni, "ld < ni");
+  const size_t n = (size_t)c->L.ni * (size_t)c->L.nj;
+  if (n > (size_t)CFD_NOALLOC_MAX_DOUBLES) {
+    cfd_set_error("cfd_upload_noalloc: ni*nj = %zu nodes exceeds the built-in staging area of %u doubles (32 MiB); "
+                  "use cfd_upload for larger grids", n, CFD_NOALLOC_MAX_DOUBLES);
+    return CFD_ERR_INVALID;
+  }
+  CFD_REQUIRE(c->device >= 0 && c->device < 64, "device ordinal outside the supported range 0..63");
+  CFD_CUDA(cudaSetDevice(c->device));
+  if (!g_noalloc_addr[c->device]) {   // one-time set-up on this device (do it before any stream capture)
+    double* p = nullptr;
+    CFD_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_stage));
+    g_noalloc_addr[c->device] = p;
+  }
+  double* stage = g_noalloc_addr[c->device];
+  // the image is overwritten completely (ni*nj doubles), so nothing left by an earlier call is ever read
+  CFD_CUDA(cudaMemcpy2DAsync(stage, (size_t)c->L.ni * sizeof(double), host, (size_t)ld * sizeof(double),
+                             (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyHostToDevice, c->stream));
+  if ((rc = cfd_launch_to_line_layout(c, stage, c->field[field], field))) return rc;
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
 extern "C" int cfd_download(cfd_ctx* c, int field, double* host, int ld) {
   CFD_REQUIRE(c && host, "null argument");
   int rc = check_field(c, field);

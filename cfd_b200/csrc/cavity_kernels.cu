@@ -346,8 +346,7 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
     const double* duC = P.du_in + (long long)i0 * LD;
     const double* duE = duC + LD;
     const double* dvC = P.dv_in + (long long)i0 * LD;
-    const long long out = (long long)i0 * LD;
-    const long long cout = (long long)i0 * P.L.cSL;
+        const long long cout = (long long)i0 * P.L.cSL;
     const double sew_i = __ldg(P.sew + i0);
     Win3 wd, wv, wdv;
     lc.init(wd, dC);

@@ -104,6 +104,18 @@ int cfd_set_geometry(cfd_ctx* ctx, int geom_id, const double* host, int n);
    (initial values cavity_fvm.f90:534-538, output 590-607) */
 int cfd_upload(cfd_ctx* ctx, int field, const double* host, int ld);
 int cfd_download(cfd_ctx* ctx, int field, double* host, int ld);
+/*
+ * cfd_upload without any run-time allocation.  (No counterpart in the reference: it exists for hosts of this
+ * library that cannot call cudaMalloc after start-up -- a driver whose own runtime has claimed all free device
+ * memory, or a solver loop that re-uploads boundary/source data every iteration and cannot afford cudaMalloc's
+ * device-wide synchronisation.)  Same arguments and result as cfd_upload, but the column-major image is staged
+ * in a 32 MiB buffer that is part of the library image on every GPU that loads it, so it calls no cudaMalloc /
+ * cudaFree.  Limit: ni*nj <= 4 194 304 nodes (e.g. 2048 x 2048); larger grids get CFD_ERR_INVALID with a
+ * message -- use cfd_upload.  The first call on each device looks the buffer's device address up
+ * (cudaGetSymbolAddress); make that first call before any stream capture.  All contexts on one GPU share
+ * the buffer: calls that overlap on the GPU (different streams or host threads) race, so issue them one at a time.
+ */
+int cfd_upload_noalloc(cfd_ctx* ctx, int field, const double* host, int ld);
 /* monitor-point read u(imon,jmon) etc. (cavity_fvm.f90:559-563); LOCAL 1-based indices */
 int cfd_probe(cfd_ctx* ctx, int field, int i, int j, double* value);
 /* raw device view for peer/NCCL halo exchange: base pointer of `field`, doubles per line, number of lines.
