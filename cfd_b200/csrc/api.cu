@@ -107,6 +107,7 @@ static int choose_layout(int ni, int nj, int want_m, Layout* L) {
   L->M = bm;
   L->T = bt;
   L->LD = (int)best;
+  L->nc = 6;
   L->cSL = 6LL * L->LD;
   L->cSK = 6 * L->T;
   return CFD_OK;
@@ -114,7 +115,8 @@ static int choose_layout(int ni, int nj, int want_m, Layout* L) {
 
 static const int kCavityFields[] = {CFD_U, CFD_V, CFD_P, CFD_PP, CFD_VIS, CFD_DEN, CFD_DU, CFD_DV};
 // order of the six arrays inside the interleaved coefficient block (Layout::cSL/cSK)
-static const int kCoefOrder[6] = {CFD_AN, CFD_AS, CFD_AP, CFD_AE, CFD_AW, CFD_SU};
+static const int kCoefOrder6[6] = {CFD_AN, CFD_AS, CFD_AP, CFD_AE, CFD_AW, CFD_SU};
+static const int kCoefOrder5[5] = {CFD_AN, CFD_AS, CFD_AE, CFD_AW, CFD_SU};
 
 static bool geom_is_j(int id) {
   switch (id) {
@@ -167,6 +169,13 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     cfd_set_error("nj=%d too long for the line layout (max %d)", cfg->nj, 1024 * CFD_MAX_M);
     return CFD_ERR_UNSUPPORTED;
   }
+  {
+    const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
+    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0);
+    c->L.nc = c->exact_assembly ? 6 : 5;
+    c->L.cSL = (long long)c->L.nc * c->L.LD;
+    c->L.cSK = c->L.nc * c->L.T;
+  }
   const size_t fbytes = (size_t)c->L.ni * c->L.LD * sizeof(double);
   for (int f : kCavityFields) {
     if (cudaMalloc(&c->field[f], fbytes) != cudaSuccess) {
@@ -176,13 +185,14 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     }
     CFD_CUDA(cudaMemset(c->field[f], 0, fbytes));
   }
-  if (cudaMalloc(&c->coef, 6 * fbytes) != cudaSuccess) {
-    cfd_set_error("cudaMalloc of %zu bytes for the coefficient block failed", 6 * fbytes);
+  if (cudaMalloc(&c->coef, c->L.nc * fbytes) != cudaSuccess) {
+    cfd_set_error("cudaMalloc of %zu bytes for the coefficient block failed", c->L.nc * fbytes);
     cfd_destroy(c);
     return CFD_ERR_NOMEM;
   }
-  CFD_CUDA(cudaMemset(c->coef, 0, 6 * fbytes));
-  for (int a = 0; a < 6; ++a) c->field[kCoefOrder[a]] = c->coef + (size_t)a * c->L.T;
+  CFD_CUDA(cudaMemset(c->coef, 0, c->L.nc * fbytes));
+  for (int a = 0; a < c->L.nc; ++a)
+    c->field[c->L.nc == 6 ? kCoefOrder6[a] : kCoefOrder5[a]] = c->coef + (size_t)a * c->L.T;
   for (int g = 0; g < CFD_GEOM_COUNT; ++g) {
     const size_t n = geom_is_j(g) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
     c->geom_host[g].assign(geom_is_j(g) ? c->L.nj : c->L.ni, 0.0);
@@ -193,10 +203,6 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     const size_t n = (g >= 4) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
     CFD_CUDA(cudaMalloc(&c->gfast[g], n * sizeof(double)));
     CFD_CUDA(cudaMemset(c->gfast[g], 0, n * sizeof(double)));
-  }
-  {
-    const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
-    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0);
   }
   c->max_partials = ((c->L.T + 31) / 32) * ((c->L.ni + 3) / 4);
   CFD_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
@@ -210,7 +216,7 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   if (!c) return CFD_OK;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
-  for (int a = 0; a < 6; ++a) c->field[kCoefOrder[a]] = nullptr;
+  for (int a = 0; a < 6; ++a) c->field[kCoefOrder6[a]] = nullptr;
   if (c->coef) cudaFree(c->coef);
   for (auto& f : c->field) if (f) cudaFree(f);
   for (auto& g : c->geom) if (g) cudaFree(g);

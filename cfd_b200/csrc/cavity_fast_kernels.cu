@@ -13,6 +13,14 @@
 namespace cfd {
 
 __device__ __forceinline__ double fmax2(double a, double b) { return a > b ? a : b; }
+// hardware reciprocal seed + two Newton steps (about 1 ulp); ap is a sum of positive coefficients
+__device__ __forceinline__ double rcp_fast(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = fma(fma(-x, r, 1.0), r, r);
+  r = fma(fma(-x, r, 1.0), r, r);
+  return r;
+}
 
 __device__ __forceinline__ void block_sum_to_fast(double v, double* partial) {
   __shared__ double wsum[32];
@@ -142,13 +150,13 @@ __global__ void __launch_bounds__(128, 4) k_assemble_u_fast(const CavParams P, c
         racc += fabs(resor);
         AP = AP * r_urf;
         SU = fma(omu * AP, u_c, SU);
-        P.ae[cout + cq] = AE;
-        P.aw[cout + cq] = AW;
-        P.an[cout + cq] = AN;
-        P.as[cout + cq] = AS;
-        P.ap[cout + cq] = AP;
-        P.su[cout + cq] = SU;
-        P.dout[out + q] = stale / AP;
+        const double rAP = rcp_fast(AP);
+        P.ae[cout + cq] = AE * rAP;
+        P.aw[cout + cq] = AW * rAP;
+        P.an[cout + cq] = AN * rAP;
+        P.as[cout + cq] = AS * rAP;
+        P.su[cout + cq] = SU * rAP;
+        P.dout[out + q] = stale * rAP;
       }
       u_s = u_c; u_c = u_n;
       dW_m = dW_c; dW_c = dW_p;
@@ -249,13 +257,13 @@ __global__ void __launch_bounds__(128, 4) k_assemble_v_fast(const CavParams P, c
         racc += fabs(resor);
         AP = AP * r_urf;
         SU = fma(omu * AP, v_c, SU);
-        P.ae[cout + cq] = AE;
-        P.aw[cout + cq] = AW;
-        P.an[cout + cq] = AN;
-        P.as[cout + cq] = AS;
-        P.ap[cout + cq] = AP;
-        P.su[cout + cq] = SU;
-        P.dout[out + q] = stale / AP;
+        const double rAP = rcp_fast(AP);
+        P.ae[cout + cq] = AE * rAP;
+        P.aw[cout + cq] = AW * rAP;
+        P.an[cout + cq] = AN * rAP;
+        P.as[cout + cq] = AS * rAP;
+        P.su[cout + cq] = SU * rAP;
+        P.dout[out + q] = stale * rAP;
       }
       uC_m = uC_c; uE_m = uE_c;
       dW_m = dW_c; dE_m = dE_c;

@@ -377,12 +377,22 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
         const double ce = ge * areae, cw = gw * areaw, cn = gn * arean, cs = gs * areas;
         const double smp = ce - cw + cn - cs;
         racc += fabs(smp);
-        P.ae[cout + cq] = AE;
-        P.aw[cout + cq] = AW;
-        P.an[cout + cq] = AN;
-        P.as[cout + cq] = AS;
-        P.ap[cout + cq] = AE + AW + AN + AS - 0.0;
-        P.su[cout + cq] = -smp;
+        if (P.L.nc == 6) {
+          P.ae[cout + cq] = AE;
+          P.aw[cout + cq] = AW;
+          P.an[cout + cq] = AN;
+          P.as[cout + cq] = AS;
+          P.ap[cout + cq] = AE + AW + AN + AS - 0.0;
+          P.su[cout + cq] = -smp;
+        } else {   // production contexts store the equation divided by ap
+          const double APs = AE + AW + AN + AS;
+          const double r = APs != 0.0 ? 1.0 / APs : 0.0;
+          P.ae[cout + cq] = AE * r;
+          P.aw[cout + cq] = AW * r;
+          P.an[cout + cq] = AN * r;
+          P.as[cout + cq] = AS * r;
+          P.su[cout + cq] = -smp * r;
+        }
       }
       LineCursor::shift(wd);
       LineCursor::shift(wv);

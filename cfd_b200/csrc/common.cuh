@@ -28,8 +28,12 @@ struct Layout {
   // The six coefficient arrays of one equation (an, as, ap, ae, aw, su -- in that order) are interleaved so that
   // the line solver can fetch "node k of every thread, all six arrays" of a line as ONE contiguous 6*T block:
   //   coefficient a, line i0, node (k,t)  at  coef + i0*cSL + k*cSK + a*T + t,   cSL = 6*LD, cSK = 6*T.
-  long long cSL;
-  int cSK;
+  // In production (red/black) contexts the equations are stored already divided by ap (an/ap, as/ap, ae/ap,
+  // aw/ap, su/ap: nc = 5 arrays, ap itself is not kept): one array less to write per assembly and to read per
+  // sweep.  Bit-exact (sequential-order) contexts keep the reference's six raw arrays (nc = 6).
+  long long cSL;   // nc*LD
+  int cSK;         // nc*T
+  int nc;
 };
 
 __host__ __device__ __forceinline__ int lpos(int j0, int M, int T) { return (j0 % M) * T + (j0 / M); }

@@ -3,13 +3,13 @@
 # dominant kernels.  Outputs land in gpurun_out/.
 set -u
 mkdir -p gpurun_out
-python bench.py --steps 20 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err
+python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err
 echo "bench rc=$?"; cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
 $CMD > gpurun_out/plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'k_tdma_rb|k_assemble_u|k_assemble_p|k_correct' -s 30 -c 8 -f -o gpurun_out/prof_r01 $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'k_tdma_tma|k_assemble_u|k_assemble_v|k_assemble_p|k_correct' -s 40 -c 26 -f -o gpurun_out/prof_r01 $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
 ls -la gpurun_out
