@@ -1,0 +1,314 @@
+"""Multi-GPU driver for the cavity family: 1-D slab decomposition along i.
+
+The S-N TDMA lines of lisolv (cavity_fvm.f90:62-80) run along j, so cutting the grid into slabs of whole lines
+keeps every tridiagonal system on one GPU; only the line Gauss-Seidel coupling crosses ranks, and with
+red/black line ordering that is one halo line of phi per colour pass.  In the device line layout a halo is a
+whole contiguous line (LD doubles) -- no packing.  Per outer iteration (cavity_fvm.f90:554-557):
+
+    exchange u,v,p -> assemble_u -> 3 x (colour 0 | exchange u | colour 1 | exchange u) -> exchange du
+    assemble_v -> 3 x (... v ...) -> assemble_p -> 3 x (... pp ...) -> broadcast pp(ipref,jpref) -> correct
+    residual sums: one all-reduce of 8 packed doubles, only when the host asks for them.
+
+One process per GPU (torch.distributed, NCCL over NVLink; gloo for the CPU tests of this plumbing), or -- for
+single-GPU tests of the slab kernels -- several slabs in one process with `LocalComm`.  The sequential-order
+debug mode does not shard (replicas only).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .cavity import CavityFVM, setgrid
+
+HALO_W, HALO_E = 2, 1        # calcu reads den(i-2) (cavity_fvm.f90:113); everything else needs one line
+
+
+def partition(ni_global: int, world: int):
+    """Owned global line ranges [lo, hi] (1-based, inclusive) per rank: near-equal contiguous slabs."""
+    base, rem = divmod(ni_global, world)
+    out, lo = [], 1
+    for r in range(world):
+        n = base + (1 if r < rem else 0)
+        out.append((lo, lo + n - 1))
+        lo += n
+    return out
+
+
+def slab_extent(ni_global: int, world: int, rank: int):
+    """(goff, ni_local, halo_w, halo_e) of rank's local arrays: owned lines plus halos, clipped at the walls."""
+    lo, hi = partition(ni_global, world)[rank]
+    hw = min(HALO_W, lo - 1) if rank > 0 else 0
+    he = min(HALO_E, ni_global - hi) if rank < world - 1 else 0
+    if world > 1 and hi - lo + 1 < HALO_W:
+        raise ValueError(f"slab of rank {rank} owns {hi - lo + 1} lines; every slab needs at least {HALO_W}")
+    return lo - 1 - hw, (hi - lo + 1) + hw + he, hw, he
+
+
+class _DevArray:
+    """Expose a raw device range to torch through __cuda_array_interface__ (zero copy)."""
+
+    def __init__(self, ptr: int, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f8", "data": (ptr, False), "version": 3}
+
+
+def device_tensor(ptr: int, shape):
+    import torch
+    return torch.as_tensor(_DevArray(ptr, shape), device="cuda")
+
+
+# ----------------------------------------------------------------------------------------------------------
+# communicators
+# ----------------------------------------------------------------------------------------------------------
+class TorchDistComm:
+    """Halo exchange / reductions over torch.distributed (NCCL on GPUs, gloo on CPU tensors)."""
+
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+
+    def exchange(self, ops):
+        """ops: list of (kind, tensor, peer) with kind 'send' | 'recv'; one grouped batch."""
+        if not ops:
+            return
+        dist = self.dist
+        reqs = dist.batch_isend_irecv([dist.P2POp(dist.isend if k == "send" else dist.irecv, t, p) for k, t, p in ops])
+        for r in reqs:
+            r.wait()
+
+    def allreduce_sum(self, t):
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+
+    def broadcast(self, t, src):
+        self.dist.broadcast(t, src=src)
+
+
+def halo_ops(lines, rank: int, world: int, hw: int, he: int, nown: int, w: int = 1, e: int = 1):
+    """P2P ops that refresh `w` west and `e` east halo lines of `lines` (tensor [ni_local, LD]).
+
+    Local line layout: [hw halo lines | nown owned lines | he halo lines].  My west halo = the last lines my
+    west neighbour owns; my east halo = the first lines my east neighbour owns.
+    """
+    ops = []
+    first, last = hw, hw + nown - 1
+    if rank > 0:
+        w_eff = min(w, hw)
+        if w_eff:
+            ops.append(("recv", lines[first - w_eff:first], rank - 1))
+        if e:   # the west neighbour's east halo (it has one, since it has an east neighbour: me)
+            ops.append(("send", lines[first:first + min(e, HALO_E)], rank - 1))
+    if rank < world - 1:
+        e_eff = min(e, he)
+        if e_eff:
+            ops.append(("recv", lines[last + 1:last + 1 + e_eff], rank + 1))
+        if w:
+            ops.append(("send", lines[last + 1 - min(w, HALO_W):last + 1], rank + 1))
+    return ops
+
+
+class LocalComm:
+    """All ranks in ONE process (single-GPU tests of the slab kernels): copies instead of messages."""
+
+    def __init__(self, world):
+        self.world = world
+
+    def exchange_all(self, slabs, name, w=1, e=1):
+        for r in range(self.world - 1):
+            a, b = slabs[r], slabs[r + 1]          # a is west of b
+            la, lb = a.lines(name), b.lines(name)
+            a_last, b_first = a.hw + a.nown - 1, b.hw
+            we = min(w, b.hw)
+            if we:
+                lb[b_first - we:b_first].copy_(la[a_last + 1 - we:a_last + 1])
+            ee = min(e, a.he)
+            if ee:
+                la[a_last + 1:a_last + 1 + ee].copy_(lb[b_first:b_first + ee])
+
+
+# ----------------------------------------------------------------------------------------------------------
+class Slab:
+    """One rank's share of the global cavity problem: a CavityFVM slab context plus its halo bookkeeping."""
+
+    def __init__(self, nicv, njcv, rank, world, *, reynolds=100.0, utop=1.0, rho=1000.0, iadv=3,
+                 urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3), device=-1, xlim=(0.0, 1.0), ylim=(0.0, 1.0)):
+        self.rank, self.world = rank, world
+        ni_g, nj = nicv + 2, njcv + 2
+        self.ni_global, self.nj = ni_g, nj
+        self.goff, self.ni, self.hw, self.he = slab_extent(ni_g, world, rank)
+        self.lo, self.hi = partition(ni_g, world)[rank]
+        self.nown = self.hi - self.lo + 1
+        g = setgrid(nicv, njcv, xlim[0], xlim[1], ylim[0], ylim[1])      # host logic, O(ni+nj)
+        sl = slice(self.goff, self.goff + self.ni)
+        self.ctx = CavityFVM(nicv, njcv, iadv=iadv, order="redblack", urf=urf, nswp=nswp, device=device,
+                             ni_local=self.ni, goff=self.goff, halo_w=self.hw, halo_e=self.he,
+                             sew_nim1=float(g["sew"][ni_g - 2]))
+        self.ctx.set_geometry(x=g["x"][sl], xu=g["xu"][sl], sew=g["sew"][sl], sewu=g["sewu"][sl],
+                              y=g["y"], yv=g["yv"], sns=g["sns"], snsv=g["snsv"])
+        # cavity_fvm.f90:534-538 on the local lines (halo lines included: den, vis are static)
+        den = np.full((self.ni, nj), rho, order="F")
+        vis = np.asfortranarray(den * utop * (xlim[1] - xlim[0]) / reynolds)
+        u = np.zeros((self.ni, nj), order="F")
+        gi = np.arange(self.goff + 1, self.goff + self.ni + 1)            # global 1-based line numbers
+        u[gi >= 2, nj - 1] = utop
+        self.ctx.upload("den", den)
+        self.ctx.upload("vis", vis)
+        self.ctx.upload("u", u)
+        self.nswp = nswp
+        self.ipref, self.jpref = self.ctx.ipref, self.ctx.jpref
+        self.owner_of_pref = self.lo <= self.ipref <= self.hi
+        self._lines = {}
+        import torch
+        self.ppref = torch.zeros(1, dtype=torch.float64, device="cuda")
+        self.res = device_tensor(self.ctx.residual_device_ptr(), (8,))
+
+    def lines(self, name):
+        """Field `name` as a torch tensor [ni_local, LD] aliasing the context's device memory."""
+        if name not in self._lines:
+            base, stride, n = self.ctx.device_view(name)
+            self._lines[name] = device_tensor(base, (n, stride))
+        return self._lines[name]
+
+    def ppref_element(self):
+        """1-element view of pp(ipref,jpref) (owner rank only)."""
+        L = self.ctx.layout
+        j0 = self.jpref - 1
+        q = (j0 % L["M"]) * L["T"] + j0 // L["M"]
+        return self.lines("pp")[self.ipref - 1 - self.goff, q:q + 1]
+
+    def owned(self, a):
+        """Owned part of a downloaded local array."""
+        return a[self.hw:self.hw + self.nown]
+
+
+# stages of one outer iteration: ("compute", fn(slab)) or ("halo", field, w, e) or ("ppref",)
+def iteration_stages(nswp):
+    st = [("halo", "u", 1, 1), ("halo", "v", 1, 1), ("halo", "p", 1, 0),
+          ("compute", lambda s: s.ctx.assemble_u()), ("halo", "du", 0, 1)]
+    for name, istart, jstart, n, first in (("u", 3, 2, nswp[0], False), ("v", 2, 3, nswp[1], False), ("pp", 2, 2, nswp[2], True)):
+        if name == "v":
+            st.append(("compute", lambda s: s.ctx.assemble_v()))
+        if name == "pp":
+            st.append(("compute", lambda s: s.ctx.assemble_p()))
+        for k in range(n):
+            for colour in (0, 1):
+                st.append(("compute", (lambda s, a=istart, b=jstart, f=name, c=colour, z=(first and k == 0):
+                                       s.ctx.sweep(a, b, f, c, first=z))))
+                st.append(("halo", name, 1, 1))
+    st += [("ppref",), ("compute", lambda s: s.ctx.correct(s.ppref.data_ptr()))]
+    return st
+
+
+class SlabCavity:
+    """SPMD driver: one Slab per process over torch.distributed (bench.py, torchrun)."""
+
+    def __init__(self, nicv, njcv, *, reynolds=1000.0, stream=None, **kw):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.comm = TorchDistComm()
+        self.rank, self.world = self.comm.rank, self.comm.world
+        self.slab = Slab(nicv, njcv, self.rank, self.world, reynolds=reynolds, device=torch.cuda.current_device(), **kw)
+        self.ctx = self.slab.ctx
+        if stream is not None:
+            self.ctx.set_stream(stream.cuda_stream)
+        self.stages = iteration_stages(self.slab.nswp)
+        self.pref_owner = [r for r, (lo, hi) in enumerate(partition(nicv + 2, self.world)) if lo <= self.slab.ipref <= hi][0]
+        # static fields: halos filled at upload (den, vis are uniform here); general case: exchange once
+        s = self.slab
+        self.comm.exchange(halo_ops(s.lines("den"), s.rank, s.world, s.hw, s.he, s.nown, HALO_W, HALO_E))
+        self.comm.exchange(halo_ops(s.lines("vis"), s.rank, s.world, s.hw, s.he, s.nown, 1, 1))
+
+    def iterate_async(self, n=1):
+        s = self.slab
+        for _ in range(n):
+            for st in self.stages:
+                if st[0] == "compute":
+                    st[1](s)
+                elif st[0] == "halo":
+                    self.comm.exchange(halo_ops(s.lines(st[1]), s.rank, s.world, s.hw, s.he, s.nown, st[2], st[3]))
+                else:
+                    if s.owner_of_pref:
+                        s.ppref.copy_(s.ppref_element())
+                    self.comm.broadcast(s.ppref, self.pref_owner)
+
+    def residuals(self):
+        r = self.slab.res.clone()
+        self.comm.allreduce_sum(r)
+        return tuple(r.cpu().tolist())
+
+    def iterate(self, n=1):
+        self.iterate_async(n)
+        return self.residuals()[:3]
+
+    def gather_field(self, name):
+        """Global (ni,nj) array on rank 0 (None elsewhere): owned lines of every slab, in order."""
+        a = np.ascontiguousarray(self.slab.owned(self.ctx.download(name)))
+        out = [None] * self.world if self.rank == 0 else None
+        self.dist.gather_object(a, out, dst=0)
+        return np.asfortranarray(np.concatenate(out, axis=0)) if self.rank == 0 else None
+
+    def e2e(self, steps):
+        """bench.py's end-to-end leg: per step upload u,v,p slabs from pinned host memory, one outer
+        iteration, download u,v,p and the residuals; max over ranks of the wall time."""
+        import time
+        torch = self.torch
+        ni, nj = self.slab.ni, self.slab.nj
+        host = {n: torch.empty((nj, ni), dtype=torch.float64, pin_memory=True) for n in ("u", "v", "p")}
+        for n in host:
+            self.ctx.download_ptr(n, host[n].data_ptr(), ni)
+        t0 = 0.0
+        for it in range(steps + 1):
+            if it == 1:
+                torch.cuda.synchronize()
+                self.dist.barrier()
+                t0 = time.perf_counter()
+            for n in host:
+                self.ctx.upload_ptr(n, host[n].data_ptr(), ni)
+            self.iterate(1)
+            for n in host:
+                self.ctx.download_ptr(n, host[n].data_ptr(), ni)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+        self.dist.all_reduce(dt, op=self.dist.ReduceOp.MAX)
+        dt = float(dt.item())
+        fb = ni * nj * 8
+        cells = (self.slab.ni_global - 2) * (nj - 2)
+        return {"value": cells * steps / dt / 1e9, "unit": "GLUPS", "h2d_bytes_per_step": 3 * fb * self.world,
+                "d2h_bytes_per_step": (3 * fb + 64) * self.world, "steps": steps, "ms_per_step": dt / steps * 1e3,
+                "what": "per step and rank: cfd_upload(u,v,p slab) from pinned host arrays, one slab-decomposed outer "
+                        "iteration with halo exchange, all-reduced residuals to the host, cfd_download(u,v,p slab)"}
+
+
+class LocalSlabCavity:
+    """All slabs in one process on one GPU (tests): same stages, LocalComm copies instead of messages."""
+
+    def __init__(self, nicv, njcv, world, **kw):
+        self.world = world
+        self.slabs = [Slab(nicv, njcv, r, world, **kw) for r in range(world)]
+        self.comm = LocalComm(world)
+        self.stages = iteration_stages(self.slabs[0].nswp)
+        self.comm.exchange_all(self.slabs, "den", HALO_W, HALO_E)
+        self.comm.exchange_all(self.slabs, "vis", 1, 1)
+
+    def iterate(self, n=1):
+        import torch
+        for _ in range(n):
+            for st in self.stages:
+                if st[0] == "compute":
+                    for s in self.slabs:
+                        st[1](s)
+                elif st[0] == "halo":
+                    self.comm.exchange_all(self.slabs, st[1], st[2], st[3])
+                else:
+                    owner = [s for s in self.slabs if s.owner_of_pref][0]
+                    for s in self.slabs:
+                        s.ppref.copy_(owner.ppref_element())
+        torch.cuda.synchronize()
+        res = sum(s.res.clone() for s in self.slabs)
+        return tuple(res.cpu().tolist())[:3]
+
+    def gather_field(self, name):
+        return np.asfortranarray(np.concatenate([s.owned(s.ctx.download(name)) for s in self.slabs], axis=0))
+
+    def close(self):
+        for s in self.slabs:
+            s.ctx.close()

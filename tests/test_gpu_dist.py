@@ -1,0 +1,76 @@
+"""Slab-decomposed SIMPLE iterations (cfd_b200/dist.py) against the single-context run.  Red/black line order
+makes the iterates independent of the partition, so fields must agree bit for bit; only the residual sums are
+reduced in a different order."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("world", [2, 3, 4])
+@pytest.mark.parametrize("shape", [(64, 40), (30, 130)])
+def test_local_slabs_match_single_context(cfd, world, shape):
+    from cfd_b200.dist import LocalSlabCavity
+    g = cfd.CavityFVM(*shape, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    s = LocalSlabCavity(*shape, world, reynolds=100.0)
+    for _ in range(3):
+        r1 = g.iterate(2)
+        r2 = s.iterate(2)
+        for a, b in zip(r1, r2):
+            assert abs(a - b) <= 1e-12 * abs(a)
+    for name in ("u", "v", "p", "pp"):
+        assert np.array_equal(s.gather_field(name), g.download(name)), name
+    s.close()
+    g.close()
+
+
+def _nccl_worker(rank, world, port, shape, q):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from cfd_b200.dist import SlabCavity
+        s = SlabCavity(*shape, reynolds=100.0)
+        res = s.iterate(6)
+        out = {n: s.gather_field(n) for n in ("u", "v", "p")}
+        if rank == 0:
+            q.put((res, out))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_nccl_slabs_match_single_context(cfd):
+    import torch
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs (run under gpurun --gpus 2)")
+    shape = (96, 130)
+    g = cfd.CavityFVM(*shape, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    want_res = g.iterate(6)
+    want = {n: g.download(n) for n in ("u", "v", "p")}
+    g.close()
+    sk = socket.socket()
+    sk.bind(("127.0.0.1", 0))
+    port = sk.getsockname()[1]
+    sk.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, shape, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res, out = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for n in want:
+        assert np.array_equal(out[n], want[n]), n
+    for a, b in zip(res, want_res):
+        assert abs(a - b) <= 1e-12 * abs(b)
