@@ -228,41 +228,40 @@ def run_ours(args):
            "residuals_last": list(res[:3]), "gpu_launches": int(launches)}
 
     # ---- roofline of the dominant kernel (the red/black line solver), timed live with CUDA events ---------
-    if rank == 0 or world > 1:
-        pass
+    ctxr = ctx0
+    with torch.cuda.stream(stream):
+        evs = []
+        for _ in range(3):
+            ctxr.assemble_u()
+            for sw in range(3):
+                for col in (0, 1):
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(stream)
+                    ctxr.sweep(3, 2, "u", col)
+                    b.record(stream)
+                    evs.append((a, b))
+        torch.cuda.synchronize()
+    t_launch = sum(a.elapsed_time(b) for a, b in evs) / len(evs) * 1e-3
+    cells_launch = ((NICV - 1) if world == 1 else NICV) / 2.0 * NJCV   # u-lines i=3..ni-1, half per colour pass
+    achieved = SWEEP_BYTES_PER_CELL * cells_launch / t_launch / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("k_tdma_rb", {}).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    out["roofline"] = {"bound": "hbm", "kernel": "k_tdma_tma (one colour pass of a line sweep)",
+                       "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                       "peak_source": peak_src, "traffic": traffic, "launch_ms": t_launch * 1e3,
+                       "algorithmic_bytes_per_launch": SWEEP_BYTES_PER_CELL * cells_launch,
+                       "note": "algorithmic = 8 doubles/cell (6 coefficients + phi read, phi written; SURVEY 8d); the kernel "
+                               "itself moves 7 (equations are stored divided by ap), so frac can exceed the copy peak",
+                       "whole_iteration": {"algorithmic_bytes_per_cell": BYTES_PER_CELL_ITER,
+                                           "achieved": BYTES_PER_CELL_ITER * glups / world,
+                                           "frac": BYTES_PER_CELL_ITER * glups / world / hbm_peak,
+                                           "frac_of_nominal_8TBs": BYTES_PER_CELL_ITER * glups / world / 8000.0}}
     if world == 1:
-        with torch.cuda.stream(stream):
-            evs = []
-            nprof = 3
-            for _ in range(nprof):
-                solver.assemble_u()
-                for sw in range(3):
-                    for col in (0, 1):
-                        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                        a.record(stream)
-                        solver.sweep(3, 2, "u", col)
-                        b.record(stream)
-                        evs.append((a, b))
-                solver.iterate_async(1)
-            torch.cuda.synchronize()
-        t_launch = sum(a.elapsed_time(b) for a, b in evs) / len(evs) * 1e-3
-        cells_launch = (NICV - 1) / 2.0 * NJCV          # u-lines i=3..ni-1, half of them per colour pass
-        achieved = SWEEP_BYTES_PER_CELL * cells_launch / t_launch / 1e9
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            try:
-                traffic = json.load(open(tp)).get("k_tdma_rb", {}).get("dram_bytes_per_launch")
-            except Exception:
-                traffic = None
-        out["roofline"] = {"bound": "hbm", "kernel": "k_tdma_rb (one colour pass of a line sweep)",
-                           "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                           "peak_source": peak_src, "traffic": traffic, "launch_ms": t_launch * 1e3,
-                           "algorithmic_bytes_per_launch": SWEEP_BYTES_PER_CELL * cells_launch,
-                           "whole_iteration": {"algorithmic_bytes_per_cell": BYTES_PER_CELL_ITER,
-                                               "achieved": BYTES_PER_CELL_ITER * glups, "frac": BYTES_PER_CELL_ITER * glups / hbm_peak,
-                                               "frac_of_nominal_8TBs": BYTES_PER_CELL_ITER * glups / 8000.0}}
-
         # ---- e2e: the drop-in call sequence with HOST arrays (pinned), copies inside the timed region --------
         ni, nj = solver.ni, solver.nj
         host = {n: torch.empty((nj, ni), dtype=torch.float64, pin_memory=True) for n in ("u", "v", "p")}
@@ -289,7 +288,6 @@ def run_ours(args):
                               "(each returns its residual to the host), cfd_download(u,v,p)"}
     else:
         out["e2e"] = solver.e2e(max(3, min(K, 10)))
-        out["roofline"] = None
 
     out["clocks"] = clocks
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -300,18 +298,88 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_heat(args):
+    """--workload heat: BASELINE.json configs[1], 2-D FTCS 16384^2 FP64 (one step = one explicit time step)."""
+    import numpy as np
+    import torch
+
+    import cfd_b200
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    K, W = args.steps, args.warmup
+    hbm_peak, peak_src = peaks()
+    n = HEAT_N
+    stream = torch.cuda.Stream()
+    h = cfd_b200.Heat2D(n, n, device=0)
+    h.set_stream(stream.cuda_stream)
+    host = torch.zeros((n, n), dtype=torch.float64, pin_memory=True)
+    host.view(-1)[:: 7] = 1.0
+    h.upload_ptr(host.data_ptr(), n)
+    sampler = ClockSampler(0)
+    with torch.cuda.stream(stream):
+        h.step(W)
+        torch.cuda.synchronize()
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        h.step(K)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        clocks = sampler.stop()
+        Ke = 3
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            h.upload_ptr(host.data_ptr(), n)
+            h.step(1)
+            h.download_ptr(host.data_ptr(), n)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    glups = n * n * K / (ms * 1e-3) / 1e9
+    achieved = HEAT_BYTES_PER_CELL * glups
+    from oracle import oracle as orc
+    m = 4096
+    t_in = np.asfortranarray(np.random.default_rng(1).random((m, m)))
+    tc = time.perf_counter()
+    nst = 0
+    while time.perf_counter() - tc < args.cpu_budget / 2 or nst < 2:
+        t_in = orc.heat2d_ftcs(t_in, 2, fast=True)
+        nst += 2
+    tcpu = time.perf_counter() - tc
+    out = {"metric": "ftcs_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": 1, "steps": K, "warmup": W,
+           "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic", "steps_per_s": K / (ms * 1e-3),
+           "config": {"workload": f"transient heat conduction 2D, explicit FTCS 5-point, {n}x{n} FP64, Fo=0.2, source q=1e3 "
+                                  "where x<0.1 (BASELINE.json configs[1])",
+                      "l2": "two 2.1 GB ping-pong buffers, far larger than L2"},
+           "gpu_launches": K,
+           "roofline": {"bound": "hbm", "kernel": "k_ftcs<false>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": achieved / hbm_peak, "peak_source": peak_src, "traffic": None,
+                        "algorithmic_bytes_per_launch": HEAT_BYTES_PER_CELL * n * n, "launch_ms": ms / K},
+           "e2e": {"value": n * n * Ke / dt / 1e9, "unit": "GLUPS", "h2d_bytes_per_step": n * n * 8,
+                   "d2h_bytes_per_step": n * n * 8, "steps": Ke,
+                   "what": "per step: cfd_heat_upload from pinned host memory, one FTCS step, cfd_heat_download"},
+           "clocks": clocks,
+           "cpu_baseline": {"value": m * m * nst / tcpu / 1e9, "unit": "GLUPS", "cores": 1, "kind": "port",
+                            "sample": f"{nst} FTCS steps on a {m}x{m} sample grid, oracle/heat_oracle.c gcc -O3 -march=native, 1 thread"}}
+    print(json.dumps(out), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "heat":
+        run_heat(args)
     else:
         run_ours(args)
 
