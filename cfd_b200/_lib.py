@@ -12,7 +12,8 @@ CFD_EQ_COUNT = 8
 FAMILY_CAVITY, FAMILY_GENERAL, FAMILY_TEACH = 0, 1, 2
 ORDER_REDBLACK, ORDER_SEQUENTIAL = 0, 1
 
-FIELDS = ("u", "v", "p", "pp", "vis", "den", "t", "cp", "ae", "aw", "an", "as", "ap", "su", "sp", "du", "dv")
+FIELDS = ("u", "v", "p", "pp", "vis", "den", "t", "cp", "ae", "aw", "an", "as", "ap", "su", "sp", "du", "dv",
+          "gamt", "susrc", "spsrc")
 FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
 GEOMS = ("x", "xu", "sew", "sewu", "y", "yv", "sns", "snsv",
          "xdif", "xcvi", "xcvip", "fx", "fxm",
@@ -25,7 +26,15 @@ class CfdConfig(C.Structure):
                 ("nswp", C.c_int * CFD_EQ_COUNT), ("urf", C.c_double * CFD_EQ_COUNT),
                 ("ipref", C.c_int), ("jpref", C.c_int), ("device", C.c_int), ("tdma_m", C.c_int),
                 ("goff", C.c_int), ("ni_global", C.c_int), ("halo_w", C.c_int), ("halo_e", C.c_int),
-                ("sew_nim1", C.c_double)]
+                ("sew_nim1", C.c_double), ("solve_flow", C.c_int), ("solve_t", C.c_int)]
+
+
+class CfdHookDesc(C.Structure):
+    _fields_ = [("kind", C.c_int), ("params", C.c_double * 4)]
+
+
+HOOK_NONE, HOOK_BOUSSINESQ, HOOK_FIELD_SOURCES = 0, 1, 2
+EQ_U, EQ_V, EQ_P, EQ_T = 0, 1, 2, 3
 
 
 class CfdHeatConfig(C.Structure):
@@ -61,6 +70,9 @@ SYMBOLS = {
     "cfd_calcu": (C.c_int, [_vp, _dp]),
     "cfd_calcv": (C.c_int, [_vp, _dp]),
     "cfd_calcp": (C.c_int, [_vp, _dp]),
+    "cfd_calct": (C.c_int, [_vp, _dp]),
+    "cfd_set_hook": (C.c_int, [_vp, C.c_int, C.POINTER(CfdHookDesc)]),
+    "cfd_assemble_t": (C.c_int, [_vp]),
     "cfd_lisolv": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "cfd_iterate": (C.c_int, [_vp, C.c_int, _dp]),
     "cfd_assemble_u": (C.c_int, [_vp]),

@@ -132,8 +132,18 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CFD_REQUIRE(out && cfg, "null argument");
   *out = nullptr;
   CFD_REQUIRE(cfg->ni >= 4 && cfg->nj >= 4, "ni, nj must be >= 4 (two boundary nodes + two cells)");
-  CFD_REQUIRE(cfg->family == CFD_FAMILY_CAVITY, "only CFD_FAMILY_CAVITY contexts are created here");
-  CFD_REQUIRE(cfg->iadv >= 1 && cfg->iadv <= 3, "iadv must be 1 (CDS), 2 (UDS) or 3 (hybrid)");
+  CFD_REQUIRE(cfg->family == CFD_FAMILY_CAVITY || cfg->family == CFD_FAMILY_GENERAL,
+              "family must be CFD_FAMILY_CAVITY or CFD_FAMILY_GENERAL");
+  const bool general = cfg->family == CFD_FAMILY_GENERAL;
+  CFD_REQUIRE(cfg->iadv >= 1 && cfg->iadv <= (general ? 4 : 3), "iadv out of range");
+  if (general) {
+    CFD_REQUIRE(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni),
+                "general-family contexts do not shard yet (single GPU)");
+    // the reference's loops use nj where ni is meant (buoyancy_cav.f90:135,150,151,390): only ni == nj is well defined
+    CFD_REQUIRE(!cfg->solve_flow || cfg->ni == cfg->nj, "the general family's flow equations need ni == nj (reference quirk)");
+    CFD_REQUIRE(cfg->nj <= cfg->ni, "the general family's calct reads den(nj,j): nj must not exceed ni");
+    CFD_REQUIRE(cfg->ni >= 6 && cfg->nj >= 6, "general family needs ni, nj >= 6");
+  }
   CFD_REQUIRE(cfg->order == CFD_ORDER_REDBLACK || cfg->order == CFD_ORDER_SEQUENTIAL, "bad order");
   CFD_REQUIRE(cfg->halo_w >= 0 && cfg->halo_e >= 0 && cfg->halo_w + cfg->halo_e < cfg->ni, "bad halo widths");
   int ndev = 0;
@@ -152,6 +162,10 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->stream = 0;
   for (auto& f : c->field) f = nullptr;
   for (auto& g : c->geom) g = nullptr;
+  for (auto& g : c->geomn) g = nullptr;
+  c->boussinesq = 0;
+  c->rgbeta = c->tref = 0.0;
+  c->has_t_sources = 0;
   c->stage = nullptr;
   c->coef = nullptr;
   c->partial = nullptr;
@@ -171,13 +185,18 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   }
   {
     const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
-    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0);
+    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || general;
     c->L.nc = c->exact_assembly ? 6 : 5;
     c->L.cSL = (long long)c->L.nc * c->L.LD;
     c->L.cSK = c->L.nc * c->L.T;
   }
   const size_t fbytes = (size_t)c->L.ni * c->L.LD * sizeof(double);
-  for (int f : kCavityFields) {
+  std::vector<int> flist(kCavityFields, kCavityFields + sizeof(kCavityFields) / sizeof(int));
+  if (general) {
+    const int extra[] = {CFD_T, CFD_CP, CFD_GAMT, CFD_SUSRC, CFD_SPSRC};
+    flist.insert(flist.end(), extra, extra + 5);
+  }
+  for (int f : flist) {
     if (cudaMalloc(&c->field[f], fbytes) != cudaSuccess) {
       cfd_set_error("cudaMalloc of %zu bytes for field %d failed", fbytes, f);
       cfd_destroy(c);
@@ -198,6 +217,9 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     c->geom_host[g].assign(geom_is_j(g) ? c->L.nj : c->L.ni, 0.0);
     CFD_CUDA(cudaMalloc(&c->geom[g], n * sizeof(double)));
     CFD_CUDA(cudaMemset(c->geom[g], 0, n * sizeof(double)));
+    const size_t nn = (size_t)(geom_is_j(g) ? c->L.nj : c->L.ni) + 2;
+    CFD_CUDA(cudaMalloc(&c->geomn[g], nn * sizeof(double)));
+    CFD_CUDA(cudaMemset(c->geomn[g], 0, nn * sizeof(double)));
   }
   for (int g = 0; g < 8; ++g) {
     const size_t n = (g >= 4) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
@@ -220,6 +242,7 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   if (c->coef) cudaFree(c->coef);
   for (auto& f : c->field) if (f) cudaFree(f);
   for (auto& g : c->geom) if (g) cudaFree(g);
+  for (auto& g : c->geomn) if (g) cudaFree(g);
   for (auto& g : c->gfast) if (g) cudaFree(g);
   if (c->stage) cudaFree(c->stage);
   if (c->partial) cudaFree(c->partial);
@@ -248,6 +271,7 @@ extern "C" int cfd_set_geometry(cfd_ctx* c, int id, const double* host, int n) {
   CFD_REQUIRE(n == (isj ? c->L.nj : c->L.ni), "geometry array length must be nj (y-arrays) or ni (x-arrays)");
   CFD_CUDA(cudaSetDevice(c->device));
   c->geom_host[id].assign(host, host + n);
+  CFD_CUDA(cudaMemcpyAsync(c->geomn[id], host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   if (!isj) {
     CFD_CUDA(cudaMemcpyAsync(c->geom[id], host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CFD_CUDA(cudaStreamSynchronize(c->stream));
@@ -415,9 +439,34 @@ extern "C" int cfd_layout_info(cfd_ctx* c, int* m, int* t, int* ld) {
 }
 
 // ---- stage entry points ----------------------------------------------------------------------------------
-extern "C" int cfd_assemble_u(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return cfd_launch_assemble_u(c); }
-extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return cfd_launch_assemble_v(c); }
-extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return cfd_launch_assemble_p(c); }
+static inline bool is_general(const cfd_ctx* c) { return c->cfg.family == CFD_FAMILY_GENERAL; }
+static int asm_u(cfd_ctx* c) { return is_general(c) ? cfd_launch_general_assemble(c, 0) : cfd_launch_assemble_u(c); }
+static int asm_v(cfd_ctx* c) { return is_general(c) ? cfd_launch_general_assemble(c, 1) : cfd_launch_assemble_v(c); }
+static int asm_p(cfd_ctx* c) { return is_general(c) ? cfd_launch_general_assemble(c, 2) : cfd_launch_assemble_p(c); }
+extern "C" int cfd_assemble_u(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_u(c); }
+extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_v(c); }
+extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_p(c); }
+extern "C" int cfd_assemble_t(cfd_ctx* c) {
+  CFD_REQUIRE(c, "null context");
+  CFD_REQUIRE(is_general(c), "cfd_assemble_t needs a CFD_FAMILY_GENERAL context");
+  return cfd_launch_general_assemble(c, 3);
+}
+extern "C" int cfd_set_hook(cfd_ctx* c, int eq, const cfd_hook_desc* d) {
+  CFD_REQUIRE(c && d, "null argument");
+  CFD_REQUIRE(is_general(c), "hooks belong to CFD_FAMILY_GENERAL contexts");
+  if (eq == CFD_EQ_V && (d->kind == CFD_HOOK_BOUSSINESQ || d->kind == CFD_HOOK_NONE)) {
+    c->boussinesq = d->kind == CFD_HOOK_BOUSSINESQ;
+    c->rgbeta = d->params[0];
+    c->tref = d->params[1];
+    return CFD_OK;
+  }
+  if (eq == CFD_EQ_T && (d->kind == CFD_HOOK_FIELD_SOURCES || d->kind == CFD_HOOK_NONE)) {
+    c->has_t_sources = d->kind == CFD_HOOK_FIELD_SOURCES;
+    return CFD_OK;
+  }
+  cfd_set_error("cfd_set_hook: hook kind %d is not defined for equation %d", d->kind, eq);
+  return CFD_ERR_UNSUPPORTED;
+}
 extern "C" int cfd_correct(cfd_ctx* c, const double* ppref) { CFD_REQUIRE(c, "null context"); return cfd_launch_correct(c, ppref); }
 
 extern "C" int cfd_sweep(cfd_ctx* c, int istart, int jstart, int field, int colour, int first) {
@@ -457,27 +506,42 @@ static int read_res(cfd_ctx* c, int eq, double* out) {
 
 static int stage_u(cfd_ctx* c) {
   int rc;
-  if ((rc = cfd_launch_assemble_u(c))) return rc;
+  if ((rc = asm_u(c))) return rc;
   for (int n = 0; n < c->cfg.nswp[CFD_EQ_U]; ++n)
     if ((rc = full_sweep(c, 3, 2, CFD_U, 0))) return rc;
   return CFD_OK;
 }
 static int stage_v(cfd_ctx* c) {
   int rc;
-  if ((rc = cfd_launch_assemble_v(c))) return rc;
+  if ((rc = asm_v(c))) return rc;
   for (int n = 0; n < c->cfg.nswp[CFD_EQ_V]; ++n)
     if ((rc = full_sweep(c, 2, 3, CFD_V, 0))) return rc;
   return CFD_OK;
 }
 static int stage_p(cfd_ctx* c) {
   int rc;
-  if ((rc = cfd_launch_assemble_p(c))) return rc;
+  if ((rc = asm_p(c))) return rc;
   if (c->cfg.nswp[CFD_EQ_P] == 0) {   // pp(:,:) = 0 with no sweep to fold it into
     CFD_CUDA(cudaMemsetAsync(c->field[CFD_PP], 0, (size_t)c->L.ni * c->L.LD * sizeof(double), c->stream));
   }
   for (int n = 0; n < c->cfg.nswp[CFD_EQ_P]; ++n)
     if ((rc = full_sweep(c, 2, 2, CFD_PP, n == 0))) return rc;
   return cfd_launch_correct(c, nullptr);
+}
+
+static int stage_t(cfd_ctx* c) {
+  int rc;
+  if ((rc = cfd_launch_general_assemble(c, 3))) return rc;
+  for (int n = 0; n < c->cfg.nswp[CFD_EQ_T]; ++n)
+    if ((rc = full_sweep(c, 2, 2, CFD_T, 0))) return rc;
+  return CFD_OK;
+}
+extern "C" int cfd_calct(cfd_ctx* c, double* resort) {
+  CFD_REQUIRE(c, "null context");
+  CFD_REQUIRE(is_general(c), "cfd_calct needs a CFD_FAMILY_GENERAL context");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc = stage_t(c);
+  return rc ? rc : read_res(c, CFD_EQ_T, resort);
 }
 
 extern "C" int cfd_calcu(cfd_ctx* c, double* resoru) {
@@ -503,10 +567,14 @@ extern "C" int cfd_iterate(cfd_ctx* c, int n, double res[8]) {
   CFD_REQUIRE(c && n >= 0, "bad argument");
   CFD_CUDA(cudaSetDevice(c->device));
   int rc;
+  const bool flow = !is_general(c) || c->cfg.solve_flow, temp = is_general(c) && c->cfg.solve_t;
   for (int it = 0; it < n; ++it) {
-    if ((rc = stage_u(c))) return rc;
-    if ((rc = stage_v(c))) return rc;
-    if ((rc = stage_p(c))) return rc;
+    if (flow) {
+      if ((rc = stage_u(c))) return rc;
+      if ((rc = stage_v(c))) return rc;
+      if ((rc = stage_p(c))) return rc;
+    }
+    if (temp && (rc = stage_t(c))) return rc;
   }
   return res ? cfd_residuals(c, res) : CFD_OK;
 }

@@ -111,7 +111,11 @@ struct cfd_ctx {
                                     // AN,AS,AP,AE,AW,SU point into `coef` (interleaved, see Layout)
   double* coef;                     // 6*ni*LD doubles
   double* geom[CFD_GEOM_COUNT];     // by-i: natural (ni doubles); by-j: line layout (LD doubles)
+  double* geomn[CFD_GEOM_COUNT];    // every geometry array in natural order (general-family kernels)
   std::vector<double> geom_host[CFD_GEOM_COUNT];
+  int boussinesq;                   // cfd_set_hook(CFD_EQ_V, CFD_HOOK_BOUSSINESQ)
+  double rgbeta, tref;
+  int has_t_sources;                // cfd_set_hook(CFD_EQ_T, CFD_HOOK_FIELD_SOURCES)
   double* stage;                    // ni*nj staging buffer for upload/download (column-major image)
   double* partial;                  // residual partial sums, CFD_EQ_COUNT * max_blocks
   int max_partials;
@@ -137,3 +141,4 @@ static inline bool cfd_is_coef_field(int f) {
 int cfd_launch_reduce_partials(cfd_ctx* c, int eq, int nblocks);
 int cfd_launch_assemble_fast(cfd_ctx* c, int which, cfd::CavParams& P, dim3 grid, dim3 block);
 int cfd_update_fast_geometry(cfd_ctx* c);
+int cfd_launch_general_assemble(cfd_ctx* c, int which);

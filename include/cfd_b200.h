@@ -47,6 +47,10 @@ typedef enum cfd_order {
 typedef enum cfd_field {
   CFD_U = 0, CFD_V, CFD_P, CFD_PP, CFD_VIS /* = gam */, CFD_DEN, CFD_T, CFD_CP,
   CFD_AE, CFD_AW, CFD_AN, CFD_AS, CFD_AP, CFD_SU, CFD_SP, CFD_DU, CFD_DV,
+  /* general family: what gamsor() (cylin_cond.f90:149-169) fills for the scalar equation nq = 4 */
+  CFD_GAMT,   /* diffusion coefficient of T (gam when nq == 4), boundary rows included (0 = adiabatic) */
+  CFD_SUSRC,  /* su per unit volume */
+  CFD_SPSRC,  /* sp per unit volume */
   CFD_FIELD_COUNT
 } cfd_field;
 
@@ -85,7 +89,22 @@ typedef struct cfd_config {
   int halo_w, halo_e;      /* halo lines at the west / east end of the local arrays (0 at a physical wall) */
   double sew_nim1;         /* value of sew(nim1) of the GLOBAL grid for the stale-scalar quirk of calcv
                               (cavity_fvm.f90:283); 0 = read it from the local geometry */
+  /* general family: lsolve(1) and lsolve(4) of module vars (cylin_cond.f90:54, :100-101) */
+  int solve_flow, solve_t;
 } cfd_config;
+
+/* Device-side form of the `user` module hook gamsor() (cylin_cond.f90:149-169; the buoyancy program's own
+   module is missing from the reference): enumerated source terms evaluated inside the kernels. */
+typedef enum cfd_hook_kind {
+  CFD_HOOK_NONE = 0,
+  CFD_HOOK_BOUSSINESQ = 1,  /* eq = CFD_EQ_V: su = params[0]*(ARIMEAN(t(i,j-1),t(i,j),fy(j)) - params[1])
+                               per unit volume, params[0] = rho*g*beta, params[1] = Tref */
+  CFD_HOOK_FIELD_SOURCES = 2 /* eq = CFD_EQ_T: su, sp per unit volume are the uploaded fields CFD_SUSRC, CFD_SPSRC */
+} cfd_hook_kind;
+typedef struct cfd_hook_desc {
+  int kind;
+  double params[4];
+} cfd_hook_desc;
 
 /* ---- life cycle ------------------------------------------------------------------------------------- */
 /* replaces array_alloc / array_dealloc (cavity_fvm.f90:432-505): fields are zero-initialised on the device */
@@ -135,6 +154,10 @@ int cfd_calcu(cfd_ctx* ctx, double* resoru);
 int cfd_calcv(cfd_ctx* ctx, double* resorv);
 /* calcp (cavity_fvm.f90:293-355): p' assembly, pp=0, nswpp sweeps, correction of p,u,v */
 int cfd_calcp(cfd_ctx* ctx, double* resorm);
+/* calct (buoyancy_cav.f90:358-433): scalar (temperature) equation of the general family */
+int cfd_calct(cfd_ctx* ctx, double* resort);
+/* install the device-side equivalent of a gamsor() source hook for equation eq (CFD_EQ_*) */
+int cfd_set_hook(cfd_ctx* ctx, int eq, const cfd_hook_desc* desc);
 /* lisolv(istart,jstart,ni,nj,phi) (cavity_fvm.f90:49-82): ONE sweep over the current coefficients */
 int cfd_lisolv(cfd_ctx* ctx, int istart, int jstart, int field);
 /* n passes of the loop body cavity_fvm.f90:554-557 without returning to the host; res[0..2] = resoru,resorv,
@@ -146,6 +169,7 @@ int cfd_iterate(cfd_ctx* ctx, int n, double res[8]);
 int cfd_assemble_u(cfd_ctx* ctx);                       /* cavity_fvm.f90:104-187 */
 int cfd_assemble_v(cfd_ctx* ctx);                       /* cavity_fvm.f90:205-285 */
 int cfd_assemble_p(cfd_ctx* ctx);                       /* cavity_fvm.f90:301-342 */
+int cfd_assemble_t(cfd_ctx* ctx);                       /* buoyancy_cav.f90:371-428 (general family) */
 /* half sweep over the lines of one colour (0/1), or a full sequential sweep if colour < 0;
    first != 0 treats phi as zero where the reference has just executed pp(:,:)=0 (cavity_fvm.f90:342) */
 int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first);

@@ -44,6 +44,20 @@ class _CavityStruct(C.Structure):
                                       "ae", "aw", "an", "as_", "ap", "su", "sp", "du", "dv")])
 
 
+class _GeneralStruct(C.Structure):
+    GEOM_I = ("x", "xu", "xdif", "sew", "sewu", "xcvi", "xcvip", "fx", "fxm")
+    GEOM_J = ("y", "yv", "ydif", "sns", "snsv", "ycvr", "ycvrs", "arx", "arxj", "arxjp", "r", "rmn", "sx", "sxmn",
+              "fv", "fvp", "fy", "fym")
+    FIELDS = ("u", "v", "p", "pp", "du", "dv", "t", "den", "gam", "cp", "ae", "aw", "an", "as_", "ap", "su", "sp")
+    _fields_ = ([(n, C.c_int) for n in ("ni", "nj", "icrd", "iadv", "ipref", "jpref", "order", "user")]
+                + [("lsolve", C.c_int * 4), ("nsweep", C.c_int * 4), ("urf", C.c_double * 4), ("resor", C.c_double * 4)]
+                + [(n, C.c_double) for n in ("xstart", "xend", "ystart", "yend", "rstart")]
+                + [(n, C.c_int) for n in ("ibnd", "is1", "is2", "js1", "js2")]
+                + [(n, C.c_double) for n in ("t0", "gam0", "gam1", "htc", "tf", "qin", "visc", "cond", "rgbeta", "tref")]
+                + [("llast", C.c_int)]
+                + [(n, _dp) for n in GEOM_I + GEOM_J + FIELDS])
+
+
 _libs: dict = {}
 
 
@@ -75,6 +89,15 @@ def lib(fast: bool = False) -> C.CDLL:
         L.orc_thomas.restype = None
         L.orc_heat2d_coeffs.argtypes = [_dp] * 4 + [C.c_double] * 2 + [_dp] * 5 + [C.c_int, C.c_int]
         L.orc_heat2d_coeffs.restype = None
+        for n in ("orc_gen_grid", "orc_gen_boundary", "orc_gen_initial", "orc_gen_assemble_u", "orc_gen_assemble_v",
+                  "orc_gen_assemble_p", "orc_gen_assemble_t", "orc_gen_correct", "orc_gen_calcu", "orc_gen_calcv",
+                  "orc_gen_calcp", "orc_gen_calct"):
+            getattr(L, n).argtypes = [C.POINTER(_GeneralStruct)]
+            getattr(L, n).restype = None
+        L.orc_gen_tdma.argtypes = [C.POINTER(_GeneralStruct), C.c_int, C.c_int, _dp]
+        L.orc_gen_tdma.restype = None
+        L.orc_gen_run.argtypes = [C.POINTER(_GeneralStruct), C.c_int, C.c_double, C.c_int, C.c_int, _dp]
+        L.orc_gen_run.restype = C.c_int
         _libs[key] = L
     return _libs[key]
 
@@ -189,3 +212,68 @@ def thomas(a, b, c, d):
     x = np.zeros_like(d)
     lib().orc_thomas(_p(a), _p(b), _p(c), _p(d), _p(x), len(d))
     return x
+
+
+class General:
+    """State of the general SIMPLE family (modules vars/user/serv, cylin_cond.f90:42-287; program main :289-312).
+
+    user="cylinder": the conduction case exactly as shipped (cylin_cond.f90:83-169).
+    user="buoyancy": the Boussinesq cavity authored by this build (the reference's own `user` module is missing).
+    """
+
+    def __init__(self, user="cylinder", ni=52, nj=52, order=0, fast=False, iadv=None, urf=None, nsweep=(3, 3, 3, 3),
+                 ra=1.0e6, pr=0.71, alpha=2.3e-5):
+        self.L = lib(fast)
+        S = _GeneralStruct
+        self.ni, self.nj = ni, nj
+        for n in S.GEOM_I:
+            setattr(self, n, np.zeros(ni))
+        for n in S.GEOM_J:
+            setattr(self, n, np.zeros(nj))
+        for n in S.FIELDS:
+            setattr(self, n, np.zeros((ni, nj), order="F"))
+        s = S(ni=ni, nj=nj, order=order, ipref=1, jpref=1)
+        if user == "cylinder":           # control(), cylin_cond.f90:83-115 and initial() :117-134
+            s.user, s.icrd, s.iadv = 1, 2, 1 if iadv is None else iadv
+            s.xstart, s.xend, s.ystart, s.yend, s.rstart = 0.0, 2.0, 0.0, 1.0, 1.0
+            s.lsolve[:] = [0, 0, 0, 1]
+            u4 = urf or (0.3, 0.3, 0.9, 1.0)
+            s.ibnd = 2
+            s.is1, s.is2, s.js2 = ni // 2 - 10, ni // 2 + 10, nj
+            s.js1 = s.js2 - 20
+            s.gam0, s.gam1, s.qin, s.htc, s.t0, s.tf = 3.0, 1.0, 50.0, 50.0, 20.0, 10.0
+        else:                            # authored Boussinesq cavity (SURVEY 8d input 4)
+            s.user, s.icrd, s.iadv = 2, 1, 3 if iadv is None else iadv
+            s.xstart, s.xend, s.ystart, s.yend, s.rstart = 0.0, 1.0, 0.0, 1.0, 1.0
+            s.lsolve[:] = [1, 0, 0, 1]
+            u4 = urf or (0.3, 0.3, 0.9, 1.0)
+            nu = pr * alpha
+            s.visc, s.cond = nu, alpha              # rho = cp = 1
+            s.rgbeta = ra * nu * alpha              # rho*g*beta = Ra*nu*alpha/(dT*L^3), dT = L = 1
+            s.tref = 0.5
+            s.ipref, s.jpref = ni // 2, nj // 2
+        for k in range(4):
+            s.urf[k] = u4[k]
+            s.nsweep[k] = nsweep[k]
+        self.imon, self.jmon = ni // 2, nj // 2
+        for n in S.GEOM_I + S.GEOM_J + S.FIELDS:
+            setattr(s, n, _p(getattr(self, n)))
+        self.s = s
+        self.L.orc_gen_grid(C.byref(s))
+        self.L.orc_gen_initial(C.byref(s))
+
+    def run(self, max_iter=19999, tol=1.0e-10, history=False):
+        hist = np.zeros((max_iter, 5)) if history else None
+        n = self.L.orc_gen_run(C.byref(self.s), max_iter, tol, self.imon, self.jmon,
+                               hist.ctypes.data_as(_dp) if history else None)
+        return (n, hist[:n]) if history else n
+
+    def call(self, name, *a):
+        getattr(self.L, "orc_gen_" + name)(C.byref(self.s), *a)
+
+    def tdma(self, istart, jstart, phi):
+        self.L.orc_gen_tdma(C.byref(self.s), istart, jstart, _p(phi))
+
+    @property
+    def resor(self):
+        return tuple(self.s.resor)
