@@ -17,7 +17,8 @@ FIELDS = ("u", "v", "p", "pp", "vis", "den", "t", "cp", "ae", "aw", "an", "as", 
 FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
 GEOMS = ("x", "xu", "sew", "sewu", "y", "yv", "sns", "snsv",
          "xdif", "xcvi", "xcvip", "fx", "fxm",
-         "ydif", "ycvr", "ycvrs", "arx", "arxj", "arxjp", "r", "rmn", "sx", "sxmn", "fv", "fvp", "fy", "fym")
+         "ydif", "ycvr", "ycvrs", "arx", "arxj", "arxjp", "r", "rmn", "sx", "sxmn", "fv", "fvp", "fy", "fym",
+         "dxep", "dxpw", "dxepu", "dxpwu", "dynp", "dyps", "dynpv", "dypsv", "rv", "rcv")
 GEOM_ID = {n: i for i, n in enumerate(GEOMS)}
 
 
@@ -26,7 +27,9 @@ class CfdConfig(C.Structure):
                 ("nswp", C.c_int * CFD_EQ_COUNT), ("urf", C.c_double * CFD_EQ_COUNT),
                 ("ipref", C.c_int), ("jpref", C.c_int), ("device", C.c_int), ("tdma_m", C.c_int),
                 ("goff", C.c_int), ("ni_global", C.c_int), ("halo_w", C.c_int), ("halo_e", C.c_int),
-                ("sew_nim1", C.c_double), ("solve_flow", C.c_int), ("solve_t", C.c_int)]
+                ("sew_nim1", C.c_double), ("solve_flow", C.c_int), ("solve_t", C.c_int),
+                ("indcos", C.c_int), ("istep", C.c_int), ("jstep", C.c_int), ("_pad", C.c_int),
+                ("viscos", C.c_double), ("flowin", C.c_double), ("great", C.c_double)]
 
 
 class CfdHookDesc(C.Structure):

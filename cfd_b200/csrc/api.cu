@@ -122,6 +122,7 @@ static bool geom_is_j(int id) {
   switch (id) {
     case CFD_G_X: case CFD_G_XU: case CFD_G_SEW: case CFD_G_SEWU:
     case CFD_G_XDIF: case CFD_G_XCVI: case CFD_G_XCVIP: case CFD_G_FX: case CFD_G_FXM:
+    case CFD_G_DXEP: case CFD_G_DXPW: case CFD_G_DXEPU: case CFD_G_DXPWU:
       return false;
     default:
       return true;
@@ -132,10 +133,18 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CFD_REQUIRE(out && cfg, "null argument");
   *out = nullptr;
   CFD_REQUIRE(cfg->ni >= 4 && cfg->nj >= 4, "ni, nj must be >= 4 (two boundary nodes + two cells)");
-  CFD_REQUIRE(cfg->family == CFD_FAMILY_CAVITY || cfg->family == CFD_FAMILY_GENERAL,
-              "family must be CFD_FAMILY_CAVITY or CFD_FAMILY_GENERAL");
-  const bool general = cfg->family == CFD_FAMILY_GENERAL;
+  CFD_REQUIRE(cfg->family == CFD_FAMILY_CAVITY || cfg->family == CFD_FAMILY_GENERAL || cfg->family == CFD_FAMILY_TEACH,
+              "family must be CFD_FAMILY_CAVITY, CFD_FAMILY_GENERAL or CFD_FAMILY_TEACH");
+  const bool general = cfg->family == CFD_FAMILY_GENERAL, teach = cfg->family == CFD_FAMILY_TEACH;
   CFD_REQUIRE(cfg->iadv >= 1 && cfg->iadv <= (general ? 4 : 3), "iadv out of range");
+  if (teach) {
+    CFD_REQUIRE(cfg->iadv == 3, "the TEACH family has the hybrid scheme only (calc.f90:69-72): iadv must be 3");
+    CFD_REQUIRE(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni),
+                "TEACH-family contexts do not shard yet (single GPU)");
+    CFD_REQUIRE(cfg->indcos == 1 || cfg->indcos == 2, "indcos must be 1 (plane) or 2 (axisymmetric)");
+    CFD_REQUIRE(cfg->istep >= 2 && cfg->jstep >= 2 && cfg->jstep < cfg->nj - 1, "istep / jstep out of range");
+    CFD_REQUIRE(cfg->ni >= 6 && cfg->nj >= 6, "TEACH family needs ni, nj >= 6");
+  }
   if (general) {
     CFD_REQUIRE(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni),
                 "general-family contexts do not shard yet (single GPU)");
@@ -185,7 +194,7 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   }
   {
     const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
-    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || general;
+    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || general || teach;
     c->L.nc = c->exact_assembly ? 6 : 5;
     c->L.cSL = (long long)c->L.nc * c->L.LD;
     c->L.cSK = c->L.nc * c->L.T;
@@ -440,9 +449,16 @@ extern "C" int cfd_layout_info(cfd_ctx* c, int* m, int* t, int* ld) {
 
 // ---- stage entry points ----------------------------------------------------------------------------------
 static inline bool is_general(const cfd_ctx* c) { return c->cfg.family == CFD_FAMILY_GENERAL; }
-static int asm_u(cfd_ctx* c) { return is_general(c) ? cfd_launch_general_assemble(c, 0) : cfd_launch_assemble_u(c); }
-static int asm_v(cfd_ctx* c) { return is_general(c) ? cfd_launch_general_assemble(c, 1) : cfd_launch_assemble_v(c); }
-static int asm_p(cfd_ctx* c) { return is_general(c) ? cfd_launch_general_assemble(c, 2) : cfd_launch_assemble_p(c); }
+static inline bool is_teach(const cfd_ctx* c) { return c->cfg.family == CFD_FAMILY_TEACH; }
+static int asm_u(cfd_ctx* c) {
+  return is_general(c) ? cfd_launch_general_assemble(c, 0) : is_teach(c) ? cfd_launch_teach_assemble(c, 0) : cfd_launch_assemble_u(c);
+}
+static int asm_v(cfd_ctx* c) {
+  return is_general(c) ? cfd_launch_general_assemble(c, 1) : is_teach(c) ? cfd_launch_teach_assemble(c, 1) : cfd_launch_assemble_v(c);
+}
+static int asm_p(cfd_ctx* c) {
+  return is_general(c) ? cfd_launch_general_assemble(c, 2) : is_teach(c) ? cfd_launch_teach_assemble(c, 2) : cfd_launch_assemble_p(c);
+}
 extern "C" int cfd_assemble_u(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_u(c); }
 extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_v(c); }
 extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_p(c); }

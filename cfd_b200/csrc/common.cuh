@@ -142,3 +142,4 @@ int cfd_launch_reduce_partials(cfd_ctx* c, int eq, int nblocks);
 int cfd_launch_assemble_fast(cfd_ctx* c, int which, cfd::CavParams& P, dim3 grid, dim3 block);
 int cfd_update_fast_geometry(cfd_ctx* c);
 int cfd_launch_general_assemble(cfd_ctx* c, int which);
+int cfd_launch_teach_assemble(cfd_ctx* c, int which);

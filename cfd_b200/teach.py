@@ -1,0 +1,134 @@
+"""Host-side mirror of the TEACH-T sudden-expansion program (backward-step-flow-2d/: control.f90, general.f90)
+over the C ABI, laminar subset (calcu, calcv, calcp with the modu / modv hooks; k-epsilon, energy and props are
+outside this subset).  Grid generation (control.f90:72-90), `init` (general.f90:69-140) and the initial fields
+(control.f90:148-179, 197-203) are O(ni+nj)/one-off host logic restated here; every per-iteration array
+operation runs in libcfd_b200.so.  The reference computes in default REAL (FP32); this path is FP64.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import CfdConfig, check
+from .cavity import CavityFVM
+
+
+def teach_grid(ni, nj, rlarge=0.0124, epsx=1.05):
+    """x(1:ni), y(1:nj) of control.f90:72-90 (geometric stretching epsx in x, uniform in y)."""
+    nim1 = ni - 1
+    x, y = np.zeros(ni + 1), np.zeros(nj + 1)
+    altot = 16.0 * rlarge
+    if epsx == 1.0:
+        sumx = 0.5 + float(ni - 3) + 0.5
+    else:
+        sumx = 0.5 * epsx ** (ni - 4) + (epsx ** (ni - 3) - 1.0) / (epsx - 1.0) + 0.5
+    dx = altot / sumx
+    x[1] = -0.5 * dx
+    x[2] = -x[1]
+    for i in range(3, nim1 + 1):
+        x[i] = x[i - 1] + dx
+        dx = epsx * dx
+    x[ni] = x[nim1] - x[ni - 2] + x[nim1]
+    dy = rlarge / float(nj - 2)
+    y[1] = -0.5 * dy
+    for j in range(2, nj + 1):
+        y[j] = y[j - 1] + dy
+    return x[1:].copy(), y[1:].copy()
+
+
+def teach_init(x, y, indcos):
+    """init (general.f90:69-140): cell sizes and radii from the node coordinates."""
+    ni, nj = len(x), len(y)
+    nim1, njm1 = ni - 1, nj - 1
+    X, Y = np.concatenate(([0.0], x)), np.concatenate(([0.0], y))      # 1-based
+    zi, zj = (lambda: np.zeros(ni + 2)), (lambda: np.zeros(nj + 2))
+    r, rv, rcv, yv, sns, snsv, dynp, dyps, dynpv, dypsv = (zj() for _ in range(10))
+    xu, sew, sewu, dxep, dxpw, dxepu, dxpwu = (zi() for _ in range(7))
+    for j in range(1, nj + 1):
+        r[j] = Y[j] if indcos != 1 else 1.0
+    for i in range(1, nim1 + 1):
+        dxep[i] = X[i + 1] - X[i]
+        dxpw[i + 1] = dxep[i]
+    for j in range(1, njm1 + 1):
+        dynp[j] = Y[j + 1] - Y[j]
+        dyps[j + 1] = dynp[j]
+    for i in range(2, nim1 + 1):
+        sew[i] = 0.5 * (dxep[i] + dxpw[i])
+    for j in range(2, njm1 + 1):
+        sns[j] = 0.5 * (dynp[j] + dyps[j])
+    for i in range(2, ni + 1):
+        xu[i] = 0.5 * (X[i] + X[i - 1])
+    for i in range(2, nim1 + 1):
+        dxepu[i] = xu[i + 1] - xu[i]
+        dxpwu[i + 1] = dxepu[i]
+    for i in range(3, nim1 + 1):
+        sewu[i] = 0.5 * (dxepu[i] + dxpwu[i])
+    for j in range(2, nj + 1):
+        rv[j] = 0.5 * (r[j] + r[j - 1])
+        rcv[j] = 0.5 * (rv[j] + rv[j - 1])
+        yv[j] = 0.5 * (Y[j] + Y[j - 1])
+    for j in range(2, njm1 + 1):
+        dynpv[j] = yv[j + 1] - yv[j]
+        dypsv[j + 1] = dynpv[j]
+    for j in range(3, njm1 + 1):
+        snsv[j] = 0.5 * (dynpv[j] + dypsv[j])
+    gi = dict(x=X, xu=xu, sew=sew, sewu=sewu, dxep=dxep, dxpw=dxpw, dxepu=dxepu, dxpwu=dxpwu)
+    gj = dict(y=Y, yv=yv, r=r, rv=rv, rcv=rcv, sns=sns, snsv=snsv, dynp=dynp, dyps=dyps, dynpv=dynpv, dypsv=dypsv)
+    out = {k: v[1:ni + 1].copy() for k, v in gi.items()}
+    out.update({k: v[1:nj + 1].copy() for k, v in gj.items()})
+    return out
+
+
+class TeachFVM(CavityFVM):
+    """One GPU context of CFD_FAMILY_TEACH with the shipped case's literals (control.f90:15-141), laminar."""
+
+    def __init__(self, ni=100, nj=100, *, order="redblack", epsx=1.05, indcos=2, rlarge=0.0124, uin=0.5,
+                 densit=1000.0, viscos=0.8e-3, urf=(0.5, 0.5, 1.0), nswp=(3, 3, 5), jstep=None, device=-1, tdma_m=0):
+        self.lib = _lib.load()
+        self.ni, self.nj = ni, nj
+        self.ni_global, self.nicv, self.njcv, self.goff = ni, ni - 2, nj - 2, 0
+        self.istep = 2
+        self.jstep = jstep if jstep is not None else max(2, int(round(0.08 * nj)))
+        self.ipref, self.jpref = 2, 2
+        self.imon, self.jmon = min(10, ni - 1), min(10, nj - 1)
+        x, y = teach_grid(ni, nj, rlarge, epsx)
+        g = teach_init(x, y, indcos)
+        for k, v in g.items():
+            setattr(self, k, v)
+        # initial fields and inlet mass flow (control.f90:148-179, 197-203)
+        den = np.full((ni, nj), densit, order="F")
+        vis = np.full((ni, nj), viscos, order="F")
+        u = np.zeros((ni, nj), order="F")
+        js, jstp1 = self.jstep, self.jstep + 1
+        u[1, 1:js] = uin
+        jfin = jstp1
+        for i in range(2, ni + 1):
+            if i >= self.istep + 1:
+                jfin = nj
+            factor = (self.yv[jstp1 - 1] * self.rv[jstp1 - 1]) / (self.yv[jfin - 1] * self.rv[jfin - 1])
+            u[i - 1, 1:jfin - 1] = uin * factor
+        flowin = 0.0
+        for j in range(2, nj):
+            arden = 0.5 * (den[0, j - 1] + den[1, j - 1]) * self.r[j - 1] * self.sns[j - 1]
+            flowin = flowin + arden * u[1, j - 1]
+        self.flowin = flowin
+        cfg = CfdConfig()
+        cfg.family = _lib.FAMILY_TEACH
+        cfg.ni, cfg.nj, cfg.iadv = ni, nj, 3
+        cfg.order = _lib.ORDER_SEQUENTIAL if order in ("sequential", "seq", 1) else _lib.ORDER_REDBLACK
+        for k in range(3):
+            cfg.nswp[k] = nswp[k]
+            cfg.urf[k] = urf[k]
+        cfg.ipref, cfg.jpref, cfg.device, cfg.tdma_m = 2, 2, device, tdma_m
+        cfg.indcos, cfg.istep, cfg.jstep = indcos, self.istep, self.jstep
+        cfg.viscos, cfg.flowin, cfg.great = viscos, flowin, 1.0e30
+        self._cfg = cfg
+        self._h = C.c_void_p()
+        check(self.lib.cfd_create(C.byref(self._h), C.byref(cfg)))
+        self.set_geometry(**g)
+        self.upload("den", den)
+        self.upload("vis", vis)
+        self.upload("u", u)
+        self.resoru = self.resorv = self.resorm = 0.0

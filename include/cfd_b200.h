@@ -62,6 +62,9 @@ typedef enum cfd_geom {
   CFD_G_XDIF, CFD_G_XCVI, CFD_G_XCVIP, CFD_G_FX, CFD_G_FXM,                         /* length ni */
   CFD_G_YDIF, CFD_G_YCVR, CFD_G_YCVRS, CFD_G_ARX, CFD_G_ARXJ, CFD_G_ARXJP,
   CFD_G_R, CFD_G_RMN, CFD_G_SX, CFD_G_SXMN, CFD_G_FV, CFD_G_FVP, CFD_G_FY, CFD_G_FYM, /* length nj */
+  /* TEACH family extras, computed by init (backward-step-flow-2d/general.f90:69-140) */
+  CFD_G_DXEP, CFD_G_DXPW, CFD_G_DXEPU, CFD_G_DXPWU,                                 /* length ni */
+  CFD_G_DYNP, CFD_G_DYPS, CFD_G_DYNPV, CFD_G_DYPSV, CFD_G_RV, CFD_G_RCV,            /* length nj */
   CFD_GEOM_COUNT
 } cfd_geom;
 
@@ -91,6 +94,10 @@ typedef struct cfd_config {
                               (cavity_fvm.f90:283); 0 = read it from the local geometry */
   /* general family: lsolve(1) and lsolve(4) of module vars (cylin_cond.f90:54, :100-101) */
   int solve_flow, solve_t;
+  /* TEACH family (backward-step-flow-2d/control.f90): indcos (1 plane, 2 axisymmetric, :66), istep / jstep
+     (:16,:67), laminar viscosity viscos (:126), inlet mass flow flowin (:197-203), great (:15) */
+  int indcos, istep, jstep;
+  double viscos, flowin, great;
 } cfd_config;
 
 /* Device-side form of the `user` module hook gamsor() (cylin_cond.f90:149-169; the buoyancy program's own

@@ -58,6 +58,23 @@ class _GeneralStruct(C.Structure):
                 + [(n, _dp) for n in GEOM_I + GEOM_J + FIELDS])
 
 
+def _teach_struct(real):
+    rp = C.POINTER(real)
+
+    class _S(C.Structure):
+        G1 = ("x", "y", "xu", "yv", "r", "rv", "rcv", "sew", "sns", "sewu", "snsv",
+              "dxep", "dxpw", "dynp", "dyps", "dxepu", "dxpwu", "dynpv", "dypsv", "yplusn", "xplusw", "taun", "tauw")
+        F2 = ("u", "v", "p", "pp", "du", "dv", "den", "vis", "te", "ae", "aw", "an", "as_", "ap", "su", "sp")
+        _fields_ = ([(n, C.c_int) for n in ("ni", "nj", "it", "indcos", "istep", "jstep", "ipref", "jpref", "order",
+                                             "nswpu", "nswpv", "nswpp")]
+                    + [(n, real) for n in ("urfu", "urfv", "urfp", "great", "viscos", "densit", "flowin",
+                                           "resoru", "resorv", "resorm")]
+                    + [(n, rp) for n in G1 + F2])
+    return _S
+
+
+_TeachF64, _TeachF32 = _teach_struct(C.c_double), _teach_struct(C.c_float)
+
 _libs: dict = {}
 
 
@@ -277,3 +294,61 @@ class General:
     @property
     def resor(self):
         return tuple(self.s.resor)
+
+
+class Teach:
+    """Laminar subset of the TEACH-T sudden-expansion program (backward-step-flow-2d/: control.f90, general.f90,
+    calc.f90, promod.f90).  dtype float64 = parity oracle of the CUDA path; float32 = the reference as written."""
+
+    def __init__(self, ni=100, nj=100, it=None, dtype=np.float64, order=0, fast=False, epsx=1.05, indcos=2,
+                 rlarge=0.0124, uin=0.5, densit=1000.0, viscos=0.8e-3, urf=(0.5, 0.5, 1.0), nswp=(3, 3, 5), jstep=None):
+        self.L = lib(fast)
+        self.dtype = np.dtype(dtype)
+        f64 = self.dtype == np.float64
+        S = _TeachF64 if f64 else _TeachF32
+        self.sfx = "_f64" if f64 else "_f32"
+        real = C.c_double if f64 else C.c_float
+        rp = C.POINTER(real)
+        it = it or ni
+        self.ni, self.nj, self.it = ni, nj, it
+        n1 = 2 * max(it, nj)
+        for n in S.G1:
+            setattr(self, n, np.zeros(n1, dtype=self.dtype))
+        for n in S.F2:
+            setattr(self, n, np.zeros((it, nj), dtype=self.dtype, order="F"))
+        jstep = jstep if jstep is not None else max(2, int(round(0.08 * nj)))
+        s = S(ni=ni, nj=nj, it=it, indcos=indcos, istep=2, jstep=jstep, ipref=2, jpref=2, order=order,
+              nswpu=nswp[0], nswpv=nswp[1], nswpp=nswp[2], urfu=urf[0], urfv=urf[1], urfp=urf[2],
+              great=1.0e30, viscos=viscos, densit=densit)
+        for n in S.G1 + S.F2:
+            setattr(s, n, getattr(self, n).ctypes.data_as(rp))
+        self.s = s
+        ptr = C.POINTER(S)
+        for n in ("grid", "init", "initial", "assemble_u", "assemble_v", "assemble_p", "correct", "calcu", "calcv",
+                  "calcp", "iterate", "lisolv"):
+            fn = getattr(self.L, "orc_teach_" + n + self.sfx)
+            fn.restype = None
+            fn.argtypes = {"grid": [ptr, real, real], "initial": [ptr, real], "iterate": [ptr, C.c_int],
+                           "lisolv": [ptr, C.c_int, C.c_int, rp]}.get(n, [ptr])
+        self._call("grid", rlarge, epsx)
+        self._call("init")
+        self._call("initial", uin)
+        self.jstep = jstep
+
+    def _call(self, name, *a):
+        getattr(self.L, "orc_teach_" + name + self.sfx)(C.byref(self.s), *a)
+
+    def call(self, name):
+        self._call(name)
+
+    def iterate(self, n=1):
+        self._call("iterate", n)
+        return self.s.resoru, self.s.resorv, self.s.resorm
+
+    def lisolv(self, istart, jstart, phi):
+        real = C.c_double if self.dtype == np.float64 else C.c_float
+        self._call("lisolv", istart, jstart, phi.ctypes.data_as(C.POINTER(real)))
+
+    @property
+    def residuals(self):
+        return self.s.resoru, self.s.resorv, self.s.resorm

@@ -1,0 +1,98 @@
+"""Parity of the TEACH-family CUDA path (calcu/calcv/calcp + modu/modv of backward-step-flow-2d through the C ABI)
+with the FP64 oracle: bit-exact in sequential-order mode; red/black mode to the same fixed point; and agreement
+with the reference's own FP32 arithmetic to single precision."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+COEF = (("ae", "ae"), ("aw", "aw"), ("an", "an"), ("as", "as_"), ("ap", "ap"), ("su", "su"))
+
+
+def linf_rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.mark.parametrize("shape,epsx,indcos", [((40, 30), 1.05, 2), ((64, 20), 1.0, 1), ((100, 100), 1.05, 2), ((24, 300), 1.02, 2)])
+def test_assembly_bitwise(cfd, oracle, shape, epsx, indcos):
+    ni, nj = shape
+    o = oracle.Teach(ni, nj, epsx=epsx, indcos=indcos)
+    g = cfd.TeachFVM(ni, nj, epsx=epsx, indcos=indcos, order="sequential")
+    assert g.flowin == o.s.flowin
+    o.iterate(3)                       # get non-trivial fields
+    for name in ("u", "v", "p"):
+        g.upload(name, getattr(o, name)[:ni, :])
+    o.call("assemble_u")
+    g.assemble_u()
+    g.synchronize()
+    sl = (slice(2, ni - 1), slice(1, nj - 1))
+    for gn, on in COEF:
+        assert np.array_equal(g.download(gn)[sl], getattr(o, on)[:ni][sl]), ("u", gn)
+    assert np.array_equal(g.download("du")[sl], o.du[:ni][sl])
+    assert np.array_equal(g.download("u"), o.u[:ni])          # symmetry row and outlet column written by modu
+    assert abs(g.residuals()[0] - o.residuals[0]) <= 1e-11 * o.residuals[0]
+    o.call("assemble_v")
+    g.assemble_v()
+    sl = (slice(1, ni - 1), slice(2, nj - 1))
+    for gn, on in COEF:
+        assert np.array_equal(g.download(gn)[sl], getattr(o, on)[:ni][sl]), ("v", gn)
+    assert np.array_equal(g.download("dv")[sl], o.dv[:ni][sl])
+    o.call("assemble_p")
+    g.assemble_p()
+    sl = (slice(1, ni - 1), slice(1, nj - 1))
+    for gn, on in COEF:
+        assert np.array_equal(g.download(gn)[sl], getattr(o, on)[:ni][sl]), ("p", gn)
+    g.close()
+
+
+@pytest.mark.parametrize("shape", [(40, 30), (100, 100)])
+def test_trajectory_sequential_bitwise(cfd, oracle, shape):
+    ni, nj = shape
+    o = oracle.Teach(ni, nj)
+    g = cfd.TeachFVM(ni, nj, order="sequential")
+    ro = o.iterate(30)
+    rg = g.iterate(30)
+    for name in ("u", "v", "p"):
+        assert np.array_equal(g.download(name), getattr(o, name)[:ni]), name
+    for a, b in zip(rg, ro):
+        assert abs(a - b) <= 1e-10 * abs(b)
+    g.close()
+
+
+def test_redblack_converged_and_reference_fp32(cfd, oracle):
+    ni, nj = 40, 30
+    o = oracle.Teach(ni, nj)
+    o.iterate(1500)
+    g = cfd.TeachFVM(ni, nj, order="redblack")
+    g.iterate(1500)
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)[:ni]) < 1e-8, name
+    f32 = oracle.Teach(ni, nj, dtype=np.float32)     # the reference as written
+    f32.iterate(400)
+    assert linf_rel(g.download("u"), f32.u[:ni].astype(np.float64)) < 1e-4
+    g.close()
+
+
+def test_leading_dimension_it_larger_than_ni(cfd, oracle):
+    """The reference allocates (it,jt) >= (ni,nj) (control.f90:22-25,49-55): uploads/downloads take ld = it."""
+    ni, nj, it = 40, 30, 64
+    o = oracle.Teach(ni, nj, it=it)
+    g = cfd.TeachFVM(ni, nj, order="sequential")
+    o.iterate(5)
+    g.iterate(5)
+    big = np.zeros((it, nj), order="F")
+    g.download_ptr("u", big.ctypes.data, it)
+    assert np.array_equal(big[:ni], o.u[:ni]) and not big[ni:].any()
+    g.close()
+
+
+def test_config5_shape_properties(cfd):
+    """BASELINE.json configs[4] at a reduced but same-aspect size (4096 x 1024, uniform x: the shipped epsx = 1.05
+    overflows at these sizes): finite fields, outlet mass balance, symmetry row."""
+    ni, nj = 4096, 1024
+    g = cfd.TeachFVM(ni, nj, epsx=1.0, order="redblack")
+    r = g.iterate(10)
+    u = g.download("u")
+    assert np.isfinite(u).all() and np.isfinite(r).all()
+    flow = (0.5 * (1000.0 + 1000.0) * g.r[1:nj - 1] * g.sns[1:nj - 1] * u[ni - 1, 1:nj - 1]).sum()
+    assert abs(flow - g.flowin) < 1e-9 * g.flowin
+    g.close()
