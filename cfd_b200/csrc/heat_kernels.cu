@@ -18,6 +18,7 @@ struct cfd_heat {
   double* buf[2];
   int cur;
   long long steps_done;
+  double* thomas;      // implicit steps: e_x[nx], temp_x[nx], e_y[ny], temp_y[ny] of the forward sweep (constant)
 };
 
 namespace cfd {
@@ -85,6 +86,139 @@ __global__ void __launch_bounds__(128) k_ftcs(const HeatParams P) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Implicit Euler, locally one-dimensional: the tridiagonal assembly of implicit-time/fdm1d_explicit_heat_cond.f90
+// :122-143 (a = c = -Fo, b = 1 + 2 Fo, identity rows at the Dirichlet ends, rhs = T + dt*QDOT/rho/cp) applied along
+// x for every interior row and then along y for every interior column, solved with the reference's `thomas`
+// (:147-184: e = c/temp, f = (d - a f_prev)/temp, x = f - e x_next).  The coefficients do not depend on the line,
+// so e and temp are computed once on the host (same operation order) and only the f / x recurrences run here,
+// one thread per line, in place, with IEEE operations in the reference's order (bit-comparable with
+// oracle/heat_oracle.c:orc_heat2d_lod).
+// ---------------------------------------------------------------------------------------------------
+struct LodParams {
+  int nx, ny;
+  double fox, foy, dt, rho, cp, xa, dx, qthr, qval;
+  double tleft, tright, tbottom, ttop;
+  const double *ex, *tx, *ey, *ty;
+  double* t;
+};
+
+// Dirichlet edges rewritten at the start of every step (same order as the explicit scheme)
+__global__ void k_lod_bc(const LodParams P) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nx = (size_t)P.nx;
+  if (n >= 1 && n <= P.ny - 2) {
+    P.t[(size_t)n * nx] = P.tleft;
+    P.t[(size_t)n * nx + nx - 1] = P.tright;
+  }
+  if (n < P.nx) {
+    P.t[n] = P.tbottom;
+    P.t[(size_t)(P.ny - 1) * nx + n] = P.ttop;
+  }
+}
+
+// x-lines: a warp owns 32 interior rows and walks along x in 32-column tiles, transposing through shared memory
+// so that global accesses are 256-byte row segments while each lane runs the recurrence of "its" row.
+__global__ void __launch_bounds__(128) k_lod_x(const LodParams P) {
+  __shared__ double tile[4][32][33];
+  const int lane = threadIdx.x, w = threadIdx.y;
+  const int row0 = 1 + (blockIdx.x * 4 + w) * 32;          // first of this warp's rows (0-based j)
+  if (row0 > P.ny - 2) return;
+  const int nx = P.nx, ntile = (nx + 31) / 32;
+  const size_t snx = (size_t)nx;
+  const int myrow = row0 + lane;
+  const bool rowok = myrow <= P.ny - 2;
+  double (*tl)[33] = tile[w];
+  // forward sweep: f overwrites T
+  double fprev = 0.0;
+  for (int tI = 0; tI < ntile; ++tI) {
+    const int c0 = tI * 32;
+    for (int r = 0; r < 32; ++r) {
+      const int j = row0 + r;
+      tl[r][lane] = (j <= P.ny - 2 && c0 + lane < nx) ? P.t[(size_t)j * snx + c0 + lane] : 0.0;
+    }
+    __syncwarp();
+    if (rowok) {
+      for (int k = 0; k < 32 && c0 + k < nx; ++k) {
+        const int i = c0 + k;
+        double d = tl[lane][k], f;
+        if (i == 0) {
+          f = __ddiv_rn(d, 1.0);
+        } else if (i == nx - 1) {
+          f = __ddiv_rn(__dsub_rn(d, __dmul_rn(0.0, fprev)), __ldg(P.tx + i));
+        } else {
+          const double xi = __dadd_rn(P.xa, __dmul_rn((double)i, P.dx));
+          const double q = (xi < P.qthr) ? P.qval : 0.0;
+          d = __dadd_rn(d, __ddiv_rn(__ddiv_rn(__dmul_rn(P.dt, q), P.rho), P.cp));
+          f = __ddiv_rn(__dsub_rn(d, __dmul_rn(-P.fox, fprev)), __ldg(P.tx + i));
+        }
+        tl[lane][k] = f;
+        fprev = f;
+      }
+    }
+    __syncwarp();
+    for (int r = 0; r < 32; ++r) {
+      const int j = row0 + r;
+      if (j <= P.ny - 2 && c0 + lane < nx) P.t[(size_t)j * snx + c0 + lane] = tl[r][lane];
+    }
+    __syncwarp();
+  }
+  // back substitution: x overwrites f, tiles right to left
+  double xnext = 0.0;
+  for (int tI = ntile - 1; tI >= 0; --tI) {
+    const int c0 = tI * 32;
+    for (int r = 0; r < 32; ++r) {
+      const int j = row0 + r;
+      tl[r][lane] = (j <= P.ny - 2 && c0 + lane < nx) ? P.t[(size_t)j * snx + c0 + lane] : 0.0;
+    }
+    __syncwarp();
+    if (rowok) {
+      for (int k = 31; k >= 0; --k) {
+        const int i = c0 + k;
+        if (i >= nx) continue;
+        const double f = tl[lane][k];
+        const double x = (i == nx - 1) ? f : __dsub_rn(f, __dmul_rn(__ldg(P.ex + i), xnext));
+        tl[lane][k] = x;
+        xnext = x;
+      }
+    }
+    __syncwarp();
+    for (int r = 0; r < 32; ++r) {
+      const int j = row0 + r;
+      if (j <= P.ny - 2 && c0 + lane < nx) P.t[(size_t)j * snx + c0 + lane] = tl[r][lane];
+    }
+    __syncwarp();
+  }
+}
+
+// y-lines: one thread per interior column, consecutive threads = consecutive x (coalesced at every j)
+__global__ void __launch_bounds__(128) k_lod_y(const LodParams P) {
+  const int i = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > P.nx - 2) return;
+  const size_t nx = (size_t)P.nx;
+  double* col = P.t + i;
+  double fprev = 0.0;
+  for (int j = 0; j < P.ny; ++j) {
+    const double d = col[(size_t)j * nx];
+    double f;
+    if (j == 0) {
+      f = __ddiv_rn(d, 1.0);
+    } else {
+      const double a = (j == P.ny - 1) ? 0.0 : -P.foy;
+      f = __ddiv_rn(__dsub_rn(d, __dmul_rn(a, fprev)), __ldg(P.ty + j));
+    }
+    col[(size_t)j * nx] = f;
+    fprev = f;
+  }
+  double xnext = 0.0;
+  for (int j = P.ny - 1; j >= 0; --j) {
+    const double f = col[(size_t)j * nx];
+    const double x = (j == P.ny - 1) ? f : __dsub_rn(f, __dmul_rn(__ldg(P.ey + j), xnext));
+    col[(size_t)j * nx] = x;
+    xnext = x;
+  }
+}
+
 }  // namespace cfd
 
 using namespace cfd;
@@ -110,6 +244,7 @@ extern "C" int cfd_heat_create(cfd_heat** out, const cfd_heat_config* cfg) {
   h->cur = 0;
   h->steps_done = 0;
   h->buf[0] = h->buf[1] = nullptr;
+  h->thomas = nullptr;
   const size_t bytes = (size_t)cfg->nx * cfg->ny * sizeof(double);
   for (int b = 0; b < 2; ++b) {
     if (cudaMalloc(&h->buf[b], bytes) != cudaSuccess) {
@@ -128,6 +263,7 @@ extern "C" int cfd_heat_destroy(cfd_heat* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   for (int b = 0; b < 2; ++b) if (h->buf[b]) cudaFree(h->buf[b]);
+  if (h->thomas) cudaFree(h->thomas);
   delete h;
   return CFD_OK;
 }
@@ -226,9 +362,59 @@ static int heat_steps(cfd_heat* h, int nsteps, bool exact) {
 extern "C" int cfd_heat2d_step(cfd_heat* h, int nsteps) { return heat_steps(h, nsteps, false); }
 extern "C" int cfd_heat2d_step_exact(cfd_heat* h, int nsteps) { return heat_steps(h, nsteps, true); }
 
+// forward-sweep constants of `thomas` for a line of n nodes with a = c = -fo, b = 1 + 2 fo and identity ends
+static void thomas_constants(int n, double fo, std::vector<double>& e, std::vector<double>& temp) {
+  e.assign(n, 0.0);
+  temp.assign(n, 1.0);
+  e[0] = 0.0 / 1.0;
+  for (int i = 1; i < n; ++i) {
+    const bool last = (i == n - 1);
+    const double a = last ? 0.0 : -fo, b = last ? 1.0 : 1.0 + 2.0 * fo, c = last ? 0.0 : -fo;
+    temp[i] = b - a * e[i - 1];
+    e[i] = c / temp[i];
+  }
+}
+
 extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) {
-  (void)h;
-  (void)nsteps;
-  cfd_set_error("cfd_heat2d_implicit_step: not built yet");
-  return CFD_ERR_UNSUPPORTED;
+  CFD_REQUIRE(h && nsteps >= 0, "bad argument");
+  const cfd_heat_config& g = h->cfg;
+  if (g.ny_global && g.ny_global != g.ny) {
+    cfd_set_error("cfd_heat2d_implicit_step: the y-lines would cross slabs; implicit steps run on whole grids only");
+    return CFD_ERR_UNSUPPORTED;
+  }
+  CFD_CUDA(cudaSetDevice(h->device));
+  const int nx = g.nx, ny = g.ny;
+  const double dx = (g.xb - g.xa) / (double)(nx - 1), dy = (g.yb - g.ya) / (double)(ny - 1);
+  LodParams P{};
+  P.nx = nx;
+  P.ny = ny;
+  P.fox = g.k * g.dt / g.rho / g.cp / (dx * dx);
+  P.foy = g.k * g.dt / g.rho / g.cp / (dy * dy);
+  P.dt = g.dt; P.rho = g.rho; P.cp = g.cp; P.xa = g.xa; P.dx = dx; P.qthr = g.qthr; P.qval = g.qval;
+  P.tleft = g.tleft; P.tright = g.tright; P.tbottom = g.tbottom; P.ttop = g.ttop;
+  if (!h->thomas) {
+    std::vector<double> ex, tx, ey, ty, all;
+    thomas_constants(nx, P.fox, ex, tx);
+    thomas_constants(ny, P.foy, ey, ty);
+    all.insert(all.end(), ex.begin(), ex.end());
+    all.insert(all.end(), tx.begin(), tx.end());
+    all.insert(all.end(), ey.begin(), ey.end());
+    all.insert(all.end(), ty.begin(), ty.end());
+    CFD_CUDA(cudaMalloc(&h->thomas, all.size() * sizeof(double)));
+    CFD_CUDA(cudaMemcpy(h->thomas, all.data(), all.size() * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  P.ex = h->thomas;
+  P.tx = h->thomas + nx;
+  P.ey = h->thomas + 2 * (size_t)nx;
+  P.ty = h->thomas + 2 * (size_t)nx + ny;
+  P.t = h->buf[h->cur];
+  const int nmax = nx > ny ? nx : ny;
+  for (int n = 0; n < nsteps; ++n) {
+    k_lod_bc<<<(nmax + 127) / 128, 128, 0, h->stream>>>(P);
+    k_lod_x<<<(ny - 2 + 127) / 128, dim3(32, 4), 0, h->stream>>>(P);
+    k_lod_y<<<(nx - 2 + 127) / 128, 128, 0, h->stream>>>(P);
+    CFD_CUDA(cudaGetLastError());
+    ++h->steps_done;
+  }
+  return CFD_OK;
 }

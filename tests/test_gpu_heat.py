@@ -68,3 +68,28 @@ def test_ftcs_full_size_eigenmode(cfd):
     lam = 1.0 - 8 * (5.0 * h.dt / dx**2) * np.sin(np.pi * dx / 2) ** 2
     assert np.abs(got - lam**10 * t0).max() < 1e-12
     h.close()
+
+
+@pytest.mark.parametrize("shape", [(5, 4), (66, 34), (130, 257), (515, 300)])
+def test_implicit_lod_bitwise(cfd, oracle, shape):
+    """Implicit Euler, locally one-dimensional (tridiagonal assembly + thomas of the implicit 1-D program applied
+    along x then y): same operation order as the oracle -> same bits."""
+    nx, ny = shape
+    t0 = noise(nx, ny, 7)
+    h = cfd.Heat2D(nx, ny, dt=2.0e-4, tleft=1.0, tright=2.0, tbottom=3.0, ttop=4.0)
+    h.upload(t0)
+    h.implicit_step(3)
+    want = oracle.heat2d_lod(t0, 3, dt=2.0e-4, tbc=(1.0, 2.0, 3.0, 4.0))
+    assert np.array_equal(h.download(), want)
+    h.close()
+
+
+def test_implicit_lod_large_time_step_is_stable(cfd):
+    """Fo = 50 (250 x the explicit limit): bounded, monotone approach to the steady state."""
+    n = 1026
+    h = cfd.Heat2D(n, n, fo=50.0, qval=0.0, tleft=1.0, tright=1.0, tbottom=1.0, ttop=1.0)
+    h.upload(np.zeros((n, n), order="F"))
+    h.implicit_step(40)
+    t = h.download()
+    assert t.min() >= -1e-12 and t.max() <= 1.0 + 1e-12
+    h.close()
