@@ -6,6 +6,7 @@ host-side mirrors of the reference's program interfaces.  No CPU fallback exists
 from ._lib import CfdError, LIB_PATH, load  # noqa: F401
 from .cavity import CavityFVM, centred_vel, setgrid  # noqa: F401
 from .heat import Heat2D  # noqa: F401
+from .fdcavity import FDCavity  # noqa: F401
 from .teach import TeachFVM, teach_grid, teach_init  # noqa: F401
 from .general import BuoyantCavity, CylinderConduction, GeneralFVM, grid  # noqa: F401
 

@@ -49,6 +49,14 @@ class CfdHeatConfig(C.Structure):
                 ("halo_s", C.c_int), ("halo_n", C.c_int)]
 
 
+class CfdFdcavConfig(C.Structure):
+    _fields_ = [("ni", C.c_int), ("nj", C.c_int), ("re", C.c_double), ("dt", C.c_double), ("utop", C.c_double),
+                ("urfp", C.c_double), ("device", C.c_int)]
+
+
+FDC_FIELDS = ("u", "v", "p", "uo", "vo", "po", "pp", "su")
+
+
 class CfdError(RuntimeError):
     pass
 
@@ -95,6 +103,12 @@ SYMBOLS = {
     "cfd_heat2d_implicit_step": (C.c_int, [_vp, C.c_int]),
     "cfd_heat_device_view": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
     "cfd_heat_synchronize": (C.c_int, [_vp]),
+    "cfd_fdcav_create": (C.c_int, [C.POINTER(_vp), C.POINTER(CfdFdcavConfig)]),
+    "cfd_fdcav_destroy": (C.c_int, [_vp]),
+    "cfd_fdcav_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_fdcav_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_fdcav_predict": (C.c_int, [_vp]),
+    "cfd_fdcav_correct": (C.c_int, [_vp, _dp]),
     "cfd_version": (C.c_char_p, []),
 }
 

@@ -1,0 +1,60 @@
+"""Host-side mirror of the explicit finite-difference cavity program
+(lid-driven-cavity-2d/fdm-explicit/fdm_explicit_cavity.f90:90-255) over the C ABI.  The stencil passes of a time
+step run on the GPU; the p' Poisson solve between them (Stone's SIP, `sipsol` :24-87) is the caller's -- pass a
+`solve_pp(su) -> pp` callable to `step` (SURVEY 8f-1 marks a device SIP as "next")."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import CfdFdcavConfig, FDC_FIELDS, check
+
+
+class FDCavity:
+    def __init__(self, ni=11, nj=11, *, re=10.0, dt=1.0e-4, utop=1.0, urfp=0.8, device=-1):
+        self.lib = _lib.load()
+        self.ni, self.nj = ni, nj
+        self._h = C.c_void_p()
+        cfg = CfdFdcavConfig(ni=ni, nj=nj, re=re, dt=dt, utop=utop, urfp=urfp, device=device)
+        check(self.lib.cfd_fdcav_create(C.byref(self._h), C.byref(cfg)))
+        # initial condition (fdm_explicit_cavity.f90:160-166)
+        uo = np.zeros((ni + 1, nj + 1), order="F")
+        uo[:ni, nj - 1:nj + 1] = 1.0
+        self.upload("uo", uo)
+        self.upload("po", np.ones((ni + 1, nj + 1), order="F"))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self.lib.cfd_fdcav_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, name, a):
+        a = np.asfortranarray(a, dtype=np.float64)
+        assert a.shape == (self.ni + 1, self.nj + 1)
+        check(self.lib.cfd_fdcav_upload(self._h, FDC_FIELDS.index(name), a.ctypes.data_as(C.c_void_p), self.ni + 1))
+
+    def download(self, name):
+        a = np.zeros((self.ni + 1, self.nj + 1), order="F")
+        check(self.lib.cfd_fdcav_download(self._h, FDC_FIELDS.index(name), a.ctypes.data_as(C.c_void_p), self.ni + 1))
+        return a
+
+    def predict(self):
+        check(self.lib.cfd_fdcav_predict(self._h))
+
+    def correct(self) -> float:
+        e = C.c_double()
+        check(self.lib.cfd_fdcav_correct(self._h, C.byref(e)))
+        return e.value
+
+    def step(self, solve_pp) -> float:
+        self.predict()
+        self.upload("pp", solve_pp(self.download("su")))
+        return self.correct()

@@ -216,6 +216,28 @@ int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps);
 int cfd_heat_device_view(cfd_heat* h, void** cur, long long* row_stride, int* nrows);
 int cfd_heat_synchronize(cfd_heat* h);
 
+/* ---- explicit finite-difference cavity: stencil passes of lid-driven-cavity-2d/fdm-explicit/
+        fdm_explicit_cavity.f90 (the SIP solve of p' between the two calls is the caller's) ------ */
+typedef enum cfd_fdc_field {
+  CFD_FDC_U = 0, CFD_FDC_V, CFD_FDC_P, CFD_FDC_UO, CFD_FDC_VO, CFD_FDC_PO, CFD_FDC_PP, CFD_FDC_SU, CFD_FDC_FIELD_COUNT
+} cfd_fdc_field;
+typedef struct cfd_fdcav_config {
+  int ni, nj;                 /* grid nodes (fdm_explicit_cavity.f90:111-112); arrays are (ni+1, nj+1) */
+  double re, dt, utop, urfp;  /* :116-119 */
+  int device;
+} cfd_fdcav_config;
+typedef struct cfd_fdcav cfd_fdcav;
+int cfd_fdcav_create(cfd_fdcav** out, const cfd_fdcav_config* cfg);
+int cfd_fdcav_destroy(cfd_fdcav* h);
+/* A(ld, nj+1) column-major, ld >= ni+1; field = cfd_fdc_field */
+int cfd_fdcav_upload(cfd_fdcav* h, int field, const double* host, int ld);
+int cfd_fdcav_download(cfd_fdcav* h, int field, double* host, int ld);
+/* u, v momentum predictors (:170-192), pp = 0 and the p' source su (:194-205) */
+int cfd_fdcav_predict(cfd_fdcav* h);
+/* correction of p, u, v with the caller-solved pp (:208-222), boundary conditions (:224-237), continuity norm
+   `error` (:239-247), uo=u, vo=v, po=p (:252-254) */
+int cfd_fdcav_correct(cfd_fdcav* h, double* error);
+
 /* library/build identification */
 const char* cfd_version(void);
 

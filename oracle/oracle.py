@@ -352,3 +352,45 @@ class Teach:
     @property
     def residuals(self):
         return self.s.resoru, self.s.resorv, self.s.resorm
+
+
+class _FdcStruct(C.Structure):
+    _fields_ = ([("ni", C.c_int), ("nj", C.c_int)] + [(n, C.c_double) for n in ("re", "dt", "utop", "urfp")]
+                + [(n, _dp) for n in ("u", "v", "p", "uo", "vo", "po", "pp", "su")] + [("sip_iters", C.c_int)])
+
+
+class FDCavity:
+    """Explicit finite-difference cavity (lid-driven-cavity-2d/fdm-explicit/fdm_explicit_cavity.f90:90-255);
+    arrays (ni+1, nj+1) Fortran-ordered, the reference's smaller extents are their leading parts."""
+
+    FIELDS = ("u", "v", "p", "uo", "vo", "po", "pp", "su")
+
+    def __init__(self, ni=11, nj=11, re=10.0, dt=1.0e-4, utop=1.0, urfp=0.8, fast=False):
+        self.L = lib(fast)
+        self.ni, self.nj = ni, nj
+        for n in self.FIELDS:
+            setattr(self, n, np.zeros((ni + 1, nj + 1), order="F"))
+        self.s = _FdcStruct(ni=ni, nj=nj, re=re, dt=dt, utop=utop, urfp=urfp)
+        for n in self.FIELDS:
+            setattr(self.s, n, _p(getattr(self, n)))
+        ptr = C.POINTER(_FdcStruct)
+        for n in ("init", "predict", "solve_pp"):
+            getattr(self.L, "orc_fdc_" + n).argtypes = [ptr]
+            getattr(self.L, "orc_fdc_" + n).restype = None
+        for n in ("correct", "step"):
+            getattr(self.L, "orc_fdc_" + n).argtypes = [ptr]
+            getattr(self.L, "orc_fdc_" + n).restype = C.c_double
+        self.L.orc_fdc_init(C.byref(self.s))
+
+    def predict(self):
+        self.L.orc_fdc_predict(C.byref(self.s))
+
+    def solve_pp(self):
+        self.L.orc_fdc_solve_pp(C.byref(self.s))
+        return self.s.sip_iters
+
+    def correct(self):
+        return self.L.orc_fdc_correct(C.byref(self.s))
+
+    def step(self):
+        return self.L.orc_fdc_step(C.byref(self.s))
