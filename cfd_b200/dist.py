@@ -312,3 +312,89 @@ class LocalSlabCavity:
     def close(self):
         for s in self.slabs:
             s.ctx.close()
+
+
+# ----------------------------------------------------------------------------------------------------------
+# 2-D FTCS heat conduction: j-slabs (rows are contiguous in the column-major layout), one halo row per side
+# and step.  The update loop is fdm1d_explicit_heat_cond.f90:130-139 in 2-D.
+# ----------------------------------------------------------------------------------------------------------
+def heat_slab_extent(ny_global: int, world: int, rank: int):
+    """(j_goff, ny_local, halo_s, halo_n): owned rows plus one halo row towards each neighbour."""
+    lo, hi = partition(ny_global, world)[rank]
+    hs = 1 if rank > 0 else 0
+    hn = 1 if rank < world - 1 else 0
+    return lo - 1 - hs, (hi - lo + 1) + hs + hn, hs, hn
+
+
+class HeatSlab:
+    def __init__(self, nx, ny_global, rank, world, device=-1, t0=None, **kw):
+        from .heat import Heat2D
+        self.rank, self.world, self.nx, self.ny_global = rank, world, nx, ny_global
+        self.j_goff, self.ny, self.hs, self.hn = heat_slab_extent(ny_global, world, rank)
+        self.nown = self.ny - self.hs - self.hn
+        dx = (kw.get("xb", 1.0) - kw.get("xa", 0.0)) / (nx - 1)
+        k, rho, cp = kw.get("k", 5.0), kw.get("rho", 1.0), kw.get("cp", 1.0)
+        if kw.get("dt") is None:
+            kw["dt"] = kw.pop("fo", 0.2) * dx * dx / (k / rho / cp)
+        self.h = Heat2D(nx, self.ny, device=device, j_goff=self.j_goff, ny_global=ny_global, halo_s=self.hs,
+                        halo_n=self.hn, **kw)
+        if t0 is not None:
+            self.h.upload(np.asfortranarray(t0[:, self.j_goff:self.j_goff + self.ny]))
+
+    def rows(self):
+        """Current field as a torch tensor [ny_local, nx] (rows contiguous) aliasing device memory."""
+        base, stride, n = self.h.device_view()
+        return device_tensor(base, (n, stride))
+
+    def halo_ops(self):
+        r, ops = self.rows(), []
+        first, last = self.hs, self.hs + self.nown - 1
+        if self.rank > 0:
+            ops += [("recv", r[first - 1:first], self.rank - 1), ("send", r[first:first + 1], self.rank - 1)]
+        if self.rank < self.world - 1:
+            ops += [("recv", r[last + 1:last + 2], self.rank + 1), ("send", r[last:last + 1], self.rank + 1)]
+        return ops
+
+    def owned(self, a):
+        return a[:, self.hs:self.hs + self.nown]
+
+
+class SlabHeat:
+    """SPMD driver over torch.distributed: step = FTCS update of the owned rows, then halo-row exchange."""
+
+    def __init__(self, nx, ny_global, *, stream=None, **kw):
+        import torch
+        self.torch = torch
+        self.comm = TorchDistComm()
+        self.slab = HeatSlab(nx, ny_global, self.comm.rank, self.comm.world, device=torch.cuda.current_device(), **kw)
+        if stream is not None:
+            self.slab.h.set_stream(stream.cuda_stream)
+
+    def step(self, n=1):
+        for _ in range(n):
+            self.slab.h.step(1)
+            self.comm.exchange(self.slab.halo_ops())
+
+
+class LocalSlabHeat:
+    """All slabs in one process on one GPU (tests)."""
+
+    def __init__(self, nx, ny_global, world, t0, **kw):
+        self.slabs = [HeatSlab(nx, ny_global, r, world, t0=t0, **dict(kw)) for r in range(world)]
+
+    def step(self, n=1):
+        for _ in range(n):
+            for s in self.slabs:
+                s.h.step(1)
+            rows = [s.rows() for s in self.slabs]
+            for r in range(len(self.slabs) - 1):
+                a, b = self.slabs[r], self.slabs[r + 1]
+                rows[r + 1][b.hs - 1:b.hs].copy_(rows[r][a.hs + a.nown - 1:a.hs + a.nown])
+                rows[r][a.hs + a.nown:a.hs + a.nown + 1].copy_(rows[r + 1][b.hs:b.hs + 1])
+
+    def gather(self):
+        return np.asfortranarray(np.concatenate([s.owned(s.h.download()) for s in self.slabs], axis=1))
+
+    def close(self):
+        for s in self.slabs:
+            s.h.close()

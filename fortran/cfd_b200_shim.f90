@@ -13,6 +13,9 @@ module cfd_b200_c
     real(c_double) :: urf(8)
     integer(c_int) :: ipref, jpref, device, tdma_m, goff, ni_global, halo_w, halo_e
     real(c_double) :: sew_nim1
+    integer(c_int) :: solve_flow, solve_t            ! general family: lsolve(1), lsolve(4)
+    integer(c_int) :: indcos, istep, jstep           ! TEACH family (control.f90:16,66,67)
+    real(c_double) :: viscos, flowin, great          ! TEACH family (control.f90:15,126,197-203)
   end type
   interface
     integer(c_int) function cfd_create(ctx, cfg) bind(c, name='cfd_create')
@@ -59,7 +62,8 @@ contains
   subroutine gpu_init()              ! call once after setgrid and the initial-value assignments (cavity_fvm.f90:538)
     type(cfd_config) :: cfg
     cfg = cfd_config(0, ni, nj, iadv, 0, [nswpu,nswpv,nswpp,0,0,0,0,0], &
-                     [urfu,urfv,urfp,0d0,0d0,0d0,0d0,0d0], ipref, jpref, -1, 0, 0, 0, 0, 0, 0d0)
+                     [urfu,urfv,urfp,0d0,0d0,0d0,0d0,0d0], ipref, jpref, -1, 0, 0, 0, 0, 0, 0d0, &
+                     0, 0, 0, 0, 0, 0d0, 0d0, 0d0)
     ierr = cfd_create(ctx, cfg)
     ierr = cfd_set_geometry(ctx, CFD_G_X, x, ni);   ierr = cfd_set_geometry(ctx, CFD_G_XU, xu, ni)
     ierr = cfd_set_geometry(ctx, CFD_G_SEW, sew, ni); ierr = cfd_set_geometry(ctx, CFD_G_SEWU, sewu, ni)

@@ -76,3 +76,14 @@ def _worker(rank, world, port, ni, ld):
 @pytest.mark.parametrize("world", [2, 3])
 def test_halo_exchange_gloo(world):
     mp.spawn(_worker, args=(world, _free_port(), 23, 16), nprocs=world, join=True)
+
+
+def test_heat_slab_extent():
+    from cfd_b200.dist import heat_slab_extent
+    ny, world = 97, 4
+    tot = 0
+    for r in range(world):
+        goff, nloc, hs, hn = heat_slab_extent(ny, world, r)
+        assert hs == (r > 0) and hn == (r < world - 1)
+        tot += nloc - hs - hn
+    assert tot == ny

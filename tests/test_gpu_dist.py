@@ -74,3 +74,18 @@ def test_nccl_slabs_match_single_context(cfd):
         assert np.array_equal(out[n], want[n]), n
     for a, b in zip(res, want_res):
         assert abs(a - b) <= 1e-12 * abs(b)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_heat_row_slabs_match_single_grid(cfd, world):
+    from cfd_b200.dist import LocalSlabHeat
+    nx, ny = 130, 97
+    t0 = np.asfortranarray(np.random.default_rng(3).random((nx, ny)))
+    h = cfd.Heat2D(nx, ny, tleft=1.0, ttop=2.0)
+    h.upload(t0)
+    h.step(7)
+    s = LocalSlabHeat(nx, ny, world, t0, tleft=1.0, ttop=2.0)
+    s.step(7)
+    assert np.array_equal(s.gather(), h.download())
+    s.close()
+    h.close()
