@@ -505,6 +505,20 @@ static int launch_assemble(cfd_ctx* c, int which, CavParams& P, int eq) {
     return CFD_OK;
   }
   const bool fast = !c->exact_assembly && which < 2;
+  static int use_tma = -1;
+  if (use_tma < 0) {
+    const char* e = getenv("CFD_B200_ASM_TMA");
+    use_tma = e ? atoi(e) : 1;
+  }
+  if (fast && use_tma && c->L.T >= 128 && c->L.T + 64 <= 768) {   // TMA-staged persistent kernels (long lines)
+    P.partial = c->partial + (size_t)eq * c->max_partials;
+    const int nb = cfd_launch_assemble_tma(c, which, P);
+    if (nb < 0) return nb;
+    k_reduce_partials<<<1, 1024, 0, c->stream>>>(P.partial, nb, c->res_dev + eq);
+    ++c->launches;
+    CFD_CUDA(cudaGetLastError());
+    return CFD_OK;
+  }
   const int by = fast ? 4 : BY;
   dim3 block(BX, by), grid((c->L.T + BX - 1) / BX, (nlines + by - 1) / by);
   const int nblocks = grid.x * grid.y;

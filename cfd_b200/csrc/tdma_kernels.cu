@@ -15,6 +15,7 @@
 //                small grids: one block, lines one after the other, the recurrence run by a single thread out
 //                of shared memory with non-contracted IEEE operations.
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace cfd {
 
@@ -202,35 +203,6 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
 // keeps streaming while the consumers are in the backward / cyclic-reduction / store phases of the previous
 // line.  One persistent block per SM.
 // ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-  unsigned ok;
-  do {
-    asm volatile(
-        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  } while (!ok);
-}
-__device__ __forceinline__ void tma_load_1d(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void consumer_sync(int nthreads) {
-  asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
-}
-
 template <int M, int BMAX>
 __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const int S) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -262,14 +234,15 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     if (tid == T) {
       const unsigned slice_bytes = (unsigned)(T * sizeof(double));
       const unsigned tx = slice_bytes * ((unsigned)nc + (zeroE ? 0u : 1u) + (zeroW ? 0u : 1u));
-      unsigned it = 0;
+      unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
       for (int line = blockIdx.x; line < P.nlines; line += gridDim.x) {
         const long long i0 = P.i_first + (long long)line * P.i_step;
         const double* csrc = P.an + i0 * P.L.cSL;       // an is array 0 of the interleaved block
         const double* esrc = P.phi + (i0 + 1) * LD;
         const double* wsrc = P.phi + (i0 - 1) * LD;
-        for (int k = 0; k < M; ++k, ++it) {
-          const unsigned s = it % (unsigned)S, ph = (it / (unsigned)S) & 1u;
+        for (int k = 0; k < M; ++k) {
+          const unsigned s = rs, ph = rph;
+          if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
           mbar_wait(empty0 + 8 * s, ph ^ 1u);
           const unsigned fb = full0 + 8 * s;
           const unsigned dst = smem_u32(ring + (size_t)s * SW);
@@ -287,7 +260,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
   const int t = tid, lane = tid & 31;
   const int j0base = t * M;
   const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.L.nj - 1, M, T);
-  unsigned it = 0;
+  unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
   double bS = 0.0, bN = 0.0;   // Dirichlet end values phi(i, jstart-1), phi(i, nj) of the current line
   if (!P.first && (int)blockIdx.x < P.nlines) {
     const double* ph = P.phi + (P.i_first + (long long)blockIdx.x * P.i_step) * LD;
@@ -306,8 +279,9 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     }
     double ca[M], cc[M], cf[M];
 #pragma unroll
-    for (int k = 0; k < M; ++k, ++it) {
-      const unsigned s = it % (unsigned)S, ph = (it / (unsigned)S) & 1u;
+    for (int k = 0; k < M; ++k) {
+      const unsigned s = rs, ph = rph;
+      if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
       mbar_wait(full0 + 8 * s, ph);
       const double* sl = ring + (size_t)s * SW + t;
       double a = sl[0], b = sl[T], d = 1.0;

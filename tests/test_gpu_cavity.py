@@ -71,7 +71,7 @@ def test_assembly_bitwise(cfd, oracle, shape, iadv):
     g.close()
 
 
-@pytest.mark.parametrize("shape", [(10, 10), (64, 64), (33, 130), (3, 3), (200, 257)])
+@pytest.mark.parametrize("shape", [(10, 10), (64, 64), (33, 130), (3, 3), (200, 257), (40, 2100), (12, 4096), (300, 4096)])
 @pytest.mark.parametrize("iadv", [1, 2, 3])
 def test_production_assembly_matches_oracle(cfd, oracle, shape, iadv):
     """Red/black mode uses the reciprocal/FMA assembly kernels and stores each equation divided by ap (five
