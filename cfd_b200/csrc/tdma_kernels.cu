@@ -203,14 +203,15 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
 // keeps streaming while the consumers are in the backward / cyclic-reduction / store phases of the previous
 // line.  One persistent block per SM.
 // ---------------------------------------------------------------------------------------------------
-template <int M, int BMAX>
+template <int M, int BMAX, int NC>
 __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const int S) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int T = P.L.T;
   const long long LD = P.L.LD;
   const int tid = threadIdx.x;
   // carve shared memory: [ring S*(nc+2)*T doubles][pcr 6*T doubles][full S][empty S]
-  const int nc = P.L.nc, SW = (nc + 2) * T;   // doubles per ring stage
+  constexpr int nc = NC;                      // coefficient arrays per node (5 normalised / 6 raw)
+  const int SW = (nc + 2) * T;                // doubles per ring stage
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* bufA = ring + (size_t)S * SW;
   double* bufB = bufA + 3 * T;
@@ -259,6 +260,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
   // ---------------- consumers ---------------------------------------------------------------------------
   const int t = tid, lane = tid & 31;
   const int j0base = t * M;
+  const unsigned T8 = (unsigned)T * 8u, stage_bytes = (unsigned)SW * 8u, ring32 = smem_u32(ring) + (unsigned)t * 8u;
   const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.L.nj - 1, M, T);
   unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
   double bS = 0.0, bN = 0.0;   // Dirichlet end values phi(i, jstart-1), phi(i, nj) of the current line
@@ -283,16 +285,17 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
       const unsigned s = rs, ph = rph;
       if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
       mbar_wait(full0 + 8 * s, ph);
-      const double* sl = ring + (size_t)s * SW + t;
-      double a = sl[0], b = sl[T], d = 1.0;
-      const double* sr = sl + 2 * T;      // ae, aw, su, phiE, phiW follow (after ap when it is stored)
+      // slice layout: an, as, [ap], ae, aw, su, phiE, phiW -- T doubles each
+      const unsigned sl = ring32 + s * stage_bytes;
+      double a = lds_f64(sl), b = lds_f64(sl + T8), d = 1.0;
+      unsigned sr = sl + 2 * T8;
       if (nc == 6) {
-        d = sl[2 * T];
-        sr += T;
+        d = lds_f64(sr);
+        sr += T8;
       }
-      double c = sr[2 * T];
-      if (!zeroW) c = fma(sr[T], sr[4 * T], c);
-      if (!zeroE) c = fma(sr[0], sr[3 * T], c);
+      double c = lds_f64(sr + 2 * T8);
+      if (!zeroW) c = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), c);
+      if (!zeroE) c = fma(lds_f64(sr), lds_f64(sr + 3 * T8), c);
       __syncwarp();
       if (lane == 0) mbar_arrive(empty0 + 8 * s);
       const int j0 = j0base + k;
@@ -452,16 +455,20 @@ template <int M>
 static int launch_tma_m(cfd_ctx* c, const SweepParams& P, int nblocks, int S, size_t smem) {
   const int nthreads = P.L.T + 32;
   cudaError_t e = cudaSuccess;
-  if (nthreads <= 352) {
-    e = cudaFuncSetAttribute(k_tdma_tma<M, 352>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_tdma_tma<M, 352><<<nblocks, nthreads, smem, c->stream>>>(P, S);
-  } else if (nthreads <= 672) {
-    e = cudaFuncSetAttribute(k_tdma_tma<M, 672>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_tdma_tma<M, 672><<<nblocks, nthreads, smem, c->stream>>>(P, S);
-  } else {
-    e = cudaFuncSetAttribute(k_tdma_tma<M, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_tdma_tma<M, 1024><<<nblocks, nthreads, smem, c->stream>>>(P, S);
+#define LAUNCH_TDMA(BM, NCV)                                                                                   \
+  {                                                                                                           \
+    e = cudaFuncSetAttribute(k_tdma_tma<M, BM, NCV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    k_tdma_tma<M, BM, NCV><<<nblocks, nthreads, smem, c->stream>>>(P, S);                                      \
   }
+  const bool five = P.L.nc == 5;
+  if (nthreads <= 352) {
+    if (five) LAUNCH_TDMA(352, 5) else LAUNCH_TDMA(352, 6)
+  } else if (nthreads <= 672) {
+    if (five) LAUNCH_TDMA(672, 5) else LAUNCH_TDMA(672, 6)
+  } else {
+    if (five) LAUNCH_TDMA(1024, 5) else LAUNCH_TDMA(1024, 6)
+  }
+#undef LAUNCH_TDMA
   ++c->launches;
   return e == cudaSuccess ? CFD_OK : CFD_ERR_CUDA;
 }

@@ -30,4 +30,10 @@ __device__ __forceinline__ void consumer_sync(int nthreads) {
   asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
+// 64-bit load from a 32-bit shared-state-space address (keeps the per-slice address arithmetic in 32 bits)
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
 }  // namespace cfd
