@@ -145,7 +145,7 @@ def run_reference(args):
            "cpu_baseline": {"value": glups, "unit": "GLUPS", "cores": 1, "kind": "port", "sample": sample,
                             "host_cores_available": os.cpu_count()},
            "e2e": {"value": glups, "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -293,7 +293,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_cavity(args.cpu_budget)
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -362,10 +362,32 @@ def run_heat(args):
            "clocks": clocks,
            "cpu_baseline": {"value": m * m * nst / tcpu / 1e9, "unit": "GLUPS", "cores": 1, "kind": "port",
                             "sample": f"{nst} FTCS steps on a {m}x{m} sample grid, oracle/heat_oracle.c gcc -O3 -march=native, 1 thread"}}
-    print(json.dumps(out), flush=True)
+    emit(out)
+
+
+_REAL_STDOUT = None
+
+
+def _capture_stdout():
+    """Rank 0 must print exactly ONE JSON line on stdout.  Libraries (NCCL prints its version banner) write to
+    fd 1 directly, so fd 1 is pointed at stderr for the whole run and the JSON line goes to the saved fd."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, line)
+    else:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
 
 
 def main():
+    _capture_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=400)
