@@ -101,6 +101,7 @@ SYMBOLS = {
     "cfd_heat2d_step": (C.c_int, [_vp, C.c_int]),
     "cfd_heat2d_step_exact": (C.c_int, [_vp, C.c_int]),
     "cfd_heat2d_implicit_step": (C.c_int, [_vp, C.c_int]),
+    "cfd_heat2d_implicit_step_exact": (C.c_int, [_vp, C.c_int]),
     "cfd_heat_device_view": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
     "cfd_heat_synchronize": (C.c_int, [_vp]),
     "cfd_fdcav_create": (C.c_int, [C.POINTER(_vp), C.POINTER(CfdFdcavConfig)]),

@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(128) k_ftcs(const HeatParams P) {
 // ---------------------------------------------------------------------------------------------------
 struct LodParams {
   int nx, ny;
-  double fox, foy, dt, rho, cp, xa, dx, qthr, qval;
+  double fox, foy, dt, rho, cp, xa, dx, qthr, qval, qdt;
   double tleft, tright, tbottom, ttop;
   const double *ex, *tx, *ey, *ty;
   double* t;
@@ -119,6 +119,7 @@ __global__ void k_lod_bc(const LodParams P) {
 
 // x-lines: a warp owns 32 interior rows and walks along x in 32-column tiles, transposing through shared memory
 // so that global accesses are 256-byte row segments while each lane runs the recurrence of "its" row.
+template <bool EXACT>
 __global__ void __launch_bounds__(128) k_lod_x(const LodParams P) {
   __shared__ double tile[4][32][33];
   const int lane = threadIdx.x, w = threadIdx.y;
@@ -129,28 +130,42 @@ __global__ void __launch_bounds__(128) k_lod_x(const LodParams P) {
   const int myrow = row0 + lane;
   const bool rowok = myrow <= P.ny - 2;
   double (*tl)[33] = tile[w];
-  // forward sweep: f overwrites T
-  double fprev = 0.0;
-  for (int tI = 0; tI < ntile; ++tI) {
-    const int c0 = tI * 32;
+  // Each lane keeps the NEXT tile's 32 row segments in registers while "its" row of the current tile is solved,
+  // so the global-load latency overlaps the serial recurrence.
+  double nxt[32];
+  auto fetch = [&](int c0) {
+#pragma unroll
     for (int r = 0; r < 32; ++r) {
       const int j = row0 + r;
-      tl[r][lane] = (j <= P.ny - 2 && c0 + lane < nx) ? P.t[(size_t)j * snx + c0 + lane] : 0.0;
+      nxt[r] = (j <= P.ny - 2 && c0 + lane < nx && c0 >= 0) ? P.t[(size_t)j * snx + c0 + lane] : 0.0;
     }
+  };
+  // forward sweep: f overwrites T
+  double fprev = 0.0;
+  fetch(0);
+  for (int tI = 0; tI < ntile; ++tI) {
+    const int c0 = tI * 32;
+#pragma unroll
+    for (int r = 0; r < 32; ++r) tl[r][lane] = nxt[r];
     __syncwarp();
+    if (tI + 1 < ntile) fetch(c0 + 32);
     if (rowok) {
       for (int k = 0; k < 32 && c0 + k < nx; ++k) {
         const int i = c0 + k;
         double d = tl[lane][k], f;
         if (i == 0) {
-          f = __ddiv_rn(d, 1.0);
+          f = d;
         } else if (i == nx - 1) {
-          f = __ddiv_rn(__dsub_rn(d, __dmul_rn(0.0, fprev)), __ldg(P.tx + i));
-        } else {
+          f = d;                      // a = 0, temp = 1
+        } else if (EXACT) {
           const double xi = __dadd_rn(P.xa, __dmul_rn((double)i, P.dx));
           const double q = (xi < P.qthr) ? P.qval : 0.0;
           d = __dadd_rn(d, __ddiv_rn(__ddiv_rn(__dmul_rn(P.dt, q), P.rho), P.cp));
           f = __ddiv_rn(__dsub_rn(d, __dmul_rn(-P.fox, fprev)), __ldg(P.tx + i));
+        } else {                      // production: reciprocal pivots, FMAs (agrees to a few ulp)
+          const double xi = __dadd_rn(P.xa, __dmul_rn((double)i, P.dx));
+          d += (xi < P.qthr) ? P.qdt : 0.0;
+          f = fma(P.fox, fprev, d) * __ldg(P.tx + i);
         }
         tl[lane][k] = f;
         fprev = f;
@@ -165,19 +180,20 @@ __global__ void __launch_bounds__(128) k_lod_x(const LodParams P) {
   }
   // back substitution: x overwrites f, tiles right to left
   double xnext = 0.0;
+  __threadfence_block();
+  fetch((ntile - 1) * 32);
   for (int tI = ntile - 1; tI >= 0; --tI) {
     const int c0 = tI * 32;
-    for (int r = 0; r < 32; ++r) {
-      const int j = row0 + r;
-      tl[r][lane] = (j <= P.ny - 2 && c0 + lane < nx) ? P.t[(size_t)j * snx + c0 + lane] : 0.0;
-    }
+#pragma unroll
+    for (int r = 0; r < 32; ++r) tl[r][lane] = nxt[r];
     __syncwarp();
+    if (tI > 0) fetch(c0 - 32);
     if (rowok) {
       for (int k = 31; k >= 0; --k) {
         const int i = c0 + k;
         if (i >= nx) continue;
         const double f = tl[lane][k];
-        const double x = (i == nx - 1) ? f : __dsub_rn(f, __dmul_rn(__ldg(P.ex + i), xnext));
+        const double x = (i == nx - 1) ? f : (EXACT ? __dsub_rn(f, __dmul_rn(__ldg(P.ex + i), xnext)) : fma(-__ldg(P.ex + i), xnext, f));
         tl[lane][k] = x;
         xnext = x;
       }
@@ -191,31 +207,60 @@ __global__ void __launch_bounds__(128) k_lod_x(const LodParams P) {
   }
 }
 
-// y-lines: one thread per interior column, consecutive threads = consecutive x (coalesced at every j)
+// y-lines: one thread per interior column, consecutive threads = consecutive x (coalesced at every j).  The
+// recurrence is serial in j but the loads are not: they are issued LOD_U rows ahead of the chain.
+#define LOD_U 16
+template <bool EXACT>
 __global__ void __launch_bounds__(128) k_lod_y(const LodParams P) {
   const int i = 1 + blockIdx.x * blockDim.x + threadIdx.x;
   if (i > P.nx - 2) return;
   const size_t nx = (size_t)P.nx;
+  const int ny = P.ny;
   double* col = P.t + i;
   double fprev = 0.0;
-  for (int j = 0; j < P.ny; ++j) {
-    const double d = col[(size_t)j * nx];
-    double f;
-    if (j == 0) {
-      f = __ddiv_rn(d, 1.0);
-    } else {
-      const double a = (j == P.ny - 1) ? 0.0 : -P.foy;
-      f = __ddiv_rn(__dsub_rn(d, __dmul_rn(a, fprev)), __ldg(P.ty + j));
+  for (int j0 = 0; j0 < ny; j0 += LOD_U) {
+    double d[LOD_U], tt[LOD_U];
+#pragma unroll
+    for (int r = 0; r < LOD_U; ++r) {
+      const int j = j0 + r;
+      d[r] = (j < ny) ? col[(size_t)j * nx] : 0.0;
+      tt[r] = (j < ny) ? __ldg(P.ty + j) : 1.0;
     }
-    col[(size_t)j * nx] = f;
-    fprev = f;
+#pragma unroll
+    for (int r = 0; r < LOD_U; ++r) {
+      const int j = j0 + r;
+      if (j < ny) {
+        double f;
+        if (j == 0 || j == ny - 1) {
+          f = d[r];                   // identity rows (a = 0, temp = 1)
+        } else if (EXACT) {
+          f = __ddiv_rn(__dsub_rn(d[r], __dmul_rn(-P.foy, fprev)), tt[r]);
+        } else {
+          f = fma(P.foy, fprev, d[r]) * tt[r];
+        }
+        col[(size_t)j * nx] = f;
+        fprev = f;
+      }
+    }
   }
   double xnext = 0.0;
-  for (int j = P.ny - 1; j >= 0; --j) {
-    const double f = col[(size_t)j * nx];
-    const double x = (j == P.ny - 1) ? f : __dsub_rn(f, __dmul_rn(__ldg(P.ey + j), xnext));
-    col[(size_t)j * nx] = x;
-    xnext = x;
+  for (int j0 = ny - 1; j0 >= 0; j0 -= LOD_U) {
+    double f[LOD_U], ee[LOD_U];
+#pragma unroll
+    for (int r = 0; r < LOD_U; ++r) {
+      const int j = j0 - r;
+      f[r] = (j >= 0) ? col[(size_t)j * nx] : 0.0;
+      ee[r] = (j >= 0) ? __ldg(P.ey + j) : 0.0;
+    }
+#pragma unroll
+    for (int r = 0; r < LOD_U; ++r) {
+      const int j = j0 - r;
+      if (j >= 0) {
+        const double x = (j == ny - 1) ? f[r] : (EXACT ? __dsub_rn(f[r], __dmul_rn(ee[r], xnext)) : fma(-ee[r], xnext, f[r]));
+        col[(size_t)j * nx] = x;
+        xnext = x;
+      }
+    }
   }
 }
 
@@ -375,7 +420,7 @@ static void thomas_constants(int n, double fo, std::vector<double>& e, std::vect
   }
 }
 
-extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) {
+static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   CFD_REQUIRE(h && nsteps >= 0, "bad argument");
   const cfd_heat_config& g = h->cfg;
   if (g.ny_global && g.ny_global != g.ny) {
@@ -400,6 +445,8 @@ extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) {
     all.insert(all.end(), tx.begin(), tx.end());
     all.insert(all.end(), ey.begin(), ey.end());
     all.insert(all.end(), ty.begin(), ty.end());
+    for (double v : tx) all.push_back(1.0 / v);      // reciprocal pivots for the production path
+    for (double v : ty) all.push_back(1.0 / v);
     CFD_CUDA(cudaMalloc(&h->thomas, all.size() * sizeof(double)));
     CFD_CUDA(cudaMemcpy(h->thomas, all.data(), all.size() * sizeof(double), cudaMemcpyHostToDevice));
   }
@@ -407,14 +454,27 @@ extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) {
   P.tx = h->thomas + nx;
   P.ey = h->thomas + 2 * (size_t)nx;
   P.ty = h->thomas + 2 * (size_t)nx + ny;
+  if (!exact) {
+    P.tx = h->thomas + 2 * (size_t)nx + 2 * (size_t)ny;
+    P.ty = P.tx + nx;
+  }
+  P.qdt = g.dt * g.qval / g.rho / g.cp;
   P.t = h->buf[h->cur];
   const int nmax = nx > ny ? nx : ny;
   for (int n = 0; n < nsteps; ++n) {
     k_lod_bc<<<(nmax + 127) / 128, 128, 0, h->stream>>>(P);
-    k_lod_x<<<(ny - 2 + 127) / 128, dim3(32, 4), 0, h->stream>>>(P);
-    k_lod_y<<<(nx - 2 + 127) / 128, 128, 0, h->stream>>>(P);
+    if (exact) {
+      k_lod_x<true><<<(ny - 2 + 127) / 128, dim3(32, 4), 0, h->stream>>>(P);
+      k_lod_y<true><<<(nx - 2 + 127) / 128, 128, 0, h->stream>>>(P);
+    } else {
+      k_lod_x<false><<<(ny - 2 + 127) / 128, dim3(32, 4), 0, h->stream>>>(P);
+      k_lod_y<false><<<(nx - 2 + 127) / 128, 128, 0, h->stream>>>(P);
+    }
     CFD_CUDA(cudaGetLastError());
     ++h->steps_done;
   }
   return CFD_OK;
 }
+
+extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) { return lod_steps(h, nsteps, false); }
+extern "C" int cfd_heat2d_implicit_step_exact(cfd_heat* h, int nsteps) { return lod_steps(h, nsteps, true); }

@@ -70,8 +70,9 @@ class Heat2D:
         fn = self.lib.cfd_heat2d_step_exact if exact else self.lib.cfd_heat2d_step
         check(fn(self._h, nsteps))
 
-    def implicit_step(self, nsteps: int = 1):
-        check(self.lib.cfd_heat2d_implicit_step(self._h, nsteps))
+    def implicit_step(self, nsteps: int = 1, exact: bool = False):
+        fn = self.lib.cfd_heat2d_implicit_step_exact if exact else self.lib.cfd_heat2d_implicit_step
+        check(fn(self._h, nsteps))
 
     def synchronize(self):
         check(self.lib.cfd_heat_synchronize(self._h))

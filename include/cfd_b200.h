@@ -213,6 +213,8 @@ int cfd_heat2d_step_exact(cfd_heat* h, int nsteps);
 /* nsteps implicit-Euler steps, locally one-dimensional: the tridiagonal assembly of
    implicit-time/fdm1d_explicit_heat_cond.f90:122-143 along x then y, batched Thomas (thomas, :147-184) */
 int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps);
+/* same, with IEEE divisions in the reference's operation order (bit-comparable with the oracle; slower) */
+int cfd_heat2d_implicit_step_exact(cfd_heat* h, int nsteps);
 int cfd_heat_device_view(cfd_heat* h, void** cur, long long* row_stride, int* nrows);
 int cfd_heat_synchronize(cfd_heat* h);
 

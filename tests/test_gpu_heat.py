@@ -78,9 +78,19 @@ def test_implicit_lod_bitwise(cfd, oracle, shape):
     t0 = noise(nx, ny, 7)
     h = cfd.Heat2D(nx, ny, dt=2.0e-4, tleft=1.0, tright=2.0, tbottom=3.0, ttop=4.0)
     h.upload(t0)
-    h.implicit_step(3)
+    h.implicit_step(3, exact=True)
     want = oracle.heat2d_lod(t0, 3, dt=2.0e-4, tbc=(1.0, 2.0, 3.0, 4.0))
     assert np.array_equal(h.download(), want)
+    h.close()
+    # production path (reciprocal pivots, FMAs): 1e-12 relative per step, restarting the oracle from the GPU state
+    h = cfd.Heat2D(nx, ny, dt=2.0e-4, tleft=1.0, tright=2.0, tbottom=3.0, ttop=4.0)
+    h.upload(t0)
+    cur = t0
+    for _ in range(3):
+        h.implicit_step(1)
+        want = oracle.heat2d_lod(cur, 1, dt=2.0e-4, tbc=(1.0, 2.0, 3.0, 4.0))
+        cur = h.download()
+        assert np.abs(cur - want).max() <= 1e-12 * np.abs(want).max()
     h.close()
 
 
