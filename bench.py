@@ -180,11 +180,17 @@ def run_ours(args):
     else:
         from cfd_b200.dist import SlabCavity
         solver = SlabCavity(NICV * world, NJCV, reynolds=REYNOLDS, stream=stream)
+        if os.environ.get("CFD_B200_GRAPH", "1") != "0":
+            with torch.cuda.stream(stream):
+                graphed = solver.enable_graph(stream)
+        else:
+            graphed = False
         step = solver.iterate_async
         sync_res = solver.residuals
         ctx0 = solver.ctx
         cells_total = NICV * world * NJCV
-        par = f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals"
+        par = (f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals, "
+               + ("one CUDA graph per outer iteration" if graphed else "eager launches"))
 
     def barrier():
         torch.cuda.synchronize()

@@ -217,7 +217,32 @@ class SlabCavity:
         self.comm.exchange(halo_ops(s.lines("den"), s.rank, s.world, s.hw, s.he, s.nown, HALO_W, HALO_E))
         self.comm.exchange(halo_ops(s.lines("vis"), s.rank, s.world, s.hw, s.he, s.nown, 1, 1))
 
+    def enable_graph(self, stream):
+        """Capture one outer iteration (kernels + NCCL halo exchanges) into a CUDA graph and replay it from then
+        on: one launch per iteration instead of ~85 host calls.  Falls back to eager issue if capture fails."""
+        torch = self.torch
+        try:
+            self._iterate_eager(2)                      # communicators, attributes, allocations: all warm
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                self._iterate_eager(1)
+            torch.cuda.synchronize()
+            self.graph = g
+        except Exception as e:                          # noqa: BLE001
+            self.graph = None
+            self.graph_error = repr(e)
+            torch.cuda.synchronize()
+        return self.graph is not None
+
     def iterate_async(self, n=1):
+        if getattr(self, "graph", None) is not None:
+            for _ in range(n):
+                self.graph.replay()
+            return
+        self._iterate_eager(n)
+
+    def _iterate_eager(self, n=1):
         s = self.slab
         for _ in range(n):
             for st in self.stages:
