@@ -180,7 +180,7 @@ def run_ours(args):
     else:
         from cfd_b200.dist import SlabCavity
         solver = SlabCavity(NICV * world, NJCV, reynolds=REYNOLDS, stream=stream)
-        if os.environ.get("CFD_B200_GRAPH", "1") != "0":
+        if os.environ.get("CFD_B200_GRAPH", "0") != "0":     # off by default: no gain measured, and teardown is slow
             with torch.cuda.stream(stream):
                 graphed = solver.enable_graph(stream)
         else:

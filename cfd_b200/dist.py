@@ -82,7 +82,16 @@ class TorchDistComm:
         self.dist.broadcast(t, src=src)
 
 
-def halo_ops(lines, rank: int, world: int, hw: int, he: int, nown: int, w: int = 1, e: int = 1):
+def colour_filter(lo: int, hi: int, istart: int, colour: int):
+    """After the colour pass `colour` of a sweep starting at line istart only lines with (i-istart)%2 == colour
+    changed.  Returns (west_halo_stale, east_halo_stale, my_first_changed, my_last_changed) for a slab owning
+    global lines lo..hi: which of the four single-line messages are needed at all."""
+    def changed(i):
+        return i >= istart and (i - istart) % 2 == colour
+    return changed(lo - 1), changed(hi + 1), changed(lo), changed(hi)
+
+
+def halo_ops(lines, rank: int, world: int, hw: int, he: int, nown: int, w: int = 1, e: int = 1, only=None):
     """P2P ops that refresh `w` west and `e` east halo lines of `lines` (tensor [ni_local, LD]).
 
     Local line layout: [hw halo lines | nown owned lines | he halo lines].  My west halo = the last lines my
@@ -90,17 +99,18 @@ def halo_ops(lines, rank: int, world: int, hw: int, he: int, nown: int, w: int =
     """
     ops = []
     first, last = hw, hw + nown - 1
+    rw, re_, sf, sl = only if only is not None else (True, True, True, True)
     if rank > 0:
         w_eff = min(w, hw)
-        if w_eff:
+        if w_eff and rw:
             ops.append(("recv", lines[first - w_eff:first], rank - 1))
-        if e:   # the west neighbour's east halo (it has one, since it has an east neighbour: me)
+        if e and sf:   # the west neighbour's east halo (it has one, since it has an east neighbour: me)
             ops.append(("send", lines[first:first + min(e, HALO_E)], rank - 1))
     if rank < world - 1:
         e_eff = min(e, he)
-        if e_eff:
+        if e_eff and re_:
             ops.append(("recv", lines[last + 1:last + 1 + e_eff], rank + 1))
-        if w:
+        if w and sl:
             ops.append(("send", lines[last + 1 - min(w, HALO_W):last + 1], rank + 1))
     return ops
 
@@ -111,16 +121,20 @@ class LocalComm:
     def __init__(self, world):
         self.world = world
 
-    def exchange_all(self, slabs, name, w=1, e=1):
+    def exchange_all(self, slabs, name, w=1, e=1, colour=None):
         for r in range(self.world - 1):
             a, b = slabs[r], slabs[r + 1]          # a is west of b
             la, lb = a.lines(name), b.lines(name)
             a_last, b_first = a.hw + a.nown - 1, b.hw
+            # same decisions the two ranks would take independently over messages
+            fa = colour_filter(a.lo, a.hi, *colour) if colour else (True,) * 4
+            fb = colour_filter(b.lo, b.hi, *colour) if colour else (True,) * 4
+            assert fa[3] == fb[0] and fa[1] == fb[2]   # sender and receiver agree
             we = min(w, b.hw)
-            if we:
+            if we and fb[0]:
                 lb[b_first - we:b_first].copy_(la[a_last + 1 - we:a_last + 1])
             ee = min(e, a.he)
-            if ee:
+            if ee and fa[1]:
                 la[a_last + 1:a_last + 1 + ee].copy_(lb[b_first:b_first + ee])
 
 
@@ -181,8 +195,8 @@ class Slab:
 
 # stages of one outer iteration: ("compute", fn(slab)) or ("halo", field, w, e) or ("ppref",)
 def iteration_stages(nswp):
-    st = [("halo", "u", 1, 1), ("halo", "v", 1, 1), ("halo", "p", 1, 0),
-          ("compute", lambda s: s.ctx.assemble_u()), ("halo", "du", 0, 1)]
+    st = [("halos", (("u", 1, 1), ("v", 1, 1), ("p", 1, 0))),
+          ("compute", lambda s: s.ctx.assemble_u()), ("halo", "du", 0, 1, None)]
     for name, istart, jstart, n, first in (("u", 3, 2, nswp[0], False), ("v", 2, 3, nswp[1], False), ("pp", 2, 2, nswp[2], True)):
         if name == "v":
             st.append(("compute", lambda s: s.ctx.assemble_v()))
@@ -192,7 +206,7 @@ def iteration_stages(nswp):
             for colour in (0, 1):
                 st.append(("compute", (lambda s, a=istart, b=jstart, f=name, c=colour, z=(first and k == 0):
                                        s.ctx.sweep(a, b, f, c, first=z))))
-                st.append(("halo", name, 1, 1))
+                st.append(("halo", name, 1, 1, (istart, colour)))   # only the lines of this colour moved
     st += [("ppref",), ("compute", lambda s: s.ctx.correct(s.ppref.data_ptr()))]
     return st
 
@@ -249,7 +263,13 @@ class SlabCavity:
                 if st[0] == "compute":
                     st[1](s)
                 elif st[0] == "halo":
-                    self.comm.exchange(halo_ops(s.lines(st[1]), s.rank, s.world, s.hw, s.he, s.nown, st[2], st[3]))
+                    only = colour_filter(s.lo, s.hi, *st[4]) if st[4] else None
+                    self.comm.exchange(halo_ops(s.lines(st[1]), s.rank, s.world, s.hw, s.he, s.nown, st[2], st[3], only))
+                elif st[0] == "halos":
+                    ops = []
+                    for name, w, e in st[1]:
+                        ops += halo_ops(s.lines(name), s.rank, s.world, s.hw, s.he, s.nown, w, e)
+                    self.comm.exchange(ops)
                 else:
                     if s.owner_of_pref:
                         s.ppref.copy_(s.ppref_element())
@@ -322,7 +342,10 @@ class LocalSlabCavity:
                     for s in self.slabs:
                         st[1](s)
                 elif st[0] == "halo":
-                    self.comm.exchange_all(self.slabs, st[1], st[2], st[3])
+                    self.comm.exchange_all(self.slabs, st[1], st[2], st[3], st[4])
+                elif st[0] == "halos":
+                    for name, w, e in st[1]:
+                        self.comm.exchange_all(self.slabs, name, w, e)
                 else:
                     owner = [s for s in self.slabs if s.owner_of_pref][0]
                     for s in self.slabs:

@@ -87,3 +87,15 @@ def test_heat_slab_extent():
         assert hs == (r > 0) and hn == (r < world - 1)
         tot += nloc - hs - hn
     assert tot == ny
+
+
+def test_colour_filter_sender_receiver_agree():
+    from cfd_b200.dist import colour_filter
+    for ni, world in ((40, 3), (4098, 8), (67, 5)):
+        parts = partition(ni, world)
+        for istart in (2, 3):
+            for colour in (0, 1):
+                for (alo, ahi), (blo, bhi) in zip(parts, parts[1:]):
+                    fa, fb = colour_filter(alo, ahi, istart, colour), colour_filter(blo, bhi, istart, colour)
+                    assert fa[3] == fb[0]      # a's last line changed  <=>  b's west halo is stale
+                    assert fa[1] == fb[2]      # a's east halo is stale <=>  b's first line changed
