@@ -110,6 +110,8 @@ SYMBOLS = {
     "cfd_fdcav_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_fdcav_predict": (C.c_int, [_vp]),
     "cfd_fdcav_correct": (C.c_int, [_vp, _dp]),
+    "cfd_fdcav_solve_pp": (C.c_int, [_vp, _ip]),
+    "cfd_fdcav_step": (C.c_int, [_vp, _dp, _ip]),
     "cfd_version": (C.c_char_p, []),
 }
 

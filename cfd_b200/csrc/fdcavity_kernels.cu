@@ -14,7 +14,16 @@ struct cfd_fdcav {
   double* f[CFD_FDC_FIELD_COUNT];
   double* partial;
   int npartial;
+  // SIP solver work space (cfd_fdcav_solve_pp): 6 arrays, band progress counters, block partials, info, rsm
+  double* sip_work;
+  unsigned long long* sip_prog;
+  double* sip_partial;
+  int* sip_info;
+  double* sip_rsm;
 };
+int cfd_launch_sip(int device, cudaStream_t stream, int ni, int nj, double aw, double ae, double as, double an, double ap,
+                   const double* su, double* phi, double* work, unsigned long long* prog, double* partial, int* info,
+                   double* rsm_out, int max_partials);
 
 namespace cfd {
 
@@ -163,6 +172,11 @@ extern "C" int cfd_fdcav_create(cfd_fdcav** out, const cfd_fdcav_config* cfg) {
   h->device = dev;
   h->stream = 0;
   h->partial = nullptr;
+  h->sip_work = nullptr;
+  h->sip_prog = nullptr;
+  h->sip_partial = nullptr;
+  h->sip_info = nullptr;
+  h->sip_rsm = nullptr;
   for (auto& f : h->f) f = nullptr;
   const size_t bytes = (size_t)(cfg->ni + 1) * (cfg->nj + 1) * sizeof(double);
   for (auto& f : h->f) {
@@ -185,6 +199,11 @@ extern "C" int cfd_fdcav_destroy(cfd_fdcav* h) {
   cudaDeviceSynchronize();
   for (auto& f : h->f) if (f) cudaFree(f);
   if (h->partial) cudaFree(h->partial);
+  if (h->sip_work) cudaFree(h->sip_work);
+  if (h->sip_prog) cudaFree(h->sip_prog);
+  if (h->sip_partial) cudaFree(h->sip_partial);
+  if (h->sip_info) cudaFree(h->sip_info);
+  if (h->sip_rsm) cudaFree(h->sip_rsm);
   delete h;
   return CFD_OK;
 }
@@ -235,4 +254,42 @@ extern "C" int cfd_fdcav_correct(cfd_fdcav* h, double* error) {
     CFD_CUDA(cudaStreamSynchronize(h->stream));
   }
   return CFD_OK;
+}
+
+// sipsol (fdm_explicit_cavity.f90:24-87) for the p' system of the current step, entirely on the device
+extern "C" int cfd_fdcav_solve_pp(cfd_fdcav* h, int* iters) {
+  CFD_REQUIRE(h, "null context");
+  CFD_CUDA(cudaSetDevice(h->device));
+  const int ni = h->cfg.ni, nj = h->cfg.nj;
+  const size_t n = (size_t)(ni + 1) * (nj + 1);
+  if (!h->sip_work) {
+    CFD_CUDA(cudaMalloc(&h->sip_work, 6 * n * sizeof(double)));
+    CFD_CUDA(cudaMalloc(&h->sip_prog, (size_t)((nj + 31) / 32 + 1) * sizeof(unsigned long long)));
+    CFD_CUDA(cudaMalloc(&h->sip_partial, 1024 * sizeof(double)));
+    CFD_CUDA(cudaMalloc(&h->sip_info, 2 * sizeof(int)));
+    CFD_CUDA(cudaMalloc(&h->sip_rsm, sizeof(double)));
+  }
+  const double dx = 1.0 / (ni - 1), dy = 1.0 / (nj - 1), dt = h->cfg.dt;
+  const double ax = dt / (dx * dx), ay = dt / (dy * dy);
+  const double ap = 2 * (dt / (dx * dx) + dt / (dy * dy));
+  int rc = cfd_launch_sip(h->device, h->stream, ni, nj, -ax, -ax, -ay, -ay, ap, h->f[CFD_FDC_SU], h->f[CFD_FDC_PP],
+                          h->sip_work, h->sip_prog, h->sip_partial, h->sip_info, h->sip_rsm, 1024);
+  if (rc) return rc;
+  int info[2] = {0, 0};
+  CFD_CUDA(cudaMemcpyAsync(info, h->sip_info, sizeof(info), cudaMemcpyDeviceToHost, h->stream));
+  CFD_CUDA(cudaStreamSynchronize(h->stream));
+  if (info[1]) {
+    cfd_set_error("cfd_fdcav_solve_pp: wavefront wait abandoned (pipeline stalled)");
+    return CFD_ERR_CUDA;
+  }
+  if (iters) *iters = info[0];
+  return CFD_OK;
+}
+
+// one pass of the time loop fdm_explicit_cavity.f90:168-255 on the device
+extern "C" int cfd_fdcav_step(cfd_fdcav* h, double* error, int* sip_iters) {
+  int rc = cfd_fdcav_predict(h);
+  if (rc) return rc;
+  if ((rc = cfd_fdcav_solve_pp(h, sip_iters))) return rc;
+  return cfd_fdcav_correct(h, error);
 }

@@ -1,0 +1,270 @@
+// sip_kernels.cu -- Stone's strongly implicit procedure (SIP) for the 5-point p' equation of the explicit
+// finite-difference cavity solver: sipsol, lid-driven-cavity-2d/fdm-explicit/fdm_explicit_cavity.f90:24-87
+// (incomplete LU factors :44-55, residual + forward substitution :59-67, backward substitution + update :71-76,
+// stop rule :78-85; maxit 600, alpha 0.88, tol 1e-5).
+//
+// Every step of the algorithm has a recurrence in BOTH grid directions (cell (i,j) needs (i-1,j) and (i,j-1)), so
+// the parallelism is a wavefront.  One persistent cooperative kernel runs the whole solve: the rows are cut into
+// bands of 32 (one warp per band), a warp walks its band chunk by chunk (32 columns) and solves each 32x32 tile
+// in shared memory along its 63 anti-diagonals; band b may work on chunk c as soon as band b-1 has published
+// chunk c (a release/acquire progress counter per band in global memory), so the bands form a software pipeline
+// that keeps nj/32 warps busy.  Tiles are read and written as 256-byte row segments.  The backward substitution
+// is the same scheme mirrored.  Between the phases of an iteration the grid synchronises (cooperative groups);
+// the residual norm is reduced in a fixed order, so every block takes the same stop decision.
+// Operation order and non-contracted IEEE arithmetic as in the reference: the result is bit-identical to
+// oracle/fdcavity_oracle.c:orc_fdc_sipsol whenever the iteration counts agree (they differ only if the ratio
+// rsm lands within rounding of tol).
+#include <cooperative_groups.h>
+#include "common.cuh"
+namespace cg = cooperative_groups;
+
+namespace cfd {
+
+struct SipParams {
+  int ni, nj, ld;            // arrays are (ni+1, nj+1) column-major with leading dimension ld; interior 2..ni x 2..nj
+  double aw, ae, as, an, ap; // constant coefficients as passed to sipsol (already negated by the caller, :206)
+  double alpha, tol;
+  int maxit;
+  const double* su;
+  double* phi;
+  double *lw, *ls, *lpr, *un, *ue, *res;   // work arrays, same shape
+  unsigned long long* prog;  // one progress counter per band
+  double* partial;           // per-block residual partial sums
+  int* info;                 // [0] iterations used, [1] abort flag
+  double* rsm_out;
+};
+
+#define SIP_W 4              // warps (bands) per block
+#define TS 33                // padded tile stride
+
+__device__ __forceinline__ unsigned long long ld_acquire(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// wait until band `b` has published at least `target`; returns false if the wait was abandoned
+__device__ __forceinline__ bool wait_band(const SipParams& P, int b, unsigned long long target) {
+  unsigned spins = 0;
+  while (ld_acquire(P.prog + b) < target) {
+    __nanosleep(64);
+    if (++spins > (1u << 24) || *(volatile int*)(P.info + 1)) {
+      P.info[1] = 1;
+      return false;
+    }
+  }
+  return true;
+}
+
+// load / store one 32x32 tile (rows jb..jb+31, columns c0..c0+31, 0-based) as coalesced row segments
+__device__ __forceinline__ void tile_load(double* tl, const double* g, int ld, int c0, int jb, int imax, int jmax, int lane) {
+  for (int r = 0; r < 32; ++r) {
+    const int i = c0 + lane, j = jb + r;
+    tl[r * TS + lane] = (i >= 1 && i <= imax && j >= 1 && j <= jmax) ? g[(size_t)j * ld + i] : 0.0;
+  }
+}
+__device__ __forceinline__ void tile_store(const double* tl, double* g, int ld, int c0, int jb, int imax, int jmax, int lane) {
+  for (int r = 0; r < 32; ++r) {
+    const int i = c0 + lane, j = jb + r;
+    if (i >= 1 && i <= imax && j >= 1 && j <= jmax) g[(size_t)j * ld + i] = tl[r * TS + lane];
+  }
+}
+
+// PHASE 0: incomplete LU factors (:44-55); 1: forward substitution (:64-65); 2: backward substitution + update (:71-76)
+template <int PHASE>
+__device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long epoch_base, int nbands, int nchunks) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int imax = P.ni - 1, jmax = P.nj - 1;          // interior 0-based: 1..imax, 1..jmax
+  double* t0 = sm + (size_t)w * (4 * 32 * TS + 4 * 32);
+  double *A = t0, *B = A + 32 * TS, *C = B + 32 * TS, *D = C + 32 * TS;   // tiles
+  double *row0 = D + 32 * TS, *row1 = row0 + 32, *col0 = row1 + 32, *col1 = col0 + 32;
+  const bool fwd = PHASE != 2;
+  for (int bb = blockIdx.x * SIP_W + w; bb < nbands; bb += gridDim.x * SIP_W) {
+    const int b = fwd ? bb : nbands - 1 - bb;           // band processed (backward: from the top)
+    const int jb = 1 + 32 * b;
+    col0[lane] = 0.0;                                   // values of the column just outside the first chunk
+    col1[lane] = 0.0;
+    __syncwarp();
+    for (int cc = 0; cc < nchunks; ++cc) {
+      const int c = fwd ? cc : nchunks - 1 - cc;
+      const int c0 = 1 + 32 * c;
+      if (bb > 0) {                                     // the band processed just before this one (other warp/block)
+        const int dep = fwd ? b - 1 : b + 1;
+        if (!wait_band(P, dep, epoch_base + (unsigned long long)cc + 1)) return;
+      }
+      // row just outside the tile in the sweep direction (south for forward phases, north for backward)
+      {
+        const int jn = fwd ? jb - 1 : jb + 32, i = c0 + lane;
+        const bool ok = jn >= 1 && jn <= jmax && i >= 1 && i <= imax;
+        if (PHASE == 0) {
+          row0[lane] = ok ? P.un[(size_t)jn * P.ld + i] : 0.0;
+          row1[lane] = ok ? P.ue[(size_t)jn * P.ld + i] : 0.0;
+        } else {
+          row0[lane] = ok ? P.res[(size_t)jn * P.ld + i] : 0.0;
+        }
+      }
+      if (PHASE == 1) {
+        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(B, P.ls, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(C, P.lw, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(D, P.lpr, P.ld, c0, jb, imax, jmax, lane);
+      } else if (PHASE == 2) {
+        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(B, P.un, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(C, P.ue, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(D, P.phi, P.ld, c0, jb, imax, jmax, lane);
+      }
+      __syncwarp();
+      for (int d = 0; d < 63; ++d) {
+        const int r = fwd ? lane : 31 - lane;           // row inside the tile
+        const int q = fwd ? d - lane : 31 - (d - lane); // column inside the tile
+        const bool act = (d - lane) >= 0 && (d - lane) < 32 && (c0 + q) <= imax && (jb + r) <= jmax;
+        if (act) {
+          const int k = r * TS + q;
+          if (PHASE == 0) {
+            // west / south neighbours of the factors un, ue
+            const double un_w = (q == 0) ? col0[r] : A[k - 1], ue_w = (q == 0) ? col1[r] : B[k - 1];
+            const double un_s = (r == 0) ? row0[q] : A[k - TS], ue_s = (r == 0) ? row1[q] : B[k - TS];
+            const double lw = __ddiv_rn(P.aw, __dadd_rn(1.0, __dmul_rn(P.alpha, un_w)));
+            const double ls = __ddiv_rn(P.as, __dadd_rn(1.0, __dmul_rn(P.alpha, ue_s)));
+            const double p1 = __dmul_rn(__dmul_rn(P.alpha, lw), un_w);
+            const double p2 = __dmul_rn(__dmul_rn(P.alpha, ls), ue_s);
+            const double den = __dsub_rn(__dsub_rn(__dadd_rn(__dadd_rn(P.ap, p1), p2), __dmul_rn(lw, ue_w)), __dmul_rn(ls, un_s));
+            const double lpr = __ddiv_rn(1.0, den);
+            A[k] = __dmul_rn(__dsub_rn(P.an, p1), lpr);   // un
+            B[k] = __dmul_rn(__dsub_rn(P.ae, p2), lpr);   // ue
+            C[k] = lw;
+            D[k] = ls;
+            // lpr goes straight to global memory (a fifth tile would not fit the budget)
+            P.lpr[(size_t)(jb + r) * P.ld + c0 + q] = lpr;
+          } else if (PHASE == 1) {
+            const double rs = (r == 0) ? row0[q] : A[k - TS], rw = (q == 0) ? col0[r] : A[k - 1];
+            A[k] = __dmul_rn(__dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], rs)), __dmul_rn(C[k], rw)), D[k]);
+          } else {
+            const double rn = (r == 31) ? row0[q] : A[k + TS], re = (q == 31) ? col0[r] : A[k + 1];
+            const double v = __dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], rn)), __dmul_rn(C[k], re));
+            A[k] = v;
+            D[k] = __dadd_rn(D[k], v);
+          }
+        }
+        __syncwarp();
+      }
+      // keep the column next to the following chunk, write the tile back, publish
+      {
+        const int qe = fwd ? 31 : 0;
+        col0[lane] = A[lane * TS + qe];
+        if (PHASE == 0) col1[lane] = B[lane * TS + qe];
+      }
+      if (PHASE == 0) {
+        tile_store(A, P.un, P.ld, c0, jb, imax, jmax, lane);
+        tile_store(B, P.ue, P.ld, c0, jb, imax, jmax, lane);
+        tile_store(C, P.lw, P.ld, c0, jb, imax, jmax, lane);
+        tile_store(D, P.ls, P.ld, c0, jb, imax, jmax, lane);
+      } else if (PHASE == 1) {
+        tile_store(A, P.res, P.ld, c0, jb, imax, jmax, lane);
+      } else {
+        tile_store(A, P.res, P.ld, c0, jb, imax, jmax, lane);
+        tile_store(D, P.phi, P.ld, c0, jb, imax, jmax, lane);
+      }
+      __threadfence();
+      __syncwarp();
+      if (lane == 0) st_release(P.prog + b, epoch_base + (unsigned long long)cc + 1);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(32 * SIP_W) k_sip_solve(const SipParams P) {
+  extern __shared__ double sm[];
+  cg::grid_group grid = cg::this_grid();
+  const int imax = P.ni - 1, jmax = P.nj - 1;
+  const int nbands = (jmax + 31) / 32, nchunks = (imax + 31) / 32;
+  const unsigned long long stride = (unsigned long long)nchunks + 1;
+  unsigned long long epoch = 1;
+  // ---- incomplete factorisation
+  sip_wavefront<0>(P, sm, epoch * stride, nbands, nchunks);
+  ++epoch;
+  grid.sync();
+  double res1 = 0.0, rsm = 0.0;
+  int iter = 0;
+  for (iter = 1; iter <= P.maxit; ++iter) {
+    // ---- residual (:61-63) and its 1-norm, fixed-order reduction
+    double acc = 0.0;
+    const long long ncell = (long long)imax * jmax;
+    for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < ncell; n += (long long)gridDim.x * blockDim.x) {
+      const int i = 1 + (int)(n % imax), j = 1 + (int)(n / imax);
+      const size_t k = (size_t)j * P.ld + i;
+      double r = __dsub_rn(P.su[k], __dmul_rn(P.aw, P.phi[k - 1]));
+      r = __dsub_rn(r, __dmul_rn(P.ae, P.phi[k + 1]));
+      r = __dsub_rn(r, __dmul_rn(P.an, P.phi[k + P.ld]));
+      r = __dsub_rn(r, __dmul_rn(P.as, P.phi[k - P.ld]));
+      r = __dsub_rn(r, __dmul_rn(P.ap, P.phi[k]));
+      P.res[k] = r;
+      acc += fabs(r);
+    }
+    {
+      __shared__ double wsum[SIP_W];
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+      if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int k = 0; k < SIP_W; ++k) s += wsum[k];
+        P.partial[blockIdx.x] = s;
+      }
+    }
+    grid.sync();
+    double resl = 0.0;
+    for (unsigned k = 0; k < gridDim.x; ++k) resl += P.partial[k];   // same order in every block
+    if (iter == 1) res1 = resl;
+    rsm = resl / res1;
+    // ---- forward and backward substitution
+    sip_wavefront<1>(P, sm, epoch * stride, nbands, nchunks);
+    ++epoch;
+    grid.sync();
+    sip_wavefront<2>(P, sm, epoch * stride, nbands, nchunks);
+    ++epoch;
+    grid.sync();
+    if (rsm < P.tol) break;
+    if (iter == 1 && res1 < 1.0e-10) break;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    P.info[0] = iter > P.maxit ? P.maxit : iter;
+    *P.rsm_out = rsm;
+  }
+}
+
+}  // namespace cfd
+using namespace cfd;
+
+// Solve the p' system of one explicit FD-cavity step on the device.  Work arrays are owned by the caller.
+int cfd_launch_sip(int device, cudaStream_t stream, int ni, int nj, double aw, double ae, double as, double an, double ap,
+                   const double* su, double* phi, double* work, unsigned long long* prog, double* partial, int* info,
+                   double* rsm_out, int max_partials) {
+  SipParams P{};
+  P.ni = ni; P.nj = nj; P.ld = ni + 1;
+  P.aw = aw; P.ae = ae; P.as = as; P.an = an; P.ap = ap;
+  P.alpha = 0.88; P.tol = 1.0e-5; P.maxit = 600;
+  P.su = su; P.phi = phi;
+  const size_t n = (size_t)(ni + 1) * (nj + 1);
+  P.lw = work; P.ls = work + n; P.lpr = work + 2 * n; P.un = work + 3 * n; P.ue = work + 4 * n; P.res = work + 5 * n;
+  P.prog = prog; P.partial = partial; P.info = info; P.rsm_out = rsm_out;
+  const int nbands = (nj - 1 + 31) / 32;
+  const size_t smem = (size_t)SIP_W * (4 * 32 * TS + 4 * 32) * sizeof(double);
+  CFD_CUDA(cudaFuncSetAttribute(k_sip_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0, nsm = 0;
+  CFD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sip_solve, 32 * SIP_W, smem));
+  CFD_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
+  int grid = (nbands + SIP_W - 1) / SIP_W;
+  if (grid > per_sm * nsm) grid = per_sm * nsm;
+  if (grid > max_partials) grid = max_partials;
+  if (grid < 1) grid = 1;
+  CFD_CUDA(cudaMemsetAsync(work, 0, 6 * n * sizeof(double), stream));
+  CFD_CUDA(cudaMemsetAsync(prog, 0, (size_t)nbands * sizeof(unsigned long long), stream));
+  CFD_CUDA(cudaMemsetAsync(info, 0, 2 * sizeof(int), stream));
+  void* args[] = {(void*)&P};
+  CFD_CUDA(cudaLaunchCooperativeKernel((void*)k_sip_solve, dim3(grid), dim3(32 * SIP_W), args, smem, stream));
+  return CFD_OK;
+}

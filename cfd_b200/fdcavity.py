@@ -54,7 +54,19 @@ class FDCavity:
         check(self.lib.cfd_fdcav_correct(self._h, C.byref(e)))
         return e.value
 
-    def step(self, solve_pp) -> float:
+    def solve_pp(self) -> int:
+        """sipsol on the device (fdm_explicit_cavity.f90:24-87); returns the SIP iterations used."""
+        it = C.c_int()
+        check(self.lib.cfd_fdcav_solve_pp(self._h, C.byref(it)))
+        return it.value
+
+    def step(self, solve_pp=None) -> float:
+        """One time step.  solve_pp=None: everything on the GPU; else a host callable su -> pp."""
+        if solve_pp is None:
+            e, it = C.c_double(), C.c_int()
+            check(self.lib.cfd_fdcav_step(self._h, C.byref(e), C.byref(it)))
+            self.sip_iters = it.value
+            return e.value
         self.predict()
         self.upload("pp", solve_pp(self.download("su")))
         return self.correct()

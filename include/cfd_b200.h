@@ -219,7 +219,7 @@ int cfd_heat_device_view(cfd_heat* h, void** cur, long long* row_stride, int* nr
 int cfd_heat_synchronize(cfd_heat* h);
 
 /* ---- explicit finite-difference cavity: stencil passes of lid-driven-cavity-2d/fdm-explicit/
-        fdm_explicit_cavity.f90 (the SIP solve of p' between the two calls is the caller's) ------ */
+        fdm_explicit_cavity.f90 (cfd_fdcav_solve_pp is the device SIP of SURVEY 8f-1) ------ */
 typedef enum cfd_fdc_field {
   CFD_FDC_U = 0, CFD_FDC_V, CFD_FDC_P, CFD_FDC_UO, CFD_FDC_VO, CFD_FDC_PO, CFD_FDC_PP, CFD_FDC_SU, CFD_FDC_FIELD_COUNT
 } cfd_fdc_field;
@@ -239,6 +239,11 @@ int cfd_fdcav_predict(cfd_fdcav* h);
 /* correction of p, u, v with the caller-solved pp (:208-222), boundary conditions (:224-237), continuity norm
    `error` (:239-247), uo=u, vo=v, po=p (:252-254) */
 int cfd_fdcav_correct(cfd_fdcav* h, double* error);
+/* sipsol (fdm_explicit_cavity.f90:24-87: Stone's SIP, maxit 600, alpha 0.88, tol 1e-5) on the p' system set up by
+   cfd_fdcav_predict, on the device; *iters receives the iterations used */
+int cfd_fdcav_solve_pp(cfd_fdcav* h, int* iters);
+/* one pass of the time loop (:168-255): predict, solve pp, correct */
+int cfd_fdcav_step(cfd_fdcav* h, double* error, int* sip_iters);
 
 /* library/build identification */
 const char* cfd_version(void);

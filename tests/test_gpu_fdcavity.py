@@ -46,3 +46,34 @@ def test_fd_cavity_converges_to_reference_default(cfd, oracle):
         o.step()
     assert np.abs(g.download("u") - o.u).max() < 1e-12
     g.close()
+
+
+@pytest.mark.parametrize("shape", [(11, 11), (33, 33), (40, 24), (24, 40), (70, 130), (257, 257)])
+def test_device_sip_matches_sipsol(cfd, oracle, shape):
+    """Stone's SIP on the device (band-pipelined wavefront) against the restated sipsol: same iteration count,
+    same bits in pp."""
+    ni, nj = shape
+    dt = 1.0e-4 if ni < 100 else 2.0e-6
+    o = oracle.FDCavity(ni, nj, dt=dt)
+    g = cfd.FDCavity(ni, nj, dt=dt)
+    for it in range(4):
+        o.predict()
+        g.predict()
+        n_o = o.solve_pp()
+        n_g = g.solve_pp()
+        assert n_g == n_o, (it, n_g, n_o)
+        assert np.array_equal(g.download("pp"), o.pp)
+        e_o, e_g = o.correct(), g.correct()
+        assert abs(e_g - e_o) <= 1e-12 * abs(e_o)
+    g.close()
+
+
+def test_fd_cavity_fully_on_device_converges(cfd, oracle):
+    o = oracle.FDCavity()
+    g = cfd.FDCavity()
+    for it in range(3000):
+        eg = g.step()
+        eo = o.step()
+    assert np.array_equal(g.download("u"), o.u) or np.abs(g.download("u") - o.u).max() < 1e-13
+    assert eg < 1e-6
+    g.close()
