@@ -51,10 +51,10 @@ class CfdHeatConfig(C.Structure):
 
 class CfdFdcavConfig(C.Structure):
     _fields_ = [("ni", C.c_int), ("nj", C.c_int), ("re", C.c_double), ("dt", C.c_double), ("utop", C.c_double),
-                ("urfp", C.c_double), ("device", C.c_int)]
+                ("urfp", C.c_double), ("device", C.c_int), ("steady", C.c_int), ("urfu", C.c_double), ("urfv", C.c_double)]
 
 
-FDC_FIELDS = ("u", "v", "p", "uo", "vo", "po", "pp", "su")
+FDC_FIELDS = ("u", "v", "p", "uo", "vo", "po", "pp", "su", "ae", "aw", "an", "as", "ap")
 
 
 class CfdError(RuntimeError):
@@ -112,6 +112,10 @@ SYMBOLS = {
     "cfd_fdcav_correct": (C.c_int, [_vp, _dp]),
     "cfd_fdcav_solve_pp": (C.c_int, [_vp, _ip]),
     "cfd_fdcav_step": (C.c_int, [_vp, _dp, _ip]),
+    "cfd_fdcav_implicit_assemble": (C.c_int, [_vp, C.c_int]),
+    "cfd_fdcav_implicit_solve": (C.c_int, [_vp, C.c_int, _ip]),
+    "cfd_fdcav_implicit_correct": (C.c_int, [_vp, _dp]),
+    "cfd_fdcav_implicit_step": (C.c_int, [_vp, _dp, _ip]),
     "cfd_version": (C.c_char_p, []),
 }
 

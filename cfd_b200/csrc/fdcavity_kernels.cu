@@ -21,9 +21,9 @@ struct cfd_fdcav {
   int* sip_info;
   double* sip_rsm;
 };
-int cfd_launch_sip(int device, cudaStream_t stream, int ni, int nj, double aw, double ae, double as, double an, double ap,
-                   const double* su, double* phi, double* work, unsigned long long* prog, double* partial, int* info,
-                   double* rsm_out, int max_partials);
+int cfd_launch_sip(int device, cudaStream_t stream, int ld, int nrows, int imax, int jmax, const double* c,
+                   const double* const* coef, double alpha, double tol, int maxit, const double* su, double* phi, double* work,
+                   unsigned long long* prog, double* partial, int* info, double* rsm_out, int max_partials);
 
 namespace cfd {
 
@@ -31,6 +31,9 @@ struct FdcParams {
   int ni, nj, ld;
   double dx, dy, dt, re, utop, urfp;
   double *u, *v, *p, *uo, *vo, *po, *pp, *su;
+  double *ae, *aw, *an, *as, *ap;
+  double urfu, urfv;
+  int steady;
   double* partial;
 };
 #define B2(a, i, j) ((a)[(size_t)((i) - 1) + (size_t)((j) - 1) * (size_t)P.ld])
@@ -141,6 +144,81 @@ __global__ void k_fdc_norm_final(double* partial, int n) {
   if (threadIdx.x == 0) partial[0] = sqrt(sm[0]);
 }
 
+// ---- implicit-Euler variant: lid-driven-cavity-2d/fdm-implicit/fdm_implicit_cavity.f90 ----------------------------
+// which: 0 u-momentum coefficients :178-198, 1 v-momentum :201-220, 2 p' equation :222-240 (pp = 0 included)
+__global__ void __launch_bounds__(256) k_fdci_assemble(const FdcParams P, const int which) {
+  const int i = 1 + blockIdx.x * blockDim.x + threadIdx.x, j = 1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int ni = P.ni, nj = P.nj;
+  if (i > ni + 1 || j > nj + 1) return;
+  const double dx = P.dx, dy = P.dy;
+  const double rex = __ddiv_rn(__ddiv_rn(1.0, P.re), __dmul_rn(dx, dx)), rey = __ddiv_rn(__ddiv_rn(1.0, P.re), __dmul_rn(dy, dy));
+  const double pterm = __dadd_rn(__ddiv_rn(1.0, P.dt), __dmul_rn(2.0, __dadd_rn(rex, rey)));
+  const double *u = P.u, *v = P.v, *p = P.p;
+  if (which == 0) {
+    if (i < 2 || i > ni - 1 || j < 2 || j > nj) return;
+    const double vel1 = __dmul_rn(0.5, __dadd_rn(B2(v, i, j), B2(v, i + 1, j)));
+    const double vel2 = __dmul_rn(0.5, __dadd_rn(B2(v, i, j - 1), B2(v, i + 1, j - 1)));
+    B2(P.ae, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(-0.5, B2(u, i + 1, j)), dx), rex);
+    B2(P.aw, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(0.5, B2(u, i - 1, j)), dx), rex);
+    B2(P.an, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(-0.5, vel1), dy), rey);
+    B2(P.as, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(0.5, vel2), dy), rey);
+    double su, ap;
+    if (P.steady) {
+      su = __ddiv_rn(__dsub_rn(B2(p, i, j), B2(p, i + 1, j)), dx);
+      ap = __dmul_rn(2.0, __dadd_rn(rex, rey));
+    } else {
+      su = __dadd_rn(__ddiv_rn(B2(u, i, j), P.dt), __ddiv_rn(__dsub_rn(B2(p, i, j), B2(p, i + 1, j)), dx));
+      ap = pterm;
+    }
+    su = __dadd_rn(su, __dmul_rn(__ddiv_rn(__dmul_rn(__dsub_rn(1.0, P.urfu), ap), P.urfu), B2(u, i, j)));
+    B2(P.su, i, j) = su;
+    B2(P.ap, i, j) = __ddiv_rn(ap, P.urfu);
+  } else if (which == 1) {
+    if (i < 2 || i > ni || j < 2 || j > nj - 1) return;
+    const double vel1 = __dmul_rn(0.5, __dadd_rn(B2(u, i, j), B2(u, i, j + 1)));
+    const double vel2 = __dmul_rn(0.5, __dadd_rn(B2(u, i - 1, j), B2(u, i - 1, j + 1)));
+    B2(P.ae, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(-0.5, vel1), dx), rex);
+    B2(P.aw, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(0.5, vel2), dx), rex);
+    B2(P.an, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(-0.5, B2(v, i, j + 1)), dy), rey);
+    B2(P.as, i, j) = __dadd_rn(__ddiv_rn(__dmul_rn(-0.5, B2(v, i, j - 1)), dy), rey);   // sign as in the source (:208)
+    double su, ap;
+    if (P.steady) {
+      su = __ddiv_rn(__dsub_rn(B2(p, i, j), B2(p, i, j + 1)), dy);
+      ap = __dmul_rn(2.0, __dadd_rn(rex, rey));
+    } else {
+      su = __dadd_rn(__ddiv_rn(B2(v, i, j), P.dt), __ddiv_rn(__dsub_rn(B2(p, i, j), B2(p, i, j + 1)), dy));
+      ap = pterm;
+    }
+    su = __dadd_rn(su, __dmul_rn(__ddiv_rn(__dmul_rn(__dsub_rn(1.0, P.urfv), ap), P.urfv), B2(v, i, j)));
+    B2(P.su, i, j) = su;
+    B2(P.ap, i, j) = __ddiv_rn(ap, P.urfv);
+  } else {
+    B2(P.pp, i, j) = 0.0;
+    if (i < 2 || i > ni || j < 2 || j > nj) return;
+    const double base = P.steady ? __ddiv_rn(1.0, __dmul_rn(2.0, __dadd_rn(rex, rey))) : __ddiv_rn(1.0, pterm);
+    const double ax = __ddiv_rn(base, __dmul_rn(dx, dx)), ay = __ddiv_rn(base, __dmul_rn(dy, dy));
+    B2(P.ae, i, j) = ax;
+    B2(P.aw, i, j) = ax;
+    B2(P.an, i, j) = ay;
+    B2(P.as, i, j) = ay;
+    B2(P.ap, i, j) = __dadd_rn(__dadd_rn(__dadd_rn(ax, ax), ay), ay);
+    B2(P.su, i, j) = __dadd_rn(__ddiv_rn(__dsub_rn(B2(u, i - 1, j), B2(u, i, j)), dx), __ddiv_rn(__dsub_rn(B2(v, i, j - 1), B2(v, i, j)), dy));
+  }
+}
+
+// :243-258
+__global__ void __launch_bounds__(256) k_fdci_correct(const FdcParams P) {
+  const int i = 1 + blockIdx.x * blockDim.x + threadIdx.x, j = 1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int ni = P.ni, nj = P.nj;
+  if (i < 2 || i > ni || j < 2 || j > nj) return;
+  const double rex = __ddiv_rn(__ddiv_rn(1.0, P.re), __dmul_rn(P.dx, P.dx)), rey = __ddiv_rn(__ddiv_rn(1.0, P.re), __dmul_rn(P.dy, P.dy));
+  const double pterm = __dadd_rn(__ddiv_rn(1.0, P.dt), __dmul_rn(2.0, __dadd_rn(rex, rey)));
+  const double ppc = B2(P.pp, i, j);
+  B2(P.p, i, j) = __dadd_rn(B2(P.p, i, j), __dmul_rn(P.urfp, ppc));
+  if (i <= ni - 1) B2(P.u, i, j) = __dsub_rn(B2(P.u, i, j), __ddiv_rn(__ddiv_rn(__dsub_rn(B2(P.pp, i + 1, j), ppc), pterm), P.dx));
+  if (j <= nj - 1) B2(P.v, i, j) = __dsub_rn(B2(P.v, i, j), __ddiv_rn(__ddiv_rn(__dsub_rn(B2(P.pp, i, j + 1), ppc), pterm), P.dy));
+}
+
 }  // namespace cfd
 using namespace cfd;
 
@@ -150,6 +228,8 @@ static void fdc_fill(const cfd_fdcav* h, FdcParams& P) {
   P.dt = h->cfg.dt; P.re = h->cfg.re; P.utop = h->cfg.utop; P.urfp = h->cfg.urfp;
   P.u = h->f[CFD_FDC_U]; P.v = h->f[CFD_FDC_V]; P.p = h->f[CFD_FDC_P]; P.uo = h->f[CFD_FDC_UO]; P.vo = h->f[CFD_FDC_VO];
   P.po = h->f[CFD_FDC_PO]; P.pp = h->f[CFD_FDC_PP]; P.su = h->f[CFD_FDC_SU];
+  P.ae = h->f[CFD_FDC_AE]; P.aw = h->f[CFD_FDC_AW]; P.an = h->f[CFD_FDC_AN]; P.as = h->f[CFD_FDC_AS]; P.ap = h->f[CFD_FDC_AP];
+  P.urfu = h->cfg.urfu; P.urfv = h->cfg.urfv; P.steady = h->cfg.steady;
   P.partial = h->partial;
 }
 static dim3 fdc_grid(const cfd_fdcav* h) { return dim3((h->cfg.ni + 1 + 31) / 32, (h->cfg.nj + 1 + 7) / 8); }
@@ -256,34 +336,95 @@ extern "C" int cfd_fdcav_correct(cfd_fdcav* h, double* error) {
   return CFD_OK;
 }
 
-// sipsol (fdm_explicit_cavity.f90:24-87) for the p' system of the current step, entirely on the device
-extern "C" int cfd_fdcav_solve_pp(cfd_fdcav* h, int* iters) {
-  CFD_REQUIRE(h, "null context");
-  CFD_CUDA(cudaSetDevice(h->device));
-  const int ni = h->cfg.ni, nj = h->cfg.nj;
-  const size_t n = (size_t)(ni + 1) * (nj + 1);
+static int sip_alloc(cfd_fdcav* h) {
+  const size_t n = (size_t)(h->cfg.ni + 1) * (h->cfg.nj + 1);
   if (!h->sip_work) {
     CFD_CUDA(cudaMalloc(&h->sip_work, 6 * n * sizeof(double)));
-    CFD_CUDA(cudaMalloc(&h->sip_prog, (size_t)((nj + 31) / 32 + 1) * sizeof(unsigned long long)));
+    CFD_CUDA(cudaMalloc(&h->sip_prog, (size_t)((h->cfg.nj + 31) / 32 + 2) * sizeof(unsigned long long)));
     CFD_CUDA(cudaMalloc(&h->sip_partial, 1024 * sizeof(double)));
     CFD_CUDA(cudaMalloc(&h->sip_info, 2 * sizeof(int)));
     CFD_CUDA(cudaMalloc(&h->sip_rsm, sizeof(double)));
   }
-  const double dx = 1.0 / (ni - 1), dy = 1.0 / (nj - 1), dt = h->cfg.dt;
-  const double ax = dt / (dx * dx), ay = dt / (dy * dy);
-  const double ap = 2 * (dt / (dx * dx) + dt / (dy * dy));
-  int rc = cfd_launch_sip(h->device, h->stream, ni, nj, -ax, -ax, -ay, -ay, ap, h->f[CFD_FDC_SU], h->f[CFD_FDC_PP],
-                          h->sip_work, h->sip_prog, h->sip_partial, h->sip_info, h->sip_rsm, 1024);
-  if (rc) return rc;
+  return CFD_OK;
+}
+static int sip_finish(cfd_fdcav* h, int* iters) {
   int info[2] = {0, 0};
   CFD_CUDA(cudaMemcpyAsync(info, h->sip_info, sizeof(info), cudaMemcpyDeviceToHost, h->stream));
   CFD_CUDA(cudaStreamSynchronize(h->stream));
   if (info[1]) {
-    cfd_set_error("cfd_fdcav_solve_pp: wavefront wait abandoned (pipeline stalled)");
+    cfd_set_error("SIP: wavefront wait abandoned (pipeline stalled)");
     return CFD_ERR_CUDA;
   }
   if (iters) *iters = info[0];
   return CFD_OK;
+}
+
+// sipsol (fdm_explicit_cavity.f90:24-87) for the p' system of the current step, entirely on the device
+extern "C" int cfd_fdcav_solve_pp(cfd_fdcav* h, int* iters) {
+  CFD_REQUIRE(h, "null context");
+  CFD_CUDA(cudaSetDevice(h->device));
+  int rc = sip_alloc(h);
+  if (rc) return rc;
+  const int ni = h->cfg.ni, nj = h->cfg.nj;
+  const double dx = 1.0 / (ni - 1), dy = 1.0 / (nj - 1), dt = h->cfg.dt;
+  const double ax = dt / (dx * dx), ay = dt / (dy * dy);
+  const double c[5] = {-ax, -ax, -ay, -ay, 2 * (dt / (dx * dx) + dt / (dy * dy))};
+  rc = cfd_launch_sip(h->device, h->stream, ni + 1, nj + 1, ni - 1, nj - 1, c, nullptr, 0.88, 1.0e-5, 600, h->f[CFD_FDC_SU],
+                      h->f[CFD_FDC_PP], h->sip_work, h->sip_prog, h->sip_partial, h->sip_info, h->sip_rsm, 1024);
+  return rc ? rc : sip_finish(h, iters);
+}
+
+// ---- implicit variant (fdm_implicit_cavity.f90:177-288) -------------------------------------------------------
+// which: 0 u, 1 v, 2 p'
+extern "C" int cfd_fdcav_implicit_assemble(cfd_fdcav* h, int which) {
+  CFD_REQUIRE(h && which >= 0 && which <= 2, "bad argument");
+  CFD_CUDA(cudaSetDevice(h->device));
+  FdcParams P{};
+  fdc_fill(h, P);
+  k_fdci_assemble<<<fdc_grid(h), dim3(32, 8), 0, h->stream>>>(P, which);
+  CFD_CUDA(cudaGetLastError());
+  return CFD_OK;
+}
+// sipsol (fdm_implicit_cavity.f90:29-92: maxit 3000, alpha 0.80, tol 1e-6) on u (i2 = ni), v (j2 = nj) or pp
+extern "C" int cfd_fdcav_implicit_solve(cfd_fdcav* h, int which, int* iters) {
+  CFD_REQUIRE(h && which >= 0 && which <= 2, "bad argument");
+  CFD_CUDA(cudaSetDevice(h->device));
+  int rc = sip_alloc(h);
+  if (rc) return rc;
+  const int ni = h->cfg.ni, nj = h->cfg.nj;
+  const double* coef[5] = {h->f[CFD_FDC_AW], h->f[CFD_FDC_AE], h->f[CFD_FDC_AS], h->f[CFD_FDC_AN], h->f[CFD_FDC_AP]};
+  double* phi = which == 0 ? h->f[CFD_FDC_U] : which == 1 ? h->f[CFD_FDC_V] : h->f[CFD_FDC_PP];
+  const int imax = which == 0 ? ni - 2 : ni - 1, jmax = which == 1 ? nj - 2 : nj - 1;
+  rc = cfd_launch_sip(h->device, h->stream, ni + 1, nj + 1, imax, jmax, nullptr, coef, 0.80, 1.0e-6, 3000, h->f[CFD_FDC_SU], phi,
+                      h->sip_work, h->sip_prog, h->sip_partial, h->sip_info, h->sip_rsm, 1024);
+  return rc ? rc : sip_finish(h, iters);
+}
+extern "C" int cfd_fdcav_implicit_correct(cfd_fdcav* h, double* error) {
+  CFD_REQUIRE(h, "null context");
+  CFD_CUDA(cudaSetDevice(h->device));
+  FdcParams P{};
+  fdc_fill(h, P);
+  dim3 block(32, 8), grid = fdc_grid(h);
+  k_fdci_correct<<<grid, block, 0, h->stream>>>(P);
+  k_fdc_bc<<<1, 1024, 0, h->stream>>>(P);
+  k_fdc_norm<<<grid, block, 0, h->stream>>>(P);
+  k_fdc_norm_final<<<1, 1024, 0, h->stream>>>(h->partial, h->npartial);
+  CFD_CUDA(cudaGetLastError());
+  if (error) {
+    CFD_CUDA(cudaMemcpyAsync(error, h->partial, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CFD_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  return CFD_OK;
+}
+// one pass of the time loop :177-288
+extern "C" int cfd_fdcav_implicit_step(cfd_fdcav* h, double* error, int iters[3]) {
+  int rc, it = 0;
+  for (int w = 0; w < 3; ++w) {
+    if ((rc = cfd_fdcav_implicit_assemble(h, w))) return rc;
+    if ((rc = cfd_fdcav_implicit_solve(h, w, &it))) return rc;
+    if (iters) iters[w] = it;
+  }
+  return cfd_fdcav_implicit_correct(h, error);
 }
 
 // one pass of the time loop fdm_explicit_cavity.f90:168-255 on the device

@@ -21,8 +21,10 @@ namespace cg = cooperative_groups;
 namespace cfd {
 
 struct SipParams {
-  int ni, nj, ld;            // arrays are (ni+1, nj+1) column-major with leading dimension ld; interior 2..ni x 2..nj
-  double aw, ae, as, an, ap; // constant coefficients as passed to sipsol (already negated by the caller, :206)
+  int imax, jmax, ld;        // arrays are column-major with leading dimension ld; interior (0-based) 1..imax x 1..jmax
+  double aw, ae, as, an, ap; // constant coefficients as passed to sipsol (already negated by the caller, :206) ...
+  const double *awp, *aep, *asp, *anp, *app;   // ... or coefficient arrays (fdm_implicit_cavity.f90:199): used if non-null,
+  double sign;               // the four neighbour arrays multiplied by `sign` (-1: the caller's `-aw, -ae, -as, -an`)
   double alpha, tol;
   int maxit;
   const double* su;
@@ -77,7 +79,7 @@ __device__ __forceinline__ void tile_store(const double* tl, double* g, int ld, 
 template <int PHASE>
 __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long epoch_base, int nbands, int nchunks) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int imax = P.ni - 1, jmax = P.nj - 1;          // interior 0-based: 1..imax, 1..jmax
+  const int imax = P.imax, jmax = P.jmax;              // interior 0-based: 1..imax, 1..jmax
   double* t0 = sm + (size_t)w * (4 * 32 * TS + 4 * 32);
   double *A = t0, *B = A + 32 * TS, *C = B + 32 * TS, *D = C + 32 * TS;   // tiles
   double *row0 = D + 32 * TS, *row1 = row0 + 32, *col0 = row1 + 32, *col1 = col0 + 32;
@@ -128,18 +130,22 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
             // west / south neighbours of the factors un, ue
             const double un_w = (q == 0) ? col0[r] : A[k - 1], ue_w = (q == 0) ? col1[r] : B[k - 1];
             const double un_s = (r == 0) ? row0[q] : A[k - TS], ue_s = (r == 0) ? row1[q] : B[k - TS];
-            const double lw = __ddiv_rn(P.aw, __dadd_rn(1.0, __dmul_rn(P.alpha, un_w)));
-            const double ls = __ddiv_rn(P.as, __dadd_rn(1.0, __dmul_rn(P.alpha, ue_s)));
+            const size_t kg = (size_t)(jb + r) * P.ld + c0 + q;
+            const double caw = P.awp ? P.sign * P.awp[kg] : P.aw, cas = P.asp ? P.sign * P.asp[kg] : P.as;
+            const double can = P.anp ? P.sign * P.anp[kg] : P.an, cae = P.aep ? P.sign * P.aep[kg] : P.ae;
+            const double cap = P.app ? P.app[kg] : P.ap;
+            const double lw = __ddiv_rn(caw, __dadd_rn(1.0, __dmul_rn(P.alpha, un_w)));
+            const double ls = __ddiv_rn(cas, __dadd_rn(1.0, __dmul_rn(P.alpha, ue_s)));
             const double p1 = __dmul_rn(__dmul_rn(P.alpha, lw), un_w);
             const double p2 = __dmul_rn(__dmul_rn(P.alpha, ls), ue_s);
-            const double den = __dsub_rn(__dsub_rn(__dadd_rn(__dadd_rn(P.ap, p1), p2), __dmul_rn(lw, ue_w)), __dmul_rn(ls, un_s));
+            const double den = __dsub_rn(__dsub_rn(__dadd_rn(__dadd_rn(cap, p1), p2), __dmul_rn(lw, ue_w)), __dmul_rn(ls, un_s));
             const double lpr = __ddiv_rn(1.0, den);
-            A[k] = __dmul_rn(__dsub_rn(P.an, p1), lpr);   // un
-            B[k] = __dmul_rn(__dsub_rn(P.ae, p2), lpr);   // ue
+            A[k] = __dmul_rn(__dsub_rn(can, p1), lpr);    // un
+            B[k] = __dmul_rn(__dsub_rn(cae, p2), lpr);    // ue
             C[k] = lw;
             D[k] = ls;
             // lpr goes straight to global memory (a fifth tile would not fit the budget)
-            P.lpr[(size_t)(jb + r) * P.ld + c0 + q] = lpr;
+            P.lpr[kg] = lpr;
           } else if (PHASE == 1) {
             const double rs = (r == 0) ? row0[q] : A[k - TS], rw = (q == 0) ? col0[r] : A[k - 1];
             A[k] = __dmul_rn(__dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], rs)), __dmul_rn(C[k], rw)), D[k]);
@@ -179,7 +185,7 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
 __global__ void __launch_bounds__(32 * SIP_W) k_sip_solve(const SipParams P) {
   extern __shared__ double sm[];
   cg::grid_group grid = cg::this_grid();
-  const int imax = P.ni - 1, jmax = P.nj - 1;
+  const int imax = P.imax, jmax = P.jmax;
   const int nbands = (jmax + 31) / 32, nchunks = (imax + 31) / 32;
   const unsigned long long stride = (unsigned long long)nchunks + 1;
   unsigned long long epoch = 1;
@@ -196,11 +202,14 @@ __global__ void __launch_bounds__(32 * SIP_W) k_sip_solve(const SipParams P) {
     for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < ncell; n += (long long)gridDim.x * blockDim.x) {
       const int i = 1 + (int)(n % imax), j = 1 + (int)(n / imax);
       const size_t k = (size_t)j * P.ld + i;
-      double r = __dsub_rn(P.su[k], __dmul_rn(P.aw, P.phi[k - 1]));
-      r = __dsub_rn(r, __dmul_rn(P.ae, P.phi[k + 1]));
-      r = __dsub_rn(r, __dmul_rn(P.an, P.phi[k + P.ld]));
-      r = __dsub_rn(r, __dmul_rn(P.as, P.phi[k - P.ld]));
-      r = __dsub_rn(r, __dmul_rn(P.ap, P.phi[k]));
+      const double caw = P.awp ? P.sign * P.awp[k] : P.aw, cae = P.aep ? P.sign * P.aep[k] : P.ae;
+      const double can = P.anp ? P.sign * P.anp[k] : P.an, cas = P.asp ? P.sign * P.asp[k] : P.as;
+      const double cap = P.app ? P.app[k] : P.ap;
+      double r = __dsub_rn(P.su[k], __dmul_rn(caw, P.phi[k - 1]));
+      r = __dsub_rn(r, __dmul_rn(cae, P.phi[k + 1]));
+      r = __dsub_rn(r, __dmul_rn(can, P.phi[k + P.ld]));
+      r = __dsub_rn(r, __dmul_rn(cas, P.phi[k - P.ld]));
+      r = __dsub_rn(r, __dmul_rn(cap, P.phi[k]));
       P.res[k] = r;
       acc += fabs(r);
     }
@@ -239,19 +248,25 @@ __global__ void __launch_bounds__(32 * SIP_W) k_sip_solve(const SipParams P) {
 }  // namespace cfd
 using namespace cfd;
 
-// Solve the p' system of one explicit FD-cavity step on the device.  Work arrays are owned by the caller.
-int cfd_launch_sip(int device, cudaStream_t stream, int ni, int nj, double aw, double ae, double as, double an, double ap,
-                   const double* su, double* phi, double* work, unsigned long long* prog, double* partial, int* info,
-                   double* rsm_out, int max_partials) {
+// Launch one SIP solve.  coef != nullptr: five coefficient arrays {aw, ae, as, an, ap} (the four neighbour arrays are
+// negated, as the callers pass `-aw, -ae, -as, -an`); otherwise the constants c[5].  Work arrays are the caller's.
+int cfd_launch_sip(int device, cudaStream_t stream, int ld, int nrows, int imax, int jmax, const double* c,
+                   const double* const* coef, double alpha, double tol, int maxit, const double* su, double* phi, double* work,
+                   unsigned long long* prog, double* partial, int* info, double* rsm_out, int max_partials) {
   SipParams P{};
-  P.ni = ni; P.nj = nj; P.ld = ni + 1;
-  P.aw = aw; P.ae = ae; P.as = as; P.an = an; P.ap = ap;
-  P.alpha = 0.88; P.tol = 1.0e-5; P.maxit = 600;
+  P.imax = imax; P.jmax = jmax; P.ld = ld;
+  if (coef) {
+    P.awp = coef[0]; P.aep = coef[1]; P.asp = coef[2]; P.anp = coef[3]; P.app = coef[4];
+    P.sign = -1.0;
+  } else {
+    P.aw = c[0]; P.ae = c[1]; P.as = c[2]; P.an = c[3]; P.ap = c[4];
+  }
+  P.alpha = alpha; P.tol = tol; P.maxit = maxit;
   P.su = su; P.phi = phi;
-  const size_t n = (size_t)(ni + 1) * (nj + 1);
+  const size_t n = (size_t)ld * nrows;
   P.lw = work; P.ls = work + n; P.lpr = work + 2 * n; P.un = work + 3 * n; P.ue = work + 4 * n; P.res = work + 5 * n;
   P.prog = prog; P.partial = partial; P.info = info; P.rsm_out = rsm_out;
-  const int nbands = (nj - 1 + 31) / 32;
+  const int nbands = (jmax + 31) / 32;
   const size_t smem = (size_t)SIP_W * (4 * 32 * TS + 4 * 32) * sizeof(double);
   CFD_CUDA(cudaFuncSetAttribute(k_sip_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0, nsm = 0;
@@ -262,7 +277,7 @@ int cfd_launch_sip(int device, cudaStream_t stream, int ni, int nj, double aw, d
   if (grid > max_partials) grid = max_partials;
   if (grid < 1) grid = 1;
   CFD_CUDA(cudaMemsetAsync(work, 0, 6 * n * sizeof(double), stream));
-  CFD_CUDA(cudaMemsetAsync(prog, 0, (size_t)nbands * sizeof(unsigned long long), stream));
+  CFD_CUDA(cudaMemsetAsync(prog, 0, (size_t)(nbands + 1) * sizeof(unsigned long long), stream));
   CFD_CUDA(cudaMemsetAsync(info, 0, 2 * sizeof(int), stream));
   void* args[] = {(void*)&P};
   CFD_CUDA(cudaLaunchCooperativeKernel((void*)k_sip_solve, dim3(grid), dim3(32 * SIP_W), args, smem, stream));

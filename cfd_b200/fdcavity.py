@@ -13,17 +13,21 @@ from ._lib import CfdFdcavConfig, FDC_FIELDS, check
 
 
 class FDCavity:
-    def __init__(self, ni=11, nj=11, *, re=10.0, dt=1.0e-4, utop=1.0, urfp=0.8, device=-1):
+    def __init__(self, ni=11, nj=11, *, re=10.0, dt=1.0e-4, utop=1.0, urfp=0.8, device=-1, implicit=False,
+                 urfu=1.0, urfv=1.0, steady=False):
         self.lib = _lib.load()
-        self.ni, self.nj = ni, nj
+        self.ni, self.nj, self.implicit = ni, nj, implicit
         self._h = C.c_void_p()
-        cfg = CfdFdcavConfig(ni=ni, nj=nj, re=re, dt=dt, utop=utop, urfp=urfp, device=device)
+        cfg = CfdFdcavConfig(ni=ni, nj=nj, re=re, dt=dt, utop=utop, urfp=urfp, device=device, steady=int(steady),
+                             urfu=urfu, urfv=urfv)
         check(self.lib.cfd_fdcav_create(C.byref(self._h), C.byref(cfg)))
-        # initial condition (fdm_explicit_cavity.f90:160-166)
         uo = np.zeros((ni + 1, nj + 1), order="F")
         uo[:ni, nj - 1:nj + 1] = 1.0
-        self.upload("uo", uo)
-        self.upload("po", np.ones((ni + 1, nj + 1), order="F"))
+        if implicit:      # initial condition fdm_implicit_cavity.f90:160-164 (u itself; p = 0)
+            self.upload("u", uo)
+        else:             # fdm_explicit_cavity.f90:160-166
+            self.upload("uo", uo)
+            self.upload("po", np.ones((ni + 1, nj + 1), order="F"))
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
@@ -70,3 +74,23 @@ class FDCavity:
         self.predict()
         self.upload("pp", solve_pp(self.download("su")))
         return self.correct()
+
+    # ---- implicit-Euler variant (fdm_implicit_cavity.f90:177-288) ----------------------------------------------
+    def implicit_assemble(self, which: int):
+        check(self.lib.cfd_fdcav_implicit_assemble(self._h, which))
+
+    def implicit_solve(self, which: int) -> int:
+        it = C.c_int()
+        check(self.lib.cfd_fdcav_implicit_solve(self._h, which, C.byref(it)))
+        return it.value
+
+    def implicit_correct(self) -> float:
+        e = C.c_double()
+        check(self.lib.cfd_fdcav_implicit_correct(self._h, C.byref(e)))
+        return e.value
+
+    def implicit_step(self):
+        e, it = C.c_double(), (C.c_int * 3)()
+        check(self.lib.cfd_fdcav_implicit_step(self._h, C.byref(e), it))
+        self.sip_iters = list(it)
+        return e.value

@@ -221,12 +221,17 @@ int cfd_heat_synchronize(cfd_heat* h);
 /* ---- explicit finite-difference cavity: stencil passes of lid-driven-cavity-2d/fdm-explicit/
         fdm_explicit_cavity.f90 (cfd_fdcav_solve_pp is the device SIP of SURVEY 8f-1) ------ */
 typedef enum cfd_fdc_field {
-  CFD_FDC_U = 0, CFD_FDC_V, CFD_FDC_P, CFD_FDC_UO, CFD_FDC_VO, CFD_FDC_PO, CFD_FDC_PP, CFD_FDC_SU, CFD_FDC_FIELD_COUNT
+  CFD_FDC_U = 0, CFD_FDC_V, CFD_FDC_P, CFD_FDC_UO, CFD_FDC_VO, CFD_FDC_PO, CFD_FDC_PP, CFD_FDC_SU,
+  CFD_FDC_AE, CFD_FDC_AW, CFD_FDC_AN, CFD_FDC_AS, CFD_FDC_AP,   /* coefficient arrays of the implicit variant */
+  CFD_FDC_FIELD_COUNT
 } cfd_fdc_field;
 typedef struct cfd_fdcav_config {
   int ni, nj;                 /* grid nodes (fdm_explicit_cavity.f90:111-112); arrays are (ni+1, nj+1) */
   double re, dt, utop, urfp;  /* :116-119 */
   int device;
+  /* implicit variant (lid-driven-cavity-2d/fdm-implicit/fdm_implicit_cavity.f90:105-125) */
+  int steady;                 /* steadysim */
+  double urfu, urfv;
 } cfd_fdcav_config;
 typedef struct cfd_fdcav cfd_fdcav;
 int cfd_fdcav_create(cfd_fdcav** out, const cfd_fdcav_config* cfg);
@@ -244,6 +249,13 @@ int cfd_fdcav_correct(cfd_fdcav* h, double* error);
 int cfd_fdcav_solve_pp(cfd_fdcav* h, int* iters);
 /* one pass of the time loop (:168-255): predict, solve pp, correct */
 int cfd_fdcav_step(cfd_fdcav* h, double* error, int* sip_iters);
+/* implicit-Euler variant, fdm_implicit_cavity.f90: coefficient assembly of u (:178-198), v (:201-220), p' (:222-240)
+   [which = 0, 1, 2]; sipsol (:29-92, maxit 3000, alpha 0.80, tol 1e-6) on that system; correction + boundary
+   conditions + continuity norm (:243-282); and the whole loop body (:177-288) */
+int cfd_fdcav_implicit_assemble(cfd_fdcav* h, int which);
+int cfd_fdcav_implicit_solve(cfd_fdcav* h, int which, int* iters);
+int cfd_fdcav_implicit_correct(cfd_fdcav* h, double* error);
+int cfd_fdcav_implicit_step(cfd_fdcav* h, double* error, int iters[3]);
 
 /* library/build identification */
 const char* cfd_version(void);

@@ -394,3 +394,44 @@ class FDCavity:
 
     def step(self):
         return self.L.orc_fdc_step(C.byref(self.s))
+
+
+class _FdciStruct(C.Structure):
+    _fields_ = ([("ni", C.c_int), ("nj", C.c_int), ("steady", C.c_int)]
+                + [(n, C.c_double) for n in ("re", "dt", "utop", "urfu", "urfv", "urfp")]
+                + [(n, _dp) for n in ("u", "v", "p", "pp", "ae", "aw", "an", "as_", "ap", "su")]
+                + [("sip_iters", C.c_int * 3)])
+
+
+class FDCavityImplicit:
+    """Implicit-Euler finite-difference cavity (lid-driven-cavity-2d/fdm-implicit/fdm_implicit_cavity.f90:96-288)."""
+
+    FIELDS = ("u", "v", "p", "pp", "ae", "aw", "an", "as_", "ap", "su")
+
+    def __init__(self, ni=11, nj=11, re=10.0, dt=1.0e-4, utop=1.0, urf=(1.0, 1.0, 0.5), steady=False, fast=False):
+        self.L = lib(fast)
+        self.ni, self.nj = ni, nj
+        for n in self.FIELDS:
+            setattr(self, n, np.zeros((ni + 1, nj + 1), order="F"))
+        self.s = _FdciStruct(ni=ni, nj=nj, steady=int(steady), re=re, dt=dt, utop=utop, urfu=urf[0], urfv=urf[1], urfp=urf[2])
+        for n in self.FIELDS:
+            setattr(self.s, n, _p(getattr(self, n)))
+        ptr = C.POINTER(_FdciStruct)
+        for n in ("init", "assemble_u", "assemble_v", "assemble_p"):
+            getattr(self.L, "orc_fdci_" + n).argtypes = [ptr]
+            getattr(self.L, "orc_fdci_" + n).restype = None
+        self.L.orc_fdci_solve.argtypes = [ptr, C.c_int]
+        self.L.orc_fdci_solve.restype = C.c_int
+        for n in ("correct", "step"):
+            getattr(self.L, "orc_fdci_" + n).argtypes = [ptr]
+            getattr(self.L, "orc_fdci_" + n).restype = C.c_double
+        self.L.orc_fdci_init(C.byref(self.s))
+
+    def call(self, name):
+        return getattr(self.L, "orc_fdci_" + name)(C.byref(self.s))
+
+    def solve(self, which):
+        return self.L.orc_fdci_solve(C.byref(self.s), which)
+
+    def step(self):
+        return self.L.orc_fdci_step(C.byref(self.s))
