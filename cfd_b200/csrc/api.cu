@@ -182,6 +182,8 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->seq_scratch = nullptr;
   c->launches = 0;
   for (auto& g : c->gfast) g = nullptr;
+  for (auto& g : c->tfast) g = nullptr;
+  c->tfast_ready = false;
   int want_m = cfg->tdma_m;
   if (want_m == 0) {
     const char* e = getenv("CFD_B200_TDMA_M");
@@ -194,7 +196,7 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   }
   {
     const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
-    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || general || teach;
+    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || general;
     c->L.nc = c->exact_assembly ? 6 : 5;
     c->L.cSL = (long long)c->L.nc * c->L.LD;
     c->L.cSK = c->L.nc * c->L.T;
@@ -253,6 +255,7 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   for (auto& g : c->geom) if (g) cudaFree(g);
   for (auto& g : c->geomn) if (g) cudaFree(g);
   for (auto& g : c->gfast) if (g) cudaFree(g);
+  for (auto& g : c->tfast) if (g) cudaFree(g);
   if (c->stage) cudaFree(c->stage);
   if (c->partial) cudaFree(c->partial);
   if (c->res_dev) cudaFree(c->res_dev);
@@ -280,6 +283,7 @@ extern "C" int cfd_set_geometry(cfd_ctx* c, int id, const double* host, int n) {
   CFD_REQUIRE(n == (isj ? c->L.nj : c->L.ni), "geometry array length must be nj (y-arrays) or ni (x-arrays)");
   CFD_CUDA(cudaSetDevice(c->device));
   c->geom_host[id].assign(host, host + n);
+  c->tfast_ready = false;
   CFD_CUDA(cudaMemcpyAsync(c->geomn[id], host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   if (!isj) {
     CFD_CUDA(cudaMemcpyAsync(c->geom[id], host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));

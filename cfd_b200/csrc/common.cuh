@@ -122,6 +122,8 @@ struct cfd_ctx {
   double* res_dev;                  // 8 packed residual sums
   double* seq_scratch;              // sequential-order debug sweep: forward-elimination arrays
   double* gfast[8];                 // FastGeom arrays (device)
+  double* tfast[16];                 // TEACH-family reciprocal geometry (teach_fast_kernels.cu), built on first use
+  bool tfast_ready;
   bool exact_assembly;              // bit-exact assembly kernels (sequential-order mode, or CFD_B200_EXACT_ASSEMBLY=1)
   long long launches;               // kernels launched by this context so far (cfd_launch_count)
 };
@@ -144,3 +146,4 @@ int cfd_update_fast_geometry(cfd_ctx* c);
 int cfd_launch_assemble_tma(cfd_ctx* c, int which, cfd::CavParams& P);
 int cfd_launch_general_assemble(cfd_ctx* c, int which);
 int cfd_launch_teach_assemble(cfd_ctx* c, int which);
+int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double* partial, const double* uinc);

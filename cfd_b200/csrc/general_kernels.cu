@@ -13,6 +13,7 @@
 // Thread mapping as in cavity_kernels.cu (one thread = M consecutive nodes of one line).  This first version
 // addresses neighbours through the layout function instead of register windows: correct first, tuned later.
 #include "common.cuh"
+#include "linepos.cuh"
 
 namespace cfd {
 
@@ -28,7 +29,7 @@ struct GenParams {
   double *ae, *aw, *an, *as, *ap, *su, *dout;
   // by-i geometry (natural order)
   const double *sew, *sewu, *xdif, *xcvi, *xcvip, *fx;
-  // by-j geometry (natural order: these kernels index j directly)
+  // by-j geometry (line layout, read through LinePos)
   const double *sns, *ydif, *ycvr, *ycvrs, *arx, *arxj, *arxjp, *r, *rmn, *sx, *sxmn, *fvp, *fy;
   double* partial;
 };
@@ -57,10 +58,8 @@ __device__ __forceinline__ double HARMEAN(double a, double b, double w) { return
 struct Fld {
   const double* p;
   long long LD;
-  int M, T;
-  __device__ __forceinline__ double operator()(int i0, int j0) const {
-    return __ldg(p + (long long)i0 * LD + (j0 % M) * T + (j0 / M));
-  }
+  LinePos lp;
+  __device__ __forceinline__ double operator()(int i0, int j0) const { return __ldg(p + (long long)i0 * LD + lp(j0)); }
 };
 
 __device__ __forceinline__ void block_sum_gen(double v, double* partial) {
@@ -79,42 +78,45 @@ __device__ __forceinline__ void block_sum_gen(double v, double* partial) {
   }
 }
 
-// 1-based helpers on 1-D arrays
+// 1-based helpers on 1-D arrays: by-i arrays in natural order, by-j arrays in line layout (needs `lp` in scope)
 #define G1(a, i) __ldg((a) + (i) - 1)
+#define GJ(a, j) __ldg((a) + lp((j) - 1))
 
 // ---- u equation: buoyancy_cav.f90:135-194 ------------------------------------------------------------------
 // x-face produced while the reference visits u-cell (ii, j): returns flow, acof of the face EAST of cell ii
 __device__ __forceinline__ void u_face_e(const GenParams& P, const Fld& U, const Fld& D, const Fld& Gm, int ii, int j,
                                          int ni, int nim1_loop, double& flow, double& acof) {
+  const LinePos& lp = U.lp;
   double diff;
   if (ii == nim1_loop) {   // east boundary (`i == njm1`, :150)
-    flow = G1(P.arx, j) * U(ni - 1, j - 1) * D(ni - 1, j - 1);
-    diff = G1(P.arx, j) * Gm(ni - 1, j - 1) / (G1(P.sew, ni - 1) * G1(P.sx, j));
+    flow = GJ(P.arx, j) * U(ni - 1, j - 1) * D(ni - 1, j - 1);
+    diff = GJ(P.arx, j) * Gm(ni - 1, j - 1) / (G1(P.sew, ni - 1) * GJ(P.sx, j));
   } else {
     const double fl = U(ii - 1, j - 1) * ARIMEAN(D(ii - 2, j - 1), D(ii - 1, j - 1), G1(P.fx, ii));
     const double flp = U(ii, j - 1) * ARIMEAN(D(ii - 1, j - 1), D(ii, j - 1), G1(P.fx, ii + 1));
-    flow = G1(P.arx, j) * 0.5 * (fl + flp);
-    diff = G1(P.arx, j) * Gm(ii - 1, j - 1) / (G1(P.sew, ii) * G1(P.sx, j));
+    flow = GJ(P.arx, j) * 0.5 * (fl + flp);
+    diff = GJ(P.arx, j) * Gm(ii - 1, j - 1) / (G1(P.sew, ii) * GJ(P.sx, j));
   }
   acof = DAPEC(flow, diff, P.iadv);
 }
 // y-face NORTH of u-cell (i, jj)
 __device__ __forceinline__ void u_face_n(const GenParams& P, const Fld& V, const Fld& D, const Fld& Gm, int i, int jj,
                                          int nj, double& flow, double& acof) {
+  const LinePos& lp = V.lp;
   double fl, flm, diff;
   if (jj == nj - 1) {
     fl = G1(P.xcvi, i) * V(i - 1, nj - 1) * D(i - 1, nj - 1);
     flm = G1(P.xcvip, i - 1) * V(i - 2, nj - 1) * D(i - 2, nj - 1);
-    diff = G1(P.r, nj) * (G1(P.xcvi, i) * Gm(i - 1, nj - 1) + G1(P.xcvip, i - 1) * Gm(i - 2, nj - 1)) / G1(P.ydif, nj);
+    diff = GJ(P.r, nj) * (G1(P.xcvi, i) * Gm(i - 1, nj - 1) + G1(P.xcvip, i - 1) * Gm(i - 2, nj - 1)) / GJ(P.ydif, nj);
   } else {
-    const double fyp = G1(P.fy, jj + 1);
+    const double fyp = GJ(P.fy, jj + 1);
     fl = G1(P.xcvi, i) * V(i - 1, jj) * ARIMEAN(D(i - 1, jj - 1), D(i - 1, jj), fyp);
     flm = G1(P.xcvip, i - 1) * V(i - 2, jj) * ARIMEAN(D(i - 2, jj - 1), D(i - 2, jj), fyp);
     const double vis_ne = HARMEAN(Gm(i - 1, jj - 1), Gm(i - 1, jj), fyp);
     const double vis_nw = HARMEAN(Gm(i - 2, jj - 1), Gm(i - 2, jj), fyp);
-    diff = G1(P.rmn, jj + 1) * (vis_ne * G1(P.xcvi, i) + vis_nw * G1(P.xcvip, i - 1)) / G1(P.ydif, jj + 1);
+    diff = GJ(P.rmn, jj + 1) * (vis_ne * G1(P.xcvi, i) + vis_nw * G1(P.xcvip, i - 1)) / GJ(P.ydif, jj + 1);
   }
-  flow = G1(P.rmn, jj + 1) * (fl + flm);
+  flow = GJ(P.rmn, jj + 1) * (fl + flm);
   acof = DAPEC(flow, diff, P.iadv);
 }
 
@@ -125,7 +127,8 @@ __global__ void __launch_bounds__(256) k_gen_assemble_u(const GenParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const Fld U{P.u, LD, M, T}, V{P.v, LD, M, T}, D{P.den, LD, M, T}, Gm{P.gam, LD, M, T}, Pr{P.p, LD, M, T};
+    const LinePos lp(M, T, t);
+    const Fld U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, Gm{P.gam, LD, lp}, Pr{P.p, LD, lp};
     const int i = i0 + 1;
     const int iloop_last = nj - 1;     // quirk: the reference loops `do i = 3, njm1` (:135,:149); ni == nj is enforced
     for (int k = 0; k < M; ++k) {
@@ -134,8 +137,8 @@ __global__ void __launch_bounds__(256) k_gen_assemble_u(const GenParams P) {
       double flow, acof, AW, AE, AS, AN;
       // west face
       if (i == 3) {
-        flow = G1(P.arx, j) * U(1, j0) * D(0, j0);
-        const double diff = G1(P.arx, j) * Gm(0, j0) / (G1(P.sew, 2) * G1(P.sx, j));
+        flow = GJ(P.arx, j) * U(1, j0) * D(0, j0);
+        const double diff = GJ(P.arx, j) * Gm(0, j0) / (G1(P.sew, 2) * GJ(P.sx, j));
         acof = DAPEC(flow, diff, P.iadv);
       } else {
         u_face_e(P, U, D, Gm, i - 1, j, ni, iloop_last, flow, acof);
@@ -148,8 +151,8 @@ __global__ void __launch_bounds__(256) k_gen_assemble_u(const GenParams P) {
       if (j == 2) {
         const double fl = G1(P.xcvi, i) * V(i0, 1) * D(i0, 0);
         const double flm = G1(P.xcvip, i - 1) * V(i0 - 1, 1) * D(i0 - 1, 0);
-        flow = G1(P.r, 1) * (fl + flm);
-        const double diff = G1(P.r, 1) * (G1(P.xcvi, i) * Gm(i0, 0) + G1(P.xcvip, i - 1) * Gm(i0 - 1, 0)) / G1(P.ydif, 2);
+        flow = GJ(P.r, 1) * (fl + flm);
+        const double diff = GJ(P.r, 1) * (G1(P.xcvi, i) * Gm(i0, 0) + G1(P.xcvip, i - 1) * Gm(i0 - 1, 0)) / GJ(P.ydif, 2);
         acof = DAPEC(flow, diff, P.iadv);
       } else {
         u_face_n(P, V, D, Gm, i, j - 1, nj, flow, acof);
@@ -158,9 +161,9 @@ __global__ void __launch_bounds__(256) k_gen_assemble_u(const GenParams P) {
       // north face
       u_face_n(P, V, D, Gm, i, j, nj, flow, acof);
       AN = (acof + gmax(0.0, flow)) - flow;
-      const double vol = G1(P.ycvr, j) * G1(P.sewu, i);
+      const double vol = GJ(P.ycvr, j) * G1(P.sewu, i);
       double SU = 0.0 * vol, SP = 0.0 * vol;
-      double DU = vol / (G1(P.xdif, i) * G1(P.sx, j));
+      double DU = vol / (G1(P.xdif, i) * GJ(P.sx, j));
       SU = SU + DU * (Pr(i0 - 1, j0) - Pr(i0, j0));
       double AP = AE + AW + AN + AS - SP;
       const double reseq = AP * U(i0, j0) - AE * U(i0 + 1, j0) - AW * U(i0 - 1, j0) - AN * U(i0, j0 + 1)
@@ -180,35 +183,37 @@ __global__ void __launch_bounds__(256) k_gen_assemble_u(const GenParams P) {
 // ---- v equation: buoyancy_cav.f90:212-273 ------------------------------------------------------------------
 __device__ __forceinline__ void v_face_e(const GenParams& P, const Fld& U, const Fld& D, const Fld& Gm, int ii, int j,
                                          int ni, double& flow, double& acof) {
+  const LinePos& lp = U.lp;
   double fl, flm, diff;
   if (ii == ni - 1) {
-    fl = G1(P.arxj, j) * U(ni - 1, j - 1) * D(ni - 1, j - 1);
-    flm = G1(P.arxjp, j - 1) * U(ni - 1, j - 2) * D(ni - 1, j - 2);
-    diff = (G1(P.arxj, j) * Gm(ni - 1, j - 1) + G1(P.arxjp, j - 1) * Gm(ni - 1, j - 2)) / (G1(P.xdif, ni) * G1(P.sxmn, j));
+    fl = GJ(P.arxj, j) * U(ni - 1, j - 1) * D(ni - 1, j - 1);
+    flm = GJ(P.arxjp, j - 1) * U(ni - 1, j - 2) * D(ni - 1, j - 2);
+    diff = (GJ(P.arxj, j) * Gm(ni - 1, j - 1) + GJ(P.arxjp, j - 1) * Gm(ni - 1, j - 2)) / (G1(P.xdif, ni) * GJ(P.sxmn, j));
   } else {
     const double fxp = G1(P.fx, ii + 1);
-    fl = G1(P.arxj, j) * U(ii, j - 1) * ARIMEAN(D(ii - 1, j - 1), D(ii, j - 1), fxp);
-    flm = G1(P.arxjp, j - 1) * U(ii, j - 2) * ARIMEAN(D(ii - 1, j - 2), D(ii, j - 2), fxp);
+    fl = GJ(P.arxj, j) * U(ii, j - 1) * ARIMEAN(D(ii - 1, j - 1), D(ii, j - 1), fxp);
+    flm = GJ(P.arxjp, j - 1) * U(ii, j - 2) * ARIMEAN(D(ii - 1, j - 2), D(ii, j - 2), fxp);
     const double vis_ne = HARMEAN(Gm(ii - 1, j - 1), Gm(ii, j - 1), fxp);
     const double vis_se = HARMEAN(Gm(ii - 1, j - 2), Gm(ii, j - 2), fxp);
-    diff = (vis_ne * G1(P.arxj, j) + vis_se * G1(P.arxjp, j - 1)) / (G1(P.xdif, ii + 1) * G1(P.sxmn, j));
+    diff = (vis_ne * GJ(P.arxj, j) + vis_se * GJ(P.arxjp, j - 1)) / (G1(P.xdif, ii + 1) * GJ(P.sxmn, j));
   }
   flow = fl + flm;
   acof = DAPEC(flow, diff, P.iadv);
 }
 __device__ __forceinline__ void v_face_n(const GenParams& P, const Fld& V, const Fld& D, const Fld& Gm, int i, int jj,
                                          int nj, double& flow, double& acof) {
+  const LinePos& lp = V.lp;
   double diff;
   if (jj == nj - 1) {
-    const double area = G1(P.r, nj) * G1(P.sew, i);
+    const double area = GJ(P.r, nj) * G1(P.sew, i);
     flow = area * V(i - 1, nj - 1) * D(i - 1, nj - 1);
-    diff = area * Gm(i - 1, nj - 1) / G1(P.sns, nj - 1);
+    diff = area * Gm(i - 1, nj - 1) / GJ(P.sns, nj - 1);
   } else {
-    const double area = G1(P.r, jj) * G1(P.sew, i);
-    const double fl = V(i - 1, jj - 1) * G1(P.rmn, jj) * G1(P.sew, i) * ARIMEAN(D(i - 1, jj - 2), D(i - 1, jj - 1), G1(P.fy, jj));
-    const double flp = V(i - 1, jj) * G1(P.rmn, jj + 1) * G1(P.sew, i) * ARIMEAN(D(i - 1, jj - 1), D(i - 1, jj), G1(P.fy, jj + 1));
-    flow = ARIMEAN(fl, flp, G1(P.fvp, jj));
-    diff = area * Gm(i - 1, jj - 1) / G1(P.sns, jj);
+    const double area = GJ(P.r, jj) * G1(P.sew, i);
+    const double fl = V(i - 1, jj - 1) * GJ(P.rmn, jj) * G1(P.sew, i) * ARIMEAN(D(i - 1, jj - 2), D(i - 1, jj - 1), GJ(P.fy, jj));
+    const double flp = V(i - 1, jj) * GJ(P.rmn, jj + 1) * G1(P.sew, i) * ARIMEAN(D(i - 1, jj - 1), D(i - 1, jj), GJ(P.fy, jj + 1));
+    flow = ARIMEAN(fl, flp, GJ(P.fvp, jj));
+    diff = area * Gm(i - 1, jj - 1) / GJ(P.sns, jj);
   }
   acof = DAPEC(flow, diff, P.iadv);
 }
@@ -220,18 +225,19 @@ __global__ void __launch_bounds__(256) k_gen_assemble_v(const GenParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const Fld U{P.u, LD, M, T}, V{P.v, LD, M, T}, D{P.den, LD, M, T}, Gm{P.gam, LD, M, T}, Pr{P.p, LD, M, T},
-        Tt{P.t, LD, M, T};
+    const LinePos lp(M, T, t);
+    const Fld U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, Gm{P.gam, LD, lp}, Pr{P.p, LD, lp},
+        Tt{P.t, LD, lp};
     const int i = i0 + 1;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < P.jlo || j0 > P.jhi) continue;
       double flow, acof, AW, AE, AS, AN;
       if (i == 2) {
-        const double fl = G1(P.arxj, j) * U(1, j0) * D(0, j0);
-        const double flm = G1(P.arxjp, j - 1) * U(1, j0 - 1) * D(0, j0 - 1);
+        const double fl = GJ(P.arxj, j) * U(1, j0) * D(0, j0);
+        const double flm = GJ(P.arxjp, j - 1) * U(1, j0 - 1) * D(0, j0 - 1);
         flow = fl + flm;
-        const double diff = (G1(P.arxj, j) * Gm(0, j0) + G1(P.arxjp, j - 1) * Gm(0, j0 - 1)) / (G1(P.xdif, 2) * G1(P.sxmn, j));
+        const double diff = (GJ(P.arxj, j) * Gm(0, j0) + GJ(P.arxjp, j - 1) * Gm(0, j0 - 1)) / (G1(P.xdif, 2) * GJ(P.sxmn, j));
         acof = DAPEC(flow, diff, P.iadv);
       } else {
         v_face_e(P, U, D, Gm, i - 1, j, ni, flow, acof);
@@ -240,9 +246,9 @@ __global__ void __launch_bounds__(256) k_gen_assemble_v(const GenParams P) {
       v_face_e(P, U, D, Gm, i, j, ni, flow, acof);
       AE = (acof + gmax(0.0, flow)) - flow;
       if (j == 3) {
-        const double area = G1(P.r, 1) * G1(P.sew, i);
+        const double area = GJ(P.r, 1) * G1(P.sew, i);
         flow = area * V(i0, 1) * D(i0, 0);
-        const double diff = area * Gm(i0, 0) * G1(P.sns, 2);     // quirk: multiply (buoyancy_cav.f90:216)
+        const double diff = area * Gm(i0, 0) * GJ(P.sns, 2);     // quirk: multiply (buoyancy_cav.f90:216)
         acof = DAPEC(flow, diff, P.iadv);
       } else {
         v_face_n(P, V, D, Gm, i, j - 1, nj, flow, acof);
@@ -250,11 +256,11 @@ __global__ void __launch_bounds__(256) k_gen_assemble_v(const GenParams P) {
       AS = acof + gmax(0.0, flow);
       v_face_n(P, V, D, Gm, i, j, nj, flow, acof);
       AN = (acof + gmax(0.0, flow)) - flow;
-      const double vol = G1(P.ycvrs, j) * G1(P.sew, i);
+      const double vol = GJ(P.ycvrs, j) * G1(P.sew, i);
       double src = 0.0;
-      if (P.boussinesq) src = P.rgbeta * (ARIMEAN(Tt(i0, j0 - 1), Tt(i0, j0), G1(P.fy, j)) - P.tref);
+      if (P.boussinesq) src = P.rgbeta * (ARIMEAN(Tt(i0, j0 - 1), Tt(i0, j0), GJ(P.fy, j)) - P.tref);
       double SU = src * vol, SP = 0.0 * vol;
-      double DV = vol / G1(P.ydif, j);
+      double DV = vol / GJ(P.ydif, j);
       SU = SU + DV * (Pr(i0, j0 - 1) - Pr(i0, j0));
       double AP = AE + AW + AN + AS - SP;
       const double reseq = AP * V(i0, j0) - AE * V(i0 + 1, j0) - AW * V(i0 - 1, j0) - AN * V(i0, j0 + 1)
@@ -279,20 +285,21 @@ __global__ void __launch_bounds__(256) k_gen_assemble_p(const GenParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const Fld U{P.u, LD, M, T}, V{P.v, LD, M, T}, D{P.den, LD, M, T}, DU{P.du_in, LD, M, T}, DV{P.dv_in, LD, M, T};
+    const LinePos lp(M, T, t);
+    const Fld U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, DU{P.du_in, LD, lp}, DV{P.dv_in, LD, lp};
     const int i = i0 + 1, nim1 = ni - 1, njm1 = nj - 1;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < P.jlo || j0 > P.jhi) continue;
-      const double areaew = G1(P.arx, j);
+      const double areaew = GJ(P.arx, j);
       double SU = 0.0, AE, AW, AN, AS;
       // inflow through the south face (scattered by cell (i,j-1), or the boundary loop :301-306)
       if (j == 2) {
-        SU = SU + D(i0, 0) * V(i0, 1) * (G1(P.rmn, 2) * G1(P.sew, i));
+        SU = SU + D(i0, 0) * V(i0, 1) * (GJ(P.rmn, 2) * G1(P.sew, i));
         AS = 0.0;
       } else {
-        const double denn = ARIMEAN(D(i0, j0 - 1), D(i0, j0), G1(P.fy, j));
-        const double arean = G1(P.rmn, j) * G1(P.sew, i);
+        const double denn = ARIMEAN(D(i0, j0 - 1), D(i0, j0), GJ(P.fy, j));
+        const double arean = GJ(P.rmn, j) * G1(P.sew, i);
         SU = SU + denn * V(i0, j0) * arean;
         AS = denn * arean * DV(i0, j0);
       }
@@ -308,12 +315,12 @@ __global__ void __launch_bounds__(256) k_gen_assemble_p(const GenParams P) {
       SU = SU - D(i0 + 1, j0) * U(i0 + 1, j0) * areaew;
       AE = (i == nim1) ? 0.0 : ARIMEAN(D(i0, j0), D(i0 + 1, j0), G1(P.fx, i + 1)) * areaew * DU(i0 + 1, j0);
       // north
-      const double arean = G1(P.rmn, j + 1) * G1(P.sew, i);
+      const double arean = GJ(P.rmn, j + 1) * G1(P.sew, i);
       if (j == njm1) {
         SU = SU - D(i0, nj - 1) * V(i0, nj - 1) * arean;
         AN = 0.0;
       } else {
-        const double denn = ARIMEAN(D(i0, j0), D(i0, j0 + 1), G1(P.fy, j + 1));
+        const double denn = ARIMEAN(D(i0, j0), D(i0, j0 + 1), GJ(P.fy, j + 1));
         SU = SU - denn * V(i0, j0 + 1) * arean;
         AN = denn * arean * DV(i0, j0 + 1);
       }
@@ -334,32 +341,34 @@ struct DenCp {
 };
 __device__ __forceinline__ void t_face_e(const GenParams& P, const Fld& U, const DenCp& D, const Fld& Gm, int ii, int j,
                                          int ni, int nj, double& flow, double& acof) {
-  const double areaew = G1(P.arx, j);
+  const LinePos& lp = U.lp;
+  const double areaew = GJ(P.arx, j);
   double diff;
   if (ii == ni - 1) {
     const double dene = D(nj - 1, j - 1);                     // quirk: den(nj,j) (buoyancy_cav.f90:390)
     flow = dene * U(ni - 1, j - 1) * areaew;
-    diff = Gm(ni - 1, j - 1) * areaew / (G1(P.xdif, ni) * G1(P.sx, j));
+    diff = Gm(ni - 1, j - 1) * areaew / (G1(P.xdif, ni) * GJ(P.sx, j));
   } else {
     const double dene = ARIMEAN(D(ii - 1, j - 1), D(ii, j - 1), G1(P.fx, ii + 1));
     flow = dene * U(ii, j - 1) * areaew;
     const double game = HARMEAN(Gm(ii - 1, j - 1), Gm(ii, j - 1), G1(P.fx, ii + 1));
-    diff = game * areaew / (G1(P.xdif, ii + 1) * G1(P.sx, j));
+    diff = game * areaew / (G1(P.xdif, ii + 1) * GJ(P.sx, j));
   }
   acof = DAPEC(flow, diff, P.iadv);
 }
 __device__ __forceinline__ void t_face_n(const GenParams& P, const Fld& V, const DenCp& D, const Fld& Gm, int i, int jj,
                                          int nj, double& flow, double& acof) {
-  const double arean = G1(P.rmn, jj + 1) * G1(P.sew, i);
+  const LinePos& lp = V.lp;
+  const double arean = GJ(P.rmn, jj + 1) * G1(P.sew, i);
   double diff;
   if (jj == nj - 1) {
     flow = D(i - 1, nj - 1) * V(i - 1, nj - 1) * arean;
-    diff = Gm(i - 1, nj - 1) * arean / G1(P.ydif, nj);
+    diff = Gm(i - 1, nj - 1) * arean / GJ(P.ydif, nj);
   } else {
-    const double denn = ARIMEAN(D(i - 1, jj - 1), D(i - 1, jj), G1(P.fy, jj + 1));
+    const double denn = ARIMEAN(D(i - 1, jj - 1), D(i - 1, jj), GJ(P.fy, jj + 1));
     flow = denn * V(i - 1, jj) * arean;
-    const double gamn = HARMEAN(Gm(i - 1, jj - 1), Gm(i - 1, jj), G1(P.fy, jj + 1));
-    diff = gamn * arean / G1(P.ydif, jj + 1);
+    const double gamn = HARMEAN(Gm(i - 1, jj - 1), Gm(i - 1, jj), GJ(P.fy, jj + 1));
+    diff = gamn * arean / GJ(P.ydif, jj + 1);
   }
   acof = DAPEC(flow, diff, P.iadv);
 }
@@ -371,17 +380,18 @@ __global__ void __launch_bounds__(256) k_gen_assemble_t(const GenParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const Fld U{P.u, LD, M, T}, V{P.v, LD, M, T}, Gm{P.gam, LD, M, T}, Tt{P.t, LD, M, T};
-    const DenCp D{Fld{P.den, LD, M, T}, Fld{P.cp, LD, M, T}, P.scale_den_by_cp};
-    const Fld Ss{P.su_src, LD, M, T}, Sp{P.sp_src, LD, M, T};
+    const LinePos lp(M, T, t);
+    const Fld U{P.u, LD, lp}, V{P.v, LD, lp}, Gm{P.gam, LD, lp}, Tt{P.t, LD, lp};
+    const DenCp D{Fld{P.den, LD, lp}, Fld{P.cp, LD, lp}, P.scale_den_by_cp};
+    const Fld Ss{P.su_src, LD, lp}, Sp{P.sp_src, LD, lp};
     const int i = i0 + 1;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < P.jlo || j0 > P.jhi) continue;
       double flow, acof, AW, AE, AS, AN;
       if (i == 2) {
-        flow = D(0, j0) * U(1, j0) * G1(P.arx, j);
-        const double diff = Gm(0, j0) * G1(P.arx, j) / (G1(P.xdif, 2) * G1(P.sx, j));
+        flow = D(0, j0) * U(1, j0) * GJ(P.arx, j);
+        const double diff = Gm(0, j0) * GJ(P.arx, j) / (G1(P.xdif, 2) * GJ(P.sx, j));
         acof = DAPEC(flow, diff, P.iadv);
       } else {
         t_face_e(P, U, D, Gm, i - 1, j, ni, nj, flow, acof);
@@ -390,9 +400,9 @@ __global__ void __launch_bounds__(256) k_gen_assemble_t(const GenParams P) {
       t_face_e(P, U, D, Gm, i, j, ni, nj, flow, acof);
       AE = (acof + gmax(0.0, flow)) - flow;
       if (j == 2) {
-        const double areas = G1(P.r, 1) * G1(P.sew, i);
+        const double areas = GJ(P.r, 1) * G1(P.sew, i);
         flow = D(i0, 0) * V(i0, 1) * areas;
-        const double diff = Gm(i0, 0) * areas / G1(P.ydif, 2);
+        const double diff = Gm(i0, 0) * areas / GJ(P.ydif, 2);
         acof = DAPEC(flow, diff, P.iadv);
       } else {
         t_face_n(P, V, D, Gm, i, j - 1, nj, flow, acof);
@@ -400,7 +410,7 @@ __global__ void __launch_bounds__(256) k_gen_assemble_t(const GenParams P) {
       AS = acof + gmax(0.0, flow);
       t_face_n(P, V, D, Gm, i, j, nj, flow, acof);
       AN = (acof + gmax(0.0, flow)) - flow;
-      const double vol = G1(P.ycvr, j) * G1(P.sew, i);
+      const double vol = GJ(P.ycvr, j) * G1(P.sew, i);
       const double SP = (P.sp_src ? Sp(i0, j0) : 0.0) * vol;
       double SU = (P.su_src ? Ss(i0, j0) : 0.0) * vol;
       double AP = AE + AW + AN + AS - SP;
@@ -432,10 +442,10 @@ int cfd_launch_general_assemble(cfd_ctx* c, int which) {
   P.ap = c->field[CFD_AP]; P.su = c->field[CFD_SU];
   P.sew = c->geomn[CFD_G_SEW]; P.sewu = c->geomn[CFD_G_SEWU]; P.xdif = c->geomn[CFD_G_XDIF];
   P.xcvi = c->geomn[CFD_G_XCVI]; P.xcvip = c->geomn[CFD_G_XCVIP]; P.fx = c->geomn[CFD_G_FX];
-  P.sns = c->geomn[CFD_G_SNS]; P.ydif = c->geomn[CFD_G_YDIF]; P.ycvr = c->geomn[CFD_G_YCVR];
-  P.ycvrs = c->geomn[CFD_G_YCVRS]; P.arx = c->geomn[CFD_G_ARX]; P.arxj = c->geomn[CFD_G_ARXJ];
-  P.arxjp = c->geomn[CFD_G_ARXJP]; P.r = c->geomn[CFD_G_R]; P.rmn = c->geomn[CFD_G_RMN]; P.sx = c->geomn[CFD_G_SX];
-  P.sxmn = c->geomn[CFD_G_SXMN]; P.fvp = c->geomn[CFD_G_FVP]; P.fy = c->geomn[CFD_G_FY];
+  P.sns = c->geom[CFD_G_SNS]; P.ydif = c->geom[CFD_G_YDIF]; P.ycvr = c->geom[CFD_G_YCVR];
+  P.ycvrs = c->geom[CFD_G_YCVRS]; P.arx = c->geom[CFD_G_ARX]; P.arxj = c->geom[CFD_G_ARXJ];
+  P.arxjp = c->geom[CFD_G_ARXJP]; P.r = c->geom[CFD_G_R]; P.rmn = c->geom[CFD_G_RMN]; P.sx = c->geom[CFD_G_SX];
+  P.sxmn = c->geom[CFD_G_SXMN]; P.fvp = c->geom[CFD_G_FVP]; P.fy = c->geom[CFD_G_FY];
   const int ni = c->L.ni, nj = c->L.nj;
   int eq = which;
   P.jhi = nj - 2;

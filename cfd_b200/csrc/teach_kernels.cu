@@ -12,6 +12,7 @@
 // sequential-order mode stays bit-comparable with oracle/teach_oracle.c (*_f64).  Compiled with -fmad=false.
 // FP64 throughout (the reference is FP32 as written).  k-epsilon / energy: not in this subset.
 #include "common.cuh"
+#include "linepos.cuh"
 
 namespace cfd {
 
@@ -34,13 +35,14 @@ __device__ __forceinline__ double tmax(double a, double b) { return a > b ? a : 
 struct TF {
   const double* p;
   long long LD;
-  int M, T;
+  LinePos lp;
   __device__ __forceinline__ double operator()(int i, int j) const {   // 1-based (i,j)
-    const int j0 = j - 1;
-    return p[(long long)(i - 1) * LD + (j0 % M) * T + (j0 / M)];
+    return __ldg(p + (long long)(i - 1) * LD + lp(j - 1));
   }
 };
+// 1-based 1-D arrays: by-i in natural order, by-j in line layout (needs `lp` in scope)
 #define T1(a, i) __ldg((a) + (i) - 1)
+#define TJ(a, j) __ldg((a) + lp((j) - 1))
 
 __device__ __forceinline__ void block_sum_teach(double v, double* partial) {
   __shared__ double wsum[32];
@@ -58,18 +60,35 @@ __device__ __forceinline__ void block_sum_teach(double v, double* partial) {
   }
 }
 
-// promod.f90:79-91: outlet mass balance, sums in the reference's order (one thread; O(nj))
-__global__ void k_teach_outlet(const TeachParams P) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  const int ni = P.L.ni, nj = P.L.nj, nim1 = ni - 1;
-  const TF U{P.u, P.L.LD, P.L.M, P.L.T}, D{P.den, P.L.LD, P.L.M, P.L.T};
+// promod.f90:79-91: outlet mass balance.  The two sums run in the reference's order (thread 0 adds them one by
+// one), but the operands are gathered by the whole block into shared memory first, tile by tile, so the serial
+// part is a chain of additions on shared memory instead of a chain of dependent global loads.
+__global__ void __launch_bounds__(1024) k_teach_outlet(const TeachParams P) {
+  __shared__ double s_ard[1024], s_u[1024];
+  const int nj = P.L.nj, nim1 = P.L.ni - 1, M = P.L.M, T = P.L.T;
+  const long long LD = P.L.LD;
+  const double* dA = P.den + (long long)(nim1 - 1) * LD;   // den(nim1, :)
+  const double* dB = dA - LD;                              // den(nim1-1, :)
+  const double* uA = P.u + (long long)(nim1 - 1) * LD;     // u(nim1, :)
   double ardent = 0.0, flow = 0.0;
-  for (int j = 2; j <= nj - 1; ++j) {
-    const double arden = 0.5 * (D(nim1, j) + D(nim1 - 1, j)) * T1(P.r, j) * T1(P.sns, j);
-    ardent = ardent + arden;
-    flow = flow + arden * U(nim1, j);
+  for (int base = 2; base <= nj - 1; base += 1024) {
+    const int j = base + threadIdx.x;
+    if (j <= nj - 1) {
+      const int q = lpos(j - 1, M, T);
+      s_ard[threadIdx.x] = 0.5 * (__ldg(dA + q) + __ldg(dB + q)) * __ldg(P.r + q) * __ldg(P.sns + q);
+      s_u[threadIdx.x] = __ldg(uA + q);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int n = (nj - base < 1024) ? nj - base : 1024;
+      for (int k = 0; k < n; ++k) {
+        ardent = ardent + s_ard[k];
+        flow = flow + s_ard[k] * s_u[k];
+      }
+    }
+    __syncthreads();
   }
-  *P.uinc = (P.flowin - flow) / ardent;
+  if (threadIdx.x == 0) *P.uinc = (P.flowin - flow) / ardent;
 }
 
 // promod.f90:72-77, 92-94: the field edits of modu, after the assembly kernel has used the old values
@@ -94,16 +113,17 @@ __global__ void __launch_bounds__(256) k_teach_assemble_u(const TeachParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const TF U{P.u, LD, M, T}, V{P.v, LD, M, T}, D{P.den, LD, M, T}, S{P.vis, LD, M, T}, Pr{P.p, LD, M, T};
+    const LinePos lp(M, T, t);
+    const TF U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, S{P.vis, LD, lp}, Pr{P.p, LD, lp};
     const int i = i0 + 1;
     const double uinc = *P.uinc;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < P.jlo || j0 > P.jhi) continue;
-      const double arean = T1(P.rv, j + 1) * T1(P.sewu, i);
-      const double areas = T1(P.rv, j) * T1(P.sewu, i);
-      const double areaew = T1(P.r, j) * T1(P.sns, j);
-      double vol = T1(P.r, j) * T1(P.sewu, i) * T1(P.sns, j);
+      const double arean = TJ(P.rv, j + 1) * T1(P.sewu, i);
+      const double areas = TJ(P.rv, j) * T1(P.sewu, i);
+      const double areaew = TJ(P.r, j) * TJ(P.sns, j);
+      double vol = TJ(P.r, j) * T1(P.sewu, i) * TJ(P.sns, j);
       const double gn = 0.5 * (D(i, j + 1) + D(i, j)) * V(i, j + 1);
       const double gnw = 0.5 * (D(i - 1, j) + D(i - 1, j + 1)) * V(i - 1, j + 1);
       const double gs = 0.5 * (D(i, j - 1) + D(i, j)) * V(i, j);
@@ -117,8 +137,8 @@ __global__ void __launch_bounds__(256) k_teach_assemble_u(const TeachParams P) {
       const double cw = 0.5 * (gp + gw) * areaew;
       const double visn = 0.25 * (S(i, j) + S(i, j + 1) + S(i - 1, j) + S(i - 1, j + 1));
       const double viss = 0.25 * (S(i, j) + S(i, j - 1) + S(i - 1, j) + S(i - 1, j - 1));
-      const double dn = visn * arean / T1(P.dynp, j);
-      const double ds = viss * areas / T1(P.dyps, j);
+      const double dn = visn * arean / TJ(P.dynp, j);
+      const double ds = viss * areas / TJ(P.dyps, j);
       const double de = S(i, j) * areaew / T1(P.dxepu, i);
       const double dw = S(i - 1, j) * areaew / T1(P.dxpwu, i);
       const double smp = cn - cs + ce - cw;
@@ -135,15 +155,15 @@ __global__ void __launch_bounds__(256) k_teach_assemble_u(const TeachParams P) {
       const double dudxm = (U(i, j) - U(i - 1, j)) / T1(P.sew, i - 1);
       SU = (S(i, j) * dudxp - S(i - 1, j) * dudxm) / T1(P.sewu, i) * vol + SU;
       const double gamp = 0.25 * (S(i, j) + S(i - 1, j) + S(i, j + 1) + S(i - 1, j + 1));
-      const double dvdxp = T1(P.rv, j + 1) * (V(i, j + 1) - V(i - 1, j + 1)) / T1(P.dxep, i);
+      const double dvdxp = TJ(P.rv, j + 1) * (V(i, j + 1) - V(i - 1, j + 1)) / T1(P.dxep, i);
       const double gamm = 0.25 * (S(i, j) + S(i - 1, j) + S(i, j - 1) + S(i - 1, j - 1));
-      const double dvdxm = T1(P.rv, j) * (V(i, j) - V(i - 1, j)) / T1(P.dxep, i);
-      SU = SU + (gamp * dvdxp - gamm * dvdxm) / T1(P.sns, j) / T1(P.r, j) * vol;
+      const double dvdxm = TJ(P.rv, j) * (V(i, j) - V(i - 1, j)) / T1(P.dxep, i);
+      SU = SU + (gamp * dvdxp - gamm * dvdxm) / TJ(P.sns, j) / TJ(P.r, j) * vol;
       // ---- modu (promod.f90:36-77), laminar wall law: yplus = 11 <= 11.63 -> tmult = viscos/yp
       if (j == njm1) {
-        const double yp = T1(P.yv, nj) - T1(P.y, njm1);
+        const double yp = TJ(P.yv, nj) - TJ(P.y, njm1);
         const double tmult = P.viscos / yp;
-        SP = SP - tmult * T1(P.sewu, i) * T1(P.rv, nj);
+        SP = SP - tmult * T1(P.sewu, i) * TJ(P.rv, nj);
         AN = 0.0;
       }
       if (i == 3 && j >= P.jstep + 1) AW = 0.0;
@@ -154,7 +174,7 @@ __global__ void __launch_bounds__(256) k_teach_assemble_u(const TeachParams P) {
       double AP = AN + AS + AE + AW - SP;
       DU = DU / AP;
       double resor = AN * U(i, j + 1) + AS * u_s + AE * u_e + AW * U(i - 1, j) - AP * U(i, j) + SU;
-      vol = T1(P.r, j) * T1(P.sew, i) * T1(P.sns, j);
+      vol = TJ(P.r, j) * T1(P.sew, i) * TJ(P.sns, j);
       const double sorvol = P.great * vol;
       if (-SP > 0.5 * sorvol) resor = resor / sorvol;
       racc += fabs(resor);
@@ -177,15 +197,16 @@ __global__ void __launch_bounds__(256) k_teach_assemble_v(const TeachParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const TF U{P.u, LD, M, T}, V{P.v, LD, M, T}, D{P.den, LD, M, T}, S{P.vis, LD, M, T}, Pr{P.p, LD, M, T};
+    const LinePos lp(M, T, t);
+    const TF U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, S{P.vis, LD, lp}, Pr{P.p, LD, lp};
     const int i = i0 + 1;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < P.jlo || j0 > P.jhi) continue;
-      const double arean = T1(P.rcv, j + 1) * T1(P.sew, i);
-      const double areas = T1(P.rcv, j) * T1(P.sew, i);
-      const double areaew = T1(P.rv, j) * T1(P.snsv, j);
-      double vol = T1(P.rv, j) * T1(P.sew, i) * T1(P.snsv, j);
+      const double arean = TJ(P.rcv, j + 1) * T1(P.sew, i);
+      const double areas = TJ(P.rcv, j) * T1(P.sew, i);
+      const double areaew = TJ(P.rv, j) * TJ(P.snsv, j);
+      double vol = TJ(P.rv, j) * T1(P.sew, i) * TJ(P.snsv, j);
       const double gn = 0.5 * (D(i, j + 1) + D(i, j)) * V(i, j + 1);
       const double gp = 0.5 * (D(i, j) + D(i, j - 1)) * V(i, j);
       const double gs = 0.5 * (D(i, j - 1) + D(i, j - 2)) * V(i, j - 1);
@@ -199,8 +220,8 @@ __global__ void __launch_bounds__(256) k_teach_assemble_v(const TeachParams P) {
       const double cw = 0.5 * (gw + gsw) * areaew;
       const double vise = 0.25 * (S(i, j) + S(i + 1, j) + S(i, j - 1) + S(i + 1, j - 1));
       const double visw = 0.25 * (S(i, j) + S(i - 1, j) + S(i, j - 1) + S(i - 1, j - 1));
-      const double dn = S(i, j) * arean / T1(P.dynpv, j);
-      const double ds = S(i, j - 1) * areas / T1(P.dypsv, j);
+      const double dn = S(i, j) * arean / TJ(P.dynpv, j);
+      const double ds = S(i, j - 1) * areas / TJ(P.dypsv, j);
       const double de = vise * areaew / T1(P.dxep, i);
       const double dw = visw * areaew / T1(P.dxpw, i);
       const double smp = cn - cs + ce - cw;
@@ -213,23 +234,23 @@ __global__ void __launch_bounds__(256) k_teach_assemble_v(const TeachParams P) {
       double DV = 0.5 * (arean + areas);
       double SU = cpo * V(i, j) + DV * (Pr(i, j - 1) - Pr(i, j));
       double SP = -cp;
-      if (P.indcos == 2) SP = SP - S(i, j) * vol / (T1(P.rv, j) * T1(P.rv, j));   // applied twice in the reference
-      if (P.indcos == 2) SP = SP - S(i, j) * vol / (T1(P.rv, j) * T1(P.rv, j));   // (calc.f90:183-184)
-      const double dudyp = (U(i + 1, j) - U(i + 1, j - 1)) / T1(P.dyps, j);
+      if (P.indcos == 2) SP = SP - S(i, j) * vol / (TJ(P.rv, j) * TJ(P.rv, j));   // applied twice in the reference
+      if (P.indcos == 2) SP = SP - S(i, j) * vol / (TJ(P.rv, j) * TJ(P.rv, j));   // (calc.f90:183-184)
+      const double dudyp = (U(i + 1, j) - U(i + 1, j - 1)) / TJ(P.dyps, j);
       const double gamp = 0.25 * (S(i, j) + S(i + 1, j) + S(i, j - 1) + S(i + 1, j - 1));
       const double gamm = 0.25 * (S(i, j) + S(i - 1, j) + S(i, j - 1) + S(i - 1, j - 1));
-      const double dudym = (U(i, j) - U(i, j - 1)) / T1(P.dyps, j);
+      const double dudym = (U(i, j) - U(i, j - 1)) / TJ(P.dyps, j);
       SU = SU + (gamp * dudyp - gamm * dudym) / T1(P.sew, i) * vol;
-      const double dvdyp = (V(i, j + 1) - V(i, j)) / T1(P.sns, j);
-      const double rgamp = S(i, j) * T1(P.r, j);
-      const double dvdym = (V(i, j) - V(i, j - 1)) / T1(P.sns, j - 1);
-      const double rgamm = S(i, j - 1) * T1(P.r, j - 1);
-      SU = SU + (rgamp * dvdyp - rgamm * dvdym) / (T1(P.r, j) * T1(P.sns, j)) * vol;
+      const double dvdyp = (V(i, j + 1) - V(i, j)) / TJ(P.sns, j);
+      const double rgamp = S(i, j) * TJ(P.r, j);
+      const double dvdym = (V(i, j) - V(i, j - 1)) / TJ(P.sns, j - 1);
+      const double rgamm = S(i, j - 1) * TJ(P.r, j - 1);
+      SU = SU + (rgamp * dvdyp - rgamm * dvdym) / (TJ(P.r, j) * TJ(P.sns, j)) * vol;
       // ---- modv (promod.f90:105-128)
       if (i == P.istep && j >= P.jstep + 1) {
         const double xp = T1(P.x, P.istep) - T1(P.xu, P.istep);
         const double tmult = P.viscos / xp;
-        SP = SP - tmult * T1(P.snsv, j) * T1(P.rv, j);
+        SP = SP - tmult * TJ(P.snsv, j) * TJ(P.rv, j);
         AW = 0.0;
       }
       if (j == njm1 && i >= P.istep) AN = 0.0;
@@ -238,7 +259,7 @@ __global__ void __launch_bounds__(256) k_teach_assemble_v(const TeachParams P) {
       double AP = AN + AS + AE + AW - SP;
       DV = DV / AP;
       double resor = AN * V(i, j + 1) + AS * V(i, j - 1) + AE * V(i + 1, j) + AW * V(i - 1, j) - AP * V(i, j) + SU;
-      vol = T1(P.r, j) * T1(P.sew, i) * T1(P.sns, j);
+      vol = TJ(P.r, j) * T1(P.sew, i) * TJ(P.sns, j);
       const double sorvol = P.great * vol;
       if (-SP > 0.5 * sorvol) resor = resor / sorvol;
       racc += fabs(resor);
@@ -261,14 +282,15 @@ __global__ void __launch_bounds__(256) k_teach_assemble_p(const TeachParams P) {
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib) {
-    const TF U{P.u, LD, M, T}, V{P.v, LD, M, T}, D{P.den, LD, M, T}, DU{P.du_in, LD, M, T}, DV{P.dv_in, LD, M, T};
+    const LinePos lp(M, T, t);
+    const TF U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, DU{P.du_in, LD, lp}, DV{P.dv_in, LD, lp};
     const int i = i0 + 1;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < P.jlo || j0 > P.jhi) continue;
-      const double arean = T1(P.rv, j + 1) * T1(P.sew, i);
-      const double areas = T1(P.rv, j) * T1(P.sew, i);
-      const double areaew = T1(P.r, j) * T1(P.sns, j);
+      const double arean = TJ(P.rv, j + 1) * T1(P.sew, i);
+      const double areas = TJ(P.rv, j) * T1(P.sew, i);
+      const double areaew = TJ(P.r, j) * TJ(P.sns, j);
       const double denn = 0.5 * (D(i, j) + D(i, j + 1));
       const double dens = 0.5 * (D(i, j) + D(i, j - 1));
       const double dene = 0.5 * (D(i, j) + D(i + 1, j));
@@ -310,12 +332,12 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which) {
   P.ap = c->field[CFD_AP]; P.su = c->field[CFD_SU];
   P.ufield = c->field[CFD_U];
   P.uinc = c->res_dev + 7;          // last slot of the packed scalar block
-  P.x = c->geomn[CFD_G_X]; P.y = c->geomn[CFD_G_Y]; P.xu = c->geomn[CFD_G_XU]; P.yv = c->geomn[CFD_G_YV];
-  P.r = c->geomn[CFD_G_R]; P.rv = c->geomn[CFD_G_RV]; P.rcv = c->geomn[CFD_G_RCV];
-  P.sew = c->geomn[CFD_G_SEW]; P.sns = c->geomn[CFD_G_SNS]; P.sewu = c->geomn[CFD_G_SEWU]; P.snsv = c->geomn[CFD_G_SNSV];
-  P.dxep = c->geomn[CFD_G_DXEP]; P.dxpw = c->geomn[CFD_G_DXPW]; P.dynp = c->geomn[CFD_G_DYNP]; P.dyps = c->geomn[CFD_G_DYPS];
-  P.dxepu = c->geomn[CFD_G_DXEPU]; P.dxpwu = c->geomn[CFD_G_DXPWU]; P.dynpv = c->geomn[CFD_G_DYNPV];
-  P.dypsv = c->geomn[CFD_G_DYPSV];
+  P.x = c->geomn[CFD_G_X]; P.y = c->geom[CFD_G_Y]; P.xu = c->geomn[CFD_G_XU]; P.yv = c->geom[CFD_G_YV];
+  P.r = c->geom[CFD_G_R]; P.rv = c->geom[CFD_G_RV]; P.rcv = c->geom[CFD_G_RCV];
+  P.sew = c->geomn[CFD_G_SEW]; P.sns = c->geom[CFD_G_SNS]; P.sewu = c->geomn[CFD_G_SEWU]; P.snsv = c->geom[CFD_G_SNSV];
+  P.dxep = c->geomn[CFD_G_DXEP]; P.dxpw = c->geomn[CFD_G_DXPW]; P.dynp = c->geom[CFD_G_DYNP]; P.dyps = c->geom[CFD_G_DYPS];
+  P.dxepu = c->geomn[CFD_G_DXEPU]; P.dxpwu = c->geomn[CFD_G_DXPWU]; P.dynpv = c->geom[CFD_G_DYNPV];
+  P.dypsv = c->geom[CFD_G_DYPSV];
   const int ni = c->L.ni, nj = c->L.nj;
   P.jhi = nj - 2;
   P.ib = ni - 2;
@@ -335,8 +357,23 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which) {
     return CFD_ERR_INVALID;
   }
   P.partial = c->partial + (size_t)which * c->max_partials;
+  if (!c->exact_assembly) {   // production (red/black) contexts: teach_fast_kernels.cu, equations stored divided by ap
+    if (which == 0) {
+      k_teach_outlet<<<1, 1024, 0, c->stream>>>(P);
+      ++c->launches;
+    }
+    const int nb = cfd_launch_teach_assemble_fast(c, which, P.ia, P.ib, P.partial, P.uinc);
+    if (nb < 0) return nb;
+    if (which == 0) {
+      const int n = (ni > nj ? ni : nj) + 1;
+      k_teach_modu_fields<<<(n + 127) / 128, 128, 0, c->stream>>>(P);
+      ++c->launches;
+    }
+    CFD_CUDA(cudaGetLastError());
+    return cfd_launch_reduce_partials(c, which, nb);
+  }
   if (which == 0) {
-    k_teach_outlet<<<1, 32, 0, c->stream>>>(P);
+    k_teach_outlet<<<1, 1024, 0, c->stream>>>(P);
     k_teach_assemble_u<<<grid, block, 0, c->stream>>>(P);
     const int n = (ni > nj ? ni : nj) + 1;
     k_teach_modu_fields<<<(n + 127) / 128, 128, 0, c->stream>>>(P);
