@@ -3,7 +3,7 @@
 (Re=1000, 4096^2 control volumes per GPU, red/black line TDMA), reported as cell-updates/s (GLUPS) and
 iterations/s, with the HBM roofline of the dominant kernel and a CPU baseline beside it.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat|step]
 
 A "step" is one pass of the hot path: calcu + calcv + calcp (cavity_fvm.f90:554-557) over the whole grid.
 For N>1 launch with torch.distributed.run (one rank per GPU); the grid is slab-decomposed along i (weak scaling:
@@ -385,6 +385,85 @@ def run_heat(args):
     emit(out)
 
 
+def run_step(args):
+    """--workload step: BASELINE.json configs[4], TEACH backward-step SIMPLE (laminar, nswp 3/3/5) on 16384 x 4096,
+    i-slabs over the N GPUs (STRONG scaling: the global grid is fixed).  One step = one outer iteration."""
+    import torch
+    import torch.distributed as dist
+
+    import cfd_b200
+    from cfd_b200.dist import SlabCavity, TeachSlab
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    K, W = args.steps, args.warmup
+    hbm_peak, peak_src = peaks()
+    NI, NJ = 16384, 4096
+    stream = torch.cuda.Stream()
+    if world == 1:
+        solver = cfd_b200.TeachFVM(NI, NJ, epsx=1.0, order="redblack", device=local)
+        solver.set_stream(stream.cuda_stream)
+        step, ctx0 = solver.iterate_async, solver
+    else:
+        solver = SlabCavity(NI - 2, NJ - 2, stream=stream, slab_cls=TeachSlab, epsx=1.0)
+        step, ctx0 = solver.iterate_async, solver.ctx
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            step(1)
+        barrier()
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        l0 = ctx0.launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(K):
+            step(1)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = ctx0.launches - l0
+        clocks = sampler.stop() if rank == 0 else None
+        res = solver.residuals()
+    if world > 1:
+        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    cells = (NI - 2) * (NJ - 2)
+    glups = cells * K / (ms * 1e-3) / 1e9
+    B = 1056                                                  # SURVEY 8(d): 132 doubles / cell / outer iteration
+    out = {"metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K,
+           "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic", "iters_per_s": K / (ms * 1e-3),
+           "config": {"workload": f"backward-facing step FVM SIMPLE (TEACH family, laminar, axisymmetric, hybrid scheme, "
+                                  f"urf .5/.5/1, nswp 3/3/5) on {NI}x{NJ}, red/black line TDMA (BASELINE.json configs[4])",
+                      "parallelism": "single GPU" if world == 1 else f"i-slabs x{world}, 1-line halo exchange (NCCL "
+                                     "send/recv), all-reduced residuals; outlet mass balance on the last rank",
+                      "l2": "inputs larger than L2 (7.5 GB of live fields); no explicit flush",
+                      "line_layout": ctx0.layout},
+           "residuals_last": [float(x) for x in res[:3]], "gpu_launches": int(launches),
+           "roofline": {"bound": "hbm", "kernel": "whole outer iteration", "achieved": B * glups / world, "peak": hbm_peak,
+                        "unit": "GB/s", "frac": B * glups / world / hbm_peak, "peak_source": peak_src, "traffic": None,
+                        "algorithmic_bytes_per_cell": B},
+           "e2e": None, "clocks": clocks}
+    if rank == 0:
+        emit(out)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 _REAL_STDOUT = None
 
 
@@ -413,7 +492,7 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat"])
+    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
@@ -422,6 +501,8 @@ def main():
         run_reference(args)
     elif args.workload == "heat":
         run_heat(args)
+    elif args.workload == "step":
+        run_step(args)
     else:
         run_ours(args)
 

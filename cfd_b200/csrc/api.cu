@@ -139,8 +139,6 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CFD_REQUIRE(cfg->iadv >= 1 && cfg->iadv <= (general ? 4 : 3), "iadv out of range");
   if (teach) {
     CFD_REQUIRE(cfg->iadv == 3, "the TEACH family has the hybrid scheme only (calc.f90:69-72): iadv must be 3");
-    CFD_REQUIRE(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni),
-                "TEACH-family contexts do not shard yet (single GPU)");
     CFD_REQUIRE(cfg->indcos == 1 || cfg->indcos == 2, "indcos must be 1 (plane) or 2 (axisymmetric)");
     CFD_REQUIRE(cfg->istep >= 2 && cfg->jstep >= 2 && cfg->jstep < cfg->nj - 1, "istep / jstep out of range");
     CFD_REQUIRE(cfg->ni >= 6 && cfg->nj >= 6, "TEACH family needs ni, nj >= 6");
@@ -197,6 +195,12 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   {
     const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
     c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || general;
+    if (teach && c->exact_assembly &&
+        !(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni))) {
+      delete c;
+      cfd_set_error("TEACH-family i-slab contexts need the red/black order with the production assembly kernels");
+      return CFD_ERR_UNSUPPORTED;
+    }
     c->L.nc = c->exact_assembly ? 6 : 5;
     c->L.cSL = (long long)c->L.nc * c->L.LD;
     c->L.cSK = c->L.nc * c->L.T;

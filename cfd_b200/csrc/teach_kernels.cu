@@ -25,6 +25,8 @@ struct TeachParams {
   double *ae, *aw, *an, *as, *ap, *su, *dout;
   double* ufield;           // u, writable (k_teach_modu_fields)
   double* uinc;             // device scalar
+  int nsym;                 // local lines 1..nsym get u(i,1) = u(i,2) (global i <= ni-1)
+  int has_outlet;           // this context holds the outlet column (global i = ni) as its last local line
   const double *x, *y, *xu, *yv, *r, *rv, *rcv, *sew, *sns, *sewu, *snsv;
   const double *dxep, *dxpw, *dynp, *dyps, *dxepu, *dxpwu, *dynpv, *dypsv;
   double* partial;
@@ -96,10 +98,10 @@ __global__ void k_teach_modu_fields(const TeachParams P) {
   const int ni = P.L.ni, nj = P.L.nj, M = P.L.M, T = P.L.T;
   const long long LD = P.L.LD;
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  const double uinc = *P.uinc;
   auto at = [&](int i, int j) -> double& { return P.ufield[(long long)(i - 1) * LD + ((j - 1) % M) * T + ((j - 1) / M)]; };
-  if (n >= 1 && n <= ni - 1) at(n, 1) = at(n, 2);                 // symmetry axis, i = 1..ni-1
-  if (n >= 2 && n <= nj - 1) {                                    // outlet column, j = 2..nj-1
+  if (n >= 1 && n <= P.nsym) at(n, 1) = at(n, 2);                 // symmetry axis, global i = 1..ni-1
+  if (P.has_outlet && n >= 2 && n <= nj - 1) {                    // outlet column, j = 2..nj-1
+    const double uinc = *P.uinc;
     if (n == 2) at(ni, 1) = at(ni, 2);                            // i = ni of the symmetry loop sees the OLD u(ni,2)
     at(ni, n) = at(ni - 1, n) + uinc;
   }
@@ -339,14 +341,26 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which) {
   P.dxepu = c->geomn[CFD_G_DXEPU]; P.dxpwu = c->geomn[CFD_G_DXPWU]; P.dynpv = c->geom[CFD_G_DYNPV];
   P.dypsv = c->geom[CFD_G_DYPSV];
   const int ni = c->L.ni, nj = c->L.nj;
+  const int NI = c->cfg.ni_global ? c->cfg.ni_global : ni, goff = c->cfg.goff;
   P.jhi = nj - 2;
-  P.ib = ni - 2;
+  // global 1-based line ranges 3..NI-1 (u) / 2..NI-1 (v, p'), clamped to the lines this context owns
+  const int lo_own = c->cfg.halo_w, hi_own = ni - 1 - c->cfg.halo_e;
+  P.ia = (which == 0 ? 2 : 1) - goff;
+  P.ib = NI - 2 - goff;
+  if (P.ia < lo_own) P.ia = lo_own;
+  if (P.ib > hi_own) P.ib = hi_own;
+  P.has_outlet = (goff + ni == NI);
+  P.nsym = (NI - 1 - goff < ni) ? NI - 1 - goff : ni;
   if (which == 0) {
-    P.ia = 2; P.jlo = 1; P.dout = c->field[CFD_DU];
+    P.jlo = 1; P.dout = c->field[CFD_DU];
   } else if (which == 1) {
-    P.ia = 1; P.jlo = 2; P.dout = c->field[CFD_DV];
+    P.jlo = 2; P.dout = c->field[CFD_DV];
   } else {
-    P.ia = 1; P.jlo = 1;
+    P.jlo = 1;
+  }
+  if (P.ib < P.ia) {   // a slab that owns none of this equation's lines still publishes a zero residual
+    CFD_CUDA(cudaMemsetAsync(c->res_dev + which, 0, sizeof(double), c->stream));
+    return CFD_OK;
   }
   P.urf = c->cfg.urf[which];
   const int nlines = P.ib - P.ia + 1;
@@ -358,7 +372,7 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which) {
   }
   P.partial = c->partial + (size_t)which * c->max_partials;
   if (!c->exact_assembly) {   // production (red/black) contexts: teach_fast_kernels.cu, equations stored divided by ap
-    if (which == 0) {
+    if (which == 0 && P.has_outlet) {
       k_teach_outlet<<<1, 1024, 0, c->stream>>>(P);
       ++c->launches;
     }

@@ -166,6 +166,9 @@ class Slab:
         self.ctx.upload("den", den)
         self.ctx.upload("vis", vis)
         self.ctx.upload("u", u)
+        self._finish(nswp)
+
+    def _finish(self, nswp):
         self.nswp = nswp
         self.ipref, self.jpref = self.ctx.ipref, self.ctx.jpref
         self.owner_of_pref = self.lo <= self.ipref <= self.hi
@@ -193,6 +196,27 @@ class Slab:
         return a[self.hw:self.hw + self.nown]
 
 
+class TeachSlab(Slab):
+    """One rank's i-slab of the TEACH backward-step problem (BASELINE.json configs[4]: 16384 x 4096 over 8 GPUs).
+    `nicv, njcv` are ni-2, nj-2 of the global grid, as for the cavity slabs.  The outlet mass balance of modu
+    (promod.f90:79-94) lives entirely on the last rank (it owns the lines ni-2 .. ni), the inlet flow is a host
+    constant, so the stage list is the cavity's: no extra exchange."""
+
+    def __init__(self, nicv, njcv, rank, world, *, device=-1, nswp=(3, 3, 5), **kw):
+        from .teach import TeachFVM
+        self.rank, self.world = rank, world
+        ni_g, nj = nicv + 2, njcv + 2
+        self.ni_global, self.nj = ni_g, nj
+        self.goff, self.ni, self.hw, self.he = slab_extent(ni_g, world, rank)
+        self.lo, self.hi = partition(ni_g, world)[rank]
+        self.nown = self.hi - self.lo + 1
+        if world > 1 and rank == world - 1 and self.nown < 3:
+            raise ValueError("the last TEACH slab must own the lines ni-2 .. ni (outlet mass balance)")
+        self.ctx = TeachFVM(ni_g, nj, order="redblack", device=device, nswp=nswp, ni_local=self.ni, goff=self.goff,
+                            halo_w=self.hw, halo_e=self.he, **kw)
+        self._finish(nswp)
+
+
 # stages of one outer iteration: ("compute", fn(slab)) or ("halo", field, w, e) or ("ppref",)
 def iteration_stages(nswp):
     st = [("halos", (("u", 1, 1), ("v", 1, 1), ("p", 1, 0))),
@@ -214,13 +238,15 @@ def iteration_stages(nswp):
 class SlabCavity:
     """SPMD driver: one Slab per process over torch.distributed (bench.py, torchrun)."""
 
-    def __init__(self, nicv, njcv, *, reynolds=1000.0, stream=None, **kw):
+    def __init__(self, nicv, njcv, *, reynolds=1000.0, stream=None, slab_cls=None, **kw):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
         self.comm = TorchDistComm()
         self.rank, self.world = self.comm.rank, self.comm.world
-        self.slab = Slab(nicv, njcv, self.rank, self.world, reynolds=reynolds, device=torch.cuda.current_device(), **kw)
+        if slab_cls is None:
+            slab_cls, kw = Slab, dict(kw, reynolds=reynolds)
+        self.slab = slab_cls(nicv, njcv, self.rank, self.world, device=torch.cuda.current_device(), **kw)
         self.ctx = self.slab.ctx
         if stream is not None:
             self.ctx.set_stream(stream.cuda_stream)
@@ -335,9 +361,9 @@ class SlabCavity:
 class LocalSlabCavity:
     """All slabs in one process on one GPU (tests): same stages, LocalComm copies instead of messages."""
 
-    def __init__(self, nicv, njcv, world, **kw):
+    def __init__(self, nicv, njcv, world, slab_cls=None, **kw):
         self.world = world
-        self.slabs = [Slab(nicv, njcv, r, world, **kw) for r in range(world)]
+        self.slabs = [(slab_cls or Slab)(nicv, njcv, r, world, **kw) for r in range(world)]
         self.comm = LocalComm(world)
         self.stages = iteration_stages(self.slabs[0].nswp)
         self.comm.exchange_all(self.slabs, "den", HALO_W, HALO_E)

@@ -82,41 +82,54 @@ def teach_init(x, y, indcos):
 
 
 class TeachFVM(CavityFVM):
-    """One GPU context of CFD_FAMILY_TEACH with the shipped case's literals (control.f90:15-141), laminar."""
+    """One GPU context of CFD_FAMILY_TEACH with the shipped case's literals (control.f90:15-141), laminar.
+
+    `ni_local / goff / halo_w / halo_e` make it an i-slab of the global ni x nj problem (lines goff+1 .. goff+ni_local,
+    red/black order only): geometry and initial fields are cut from the global 1-D arrays / per-line formulas."""
 
     def __init__(self, ni=100, nj=100, *, order="redblack", epsx=1.05, indcos=2, rlarge=0.0124, uin=0.5,
-                 densit=1000.0, viscos=0.8e-3, urf=(0.5, 0.5, 1.0), nswp=(3, 3, 5), jstep=None, device=-1, tdma_m=0):
+                 densit=1000.0, viscos=0.8e-3, urf=(0.5, 0.5, 1.0), nswp=(3, 3, 5), jstep=None, device=-1, tdma_m=0,
+                 ni_local=None, goff=0, halo_w=0, halo_e=0):
         self.lib = _lib.load()
-        self.ni, self.nj = ni, nj
-        self.ni_global, self.nicv, self.njcv, self.goff = ni, ni - 2, nj - 2, 0
+        nl = ni if ni_local is None else ni_local
+        self.ni, self.nj = nl, nj
+        self.ni_global, self.nicv, self.njcv, self.goff = ni, ni - 2, nj - 2, goff
         self.istep = 2
         self.jstep = jstep if jstep is not None else max(2, int(round(0.08 * nj)))
         self.ipref, self.jpref = 2, 2
         self.imon, self.jmon = min(10, ni - 1), min(10, nj - 1)
         x, y = teach_grid(ni, nj, rlarge, epsx)
-        g = teach_init(x, y, indcos)
-        for k, v in g.items():
+        g = teach_init(x, y, indcos)                                   # global 1-D arrays (host logic, O(ni+nj))
+        self.geometry_global = g
+        sl = slice(goff, goff + nl)
+        gl = {k: (v[sl].copy() if len(v) == ni and k in _BY_I else v) for k, v in g.items()}
+        for k, v in gl.items():
             setattr(self, k, v)
-        # initial fields and inlet mass flow (control.f90:148-179, 197-203)
-        den = np.full((ni, nj), densit, order="F")
-        vis = np.full((ni, nj), viscos, order="F")
-        u = np.zeros((ni, nj), order="F")
+        # initial fields and inlet mass flow (control.f90:148-179, 197-203), local lines only
+        den = np.full((nl, nj), densit, order="F")
+        vis = np.full((nl, nj), viscos, order="F")
+        u = np.zeros((nl, nj), order="F")
         js, jstp1 = self.jstep, self.jstep + 1
-        u[1, 1:js] = uin
-        jfin = jstp1
-        for i in range(2, ni + 1):
-            if i >= self.istep + 1:
-                jfin = nj
-            factor = (self.yv[jstp1 - 1] * self.rv[jstp1 - 1]) / (self.yv[jfin - 1] * self.rv[jfin - 1])
-            u[i - 1, 1:jfin - 1] = uin * factor
-        flowin = 0.0
+        yv, rv = g["yv"], g["rv"]
+        for il in range(nl):
+            i = il + 1 + goff                                           # global 1-based line
+            if i == 2:
+                u[il, 1:js] = uin
+            if i >= 2:
+                jfin = nj if i >= self.istep + 1 else jstp1
+                factor = (yv[jstp1 - 1] * rv[jstp1 - 1]) / (yv[jfin - 1] * rv[jfin - 1])
+                u[il, 1:jfin - 1] = uin * factor
+        flowin = 0.0                                                    # inlet plane: den uniform, u(2,j) as set above
+        jfin2 = nj if 2 >= self.istep + 1 else jstp1
+        u2 = np.zeros(nj)
+        u2[1:jfin2 - 1] = uin * (yv[jstp1 - 1] * rv[jstp1 - 1]) / (yv[jfin2 - 1] * rv[jfin2 - 1])
         for j in range(2, nj):
-            arden = 0.5 * (den[0, j - 1] + den[1, j - 1]) * self.r[j - 1] * self.sns[j - 1]
-            flowin = flowin + arden * u[1, j - 1]
+            arden = 0.5 * (densit + densit) * g["r"][j - 1] * g["sns"][j - 1]
+            flowin = flowin + arden * u2[j - 1]
         self.flowin = flowin
         cfg = CfdConfig()
         cfg.family = _lib.FAMILY_TEACH
-        cfg.ni, cfg.nj, cfg.iadv = ni, nj, 3
+        cfg.ni, cfg.nj, cfg.iadv = nl, nj, 3
         cfg.order = _lib.ORDER_SEQUENTIAL if order in ("sequential", "seq", 1) else _lib.ORDER_REDBLACK
         for k in range(3):
             cfg.nswp[k] = nswp[k]
@@ -124,11 +137,17 @@ class TeachFVM(CavityFVM):
         cfg.ipref, cfg.jpref, cfg.device, cfg.tdma_m = 2, 2, device, tdma_m
         cfg.indcos, cfg.istep, cfg.jstep = indcos, self.istep, self.jstep
         cfg.viscos, cfg.flowin, cfg.great = viscos, flowin, 1.0e30
+        cfg.goff = goff
+        cfg.ni_global = ni if ni_local is not None else 0
+        cfg.halo_w, cfg.halo_e = halo_w, halo_e
         self._cfg = cfg
         self._h = C.c_void_p()
         check(self.lib.cfd_create(C.byref(self._h), C.byref(cfg)))
-        self.set_geometry(**g)
+        self.set_geometry(**gl)
         self.upload("den", den)
         self.upload("vis", vis)
         self.upload("u", u)
         self.resoru = self.resorv = self.resorm = 0.0
+
+
+_BY_I = ("x", "xu", "sew", "sewu", "dxep", "dxpw", "dxepu", "dxpwu")

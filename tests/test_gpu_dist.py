@@ -28,6 +28,25 @@ def test_local_slabs_match_single_context(cfd, world, shape):
     g.close()
 
 
+@pytest.mark.parametrize("world,shape", [(2, (40, 34)), (3, (66, 50)), (4, (130, 96))])
+def test_teach_local_slabs_match_single_context(cfd, world, shape):
+    """Backward-step family cut into i-slabs: same bits as the single red/black context (fields and residuals up to
+    the order of the residual sums), including the outlet mass balance on the last slab and the step-wall hooks."""
+    from cfd_b200.dist import LocalSlabCavity, TeachSlab
+    ni, nj = shape
+    g = cfd.TeachFVM(ni, nj, order="redblack")
+    s = LocalSlabCavity(ni - 2, nj - 2, world, slab_cls=TeachSlab)
+    for _ in range(3):
+        r1 = g.iterate(3)
+        r2 = s.iterate(3)
+        for a, b in zip(r1, r2):
+            assert abs(a - b) <= 1e-11 * abs(a)
+    for name in ("u", "v", "p", "pp"):
+        assert np.array_equal(s.gather_field(name), g.download(name)), name
+    s.close()
+    g.close()
+
+
 def _nccl_worker(rank, world, port, shape, q):
     import torch
     import torch.distributed as dist
