@@ -29,7 +29,9 @@ class CfdConfig(C.Structure):
                 ("goff", C.c_int), ("ni_global", C.c_int), ("halo_w", C.c_int), ("halo_e", C.c_int),
                 ("sew_nim1", C.c_double), ("solve_flow", C.c_int), ("solve_t", C.c_int),
                 ("indcos", C.c_int), ("istep", C.c_int), ("jstep", C.c_int), ("_pad", C.c_int),
-                ("viscos", C.c_double), ("flowin", C.c_double), ("great", C.c_double)]
+                ("viscos", C.c_double), ("flowin", C.c_double), ("great", C.c_double),
+                ("joff", C.c_int), ("nj_global", C.c_int), ("halo_s", C.c_int), ("halo_n", C.c_int),
+                ("sns_njm1", C.c_double)]
 
 
 class CfdHookDesc(C.Structure):
@@ -91,6 +93,11 @@ SYMBOLS = {
     "cfd_assemble_p": (C.c_int, [_vp]),
     "cfd_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cfd_correct": (C.c_int, [_vp, _vp]),
+    "cfd_spike_basis": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "cfd_spike_pack": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
+    "cfd_spike_finish": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int, C.c_int]),
+    "cfd_rows_pack": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp]),
+    "cfd_rows_unpack": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp]),
     "cfd_residuals": (C.c_int, [_vp, _dp]),
     "cfd_residual_device_ptr": (C.c_int, [_vp, C.POINTER(_vp)]),
     "cfd_heat_create": (C.c_int, [C.POINTER(_vp), C.POINTER(CfdHeatConfig)]),

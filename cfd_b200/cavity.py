@@ -53,17 +53,21 @@ class CavityFVM:
 
     def __init__(self, nicv=10, njcv=10, *, iadv=3, order="redblack", urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3),
                  ipref=None, jpref=None, device=-1, tdma_m=0,
-                 ni_local=None, goff=0, halo_w=0, halo_e=0, sew_nim1=0.0):
+                 ni_local=None, goff=0, halo_w=0, halo_e=0, sew_nim1=0.0,
+                 nj_local=None, joff=0, halo_s=0, halo_n=0, sns_njm1=0.0):
         self.lib = _lib.load()
         self.nicv, self.njcv = nicv, njcv
         self.ni_global, self.nj = nicv + 2, njcv + 2
+        self.nj_global, self.joff = self.nj, joff
+        if nj_local is not None:
+            self.nj = nj_local
         self.ni = ni_local if ni_local is not None else self.ni_global
-        self.nim1, self.njm1 = self.ni_global - 1, self.nj - 1
+        self.nim1, self.njm1 = self.ni_global - 1, self.nj_global - 1
         self.iadv = iadv
         self.urfu, self.urfv, self.urfp = urf
         self.nswpu, self.nswpv, self.nswpp = nswp
         self.ipref = ipref if ipref is not None else self.ni_global // 2      # cavity_fvm.f90:549-550
-        self.jpref = jpref if jpref is not None else self.nj // 2
+        self.jpref = jpref if jpref is not None else self.nj_global // 2
         self.imon, self.jmon = self.ipref, self.jpref
         self.goff = goff
         cfg = CfdConfig()
@@ -81,6 +85,10 @@ class CavityFVM:
         cfg.ni_global = self.ni_global if (ni_local is not None) else 0
         cfg.halo_w, cfg.halo_e = halo_w, halo_e
         cfg.sew_nim1 = sew_nim1
+        cfg.joff = joff
+        cfg.nj_global = self.nj_global if (nj_local is not None) else 0
+        cfg.halo_s, cfg.halo_n = halo_s, halo_n
+        cfg.sns_njm1 = sns_njm1
         self._cfg = cfg
         self._h = C.c_void_p()
         check(self.lib.cfd_create(C.byref(self._h), C.byref(cfg)))
@@ -218,6 +226,23 @@ class CavityFVM:
 
     def correct(self, ppref_device_ptr: int | None = None):
         check(self.lib.cfd_correct(self._h, C.c_void_p(ppref_device_ptr) if ppref_device_ptr else None))
+
+    # -- j-slabs: partition method for lines cut across contexts (device pointers as ints) ------------------
+    def spike_basis(self, istart, jstart):
+        check(self.lib.cfd_spike_basis(self._h, istart, jstart))
+
+    def spike_pack(self, istart, jstart, phi, colour, which, buf_ptr: int):
+        check(self.lib.cfd_spike_pack(self._h, istart, jstart, FIELD_ID[phi], colour, which, C.c_void_p(buf_ptr)))
+
+    def spike_finish(self, istart, jstart, phi, colour, wz_all_ptr: int, y_all_ptr: int, rank: int, world: int):
+        check(self.lib.cfd_spike_finish(self._h, istart, jstart, FIELD_ID[phi], colour, C.c_void_p(wz_all_ptr),
+                                        C.c_void_p(y_all_ptr), rank, world))
+
+    def rows_pack(self, name, j_first, nrows, buf_ptr: int):
+        check(self.lib.cfd_rows_pack(self._h, FIELD_ID[name], j_first, nrows, C.c_void_p(buf_ptr)))
+
+    def rows_unpack(self, name, j_first, nrows, buf_ptr: int):
+        check(self.lib.cfd_rows_unpack(self._h, FIELD_ID[name], j_first, nrows, C.c_void_p(buf_ptr)))
 
     def residual_device_ptr(self) -> int:
         p = C.c_void_p()

@@ -153,6 +153,12 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   }
   CFD_REQUIRE(cfg->order == CFD_ORDER_REDBLACK || cfg->order == CFD_ORDER_SEQUENTIAL, "bad order");
   CFD_REQUIRE(cfg->halo_w >= 0 && cfg->halo_e >= 0 && cfg->halo_w + cfg->halo_e < cfg->ni, "bad halo widths");
+  CFD_REQUIRE(cfg->halo_s >= 0 && cfg->halo_n >= 0 && cfg->halo_s + cfg->halo_n < cfg->nj, "bad halo row counts");
+  if (cfg->halo_s || cfg->halo_n || cfg->joff) {
+    CFD_REQUIRE(cfg->family == CFD_FAMILY_CAVITY && cfg->order == CFD_ORDER_REDBLACK,
+                "j-slab contexts: cavity family, red/black order only");
+    CFD_REQUIRE(cfg->nj_global >= cfg->nj, "j-slab contexts need nj_global");
+  }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     cfd_set_error("no CUDA device visible; libcfd_b200 has no CPU fallback");
@@ -181,6 +187,7 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->launches = 0;
   for (auto& g : c->gfast) g = nullptr;
   for (auto& g : c->tfast) g = nullptr;
+  c->spike_w = c->spike_z = c->spike_small = nullptr;
   c->tfast_ready = false;
   int want_m = cfg->tdma_m;
   if (want_m == 0) {
@@ -260,6 +267,9 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   for (auto& g : c->geomn) if (g) cudaFree(g);
   for (auto& g : c->gfast) if (g) cudaFree(g);
   for (auto& g : c->tfast) if (g) cudaFree(g);
+  if (c->spike_w) cudaFree(c->spike_w);
+  if (c->spike_z) cudaFree(c->spike_z);
+  if (c->spike_small) cudaFree(c->spike_small);
   if (c->stage) cudaFree(c->stage);
   if (c->partial) cudaFree(c->partial);
   if (c->res_dev) cudaFree(c->res_dev);

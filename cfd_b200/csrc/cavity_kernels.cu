@@ -409,6 +409,7 @@ struct CorrParams {
   Layout L;
   int ia, ib, jlo, jhi;
   int i_skip;            // local 0-based line where u is NOT corrected (global i == 2), or -1
+  int j_skip;            // local 0-based node where v is NOT corrected (global j == 2)
   double urfp;
   const double *pp, *du, *dv;
   const double* ppref;   // device address of pp(ipref,jpref)
@@ -434,7 +435,7 @@ __global__ void __launch_bounds__(256) k_correct(const CorrParams P) {
     if (j0 >= P.jlo && j0 <= P.jhi) {
       P.p[o + q] = P.p[o + q] + P.urfp * (pp_c - ppref);
       if (i0 != P.i_skip) P.u[o + q] = P.u[o + q] + __ldg(P.du + o + q) * (__ldg(ppW + q) - pp_c);
-      if (j0 != P.jlo) P.v[o + q] = P.v[o + q] + __ldg(P.dv + o + q) * (pp_m - pp_c);
+      if (j0 != P.j_skip) P.v[o + q] = P.v[o + q] + __ldg(P.dv + o + q) * (pp_m - pp_c);
     }
     pp_m = pp_c;
   }
@@ -500,7 +501,7 @@ static const int BX = 32, BY = 8;
 // which: 0 = u, 1 = v, 2 = p'
 static int launch_assemble(cfd_ctx* c, int which, CavParams& P, int eq) {
   const int nlines = P.ib - P.ia + 1;
-  if (nlines <= 0) {   // a slab that owns none of this equation's lines still publishes a zero residual
+  if (nlines <= 0 || P.jhi < P.jlo) {   // a slab that owns none of this equation's cells still publishes a zero residual
     CFD_CUDA(cudaMemsetAsync(c->res_dev + eq, 0, sizeof(double), c->stream));
     return CFD_OK;
   }
@@ -510,7 +511,8 @@ static int launch_assemble(cfd_ctx* c, int which, CavParams& P, int eq) {
     const char* e = getenv("CFD_B200_ASM_TMA");
     use_tma = e ? atoi(e) : 1;
   }
-  if (fast && use_tma && c->L.T >= 128 && c->L.T + 64 <= 768) {   // TMA-staged persistent kernels (long lines)
+  const bool jslab = c->cfg.halo_s > 0 || c->cfg.halo_n > 0;
+  if (fast && use_tma && !jslab && c->L.T >= 128 && c->L.T + 64 <= 768) {   // TMA-staged persistent kernels (long lines)
     P.partial = c->partial + (size_t)eq * c->max_partials;
     const int nb = cfd_launch_assemble_tma(c, which, P);
     if (nb < 0) return nb;
@@ -552,10 +554,10 @@ int cfd_launch_assemble_u(cfd_ctx* c) {
   fill_common(c, P);
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   owned_range(c, 3, NI - 1, &P.ia, &P.ib);
-  P.jlo = 1;
-  P.jhi = c->L.nj - 2;
+  const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
+  cfd_local_j_range(c, 1, NJ - 2, &P.jlo, &P.jhi);
   P.urf = c->cfg.urf[CFD_EQ_U];
-  P.stale_area = c->geom_host[CFD_G_SNS][c->L.nj - 2];   // sns(njm1)
+  P.stale_area = c->cfg.sns_njm1 != 0.0 ? c->cfg.sns_njm1 : c->geom_host[CFD_G_SNS][c->L.nj - 2];   // sns(njm1)
   P.dout = c->field[CFD_DU];
   return launch_assemble(c, 0, P, CFD_EQ_U);
 }
@@ -565,8 +567,8 @@ int cfd_launch_assemble_v(cfd_ctx* c) {
   fill_common(c, P);
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   owned_range(c, 2, NI - 1, &P.ia, &P.ib);
-  P.jlo = 2;
-  P.jhi = c->L.nj - 2;
+  const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
+  cfd_local_j_range(c, 2, NJ - 2, &P.jlo, &P.jhi);
   P.urf = c->cfg.urf[CFD_EQ_V];
   if (c->cfg.sew_nim1 != 0.0) {
     P.stale_area = c->cfg.sew_nim1;
@@ -582,8 +584,8 @@ int cfd_launch_assemble_p(cfd_ctx* c) {
   fill_common(c, P);
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   owned_range(c, 2, NI - 1, &P.ia, &P.ib);
-  P.jlo = 1;
-  P.jhi = c->L.nj - 2;
+  const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
+  cfd_local_j_range(c, 1, NJ - 2, &P.jlo, &P.jhi);
   P.dout = nullptr;
   return launch_assemble(c, 2, P, CFD_EQ_P);
 }
@@ -594,8 +596,10 @@ int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev) {
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   owned_range(c, 2, NI - 1, &P.ia, &P.ib);
   if (P.ib < P.ia) return CFD_OK;
-  P.jlo = 1;
-  P.jhi = c->L.nj - 2;
+  const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
+  cfd_local_j_range(c, 1, NJ - 2, &P.jlo, &P.jhi);
+  if (P.jhi < P.jlo) return CFD_OK;
+  P.j_skip = 2 - 1 - c->cfg.joff;
   P.i_skip = 2 - 1 - c->cfg.goff;
   P.urfp = c->cfg.urf[CFD_EQ_P];
   P.pp = c->field[CFD_PP];
@@ -607,7 +611,7 @@ int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev) {
   if (ppref_dev) {
     P.ppref = ppref_dev;
   } else {
-    const int il = c->cfg.ipref - 1 - c->cfg.goff, jl = c->cfg.jpref - 1;
+    const int il = c->cfg.ipref - 1 - c->cfg.goff, jl = c->cfg.jpref - 1 - c->cfg.joff;
     if (il < 0 || il >= c->L.ni || jl < 0 || jl >= c->L.nj) {
       cfd_set_error("cfd_correct: pressure reference cell (%d,%d) is not in this context", c->cfg.ipref, c->cfg.jpref);
       return CFD_ERR_INVALID;

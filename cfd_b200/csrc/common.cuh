@@ -79,6 +79,13 @@ struct SweepParams {
   int first_colour;      // for first==1: 0 -> both neighbours zero, 1 -> neighbours are freshly written
   const double *ae, *aw, *an, *as, *ap, *su;
   double* phi;
+  // partition method across j-slabs (jslab_kernels.cu): the Dirichlet end values phi(jlo-1), phi(jhi+1) may be
+  // constants instead of the stored values, the right-hand side may be dropped (spike vectors depend on the
+  // matrix only), and the solution may go to another array than phi.
+  int basis;                 // 1: rhs = 0
+  int end_s_const, end_n_const;
+  double end_s, end_n;
+  double* out;               // solution array (same layout as phi); phi itself unless a spike vector is built
 };
 
 }  // namespace cfd
@@ -122,6 +129,9 @@ struct cfd_ctx {
   double* res_dev;                  // 8 packed residual sums
   double* seq_scratch;              // sequential-order debug sweep: forward-elimination arrays
   double* gfast[8];                 // FastGeom arrays (device)
+  double* spike_w;                   // j-slab partition method: spike vectors of the current equation (ni*LD each)
+  double* spike_z;
+  double* spike_small;               // x_s, x_n of the lines of one colour
   double* tfast[16];                 // TEACH-family reciprocal geometry (teach_fast_kernels.cu), built on first use
   bool tfast_ready;
   bool exact_assembly;              // bit-exact assembly kernels (sequential-order mode, or CFD_B200_EXACT_ASSEMBLY=1)
@@ -135,6 +145,8 @@ int cfd_launch_assemble_p(cfd_ctx* c);
 int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev);
 int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first);
 int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int first);
+int cfd_launch_spike_basis(cfd_ctx* c, int istart, int jstart);
+void cfd_local_j_range(const cfd_ctx* c, int gj_lo, int gj_hi, int* jlo, int* jhi);
 int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst, int field);
 int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor, int field);
 static inline bool cfd_is_coef_field(int f) {

@@ -75,7 +75,8 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
     const double* ae = P.ae + oc;
     const double* aw = P.aw + oc;
     const double* su = P.su + oc;
-    double* phi = P.phi + o;
+    const double* phi = P.phi + o;
+    double* xout = P.out + o;
     const double* phiE = phi + LD;
     const double* phiW = phi - LD;
 
@@ -94,12 +95,14 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
           d[k] = (P.L.nc == 6) ? __ldg(ap + cq) : 1.0;
           const double e = zeroE ? 0.0 : __ldg(phiE + q);
           const double w = zeroW ? 0.0 : __ldg(phiW + q);
-          cc[k] = fma(__ldg(ae + cq), e, fma(__ldg(aw + cq), w, __ldg(su + cq)));
+          cc[k] = P.basis ? 0.0 : fma(__ldg(ae + cq), e, fma(__ldg(aw + cq), w, __ldg(su + cq)));
         } else {
           a[k] = 0.0;
           b[k] = 0.0;
           d[k] = 1.0;
           cc[k] = (valid && j0 < P.L.nj && !(P.first)) ? __ldg(phi + q) : 0.0;
+          if (j0 == P.jlo - 1 && P.end_s_const) cc[k] = P.end_s;
+          if (j0 == P.jhi + 1 && P.end_n_const) cc[k] = P.end_n;
         }
       }
       {
@@ -185,7 +188,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
         const int j0 = j0base + k, q = k * T + t;
         if (j0 >= P.jlo && j0 <= P.jhi) {
           const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
-          phi[q] = xk;
+          xout[q] = xk;
         }
       }
     }
@@ -261,7 +264,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
   const int t = tid, lane = tid & 31;
   const int j0base = t * M;
   const unsigned T8 = (unsigned)T * 8u, stage_bytes = (unsigned)SW * 8u, ring32 = smem_u32(ring) + (unsigned)t * 8u;
-  const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.L.nj - 1, M, T);
+  const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.jhi + 1, M, T);
   unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
   double bS = 0.0, bN = 0.0;   // Dirichlet end values phi(i, jstart-1), phi(i, nj) of the current line
   if (!P.first && (int)blockIdx.x < P.nlines) {
@@ -269,16 +272,20 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     bS = __ldg(ph + q_s);
     bN = __ldg(ph + q_n);
   }
+  if (P.end_s_const) bS = P.end_s;
+  if (P.end_n_const) bN = P.end_n;
   for (int line = blockIdx.x; line < P.nlines; line += gridDim.x) {
     const long long i0 = P.i_first + (long long)line * P.i_step;
-    double* phi = P.phi + i0 * LD;
+    double* phi = P.out + i0 * LD;
     // end values of the NEXT line, fetched a whole line ahead
     double bS_next = 0.0, bN_next = 0.0;
     if (!P.first && line + (int)gridDim.x < P.nlines) {
-      const double* ph = phi + (long long)gridDim.x * P.i_step * LD;
+      const double* ph = P.phi + (i0 + (long long)gridDim.x * P.i_step) * LD;
       bS_next = __ldg(ph + q_s);
       bN_next = __ldg(ph + q_n);
     }
+    if (P.end_s_const) bS_next = P.end_s;
+    if (P.end_n_const) bN_next = P.end_n;
     double ca[M], cc[M], cf[M];
 #pragma unroll
     for (int k = 0; k < M; ++k) {
@@ -299,11 +306,12 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
       __syncwarp();
       if (lane == 0) mbar_arrive(empty0 + 8 * s);
       const int j0 = j0base + k;
+      if (P.basis) c = 0.0;
       if (!(j0 >= P.jlo && j0 <= P.jhi)) {
         a = 0.0;
         b = 0.0;
         d = 1.0;
-        c = (j0 == P.jlo - 1) ? bS : ((j0 == P.L.nj - 1) ? bN : 0.0);
+        c = (j0 == P.jlo - 1) ? bS : ((j0 == P.jhi + 1) ? bN : 0.0);
       }
       if (k == 0) {
         const double inv = rcp(d);
@@ -496,8 +504,21 @@ static int launch_rb_m(cfd_ctx* c, const SweepParams& P, int nblocks, dim3 block
 
 using namespace cfd;
 
+// Local 0-based node range of the GLOBAL 0-based range [gj_lo, gj_hi], clamped to the rows this context owns.
+void cfd_local_j_range(const cfd_ctx* c, int gj_lo, int gj_hi, int* jlo, int* jhi) {
+  int a = gj_lo - c->cfg.joff, b = gj_hi - c->cfg.joff;
+  const int lo_own = c->cfg.halo_s, hi_own = c->L.nj - 1 - c->cfg.halo_n;
+  if (a < lo_own) a = lo_own;
+  if (b > hi_own) b = hi_own;
+  *jlo = a;
+  *jhi = b;
+}
+
+static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P);
+
 int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first) {
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
+  const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
   // owned lines, global 1-based [glo, ghi], restricted to istart..NI-1
   int glo = c->cfg.goff + c->cfg.halo_w + 1, ghi = c->cfg.goff + c->L.ni - c->cfg.halo_e;
   if (glo < istart) glo = istart;
@@ -510,8 +531,8 @@ int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int col
   P.i_first = g0 - 1 - c->cfg.goff;
   P.i_step = 2;
   P.nlines = (ghi - g0) / 2 + 1;
-  P.jlo = jstart - 1;
-  P.jhi = c->L.nj - 2;
+  cfd_local_j_range(c, jstart - 1, NJ - 2, &P.jlo, &P.jhi);
+  if (P.jhi < P.jlo) return CFD_OK;
   P.first = first ? 1 : 0;
   P.first_colour = colour;
   P.ae = c->field[CFD_AE];
@@ -521,6 +542,55 @@ int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int col
   P.ap = c->field[CFD_AP];
   P.su = c->field[CFD_SU];
   P.phi = phi;
+  P.out = phi;
+  // a j-slab solves its piece of every line with zero values at the cut ends (the partition method's particular
+  // solution, jslab_kernels.cu); physical ends keep the stored Dirichlet values
+  P.end_s_const = c->cfg.halo_s > 0;
+  P.end_n_const = c->cfg.halo_n > 0;
+  return launch_sweep(c, P);
+}
+
+// Spike vectors of the partition method for the current coefficients: for EVERY line i >= istart the solutions of
+// the local tridiagonal piece with zero right-hand side and end values (1,0) -> spike_w, (0,1) -> spike_z.
+int cfd_launch_spike_basis(cfd_ctx* c, int istart, int jstart) {
+  const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
+  const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
+  int glo = c->cfg.goff + c->cfg.halo_w + 1, ghi = c->cfg.goff + c->L.ni - c->cfg.halo_e;
+  if (glo < istart) glo = istart;
+  if (ghi > NI - 1) ghi = NI - 1;
+  if (glo > ghi) return CFD_OK;
+  const size_t fbytes = (size_t)c->L.ni * c->L.LD * sizeof(double);
+  if (!c->spike_w) {
+    CFD_CUDA(cudaMalloc(&c->spike_w, fbytes));
+    CFD_CUDA(cudaMalloc(&c->spike_z, fbytes));
+    CFD_CUDA(cudaMemsetAsync(c->spike_w, 0, fbytes, c->stream));
+    CFD_CUDA(cudaMemsetAsync(c->spike_z, 0, fbytes, c->stream));
+  }
+  for (int which = 0; which < 2; ++which) {
+    SweepParams P{};
+    P.L = c->L;
+    P.i_first = glo - 1 - c->cfg.goff;
+    P.i_step = 1;
+    P.nlines = ghi - glo + 1;
+    cfd_local_j_range(c, jstart - 1, NJ - 2, &P.jlo, &P.jhi);
+    if (P.jhi < P.jlo) return CFD_OK;
+    P.first = 0;
+    P.first_colour = 0;
+    P.ae = c->field[CFD_AE]; P.aw = c->field[CFD_AW]; P.an = c->field[CFD_AN]; P.as = c->field[CFD_AS];
+    P.ap = c->field[CFD_AP]; P.su = c->field[CFD_SU];
+    P.phi = c->field[CFD_PP];          // never read for values that matter (rhs dropped, both ends constant)
+    P.out = which == 0 ? c->spike_w : c->spike_z;
+    P.basis = 1;
+    P.end_s_const = P.end_n_const = 1;
+    P.end_s = which == 0 ? 1.0 : 0.0;
+    P.end_n = which == 0 ? 0.0 : 1.0;
+    int rc = launch_sweep(c, P);
+    if (rc) return rc;
+  }
+  return CFD_OK;
+}
+
+static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P) {
   const int T = c->L.T;
   static int num_sms = 0;
   if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device));

@@ -481,3 +481,270 @@ class LocalSlabHeat:
     def close(self):
         for s in self.slabs:
             s.h.close()
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Cavity family cut along j (second variant; north_star: "lines along the slab direction are solved
+# with a partitioned Thomas (Wang/SPIKE) method whose small reduced system is all-gathered").
+#
+# Every rank holds ALL lines but only rows joff+1 .. joff+nj of each, so each tridiagonal system of lisolv
+# (cavity_fvm.f90:62-80) is cut into `world` pieces.  Per colour pass of a sweep:
+#     cfd_sweep            piece solution y with zero values at the cut ends            (local, 8 doubles/cell)
+#     cfd_spike_pack       first/last y of every piece -> [nlines, 2]                   (tiny)
+#     all_gather           -> [world, nlines, 2]                                        (NCCL)
+#     cfd_spike_finish     reduced solve per line + x = y + w*x_s + z*x_n, halo rows    (local, 4 doubles/cell)
+# and once per assembly cfd_spike_basis (w, z: two matrix-only solves) + all_gather of [ni, 4].  Red/black line
+# colouring needs NO exchange here (all lines are local); halo ROWS of u, v, p move once per outer iteration,
+# of dv once before the p' assembly.
+# ----------------------------------------------------------------------------------------------------------
+JHALO_S, JHALO_N = 2, 1      # calcv reads den(i, j-2) (cavity_fvm.f90:215); everything else needs one row
+
+
+def jslab_extent(nj_global: int, world: int, rank: int):
+    """(joff, nj_local, halo_s, halo_n) of rank's local arrays: owned rows plus halo rows, clipped at the walls."""
+    lo, hi = partition(nj_global, world)[rank]
+    hs = min(JHALO_S, lo - 1) if rank > 0 else 0
+    hn = min(JHALO_N, nj_global - hi) if rank < world - 1 else 0
+    if world > 1 and hi - lo + 1 < 3:
+        raise ValueError(f"j-slab of rank {rank} owns {hi - lo + 1} rows; every slab needs at least 3")
+    return lo - 1 - hs, (hi - lo + 1) + hs + hn, hs, hn
+
+
+class JSlab:
+    """One rank's rows of the global cavity problem plus the device buffers of the partition method."""
+
+    def __init__(self, nicv, njcv, rank, world, *, reynolds=100.0, utop=1.0, rho=1000.0, iadv=3,
+                 urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3), device=-1, xlim=(0.0, 1.0), ylim=(0.0, 1.0)):
+        import torch
+        self.torch = torch
+        self.rank, self.world = rank, world
+        ni, nj_g = nicv + 2, njcv + 2
+        self.ni, self.nj_global = ni, nj_g
+        self.joff, self.nj, self.hs, self.hn = jslab_extent(nj_g, world, rank)
+        self.lo, self.hi = partition(nj_g, world)[rank]
+        self.nown = self.hi - self.lo + 1
+        g = setgrid(nicv, njcv, xlim[0], xlim[1], ylim[0], ylim[1])
+        sl = slice(self.joff, self.joff + self.nj)
+        self.ctx = CavityFVM(nicv, njcv, iadv=iadv, order="redblack", urf=urf, nswp=nswp, device=device,
+                             nj_local=self.nj, joff=self.joff, halo_s=self.hs, halo_n=self.hn,
+                             sns_njm1=float(g["sns"][nj_g - 2]))
+        self.ctx.set_geometry(x=g["x"], xu=g["xu"], sew=g["sew"], sewu=g["sewu"],
+                              y=g["y"][sl], yv=g["yv"][sl], sns=g["sns"][sl], snsv=g["snsv"][sl])
+        den = np.full((ni, self.nj), rho, order="F")
+        vis = np.asfortranarray(den * utop * (xlim[1] - xlim[0]) / reynolds)
+        u = np.zeros((ni, self.nj), order="F")
+        jl = nj_g - 1 - self.joff                                      # local index of the lid row
+        if 0 <= jl < self.nj:
+            u[1:, jl] = utop
+        self.ctx.upload("den", den)
+        self.ctx.upload("vis", vis)
+        self.ctx.upload("u", u)
+        self.nswp = nswp
+        self.ipref, self.jpref = self.ctx.ipref, self.ctx.jpref
+        self.owner_of_pref = self.lo <= self.jpref <= self.hi
+        self.ppref = torch.zeros(1, dtype=torch.float64, device="cuda")
+        self.res = device_tensor(self.ctx.residual_device_ptr(), (8,))
+        f64 = dict(dtype=torch.float64, device="cuda")
+        self.wz_local = torch.zeros((ni, 4), **f64)
+        self.wz_all = torch.zeros((world, ni, 4), **f64)
+        self._y = {}
+        self.row_send = {k: torch.zeros((2, ni), **f64) for k in ("s", "n")}     # to the south / north neighbour
+        self.row_recv = {k: torch.zeros((2, ni), **f64) for k in ("s", "n")}
+        self._pp_lines = None
+
+    def y_buffers(self, nl):
+        if nl not in self._y:
+            t = self.torch
+            self._y[nl] = (t.zeros((nl, 2), dtype=t.float64, device="cuda"),
+                           t.zeros((self.world, nl, 2), dtype=t.float64, device="cuda"))
+        return self._y[nl]
+
+    def ppref_element(self):
+        if self._pp_lines is None:
+            base, stride, n = self.ctx.device_view("pp")
+            self._pp_lines = device_tensor(base, (n, stride))
+        L = self.ctx.layout
+        j0 = self.jpref - 1 - self.joff
+        q = (j0 % L["M"]) * L["T"] + j0 // L["M"]
+        return self._pp_lines[self.ipref - 1, q:q + 1]
+
+    def owned(self, a):
+        return a[:, self.hs:self.hs + self.nown]
+
+
+def _nlines(ni, istart, colour):
+    return len(range(istart + colour, ni, 2))          # global lines istart..ni-1 with (i-istart)%2 == colour
+
+
+class _JSlabEngine:
+    """Stage sequence of one outer iteration over a list of slabs (one per process under torch.distributed, all of
+    them in one process for single-GPU tests); `gather` and `rows` do the two kinds of communication."""
+
+    def _equation(self, name, istart, jstart, nsw, first):
+        slabs = self.slabs
+        for s in slabs:
+            s.ctx.spike_basis(istart, jstart)
+            s.ctx.spike_pack(istart, jstart, name, 0, 1, s.wz_local.data_ptr())
+        self.gather([(s.wz_local, s.wz_all) for s in slabs])
+        for k in range(nsw):
+            for colour in (0, 1):
+                nl = _nlines(slabs[0].ni, istart, colour)
+                if nl == 0:
+                    continue
+                for s in slabs:
+                    yl, _ = s.y_buffers(nl)
+                    s.ctx.sweep(istart, jstart, name, colour, first=(first and k == 0))
+                    s.ctx.spike_pack(istart, jstart, name, colour, 0, yl.data_ptr())
+                self.gather([s.y_buffers(nl) for s in slabs])
+                for s in slabs:
+                    _, ya = s.y_buffers(nl)
+                    s.ctx.spike_finish(istart, jstart, name, colour, s.wz_all.data_ptr(), ya.data_ptr(), s.rank, s.world)
+
+    def _iterate_once(self):
+        slabs = self.slabs
+        nswp = slabs[0].nswp
+        self.rows((("u", 1, 1), ("v", 1, 1), ("p", 1, 0)))
+        for s in slabs:
+            s.ctx.assemble_u()
+        self._equation("u", 3, 2, nswp[0], False)
+        for s in slabs:
+            s.ctx.assemble_v()
+        self._equation("v", 2, 3, nswp[1], False)
+        self.rows((("dv", 0, 1),))
+        for s in slabs:
+            s.ctx.assemble_p()
+        self._equation("pp", 2, 2, nswp[2], True)
+        self.bcast_ppref()
+        for s in slabs:
+            s.ctx.correct(s.ppref.data_ptr())
+
+
+class LocalJSlabCavity(_JSlabEngine):
+    """All j-slabs in one process on one GPU (tests): copies instead of messages."""
+
+    def __init__(self, nicv, njcv, world, **kw):
+        self.world = world
+        self.slabs = [JSlab(nicv, njcv, r, world, **kw) for r in range(world)]
+
+    def gather(self, pairs):
+        for _, dst in pairs:
+            for r, (src, _) in enumerate(pairs):
+                dst[r].copy_(src)
+
+    def rows(self, spec):
+        for name, ns, nn in spec:
+            for r in range(self.world - 1):
+                a, b = self.slabs[r], self.slabs[r + 1]          # a is south of b
+                n_s = min(ns, b.hs)                               # b's south halo <- a's last owned rows
+                if n_s:
+                    buf = b.row_recv["s"][:n_s]
+                    a.ctx.rows_pack(name, a.hs + a.nown - n_s + 1, n_s, buf.data_ptr())
+                    b.ctx.rows_unpack(name, b.hs - n_s + 1, n_s, buf.data_ptr())
+                n_n = min(nn, a.hn)                               # a's north halo <- b's first owned rows
+                if n_n:
+                    buf = a.row_recv["n"][:n_n]
+                    b.ctx.rows_pack(name, b.hs + 1, n_n, buf.data_ptr())
+                    a.ctx.rows_unpack(name, a.hs + a.nown + 1, n_n, buf.data_ptr())
+
+    def bcast_ppref(self):
+        owner = [s for s in self.slabs if s.owner_of_pref][0]
+        for s in self.slabs:
+            s.ppref.copy_(owner.ppref_element())
+
+    def iterate(self, n=1):
+        import torch
+        for _ in range(n):
+            self._iterate_once()
+        torch.cuda.synchronize()
+        res = sum(s.res.clone() for s in self.slabs)
+        return tuple(res.cpu().tolist())[:3]
+
+    def gather_field(self, name):
+        return np.asfortranarray(np.concatenate([s.owned(s.ctx.download(name)) for s in self.slabs], axis=1))
+
+    def close(self):
+        for s in self.slabs:
+            s.ctx.close()
+
+
+class JSlabCavity(_JSlabEngine):
+    """SPMD driver: one JSlab per process over torch.distributed (NCCL all_gather + send/recv of halo rows)."""
+
+    def __init__(self, nicv, njcv, *, reynolds=1000.0, stream=None, **kw):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.comm = TorchDistComm()
+        self.rank, self.world = self.comm.rank, self.comm.world
+        self.slab = JSlab(nicv, njcv, self.rank, self.world, reynolds=reynolds, device=torch.cuda.current_device(), **kw)
+        self.slabs = [self.slab]
+        self.ctx = self.slab.ctx
+        if stream is not None:
+            self.ctx.set_stream(stream.cuda_stream)
+        self.pref_owner = [r for r, (lo, hi) in enumerate(partition(njcv + 2, self.world)) if lo <= self.slab.jpref <= hi][0]
+
+    def gather(self, pairs):
+        for src, dst in pairs:
+            self.dist.all_gather_into_tensor(dst, src)
+
+    def rows(self, spec):
+        s, ops, todo = self.slab, [], []
+        for k, (name, ns, nn) in enumerate(spec):
+            if s.rank > 0:                                        # south neighbour: my first owned rows go to its north halo
+                if nn:
+                    buf = self._rowbuf("ss", k)[:1]
+                    s.ctx.rows_pack(name, s.hs + 1, 1, buf.data_ptr())
+                    ops.append(("send", buf, s.rank - 1))
+                n_s = min(ns, s.hs)
+                if n_s:
+                    buf = self._rowbuf("rs", k)[:n_s]
+                    ops.append(("recv", buf, s.rank - 1))
+                    todo.append((name, s.hs - n_s + 1, n_s, buf))
+            if s.rank < s.world - 1:                              # north neighbour
+                if ns:
+                    n_s = min(ns, JHALO_S)
+                    buf = self._rowbuf("sn", k)[:n_s]
+                    s.ctx.rows_pack(name, s.hs + s.nown - n_s + 1, n_s, buf.data_ptr())
+                    ops.append(("send", buf, s.rank + 1))
+                n_n = min(nn, s.hn)
+                if n_n:
+                    buf = self._rowbuf("rn", k)[:n_n]
+                    ops.append(("recv", buf, s.rank + 1))
+                    todo.append((name, s.hs + s.nown + 1, n_n, buf))
+        self.comm.exchange(ops)
+        for name, j1, n, buf in todo:
+            s.ctx.rows_unpack(name, j1, n, buf.data_ptr())
+
+    def _rowbuf(self, kind, k):
+        key = (kind, k)
+        if not hasattr(self, "_rb"):
+            self._rb = {}
+        if key not in self._rb:
+            t = self.torch
+            self._rb[key] = t.zeros((2, self.slab.ni), dtype=t.float64, device="cuda")
+        return self._rb[key]
+
+    def bcast_ppref(self):
+        s = self.slab
+        if s.owner_of_pref:
+            s.ppref.copy_(s.ppref_element())
+        self.comm.broadcast(s.ppref, self.pref_owner)
+
+    def iterate_async(self, n=1):
+        for _ in range(n):
+            self._iterate_once()
+
+    def residuals(self):
+        r = self.slab.res.clone()
+        self.comm.allreduce_sum(r)
+        return tuple(r.cpu().tolist())
+
+    def iterate(self, n=1):
+        self.iterate_async(n)
+        return self.residuals()[:3]
+
+    def gather_field(self, name):
+        a = np.ascontiguousarray(self.slab.owned(self.ctx.download(name)))
+        out = [None] * self.world if self.rank == 0 else None
+        self.dist.gather_object(a, out, dst=0)
+        return np.asfortranarray(np.concatenate(out, axis=1)) if self.rank == 0 else None

@@ -98,6 +98,13 @@ typedef struct cfd_config {
      (:16,:67), laminar viscosity viscos (:126), inlet mass flow flowin (:197-203), great (:15) */
   int indcos, istep, jstep;
   double viscos, flowin, great;
+  /* j-slab description (cavity family, red/black order): the S-N lines themselves are cut, each context holds rows
+     joff+1 .. joff+nj of every line and solves them with the partition method (cfd_spike_*, below) */
+  int joff;                /* global j of local row 1, minus 1 */
+  int nj_global;           /* 0 = nj */
+  int halo_s, halo_n;      /* halo rows at the south / north end of the local arrays (0 at a physical wall) */
+  double sns_njm1;         /* sns(njm1) of the GLOBAL grid for the stale-scalar quirk of calcu (cavity_fvm.f90:186);
+                              0 = read it from the local geometry */
 } cfd_config;
 
 /* Device-side form of the `user` module hook gamsor() (cylin_cond.f90:149-169; the buoyancy program's own
@@ -181,6 +188,28 @@ int cfd_assemble_t(cfd_ctx* ctx);                       /* buoyancy_cav.f90:371-
    first != 0 treats phi as zero where the reference has just executed pp(:,:)=0 (cavity_fvm.f90:342) */
 int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first);
 int cfd_correct(cfd_ctx* ctx, const double* ppref_device); /* cavity_fvm.f90:346-354; NULL = pp(ipref,jpref) */
+
+/* ---- j-slabs: lisolv's tridiagonal systems (cavity_fvm.f90:62-80) cut across contexts ----------------------
+   Partition (Wang / SPIKE) method.  With x_s, x_n the still unknown values just outside a context's piece of a
+   line, the piece's solution is  x = y + w*x_s + z*x_n :  y solves the piece with zero end values (that is what
+   cfd_sweep does in a j-slab context), w and z are the spike vectors of the matrix alone.  The first and last
+   unknown of every piece give a small reduced system per line; its six coefficients per piece are all-gathered
+   (by the caller: torch.distributed / NCCL), every context solves the reduced systems redundantly and finishes
+   its own pieces.  All buffers are DEVICE pointers; all calls are asynchronous on the context's stream.
+     cfd_spike_basis    w, z of every line for the coefficients now in the context (once per assembly)
+     cfd_spike_pack     which = 1: (w_first, w_last, z_first, z_last) of all ni local lines -> buf[ni][4]
+                        which = 0: (y_first, y_last) of the lines of `colour` in `field`    -> buf[nlines][2]
+     cfd_spike_finish   reduced solve + x = y + w*x_s + z*x_n on the lines of `colour`; also stores x_s, x_n in the
+                        halo rows, so the field's halos are current afterwards.  wz_all = [world][ni][4],
+                        y_all = [world][nlines][2] as gathered in rank order (rank = position along j).
+     cfd_rows_pack / cfd_rows_unpack   rows j_first .. j_first+nrows-1 (1-based local) of `field` <-> buf[nrows][ni]
+                        (a halo row is strided in the line layout) */
+int cfd_spike_basis(cfd_ctx* ctx, int istart, int jstart);
+int cfd_spike_pack(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int which, double* buf);
+int cfd_spike_finish(cfd_ctx* ctx, int istart, int jstart, int field, int colour, const double* wz_all,
+                     const double* y_all, int rank, int world);
+int cfd_rows_pack(cfd_ctx* ctx, int field, int j_first, int nrows, double* buf);
+int cfd_rows_unpack(cfd_ctx* ctx, int field, int j_first, int nrows, const double* buf);
 /* finish the deterministic residual reduction and copy res[0..7] to the host (synchronises) */
 int cfd_residuals(cfd_ctx* ctx, double res[8]);
 /* device address of the 8 packed residual sums (for an NCCL all-reduce) */

@@ -47,6 +47,26 @@ def test_teach_local_slabs_match_single_context(cfd, world, shape):
     g.close()
 
 
+@pytest.mark.parametrize("world,shape", [(2, (30, 34)), (3, (40, 66)), (4, (64, 130)), (8, (34, 96))])
+def test_local_jslabs_partitioned_thomas(cfd, world, shape):
+    """Lines cut ACROSS contexts (j-slabs): piece solves + spike vectors + reduced system reproduce the single
+    context's line solves up to rounding (the partition method reorders the elimination)."""
+    from cfd_b200.dist import LocalJSlabCavity
+    g = cfd.CavityFVM(*shape, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    s = LocalJSlabCavity(*shape, world, reynolds=100.0)
+    for _ in range(4):
+        r1 = g.iterate(3)
+        r2 = s.iterate(3)
+        for a, b in zip(r1, r2):
+            assert abs(a - b) <= 1e-9 * abs(a), (r1, r2)
+    for name in ("u", "v", "p", "pp"):
+        a, b = s.gather_field(name), g.download(name)
+        assert np.abs(a - b).max() <= 1e-10 * max(1.0, np.abs(b).max()), (name, np.abs(a - b).max())
+    s.close()
+    g.close()
+
+
 def _nccl_worker(rank, world, port, shape, q):
     import torch
     import torch.distributed as dist
