@@ -178,9 +178,14 @@ def run_ours(args):
         cells_total = NICV * NJCV
         par = "single GPU"
     else:
-        from cfd_b200.dist import SlabCavity
-        solver = SlabCavity(NICV * world, NJCV, reynolds=REYNOLDS, stream=stream)
-        if os.environ.get("CFD_B200_GRAPH", "0") != "0":     # off by default: no gain measured, and teardown is slow
+        from cfd_b200.dist import JSlabCavity, SlabCavity
+        if args.slabs == "j":
+            solver = JSlabCavity(NICV, NJCV * world, reynolds=REYNOLDS, stream=stream)
+        else:
+            solver = SlabCavity(NICV * world, NJCV, reynolds=REYNOLDS, stream=stream)
+        if args.slabs == "j":
+            graphed = False
+        elif os.environ.get("CFD_B200_GRAPH", "0") != "0":     # off by default: no gain measured, and teardown is slow
             with torch.cuda.stream(stream):
                 graphed = solver.enable_graph(stream)
         else:
@@ -191,6 +196,9 @@ def run_ours(args):
         cells_total = NICV * world * NJCV
         par = (f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals, "
                + ("one CUDA graph per outer iteration" if graphed else "eager launches"))
+        if args.slabs == "j":
+            par = (f"j-slabs x{world}: lines cut across GPUs, partitioned Thomas (piece solves + spike vectors, "
+                   "all-gathered reduced system per line), halo rows once per iteration, all-reduced residuals")
 
     def barrier():
         torch.cuda.synchronize()
@@ -228,7 +236,8 @@ def run_ours(args):
            "iters_per_s": K / (ms * 1e-3),
            "config": {"workload": f"lid-driven cavity FVM SIMPLE Re=1000, {NICV}x{NJCV} CV per GPU, hybrid scheme, "
                                   "urf .5/.5/.8, nswp 3/3/3, red/black line TDMA (BASELINE.json configs[2])",
-                      "global_grid": f"{NICV * world}x{NJCV}", "parallelism": par,
+                      "global_grid": (f"{NICV}x{NJCV * world}" if (world > 1 and args.slabs == "j") else f"{NICV * world}x{NJCV}"),
+                      "parallelism": par,
                       "l2": "inputs larger than L2 (1.9 GB of live fields per GPU vs 126 MB L2); no explicit flush",
                       "line_layout": ctx0.layout},
            "residuals_last": list(res[:3]), "gpu_launches": int(launches)}
@@ -493,6 +502,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step"])
+    ap.add_argument("--slabs", default="i", choices=["i", "j"], help="N>1 cavity: cut along i (whole lines per GPU) or j")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()

@@ -235,7 +235,50 @@ def iteration_stages(nswp):
     return st
 
 
-class SlabCavity:
+class _E2EMixin:
+    def e2e(self, steps):
+        """bench.py's end-to-end leg: per step upload u,v,p slabs from pinned host memory, one outer
+        iteration, download u,v,p and the residuals; max over ranks of the wall time."""
+        import time
+        torch = self.torch
+        ni, nj = self.slab.ni, self.slab.nj
+        host = {n: torch.empty((nj, ni), dtype=torch.float64, pin_memory=True) for n in ("u", "v", "p")}
+        for n in host:
+            self.ctx.download_ptr(n, host[n].data_ptr(), ni)
+        fb = ni * nj * 8
+        cells = self._global_cells()
+
+        def leg(full_download):
+            t0 = 0.0
+            for it in range(steps + 1):
+                if it == 1:
+                    torch.cuda.synchronize()
+                    self.dist.barrier()
+                    t0 = time.perf_counter()
+                for n in host:
+                    self.ctx.upload_ptr(n, host[n].data_ptr(), ni)
+                self.iterate(1)                               # all-reduced residuals come back to the host
+                if full_download:
+                    for n in host:
+                        self.ctx.download_ptr(n, host[n].data_ptr(), ni)
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+            self.dist.all_reduce(dt, op=self.dist.ReduceOp.MAX)
+            return float(dt.item())
+
+        dt, dt_full = leg(False), leg(True)
+        return {"value": cells * steps / dt / 1e9, "unit": "GLUPS", "h2d_bytes_per_step": 3 * fb * self.world,
+                "d2h_bytes_per_step": 64 * self.world, "steps": steps, "ms_per_step": dt / steps * 1e3,
+                "what": "per step and rank: cfd_upload(u,v,p slab) from pinned host arrays, one slab-decomposed outer "
+                        "iteration with halo exchange, all-reduced residuals to the host",
+                "roundtrip": {"value": cells * steps / dt_full / 1e9, "unit": "GLUPS",
+                              "h2d_bytes_per_step": 3 * fb * self.world,
+                              "d2h_bytes_per_step": (3 * fb + 64) * self.world, "ms_per_step": dt_full / steps * 1e3,
+                              "what": "same, plus cfd_download(u,v,p slab) of the whole fields every step"}}
+
+
+
+class SlabCavity(_E2EMixin):
     """SPMD driver: one Slab per process over torch.distributed (bench.py, torchrun)."""
 
     def __init__(self, nicv, njcv, *, reynolds=1000.0, stream=None, slab_cls=None, **kw):
@@ -256,6 +299,9 @@ class SlabCavity:
         s = self.slab
         self.comm.exchange(halo_ops(s.lines("den"), s.rank, s.world, s.hw, s.he, s.nown, HALO_W, HALO_E))
         self.comm.exchange(halo_ops(s.lines("vis"), s.rank, s.world, s.hw, s.he, s.nown, 1, 1))
+
+    def _global_cells(self):
+        return (self.slab.ni_global - 2) * (self.slab.nj - 2)
 
     def enable_graph(self, stream):
         """Capture one outer iteration (kernels + NCCL halo exchanges) into a CUDA graph and replay it from then
@@ -316,47 +362,6 @@ class SlabCavity:
         out = [None] * self.world if self.rank == 0 else None
         self.dist.gather_object(a, out, dst=0)
         return np.asfortranarray(np.concatenate(out, axis=0)) if self.rank == 0 else None
-
-    def e2e(self, steps):
-        """bench.py's end-to-end leg: per step upload u,v,p slabs from pinned host memory, one outer
-        iteration, download u,v,p and the residuals; max over ranks of the wall time."""
-        import time
-        torch = self.torch
-        ni, nj = self.slab.ni, self.slab.nj
-        host = {n: torch.empty((nj, ni), dtype=torch.float64, pin_memory=True) for n in ("u", "v", "p")}
-        for n in host:
-            self.ctx.download_ptr(n, host[n].data_ptr(), ni)
-        fb = ni * nj * 8
-        cells = (self.slab.ni_global - 2) * (nj - 2)
-
-        def leg(full_download):
-            t0 = 0.0
-            for it in range(steps + 1):
-                if it == 1:
-                    torch.cuda.synchronize()
-                    self.dist.barrier()
-                    t0 = time.perf_counter()
-                for n in host:
-                    self.ctx.upload_ptr(n, host[n].data_ptr(), ni)
-                self.iterate(1)                               # all-reduced residuals come back to the host
-                if full_download:
-                    for n in host:
-                        self.ctx.download_ptr(n, host[n].data_ptr(), ni)
-            torch.cuda.synchronize()
-            dt = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
-            self.dist.all_reduce(dt, op=self.dist.ReduceOp.MAX)
-            return float(dt.item())
-
-        dt, dt_full = leg(False), leg(True)
-        return {"value": cells * steps / dt / 1e9, "unit": "GLUPS", "h2d_bytes_per_step": 3 * fb * self.world,
-                "d2h_bytes_per_step": 64 * self.world, "steps": steps, "ms_per_step": dt / steps * 1e3,
-                "what": "per step and rank: cfd_upload(u,v,p slab) from pinned host arrays, one slab-decomposed outer "
-                        "iteration with halo exchange, all-reduced residuals to the host",
-                "roundtrip": {"value": cells * steps / dt_full / 1e9, "unit": "GLUPS",
-                              "h2d_bytes_per_step": 3 * fb * self.world,
-                              "d2h_bytes_per_step": (3 * fb + 64) * self.world, "ms_per_step": dt_full / steps * 1e3,
-                              "what": "same, plus cfd_download(u,v,p slab) of the whole fields every step"}}
-
 
 class LocalSlabCavity:
     """All slabs in one process on one GPU (tests): same stages, LocalComm copies instead of messages."""
@@ -667,7 +672,7 @@ class LocalJSlabCavity(_JSlabEngine):
             s.ctx.close()
 
 
-class JSlabCavity(_JSlabEngine):
+class JSlabCavity(_JSlabEngine, _E2EMixin):
     """SPMD driver: one JSlab per process over torch.distributed (NCCL all_gather + send/recv of halo rows)."""
 
     def __init__(self, nicv, njcv, *, reynolds=1000.0, stream=None, **kw):
@@ -723,6 +728,9 @@ class JSlabCavity(_JSlabEngine):
             t = self.torch
             self._rb[key] = t.zeros((2, self.slab.ni), dtype=t.float64, device="cuda")
         return self._rb[key]
+
+    def _global_cells(self):
+        return (self.slab.ni - 2) * (self.slab.nj_global - 2)
 
     def bcast_ppref(self):
         s = self.slab
