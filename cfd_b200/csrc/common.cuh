@@ -157,5 +157,6 @@ int cfd_launch_assemble_fast(cfd_ctx* c, int which, cfd::CavParams& P, dim3 grid
 int cfd_update_fast_geometry(cfd_ctx* c);
 int cfd_launch_assemble_tma(cfd_ctx* c, int which, cfd::CavParams& P);
 int cfd_launch_general_assemble(cfd_ctx* c, int which);
+int cfd_launch_general_assemble_fast(cfd_ctx* c, int which, double* partial);
 int cfd_launch_teach_assemble(cfd_ctx* c, int which);
 int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double* partial, const double* uinc);

@@ -475,6 +475,11 @@ int cfd_launch_general_assemble(cfd_ctx* c, int which) {
     return CFD_ERR_INVALID;
   }
   P.partial = c->partial + (size_t)eq * c->max_partials;
+  if (!c->exact_assembly) {   // production (red/black) contexts: general_fast_kernels.cu, equations stored divided by ap
+    const int nb = cfd_launch_general_assemble_fast(c, which, P.partial);
+    if (nb < 0) return nb;
+    return cfd_launch_reduce_partials(c, eq, nb);
+  }
   switch (which) {
     case 0: k_gen_assemble_u<<<grid, block, 0, c->stream>>>(P); break;
     case 1: k_gen_assemble_v<<<grid, block, 0, c->stream>>>(P); break;

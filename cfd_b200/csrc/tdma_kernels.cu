@@ -197,6 +197,10 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_rb(const SweepParams P) {
 }
 
 // ---------------------------------------------------------------------------------------------------
+__host__ __device__ constexpr bool tdma_cf_in_smem(int M, int BMAX) {
+  return (BMAX == 672 && M > 8) || (BMAX == 1024 && M > 5);
+}
+
 // TMA-staged line solver (production path for long lines).
 //
 // Same algorithm as k_tdma_rb, but the operands never pass through load registers: an extra producer warp
@@ -215,10 +219,14 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
   // carve shared memory: [ring S*(nc+2)*T doubles][pcr 6*T doubles][full S][empty S]
   constexpr int nc = NC;                      // coefficient arrays per node (5 normalised / 6 raw)
   const int SW = (nc + 2) * T;                // doubles per ring stage
+  // Long lines leave too few registers per thread for the three per-node arrays (ca, cc, cf): the spike array
+  // cf then lives in shared memory (conflict-free: node k of thread t at k*T + t) instead of spilling to local.
+  constexpr bool CFS = tdma_cf_in_smem(M, BMAX);
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* bufA = ring + (size_t)S * SW;
   double* bufB = bufA + 3 * T;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(bufB + 3 * T);
+  double* cfs = reinterpret_cast<double*>(bars + 2 * S);
   const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S);
   const int ncw = T / 32;   // consumer warps
   const bool zeroE = P.first && (P.first_colour == 0 || P.i_step == 1);
@@ -286,7 +294,17 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     }
     if (P.end_s_const) bS_next = P.end_s;
     if (P.end_n_const) bN_next = P.end_n;
-    double ca[M], cc[M], cf[M];
+    double ca[M], cc[M], cf[CFS ? 1 : M];
+    double* cft = cfs + t;
+#define CF_GET(k) (CFS ? cft[(k) * T] : cf[CFS ? 0 : (k)])
+#define CF_SET(k, v)            \
+  {                             \
+    if (CFS) {                  \
+      cft[(k) * T] = (v);       \
+    } else {                    \
+      cf[CFS ? 0 : (k)] = (v);  \
+    }                           \
+  }
 #pragma unroll
     for (int k = 0; k < M; ++k) {
       const unsigned s = rs, ph = rph;
@@ -317,28 +335,28 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
         const double inv = rcp(d);
         ca[0] = a * inv;
         cc[0] = c * inv;
-        cf[0] = b * inv;
+        CF_SET(0, b * inv)
       } else {
         const double inv = rcp(fma(-b, ca[k > 0 ? k - 1 : 0], d));
         ca[k] = a * inv;
         cc[k] = fma(b, cc[k > 0 ? k - 1 : 0], c) * inv;
-        cf[k] = b * cf[k > 0 ? k - 1 : 0] * inv;
+        CF_SET(k, b * CF_GET(k > 0 ? k - 1 : 0) * inv)
       }
     }
 #pragma unroll
     for (int k = M - 3; k >= 0; --k) {
       cc[k] = fma(ca[k], cc[k + 1], cc[k]);
-      cf[k] = fma(ca[k], cf[k + 1], cf[k]);
+      CF_SET(k, fma(ca[k], CF_GET(k + 1), CF_GET(k)))
       ca[k] = ca[k] * ca[k + 1];
     }
     double l, u, r;
     if (M == 1) {
-      l = cf[0];
+      l = CF_GET(0);
       u = ca[0];
       r = cc[0];
     } else {
       bufB[t] = cc[0];
-      bufB[T + t] = cf[0];
+      bufB[T + t] = CF_GET(0);
       bufB[2 * T + t] = ca[0];
       consumer_sync(T);
       double ncc = 0.0, ncf = 0.0, ng = 0.0;
@@ -348,7 +366,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
         ng = bufB[2 * T + t + 1];
       }
       const double inv = rcp(fma(-ca[M - 1], ncf, 1.0));
-      l = cf[M - 1] * inv;
+      l = CF_GET(M - 1) * inv;
       u = ca[M - 1] * ng * inv;
       r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
     }
@@ -388,7 +406,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     for (int k = 0; k < M; ++k) {
       const int j0 = j0base + k;
       if (j0 >= P.jlo && j0 <= P.jhi) {
-        const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
+        const double xk = (k == M - 1) ? xe : fma(CF_GET(k), xp, fma(ca[k], xe, cc[k]));
         phi[k * T + t] = xk;
       }
     }
@@ -396,6 +414,8 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     bN = bN_next;
     consumer_sync(T);   // PCR buffers are reused by the next line
   }
+#undef CF_GET
+#undef CF_SET
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -602,11 +622,13 @@ static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P) {
   if (use_tma && T >= 128 && T + 32 <= 1024) {
     // TMA-staged persistent kernel: ring of S slices (8*T doubles each), S a power of two
     const size_t stage = (size_t)(c->L.nc + 2) * T * sizeof(double), pcr = (size_t)6 * T * sizeof(double);
+    const int bmax = (T + 32 <= 352) ? 352 : (T + 32 <= 672 ? 672 : 1024);
+    const size_t cfs = tdma_cf_in_smem(c->L.M, bmax) ? (size_t)c->L.M * T * sizeof(double) : 0;
     int S = 16;
     const char* es = getenv("CFD_B200_TDMA_STAGES");
     if (es && atoi(es) > 0) S = atoi(es);
-    while (S > 1 && S * stage + pcr + 2 * S * 8 > 200 * 1024) S >>= 1;
-    const size_t smem = S * stage + pcr + 2 * (size_t)S * 8;
+    while (S > 1 && S * stage + pcr + cfs + 2 * S * 8 > 220 * 1024) --S;
+    const size_t smem = S * stage + pcr + cfs + 2 * (size_t)S * 8;
     const int nblocks = P.nlines < num_sms ? P.nlines : num_sms;
     int rc = CFD_OK;
     switch (c->L.M) {

@@ -94,6 +94,36 @@ def test_buoyancy_trajectory_sequential_bitwise(cfd, oracle, n):
     g.close()
 
 
+@pytest.mark.parametrize("n", [12, 34, 67])
+@pytest.mark.parametrize("iadv", [1, 2, 3, 4])
+def test_buoyancy_production_assembly_vs_oracle(cfd, oracle, n, iadv):
+    """Red/black contexts use general_fast_kernels.cu and store the equations divided by ap: every coefficient must
+    equal the oracle's coefficient / ap to rounding (same randomised fields as the bitwise test)."""
+    o = oracle.General("buoyancy", ni=n, nj=n, iadv=iadv)
+    g = cfd.BuoyantCavity(n, n, iadv=iadv, order="redblack")
+    randomise_buoyancy(o, g, 3 + iadv)
+    sl_u = (slice(2, n - 1), slice(1, n - 1))
+    sl_v = (slice(1, n - 1), slice(2, n - 1))
+    sl_p = (slice(1, n - 1), slice(1, n - 1))
+    for eq, name, sl, dname in ((0, "u", sl_u, "du"), (1, "v", sl_v, "dv"), (2, "p", sl_p, None), (3, "t", sl_p, None)):
+        o.call("assemble_" + name)
+        getattr(g, "assemble_" + name)()
+        ap = o.ap[sl]
+        for gn, on in COEF:
+            if gn == "ap":
+                continue
+            want = getattr(o, on)[sl] / ap
+            got = g.download(gn)[sl]
+            assert np.abs(got - want).max() <= 1e-11 * max(1e-300, np.abs(want).max()), (name, gn, np.abs(got - want).max())
+        if dname:
+            want = getattr(o, dname)[sl]
+            assert np.abs(g.download(dname)[sl] - want).max() <= 1e-11 * np.abs(want).max(), dname
+        assert abs(g.residuals()[eq] - o.resor[eq]) <= 1e-10 * abs(o.resor[eq]) + 1e-300
+        if name == "t":
+            o.den[:, :] = o.den / o.cp
+    g.close()
+
+
 def test_buoyancy_redblack_converged_vs_sequential_oracle(cfd, oracle):
     n = 34
     o = oracle.General("buoyancy", ni=n, nj=n)
