@@ -13,7 +13,7 @@ FAMILY_CAVITY, FAMILY_GENERAL, FAMILY_TEACH = 0, 1, 2
 ORDER_REDBLACK, ORDER_SEQUENTIAL = 0, 1
 
 FIELDS = ("u", "v", "p", "pp", "vis", "den", "t", "cp", "ae", "aw", "an", "as", "ap", "su", "sp", "du", "dv",
-          "gamt", "susrc", "spsrc")
+          "gamt", "susrc", "spsrc", "te", "ed", "gen", "gamh")
 FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
 GEOMS = ("x", "xu", "sew", "sewu", "y", "yv", "sns", "snsv",
          "xdif", "xcvi", "xcvip", "fx", "fxm",
@@ -39,7 +39,14 @@ class CfdHookDesc(C.Structure):
 
 
 HOOK_NONE, HOOK_BOUSSINESQ, HOOK_FIELD_SOURCES = 0, 1, 2
-EQ_U, EQ_V, EQ_P, EQ_T = 0, 1, 2, 3
+EQ_U, EQ_V, EQ_P, EQ_T, EQ_TE, EQ_ED = 0, 1, 2, 3, 4, 5
+WALL_ID = {"taun": 0, "tauw": 1, "yplusn": 2, "xplusw": 3}
+
+
+class CfdTurbulence(C.Structure):
+    _fields_ = ([(n, C.c_double) for n in ("cmu", "cd", "c1", "c2", "cappa", "elog", "pred", "prte", "prandl", "prandt",
+                                           "pfun", "twalln", "urfk", "urfe", "urft", "urfvis")]
+                + [(n, C.c_int) for n in ("nswpk", "nswpd", "nswpt", "incalk", "incald", "incalt", "inpro")])
 
 
 class CfdHeatConfig(C.Structure):
@@ -93,6 +100,14 @@ SYMBOLS = {
     "cfd_assemble_p": (C.c_int, [_vp]),
     "cfd_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cfd_correct": (C.c_int, [_vp, _vp]),
+    "cfd_set_turbulence": (C.c_int, [_vp, C.POINTER(CfdTurbulence)]),
+    "cfd_wall_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_wall_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_calcte": (C.c_int, [_vp, _dp]),
+    "cfd_calced": (C.c_int, [_vp, _dp]),
+    "cfd_props": (C.c_int, [_vp]),
+    "cfd_assemble_te": (C.c_int, [_vp]),
+    "cfd_assemble_ed": (C.c_int, [_vp]),
     "cfd_spike_basis": (C.c_int, [_vp, C.c_int, C.c_int]),
     "cfd_spike_pack": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
     "cfd_spike_finish": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int, C.c_int]),

@@ -188,6 +188,9 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   for (auto& g : c->gfast) g = nullptr;
   for (auto& g : c->tfast) g = nullptr;
   c->spike_w = c->spike_z = c->spike_small = nullptr;
+  c->turbulent = false;
+  for (auto& w : c->wall) w = nullptr;
+  c->tmult_n = c->tmult_w = nullptr;
   c->tfast_ready = false;
   int want_m = cfg->tdma_m;
   if (want_m == 0) {
@@ -270,6 +273,9 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   if (c->spike_w) cudaFree(c->spike_w);
   if (c->spike_z) cudaFree(c->spike_z);
   if (c->spike_small) cudaFree(c->spike_small);
+  for (auto& w : c->wall) if (w) cudaFree(w);
+  if (c->tmult_n) cudaFree(c->tmult_n);
+  if (c->tmult_w) cudaFree(c->tmult_w);
   if (c->stage) cudaFree(c->stage);
   if (c->partial) cudaFree(c->partial);
   if (c->res_dev) cudaFree(c->res_dev);
@@ -469,9 +475,17 @@ extern "C" int cfd_layout_info(cfd_ctx* c, int* m, int* t, int* ld) {
 static inline bool is_general(const cfd_ctx* c) { return c->cfg.family == CFD_FAMILY_GENERAL; }
 static inline bool is_teach(const cfd_ctx* c) { return c->cfg.family == CFD_FAMILY_TEACH; }
 static int asm_u(cfd_ctx* c) {
+  if (is_teach(c) && c->turbulent) {
+    int rc = cfd_launch_teach_wall(c, 0);
+    if (rc) return rc;
+  }
   return is_general(c) ? cfd_launch_general_assemble(c, 0) : is_teach(c) ? cfd_launch_teach_assemble(c, 0) : cfd_launch_assemble_u(c);
 }
 static int asm_v(cfd_ctx* c) {
+  if (is_teach(c) && c->turbulent) {
+    int rc = cfd_launch_teach_wall(c, 1);
+    if (rc) return rc;
+  }
   return is_general(c) ? cfd_launch_general_assemble(c, 1) : is_teach(c) ? cfd_launch_teach_assemble(c, 1) : cfd_launch_assemble_v(c);
 }
 static int asm_p(cfd_ctx* c) {
@@ -563,8 +577,17 @@ static int stage_p(cfd_ctx* c) {
   return cfd_launch_correct(c, nullptr);
 }
 
+static int stage_scalar_teach(cfd_ctx* c, int eq, int field, int nsw) {
+  int rc;
+  if ((rc = cfd_launch_teach_scalar(c, eq))) return rc;
+  for (int n = 0; n < nsw; ++n)
+    if ((rc = full_sweep(c, 2, 2, field, 0))) return rc;
+  return CFD_OK;
+}
+
 static int stage_t(cfd_ctx* c) {
   int rc;
+  if (is_teach(c)) return stage_scalar_teach(c, CFD_EQ_T, CFD_T, c->turb.nswpt);
   if ((rc = cfd_launch_general_assemble(c, 3))) return rc;
   for (int n = 0; n < c->cfg.nswp[CFD_EQ_T]; ++n)
     if ((rc = full_sweep(c, 2, 2, CFD_T, 0))) return rc;
@@ -572,10 +595,98 @@ static int stage_t(cfd_ctx* c) {
 }
 extern "C" int cfd_calct(cfd_ctx* c, double* resort) {
   CFD_REQUIRE(c, "null context");
-  CFD_REQUIRE(is_general(c), "cfd_calct needs a CFD_FAMILY_GENERAL context");
+  CFD_REQUIRE(is_general(c) || (is_teach(c) && c->turbulent),
+              "cfd_calct needs a CFD_FAMILY_GENERAL context, or a TEACH context after cfd_set_turbulence");
   CFD_CUDA(cudaSetDevice(c->device));
   int rc = stage_t(c);
   return rc ? rc : read_res(c, CFD_EQ_T, resort);
+}
+
+// ---- TEACH family: k-epsilon / energy (teach_turb_kernels.cu) ---------------------------------------------------
+extern "C" int cfd_set_turbulence(cfd_ctx* c, const cfd_turbulence* m) {
+  CFD_REQUIRE(c && m, "null argument");
+  CFD_REQUIRE(is_teach(c), "cfd_set_turbulence needs a CFD_FAMILY_TEACH context");
+  CFD_REQUIRE(c->cfg.goff == 0 && c->cfg.halo_w == 0 && c->cfg.halo_e == 0, "turbulent TEACH contexts do not shard yet");
+  CFD_REQUIRE(m->urfk > 0 && m->urfe > 0 && m->urft > 0 && m->nswpk >= 0 && m->nswpd >= 0 && m->nswpt >= 0, "bad model values");
+  CFD_CUDA(cudaSetDevice(c->device));
+  const size_t fbytes = (size_t)c->L.ni * c->L.LD * sizeof(double);
+  const int extra[] = {CFD_T, CFD_TE, CFD_ED, CFD_GEN, CFD_GAMH};
+  for (int f : extra) {
+    if (!c->field[f]) {
+      if (cudaMalloc(&c->field[f], fbytes) != cudaSuccess) {
+        cfd_set_error("cudaMalloc of %zu bytes for field %d failed", fbytes, f);
+        return CFD_ERR_NOMEM;
+      }
+      CFD_CUDA(cudaMemsetAsync(c->field[f], 0, fbytes, c->stream));
+    }
+  }
+  const size_t n1 = (size_t)(c->L.ni > c->L.nj ? c->L.ni : c->L.nj) + 2;
+  for (auto& w : c->wall) {
+    if (!w) {
+      CFD_CUDA(cudaMalloc(&w, n1 * sizeof(double)));
+      CFD_CUDA(cudaMemsetAsync(w, 0, n1 * sizeof(double), c->stream));
+    }
+  }
+  if (!c->tmult_n) {
+    CFD_CUDA(cudaMalloc(&c->tmult_n, n1 * sizeof(double)));
+    CFD_CUDA(cudaMalloc(&c->tmult_w, n1 * sizeof(double)));
+    CFD_CUDA(cudaMemsetAsync(c->tmult_n, 0, n1 * sizeof(double), c->stream));
+    CFD_CUDA(cudaMemsetAsync(c->tmult_w, 0, n1 * sizeof(double), c->stream));
+  }
+  c->turb = *m;
+  c->turbulent = true;
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
+static int wall_args(cfd_ctx* c, int which, const void* host, int n) {
+  CFD_REQUIRE(c && host, "null argument");
+  CFD_REQUIRE(c->turbulent, "wall arrays exist after cfd_set_turbulence");
+  CFD_REQUIRE(which >= 0 && which < 4, "bad wall array id");
+  const int want = (which == CFD_WALL_TAUN || which == CFD_WALL_YPLUSN) ? c->L.ni : c->L.nj;
+  CFD_REQUIRE(n == want, "wall array length must be ni (taun, yplusn) or nj (tauw, xplusw)");
+  return CFD_OK;
+}
+extern "C" int cfd_wall_upload(cfd_ctx* c, int which, const double* host, int n) {
+  int rc = wall_args(c, which, host, n);
+  if (rc) return rc;
+  CFD_CUDA(cudaSetDevice(c->device));
+  CFD_CUDA(cudaMemcpyAsync(c->wall[which], host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+extern "C" int cfd_wall_download(cfd_ctx* c, int which, double* host, int n) {
+  int rc = wall_args(c, which, host, n);
+  if (rc) return rc;
+  CFD_CUDA(cudaSetDevice(c->device));
+  CFD_CUDA(cudaMemcpyAsync(host, c->wall[which], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+extern "C" int cfd_assemble_te(cfd_ctx* c) {
+  CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  return cfd_launch_teach_scalar(c, CFD_EQ_TE);
+}
+extern "C" int cfd_assemble_ed(cfd_ctx* c) {
+  CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  return cfd_launch_teach_scalar(c, CFD_EQ_ED);
+}
+extern "C" int cfd_calcte(cfd_ctx* c, double* resork) {
+  CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc = stage_scalar_teach(c, CFD_EQ_TE, CFD_TE, c->turb.nswpk);
+  return rc ? rc : read_res(c, CFD_EQ_TE, resork);
+}
+extern "C" int cfd_calced(cfd_ctx* c, double* resore) {
+  CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  CFD_CUDA(cudaSetDevice(c->device));
+  int rc = stage_scalar_teach(c, CFD_EQ_ED, CFD_ED, c->turb.nswpd);
+  return rc ? rc : read_res(c, CFD_EQ_ED, resore);
+}
+extern "C" int cfd_props(cfd_ctx* c) {
+  CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  CFD_CUDA(cudaSetDevice(c->device));
+  return cfd_launch_teach_props(c);
 }
 
 extern "C" int cfd_calcu(cfd_ctx* c, double* resoru) {
@@ -609,6 +720,12 @@ extern "C" int cfd_iterate(cfd_ctx* c, int n, double res[8]) {
       if ((rc = stage_p(c))) return rc;
     }
     if (temp && (rc = stage_t(c))) return rc;
+    if (is_teach(c) && c->turbulent) {   // control.f90:213-217
+      if (c->turb.incalk && (rc = stage_scalar_teach(c, CFD_EQ_TE, CFD_TE, c->turb.nswpk))) return rc;
+      if (c->turb.incald && (rc = stage_scalar_teach(c, CFD_EQ_ED, CFD_ED, c->turb.nswpd))) return rc;
+      if (c->turb.incalt && (rc = stage_scalar_teach(c, CFD_EQ_T, CFD_T, c->turb.nswpt))) return rc;
+      if (c->turb.inpro && (rc = cfd_launch_teach_props(c))) return rc;
+    }
   }
   return res ? cfd_residuals(c, res) : CFD_OK;
 }

@@ -129,6 +129,11 @@ struct cfd_ctx {
   double* res_dev;                  // 8 packed residual sums
   double* seq_scratch;              // sequential-order debug sweep: forward-elimination arrays
   double* gfast[8];                 // FastGeom arrays (device)
+  bool turbulent;                    // cfd_set_turbulence was called (TEACH family)
+  cfd_turbulence turb;
+  double* wall[4];                   // taun, tauw, yplusn, xplusw (max(ni,nj)+2 doubles each)
+  double* tmult_n;                   // wall-law multiplier per i (modu) / per j (modv), refreshed before each assembly
+  double* tmult_w;
   double* spike_w;                   // j-slab partition method: spike vectors of the current equation (ni*LD each)
   double* spike_z;
   double* spike_small;               // x_s, x_n of the lines of one colour
@@ -159,4 +164,7 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, cfd::CavParams& P);
 int cfd_launch_general_assemble(cfd_ctx* c, int which);
 int cfd_launch_general_assemble_fast(cfd_ctx* c, int which, double* partial);
 int cfd_launch_teach_assemble(cfd_ctx* c, int which);
+int cfd_launch_teach_wall(cfd_ctx* c, int which);
+int cfd_launch_teach_scalar(cfd_ctx* c, int eq);
+int cfd_launch_teach_props(cfd_ctx* c);
 int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double* partial, const double* uinc);

@@ -24,6 +24,7 @@ struct TeachFastParams {
   const double *u, *v, *p, *den, *vis, *du_in, *dv_in;
   double *ae, *aw, *an, *as, *su, *dout;
   const double* uinc;
+  const double *tmult_n_arr, *tmult_w_arr;   // turbulent contexts: wall-law multipliers per i / per j, else null
   // by-i (natural order, local index)
   const double *sew, *sewu, *r_sew, *r_dxep, *r_dxpw, *r_dxepu, *r_dxpwu;
   // by-j (line layout)
@@ -151,7 +152,7 @@ __global__ void __launch_bounds__(128, 4) k_teach_assemble_u_fast(const TeachFas
         const double dvdxp = rv_p * (vC_p - vW_p) * r_dxep_i, dvdxm = rv_c * (vC_c - vW_c) * r_dxep_i;
         SU = fma(visn * dvdxp - viss * dvdxm, sewu_i, SU);                    // (...)/sns/r*vol
         if (j0 == nj - 2) {                                                   // modu: top wall (promod.f90:36-60)
-          SP = SP - P.tmult_n * sewu_i * rv_p;
+          SP = SP - (P.tmult_n_arr ? __ldg(P.tmult_n_arr + i0) : P.tmult_n) * sewu_i * rv_p;
           AN = 0.0;
         }
         if (first_u && j0 >= P.jstep) AW = 0.0;                               // step wall (:67-69)
@@ -267,7 +268,7 @@ __global__ void __launch_bounds__(128, 4) k_teach_assemble_v_fast(const TeachFas
         const double dvdyp = (v_n - v_c) * rsns_c, dvdym = (v_c - v_s) * rsns_m;
         SU = fma((sC_c * r_c) * dvdyp - (sC_m * r_m) * dvdym, c3 * sew_i, SU);  // (...)/(r*sns)*vol
         if (at_step && j0 >= P.jstep) {                                        // modv: side wall (promod.f90:105-121)
-          SP = SP - P.tmult_w * aewv;
+          SP = SP - (P.tmult_w_arr ? __ldg(P.tmult_w_arr + j0) : P.tmult_w) * aewv;
           AW = 0.0;
         }
         if (j0 == nj - 2 && past_step) AN = 0.0;
@@ -432,6 +433,8 @@ int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double
   P.ae = c->field[CFD_AE]; P.aw = c->field[CFD_AW]; P.an = c->field[CFD_AN]; P.as = c->field[CFD_AS]; P.su = c->field[CFD_SU];
   P.dout = which == 0 ? c->field[CFD_DU] : c->field[CFD_DV];
   P.uinc = uinc;
+  P.tmult_n_arr = c->turbulent ? c->tmult_n : nullptr;
+  P.tmult_w_arr = c->turbulent ? c->tmult_w : nullptr;
   P.sew = c->geom[CFD_G_SEW]; P.sewu = c->geom[CFD_G_SEWU];
   P.r_sew = c->tfast[0]; P.r_dxep = c->tfast[1]; P.r_dxpw = c->tfast[2]; P.r_dxepu = c->tfast[3]; P.r_dxpwu = c->tfast[4];
   P.rv = c->geom[CFD_G_RV]; P.rcv = c->geom[CFD_G_RCV]; P.r = c->geom[CFD_G_R];

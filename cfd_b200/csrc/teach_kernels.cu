@@ -25,6 +25,7 @@ struct TeachParams {
   double *ae, *aw, *an, *as, *ap, *su, *dout;
   double* ufield;           // u, writable (k_teach_modu_fields)
   double* uinc;             // device scalar
+  const double *tmult_n, *tmult_w;   // wall-law multipliers per i / per j (turbulent contexts), else null
   int nsym;                 // local lines 1..nsym get u(i,1) = u(i,2) (global i <= ni-1)
   int has_outlet;           // this context holds the outlet column (global i = ni) as its last local line
   const double *x, *y, *xu, *yv, *r, *rv, *rcv, *sew, *sns, *sewu, *snsv;
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(256) k_teach_assemble_u(const TeachParams P) {
       // ---- modu (promod.f90:36-77), laminar wall law: yplus = 11 <= 11.63 -> tmult = viscos/yp
       if (j == njm1) {
         const double yp = TJ(P.yv, nj) - TJ(P.y, njm1);
-        const double tmult = P.viscos / yp;
+        const double tmult = P.tmult_n ? __ldg(P.tmult_n + i - 1) : P.viscos / yp;
         SP = SP - tmult * T1(P.sewu, i) * TJ(P.rv, nj);
         AN = 0.0;
       }
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(256) k_teach_assemble_v(const TeachParams P) {
       // ---- modv (promod.f90:105-128)
       if (i == P.istep && j >= P.jstep + 1) {
         const double xp = T1(P.x, P.istep) - T1(P.xu, P.istep);
-        const double tmult = P.viscos / xp;
+        const double tmult = P.tmult_w ? __ldg(P.tmult_w + j - 1) : P.viscos / xp;
         SP = SP - tmult * TJ(P.snsv, j) * TJ(P.rv, j);
         AW = 0.0;
       }
@@ -334,6 +335,8 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which) {
   P.ap = c->field[CFD_AP]; P.su = c->field[CFD_SU];
   P.ufield = c->field[CFD_U];
   P.uinc = c->res_dev + 7;          // last slot of the packed scalar block
+  P.tmult_n = c->turbulent ? c->tmult_n : nullptr;
+  P.tmult_w = c->turbulent ? c->tmult_w : nullptr;
   P.x = c->geomn[CFD_G_X]; P.y = c->geom[CFD_G_Y]; P.xu = c->geomn[CFD_G_XU]; P.yv = c->geom[CFD_G_YV];
   P.r = c->geom[CFD_G_R]; P.rv = c->geom[CFD_G_RV]; P.rcv = c->geom[CFD_G_RCV];
   P.sew = c->geomn[CFD_G_SEW]; P.sns = c->geom[CFD_G_SNS]; P.sewu = c->geomn[CFD_G_SEWU]; P.snsv = c->geom[CFD_G_SNSV];

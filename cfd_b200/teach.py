@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import CfdConfig, check
+from ._lib import CfdConfig, CfdTurbulence, WALL_ID, check
 from .cavity import CavityFVM
 
 
@@ -89,7 +89,8 @@ class TeachFVM(CavityFVM):
 
     def __init__(self, ni=100, nj=100, *, order="redblack", epsx=1.05, indcos=2, rlarge=0.0124, uin=0.5,
                  densit=1000.0, viscos=0.8e-3, urf=(0.5, 0.5, 1.0), nswp=(3, 3, 5), jstep=None, device=-1, tdma_m=0,
-                 ni_local=None, goff=0, halo_w=0, halo_e=0):
+                 ni_local=None, goff=0, halo_w=0, halo_e=0, turbulent=False, urf_turb=(0.7, 0.7, 1.0, 0.7),
+                 nswp_turb=(3, 3, 3), tin=0.0, turbin=0.03, alamda=0.005, twalln=100.0, prandl=7.0):
         self.lib = _lib.load()
         nl = ni if ni_local is None else ni_local
         self.ni, self.nj = nl, nj
@@ -148,6 +149,89 @@ class TeachFVM(CavityFVM):
         self.upload("vis", vis)
         self.upload("u", u)
         self.resoru = self.resorv = self.resorm = 0.0
+        self.turbulent = False
+        if turbulent:
+            if ni_local is not None:
+                raise ValueError("turbulent TEACH contexts do not shard yet")
+            self._init_turbulence(uin, rlarge, urf_turb, nswp_turb, tin, turbin, alamda, twalln, prandl)
+
+    # -- k-epsilon / energy (control.f90:105-179): constants, initial k, eps, T, wall y+, first props ------------
+    def _init_turbulence(self, uin, rlarge, urf_turb, nswp_turb, tin, turbin, alamda, twalln, prandl):
+        ni, nj, js = self.ni, self.nj, self.jstep
+        m = CfdTurbulence()
+        m.cmu, m.cd, m.c1, m.c2, m.cappa, m.elog = 0.09, 1.00, 1.44, 1.92, .4187, 9.793
+        m.pred = m.cappa * m.cappa / (m.c2 - m.c1) / (m.cmu ** .5)
+        m.prte, m.prandt, m.prandl = 1.0, 0.9, prandl
+        pfun = m.prandl / m.prandt
+        m.pfun = 9.24 * (pfun ** 0.75 - 1.0) * (1.0 + 0.28 * np.exp(-0.007 * pfun))
+        m.twalln = twalln
+        m.urfk, m.urfe, m.urft, m.urfvis = urf_turb
+        m.nswpk, m.nswpd, m.nswpt = nswp_turb
+        m.incalk = m.incald = m.incalt = m.inpro = 1
+        self.model = m
+        check(self.lib.cfd_set_turbulence(self._h, C.byref(m)))
+        self.turbulent = True
+        tein = turbin * (uin * uin)
+        edin = tein ** 1.5 / (alamda * rlarge)
+        te, ed, t = (np.zeros((ni, nj), order="F") for _ in range(3))
+        te[0, 1:js] = tein
+        ed[0, 1:js] = edin
+        t[0, 1:js] = tin
+        for i in range(2, ni + 1):
+            jfin = nj if i >= self.istep + 1 else js + 1
+            te[i - 1, 1:jfin - 1] = tein
+            ed[i - 1, 1:jfin - 1] = edin
+        t[1:ni - 1, nj - 1] = twalln
+        t[0, js - 1:nj] = tin
+        yplusn, xplusw = np.zeros(ni), np.zeros(nj)
+        yplusn[1:ni - 1] = 11.0
+        xplusw[js - 1:nj] = 11.0
+        xplusw[js - 1] = 0.0
+        self.upload("te", te)
+        self.upload("ed", ed)
+        self.upload("t", t)
+        self.wall_upload("yplusn", yplusn)
+        self.wall_upload("xplusw", xplusw)
+        self.props()
+
+    def wall_upload(self, name, a):
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        check(self.lib.cfd_wall_upload(self._h, WALL_ID[name], a.ctypes.data_as(C.c_void_p), a.size))
+
+    def wall_download(self, name):
+        a = np.zeros(self.ni if name in ("taun", "yplusn") else self.nj)
+        check(self.lib.cfd_wall_download(self._h, WALL_ID[name], a.ctypes.data_as(C.c_void_p), a.size))
+        return a
+
+    def props(self):
+        check(self.lib.cfd_props(self._h))
+
+    def assemble_te(self):
+        check(self.lib.cfd_assemble_te(self._h))
+
+    def assemble_ed(self):
+        check(self.lib.cfd_assemble_ed(self._h))
+
+    def calcte(self):
+        r = C.c_double()
+        check(self.lib.cfd_calcte(self._h, C.byref(r)))
+        return r.value
+
+    def calced(self):
+        r = C.c_double()
+        check(self.lib.cfd_calced(self._h, C.byref(r)))
+        return r.value
+
+    def calct(self):
+        r = C.c_double()
+        check(self.lib.cfd_calct(self._h, C.byref(r)))
+        return r.value
+
+    def iterate_turb(self, n=1):
+        """n passes of control.f90:210-217; returns (resoru, resorv, resorm, resort, resork, resore)."""
+        res = (C.c_double * 8)()
+        check(self.lib.cfd_iterate(self._h, n, res))
+        return res[0], res[1], res[2], res[3], res[4], res[5]
 
 
 _BY_I = ("x", "xu", "sew", "sewu", "dxep", "dxpw", "dxepu", "dxpwu")

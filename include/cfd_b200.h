@@ -51,6 +51,8 @@ typedef enum cfd_field {
   CFD_GAMT,   /* diffusion coefficient of T (gam when nq == 4), boundary rows included (0 = adiabatic) */
   CFD_SUSRC,  /* su per unit volume */
   CFD_SPSRC,  /* sp per unit volume */
+  /* TEACH family with cfd_set_turbulence: te, ed, gen, gamh of module general (general.f90:30-40) */
+  CFD_TE, CFD_ED, CFD_GEN, CFD_GAMH,
   CFD_FIELD_COUNT
 } cfd_field;
 
@@ -69,7 +71,7 @@ typedef enum cfd_geom {
 } cfd_geom;
 
 /* Equation slots for urf[] / nswp[] / residuals: nq of module vars (cylin_cond.f90:47). */
-enum { CFD_EQ_U = 0, CFD_EQ_V = 1, CFD_EQ_P = 2, CFD_EQ_T = 3, CFD_EQ_COUNT = 8 };
+enum { CFD_EQ_U = 0, CFD_EQ_V = 1, CFD_EQ_P = 2, CFD_EQ_T = 3, CFD_EQ_TE = 4, CFD_EQ_ED = 5, CFD_EQ_COUNT = 8 };
 
 /*
  * The literals `program cavity_fvm` sets before its loop (cavity_fvm.f90:519-552), as one struct.
@@ -188,6 +190,34 @@ int cfd_assemble_t(cfd_ctx* ctx);                       /* buoyancy_cav.f90:371-
    first != 0 treats phi as zero where the reference has just executed pp(:,:)=0 (cavity_fvm.f90:342) */
 int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first);
 int cfd_correct(cfd_ctx* ctx, const double* ppref_device); /* cavity_fvm.f90:346-354; NULL = pp(ipref,jpref) */
+
+/* ---- TEACH family: k-epsilon model, energy equation, wall functions -------------------------------
+   cfd_set_turbulence allocates te, ed, t, gen, gamh and switches on the wall-function branches of modu / modv
+   (promod.f90:36-60, 105-121).  The literals are those `contro` sets (control.f90:105-141).  After it:
+     cfd_calcte  = calcte (calc.f90:388-485) with modte (promod.f90:182-256)     residual slot CFD_EQ_TE
+     cfd_calced  = calced (calc.f90:490-577) with moded (promod.f90:260-296)     residual slot CFD_EQ_ED
+     cfd_calct   = calct  (calc.f90:309-385) with modt  (promod.f90:146-178)     residual slot CFD_EQ_T
+     cfd_props   = props  (general.f90:165-190)
+   and cfd_iterate runs calcu, calcv, calcp, calcte, calced, calct, props per pass (control.f90:210-217; each
+   switched by incalk / incald / incalt / inpro).  The 1-D wall arrays taun, tauw, yplusn, xplusw (general.f90:45-46)
+   live on the device; cfd_wall_upload / cfd_wall_download move them (n = ni for taun, yplusn; nj for tauw, xplusw).
+   log / pow of the wall laws come from the CUDA math library: results agree with the reference arithmetic to
+   rounding (1e-12 class), not bit for bit. */
+typedef struct cfd_turbulence {
+  double cmu, cd, c1, c2, cappa, elog, pred, prte, prandl, prandt, pfun, twalln;
+  double urfk, urfe, urft, urfvis;
+  int nswpk, nswpd, nswpt;
+  int incalk, incald, incalt, inpro;
+} cfd_turbulence;
+typedef enum cfd_wall_array { CFD_WALL_TAUN = 0, CFD_WALL_TAUW = 1, CFD_WALL_YPLUSN = 2, CFD_WALL_XPLUSW = 3 } cfd_wall_array;
+int cfd_set_turbulence(cfd_ctx* ctx, const cfd_turbulence* model);
+int cfd_wall_upload(cfd_ctx* ctx, int which, const double* host, int n);
+int cfd_wall_download(cfd_ctx* ctx, int which, double* host, int n);
+int cfd_calcte(cfd_ctx* ctx, double* resork);
+int cfd_calced(cfd_ctx* ctx, double* resore);
+int cfd_props(cfd_ctx* ctx);
+int cfd_assemble_te(cfd_ctx* ctx);
+int cfd_assemble_ed(cfd_ctx* ctx);
 
 /* ---- j-slabs: lisolv's tridiagonal systems (cavity_fvm.f90:62-80) cut across contexts ----------------------
    Partition (Wang / SPIKE) method.  With x_s, x_n the still unknown values just outside a context's piece of a

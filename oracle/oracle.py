@@ -75,6 +75,21 @@ def _teach_struct(real):
 
 _TeachF64, _TeachF32 = _teach_struct(C.c_double), _teach_struct(C.c_float)
 
+
+def _teach_turb_struct(real, base):
+    rp = C.POINTER(real)
+
+    class _S(C.Structure):
+        F2 = ("ed", "t", "gen", "gamh", "sukd", "spkd")
+        _fields_ = ([("b", C.POINTER(base))] + [(n, C.c_int) for n in ("nswpk", "nswpd", "nswpt")]
+                    + [(n, real) for n in ("urfk", "urfe", "urft", "urfvis", "cmu", "cd", "c1", "c2", "cappa", "elog",
+                                           "pred", "prte", "prandl", "prandt", "pfun", "twalln", "resork", "resore", "resort")]
+                    + [(n, rp) for n in F2])
+    return _S
+
+
+_TeachTurbF64, _TeachTurbF32 = _teach_turb_struct(C.c_double, _TeachF64), _teach_turb_struct(C.c_float, _TeachF32)
+
 _libs: dict = {}
 
 
@@ -352,6 +367,43 @@ class Teach:
     @property
     def residuals(self):
         return self.s.resoru, self.s.resorv, self.s.resorm
+
+
+class TeachTurb(Teach):
+    """The TEACH-T program as shipped: k-epsilon + energy on top of `Teach` (calcte, calced, calct, props and the
+    wall-function hooks modte / moded / modt; teach_turb.inc)."""
+
+    def __init__(self, ni=100, nj=100, *, urf_turb=(0.7, 0.7, 1.0, 0.7), nswp_turb=(3, 3, 3), tin=0.0, turbin=0.03,
+                 alamda=0.005, rlarge=0.0124, uin=0.5, **kw):
+        super().__init__(ni, nj, rlarge=rlarge, uin=uin, **kw)
+        f64 = self.dtype == np.float64
+        S = _TeachTurbF64 if f64 else _TeachTurbF32
+        real = C.c_double if f64 else C.c_float
+        rp = C.POINTER(real)
+        for n in S.F2:
+            setattr(self, n, np.zeros((self.it, self.nj), dtype=self.dtype, order="F"))
+        q = S(b=C.pointer(self.s), nswpk=nswp_turb[0], nswpd=nswp_turb[1], nswpt=nswp_turb[2],
+              urfk=urf_turb[0], urfe=urf_turb[1], urft=urf_turb[2], urfvis=urf_turb[3])
+        for n in S.F2:
+            setattr(q, n, getattr(self, n).ctypes.data_as(rp))
+        self.q = q
+        ptr = C.POINTER(S)
+        for n in ("turb_initial", "props", "assemble_te", "assemble_ed", "assemble_t", "calcte", "calced", "calct",
+                  "iterate_turb"):
+            fn = getattr(self.L, "orc_teach_" + n + self.sfx)
+            fn.restype = None
+            fn.argtypes = {"turb_initial": [ptr] + [real] * 5, "iterate_turb": [ptr, C.c_int]}.get(n, [ptr])
+        self._tcall("turb_initial", uin, tin, turbin, alamda, rlarge)
+
+    def _tcall(self, name, *a):
+        getattr(self.L, "orc_teach_" + name + self.sfx)(C.byref(self.q), *a)
+
+    def tcall(self, name):
+        self._tcall(name)
+
+    def iterate_turb(self, n=1):
+        self._tcall("iterate_turb", n)
+        return (self.s.resoru, self.s.resorv, self.s.resorm, self.q.resort, self.q.resork, self.q.resore)
 
 
 class _FdcStruct(C.Structure):

@@ -15,7 +15,7 @@
  * The reference computes in default REAL (FP32); BASELINE.json:north_star asks for FP64.  The body
  * (teach_body.inc) is therefore compiled twice: *_f64 is the parity oracle of the FP64 CUDA path, *_f32 is the
  * reference "as written", used to check that the two agree to single-precision accuracy.
- * k-epsilon, energy equation, props: out of this subset (SURVEY 8f-2 "next").
+ * k-epsilon, energy equation and props: teach_turb.inc, same two precisions.
  *
  * PARITY PIN: none exists -- the reference ships no outputs for this program and SURVEY 8(c) has no table for
  * it; "parity unpinned" applies to this family.
@@ -31,14 +31,17 @@
 #define SQRT sqrt
 #define POW pow
 #define LOG log
+#define EXP exp
 #define RABS(x) fabs(x)
 #define RMAX(a, b) ((a) > (b) ? (a) : (b))
 #include "teach_body.inc"
+#include "teach_turb.inc"
 #undef REAL
 #undef NAME
 #undef SQRT
 #undef POW
 #undef LOG
+#undef EXP
 #undef RABS
 
 #define REAL float
@@ -46,5 +49,7 @@
 #define SQRT sqrtf
 #define POW powf
 #define LOG logf
+#define EXP expf
 #define RABS(x) fabsf(x)
 #include "teach_body.inc"
+#include "teach_turb.inc"

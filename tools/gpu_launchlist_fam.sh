@@ -1,6 +1,6 @@
 #!/bin/bash
 # ncu launch list (kernel durations) for the buoyancy / backward-step configs
-for w in buoyancy step; do
+for w in ${1:-buoyancy step}; do
 CMD="python tools/bench_families.py $w"
 $CMD > gpurun_out/fam_$w.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 150 --csv --log-file gpurun_out/launches_$w.csv $CMD > gpurun_out/ncu_fam_$w.log 2>&1
 cat gpurun_out/fam_$w.log
