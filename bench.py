@@ -335,11 +335,55 @@ def run_heat(args):
     import cfd_b200
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
     K, W = args.steps, args.warmup
     hbm_peak, peak_src = peaks()
     n = HEAT_N
     stream = torch.cuda.Stream()
-    h = cfd_b200.Heat2D(n, n, device=0)
+    if world > 1:
+        # weak scaling: 16384 x 16384 rows per GPU, row slabs with one halo row per side and step (NCCL send/recv)
+        from cfd_b200.dist import SlabHeat
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        sh = SlabHeat(n, n * world, stream=stream)
+        step = sh.step
+        with torch.cuda.stream(stream):
+            step(W)
+            torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+            sampler = ClockSampler(local)
+            if rank == 0:
+                sampler.start()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            step(K)
+            e1.record(stream)
+            torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            clocks = sampler.stop() if rank == 0 else None
+        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+        glups = n * n * world * K / (ms * 1e-3) / 1e9
+        out = {"metric": "ftcs_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K, "warmup": W,
+               "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic", "steps_per_s": K / (ms * 1e-3),
+               "config": {"workload": f"2-D FTCS heat conduction, {n}x{n} nodes per GPU, FP64, Fo=0.2 (BASELINE.json configs[1])",
+                          "global_grid": f"{n}x{n * world}",
+                          "parallelism": f"row slabs x{world}, one halo row per side and step (NCCL send/recv)",
+                          "l2": "field (2.1 GB per GPU) larger than L2; ping-pong buffers"},
+               "gpu_launches": K,
+               "roofline": {"bound": "hbm", "kernel": "k_ftcs<false>", "achieved": HEAT_BYTES_PER_CELL * glups / world,
+                            "peak": hbm_peak, "unit": "GB/s", "frac": HEAT_BYTES_PER_CELL * glups / world / hbm_peak,
+                            "peak_source": peak_src, "traffic": None},
+               "e2e": None, "clocks": clocks}
+        if rank == 0:
+            emit(out)
+        dist.destroy_process_group()
+        return
+    h = cfd_b200.Heat2D(n, n, device=local)
     h.set_stream(stream.cuda_stream)
     host = torch.zeros((n, n), dtype=torch.float64, pin_memory=True)
     host.view(-1)[:: 7] = 1.0

@@ -54,6 +54,17 @@ def main():
                           "frac_of_measured_hbm": 1056 * cells / ms / 1e6 / PEAK, "layout": g.layout,
                           "finite": bool(np.isfinite(r).all())}), flush=True)
         g.close()
+    if "step_turb" in which:
+        ni, nj = 16384, 4096
+        g = cfd_b200.TeachFVM(ni, nj, epsx=1.0, order="redblack", turbulent=True)
+        ms = timed(lambda k: g.iterate_async(k), 10)
+        cells = (ni - 2) * (nj - 2)
+        r = g.iterate_turb(1)
+        print(json.dumps({"case": "backward step 16384x4096 as shipped: k-epsilon + energy + props (SURVEY 8d: ~1992 B/cell)",
+                          "ms_per_iteration": ms, "GLUPS": cells / ms / 1e6, "algorithmic_GBs": 1992 * cells / ms / 1e6,
+                          "frac_of_measured_hbm": 1992 * cells / ms / 1e6 / PEAK, "layout": g.layout,
+                          "finite": bool(np.isfinite(r).all()), "residuals": list(r)}), flush=True)
+        g.close()
     if "implicit" in which:
         n = 16384
         h = cfd_b200.Heat2D(n, n, fo=5.0)
