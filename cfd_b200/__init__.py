@@ -9,5 +9,6 @@ from .heat import Heat2D  # noqa: F401
 from .fdcavity import FDCavity  # noqa: F401
 from .teach import TeachFVM, teach_grid, teach_init  # noqa: F401
 from .general import BuoyantCavity, CylinderConduction, GeneralFVM, grid  # noqa: F401
+from .scalar import LinearSystem5, ObliqueConvection, StagnationPoint, StagnationPointUnsteady, lin_grid  # noqa: F401
 
 __version__ = "0.1.0"

@@ -31,7 +31,7 @@ class CfdConfig(C.Structure):
                 ("indcos", C.c_int), ("istep", C.c_int), ("jstep", C.c_int), ("_pad", C.c_int),
                 ("viscos", C.c_double), ("flowin", C.c_double), ("great", C.c_double),
                 ("joff", C.c_int), ("nj_global", C.c_int), ("halo_s", C.c_int), ("halo_n", C.c_int),
-                ("sns_njm1", C.c_double)]
+                ("sns_njm1", C.c_double), ("raw_coefficients", C.c_int)]
 
 
 class CfdHookDesc(C.Structure):
@@ -108,6 +108,12 @@ SYMBOLS = {
     "cfd_props": (C.c_int, [_vp]),
     "cfd_assemble_te": (C.c_int, [_vp]),
     "cfd_assemble_ed": (C.c_int, [_vp]),
+    "cfd_lin_wesweep": (C.c_int, [_vp, C.c_int]),
+    "cfd_lin_snsweep": (C.c_int, [_vp, C.c_int]),
+    "cfd_lin_residual": (C.c_int, [_vp, C.c_int, _dp]),
+    "cfd_lin_solve": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, _ip, _dp]),
+    "cfd_lin_time_terms": (C.c_int, [_vp, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int]),
+    "cfd_field_copy": (C.c_int, [_vp, C.c_int, C.c_int]),
     "cfd_spike_basis": (C.c_int, [_vp, C.c_int, C.c_int]),
     "cfd_spike_pack": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
     "cfd_spike_finish": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int, C.c_int]),

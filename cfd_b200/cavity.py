@@ -54,7 +54,7 @@ class CavityFVM:
     def __init__(self, nicv=10, njcv=10, *, iadv=3, order="redblack", urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3),
                  ipref=None, jpref=None, device=-1, tdma_m=0,
                  ni_local=None, goff=0, halo_w=0, halo_e=0, sew_nim1=0.0,
-                 nj_local=None, joff=0, halo_s=0, halo_n=0, sns_njm1=0.0):
+                 nj_local=None, joff=0, halo_s=0, halo_n=0, sns_njm1=0.0, raw_coefficients=False):
         self.lib = _lib.load()
         self.nicv, self.njcv = nicv, njcv
         self.ni_global, self.nj = nicv + 2, njcv + 2
@@ -89,6 +89,7 @@ class CavityFVM:
         cfg.nj_global = self.nj_global if (nj_local is not None) else 0
         cfg.halo_s, cfg.halo_n = halo_s, halo_n
         cfg.sns_njm1 = sns_njm1
+        cfg.raw_coefficients = 1 if raw_coefficients else 0
         self._cfg = cfg
         self._h = C.c_void_p()
         check(self.lib.cfd_create(C.byref(self._h), C.byref(cfg)))

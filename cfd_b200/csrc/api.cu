@@ -204,7 +204,7 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   }
   {
     const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
-    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0);
+    c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || cfg->raw_coefficients;
     if (teach && c->exact_assembly &&
         !(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni))) {
       delete c;

@@ -151,6 +151,7 @@ int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev);
 int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first);
 int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int first);
 int cfd_launch_spike_basis(cfd_ctx* c, int istart, int jstart);
+int cfd_launch_sweep_seq2(cfd_ctx* c, int istart, int jstart, double* phi, int first, int two_div);
 void cfd_local_j_range(const cfd_ctx* c, int gj_lo, int gj_hi, int* jlo, int* jhi);
 int cfd_launch_to_line_layout(cfd_ctx* c, const double* colmajor, double* dst, int field);
 int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor, int field);

@@ -426,6 +426,8 @@ struct SeqParams {
   int ia, ib;        // 0-based inclusive local line range, swept in increasing order
   int jlo, jhi;
   int first;         // phi(i+1,:) taken as zero (pp(:,:) = 0 folded in)
+  int two_div;       // 1: the `tdma` of the scalar-transport demos (fvm2d_stag_point.f90:232-260): rhs summed as
+                     //    su + aw*phiW + ae*phiE and two divisions per row instead of one reciprocal
   const double *ae, *aw, *an, *as, *ap, *su;
   double* phi;
 };
@@ -452,7 +454,8 @@ __global__ void __launch_bounds__(1024, 1) k_tdma_seq(const SeqParams P) {
         sa[j0] = P.an[cq];
         sb[j0] = P.as[cq];
         sd[j0] = (P.L.nc == 6) ? P.ap[cq] : 1.0;
-        sc[j0] = __dadd_rn(__dadd_rn(__dmul_rn(P.ae[cq], e), __dmul_rn(P.aw[cq], w)), P.su[cq]);
+        sc[j0] = P.two_div ? __dadd_rn(__dadd_rn(P.su[cq], __dmul_rn(P.aw[cq], w)), __dmul_rn(P.ae[cq], e))
+                           : __dadd_rn(__dadd_rn(__dmul_rn(P.ae[cq], e), __dmul_rn(P.aw[cq], w)), P.su[cq]);
       }
     }
     __syncthreads();
@@ -460,9 +463,15 @@ __global__ void __launch_bounds__(1024, 1) k_tdma_seq(const SeqParams P) {
       double ap_ = 0.0, cp_ = sx[P.jlo - 1];
       for (int j0 = P.jlo; j0 <= P.jhi; ++j0) {
         const double b = sb[j0];
-        const double term = __ddiv_rn(1.0, __dsub_rn(sd[j0], __dmul_rn(b, ap_)));
-        ap_ = __dmul_rn(sa[j0], term);
-        cp_ = __dmul_rn(__dadd_rn(sc[j0], __dmul_rn(b, cp_)), term);
+        if (P.two_div) {
+          const double denom = __dsub_rn(sd[j0], __dmul_rn(b, ap_));
+          ap_ = __ddiv_rn(sa[j0], denom);
+          cp_ = __ddiv_rn(__dadd_rn(sc[j0], __dmul_rn(b, cp_)), denom);
+        } else {
+          const double term = __ddiv_rn(1.0, __dsub_rn(sd[j0], __dmul_rn(b, ap_)));
+          ap_ = __dmul_rn(sa[j0], term);
+          cp_ = __dmul_rn(__dadd_rn(sc[j0], __dmul_rn(b, cp_)), term);
+        }
         sa[j0] = ap_;
         sc[j0] = cp_;
       }
@@ -678,7 +687,11 @@ static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P) {
   return CFD_OK;
 }
 
+int cfd_launch_sweep_seq2(cfd_ctx* c, int istart, int jstart, double* phi, int first, int two_div);
 int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int first) {
+  return cfd_launch_sweep_seq2(c, istart, jstart, phi, first, 0);
+}
+int cfd_launch_sweep_seq2(cfd_ctx* c, int istart, int jstart, double* phi, int first, int two_div) {
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   if (c->cfg.goff != 0 || (c->cfg.ni_global && c->cfg.ni_global != c->L.ni)) {
     cfd_set_error("sequential-order sweeps do not shard: replicas only (single-GPU contexts)");
@@ -691,6 +704,7 @@ int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int fi
   P.jlo = jstart - 1;
   P.jhi = c->L.nj - 2;
   P.first = first ? 1 : 0;
+  P.two_div = two_div;
   P.ae = c->field[CFD_AE];
   P.aw = c->field[CFD_AW];
   P.an = c->field[CFD_AN];

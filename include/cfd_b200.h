@@ -107,6 +107,8 @@ typedef struct cfd_config {
   int halo_s, halo_n;      /* halo rows at the south / north end of the local arrays (0 at a physical wall) */
   double sns_njm1;         /* sns(njm1) of the GLOBAL grid for the stale-scalar quirk of calcu (cavity_fvm.f90:186);
                               0 = read it from the local geometry */
+  int raw_coefficients;    /* 1: keep the six coefficient arrays as the reference stores them also in a red/black context
+                              (needed by cfd_lin_* and by hosts that upload their own coefficients) */
 } cfd_config;
 
 /* Device-side form of the `user` module hook gamsor() (cylin_cond.f90:149-169; the buoyancy program's own
@@ -218,6 +220,26 @@ int cfd_calced(cfd_ctx* ctx, double* resore);
 int cfd_props(cfd_ctx* ctx);
 int cfd_assemble_te(cfd_ctx* ctx);
 int cfd_assemble_ed(cfd_ctx* ctx);
+
+/* ---- generic 5-point systems: the iterative line-by-line TDMA of the scalar-transport demos -------
+   The context's coefficient fields (uploaded with cfd_upload, CFD_AE .. CFD_SU, raw storage) define
+   ap*phi = ae*phiE + aw*phiW + an*phiN + as*phiS + su  on the interior nodes; boundary values are the Dirichlet
+   data in `field`.  cfd_lin_wesweep = wesweep (stagnation-point-flow-2d/steady/fvm2d_stag_point.f90:164-196),
+   cfd_lin_snsweep = snsweep (:198-230), both with `tdma` (:232-260, two divisions per row), cfd_lin_residual = the
+   sum of :99-106, cfd_lin_solve = the loops tdma_we / tdma_sn (:82-162; variant 1: tdma_solver of
+   diagonal-convection-2d/fvm2d_oblique_conv.f90:284-318, whose all-terms-on-the-left convention is obtained by
+   uploading -ae, -aw, -an, -as).  Sequential-order contexts follow the reference's line order and arithmetic. */
+int cfd_lin_wesweep(cfd_ctx* ctx, int field);
+int cfd_lin_snsweep(cfd_ctx* ctx, int field);
+int cfd_lin_residual(cfd_ctx* ctx, int field, double* res);
+int cfd_lin_solve(cfd_ctx* ctx, int field, int dir, int variant, int maxit, double tol, int* iters, double* rsm);
+/* time discretisation of stag_point_unsteady.f90:634-688 on the device: from the steady coefficients kept in four
+   plain fields (base_fields = ae, aw, an, as), ct = den/dt*dx*dy (ct_field) and the old solution (phio_field) build
+   ae .. su of the step: itsch 1 explicit Euler, 2 implicit Euler, 3 Crank-Nicolson; the neighbour coefficients are
+   stored negated, which turns that program's all-terms-on-the-left solver convention (:159-261) into the form
+   cfd_lin_* solve.  cfd_field_copy: phio = phi (:586). */
+int cfd_lin_time_terms(cfd_ctx* ctx, int itsch, int phio_field, const int base_fields[4], int ct_field);
+int cfd_field_copy(cfd_ctx* ctx, int dst_field, int src_field);
 
 /* ---- j-slabs: lisolv's tridiagonal systems (cavity_fvm.f90:62-80) cut across contexts ----------------------
    Partition (Wang / SPIKE) method.  With x_s, x_n the still unknown values just outside a context's piece of a

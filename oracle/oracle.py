@@ -487,3 +487,107 @@ class FDCavityImplicit:
 
     def step(self):
         return self.L.orc_fdci_step(C.byref(self.s))
+
+
+# ---- scalar-transport demos (oracle/lin_oracle.c) ------------------------------------------------------------------
+class _LinBase:
+    COEF = ("aw", "ae", "as_", "an", "ap", "su")
+
+    def _alloc(self, nicv, njcv, fast):
+        self.L = lib(fast)
+        self.nicv, self.njcv = nicv, njcv
+        self.ni, self.nj = nicv + 2, njcv + 2
+        for n, m in (("x", self.ni), ("y", self.nj), ("xc", self.ni), ("yc", self.nj), ("fx", self.ni), ("fy", self.nj)):
+            setattr(self, n, np.zeros(m))
+        for n in ("u", "v", "phi", "phio", "ae", "aw", "an", "as_", "ap", "su"):
+            setattr(self, n, np.zeros((self.ni, self.nj), order="F"))
+        self.L.orc_lin_grid.argtypes = [C.c_int, C.c_int] + [C.c_double] * 4 + [_dp] * 6
+        self.L.orc_lin_grid.restype = None
+        self.L.orc_lin_grid(nicv, njcv, 0.0, 1.0, 0.0, 1.0, *(_p(getattr(self, n)) for n in ("x", "y", "xc", "yc", "fx", "fy")))
+
+    def _coef(self):
+        return [_p(getattr(self, n)) for n in self.COEF]
+
+
+class StagPoint(_LinBase):
+    """fvm2d_stag_point.f90 / stag_point_unsteady.f90 restated (oracle/lin_oracle.c)."""
+
+    def __init__(self, nicv=20, njcv=20, isch=1, isol=2, den=1.2, gam=0.1, order=0, fast=False):
+        self._alloc(nicv, njcv, fast)
+        self.isch, self.isol, self.den, self.gam, self.order = isch, isol, den, gam, order
+        L = self.L
+        L.orc_stag_setup.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double] + [_dp] * 15
+        L.orc_stag_setup.restype = None
+        L.orc_stag_setup(nicv, njcv, isch, den, gam, *(_p(getattr(self, n)) for n in
+                         ("x", "y", "xc", "yc", "fx", "fy", "u", "v", "phi", "ae", "aw", "an", "as_", "ap", "su")))
+        for n in ("orc_stag_wesweep", "orc_stag_snsweep"):
+            getattr(L, n).argtypes = [C.c_int] * 3 + [_dp] * 7
+            getattr(L, n).restype = None
+        L.orc_stag_residual.argtypes = [C.c_int] * 2 + [_dp] * 7
+        L.orc_stag_residual.restype = C.c_double
+        L.orc_stag_solve.argtypes = [C.c_int] * 5 + [C.c_double] + [_dp] * 8
+        L.orc_stag_solve.restype = C.c_int
+        L.orc_stag_finish.argtypes = [C.c_int, C.c_int, C.c_double, _dp, _dp, _dp]
+        L.orc_stag_finish.restype = C.c_double
+        L.orc_stag_time_terms.argtypes = [C.c_int] * 4 + [C.c_double] * 3 + [_dp] * 15
+        L.orc_stag_time_terms.restype = None
+        L.orc_ustag_solve.argtypes = [C.c_int] * 5 + [C.c_double] + [_dp] * 8
+        L.orc_ustag_solve.restype = C.c_int
+
+    def wesweep(self):
+        self.L.orc_stag_wesweep(self.ni, self.nj, self.order, *self._coef(), _p(self.phi))
+
+    def snsweep(self):
+        self.L.orc_stag_snsweep(self.ni, self.nj, self.order, *self._coef(), _p(self.phi))
+
+    def residual(self):
+        return self.L.orc_stag_residual(self.ni, self.nj, *self._coef(), _p(self.phi))
+
+    def solve(self, maxit=1000, tol=1.0e-4):
+        rsm = C.c_double()
+        it = self.L.orc_stag_solve(self.ni, self.nj, self.order, 0 if self.isol == 1 else 1, maxit, tol, *self._coef(),
+                                   _p(self.phi), C.byref(rsm))
+        self.rsm = rsm.value
+        return it
+
+    def finish(self):
+        return self.L.orc_stag_finish(self.ni, self.nj, self.gam, _p(self.y), _p(self.xc), _p(self.phi))
+
+    def step(self, itsch, dt=1.0e-3):
+        """One pass of the time loop of stag_point_unsteady.f90:583-700; returns the solver's iteration count."""
+        self.phio[:, :] = self.phi
+        self.L.orc_stag_time_terms(self.nicv, self.njcv, self.isch, itsch, self.den, self.gam, dt,
+                                   *(_p(getattr(self, n)) for n in ("x", "y", "xc", "yc", "fx", "fy", "u", "v", "phio",
+                                                                   "ae", "aw", "an", "as_", "ap", "su")))
+        rsm = C.c_double()      # the unsteady file's own solver copies (all terms on the left)
+        it = self.L.orc_ustag_solve(self.ni, self.nj, self.order, 0 if self.isol == 1 else 1, 1000, 1.0e-4, *self._coef(),
+                                    _p(self.phi), C.byref(rsm))
+        self.rsm = rsm.value
+        return it
+
+
+class Oblique(_LinBase):
+    """fvm2d_oblique_conv.f90 restated (oracle/lin_oracle.c)."""
+
+    def __init__(self, nicv=20, njcv=20, vel=2.0, east_north_bc=1, order=0, fast=False):
+        self._alloc(nicv, njcv, fast)
+        self.order, self.bc = order, east_north_bc
+        L = self.L
+        L.orc_oblique_setup.argtypes = [C.c_int, C.c_int, C.c_double, C.c_int] + [_dp] * 11
+        L.orc_oblique_setup.restype = None
+        L.orc_oblique_setup(nicv, njcv, vel, east_north_bc, *(_p(getattr(self, n)) for n in
+                            ("x", "y", "u", "v", "phi", "ae", "aw", "an", "as_", "ap", "su")))
+        L.orc_oblique_solve.argtypes = [C.c_int] * 4 + [C.c_double] + [_dp] * 8
+        L.orc_oblique_solve.restype = C.c_int
+
+    def solve(self, maxit=100, tol=1.0e-4):
+        rsm = C.c_double()
+        it = self.L.orc_oblique_solve(self.ni, self.nj, self.order, maxit, tol, *self._coef(), _p(self.phi), C.byref(rsm))
+        self.rsm = rsm.value
+        return it
+
+    def finish(self):
+        if self.bc == 1:
+            self.phi[self.ni - 1, :] = self.phi[self.ni - 2, :]
+            self.phi[:, self.nj - 1] = self.phi[:, self.nj - 2]
+        return self.phi

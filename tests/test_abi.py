@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol(cfd):
 def test_struct_layout_matches_header(cfd):
     from cfd_b200 import _lib
     # 5 ints + 8 ints + (pad) 8 doubles + 8 ints + double = natural C layout
-    assert C.sizeof(_lib.CfdConfig) == 5 * 4 + 8 * 4 + 4 + 8 * 8 + 8 * 4 + 8 + 2 * 4 + 3 * 4 + 4 + 3 * 8 + 4 * 4 + 8
+    assert C.sizeof(_lib.CfdConfig) == 5 * 4 + 8 * 4 + 4 + 8 * 8 + 8 * 4 + 8 + 2 * 4 + 3 * 4 + 4 + 3 * 8 + 4 * 4 + 8 + 8
     assert C.sizeof(_lib.CfdHeatConfig) == 8 + 14 * 8 + 5 * 4 + 4
 
 
