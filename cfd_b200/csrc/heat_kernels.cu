@@ -264,6 +264,158 @@ __global__ void __launch_bounds__(128) k_lod_y(const LodParams P) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Production LOD sweeps with the lines cut into chunks.
+//
+// One thread per line leaves only nx (or ny) threads on the whole GPU -- a third of the loads needed in flight to
+// keep HBM busy.  Both recurrences of `thomas` are contractions: f_i = (d_i + Fo f_{i-1})/temp_i and
+// x_i = f_i - e_i x_{i+1} forget their starting value at the rate m = lim e_i = ((1+2Fo) - sqrt(1+4Fo))/(2Fo) < 1 per
+// node.  A chunk therefore starts W nodes early from zero, W chosen so that m^W < 2^-70: the neglected coupling is far
+// below the last bit of the result, and `nchunk` threads can work on every line.  The passes go out of place
+// (forward src -> dst, backward dst -> src), because a chunk's warm-up reads nodes another chunk is producing.
+// The exact mode keeps the one-thread-per-line kernels above.
+// ---------------------------------------------------------------------------------------------------
+struct LodChunk {
+  int ch;        // nodes per chunk (multiple of 32)
+  int warm;      // warm-up nodes (multiple of 32)
+  const double* src;
+  double* dst;
+};
+
+// y-lines.  DIR 0: forward elimination bottom -> top, DIR 1: back substitution top -> bottom.
+template <int DIR>
+__global__ void __launch_bounds__(128, 8) k_lod_y_chunk(const LodParams P, const LodChunk C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P.nx) return;
+  const size_t nx = (size_t)P.nx;
+  const int ny = P.ny;
+  const int r0 = blockIdx.y * C.ch, r1 = min(ny, r0 + C.ch);       // own rows [r0, r1)
+  if (r0 >= ny) return;
+  const double* s = C.src + i;
+  double* d = C.dst + i;
+  const bool ident = (i == 0 || i == P.nx - 1);                     // Dirichlet columns: carried along unchanged
+  constexpr int U = 16;
+  if (DIR == 0) {
+    const int rs = max(0, r0 - C.warm);
+    double fprev = 0.0;
+    for (int j0 = rs; j0 < r1; j0 += U) {
+      double v[U];
+#pragma unroll
+      for (int r = 0; r < U; ++r) v[r] = (j0 + r < r1) ? s[(size_t)(j0 + r) * nx] : 0.0;
+#pragma unroll
+      for (int r = 0; r < U; ++r) {
+        const int j = j0 + r;
+        if (j < r1) {
+          const double f = (ident || j == 0 || j == ny - 1) ? v[r] : fma(P.foy, fprev, v[r]) * __ldg(P.ty + j);
+          if (j >= r0) d[(size_t)j * nx] = f;
+          fprev = f;
+        }
+      }
+    }
+  } else {
+    const int re = min(ny - 1, r1 - 1 + C.warm);                    // start above the chunk
+    double xnext = 0.0;
+    for (int j0 = re; j0 >= r0; j0 -= U) {
+      double v[U];
+#pragma unroll
+      for (int r = 0; r < U; ++r) v[r] = (j0 - r >= r0) ? s[(size_t)(j0 - r) * nx] : 0.0;
+#pragma unroll
+      for (int r = 0; r < U; ++r) {
+        const int j = j0 - r;
+        if (j >= r0) {
+          const double x = (ident || j == ny - 1) ? v[r] : fma(-__ldg(P.ey + j), xnext, v[r]);
+          if (j < r1) d[(size_t)j * nx] = x;
+          xnext = x;
+        }
+      }
+    }
+  }
+}
+
+// x-lines: a warp owns 32 rows and one chunk of columns, walking 32-column tiles transposed through shared memory.
+template <int DIR>
+__global__ void __launch_bounds__(128) k_lod_x_chunk(const LodParams P, const LodChunk C) {
+  __shared__ double tile[4][32][33];
+  const int lane = threadIdx.x, w = threadIdx.y;
+  const int row0 = (blockIdx.x * 4 + w) * 32;                       // rows 0 .. ny-1 (boundary rows are copied)
+  if (row0 >= P.ny) return;
+  const int nx = P.nx;
+  const size_t snx = (size_t)nx;
+  const int c_lo = blockIdx.y * C.ch, c_hi = min(nx, c_lo + C.ch);  // own columns [c_lo, c_hi)
+  if (c_lo >= nx) return;
+  const int myrow = row0 + lane;
+  const bool rowin = myrow < P.ny;
+  const bool solve = rowin && myrow >= 1 && myrow <= P.ny - 2;      // interior row: recurrence; boundary row: copy
+  double (*tl)[33] = tile[w];
+  double nxt[32];
+  auto fetch = [&](int c0) {
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      const int j = row0 + r;
+      nxt[r] = (j < P.ny && c0 + lane < nx) ? C.src[(size_t)j * snx + c0 + lane] : 0.0;
+    }
+  };
+  auto store = [&](int c0) {
+    for (int r = 0; r < 32; ++r) {
+      const int j = row0 + r;
+      if (j < P.ny && c0 + lane < c_hi) C.dst[(size_t)j * snx + c0 + lane] = tl[r][lane];
+    }
+  };
+  if (DIR == 0) {
+    const int cs = max(0, c_lo - C.warm);
+    double fprev = 0.0;
+    fetch(cs);
+    for (int c0 = cs; c0 < c_hi; c0 += 32) {
+#pragma unroll
+      for (int r = 0; r < 32; ++r) tl[r][lane] = nxt[r];
+      __syncwarp();
+      if (c0 + 32 < c_hi) fetch(c0 + 32);
+      if (solve) {
+        for (int k = 0; k < 32 && c0 + k < c_hi; ++k) {
+          const int i = c0 + k;
+          double dd = tl[lane][k], f;
+          if (i == 0 || i == nx - 1) {
+            f = dd;
+          } else {
+            const double xi = __dadd_rn(P.xa, __dmul_rn((double)i, P.dx));
+            dd += (xi < P.qthr) ? P.qdt : 0.0;
+            f = fma(P.fox, fprev, dd) * __ldg(P.tx + i);
+          }
+          tl[lane][k] = f;
+          fprev = f;
+        }
+      }
+      __syncwarp();
+      if (c0 >= c_lo) store(c0);
+      __syncwarp();
+    }
+  } else {
+    const int ce = min(((nx + 31) / 32) * 32, c_hi + C.warm);       // tile-aligned start to the right of the chunk
+    double xnext = 0.0;
+    fetch(ce - 32);
+    for (int c0 = ce - 32; c0 >= c_lo; c0 -= 32) {
+#pragma unroll
+      for (int r = 0; r < 32; ++r) tl[r][lane] = nxt[r];
+      __syncwarp();
+      if (c0 - 32 >= c_lo) fetch(c0 - 32);
+      if (solve) {
+        for (int k = 31; k >= 0; --k) {
+          const int i = c0 + k;
+          if (i >= nx) continue;
+          const double f = tl[lane][k];
+          const double x = (i == nx - 1) ? f : fma(-__ldg(P.ex + i), xnext, f);
+          tl[lane][k] = x;
+          xnext = x;
+        }
+      }
+      __syncwarp();
+      if (c0 < c_hi) store(c0);
+      __syncwarp();
+    }
+  }
+}
+
 }  // namespace cfd
 
 using namespace cfd;
@@ -461,11 +613,45 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   P.qdt = g.dt * g.qval / g.rho / g.cp;
   P.t = h->buf[h->cur];
   const int nmax = nx > ny ? nx : ny;
+  // chunked production sweeps: warm-up length from the contraction rate of the recurrences (see k_lod_y_chunk)
+  // `slots` = blocks of the sweep kernel resident on the GPU at once: every block lives as long as the kernel, so
+  // the grid should fit in one wave (a second, partial wave would double the time)
+  static int num_sms = 0;
+  if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, h->device));
+  auto plan = [](int n, int nlines, int slots, double fo, LodChunk& c) {
+    const double m = fo > 0 ? ((1.0 + 2.0 * fo) - sqrt(1.0 + 4.0 * fo)) / (2.0 * fo) : 0.0;
+    int warm = (m > 0 && m < 1) ? (int)ceil(70.0 * log(2.0) / -log(m)) : 1;
+    warm = ((warm + 31) / 32) * 32;
+    const int line_blocks = (nlines + 127) / 128;
+    int nch = slots / line_blocks;
+    if (nch > 16) nch = 16;
+    if (nch < 1) nch = 1;
+    while (nch > 1 && (n / nch < 4 * warm || n / nch < 256)) --nch;
+    c.ch = (((n + nch - 1) / nch + 31) / 32) * 32;
+    c.warm = warm;
+    return nch;
+  };
+  LodChunk cx{}, cy{};
+  const int ncx = plan(nx, ny, num_sms * 4, P.fox, cx), ncy = plan(ny, nx, num_sms * 8, P.foy, cy);
+  const bool chunked = !exact && (ncx > 1 || ncy > 1);
   for (int n = 0; n < nsteps; ++n) {
     k_lod_bc<<<(nmax + 127) / 128, 128, 0, h->stream>>>(P);
     if (exact) {
       k_lod_x<true><<<(ny - 2 + 127) / 128, dim3(32, 4), 0, h->stream>>>(P);
       k_lod_y<true><<<(nx - 2 + 127) / 128, 128, 0, h->stream>>>(P);
+    } else if (chunked) {
+      // forward / backward, out of place: cur -> other -> cur for x, then the same for y; the result is in cur
+      double* A = h->buf[h->cur];
+      double* B = h->buf[h->cur ^ 1];
+      const dim3 gx((ny + 127) / 128, (nx + cx.ch - 1) / cx.ch), gy((nx + 127) / 128, (ny + cy.ch - 1) / cy.ch);
+      cx.src = A; cx.dst = B;
+      k_lod_x_chunk<0><<<gx, dim3(32, 4), 0, h->stream>>>(P, cx);
+      cx.src = B; cx.dst = A;
+      k_lod_x_chunk<1><<<gx, dim3(32, 4), 0, h->stream>>>(P, cx);
+      cy.src = A; cy.dst = B;
+      k_lod_y_chunk<0><<<gy, 128, 0, h->stream>>>(P, cy);
+      cy.src = B; cy.dst = A;
+      k_lod_y_chunk<1><<<gy, 128, 0, h->stream>>>(P, cy);
     } else {
       k_lod_x<false><<<(ny - 2 + 127) / 128, dim3(32, 4), 0, h->stream>>>(P);
       k_lod_y<false><<<(nx - 2 + 127) / 128, 128, 0, h->stream>>>(P);

@@ -94,6 +94,32 @@ def test_implicit_lod_bitwise(cfd, oracle, shape):
     h.close()
 
 
+@pytest.mark.parametrize("shape,fo", [((2100, 1300), 5.0), ((1030, 4100), 0.7), ((4100, 1030), 20.0)])
+def test_implicit_lod_chunked_lines_match_the_serial_solve(cfd, oracle, shape, fo):
+    """Grids large enough for the production sweeps to cut the lines into chunks (each warming up over the
+    contraction length of the Thomas recurrences): same result as the one-thread-per-line exact mode, which is
+    bit-identical with the oracle, to rounding."""
+    nx, ny = shape
+    t0 = noise(nx, ny, 11) * 100.0
+    kw = dict(fo=fo, tleft=1.0, tright=2.0, tbottom=3.0, ttop=4.0)
+    a, b = cfd.Heat2D(nx, ny, **kw), cfd.Heat2D(nx, ny, **kw)
+    a.upload(t0)
+    b.upload(t0)
+    for k in range(3):
+        a.implicit_step(1, exact=True)
+        b.implicit_step(1)
+        ta, tb = a.download(), b.download()
+        assert np.abs(ta - tb).max() <= 1e-12 * np.abs(ta).max(), k
+        b.upload(ta)
+    want = oracle.heat2d_lod(t0, 1, dt=a.dt, tbc=(1.0, 2.0, 3.0, 4.0)) if nx * ny < 3_000_000 else None
+    if want is not None:
+        a.upload(t0)
+        a.implicit_step(1, exact=True)
+        assert np.array_equal(a.download(), want)
+    a.close()
+    b.close()
+
+
 def test_implicit_lod_large_time_step_is_stable(cfd):
     """Fo = 50 (250 x the explicit limit): bounded, monotone approach to the steady state."""
     n = 1026
