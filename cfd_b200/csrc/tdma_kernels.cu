@@ -245,7 +245,10 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
     // ---------------- producer warp: one elected thread issues the bulk copies -------------------------
     if (tid == T) {
       const unsigned slice_bytes = (unsigned)(T * sizeof(double));
-      const unsigned tx = slice_bytes * ((unsigned)nc + (zeroE ? 0u : 1u) + (zeroW ? 0u : 1u));
+      // spike vectors need the matrix only: an, as (and ap) are the first arrays of every slice
+      const unsigned nmat = nc == 6 ? 3u : 2u;
+      const unsigned tx = P.basis ? slice_bytes * nmat
+                                  : slice_bytes * ((unsigned)nc + (zeroE ? 0u : 1u) + (zeroW ? 0u : 1u));
       unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
       for (int line = blockIdx.x; line < P.nlines; line += gridDim.x) {
         const long long i0 = P.i_first + (long long)line * P.i_step;
@@ -259,9 +262,13 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
           const unsigned fb = full0 + 8 * s;
           const unsigned dst = smem_u32(ring + (size_t)s * SW);
           mbar_expect_tx(fb, tx);
-          tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, nc * slice_bytes, fb);
-          if (!zeroE) tma_load_1d(dst + nc * slice_bytes, esrc + (size_t)k * T, slice_bytes, fb);
-          if (!zeroW) tma_load_1d(dst + (nc + 1) * slice_bytes, wsrc + (size_t)k * T, slice_bytes, fb);
+          if (P.basis) {
+            tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, nmat * slice_bytes, fb);
+          } else {
+            tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, nc * slice_bytes, fb);
+            if (!zeroE) tma_load_1d(dst + nc * slice_bytes, esrc + (size_t)k * T, slice_bytes, fb);
+            if (!zeroW) tma_load_1d(dst + (nc + 1) * slice_bytes, wsrc + (size_t)k * T, slice_bytes, fb);
+          }
         }
       }
     }
@@ -318,13 +325,15 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_tma(const SweepParams P, const
         d = lds_f64(sr);
         sr += T8;
       }
-      double c = lds_f64(sr + 2 * T8);
-      if (!zeroW) c = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), c);
-      if (!zeroE) c = fma(lds_f64(sr), lds_f64(sr + 3 * T8), c);
+      double c = 0.0;
+      if (!P.basis) {
+        c = lds_f64(sr + 2 * T8);
+        if (!zeroW) c = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), c);
+        if (!zeroE) c = fma(lds_f64(sr), lds_f64(sr + 3 * T8), c);
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty0 + 8 * s);
       const int j0 = j0base + k;
-      if (P.basis) c = 0.0;
       if (!(j0 >= P.jlo && j0 <= P.jhi)) {
         a = 0.0;
         b = 0.0;

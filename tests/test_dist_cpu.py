@@ -99,3 +99,70 @@ def test_colour_filter_sender_receiver_agree():
                     fa, fb = colour_filter(alo, ahi, istart, colour), colour_filter(blo, bhi, istart, colour)
                     assert fa[3] == fb[0]      # a's last line changed  <=>  b's west halo is stale
                     assert fa[1] == fb[2]      # a's east halo is stale <=>  b's first line changed
+
+
+def test_jslab_extent_and_line_counts():
+    from cfd_b200.dist import JHALO_N, JHALO_S, _nlines, jslab_extent
+    nj, world = 130, 4
+    for r in range(world):
+        joff, nloc, hs, hn = jslab_extent(nj, world, r)
+        lo, hi = partition(nj, world)[r]
+        assert hs == (0 if r == 0 else JHALO_S) and hn == (0 if r == world - 1 else JHALO_N)
+        assert joff == lo - 1 - hs and nloc == hi - lo + 1 + hs + hn
+    with pytest.raises(ValueError):
+        jslab_extent(9, 4, 1)
+    # lines istart..ni-1 of one colour: the count every rank must agree on for the all-gathered buffers
+    for ni in (12, 13, 4098):
+        for istart in (2, 3):
+            assert _nlines(ni, istart, 0) + _nlines(ni, istart, 1) == ni - istart
+            assert _nlines(ni, istart, 0) == len([i for i in range(istart, ni) if (i - istart) % 2 == 0])
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_partition_method_algebra(world):
+    """The reduced system the j-slab driver all-gathers (dist.py / jslab_kernels.cu), in numpy on one line:
+    piece solutions y with zero cut ends, spike vectors w, z, 2*world interface unknowns, x = y + w*x_s + z*x_n."""
+    rng = np.random.default_rng(world)
+    n = 8 * world + 5
+    an, as_ = rng.random(n) * 0.4, rng.random(n) * 0.4          # x_j = an x_{j+1} + as x_{j-1} + c   (ap = 1)
+    c = rng.random(n)
+    bs, bn = 0.7, -0.3                                          # Dirichlet values below / above the line
+
+    def solve(lo, hi, rhs, xs, xn):                             # unknowns lo..hi-1 with end values xs, xn
+        m = hi - lo
+        A = np.eye(m)
+        b = rhs[lo:hi].copy()
+        for k in range(m):
+            j = lo + k
+            if k > 0:
+                A[k, k - 1] = -as_[j]
+            else:
+                b[k] += as_[j] * xs
+            if k < m - 1:
+                A[k, k + 1] = -an[j]
+            else:
+                b[k] += an[j] * xn
+        return np.linalg.solve(A, b)
+
+    want = solve(0, n, c, bs, bn)
+    cuts = [p[0] - 1 for p in partition(n, world)] + [n]
+    zero = np.zeros(n)
+    Y, W, Z = [], [], []
+    for r in range(world):
+        lo, hi = cuts[r], cuts[r + 1]
+        Y.append(solve(lo, hi, c, bs if r == 0 else 0.0, bn if r == world - 1 else 0.0))
+        W.append(solve(lo, hi, zero, 1.0, 0.0))
+        Z.append(solve(lo, hi, zero, 0.0, 1.0))
+    N = 2 * world
+    A, b = np.eye(N), np.zeros(N)
+    for r in range(world):
+        lo_, hi_ = 2 * r, 2 * r + 1
+        if r > 0:
+            A[lo_, hi_ - 2], A[hi_, hi_ - 2] = -W[r][0], -W[r][-1]
+        if r < world - 1:
+            A[lo_, lo_ + 2], A[hi_, lo_ + 2] = -Z[r][0], -Z[r][-1]
+        b[lo_], b[hi_] = Y[r][0], Y[r][-1]
+    x = np.linalg.solve(A, b)
+    got = np.concatenate([Y[r] + (W[r] * x[2 * (r - 1) + 1] if r > 0 else 0.0) + (Z[r] * x[2 * (r + 1)] if r < world - 1 else 0.0)
+                          for r in range(world)])
+    assert np.abs(got - want).max() < 1e-13
