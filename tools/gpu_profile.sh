@@ -10,6 +10,6 @@ $CMD > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
 $CMD > gpurun_out/plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'k_tdma_tma|k_assemble_u|k_assemble_v|k_assemble_p|k_correct' -s 30 -c 30 -f -o gpurun_out/prof_r01 $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'k_tdma_tma|k_assemble_u|k_assemble_v|k_assemble_p|k_correct' -s 30 -c 14 -f -o gpurun_out/prof_r01 $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
 ls -la gpurun_out
