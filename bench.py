@@ -3,7 +3,7 @@
 (Re=1000, 4096^2 control volumes per GPU, red/black line TDMA), reported as cell-updates/s (GLUPS) and
 iterations/s, with the HBM roofline of the dominant kernel and a CPU baseline beside it.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat|step]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat|step|cavity16k]
 
 A "step" is one pass of the hot path: calcu + calcv + calcp (cavity_fvm.f90:554-557) over the whole grid.
 For N>1 launch with torch.distributed.run (one rank per GPU); the grid is slab-decomposed along i (weak scaling:
@@ -438,6 +438,83 @@ def run_heat(args):
     emit(out)
 
 
+def run_cavity16k(args):
+    """--workload cavity16k: north_star's "8 GPUs on 16384^2" case, STRONG scaling.  A line of 16386 nodes does not fit
+    one thread block's registers, so the lines are cut along j and solved with the partition method (j-slabs): N ranks
+    each hold 16384/N rows of every line.  N = 1 runs the same algorithm with two slabs on the one GPU."""
+    import torch
+    import torch.distributed as dist
+
+    from cfd_b200.dist import JSlabCavity, LocalJSlabCavity
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    K, W = args.steps, args.warmup
+    hbm_peak, peak_src = peaks()
+    NG = 16384
+    stream = torch.cuda.current_stream()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        solver = JSlabCavity(NG, NG, reynolds=REYNOLDS)
+        step, ctx0 = solver.iterate_async, solver.ctx
+    else:
+        solver = LocalJSlabCavity(NG, NG, 2, reynolds=REYNOLDS)
+        step, ctx0 = (lambda n: [solver._iterate_once() for _ in range(n)]), solver.slabs[0].ctx
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(W):
+        step(1)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx0.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(K):
+        step(1)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = (ctx0.launches - l0) * (2 if world == 1 else 1)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+        res = solver.residuals()
+    else:
+        res = tuple(sum(s.res.clone() for s in solver.slabs).cpu().tolist())
+    glups = NG * NG * K / (ms * 1e-3) / 1e9
+    out = {"metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K,
+           "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic", "iters_per_s": K / (ms * 1e-3),
+           "config": {"workload": f"lid-driven cavity FVM SIMPLE Re=1000, {NG}x{NG} CV in total, hybrid scheme, urf .5/.5/.8, "
+                                  "nswp 3/3/3, red/black lines cut along j (partitioned Thomas)",
+                      "parallelism": (f"j-slabs x{world}: piece solves + spike vectors, all-gathered reduced system per line "
+                                      "(NCCL), halo rows once per iteration" if world > 1 else
+                                      "single GPU, two j-slabs in one process (same algorithm, copies instead of messages)"),
+                      "l2": "inputs larger than L2; no explicit flush", "line_layout": ctx0.layout},
+           "residuals_last": [float(x) for x in res[:3]], "gpu_launches": int(launches),
+           "roofline": {"bound": "hbm", "kernel": "whole outer iteration", "achieved": BYTES_PER_CELL_ITER * glups / world,
+                        "peak": hbm_peak, "unit": "GB/s", "frac": BYTES_PER_CELL_ITER * glups / world / hbm_peak,
+                        "peak_source": peak_src, "traffic": None,
+                        "note": "algorithmic bytes of the single-context algorithm (928 B/cell); the partition method moves more"},
+           "e2e": None, "clocks": clocks}
+    if rank == 0:
+        emit(out)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_step(args):
     """--workload step: BASELINE.json configs[4], TEACH backward-step SIMPLE (laminar, nswp 3/3/5) on 16384 x 4096,
     i-slabs over the N GPUs (STRONG scaling: the global grid is fixed).  One step = one outer iteration."""
@@ -545,7 +622,7 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step"])
+    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step", "cavity16k"])
     ap.add_argument("--slabs", default="i", choices=["i", "j"], help="N>1 cavity: cut along i (whole lines per GPU) or j")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
@@ -557,6 +634,8 @@ def main():
         run_heat(args)
     elif args.workload == "step":
         run_step(args)
+    elif args.workload == "cavity16k":
+        run_cavity16k(args)
     else:
         run_ours(args)
 

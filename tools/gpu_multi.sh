@@ -18,3 +18,4 @@ run cavity_i --steps 200 --warmup 10
 run cavity_j --slabs j --steps 100 --warmup 10
 run step --workload step --steps 50 --warmup 5
 run heat --workload heat --steps 100 --warmup 10
+run cavity16k --workload cavity16k --steps 20 --warmup 3
