@@ -16,6 +16,14 @@ module cfd_b200_c
     integer(c_int) :: solve_flow, solve_t            ! general family: lsolve(1), lsolve(4)
     integer(c_int) :: indcos, istep, jstep           ! TEACH family (control.f90:16,66,67)
     real(c_double) :: viscos, flowin, great          ! TEACH family (control.f90:15,126,197-203)
+    integer(c_int) :: joff, nj_global, halo_s, halo_n ! j-slab description (lines cut across contexts)
+    real(c_double) :: sns_njm1
+    integer(c_int) :: raw_coefficients               ! 1: keep ae..su as stored by the reference (cfd_lin_*)
+  end type
+  type, bind(c) :: cfd_turbulence                    ! literals of contro (control.f90:105-141)
+    real(c_double) :: cmu, cd, c1, c2, cappa, elog, pred, prte, prandl, prandt, pfun, twalln
+    real(c_double) :: urfk, urfe, urft, urfvis
+    integer(c_int) :: nswpk, nswpd, nswpt, incalk, incald, incalt, inpro
   end type
   interface
     integer(c_int) function cfd_create(ctx, cfg) bind(c, name='cfd_create')
@@ -50,6 +58,30 @@ module cfd_b200_c
     end function
     integer(c_int) function cfd_iterate(ctx, n, res) bind(c, name='cfd_iterate')
       import; type(c_ptr), value :: ctx; integer(c_int), value :: n; real(c_double) :: res(8)
+    end function
+    ! general family: calct (buoyancy_cav.f90:358-433); TEACH family after cfd_set_turbulence: calct / calcte / calced / props
+    integer(c_int) function cfd_calct(ctx, res) bind(c, name='cfd_calct')
+      import; type(c_ptr), value :: ctx; real(c_double) :: res
+    end function
+    integer(c_int) function cfd_set_turbulence(ctx, model) bind(c, name='cfd_set_turbulence')
+      import; type(c_ptr), value :: ctx; type(cfd_turbulence) :: model
+    end function
+    integer(c_int) function cfd_calcte(ctx, res) bind(c, name='cfd_calcte')
+      import; type(c_ptr), value :: ctx; real(c_double) :: res
+    end function
+    integer(c_int) function cfd_calced(ctx, res) bind(c, name='cfd_calced')
+      import; type(c_ptr), value :: ctx; real(c_double) :: res
+    end function
+    integer(c_int) function cfd_props(ctx) bind(c, name='cfd_props')
+      import; type(c_ptr), value :: ctx
+    end function
+    integer(c_int) function cfd_wall_download(ctx, which, a, n) bind(c, name='cfd_wall_download')
+      import; type(c_ptr), value :: ctx; integer(c_int), value :: which, n; real(c_double) :: a(*)
+    end function
+    ! scalar-transport demos: tdma_we / tdma_sn / tdma_solver on uploaded coefficients
+    integer(c_int) function cfd_lin_solve(ctx, field, dir, variant, maxit, tol, iters, rsm) bind(c, name='cfd_lin_solve')
+      import; type(c_ptr), value :: ctx; integer(c_int), value :: field, dir, variant, maxit
+      real(c_double), value :: tol; integer(c_int) :: iters; real(c_double) :: rsm
     end function
   end interface
 end module
