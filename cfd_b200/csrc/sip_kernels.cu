@@ -37,7 +37,7 @@ struct SipParams {
 };
 
 #define SIP_W 4              // warps (bands) per block
-#define TS 33                // padded tile stride
+#define TS 34                // padded tile stride: the anti-diagonal (lane l at row l, column d-l) sits at 33*l + d -> 32 different banks
 
 __device__ __forceinline__ unsigned long long ld_acquire(const unsigned long long* p) {
   unsigned long long v;
@@ -63,9 +63,19 @@ __device__ __forceinline__ bool wait_band(const SipParams& P, int b, unsigned lo
 
 // load / store one 32x32 tile (rows jb..jb+31, columns c0..c0+31, 0-based) as coalesced row segments
 __device__ __forceinline__ void tile_load(double* tl, const double* g, int ld, int c0, int jb, int imax, int jmax, int lane) {
-  for (int r = 0; r < 32; ++r) {
-    const int i = c0 + lane, j = jb + r;
-    tl[r * TS + lane] = (i >= 1 && i <= imax && j >= 1 && j <= jmax) ? g[(size_t)j * ld + i] : 0.0;
+  // sixteen row segments in flight per lane before the first one is needed (a rolled loop would wait for every load)
+  const int i = c0 + lane;
+  const bool iok = i >= 1 && i <= imax;
+#pragma unroll
+  for (int r0 = 0; r0 < 32; r0 += 16) {
+    double v[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const int j = jb + r0 + r;
+      v[r] = (iok && j >= 1 && j <= jmax) ? __ldcg(g + (size_t)j * ld + i) : 0.0;
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) tl[(r0 + r) * TS + lane] = v[r];
   }
 }
 __device__ __forceinline__ void tile_store(const double* tl, double* g, int ld, int c0, int jb, int imax, int jmax, int lane) {
@@ -93,6 +103,18 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
     for (int cc = 0; cc < nchunks; ++cc) {
       const int c = fwd ? cc : nchunks - 1 - cc;
       const int c0 = 1 + 32 * c;
+      // the tile's own operands do not depend on the neighbouring band: fetch them before waiting for it
+      if (PHASE == 1) {
+        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(B, P.ls, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(C, P.lw, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(D, P.lpr, P.ld, c0, jb, imax, jmax, lane);
+      } else if (PHASE == 2) {
+        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(B, P.un, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(C, P.ue, P.ld, c0, jb, imax, jmax, lane);
+        tile_load(D, P.phi, P.ld, c0, jb, imax, jmax, lane);
+      }
       if (bb > 0) {                                     // the band processed just before this one (other warp/block)
         const int dep = fwd ? b - 1 : b + 1;
         if (!wait_band(P, dep, epoch_base + (unsigned long long)cc + 1)) return;
@@ -107,17 +129,6 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
         } else {
           row0[lane] = ok ? P.res[(size_t)jn * P.ld + i] : 0.0;
         }
-      }
-      if (PHASE == 1) {
-        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(B, P.ls, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(C, P.lw, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(D, P.lpr, P.ld, c0, jb, imax, jmax, lane);
-      } else if (PHASE == 2) {
-        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(B, P.un, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(C, P.ue, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(D, P.phi, P.ld, c0, jb, imax, jmax, lane);
       }
       __syncwarp();
       for (int d = 0; d < 63; ++d) {
@@ -198,20 +209,32 @@ __global__ void __launch_bounds__(32 * SIP_W) k_sip_solve(const SipParams P) {
   for (iter = 1; iter <= P.maxit; ++iter) {
     // ---- residual (:61-63) and its 1-norm, fixed-order reduction
     double acc = 0.0;
-    const long long ncell = (long long)imax * jmax;
-    for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < ncell; n += (long long)gridDim.x * blockDim.x) {
-      const int i = 1 + (int)(n % imax), j = 1 + (int)(n / imax);
-      const size_t k = (size_t)j * P.ld + i;
-      const double caw = P.awp ? P.sign * P.awp[k] : P.aw, cae = P.aep ? P.sign * P.aep[k] : P.ae;
-      const double can = P.anp ? P.sign * P.anp[k] : P.an, cas = P.asp ? P.sign * P.asp[k] : P.as;
-      const double cap = P.app ? P.app[k] : P.ap;
-      double r = __dsub_rn(P.su[k], __dmul_rn(caw, P.phi[k - 1]));
-      r = __dsub_rn(r, __dmul_rn(cae, P.phi[k + 1]));
-      r = __dsub_rn(r, __dmul_rn(can, P.phi[k + P.ld]));
-      r = __dsub_rn(r, __dmul_rn(cas, P.phi[k - P.ld]));
-      r = __dsub_rn(r, __dmul_rn(cap, P.phi[k]));
-      P.res[k] = r;
-      acc += fabs(r);
+    // rows are dealt to the warps of the whole grid, a warp reads 256-byte row segments, four per lane in flight
+    {
+      const int lane = threadIdx.x & 31;
+      const int gw = blockIdx.x * SIP_W + (threadIdx.x >> 5), nw = gridDim.x * SIP_W;
+      for (int j = 1 + gw; j <= jmax; j += nw) {
+        const size_t row = (size_t)j * P.ld;
+        for (int i0 = 1; i0 <= imax; i0 += 128) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int i = i0 + 32 * u + lane;
+            if (i <= imax) {
+              const size_t k = row + i;
+              const double caw = P.awp ? P.sign * P.awp[k] : P.aw, cae = P.aep ? P.sign * P.aep[k] : P.ae;
+              const double can = P.anp ? P.sign * P.anp[k] : P.an, cas = P.asp ? P.sign * P.asp[k] : P.as;
+              const double cap = P.app ? P.app[k] : P.ap;
+              double r = __dsub_rn(P.su[k], __dmul_rn(caw, P.phi[k - 1]));
+              r = __dsub_rn(r, __dmul_rn(cae, P.phi[k + 1]));
+              r = __dsub_rn(r, __dmul_rn(can, P.phi[k + P.ld]));
+              r = __dsub_rn(r, __dmul_rn(cas, P.phi[k - P.ld]));
+              r = __dsub_rn(r, __dmul_rn(cap, P.phi[k]));
+              P.res[k] = r;
+              acc += fabs(r);
+            }
+          }
+        }
+      }
     }
     {
       __shared__ double wsum[SIP_W];
@@ -272,8 +295,9 @@ int cfd_launch_sip(int device, cudaStream_t stream, int ld, int nrows, int imax,
   int per_sm = 0, nsm = 0;
   CFD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sip_solve, 32 * SIP_W, smem));
   CFD_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
-  int grid = (nbands + SIP_W - 1) / SIP_W;
-  if (grid > per_sm * nsm) grid = per_sm * nsm;
+  // every SM takes part (the residual phase is a plain streaming pass); bands beyond nbands simply do not exist
+  int grid = per_sm * nsm;
+  (void)nbands;
   if (grid > max_partials) grid = max_partials;
   if (grid < 1) grid = 1;
   CFD_CUDA(cudaMemsetAsync(work, 0, 6 * n * sizeof(double), stream));
