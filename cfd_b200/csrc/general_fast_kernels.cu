@@ -555,9 +555,8 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_t_fast(const GenFastPar
         racc += fabs(reseq);
         AP = AP * r_urf;
         SU = fma(omu * AP, t_c, SU);
-        double rAPout;
+        [[maybe_unused]] double rAPout;
         GEN_STORE(AE, AW, AN, AS, SU, AP)
-        (void)rAPout;
       }
       aS = acofN + gf_max(0.0, flowN);
       D_m = D_c; D_c = D_p;

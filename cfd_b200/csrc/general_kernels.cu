@@ -10,8 +10,9 @@
 // p' source in the reference's order ((src + south) + west) - east - north.  Compiled with -fmad=false; all
 // arithmetic follows the reference's operation order (bit-comparable with oracle/general_oracle.c).
 //
-// Thread mapping as in cavity_kernels.cu (one thread = M consecutive nodes of one line).  This first version
-// addresses neighbours through the layout function instead of register windows: correct first, tuned later.
+// Thread mapping as in cavity_kernels.cu (one thread = M consecutive nodes of one line).  Neighbours are addressed
+// through LinePos (adds / selects relative to the thread's chunk, linepos.cuh); the production path with register
+// windows is general_fast_kernels.cu.
 #include "common.cuh"
 #include "linepos.cuh"
 

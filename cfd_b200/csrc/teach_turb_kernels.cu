@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) k_teach_props(const TurbParams P) {
 // EQ: CFD_EQ_TE, CFD_EQ_ED, CFD_EQ_T
 template <int EQ>
 __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
-  const int M = P.L.M, T = P.L.T, ni = P.L.ni, nj = P.L.nj, nim1 = ni - 1, njm1 = nj - 1;
+  const int M = P.L.M, T = P.L.T, ni = P.L.ni, nj = P.L.nj, njm1 = nj - 1;
   const long long LD = P.L.LD;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int i0 = 1 + blockIdx.y * blockDim.y + threadIdx.y;
