@@ -13,7 +13,6 @@
 // library, so agreement with oracle/teach_turb.inc is to rounding, not bitwise.  Works for both coefficient
 // storages (nc = 6 raw, nc = 5 divided by ap).
 #include "common.cuh"
-#include "linepos.cuh"
 
 namespace cfd {
 
@@ -34,14 +33,18 @@ struct TurbParams {
 
 __device__ __forceinline__ double tq_max(double a, double b) { return a > b ? a : b; }
 
-struct TQ {   // 1-based (i,j) access into a line-layout field
-  const double* p;
-  long long LD;
-  LinePos lp;
-  __device__ __forceinline__ double operator()(int i, int j) const { return __ldg(p + (long long)(i - 1) * LD + lp(j - 1)); }
-};
 #define Q1(a, i) __ldg((a) + (i) - 1)
-#define QJ(a, j) __ldg((a) + lp((j) - 1))
+
+// field access relative to the current cell: at<DI, DJ>() = f(i+DI, j+DJ), DI, DJ in {-1, 0, 1}
+struct RelQ {
+  const double* c;      // start of line i
+  long long LD;
+  int qm, qc, qp;       // positions of rows j-1, j, j+1 inside a line
+  template <int DI, int DJ>
+  __device__ __forceinline__ double at() const {
+    return __ldg(c + DI * LD + (DJ < 0 ? qm : (DJ > 0 ? qp : qc)));
+  }
+};
 
 __device__ __forceinline__ void tq_block_sum(double v, double* partial) {
   __shared__ double wsum[32];
@@ -142,35 +145,38 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
   const int i0 = 1 + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= ni - 2) {
-    const LinePos lp(M, T, t);
     const int i = i0 + 1, jstp1 = P.jstep + 1, istep = P.istep;
     double* phi_w = EQ == CFD_EQ_TE ? P.te : (EQ == CFD_EQ_ED ? P.ed : P.t);
-    const TQ U{P.u, LD, lp}, V{P.v, LD, lp}, D{P.den, LD, lp}, S{P.vis, LD, lp}, TE{P.te, LD, lp}, PHI{phi_w, LD, lp};
-    const TQ GM{EQ == CFD_EQ_T ? P.gamh : P.vis, LD, lp};
+    const long long oline = (long long)i0 * LD;
     const double pr = EQ == CFD_EQ_TE ? P.m.prte : P.m.pred;
     const double cdterm = pow(P.m.cmu, 0.25), cmu75 = pow(P.m.cmu, .75);
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < 1 || j0 > nj - 2) continue;
+      // positions of rows j-1, j, j+1 in the line; every access below is base + {-LD, 0, +LD} + one of them
+      const int qc = k * T + t, qp = (k + 1 < M) ? qc + T : t + 1, qm = (k > 0) ? qc - T : (M - 1) * T + t - 1;
+      const RelQ U{P.u + oline, LD, qm, qc, qp}, V{P.v + oline, LD, qm, qc, qp}, D{P.den + oline, LD, qm, qc, qp};
+      const RelQ S{P.vis + oline, LD, qm, qc, qp}, TE{P.te + oline, LD, qm, qc, qp}, PHI{phi_w + oline, LD, qm, qc, qp};
+      const RelQ GM{(EQ == CFD_EQ_T ? P.gamh : P.vis) + oline, LD, qm, qc, qp};
       // ---- chapter 1 (calc.f90:321-352 / 402-425 / 503-526)
-      const double arean = QJ(P.rv, j + 1) * Q1(P.sew, i);
-      const double areas = QJ(P.rv, j) * Q1(P.sew, i);
-      const double areaew = QJ(P.r, j) * QJ(P.sns, j);
-      double vol = QJ(P.r, j) * QJ(P.sns, j) * Q1(P.sew, i);
-      const double gn = 0.5 * (D(i, j) + D(i, j + 1)) * V(i, j + 1);
-      const double gs = 0.5 * (D(i, j) + D(i, j - 1)) * V(i, j);
-      const double ge = 0.5 * (D(i, j) + D(i + 1, j)) * U(i + 1, j);
-      const double gw = 0.5 * (D(i, j) + D(i - 1, j)) * U(i, j);
+      const double arean = __ldg(P.rv + qp) * Q1(P.sew, i);
+      const double areas = __ldg(P.rv + qc) * Q1(P.sew, i);
+      const double areaew = __ldg(P.r + qc) * __ldg(P.sns + qc);
+      double vol = __ldg(P.r + qc) * __ldg(P.sns + qc) * Q1(P.sew, i);
+      const double gn = 0.5 * (D.at<0, 0>() + D.at<0, 1>()) * V.at<0, 1>();
+      const double gs = 0.5 * (D.at<0, 0>() + D.at<0, -1>()) * V.at<0, 0>();
+      const double ge = 0.5 * (D.at<0, 0>() + D.at<1, 0>()) * U.at<1, 0>();
+      const double gw = 0.5 * (D.at<0, 0>() + D.at<-1, 0>()) * U.at<0, 0>();
       const double cn = gn * arean, cs = gs * areas, ce = ge * areaew, cw = gw * areaew;
-      double gamn = 0.5 * (GM(i, j) + GM(i, j + 1));
-      double gams = 0.5 * (GM(i, j) + GM(i, j - 1));
-      double game = 0.5 * (GM(i, j) + GM(i + 1, j));
-      double gamw = 0.5 * (GM(i, j) + GM(i - 1, j));
+      double gamn = 0.5 * (GM.at<0, 0>() + GM.at<0, 1>());
+      double gams = 0.5 * (GM.at<0, 0>() + GM.at<0, -1>());
+      double game = 0.5 * (GM.at<0, 0>() + GM.at<1, 0>());
+      double gamw = 0.5 * (GM.at<0, 0>() + GM.at<-1, 0>());
       if (EQ != CFD_EQ_T) {
         gamn = gamn / pr; gams = gams / pr; game = game / pr; gamw = gamw / pr;
       }
-      const double dn = gamn * arean / QJ(P.dynp, j);
-      const double ds = gams * areas / QJ(P.dyps, j);
+      const double dn = gamn * arean / __ldg(P.dynp + qc);
+      const double ds = gams * areas / __ldg(P.dyps + qc);
       const double de = game * areaew / Q1(P.dxep, i);
       const double dw = gamw * areaew / Q1(P.dxpw, i);
       const double smp = cn - cs + ce - cw;
@@ -180,25 +186,25 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
       double AS = tq_max(fabs(0.5 * cs), ds) + 0.5 * cs;
       double AE = tq_max(fabs(0.5 * ce), de) - 0.5 * ce;
       double AW = tq_max(fabs(0.5 * cw), dw) + 0.5 * cw;
-      const double phi_c = PHI(i, j);
+      const double phi_c = PHI.at<0, 0>();
       double SU = cpo * phi_c;
       double SP = -cp;
-      double phi_s = PHI(i, j - 1);
+      double phi_s = PHI.at<0, -1>();
       const long long oq = (long long)i0 * LD + k * T + t;
       if (EQ == CFD_EQ_TE) {
         // velocity gradients at the cell centre (calc.f90:430-436; the same expressions in promod.f90:199-200, 227-228)
-        const double dudx = (U(i + 1, j) - U(i, j)) / Q1(P.sew, i);
-        const double dvdy = (V(i, j + 1) - V(i, j)) / QJ(P.sns, j);
-        const double dudy = ((U(i, j) + U(i + 1, j) + U(i, j + 1) + U(i + 1, j + 1)) / 4.
-                             - (U(i, j) + U(i + 1, j) + U(i, j - 1) + U(i + 1, j - 1)) / 4.) / QJ(P.sns, j);
-        const double dvdx = ((V(i, j) + V(i, j + 1) + V(i + 1, j) + V(i + 1, j + 1)) / 4.
-                             - (V(i, j) + V(i, j + 1) + V(i - 1, j) + V(i - 1, j + 1)) / 4.) / Q1(P.sew, i);
-        const double vis_c = S(i, j), den_c = D(i, j);
+        const double dudx = (U.at<1, 0>() - U.at<0, 0>()) / Q1(P.sew, i);
+        const double dvdy = (V.at<0, 1>() - V.at<0, 0>()) / __ldg(P.sns + qc);
+        const double dudy = ((U.at<0, 0>() + U.at<1, 0>() + U.at<0, 1>() + U.at<1, 1>()) / 4.
+                             - (U.at<0, 0>() + U.at<1, 0>() + U.at<0, -1>() + U.at<1, -1>()) / 4.) / __ldg(P.sns + qc);
+        const double dvdx = ((V.at<0, 0>() + V.at<0, 1>() + V.at<1, 0>() + V.at<1, 1>()) / 4.
+                             - (V.at<0, 0>() + V.at<0, 1>() + V.at<-1, 0>() + V.at<-1, 1>()) / 4.) / Q1(P.sew, i);
+        const double vis_c = S.at<0, 0>(), den_c = D.at<0, 0>();
         double gen = (2. * (dudx * dudx + dvdy * dvdy) + (dudy + dvdx) * (dudy + dvdx)) * vis_c;
-        double vdr = V(i, j) / QJ(P.rv, j);
+        double vdr = V.at<0, 0>() / __ldg(P.rv + qc);
         if (j == 2) vdr = 0.0;
         if (P.indcos == 2) {
-          const double h = vdr + V(i, j + 1) / QJ(P.rv, j + 1);
+          const double h = vdr + V.at<0, 1>() / __ldg(P.rv + qp);
           gen = gen + vis_c * 0.5 * (h * h);
         }
         const double sukd = SU;
@@ -209,7 +215,7 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
         if (j == njm1) {
           const double yp = P.yvn[nj - 1] - P.yn[njm1 - 1];
           const double sqrtk = sqrt(phi_c);
-          const double gencou = 0.5 * (fabs(P.taun[i] * U(i + 1, j)) + fabs(P.taun[i - 1] * U(i, j))) / yp;
+          const double gencou = 0.5 * (fabs(P.taun[i] * U.at<1, 0>()) + fabs(P.taun[i - 1] * U.at<0, 0>())) / yp;
           const double yplus = den_c * sqrtk * cdterm * yp / P.viscos;
           P.yplusn[i - 1] = yplus;
           const double genres = gen - vis_c * (dudy * dudy);
@@ -229,7 +235,7 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
           const double sqrtk = sqrt(phi_c);
           const double xplus = den_c * sqrtk * cdterm * xp / P.viscos;
           P.xplusw[j - 1] = xplus;
-          const double gencou = 0.5 * (fabs(P.tauw[j] * V(i, j + 1)) + fabs(P.tauw[j - 1] * V(i, j))) / xp;
+          const double gencou = 0.5 * (fabs(P.tauw[j] * V.at<0, 1>()) + fabs(P.tauw[j - 1] * V.at<0, 0>())) / xp;
           const double genres = gen - vis_c * (dvdx * dvdx);
           gen = genres + gencou;
           double diterm;
@@ -243,7 +249,7 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
           AW = 0.0;
         }
         if (j == 2) {
-          P.te[(long long)i0 * LD + lp(0)] = phi_c;      // te(i,1) = te(i,2)
+          P.te[oline + lpos(0, M, T)] = phi_c;      // te(i,1) = te(i,2)
           phi_s = phi_c;
           gen = gen - vis_c * (dudy * dudy);
           SU = sukd + gen * vol;
@@ -251,7 +257,7 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
         }
         P.gen[oq] = gen;
       } else if (EQ == CFD_EQ_ED) {
-        const double vis_c = S(i, j), den_c = D(i, j), te_c = TE(i, j);
+        const double vis_c = S.at<0, 0>(), den_c = D.at<0, 0>(), te_c = TE.at<0, 0>();
         SU = SU + P.m.c1 * P.m.cmu * __ldg(P.gen + oq) * vol * den_c * te_c / vis_c;
         SP = SP - P.m.c2 * den_c * phi_c * vol / te_c;
         // ---- moded (promod.f90:260-296): fixed values through the great-source trick
@@ -273,14 +279,14 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
         if (j == njm1) {
           const double dyn = P.yvn[nj - 1] - P.yn[njm1 - 1];
           AN = 0.0;
-          const double area = QJ(P.rv, j + 1) * Q1(P.sew, i);
+          const double area = __ldg(P.rv + qp) * Q1(P.sew, i);
           const double yplus = P.yplusn[i - 1];
           double gt;
           if (yplus <= 11.63) {
             gt = P.viscos / (P.m.prandl * dyn);
           } else {
             const double uplus = log(P.m.elog * yplus) / P.m.cappa;
-            gt = D(i, j) * cdterm * sqrt(TE(i, j)) / (P.m.prandt * (uplus + P.m.pfun));
+            gt = D.at<0, 0>() * cdterm * sqrt(TE.at<0, 0>()) / (P.m.prandt * (uplus + P.m.pfun));
           }
           const double term = gt * area;
           SU = SU + term * P.m.twalln;
@@ -291,8 +297,8 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
       }
       // ---- chapter 3
       double AP = AN + AS + AE + AW - SP;
-      double resor = AN * PHI(i, j + 1) + AS * phi_s + AE * PHI(i + 1, j) + AW * PHI(i - 1, j) - AP * phi_c + SU;
-      vol = QJ(P.r, j) * Q1(P.sew, i) * QJ(P.sns, j);
+      double resor = AN * PHI.at<0, 1>() + AS * phi_s + AE * PHI.at<1, 0>() + AW * PHI.at<-1, 0>() - AP * phi_c + SU;
+      vol = __ldg(P.r + qc) * Q1(P.sew, i) * __ldg(P.sns + qc);
       const double sorvol = P.great * vol;
       if (-SP > 0.5 * sorvol) resor = resor / sorvol;
       racc += fabs(resor);
