@@ -99,6 +99,7 @@ SYMBOLS = {
     "cfd_assemble_v": (C.c_int, [_vp]),
     "cfd_assemble_p": (C.c_int, [_vp]),
     "cfd_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "cfd_sweep_part": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cfd_correct": (C.c_int, [_vp, _vp]),
     "cfd_set_turbulence": (C.c_int, [_vp, C.POINTER(CfdTurbulence)]),
     "cfd_wall_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),

@@ -225,6 +225,9 @@ class CavityFVM:
     def sweep(self, istart, jstart, phi, colour, first=False):
         check(self.lib.cfd_sweep(self._h, istart, jstart, FIELD_ID[phi], colour, 1 if first else 0))
 
+    def sweep_part(self, istart, jstart, phi, colour, first=False, part=0):
+        check(self.lib.cfd_sweep_part(self._h, istart, jstart, FIELD_ID[phi], colour, 1 if first else 0, part))
+
     def correct(self, ppref_device_ptr: int | None = None):
         check(self.lib.cfd_correct(self._h, C.c_void_p(ppref_device_ptr) if ppref_device_ptr else None))
 

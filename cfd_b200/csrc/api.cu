@@ -527,6 +527,16 @@ extern "C" int cfd_sweep(cfd_ctx* c, int istart, int jstart, int field, int colo
   return cfd_launch_sweep_rb(c, istart, jstart, c->field[field], colour, first);
 }
 
+extern "C" int cfd_sweep_part(cfd_ctx* c, int istart, int jstart, int field, int colour, int first, int part) {
+  CFD_REQUIRE(c, "null context");
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(istart >= 2 && jstart >= 2 && jstart <= c->L.nj - 1, "istart/jstart out of range");
+  CFD_REQUIRE(colour == 0 || colour == 1, "colour must be 0 or 1");
+  CFD_REQUIRE(part >= 0 && part <= 2, "part must be 0 (all lines), 1 (slab-edge lines) or 2 (the others)");
+  return cfd_launch_sweep_rb_part(c, istart, jstart, c->field[field], colour, first, part);
+}
+
 static int full_sweep(cfd_ctx* c, int istart, int jstart, int field, int first) {
   int rc;
   if (c->cfg.order == CFD_ORDER_SEQUENTIAL) return cfd_launch_sweep_seq(c, istart, jstart, c->field[field], first);

@@ -149,6 +149,7 @@ int cfd_launch_assemble_v(cfd_ctx* c);
 int cfd_launch_assemble_p(cfd_ctx* c);
 int cfd_launch_correct(cfd_ctx* c, const double* ppref_dev);
 int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first);
+int cfd_launch_sweep_rb_part(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first, int part);
 int cfd_launch_sweep_seq(cfd_ctx* c, int istart, int jstart, double* phi, int first);
 int cfd_launch_spike_basis(cfd_ctx* c, int istart, int jstart);
 int cfd_launch_sweep_seq2(cfd_ctx* c, int istart, int jstart, double* phi, int first, int two_div);

@@ -553,39 +553,64 @@ void cfd_local_j_range(const cfd_ctx* c, int gj_lo, int gj_hi, int* jlo, int* jh
 }
 
 static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P);
+int cfd_launch_sweep_rb_part(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first, int part);
 
 int cfd_launch_sweep_rb(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first) {
+  return cfd_launch_sweep_rb_part(c, istart, jstart, phi, colour, first, 0);
+}
+
+// part 0: every line of the colour; 1: only the lines a neighbouring i-slab needs (first / last owned line, if they
+// have this colour and there is a neighbour on that side); 2: the others.  Parts 1 and 2 let the driver send the edge
+// lines while the interior is still being solved.
+int cfd_launch_sweep_rb_part(cfd_ctx* c, int istart, int jstart, double* phi, int colour, int first, int part) {
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   const int NJ = c->cfg.nj_global ? c->cfg.nj_global : c->L.nj;
   // owned lines, global 1-based [glo, ghi], restricted to istart..NI-1
-  int glo = c->cfg.goff + c->cfg.halo_w + 1, ghi = c->cfg.goff + c->L.ni - c->cfg.halo_e;
+  const int own_lo = c->cfg.goff + c->cfg.halo_w + 1, own_hi = c->cfg.goff + c->L.ni - c->cfg.halo_e;
+  int glo = own_lo, ghi = own_hi;
   if (glo < istart) glo = istart;
   if (ghi > NI - 1) ghi = NI - 1;
   // first line of this colour: (i - istart) % 2 == colour
-  int g0 = glo + ((((glo - istart) & 1) != colour) ? 1 : 0);
+  const int g0 = glo + ((((glo - istart) & 1) != colour) ? 1 : 0);
   if (g0 > ghi) return CFD_OK;
-  SweepParams P{};
-  P.L = c->L;
-  P.i_first = g0 - 1 - c->cfg.goff;
-  P.i_step = 2;
-  P.nlines = (ghi - g0) / 2 + 1;
-  cfd_local_j_range(c, jstart - 1, NJ - 2, &P.jlo, &P.jhi);
-  if (P.jhi < P.jlo) return CFD_OK;
-  P.first = first ? 1 : 0;
-  P.first_colour = colour;
-  P.ae = c->field[CFD_AE];
-  P.aw = c->field[CFD_AW];
-  P.an = c->field[CFD_AN];
-  P.as = c->field[CFD_AS];
-  P.ap = c->field[CFD_AP];
-  P.su = c->field[CFD_SU];
-  P.phi = phi;
-  P.out = phi;
-  // a j-slab solves its piece of every line with zero values at the cut ends (the partition method's particular
-  // solution, jslab_kernels.cu); physical ends keep the stored Dirichlet values
-  P.end_s_const = c->cfg.halo_s > 0;
-  P.end_n_const = c->cfg.halo_n > 0;
-  return launch_sweep(c, P);
+  const int gl = g0 + 2 * ((ghi - g0) / 2);                 // last line of this colour
+  const bool west_edge = c->cfg.halo_w > 0 && g0 == own_lo, east_edge = c->cfg.halo_e > 0 && gl == own_hi;
+  int seg_first[2], seg_n[2], nseg = 0;
+  if (part == 0) {
+    seg_first[0] = g0; seg_n[0] = (gl - g0) / 2 + 1; nseg = 1;
+  } else if (part == 1) {
+    if (west_edge) { seg_first[nseg] = g0; seg_n[nseg] = 1; ++nseg; }
+    if (east_edge && !(west_edge && gl == g0)) { seg_first[nseg] = gl; seg_n[nseg] = 1; ++nseg; }
+  } else {
+    const int a = g0 + (west_edge ? 2 : 0), b = gl - (east_edge ? 2 : 0);
+    if (a <= b) { seg_first[0] = a; seg_n[0] = (b - a) / 2 + 1; nseg = 1; }
+  }
+  for (int sgm = 0; sgm < nseg; ++sgm) {
+    SweepParams P{};
+    P.L = c->L;
+    P.i_first = seg_first[sgm] - 1 - c->cfg.goff;
+    P.i_step = 2;
+    P.nlines = seg_n[sgm];
+    cfd_local_j_range(c, jstart - 1, NJ - 2, &P.jlo, &P.jhi);
+    if (P.jhi < P.jlo) return CFD_OK;
+    P.first = first ? 1 : 0;
+    P.first_colour = colour;
+    P.ae = c->field[CFD_AE];
+    P.aw = c->field[CFD_AW];
+    P.an = c->field[CFD_AN];
+    P.as = c->field[CFD_AS];
+    P.ap = c->field[CFD_AP];
+    P.su = c->field[CFD_SU];
+    P.phi = phi;
+    P.out = phi;
+    // a j-slab solves its piece of every line with zero values at the cut ends (the partition method's particular
+    // solution, jslab_kernels.cu); physical ends keep the stored Dirichlet values
+    P.end_s_const = c->cfg.halo_s > 0;
+    P.end_n_const = c->cfg.halo_n > 0;
+    int rc = launch_sweep(c, P);
+    if (rc) return rc;
+  }
+  return CFD_OK;
 }
 
 // Spike vectors of the partition method for the current coefficients: for EVERY line i >= istart the solutions of

@@ -15,6 +15,8 @@ debug mode does not shard (replicas only).
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 from .cavity import CavityFVM, setgrid
@@ -217,7 +219,8 @@ class TeachSlab(Slab):
         self._finish(nswp)
 
 
-# stages of one outer iteration: ("compute", fn(slab)) or ("halo", field, w, e) or ("ppref",)
+# stages of one outer iteration: ("compute", fn(slab)), ("halo", field, w, e, colour filter), ("halos", ...),
+# ("sweep", field, istart, jstart, colour, first) = colour pass + halo exchange of that colour's edge lines, ("ppref",)
 def iteration_stages(nswp):
     st = [("halos", (("u", 1, 1), ("v", 1, 1), ("p", 1, 0))),
           ("compute", lambda s: s.ctx.assemble_u()), ("halo", "du", 0, 1, None)]
@@ -228,9 +231,8 @@ def iteration_stages(nswp):
             st.append(("compute", lambda s: s.ctx.assemble_p()))
         for k in range(n):
             for colour in (0, 1):
-                st.append(("compute", (lambda s, a=istart, b=jstart, f=name, c=colour, z=(first and k == 0):
-                                       s.ctx.sweep(a, b, f, c, first=z))))
-                st.append(("halo", name, 1, 1, (istart, colour)))   # only the lines of this colour moved
+                # colour pass + exchange of the lines of this colour at the slab edges (only they moved)
+                st.append(("sweep", name, istart, jstart, colour, first and k == 0))
     st += [("ppref",), ("compute", lambda s: s.ctx.correct(s.ppref.data_ptr()))]
     return st
 
@@ -294,6 +296,8 @@ class SlabCavity(_E2EMixin):
         if stream is not None:
             self.ctx.set_stream(stream.cuda_stream)
         self.stages = iteration_stages(self.slab.nswp)
+        self.overlap = os.environ.get("CFD_B200_OVERLAP", "0") != "0"   # measured: no gain at N=2
+        self._comm_stream = None
         self.pref_owner = [r for r, (lo, hi) in enumerate(partition(nicv + 2, self.world)) if lo <= self.slab.ipref <= hi][0]
         # static fields: halos filled at upload (den, vis are uniform here); general case: exchange once
         s = self.slab
@@ -334,6 +338,8 @@ class SlabCavity(_E2EMixin):
             for st in self.stages:
                 if st[0] == "compute":
                     st[1](s)
+                elif st[0] == "sweep":
+                    self._sweep_and_exchange(*st[1:])
                 elif st[0] == "halo":
                     only = colour_filter(s.lo, s.hi, *st[4]) if st[4] else None
                     self.comm.exchange(halo_ops(s.lines(st[1]), s.rank, s.world, s.hw, s.he, s.nown, st[2], st[3], only))
@@ -346,6 +352,35 @@ class SlabCavity(_E2EMixin):
                     if s.owner_of_pref:
                         s.ppref.copy_(s.ppref_element())
                     self.comm.broadcast(s.ppref, self.pref_owner)
+
+    def _sweep_and_exchange(self, name, istart, jstart, colour, first):
+        """One colour pass with the halo exchange hidden behind it: the slab-edge lines of the colour are solved
+        first (cfd_sweep_part 1), their exchange runs on a side stream while the other lines are solved (part 2);
+        the compute stream then waits for the exchange before anything reads the halos."""
+        s, torch = self.slab, self.torch
+        only = colour_filter(s.lo, s.hi, istart, colour)
+        ops = halo_ops(s.lines(name), s.rank, s.world, s.hw, s.he, s.nown, 1, 1, only)
+        if not self.overlap or not ops:
+            s.ctx.sweep(istart, jstart, name, colour, first=first)
+            self.comm.exchange(ops)
+            return
+        main = torch.cuda.current_stream()
+        if self._comm_stream is None:
+            self._comm_stream = torch.cuda.Stream(priority=-1)   # its two small launches must not queue behind the bulk
+            self._ev = [torch.cuda.Event(), torch.cuda.Event()]
+        side = self._comm_stream
+        # edge lines + their exchange on the side stream, concurrently with the other lines on the compute stream
+        # (the two launches touch disjoint lines of this colour and only read lines of the other colour)
+        self._ev[0].record(main)
+        side.wait_event(self._ev[0])
+        s.ctx.set_stream(side.cuda_stream)
+        s.ctx.sweep_part(istart, jstart, name, colour, first=first, part=1)
+        s.ctx.set_stream(main.cuda_stream)
+        with torch.cuda.stream(side):
+            self.comm.exchange(ops)
+            self._ev[1].record(side)
+        s.ctx.sweep_part(istart, jstart, name, colour, first=first, part=2)
+        main.wait_event(self._ev[1])
 
     def residuals(self):
         r = self.slab.res.clone()
@@ -381,6 +416,13 @@ class LocalSlabCavity:
                 if st[0] == "compute":
                     for s in self.slabs:
                         st[1](s)
+                elif st[0] == "sweep":       # same split as the SPMD driver: edge lines, exchange, the other lines
+                    name, istart, jstart, colour, first = st[1:]
+                    for s in self.slabs:
+                        s.ctx.sweep_part(istart, jstart, name, colour, first=first, part=1)
+                    self.comm.exchange_all(self.slabs, name, 1, 1, (istart, colour))
+                    for s in self.slabs:
+                        s.ctx.sweep_part(istart, jstart, name, colour, first=first, part=2)
                 elif st[0] == "halo":
                     self.comm.exchange_all(self.slabs, st[1], st[2], st[3], st[4])
                 elif st[0] == "halos":

@@ -191,6 +191,10 @@ int cfd_assemble_t(cfd_ctx* ctx);                       /* buoyancy_cav.f90:371-
 /* half sweep over the lines of one colour (0/1), or a full sequential sweep if colour < 0;
    first != 0 treats phi as zero where the reference has just executed pp(:,:)=0 (cavity_fvm.f90:342) */
 int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first);
+/* one colour pass in two launches: part 1 = the first / last owned line of an i-slab (if it has this colour and a
+   neighbour on that side), part 2 = the other lines of the colour, part 0 = all (= cfd_sweep).  Lets a multi-GPU
+   driver send the edge lines while the interior is still being solved. */
+int cfd_sweep_part(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first, int part);
 int cfd_correct(cfd_ctx* ctx, const double* ppref_device); /* cavity_fvm.f90:346-354; NULL = pp(ipref,jpref) */
 
 /* ---- TEACH family: k-epsilon model, energy equation, wall functions -------------------------------
