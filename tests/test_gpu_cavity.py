@@ -282,3 +282,20 @@ def test_error_paths(cfd):
     with pytest.raises(cfd.CfdError):
         g.lisolv(1, 2, "u")
     g.close()
+
+
+@pytest.mark.parametrize("njcv", [5000, 8192, 12000, 16382])
+def test_long_lines_redblack(cfd, oracle, njcv):
+    """Lines up to the layout's maximum (16384 nodes): the line solver variants for long lines (the spike array in
+    shared memory above 352 threads, the register-staged kernel at 1024 threads) against the oracle's red/black order."""
+    nicv = 12
+    o = oracle.Cavity(nicv, njcv, 100.0, order=1, fast=True)
+    g = cfd.CavityFVM(nicv, njcv, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    o.run(maxit=2, tol=0.0)
+    res = g.iterate(2)
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-9, (name, g.layout)
+    for a, b in zip(res, o.residuals):
+        assert abs(a - b) <= 1e-9 * abs(b)
+    g.close()
