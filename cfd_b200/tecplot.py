@@ -49,3 +49,76 @@ def write_centrelines(path_u, path_v, x, y, uc, vc, imon, jmon):
     with open(path_v, "w") as f:
         for i in range(ni):
             f.write("".join(" " + es14_7(v) for v in (x[i], y[jmon - 1], vc[i, jmon - 1])) + "\n")
+
+
+# ---- general family: postproc (buoyancy-driven-cavity-2d/buoyancy_cav.f90:435-469) -------------------------------
+def general_postproc(u, v, p, t, xdif, ydif, ipref, jpref, lprint=(True, True, True, True)):
+    """Cell-centred velocities, pressure extrapolated to the boundaries / corners and referenced to (ipref,jpref),
+    corner temperatures -- on downloaded fields, same statement order as the reference.  Returns (uc, vc, p, t)."""
+    ni, nj = u.shape
+    uc, vc = np.zeros_like(u), np.zeros_like(v)
+    p, t = np.array(p, order="F", copy=True), np.array(t, order="F", copy=True)
+    if lprint[0]:
+        uc[0, :] = u[1, :]
+        uc[ni - 1, :] = u[ni - 1, :]
+        uc[1:ni - 1, :] = 0.5 * (u[1:ni - 1, :] + u[2:ni, :])
+    if lprint[1]:
+        vc[:, 0] = v[:, 1]
+        vc[:, nj - 1] = v[:, nj - 1]
+        vc[:, 1:nj - 1] = 0.5 * (v[:, 1:nj - 1] + v[:, 2:nj])
+    if lprint[2]:
+        p[0, :] = p[1, :] + (p[1, :] - p[2, :]) * xdif[1] / xdif[2]
+        p[ni - 1, :] = p[ni - 2, :] + (p[ni - 2, :] - p[ni - 3, :]) * xdif[ni - 1] / xdif[ni - 2]
+        p[:, 0] = p[:, 1] + (p[:, 1] - p[:, 2]) * ydif[1] / ydif[2]
+        p[:, nj - 1] = p[:, nj - 2] + (p[:, nj - 2] - p[:, nj - 3]) * ydif[nj - 1] / ydif[nj - 2]
+        p[0, 0] = p[1, 0] + p[0, 1] - p[1, 1]
+        p[0, nj - 1] = p[0, nj - 2] + p[1, nj - 1] - p[1, nj - 2]
+        p[ni - 1, 0] = p[ni - 2, 0] + p[ni - 1, 1] - p[ni - 2, 1]
+        p[ni - 1, nj - 1] = p[ni - 1, nj - 2] + p[ni - 2, nj - 1] - p[ni - 2, nj - 2]
+        p[:, :] = p - p[ipref - 1, jpref - 1]
+    if lprint[3]:
+        t[0, 0] = t[1, 0] + t[0, 1] - t[1, 1]
+        t[0, nj - 1] = t[0, nj - 2] + t[1, nj - 1] - t[1, nj - 2]
+        t[ni - 1, 0] = t[ni - 2, 0] + t[ni - 1, 1] - t[ni - 2, 1]
+        t[ni - 1, nj - 1] = t[ni - 1, nj - 2] + t[ni - 2, nj - 1] - t[ni - 2, nj - 2]
+    return uc, vc, p, t
+
+
+# ---- TEACH family: centred_vels, tecprint, velprint (backward-step-flow-2d/general.f90:238-289, 331-350) ---------
+def teach_centred_vels(u, v):
+    ni, nj = u.shape
+    uc, vc = np.zeros_like(u), np.zeros_like(v)
+    uc[2:ni - 1, 1:nj] = u[2:ni - 1, 1:nj] + 0.5 * (u[3:ni, 1:nj] - u[2:ni - 1, 1:nj])
+    vc[1:ni, 2:nj - 1] = v[1:ni, 2:nj - 1] + 0.5 * (v[1:ni, 2:nj - 1] - v[1:ni, 3:nj])
+    return uc, vc
+
+
+def _es10_3(v: float) -> str:
+    return "%10.3E" % v
+
+
+def teach_tecprint(path, istart, jstart, x, y, phi, mode="w"):
+    """tecprint: format 120 `/'ZONE',3x,'I=',i3,3x,'j=',i3,3x,'F=POINT'` (i3 prints *** beyond 999, as Fortran does),
+    then one `1x,es10.3,3x,es10.3,3x,es10.3` record per node, i fastest."""
+    ni, nj = phi.shape
+
+    def i3(n):
+        return "%3d" % n if -99 <= n <= 999 else "***"
+    with open(path, mode) as f:
+        f.write("\n" + "ZONE" + "   " + "I=" + i3(ni - 1) + "   " + "j=" + i3(nj - 1) + "   " + "F=POINT" + "\n")
+        for j in range(jstart, nj + 1):
+            for i in range(istart, ni + 1):
+                f.write(" " + _es10_3(x[i - 1]) + "   " + _es10_3(y[j - 1]) + "   " + _es10_3(phi[i - 1, j - 1]) + "\n")
+
+
+def teach_velprint(path, istart, jstart, x, y, uvel, vvel, mode="w"):
+    ni, nj = uvel.shape
+
+    def i3(n):
+        return "%3d" % n if -99 <= n <= 999 else "***"
+    with open(path, mode) as f:
+        f.write("\n" + "ZONE" + "   " + "I=" + i3(ni - 1) + "   " + "j=" + i3(nj - 1) + "   " + "F=POINT" + "\n")
+        for j in range(jstart, nj + 1):
+            for i in range(istart, ni + 1):
+                f.write(" " + _es10_3(x[i - 1]) + "   " + _es10_3(y[j - 1]) + "   " + _es10_3(uvel[i - 1, j - 1]) + "   "
+                        + _es10_3(vvel[i - 1, j - 1]) + "\n")

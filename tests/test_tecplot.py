@@ -28,3 +28,33 @@ def test_result_files_structure(tmp_path, oracle):
     assert float(rec[2]) == float(tecplot.es14_7(uc[5, 5])) and abs(float(rec[2]) + 0.15782975) < 1e-8
     tecplot.write_centrelines(tmp_path / "uvel.txt", tmp_path / "vvel.txt", c.x, c.y, uc, vc, c.imon, c.jmon)
     assert len(open(tmp_path / "uvel.txt").read().splitlines()) == 12
+
+
+def test_general_postproc_and_teach_writers(tmp_path):
+    import numpy as np
+    from cfd_b200 import tecplot as tp
+    rng = np.random.default_rng(5)
+    ni, nj = 7, 6
+    u, v, p, t = (np.asfortranarray(rng.random((ni, nj))) for _ in range(4))
+    xdif, ydif = 0.1 + rng.random(ni), 0.1 + rng.random(nj)
+    uc, vc, pp, tt = tp.general_postproc(u, v, p, t, xdif, ydif, 3, 3)
+    assert uc[0, 2] == u[1, 2] and uc[3, 2] == 0.5 * (u[3, 2] + u[4, 2]) and vc[2, 0] == v[2, 1]
+    assert pp[2, 2] == 0.0                                           # referenced to (ipref, jpref)
+    assert tt[0, 0] == t[1, 0] + t[0, 1] - t[1, 1] and np.array_equal(tt[1:-1, 1:-1], t[1:-1, 1:-1])
+    # linear pressure field is extrapolated exactly on a uniform grid
+    xi, yj = np.arange(ni)[:, None] * 1.0, np.arange(nj)[None, :] * 1.0
+    lin = np.asfortranarray(2.0 * xi + 3.0 * yj)
+    lin_in = lin.copy(); lin_in[0, :] = lin_in[-1, :] = 0; lin_in[:, 0] = lin_in[:, -1] = 0
+    _, _, pl, _ = tp.general_postproc(u, v, lin_in, t, np.ones(ni), np.ones(nj), 3, 3)
+    assert np.allclose(pl, lin - lin[2, 2], atol=1e-12)
+    uc2, vc2 = tp.teach_centred_vels(u, v)
+    assert uc2[2, 1] == u[2, 1] + 0.5 * (u[3, 1] - u[2, 1]) and vc2[1, 2] == v[1, 2] + 0.5 * (v[1, 2] - v[1, 3])
+    f = tmp_path / "vel.dat"
+    tp.teach_velprint(f, 2, 2, np.arange(ni) * 0.5, np.arange(nj) * 0.25, u, v)
+    lines = f.read_text().split("\n")
+    assert lines[0] == "" and lines[1] == "ZONE   I=  6   j=  5   F=POINT"
+    assert len([x for x in lines[2:] if x]) == (ni - 1) * (nj - 1)
+    assert lines[2].startswith("  5.000E-01    2.500E-01   ") and len(lines[2]) == 1 + 10 + 3 * 13
+    g = tmp_path / "t.dat"
+    tp.teach_tecprint(g, 2, 2, np.arange(ni) * 0.5, np.arange(nj) * 0.25, t)
+    assert len(g.read_text().split("\n")[2]) == 1 + 10 + 2 * 13
