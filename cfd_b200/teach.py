@@ -227,6 +227,32 @@ class TeachFVM(CavityFVM):
         check(self.lib.cfd_calct(self._h, C.byref(r)))
         return r.value
 
+    def wall_coefficients(self, rlarge=0.0124, rsmall=None, uin=0.5, densit=1000.0, tin=0.0, cpp=4.190e3, tk=6.0e-1):
+        """Shear-stress coefficient and Nusselt number along the large-duct wall (control.f90:243-272), from the
+        device's taun / yplusn and the fields te, t, den; returns rows (i, xu/h, ssc, nusselt, x/h), i = istep..nim1."""
+        m = self.model
+        ni, nj = self.ni, self.nj
+        rsmall = rsmall if rsmall is not None else 0.5 * (self.y[self.jstep - 1] + self.y[self.jstep])   # control.f90:91
+        ularge = uin * (rsmall / rlarge) ** 2
+        taun, yplusn = self.wall_download("taun"), self.wall_download("yplusn")
+        te, t, den = self.download("te"), self.download("t"), self.download("den")
+        j = nj - 1                                                          # njm1
+        xlref, tref, delt = rlarge - rsmall, tin, abs(tin - m.twalln)
+        dyn = self.yv[nj - 1] - self.y[nj - 2]
+        rows = []
+        for i in range(self.istep, ni):                                     # istep .. nim1
+            ssc = taun[i - 1] / (densit * ularge * ularge)
+            xuh = self.xu[i - 1] / (rlarge - rsmall)
+            xh = self.x[i - 1] / xlref
+            if yplusn[i - 1] <= 11.63:
+                hfluxn = tk * abs(m.twalln - t[i - 1, j - 1]) / dyn
+            else:
+                uplusn = np.log(m.elog * yplusn[i - 1]) / m.cappa
+                hfluxn = den[i - 1, j - 1] * cpp * np.sqrt(te[i - 1, j - 1]) * (tref - t[i - 1, j - 1]) / m.prandt / (uplusn + m.pfun)
+            hfluxn = abs(hfluxn)
+            rows.append((i, xuh, ssc, hfluxn * xlref / (tk * delt), xh))
+        return rows
+
     def iterate_turb(self, n=1):
         """n passes of control.f90:210-217; returns (resoru, resorv, resorm, resort, resork, resore)."""
         res = (C.c_double * 8)()

@@ -150,3 +150,14 @@ def test_turbulent_stagewise_vs_oracle(cfd, oracle):
     g.props()
     assert _rel(g.download("vis"), o.vis) < 1e-12
     g.close()
+
+
+def test_wall_coefficients_postprocessing(cfd):
+    """control.f90:243-272 on the device's wall arrays: finite, one row per wall node, Nusselt number positive."""
+    g = cfd.TeachFVM(40, 30, order="redblack", turbulent=True)
+    g.iterate_turb(30)
+    rows = g.wall_coefficients()
+    assert len(rows) == 40 - 1 - g.istep + 1
+    a = np.array(rows)
+    assert np.isfinite(a).all() and (a[:, 3] > 0).all() and (np.diff(a[:, 4]) > 0).all()
+    g.close()
