@@ -3,7 +3,7 @@
 (Re=1000, 4096^2 control volumes per GPU, red/black line TDMA), reported as cell-updates/s (GLUPS) and
 iterations/s, with the HBM roofline of the dominant kernel and a CPU baseline beside it.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat|step|cavity16k]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cavity|heat|step|buoyancy|cavity16k]
 
 A "step" is one pass of the hot path: calcu + calcv + calcp (cavity_fvm.f90:554-557) over the whole grid.
 For N>1 launch with torch.distributed.run (one rank per GPU); the grid is slab-decomposed along i (weak scaling:
@@ -515,14 +515,14 @@ def run_cavity16k(args):
         dist.destroy_process_group()
 
 
-def run_step(args):
+def run_step(args, kind="step"):
     """--workload step: BASELINE.json configs[4], TEACH backward-step SIMPLE (laminar, nswp 3/3/5) on 16384 x 4096,
     i-slabs over the N GPUs (STRONG scaling: the global grid is fixed).  One step = one outer iteration."""
     import torch
     import torch.distributed as dist
 
     import cfd_b200
-    from cfd_b200.dist import SlabCavity, TeachSlab
+    from cfd_b200.dist import BuoyancySlab, SlabCavity, TeachSlab
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -533,14 +533,20 @@ def run_step(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     K, W = args.steps, args.warmup
     hbm_peak, peak_src = peaks()
-    NI, NJ = 16384, 4096
+    NI, NJ = (16384, 4096) if kind == "step" else (8194, 8194)
     stream = torch.cuda.Stream()
     if world == 1:
-        solver = cfd_b200.TeachFVM(NI, NJ, epsx=1.0, order="redblack", device=local)
+        if kind == "step":
+            solver = cfd_b200.TeachFVM(NI, NJ, epsx=1.0, order="redblack", device=local)
+        else:
+            solver = cfd_b200.BuoyantCavity(NI, NJ, order="redblack", device=local)
         solver.set_stream(stream.cuda_stream)
         step, ctx0 = solver.iterate_async, solver
-    else:
+    elif kind == "step":
         solver = SlabCavity(NI - 2, NJ - 2, stream=stream, slab_cls=TeachSlab, epsx=1.0)
+        step, ctx0 = solver.iterate_async, solver.ctx
+    else:
+        solver = SlabCavity(NI - 2, NJ - 2, stream=stream, slab_cls=BuoyancySlab)
         step, ctx0 = solver.iterate_async, solver.ctx
 
     def barrier():
@@ -573,15 +579,18 @@ def run_step(args):
         ms = float(tms.item())
     cells = (NI - 2) * (NJ - 2)
     glups = cells * K / (ms * 1e-3) / 1e9
-    B = 1056                                                  # 132 doubles / cell / outer iteration
+    B = 1056 if kind == "step" else 1224                      # 132 / 153 doubles per cell and outer iteration
+    wl = (f"backward-facing step FVM SIMPLE (TEACH family, laminar, axisymmetric, hybrid scheme, urf .5/.5/1, nswp 3/3/5) "
+          f"on {NI}x{NJ}, red/black line TDMA (BASELINE.json configs[4])") if kind == "step" else (
+          f"buoyancy-driven cavity Ra=1e6 (Boussinesq, coupled T equation) SIMPLE on {NI - 2}^2 CV, hybrid scheme, urf "
+          ".3/.3/.9/1, nsweep 3/3/3/3, red/black line TDMA (BASELINE.json configs[3])")
     out = {"metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K,
            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic", "iters_per_s": K / (ms * 1e-3),
-           "config": {"workload": f"backward-facing step FVM SIMPLE (TEACH family, laminar, axisymmetric, hybrid scheme, "
-                                  f"urf .5/.5/1, nswp 3/3/5) on {NI}x{NJ}, red/black line TDMA (BASELINE.json configs[4])",
+           "config": {"workload": wl,
                       "parallelism": "single GPU" if world == 1 else f"i-slabs x{world}, 1-line halo exchange (NCCL "
-                                     "send/recv), all-reduced residuals; outlet mass balance on the last rank",
-                      "l2": "inputs larger than L2 (7.5 GB of live fields); no explicit flush",
+                                     "send/recv), all-reduced residuals",
+                      "l2": "inputs larger than L2 (several GB of live fields); no explicit flush",
                       "line_layout": ctx0.layout},
            "residuals_last": [float(x) for x in res[:3]], "gpu_launches": int(launches),
            "roofline": {"bound": "hbm", "kernel": "whole outer iteration", "achieved": B * glups / world, "peak": hbm_peak,
@@ -622,7 +631,7 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step", "cavity16k"])
+    ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step", "cavity16k", "buoyancy"])
     ap.add_argument("--slabs", default="i", choices=["i", "j"], help="N>1 cavity: cut along i (whole lines per GPU) or j")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
@@ -634,6 +643,8 @@ def main():
         run_heat(args)
     elif args.workload == "step":
         run_step(args)
+    elif args.workload == "buoyancy":
+        run_step(args, "buoyancy")
     elif args.workload == "cavity16k":
         run_cavity16k(args)
     else:

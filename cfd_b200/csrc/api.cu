@@ -144,11 +144,10 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     CFD_REQUIRE(cfg->ni >= 6 && cfg->nj >= 6, "TEACH family needs ni, nj >= 6");
   }
   if (general) {
-    CFD_REQUIRE(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni),
-                "general-family contexts do not shard yet (single GPU)");
     // the reference's loops use nj where ni is meant (buoyancy_cav.f90:135,150,151,390): only ni == nj is well defined
-    CFD_REQUIRE(!cfg->solve_flow || cfg->ni == cfg->nj, "the general family's flow equations need ni == nj (reference quirk)");
-    CFD_REQUIRE(cfg->nj <= cfg->ni, "the general family's calct reads den(nj,j): nj must not exceed ni");
+    const int NIg = cfg->ni_global ? cfg->ni_global : cfg->ni;
+    CFD_REQUIRE(!cfg->solve_flow || NIg == cfg->nj, "the general family's flow equations need ni == nj (reference quirk)");
+    CFD_REQUIRE(cfg->nj <= NIg, "the general family's calct reads den(nj,j): nj must not exceed ni");
     CFD_REQUIRE(cfg->ni >= 6 && cfg->nj >= 6, "general family needs ni, nj >= 6");
   }
   CFD_REQUIRE(cfg->order == CFD_ORDER_REDBLACK || cfg->order == CFD_ORDER_SEQUENTIAL, "bad order");
@@ -205,10 +204,10 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   {
     const char* e = getenv("CFD_B200_EXACT_ASSEMBLY");
     c->exact_assembly = (cfg->order == CFD_ORDER_SEQUENTIAL) || (e && atoi(e) != 0) || cfg->raw_coefficients;
-    if (teach && c->exact_assembly &&
+    if ((teach || general) && c->exact_assembly &&
         !(cfg->goff == 0 && cfg->halo_w == 0 && cfg->halo_e == 0 && (cfg->ni_global == 0 || cfg->ni_global == cfg->ni))) {
       delete c;
-      cfd_set_error("TEACH-family i-slab contexts need the red/black order with the production assembly kernels");
+      cfd_set_error("TEACH / general-family i-slab contexts need the red/black order with the production assembly kernels");
       return CFD_ERR_UNSUPPORTED;
     }
     c->L.nc = c->exact_assembly ? 6 : 5;

@@ -16,6 +16,7 @@ namespace cfd {
 struct GenFastParams {
   Layout L;
   int ia, ib, jlo, jhi;
+  int goff, NI;              // i-slabs: global 1-based i of local line i0 is i0 + 1 + goff; NI = global ni
   int iadv;
   double urf;
   int boussinesq;
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_u_fast(const GenFastPar
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib && t * M <= P.jhi && t * M + M - 1 >= P.jlo) {
-    const int j0base = t * M, i = i0 + 1, iadv = P.iadv;
+    const int j0base = t * M, i = i0 + 1 + P.goff, iadv = P.iadv;   // i: global line number (boundary tests only)
     const double* uW = P.u + (long long)(i0 - 1) * LD;
     const double* uC = uW + LD;
     const double* uE = uC + LD;
@@ -226,13 +227,13 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_u_fast(const GenFastPar
 
 // ---- v: buoyancy_cav.f90:212-273 ------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128, 4) k_gen_assemble_v_fast(const GenFastParams P) {
-  const int M = P.L.M, T = P.L.T, nj = P.L.nj, ni = P.L.ni;
+  const int M = P.L.M, T = P.L.T, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib && t * M <= P.jhi && t * M + M - 1 >= P.jlo) {
-    const int j0base = t * M, i = i0 + 1, iadv = P.iadv;
+    const int j0base = t * M, i = i0 + 1 + P.goff, iadv = P.iadv;   // i: global line number (boundary tests only)
     const double* uC = P.u + (long long)i0 * LD;        // u(i,.)   : west face flux
     const double* uE = uC + LD;                         // u(i+1,.) : east face flux
     const double* vW = P.v + (long long)(i0 - 1) * LD;
@@ -250,7 +251,7 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_v_fast(const GenFastPar
     const double fx_c = __ldg(P.fx + i0), fx_e = __ldg(P.fx + i0 + 1);
     const double rxdif_c = __ldg(P.r_xdif + i0), rxdif_e = __ldg(P.r_xdif + i0 + 1);
     const double sew_i = __ldg(P.sew + i0);
-    const bool west_b = (i == 2), east_b = (i == ni - 1);
+    const bool west_b = (i == 2), east_b = (i == P.NI - 1);
     const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
     const bool hasprev = j0base >= 1;
     const int qp0 = GPOS_PREV0;
@@ -359,13 +360,13 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_v_fast(const GenFastPar
 
 // ---- p': buoyancy_cav.f90:294-340 ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(128, 4) k_gen_assemble_p_fast(const GenFastParams P) {
-  const int M = P.L.M, T = P.L.T, nj = P.L.nj, ni = P.L.ni;
+  const int M = P.L.M, T = P.L.T, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib && t * M <= P.jhi && t * M + M - 1 >= P.jlo) {
-    const int j0base = t * M, i = i0 + 1;
+    const int j0base = t * M, i = i0 + 1 + P.goff;
     const double* uC = P.u + (long long)i0 * LD;
     const double* uE = uC + LD;
     const double* vC = P.v + (long long)i0 * LD;
@@ -377,7 +378,7 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_p_fast(const GenFastPar
     const double* dvC = P.dv_in + (long long)i0 * LD;
     const long long cout = (long long)i0 * P.L.cSL;
     const double sew_i = __ldg(P.sew + i0), fx_c = __ldg(P.fx + i0), fx_e = __ldg(P.fx + i0 + 1);
-    const bool west_b = (i == 2), east_b = (i == ni - 1);
+    const bool west_b = (i == 2), east_b = (i == P.NI - 1);
     const bool hasprev = j0base >= 1;
     double d_m = hasprev ? __ldg(dC + GPOS_PREV0) : 0.0, d_c = __ldg(dC + t), d_p;
     // south face of the chunk's first cell: mass flux in and conductance
@@ -446,13 +447,13 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_p_fast(const GenFastPar
 
 // ---- T: buoyancy_cav.f90:373-428 ------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128, 4) k_gen_assemble_t_fast(const GenFastParams P) {
-  const int M = P.L.M, T = P.L.T, nj = P.L.nj, ni = P.L.ni;
+  const int M = P.L.M, T = P.L.T, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int i0 = P.ia + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
   if (t < T && i0 <= P.ib && t * M <= P.jhi && t * M + M - 1 >= P.jlo) {
-    const int j0base = t * M, i = i0 + 1, iadv = P.iadv;
+    const int j0base = t * M, i = i0 + 1 + P.goff, iadv = P.iadv;   // i: global line number (boundary tests only)
     const double* uC = P.u + (long long)i0 * LD;
     const double* uE = uC + LD;
     const double* vC = P.v + (long long)i0 * LD;
@@ -471,7 +472,7 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_t_fast(const GenFastPar
     const long long cout = (long long)i0 * P.L.cSL;
     const double sew_i = __ldg(P.sew + i0), fx_c = __ldg(P.fx + i0), fx_e = __ldg(P.fx + i0 + 1);
     const double rxdif_c = __ldg(P.r_xdif + i0), rxdif_e = __ldg(P.r_xdif + i0 + 1);
-    const bool west_b = (i == 2), east_b = (i == ni - 1);
+    const bool west_b = (i == 2), east_b = (i == P.NI - 1);
     const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
     const bool hasprev = j0base >= 1;
     const int qp0 = GPOS_PREV0;
@@ -535,7 +536,8 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_t_fast(const GenFastPar
           diff_w = gf_harm(g_w, g_c, fx_c) * arx * (rxdif_c * rsx);
         }
         if (east_b) {                                            // quirk: den(nj,j) (:390)
-          const double dq = __ldg(P.den + (long long)(nj - 1) * LD + q) * __ldg(P.cp + (long long)(nj - 1) * LD + q);
+          const long long lq = (long long)(nj - 1 - P.goff) * LD + q;     // global line nj, held by the last slab
+          const double dq = __ldg(P.den + lq) * __ldg(P.cp + lq);
           flow_e = dq * u_e * arx;
           diff_e = g_e * arx * (rxdif_e * rsx);
         } else {
@@ -625,23 +627,30 @@ int cfd_launch_general_assemble_fast(cfd_ctx* c, int which, double* partial) {
   P.ycvrs = c->geom[CFD_G_YCVRS]; P.sns = c->geom[CFD_G_SNS];
   P.r_sx = c->tfast[6]; P.r_ydif = c->tfast[7]; P.r_sxmn = c->tfast[8]; P.r_sns = c->tfast[9];
   const int ni = c->L.ni, nj = c->L.nj;
+  P.goff = c->cfg.goff;
+  P.NI = c->cfg.ni_global ? c->cfg.ni_global : ni;
   P.jhi = nj - 2;
-  P.ib = ni - 2;
+  // global line ranges 3..NI-1 (u) / 2..NI-1 (v, p', T), clamped to the lines this context owns
+  P.ia = (which == 0 ? 2 : 1) - P.goff;
+  P.ib = P.NI - 2 - P.goff;
+  if (P.ia < c->cfg.halo_w) P.ia = c->cfg.halo_w;
+  if (P.ib > ni - 1 - c->cfg.halo_e) P.ib = ni - 1 - c->cfg.halo_e;
   if (which == 0) {
-    P.ia = 2; P.jlo = 1; P.gam = c->field[CFD_VIS]; P.dout = c->field[CFD_DU];
+    P.jlo = 1; P.gam = c->field[CFD_VIS]; P.dout = c->field[CFD_DU];
   } else if (which == 1) {
-    P.ia = 1; P.jlo = 2; P.gam = c->field[CFD_VIS]; P.dout = c->field[CFD_DV];
+    P.jlo = 2; P.gam = c->field[CFD_VIS]; P.dout = c->field[CFD_DV];
     P.boussinesq = c->boussinesq; P.rgbeta = c->rgbeta; P.tref = c->tref;
     if (!P.boussinesq) P.t = nullptr;
   } else if (which == 2) {
-    P.ia = 1; P.jlo = 1;
+    P.jlo = 1;
   } else {
-    P.ia = 1; P.jlo = 1; P.gam = c->field[CFD_GAMT];
+    P.jlo = 1; P.gam = c->field[CFD_GAMT];
     P.su_src = c->has_t_sources ? c->field[CFD_SUSRC] : nullptr;
     P.sp_src = c->has_t_sources ? c->field[CFD_SPSRC] : nullptr;
   }
   P.partial = partial;
   const int nlines = P.ib - P.ia + 1;
+  if (nlines <= 0) return 0;          // a slab that owns none of this equation's lines
   dim3 block(32, 4), grid((c->L.T + 31) / 32, (nlines + 3) / 4);
   const int nblocks = grid.x * grid.y;
   if (nblocks > c->max_partials) {

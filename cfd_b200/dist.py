@@ -219,9 +219,28 @@ class TeachSlab(Slab):
         self._finish(nswp)
 
 
+class BuoyancySlab(Slab):
+    """One rank's i-slab of the Boussinesq cavity (general family, BASELINE.json configs[3]).  `nicv, njcv` = ni-2,
+    nj-2 of the global (square) grid.  Adds the temperature equation to the stage list (`solve_t`)."""
+
+    solve_t = True
+
+    def __init__(self, nicv, njcv, rank, world, *, device=-1, nswp=(3, 3, 3, 3), **kw):
+        from .general import BuoyantCavity
+        self.rank, self.world = rank, world
+        ni_g, nj = nicv + 2, njcv + 2
+        self.ni_global, self.nj = ni_g, nj
+        self.goff, self.ni, self.hw, self.he = slab_extent(ni_g, world, rank)
+        self.lo, self.hi = partition(ni_g, world)[rank]
+        self.nown = self.hi - self.lo + 1
+        self.ctx = BuoyantCavity(ni_g, nj, order="redblack", device=device, nsweep=nswp, ni_local=self.ni, goff=self.goff,
+                                 halo_w=self.hw, halo_e=self.he, **kw)
+        self._finish(nswp)
+
+
 # stages of one outer iteration: ("compute", fn(slab)), ("halo", field, w, e, colour filter), ("halos", ...),
 # ("sweep", field, istart, jstart, colour, first) = colour pass + halo exchange of that colour's edge lines, ("ppref",)
-def iteration_stages(nswp):
+def iteration_stages(nswp, solve_t=False):
     st = [("halos", (("u", 1, 1), ("v", 1, 1), ("p", 1, 0))),
           ("compute", lambda s: s.ctx.assemble_u()), ("halo", "du", 0, 1, None)]
     for name, istart, jstart, n, first in (("u", 3, 2, nswp[0], False), ("v", 2, 3, nswp[1], False), ("pp", 2, 2, nswp[2], True)):
@@ -234,6 +253,11 @@ def iteration_stages(nswp):
                 # colour pass + exchange of the lines of this colour at the slab edges (only they moved)
                 st.append(("sweep", name, istart, jstart, colour, first and k == 0))
     st += [("ppref",), ("compute", lambda s: s.ctx.correct(s.ppref.data_ptr()))]
+    if solve_t:     # calct (buoyancy_cav.f90:358-433): reads the corrected u(i+1), t(i-1 .. i+1)
+        st += [("halos", (("u", 0, 1), ("t", 1, 1))), ("compute", lambda s: s.ctx.assemble_t())]
+        for k in range(nswp[3]):
+            for colour in (0, 1):
+                st.append(("sweep", "t", 2, 2, colour, False))
     return st
 
 
@@ -295,7 +319,7 @@ class SlabCavity(_E2EMixin):
         self.ctx = self.slab.ctx
         if stream is not None:
             self.ctx.set_stream(stream.cuda_stream)
-        self.stages = iteration_stages(self.slab.nswp)
+        self.stages = iteration_stages(self.slab.nswp, getattr(self.slab, "solve_t", False))
         self.overlap = os.environ.get("CFD_B200_OVERLAP", "0") != "0"   # measured: no gain at N=2
         self._comm_stream = None
         self.pref_owner = [r for r, (lo, hi) in enumerate(partition(nicv + 2, self.world)) if lo <= self.slab.ipref <= hi][0]
@@ -405,7 +429,7 @@ class LocalSlabCavity:
         self.world = world
         self.slabs = [(slab_cls or Slab)(nicv, njcv, r, world, **kw) for r in range(world)]
         self.comm = LocalComm(world)
-        self.stages = iteration_stages(self.slabs[0].nswp)
+        self.stages = iteration_stages(self.slabs[0].nswp, getattr(self.slabs[0], "solve_t", False))
         self.comm.exchange_all(self.slabs, "den", HALO_W, HALO_E)
         self.comm.exchange_all(self.slabs, "vis", 1, 1)
 

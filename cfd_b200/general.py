@@ -115,17 +115,20 @@ class GeneralFVM(CavityFVM):
 
     def __init__(self, ni, nj, *, icrd=1, iadv=3, order="redblack", urf=(0.3, 0.3, 0.9, 1.0), nsweep=(3, 3, 3, 3),
                  lsolve_flow=True, lsolve_t=True, ipref=1, jpref=1, xstart=0.0, xend=1.0, ystart=0.0, yend=1.0,
-                 rstart=1.0, device=-1, tdma_m=0):
+                 rstart=1.0, device=-1, tdma_m=0, ni_local=None, goff=0, halo_w=0, halo_e=0):
         self.lib = _lib.load()
-        self.ni, self.nj, self.icrd, self.iadv = ni, nj, icrd, iadv
+        nl = ni if ni_local is None else ni_local           # i-slab: lines goff+1 .. goff+nl of the global ni x nj grid
+        self.ni, self.nj, self.icrd, self.iadv = nl, nj, icrd, iadv
         self.ni_global, self.nicv, self.njcv = ni, ni - 2, nj - 2
         self.ipref, self.jpref = ipref, jpref
         self.imon, self.jmon = ni // 2, nj // 2
-        self.goff = 0
+        self.goff = goff
         self.lsolve_flow, self.lsolve_t = lsolve_flow, lsolve_t
         cfg = CfdConfig()
         cfg.family = _lib.FAMILY_GENERAL
-        cfg.ni, cfg.nj, cfg.iadv = ni, nj, iadv
+        cfg.ni, cfg.nj, cfg.iadv = nl, nj, iadv
+        cfg.goff, cfg.halo_w, cfg.halo_e = goff, halo_w, halo_e
+        cfg.ni_global = ni if ni_local is not None else 0
         cfg.order = _lib.ORDER_SEQUENTIAL if order in ("sequential", "seq", 1) else _lib.ORDER_REDBLACK
         for k in range(4):
             cfg.nswp[k] = nsweep[k]
@@ -136,7 +139,10 @@ class GeneralFVM(CavityFVM):
         self._h = C.c_void_p()
         check(self.lib.cfd_create(C.byref(self._h), C.byref(cfg)))
         self.resor = [0.0] * 4
-        g = grid(ni, nj, xstart, xend, ystart, yend, rstart, icrd)
+        g = grid(ni, nj, xstart, xend, ystart, yend, rstart, icrd)       # global 1-D arrays, O(ni+nj) host logic
+        self.geometry_global = g
+        if ni_local is not None:
+            g = {k: (v[goff:goff + nl].copy() if k in GEOM_I else v) for k, v in g.items()}
         for k, v in g.items():
             setattr(self, k, v)
         self.set_geometry(**g)
@@ -239,17 +245,19 @@ class BuoyantCavity(GeneralFVM):
                          ipref=ni // 2, jpref=nj // 2, **kw)
         nu = pr * alpha
         self.visc, self.cond, self.rgbeta, self.tref = nu, alpha, ra * nu * alpha, 0.5
-        one = np.ones((ni, nj), order="F")
-        t = np.full((ni, nj), self.tref, order="F")
-        t[0, :] = 1.0
-        t[ni - 1, :] = 0.0
+        nl, gi = self.ni, np.arange(self.goff + 1, self.goff + self.ni + 1)      # local lines and their global numbers
+        one = np.ones((nl, nj), order="F")
+        t = np.full((nl, nj), self.tref, order="F")
+        t[gi == 1, :] = 1.0
+        t[gi == ni, :] = 0.0
         self.upload("t", t)
         self.upload("den", one)
         self.upload("cp", one)
-        self.upload("vis", np.full((ni, nj), self.visc, order="F"))
-        gamt = np.full((ni, nj), self.cond, order="F")
-        gamt[1:ni - 1, nj - 1] = 0.0
-        gamt[1:ni - 1, 0] = 0.0
+        self.upload("vis", np.full((nl, nj), self.visc, order="F"))
+        gamt = np.full((nl, nj), self.cond, order="F")
+        inner = (gi >= 2) & (gi <= ni - 1)
+        gamt[inner, nj - 1] = 0.0
+        gamt[inner, 0] = 0.0
         self.upload("gamt", gamt)
         self.set_hook(_lib.EQ_V, _lib.HOOK_BOUSSINESQ, self.rgbeta, self.tref)
 

@@ -67,6 +67,24 @@ def test_local_jslabs_partitioned_thomas(cfd, world, shape):
     g.close()
 
 
+@pytest.mark.parametrize("world,n", [(2, 34), (3, 50), (4, 66)])
+def test_buoyancy_local_slabs_match_single_context(cfd, world, n):
+    """General family (Boussinesq cavity with its temperature equation) cut into i-slabs: same bits as the single
+    red/black context."""
+    from cfd_b200.dist import BuoyancySlab, LocalSlabCavity
+    g = cfd.BuoyantCavity(n, n, order="redblack")
+    s = LocalSlabCavity(n - 2, n - 2, world, slab_cls=BuoyancySlab)
+    for _ in range(3):
+        r1 = g.iterate(3)
+        r2 = s.iterate(3)
+        for a, b in zip(r1[:3], r2):
+            assert abs(a - b) <= 1e-11 * abs(a) + 1e-300
+    for name in ("u", "v", "p", "pp", "t"):
+        assert np.array_equal(s.gather_field(name), g.download(name)), name
+    s.close()
+    g.close()
+
+
 def _nccl_worker(rank, world, port, shape, q, kind="i"):
     import torch
     import torch.distributed as dist
@@ -74,8 +92,10 @@ def _nccl_worker(rank, world, port, shape, q, kind="i"):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        from cfd_b200.dist import JSlabCavity, SlabCavity, TeachSlab
-        if kind == "j":
+        from cfd_b200.dist import BuoyancySlab, JSlabCavity, SlabCavity, TeachSlab
+        if kind == "buoyancy":
+            s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=BuoyancySlab)
+        elif kind == "j":
             s = JSlabCavity(*shape, reynolds=100.0)
         elif kind == "teach":
             s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab)
@@ -89,15 +109,17 @@ def _nccl_worker(rank, world, port, shape, q, kind="i"):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kind", ["i", "j", "teach"])
+@pytest.mark.parametrize("kind", ["i", "j", "teach", "buoyancy"])
 def test_nccl_slabs_match_single_context(cfd, kind):
     import torch
     import torch.multiprocessing as mp
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("needs at least 2 GPUs (run under gpurun --gpus 2)")
-    shape = (96, 130)
-    if kind == "teach":
+    shape = (96, 130) if kind != "buoyancy" else (98, 98)
+    if kind == "buoyancy":
+        g = cfd.BuoyantCavity(*shape, order="redblack")
+    elif kind == "teach":
         g = cfd.TeachFVM(*shape, order="redblack")
     else:
         g = cfd.CavityFVM(*shape, order="redblack")
