@@ -2,6 +2,7 @@
 // context life cycle, host<->device layout conversion, and the composition of the stage kernels into the
 // reference's subroutines calcu / calcv / calcp / lisolv and the outer-loop body.
 #include <cstdarg>
+#include <cmath>
 #include "common.cuh"
 
 using namespace cfd;
@@ -24,6 +25,7 @@ extern "C" const char* cfd_strerror(int s) {
     case CFD_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
     case CFD_ERR_UNSUPPORTED: return "unsupported in this build";
     case CFD_ERR_NOMEM: return "out of device memory";
+    case CFD_ERR_DIVERGED: return "non-finite residual (the iteration diverged or a field holds NaN/Inf)";
     default: return "unknown status";
   }
 }
@@ -736,7 +738,18 @@ extern "C" int cfd_iterate(cfd_ctx* c, int n, double res[8]) {
       if (c->turb.inpro && (rc = cfd_launch_teach_props(c))) return rc;
     }
   }
-  return res ? cfd_residuals(c, res) : CFD_OK;
+  if (!res) return CFD_OK;
+  if ((rc = cfd_residuals(c, res))) return rc;
+  // failure detection: the residual sums are |.|-sums over every cell of their equation
+  const bool turb = is_teach(c) && c->turbulent;
+  const bool used[6] = {flow, flow, flow, temp || (turb && c->turb.incalt), turb && c->turb.incalk, turb && c->turb.incald};
+  for (int k = 0; k < 6; ++k) {
+    if (n > 0 && used[k] && !std::isfinite(res[k])) {
+      cfd_set_error("cfd_iterate: residual of equation %d is not finite after %d passes", k, n);
+      return CFD_ERR_DIVERGED;
+    }
+  }
+  return CFD_OK;
 }
 
 extern "C" int cfd_residuals(cfd_ctx* c, double res[8]) {

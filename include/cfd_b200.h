@@ -27,7 +27,9 @@ typedef enum cfd_status {
   CFD_ERR_CUDA = -2,         /* a CUDA runtime call failed; cfd_last_error() has the text */
   CFD_ERR_NO_DEVICE = -3,    /* no CUDA device: there is NO CPU fallback */
   CFD_ERR_UNSUPPORTED = -4,  /* valid request outside what this build implements */
-  CFD_ERR_NOMEM = -5
+  CFD_ERR_NOMEM = -5,
+  CFD_ERR_DIVERGED = -6      /* cfd_iterate: a residual sum came back NaN/Inf (the sums are |.|-sums over all cells, so any
+                                non-finite field value shows up in them); the fields are left as they are */
 } cfd_status;
 
 /* Which reference program family the context mirrors. */

@@ -299,3 +299,17 @@ def test_long_lines_redblack(cfd, oracle, njcv):
     for a, b in zip(res, o.residuals):
         assert abs(a - b) <= 1e-9 * abs(b)
     g.close()
+
+
+def test_iterate_reports_divergence(cfd):
+    """Failure detection: a non-finite field shows up in the |.|-sums of the residuals, cfd_iterate says so."""
+    g = cfd.CavityFVM(20, 20, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    g.iterate(2)
+    u = g.download("u")
+    u[7, 9] = np.nan
+    g.upload("u", u)
+    with pytest.raises(cfd.CfdError, match="non-finite residual"):
+        g.iterate(1)
+    g.iterate_async(1)          # without a residual read-back nothing is checked (and nothing blocks)
+    g.close()
