@@ -103,13 +103,16 @@ def _rel(a, b):
     return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
 
 
-@pytest.mark.parametrize("shape,order", [((24, 20), "sequential"), ((40, 30), "sequential"), ((40, 30), "redblack")])
-def test_turbulent_trajectory_vs_oracle(cfd, oracle, shape, order):
+@pytest.mark.parametrize("shape,order,viscos", [((24, 20), "sequential", 0.8e-3), ((40, 30), "sequential", 0.8e-3),
+                                                ((40, 30), "redblack", 0.8e-3), ((40, 30), "sequential", 2.0e-5),
+                                                ((40, 30), "redblack", 2.0e-5)])
+def test_turbulent_trajectory_vs_oracle(cfd, oracle, shape, order, viscos):
     """The shipped case (k-epsilon + energy, all incal* on): every field and wall array follows the restatement to
     rounding (log / pow / sqrt of the wall laws come from different math libraries, so not bit for bit)."""
     ni, nj = shape
-    o = oracle.TeachTurb(ni, nj, order=0 if order == "sequential" else 1)
-    g = cfd.TeachFVM(ni, nj, order=order, turbulent=True)
+    # viscos = 2e-5 puts the top-wall y+ above 11.63: the log-law branches of modu / modte / modt are exercised too
+    o = oracle.TeachTurb(ni, nj, order=0 if order == "sequential" else 1, viscos=viscos)
+    g = cfd.TeachFVM(ni, nj, order=order, turbulent=True, viscos=viscos)
     for name in ("vis", "gamh", "te", "ed", "t"):
         assert _rel(g.download(name), getattr(o, name)) < 1e-14, ("initial", name)
     for it in range(4):
@@ -124,6 +127,8 @@ def test_turbulent_trajectory_vs_oracle(cfd, oracle, shape, order):
         assert _rel(g.wall_download(name)[:ni], getattr(o, name)[:ni]) < tol, name
     for name in ("tauw", "xplusw"):
         assert _rel(g.wall_download(name)[:nj], getattr(o, name)[:nj]) < tol, name
+    if viscos < 1e-4 and order == "sequential":
+        assert g.wall_download("yplusn").max() > 11.63 and o.yplusn[:ni].max() > 11.63
     g.close()
 
 

@@ -39,3 +39,30 @@ def test_host_grid_and_init_match_oracle_bitwise(cfd, oracle):
         g = cfd.teach_init(x, y, indcos)
         for k, v in g.items():
             assert np.array_equal(v, getattr(o, k)[:len(v)]), k
+
+
+def test_turbulent_restatement_precisions_agree_and_converge(oracle):
+    """teach_turb.inc (k-epsilon + energy + wall functions): the FP64 oracle and the FP32 build (the reference's own
+    arithmetic) follow the same trajectory to single precision; residuals fall; wall y+ leaves the laminar branch."""
+    import numpy as np
+    o64 = oracle.TeachTurb(40, 30)
+    o32 = oracle.TeachTurb(40, 30, dtype=np.float32)
+    # initial effective viscosity = laminar + turbulent part from the inlet k, eps (props, general.f90:165-190)
+    te0, ed0 = 0.03 * 0.5 ** 2, (0.03 * 0.5 ** 2) ** 1.5 / (0.005 * 0.0124)
+    v0 = 0.7 * (1000.0 * te0 ** 2 * 0.09 / ed0 + 0.8e-3) + 0.3 * 0.8e-3
+    assert abs(o64.vis[5, 5] - v0) < 1e-15
+    r_first = o64.iterate_turb(20)
+    o32.iterate_turb(20)
+    r_last = o64.iterate_turb(80)
+    o32.iterate_turb(80)
+    assert all(np.isfinite(r_last)) and r_last[0] < r_first[0] and r_last[3] < r_first[3]
+    for name in ("u", "te", "t", "vis"):
+        a, b = getattr(o64, name), getattr(o32, name)
+        assert np.abs(a - b).max() <= 2e-5 * np.abs(a).max(), name
+    assert (o64.t >= -1e-9).all() and o64.t.max() <= 100.0 + 1e-9          # between inlet and wall temperature
+    assert o64.te.min() >= 0.0 and (o64.ed[1:-1, 1:-1] > 0).all()
+    assert o64.xplusw[:30].max() > 11.63                                     # step wall: log-law branch already active
+    assert o64.yplusn[1:39].max() < 11.63                                    # top wall: still the laminar branch ...
+    lo = oracle.TeachTurb(40, 30, viscos=2.0e-5)
+    r = lo.iterate_turb(20)
+    assert all(np.isfinite(r)) and lo.yplusn[1:39].max() > 11.63             # ... the log law needs a lower viscosity
