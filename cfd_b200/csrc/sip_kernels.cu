@@ -36,6 +36,9 @@ struct SipParams {
   double* rsm_out;
 };
 
+#ifndef SIP_TIMING
+#define SIP_TIMING 0
+#endif
 #define SIP_W 4              // warps (bands) per block
 #define TS 34                // padded tile stride: the anti-diagonal (lane l at row l, column d-l) sits at 33*l + d -> 32 different banks
 
@@ -85,6 +88,33 @@ __device__ __forceinline__ void tile_store(const double* tl, double* g, int ld, 
   }
 }
 
+// the four operand tiles of a chunk in two round trips: sixteen rows of all four arrays (64 values per lane) are in
+// flight together (one block per SM leaves each thread up to 255 registers)
+__device__ __forceinline__ void tile_load4(double* A, double* B, double* C, double* D, const double* ga, const double* gb,
+                                           const double* gc, const double* gd, int ld, int c0, int jb, int imax, int jmax, int lane) {
+  const int i = c0 + lane;
+  const bool iok = i >= 1 && i <= imax;
+#pragma unroll
+  for (int r0 = 0; r0 < 32; r0 += 16) {
+    double va[16], vb[16], vc[16], vd[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const int j = jb + r0 + r;
+      const bool ok = iok && j >= 1 && j <= jmax;
+      const size_t k = (size_t)j * ld + i;
+      va[r] = ok ? __ldcg(ga + k) : 0.0;
+      vb[r] = ok ? __ldcg(gb + k) : 0.0;
+      vc[r] = ok ? __ldcg(gc + k) : 0.0;
+      vd[r] = ok ? __ldcg(gd + k) : 0.0;
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const int o = (r0 + r) * TS + lane;
+      A[o] = va[r]; B[o] = vb[r]; C[o] = vc[r]; D[o] = vd[r];
+    }
+  }
+}
+
 // PHASE 0: incomplete LU factors (:44-55); 1: forward substitution (:64-65); 2: backward substitution + update (:71-76)
 template <int PHASE>
 __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long epoch_base, int nbands, int nchunks) {
@@ -94,6 +124,8 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
   double *A = t0, *B = A + 32 * TS, *C = B + 32 * TS, *D = C + 32 * TS;   // tiles
   double *row0 = D + 32 * TS, *row1 = row0 + 32, *col0 = row1 + 32, *col1 = col0 + 32;
   const bool fwd = PHASE != 2;
+  long long tm[6] = {0, 0, 0, 0, 0, 0}, tq = 0;
+#define TICK(n) if (SIP_TIMING) { const long long now__ = clock64(); tm[n] += now__ - tq; tq = now__; }
   for (int bb = blockIdx.x * SIP_W + w; bb < nbands; bb += gridDim.x * SIP_W) {
     const int b = fwd ? bb : nbands - 1 - bb;           // band processed (backward: from the top)
     const int jb = 1 + 32 * b;
@@ -103,22 +135,19 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
     for (int cc = 0; cc < nchunks; ++cc) {
       const int c = fwd ? cc : nchunks - 1 - cc;
       const int c0 = 1 + 32 * c;
+      if (SIP_TIMING) tq = clock64();
       // the tile's own operands do not depend on the neighbouring band: fetch them before waiting for it
       if (PHASE == 1) {
-        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(B, P.ls, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(C, P.lw, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(D, P.lpr, P.ld, c0, jb, imax, jmax, lane);
+        tile_load4(A, B, C, D, P.res, P.ls, P.lw, P.lpr, P.ld, c0, jb, imax, jmax, lane);
       } else if (PHASE == 2) {
-        tile_load(A, P.res, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(B, P.un, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(C, P.ue, P.ld, c0, jb, imax, jmax, lane);
-        tile_load(D, P.phi, P.ld, c0, jb, imax, jmax, lane);
+        tile_load4(A, B, C, D, P.res, P.un, P.ue, P.phi, P.ld, c0, jb, imax, jmax, lane);
       }
+      TICK(0)
       if (bb > 0) {                                     // the band processed just before this one (other warp/block)
         const int dep = fwd ? b - 1 : b + 1;
         if (!wait_band(P, dep, epoch_base + (unsigned long long)cc + 1)) return;
       }
+      TICK(1)
       // row just outside the tile in the sweep direction (south for forward phases, north for backward)
       {
         const int jn = fwd ? jb - 1 : jb + 32, i = c0 + lane;
@@ -131,13 +160,13 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
         }
       }
       __syncwarp();
-      for (int d = 0; d < 63; ++d) {
-        const int r = fwd ? lane : 31 - lane;           // row inside the tile
-        const int q = fwd ? d - lane : 31 - (d - lane); // column inside the tile
-        const bool act = (d - lane) >= 0 && (d - lane) < 32 && (c0 + q) <= imax && (jb + r) <= jmax;
-        if (act) {
-          const int k = r * TS + q;
-          if (PHASE == 0) {
+      TICK(2)
+      if (PHASE == 0) {
+        for (int d = 0; d < 63; ++d) {
+          const int r = lane, q = d - lane;               // row / column inside the tile
+          const bool act = q >= 0 && q < 32 && (c0 + q) <= imax && (jb + r) <= jmax;
+          if (act) {
+            const int k = r * TS + q;
             // west / south neighbours of the factors un, ue
             const double un_w = (q == 0) ? col0[r] : A[k - 1], ue_w = (q == 0) ? col1[r] : B[k - 1];
             const double un_s = (r == 0) ? row0[q] : A[k - TS], ue_s = (r == 0) ? row1[q] : B[k - TS];
@@ -157,18 +186,47 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
             D[k] = ls;
             // lpr goes straight to global memory (a fifth tile would not fit the budget)
             P.lpr[kg] = lpr;
-          } else if (PHASE == 1) {
-            const double rs = (r == 0) ? row0[q] : A[k - TS], rw = (q == 0) ? col0[r] : A[k - 1];
-            A[k] = __dmul_rn(__dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], rs)), __dmul_rn(C[k], rw)), D[k]);
-          } else {
-            const double rn = (r == 31) ? row0[q] : A[k + TS], re = (q == 31) ? col0[r] : A[k + 1];
-            const double v = __dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], rn)), __dmul_rn(C[k], re));
-            A[k] = v;
-            D[k] = __dadd_rn(D[k], v);
+          }
+          __syncwarp();
+        }
+      } else {
+        // Forward / backward substitution: lane = row, marching along the columns one step behind the lane before it.
+        // The two recurrence inputs never touch shared memory: the value of the previous row at this column is what
+        // the neighbouring lane produced one step ago (shuffle), the value of the previous column is this lane's own
+        // last result (register).  Shared memory only supplies the cell's operands and receives the result.
+        double last = 0.0;
+        // per-lane constants of the skewed walk: the lane is active for d in [lane, dhi]; its cell at step d sits at
+        // kb + d (forward) / kb - d (backward) in the tile, the row-0 / column-0 inputs likewise
+        const int r = fwd ? lane : 31 - lane;
+        int ncol = imax - c0 + 1;                          // valid columns of this chunk
+        if (ncol > 32) ncol = 32;
+        const bool rowok = (jb + r) <= jmax;
+        // forward: q = d - lane valid for q < ncol; backward: q = 31 - (d - lane) valid for q < ncol <=> d - lane > 31 - ncol
+        const int dlo = fwd ? lane : lane + (32 - ncol);
+        const int dhi = rowok ? (fwd ? lane + ncol - 1 : lane + 31) : -1;
+        const int kb = fwd ? r * TS - lane : r * TS + 31 + lane;
+        const double cin = col0[r];
+#pragma unroll
+        for (int d = 0; d < 63; ++d) {
+          const double from_row = __shfl_up_sync(0xffffffffu, last, 1);
+          if (d >= dlo && d <= dhi) {
+            const int k = fwd ? kb + d : kb - d;
+            const int q = fwd ? d - lane : 31 + lane - d;
+            const double nb_row = (lane == 0) ? row0[q] : from_row;              // south (forward) / north (backward)
+            const double nb_col = (d == lane) ? cin : last;                      // west (forward) / east (backward)
+            if (PHASE == 1) {
+              last = __dmul_rn(__dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], nb_row)), __dmul_rn(C[k], nb_col)), D[k]);
+              A[k] = last;
+            } else {
+              last = __dsub_rn(__dsub_rn(A[k], __dmul_rn(B[k], nb_row)), __dmul_rn(C[k], nb_col));
+              A[k] = last;
+              D[k] = __dadd_rn(D[k], last);
+            }
           }
         }
         __syncwarp();
       }
+      TICK(3)
       // keep the column next to the following chunk, write the tile back, publish
       {
         const int qe = fwd ? 31 : 0;
@@ -186,11 +244,17 @@ __device__ void sip_wavefront(const SipParams& P, double* sm, unsigned long long
         tile_store(A, P.res, P.ld, c0, jb, imax, jmax, lane);
         tile_store(D, P.phi, P.ld, c0, jb, imax, jmax, lane);
       }
+      TICK(4)
       __threadfence();
       __syncwarp();
       if (lane == 0) st_release(P.prog + b, epoch_base + (unsigned long long)cc + 1);
+      TICK(5)
     }
+    if (SIP_TIMING && lane == 0 && (bb == 1 || bb == nbands / 2) && epoch_base / ((unsigned long long)nchunks + 1) == (PHASE == 1 ? 6 : 7))
+      printf("SIP phase %d band %d: loads %lld wait %lld row0 %lld steps %lld stores %lld fence+flag %lld cycles over %d chunks\n",
+             PHASE, bb, tm[0], tm[1], tm[2], tm[3], tm[4], tm[5], nchunks);
   }
+#undef TICK
 }
 
 __global__ void __launch_bounds__(32 * SIP_W) k_sip_solve(const SipParams P) {
