@@ -83,6 +83,13 @@ class TorchDistComm:
     def broadcast(self, t, src):
         self.dist.broadcast(t, src=src)
 
+    def allgather(self, dst, src):
+        """dst[r] = rank r's src (dst contiguous, [world, ...]).  One fused call over NCCL; gloo has no tensor form."""
+        if self.dist.get_backend() == "nccl":
+            self.dist.all_gather_into_tensor(dst, src)
+        else:
+            self.dist.all_gather(list(dst.unbind(0)), src)
+
 
 def colour_filter(lo: int, hi: int, istart: int, colour: int):
     """After the colour pass `colour` of a sweep starting at line istart only lines with (i-istart)%2 == colour
@@ -756,7 +763,7 @@ class JSlabCavity(_JSlabEngine, _E2EMixin):
 
     def gather(self, pairs):
         for src, dst in pairs:
-            self.dist.all_gather_into_tensor(dst, src)
+            self.comm.allgather(dst, src)
 
     def rows(self, spec):
         s, ops, todo = self.slab, [], []
@@ -792,7 +799,7 @@ class JSlabCavity(_JSlabEngine, _E2EMixin):
             self._rb = {}
         if key not in self._rb:
             t = self.torch
-            self._rb[key] = t.zeros((2, self.slab.ni), dtype=t.float64, device="cuda")
+            self._rb[key] = t.zeros((2, self.slab.ni), dtype=t.float64, device=getattr(self, "_device", "cuda"))
         return self._rb[key]
 
     def _global_cells(self):

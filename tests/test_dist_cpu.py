@@ -166,3 +166,68 @@ def test_partition_method_algebra(world):
     got = np.concatenate([Y[r] + (W[r] * x[2 * (r - 1) + 1] if r > 0 else 0.0) + (Z[r] * x[2 * (r + 1)] if r < world - 1 else 0.0)
                           for r in range(world)])
     assert np.abs(got - want).max() < 1e-13
+
+
+# ---- j-slab driver plumbing over gloo: halo ROWS (packed / unpacked through the context) and the all-gathers ------------
+class _StubCtx:
+    """Stands in for the CUDA context: fields are host arrays (ni, nj_local), rows_pack / rows_unpack move rows
+    j_first .. j_first+n-1 (1-based) to / from a [n, ni] buffer given by address, like cfd_rows_pack / cfd_rows_unpack."""
+
+    def __init__(self, fields):
+        self.f = fields
+
+    def rows_pack(self, name, j_first, nrows, ptr):
+        import ctypes
+        rows = np.ascontiguousarray(self.f[name][:, j_first - 1:j_first - 1 + nrows].T)
+        ctypes.memmove(ptr, rows.ctypes.data, rows.nbytes)
+
+    def rows_unpack(self, name, j_first, nrows, ptr):
+        import ctypes
+        ni = self.f[name].shape[0]
+        buf = np.empty((nrows, ni))
+        ctypes.memmove(buf.ctypes.data, ptr, buf.nbytes)
+        self.f[name][:, j_first - 1:j_first - 1 + nrows] = buf.T
+
+
+def _jslab_worker(rank, world, port, ni, nj):
+    from types import SimpleNamespace
+    from cfd_b200.dist import JSlabCavity, jslab_extent
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(11)
+        glob = {n: rng.random((ni, nj)) for n in ("u", "p", "dv")}
+        joff, njl, hs, hn = jslab_extent(nj, world, rank)
+        lo, hi = partition(nj, world)[rank]
+        nown = hi - lo + 1
+        loc = {n: np.full((ni, njl), -1.0) for n in glob}
+        for n in glob:
+            loc[n][:, hs:hs + nown] = glob[n][:, lo - 1:hi]            # owned rows only; halo rows unknown
+        drv = object.__new__(JSlabCavity)                              # the driver's communication methods, no CUDA
+        drv.torch, drv.dist, drv.comm, drv._device = torch, dist, TorchDistComm(), "cpu"
+        drv.slab = SimpleNamespace(rank=rank, world=world, ni=ni, hs=hs, hn=hn, nown=nown, ctx=_StubCtx(loc))
+        drv.rows((("u", 1, 1), ("p", 1, 0)))
+        drv.rows((("dv", 0, 1),))
+        for n, (ns, nn) in (("u", (1, 1)), ("p", (1, 0)), ("dv", (0, 1))):
+            want = np.full((ni, njl), -1.0)
+            want[:, hs:hs + nown] = glob[n][:, lo - 1:hi]
+            if rank > 0 and ns:
+                want[:, hs - 1] = glob[n][:, lo - 2]
+            if rank < world - 1 and nn:
+                want[:, hs + nown] = glob[n][:, hi]
+            assert np.array_equal(loc[n], want), (rank, n)
+        # the two all-gathers of the partition method: [ni, 4] spike ends, [nlines, 2] piece ends, in rank order
+        wz_local = torch.full((ni, 4), float(rank + 1), dtype=torch.float64)
+        wz_all = torch.zeros((world, ni, 4), dtype=torch.float64)
+        y_local = torch.arange(10, dtype=torch.float64).reshape(5, 2) + 100 * rank
+        y_all = torch.zeros((world, 5, 2), dtype=torch.float64)
+        drv.gather([(wz_local, wz_all), (y_local, y_all)])
+        for r in range(world):
+            assert bool((wz_all[r] == r + 1).all()) and y_all[r, 0, 0].item() == 100 * r
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_jslab_rows_and_gathers_gloo(world):
+    mp.spawn(_jslab_worker, args=(world, _free_port(), 9, 31), nprocs=world, join=True)
