@@ -13,7 +13,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import CfdConfig, CfdHookDesc, FIELD_ID, GEOM_ID, check
+from ._lib import CfdConfig, CfdHookDesc, check
 from .cavity import CavityFVM
 
 GEOM_I = ("x", "xu", "xdif", "sew", "sewu", "xcvi", "xcvip", "fx", "fxm")

@@ -4,7 +4,6 @@ SURVEY 8(d) algorithmic bytes (1224 B and 1056 B per cell and outer iteration)."
 import json
 import os
 import sys
-import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
