@@ -147,6 +147,37 @@ def test_buoyancy_130_trajectory_redblack(cfd, oracle):
     g.close()
 
 
+def test_full_size_8194_buoyancy_properties(cfd):
+    """BASELINE.json configs[3] size (8192^2 CV): no CPU answer exists here, so check size-independent properties:
+    finite fields, Dirichlet T walls and no-slip walls untouched, p(ipref,jpref) stays the reference 0, the hot wall
+    heats its neighbours and nothing leaves [0,1] by more than rounding of the hybrid scheme, and the C-ABI
+    subroutine path (calcu+calcv+calcp+calct) gives the same bits as cfd_iterate."""
+    n = 8194
+    g = cfd.BuoyantCavity(n, n, order="redblack")
+    r1 = g.iterate(1)
+    r4 = g.iterate(3)
+    assert np.isfinite(r1).all() and np.isfinite(r4).all()
+    t = g.download("t")
+    assert np.isfinite(t).all()
+    assert np.all(t[0, :] == 1.0) and np.all(t[-1, :] == 0.0)
+    assert t[1, 1:-1].min() > 0.5 and t[-2, 1:-1].max() < 0.5          # conduction has started at both walls
+    assert t.min() >= -1e-9 and t.max() <= 1.0 + 1e-9
+    for name in ("u", "v"):
+        a = g.download(name)
+        assert np.isfinite(a).all()
+        assert not a[0, :].any() and not a[-1, :].any() and not a[:, 0].any() and not a[:, -1].any(), name
+    v = g.download("v")
+    assert v[2, n // 2] > 0.0 and v[-2, n // 2] < 0.0                   # up the hot wall, down the cold one
+    assert g.probe("p", g.ipref, g.jpref) == 0.0
+    del a, v
+    h = cfd.BuoyantCavity(n, n, order="redblack")
+    for _ in range(4):
+        h.calcu(); h.calcv(); h.calcp(); h.calct()
+    assert np.array_equal(h.download("t"), t)
+    assert np.array_equal(h.download("u"), g.download("u"))
+    g.close(); h.close()
+
+
 def test_general_rejects_what_the_reference_cannot_do(cfd):
     with pytest.raises(cfd.CfdError, match="ni == nj"):
         cfd.GeneralFVM(40, 30, lsolve_flow=True)
