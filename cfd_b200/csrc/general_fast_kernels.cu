@@ -10,50 +10,9 @@
 // contract into FMAs, and the equations are stored divided by ap (nc = 5).  Differences from the bit-exact kernels
 // are a few ulps per coefficient; the sequential-order mode keeps using general_kernels.cu.
 #include "common.cuh"
+#include "general_fast.cuh"
 
 namespace cfd {
-
-struct GenFastParams {
-  Layout L;
-  int ia, ib, jlo, jhi;
-  int goff, NI;              // i-slabs: global 1-based i of local line i0 is i0 + 1 + goff; NI = global ni
-  int iadv;
-  double urf;
-  int boussinesq;
-  double rgbeta, tref;
-  const double *u, *v, *p, *t, *den, *gam, *cp, *du_in, *dv_in, *su_src, *sp_src;
-  double *ae, *aw, *an, *as, *su, *dout;
-  // by-i (natural order)
-  const double *sew, *sewu, *xcvi, *xcvip, *fx, *r_sew, *r_xdif;
-  // by-j (line layout)
-  const double *arx, *arxj, *arxjp, *r, *rmn, *fy, *fvp, *ycvr, *ycvrs, *sns, *r_sx, *r_ydif, *r_sxmn, *r_sns;
-  double* partial;
-};
-
-__device__ __forceinline__ double gf_max(double a, double b) { return a > b ? a : b; }
-__device__ __forceinline__ double gf_rcp(double x) {
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-  r = fma(fma(-x, r, 1.0), r, r);
-  r = fma(fma(-x, r, 1.0), r, r);
-  return r;
-}
-__device__ __forceinline__ double gf_arim(double a, double b, double w) { return fma(b - a, w, a); }
-__device__ __forceinline__ double gf_harm(double a, double b, double w) { return a * b * gf_rcp(fma(b - a, w, a)); }
-__device__ __forceinline__ double gf_dapec(double flow, double diff, int iadv) {
-  if (flow == 0.0) return diff;
-  switch (iadv) {
-    case 1: return fma(-0.5, fabs(flow), diff);
-    case 2: return diff;
-    case 3: return gf_max(0.0, fma(-0.5, fabs(flow), diff));
-    case 4: {
-      const double q = 1.0 - 0.1 * fabs(flow / diff);
-      const double q2 = q * q;
-      return gf_max(0.0, q2 * q2 * q) * diff;
-    }
-    default: return diff;
-  }
-}
 
 __device__ __forceinline__ void gf_block_sum(double v, double* partial) {
   __shared__ double wsum[32];
@@ -87,32 +46,7 @@ __device__ __forceinline__ void gf_block_sum(double v, double* partial) {
     rAPout = rAP__;                              \
   }
 
-// ---- u: buoyancy_cav.f90:135-194 ----------------------------------------------------------------------------
-// y-face between rows lo (j) and hi (j+1) of the u-cell column i: flow and diffusion conductance
-__device__ __forceinline__ void gf_u_face_y(double Dc_lo, double Dc_hi, double Dw_lo, double Dw_hi, double Gc_lo, double Gc_hi,
-                                            double Gw_lo, double Gw_hi, double Vc, double Vw, double xcvi, double xcvip,
-                                            double fy_h, double rmn_h, double rydif_h, double r_lo, double r_hi,
-                                            bool south_b, bool north_b, int iadv, double& flow, double& acof) {
-  double fl, flm, diff;
-  if (north_b) {          // hi is the wall row nj (:163-166)
-    fl = xcvi * Vc * Dc_hi;
-    flm = xcvip * Vw * Dw_hi;
-    diff = r_hi * (xcvi * Gc_hi + xcvip * Gw_hi) * rydif_h;
-    flow = rmn_h * (fl + flm);
-  } else if (south_b) {   // lo is the wall row 1 (:135-142)
-    fl = xcvi * Vc * Dc_lo;
-    flm = xcvip * Vw * Dw_lo;
-    diff = r_lo * (xcvi * Gc_lo + xcvip * Gw_lo) * rydif_h;
-    flow = r_lo * (fl + flm);
-  } else {
-    fl = xcvi * Vc * gf_arim(Dc_lo, Dc_hi, fy_h);
-    flm = xcvip * Vw * gf_arim(Dw_lo, Dw_hi, fy_h);
-    diff = rmn_h * (gf_harm(Gc_lo, Gc_hi, fy_h) * xcvi + gf_harm(Gw_lo, Gw_hi, fy_h) * xcvip) * rydif_h;
-    flow = rmn_h * (fl + flm);
-  }
-  acof = gf_dapec(flow, diff, iadv);
-}
-
+// ---- u: buoyancy_cav.f90:135-194 (y-face helper gf_u_face_y in general_fast.cuh) ---------------------------
 __global__ void __launch_bounds__(128, 4) k_gen_assemble_u_fast(const GenFastParams P) {
   const int M = P.L.M, T = P.L.T, nj = P.L.nj, ni = P.L.ni;
   const long long LD = P.L.LD;
@@ -574,13 +508,13 @@ __global__ void __launch_bounds__(128, 4) k_gen_assemble_t_fast(const GenFastPar
 using namespace cfd;
 
 // Reciprocal geometry, rebuilt from the host copies whenever the geometry changed (shares cfd_ctx::tfast with the
-// TEACH family -- a context belongs to one family): [0] 1/sew(i), [1] 1/xdif(i); [6..9] 1/sx, 1/ydif, 1/sxmn, 1/sns (j).
+// TEACH family -- a context belongs to one family): [0] 1/sew(i), [1] 1/xdif(i); [6..10] 1/sx, 1/ydif, 1/sxmn, 1/sns, r/sns (j).
 static int ensure_gen_fast(cfd_ctx* c) {
   if (c->tfast_ready) return CFD_OK;
   const int ni = c->L.ni, nj = c->L.nj;
   auto inv = [](double d) { return d != 0.0 ? 1.0 / d : 0.0; };
   auto& G = c->geom_host;
-  std::vector<double> bi[2], bj[4];
+  std::vector<double> bi[2], bj[5];
   for (auto& v : bi) v.assign((size_t)ni + 2, 0.0);
   for (auto& v : bj) v.assign((size_t)c->L.LD, 0.0);
   for (int i = 0; i < ni; ++i) {
@@ -593,13 +527,14 @@ static int ensure_gen_fast(cfd_ctx* c) {
     bj[1][q] = inv(G[CFD_G_YDIF][j]);
     bj[2][q] = inv(G[CFD_G_SXMN][j]);
     bj[3][q] = inv(G[CFD_G_SNS][j]);
+    bj[4][q] = G[CFD_G_R][j] * bj[3][q];
   }
   CFD_CUDA(cudaSetDevice(c->device));
   for (int g = 0; g < 2; ++g) {
     if (!c->tfast[g]) CFD_CUDA(cudaMalloc(&c->tfast[g], bi[g].size() * sizeof(double)));
     CFD_CUDA(cudaMemcpyAsync(c->tfast[g], bi[g].data(), bi[g].size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   }
-  for (int g = 0; g < 4; ++g) {
+  for (int g = 0; g < 5; ++g) {
     if (!c->tfast[6 + g]) CFD_CUDA(cudaMalloc(&c->tfast[6 + g], bj[g].size() * sizeof(double)));
     CFD_CUDA(cudaMemcpyAsync(c->tfast[6 + g], bj[g].data(), bj[g].size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   }
@@ -625,7 +560,7 @@ int cfd_launch_general_assemble_fast(cfd_ctx* c, int which, double* partial) {
   P.arx = c->geom[CFD_G_ARX]; P.arxj = c->geom[CFD_G_ARXJ]; P.arxjp = c->geom[CFD_G_ARXJP]; P.r = c->geom[CFD_G_R];
   P.rmn = c->geom[CFD_G_RMN]; P.fy = c->geom[CFD_G_FY]; P.fvp = c->geom[CFD_G_FVP]; P.ycvr = c->geom[CFD_G_YCVR];
   P.ycvrs = c->geom[CFD_G_YCVRS]; P.sns = c->geom[CFD_G_SNS];
-  P.r_sx = c->tfast[6]; P.r_ydif = c->tfast[7]; P.r_sxmn = c->tfast[8]; P.r_sns = c->tfast[9];
+  P.r_sx = c->tfast[6]; P.r_ydif = c->tfast[7]; P.r_sxmn = c->tfast[8]; P.r_sns = c->tfast[9]; P.r_rsns = c->tfast[10];
   const int ni = c->L.ni, nj = c->L.nj;
   P.goff = c->cfg.goff;
   P.NI = c->cfg.ni_global ? c->cfg.ni_global : ni;
@@ -651,6 +586,7 @@ int cfd_launch_general_assemble_fast(cfd_ctx* c, int which, double* partial) {
   P.partial = partial;
   const int nlines = P.ib - P.ia + 1;
   if (nlines <= 0) return 0;          // a slab that owns none of this equation's lines
+  if (cfd_general_tma_eligible(c, which)) return cfd_launch_general_assemble_tma(c, which, P);
   dim3 block(32, 4), grid((c->L.T + 31) / 32, (nlines + 3) / 4);
   const int nblocks = grid.x * grid.y;
   if (nblocks > c->max_partials) {

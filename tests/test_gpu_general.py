@@ -99,8 +99,20 @@ def test_buoyancy_trajectory_sequential_bitwise(cfd, oracle, n):
 def test_buoyancy_production_assembly_vs_oracle(cfd, oracle, n, iadv):
     """Red/black contexts use general_fast_kernels.cu and store the equations divided by ap: every coefficient must
     equal the oracle's coefficient / ap to rounding (same randomised fields as the bitwise test)."""
+    check_production_assembly(cfd, oracle, n, iadv)
+
+
+@pytest.mark.parametrize("n,tdma_m", [(2100, 16), (5200, 13)])
+@pytest.mark.parametrize("iadv", [3, 4])
+def test_buoyancy_tma_assembly_vs_oracle(cfd, oracle, n, tdma_m, iadv):
+    """Long lines take the TMA-staged kernels of general_tma_kernels.cu (T = 160 consumer threads in the 384-thread
+    build, T = 416 in the 768-thread one): same check as above."""
+    check_production_assembly(cfd, oracle, n, iadv, tdma_m=tdma_m)
+
+
+def check_production_assembly(cfd, oracle, n, iadv, **kw):
     o = oracle.General("buoyancy", ni=n, nj=n, iadv=iadv)
-    g = cfd.BuoyantCavity(n, n, iadv=iadv, order="redblack")
+    g = cfd.BuoyantCavity(n, n, iadv=iadv, order="redblack", **kw)
     randomise_buoyancy(o, g, 3 + iadv)
     sl_u = (slice(2, n - 1), slice(1, n - 1))
     sl_v = (slice(1, n - 1), slice(2, n - 1))

@@ -1,0 +1,53 @@
+"""Times the four production assembly launches of the general family alone (buoyancy cavity, n x n nodes) and checks
+that cfd_iterate and the subroutine path give the same bits.  Usage: python tools/bench_gen_assemble.py [n] [check]"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+import cfd_b200
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 8194
+    g = cfd_b200.BuoyantCavity(n, n, order="redblack")
+    g.iterate(3)
+    out = {"n": n, "tma": os.environ.get("CFD_B200_GEN_TMA", "1"), "stages": os.environ.get("CFD_B200_ASM_STAGES", "")}
+    cells = (n - 2) ** 2
+    for name in ("u", "v", "p", "t"):
+        fn = getattr(g, "assemble_" + name)
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(10):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        us = a.elapsed_time(b) * 100.0
+        out[name + "_us"] = round(us, 1)
+        out[name + "_B_per_cell_at_7TBs"] = round(us * 1e-6 * 7.0e12 / cells, 1)
+    print(json.dumps(out))
+    if len(sys.argv) > 2:
+        g.close()
+        g = cfd_b200.BuoyantCavity(n, n, order="redblack")
+        h = cfd_b200.BuoyantCavity(n, n, order="redblack")
+        for it in range(4):
+            g.iterate(1)
+            h.calcu(); h.calcv(); h.calcp(); h.calct()
+            for name in ("u", "v", "p", "t"):
+                a, b = g.download(name), h.download(name)
+                d = np.argwhere(a != b)
+                if len(d):
+                    print("iteration", it + 1, name, "differs in", len(d), "nodes; first", d[:5].tolist(),
+                          "max abs", float(np.abs(a - b).max()), "values", float(a[tuple(d[0])]), float(b[tuple(d[0])]), "i range", int(d[:, 0].min()), int(d[:, 0].max()),
+                          "j range", int(d[:, 1].min()), int(d[:, 1].max()))
+        print("check done")
+
+
+if __name__ == "__main__":
+    main()
