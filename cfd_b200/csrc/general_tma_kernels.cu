@@ -1,15 +1,18 @@
 // general_tma_kernels.cu -- TMA-staged production assembly of the general family's equations
-// (calcu buoyancy-driven-cavity-2d/buoyancy_cav.f90:122-198, calcv :200-277, calct :358-428; same arithmetic and
-// the same reference quirks as general_fast_kernels.cu, which remains the path for short lines and j-slabs).
+// (calcu buoyancy-driven-cavity-2d/buoyancy_cav.f90:122-198, calcv :200-277, calcp :279-343, calct :358-428; same
+// arithmetic and the same reference quirks as general_fast_kernels.cu, which remains the path for short lines and
+// j-slabs).
 //
 // The register-window kernels issue the loads of one node row per loop trip and wait for them: ~70 KB per SM in
-// flight, 40 % of the HBM roofline at 8192^2.  Here, as in cavity_tma_kernels.cu, one persistent block per SM owns
-// whole S-N lines; producer warps stream, per node slice k of the line, every array slice the stencil touches into
-// a shared-memory ring with 1-D bulk copies (TMA) completing on mbarriers, slices ahead and across line ends; the
-// T consumer threads read each staged value once, keep the j windows in registers (the cell of slice k-1 is
-// evaluated when slice k has arrived, because its north face needs row k) and store the five normalised
-// coefficients and du/dv coalesced.  The chunk-edge neighbours (two per thread and line) come from global memory,
-// fetched one line ahead.  The 1-D j geometry (line layout, same for every line) is read through L1.
+// flight, 40 % of the HBM roofline at 8192^2.  Here, as in cavity_tma_kernels.cu, persistent blocks own whole S-N
+// lines (or an aligned part of every slice of them, see GT_RING_SETUP); producer warps stream, per node slice k of
+// the line, every array slice the stencil touches into a shared-memory ring with 1-D bulk copies (TMA) completing
+// on mbarriers, slices ahead and across line ends; the consumer threads read each staged value once and store the
+// five normalised coefficients and du/dv coalesced.  The north face of a cell needs the row above it: the kernels
+// stage that row a second time beside the row itself ("north copies", L2 hits), finish the cell of
+// slice k when slice k arrives and carry only the south-looking windows (so does the u kernel, with seven copies).  The
+// chunk-edge neighbours (two rows per thread and line) come from global memory, fetched one line ahead.  The 1-D
+// j geometry (line layout, same for every line) is read through L2 one slice ahead.
 #include "common.cuh"
 #include "general_fast.cuh"
 #include "tma.cuh"
@@ -60,12 +63,18 @@ __device__ __forceinline__ void gt_consumer_sum(double v, double* red, int T, in
   __syncthreads();                                                                   \
   const int nlines = P.ib - P.ia + 1;
 
-// Producer loop: the variadic part declares `const double* src[NARR]` for line i0.
-#define GT_PRODUCE(NARR, ...)                                                                         \
+// Producer loop.  NORTH_MASK: arrays that are another array one row north (their src pointer is already advanced by
+// T; not copied in the last slice, whose row north is not 16-byte aligned in the layout -- the consumers take it
+// from global memory).  ABSENT_MASK: optional arrays this launch does not have.  The variadic part declares
+// `const double* src[NARR]` for line i0.  The wait on a free slot backs off with nanosleep: a spinning producer
+// warp took a fifth of the block's issue slots.
+#define GT_PRODUCE(NARR, NORTH_MASK, ABSENT_MASK, ...)                                                 \
   if (tid >= TT) {                                                                                     \
     if (((tid - TT) & 31) == 0) {                                                                      \
       const int pw = (tid - TT) >> 5;                                                                  \
       const unsigned sb = (unsigned)(TT * sizeof(double));                                             \
+      const unsigned absent = (ABSENT_MASK);                                                           \
+      const int n_all = (NARR) - __popc(absent), n_last = n_all - __popc((NORTH_MASK) & ~absent);      \
       unsigned rs = 0, rph = 0;                                                                        \
       for (int line = bline; line < nlines; line += lstride) {                                         \
         const long long i0 = P.ia + line;                                                              \
@@ -73,12 +82,15 @@ __device__ __forceinline__ void gt_consumer_sum(double v, double* red, int T, in
         for (int k = 0; k < M; ++k) {                                                                  \
           const unsigned s = rs, ph = rph;                                                             \
           if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }                                              \
-          mbar_wait(empty0 + 8 * s, ph ^ 1u);                                                          \
+          mbar_wait_backoff(empty0 + 8 * s, ph ^ 1u);                                                  \
           const unsigned fb = full0 + 8 * s;                                                           \
           const unsigned dst = smem_u32(ring + (size_t)s * SW);                                        \
-          if (pw == 0) mbar_expect_tx(fb, (NARR) * sb);                                                \
+          const bool last = k + 1 >= M;                                                                \
+          const unsigned skip = absent | (last ? (unsigned)(NORTH_MASK) : 0u);                         \
+          if (pw == 0) mbar_expect_tx(fb, (last ? n_last : n_all) * sb);                               \
           _Pragma("unroll") for (int a = 0; a < (NARR); ++a)                                           \
-            if ((a % GT_PRODUCER_WARPS) == pw) tma_load_1d(dst + a * sb, src[a] + (size_t)k * T + toff, sb, fb); \
+            if ((a % GT_PRODUCER_WARPS) == pw && !((skip >> a) & 1u))                                  \
+              tma_load_1d(dst + a * sb, src[a] + (size_t)k * T + toff, sb, fb);                        \
         }                                                                                              \
       }                                                                                                \
     }                                                                                                  \
@@ -95,162 +107,148 @@ __device__ __forceinline__ void gt_consumer_sum(double v, double* red, int T, in
 
 // =====================================================================================================
 // u-momentum (buoyancy_cav.f90:135-194).
-// Stage layout (T doubles each): 0 uC 1 vW 2 vC 3 dW 4 dC 5 gW 6 gC | 7 uW 8 uE 9 dWW 10 dE 11 pW 12 pC
-//   arrays 0-6 are needed one row ahead (north face), 7-12 only at the cell itself (held for one slice).
+// Stage layout (TT doubles each): 0 uC 1 dW 2 dC 3 gW 4 gC | 5 uW 6 uE 7 dWW 8 dE 9 pW 10 pC |
+//   north copies 11 uN 12 vWN 13 vCN 14 dWN 15 dCN 16 gWN 17 gCN
+//   Only the south face (aS) and u(j-1) are carried from cell to cell.  The two faces at the chunk ends (south of
+//   the first cell, north of the last) are evaluated from global memory one line ahead.
+//   (A variant that staged each row once and evaluated the cell of slice k-1 when slice k had arrived was 7 %
+//   faster but not reproducible from launch to launch in the one warp of a line that holds padding nodes; it was
+//   dropped.)
 // =====================================================================================================
-#define GT_NU 13
+#define GT_NU 18
+#define GT_NU_NORTH 0x3F800u
+struct GtUEdge { double aS, us, flowN, acofN, uN; };
+
 __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastParams P, const int S, const int NSPLIT) {
   GT_RING_SETUP(GT_NU)
-  GT_PRODUCE(GT_NU,
-             const double* src[GT_NU] = {P.u + i0 * LD,         P.v + (i0 - 1) * LD,   P.v + i0 * LD,
-                                         P.den + (i0 - 1) * LD, P.den + i0 * LD,       P.gam + (i0 - 1) * LD,
-                                         P.gam + i0 * LD,       P.u + (i0 - 1) * LD,   P.u + (i0 + 1) * LD,
-                                         P.den + (i0 - 2) * LD, P.den + (i0 + 1) * LD, P.p + (i0 - 1) * LD,
-                                         P.p + i0 * LD};)
+  GT_PRODUCE(GT_NU, GT_NU_NORTH, 0u,
+             const double* src[GT_NU] = {P.u + i0 * LD,           P.den + (i0 - 1) * LD,     P.den + i0 * LD,
+                                         P.gam + (i0 - 1) * LD,   P.gam + i0 * LD,           P.u + (i0 - 1) * LD,
+                                         P.u + (i0 + 1) * LD,     P.den + (i0 - 2) * LD,     P.den + (i0 + 1) * LD,
+                                         P.p + (i0 - 1) * LD,     P.p + i0 * LD,             P.u + i0 * LD + T,
+                                         P.v + (i0 - 1) * LD + T, P.v + i0 * LD + T,         P.den + (i0 - 1) * LD + T,
+                                         P.den + i0 * LD + T,     P.gam + (i0 - 1) * LD + T, P.gam + i0 * LD + T};)
   // ---- consumers
-  const int t = toff + tid, lane = tid & 31;     // t: position inside a slice; tid: position inside the staged part
+  const int t = toff + tid, lane = tid & 31;
   const int j0base = t * M;
-  const bool hasprev = j0base >= 1, hasnext = j0base + M < nj;
-  const int qprev = (M - 1) * T + t - 1, qnext = t + 1;
+  const bool hasprev = j0base >= 1 && j0base < nj, hasnext = j0base + M < nj;
+  const int qprev = (M - 1) * T + t - 1, qnext = t + 1, qlast = (M - 1) * T + t;
   const int iadv = P.iadv, ni = P.L.ni;
   const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
   double racc = 0.0;
   unsigned rs = 0, rph = 0;
-  // row j0base-1 of the first line (the row below the chunk), fetched ahead: u, den W/C, gam W/C
-  double em_u = 0, em_dW = 0, em_dC = 0, em_gW = 0, em_gC = 0;
-  const double em_r = hasprev ? __ldg(P.r + qprev) : 0.0;
-  if (bline < nlines && hasprev) {
-    const long long i0 = P.ia + bline;
-    em_u = __ldg(P.u + i0 * LD + qprev);
-    em_dW = __ldg(P.den + (i0 - 1) * LD + qprev);
-    em_dC = __ldg(P.den + i0 * LD + qprev);
-    em_gW = __ldg(P.gam + (i0 - 1) * LD + qprev);
-    em_gC = __ldg(P.gam + i0 * LD + qprev);
-  }
-  // 1-D j geometry of the row that arrives next, loaded one slice ahead (it does not depend on the line; with the
-  // ring taking the shared memory these loads miss L1, and waiting for them in the slice they are used in was the
-  // largest stall of the first version of this kernel)
-  double x_fy = __ldg(P.fy + t), x_rmn = __ldg(P.rmn + t), x_rydif = __ldg(P.r_ydif + t), x_r = __ldg(P.r + t);
-  double x_arx = __ldg(P.arx + t), x_rsx = __ldg(P.r_sx + t), x_ycvr = __ldg(P.ycvr + t);
+  // faces at the two ends of this thread's chunk of line i0, and the u values beyond them
+  auto load_edge = [&](long long i0) {
+    GtUEdge e{};
+    const double xcvi = __ldg(P.xcvi + i0), xcvip = __ldg(P.xcvip + i0 - 1);
+    const double *dW = P.den + (i0 - 1) * LD, *dC = P.den + i0 * LD, *gW = P.gam + (i0 - 1) * LD, *gC = P.gam + i0 * LD;
+    const double *vW = P.v + (i0 - 1) * LD, *vC = P.v + i0 * LD;
+    if (hasprev) {
+      double flow, acof;
+      gf_u_face_y(__ldg(dC + qprev), __ldg(dC + t), __ldg(dW + qprev), __ldg(dW + t), __ldg(gC + qprev), __ldg(gC + t),
+                  __ldg(gW + qprev), __ldg(gW + t), __ldg(vC + t), __ldg(vW + t), xcvi, xcvip, __ldg(P.fy + t),
+                  __ldg(P.rmn + t), __ldg(P.r_ydif + t), __ldg(P.r + qprev), __ldg(P.r + t), j0base == 1,
+                  j0base == nj - 1, iadv, flow, acof);
+      e.aS = acof + gf_max(0.0, flow);
+      e.us = __ldg(P.u + i0 * LD + qprev);
+    }
+    if (hasnext) {
+      gf_u_face_y(__ldg(dC + qlast), __ldg(dC + qnext), __ldg(dW + qlast), __ldg(dW + qnext), __ldg(gC + qlast),
+                  __ldg(gC + qnext), __ldg(gW + qlast), __ldg(gW + qnext), __ldg(vC + qnext), __ldg(vW + qnext), xcvi, xcvip,
+                  __ldg(P.fy + qnext), __ldg(P.rmn + qnext), __ldg(P.r_ydif + qnext), __ldg(P.r + qlast), __ldg(P.r + qnext),
+                  j0base + M == 1, j0base + M == nj - 1, iadv, e.flowN, e.acofN);
+      e.uN = __ldg(P.u + i0 * LD + qnext);
+    }
+    return e;
+  };
+  GtUEdge em{};
+  if (bline < nlines) em = load_edge(P.ia + bline);
+  // 1-D j geometry one slice ahead (it does not depend on the line; with the ring taking the shared memory these
+  // loads miss L1): x_ = the row of the next slice, y_ = the row north of it
+  double x_arx = __ldg(P.arx + t), x_rsx = __ldg(P.r_sx + t), x_ycvr = __ldg(P.ycvr + t), x_r = __ldg(P.r + t);
+  const int q1 = M > 1 ? T + t : t + 1;
+  double y_fy = __ldg(P.fy + q1), y_rmn = __ldg(P.rmn + q1), y_rydif = __ldg(P.r_ydif + q1), y_r = __ldg(P.r + q1);
   for (int line = bline; line < nlines; line += lstride) {
     const long long i0 = P.ia + line;
     const int i = (int)i0 + 1 + P.goff;                               // global line number (boundary tests only)
     const long long out = i0 * LD, cout = i0 * P.L.cSL;
-    // row j0base+M of this line (used after the last slice) and row j0base-1 of the block's next line
-    double ep_u = 0, ep_dW = 0, ep_dC = 0, ep_gW = 0, ep_gC = 0, ep_vW = 0, ep_vC = 0;
-    if (hasnext) {
-      ep_u = __ldg(P.u + i0 * LD + qnext);
-      ep_dW = __ldg(P.den + (i0 - 1) * LD + qnext);
-      ep_dC = __ldg(P.den + i0 * LD + qnext);
-      ep_gW = __ldg(P.gam + (i0 - 1) * LD + qnext);
-      ep_gC = __ldg(P.gam + i0 * LD + qnext);
-      ep_vW = __ldg(P.v + (i0 - 1) * LD + qnext);
-      ep_vC = __ldg(P.v + i0 * LD + qnext);
-    }
-    double nm_u = 0, nm_dW = 0, nm_dC = 0, nm_gW = 0, nm_gC = 0;
-    if (line + lstride < nlines && hasprev) {
-      const long long n0 = i0 + lstride;
-      nm_u = __ldg(P.u + n0 * LD + qprev);
-      nm_dW = __ldg(P.den + (n0 - 1) * LD + qprev);
-      nm_dC = __ldg(P.den + n0 * LD + qprev);
-      nm_gW = __ldg(P.gam + (n0 - 1) * LD + qprev);
-      nm_gC = __ldg(P.gam + n0 * LD + qprev);
-    }
+    GtUEdge nm{};
+    if (line + lstride < nlines) nm = load_edge(i0 + lstride);
     const double xcvi = __ldg(P.xcvi + i0), xcvip = __ldg(P.xcvip + i0 - 1);
     const double fx_w = __ldg(P.fx + i0 - 1), fx_c = __ldg(P.fx + i0), fx_e = __ldg(P.fx + i0 + 1);
     const double rsew_w = __ldg(P.r_sew + i0 - 1), rsew_c = __ldg(P.r_sew + i0);
     const double sewu_i = __ldg(P.sewu + i0), rxdif_i = __ldg(P.r_xdif + i0);
     const bool west_b = (i == 3), east_b = (i == nj - 1);          // quirk: `do i = 3, njm1`, `if (i == njm1)` (:135,:150)
-    // windows: _c = row of the pending cell (slice k-1), _p = the row that has just arrived (slice k)
-    double u_s = 0, u_c = em_u, u_n = 0;
-    double dW_c = em_dW, dC_c = em_dC, gW_c = em_gW, gC_c = em_gC, r_c = em_r;
-    double dW_p = 0, dC_p = 0, gW_p = 0, gC_p = 0, vW_p = 0, vC_p = 0, r_p = 0;
-    double o_uW = 0, o_uE = 0, o_dWW = 0, o_dE = 0, o_pW = 0, o_pC = 0;     // singles of the pending cell
-    double g_arx = 0, g_rsx = 0, g_ycvr = 0;                                // its geometry
-    double aS = 0.0;                                                        // acof + max(0, flow) of its south face
-    for (int k = 0; k <= M; ++k) {
-      double n_uW = 0, n_uE = 0, n_dWW = 0, n_dE = 0, n_pW = 0, n_pC = 0;
-      const double h_fy = x_fy, h_rmn = x_rmn, h_rydif = x_rydif, ng_arx = x_arx, ng_rsx = x_rsx, ng_ycvr = x_ycvr;
-      r_p = x_r;
-      {   // geometry of the next row to arrive: slice k+1, the row above the chunk, or slice 0 of the next line
-        const int qx = (k + 1 < M) ? (k + 1) * T + t : (k + 1 == M ? qnext : t);
-        x_fy = __ldg(P.fy + qx); x_rmn = __ldg(P.rmn + qx); x_rydif = __ldg(P.r_ydif + qx); x_r = __ldg(P.r + qx);
-        x_arx = __ldg(P.arx + qx); x_rsx = __ldg(P.r_sx + qx); x_ycvr = __ldg(P.ycvr + qx);
+    double aS = em.aS, u_s = em.us;
+    for (int k = 0; k < M; ++k) {
+      const int j0 = j0base + k;
+      const double arx = x_arx, rsx = x_rsx, ycvr = x_ycvr, r_c = x_r;
+      const double fy_p = y_fy, rmn_p = y_rmn, rydif_p = y_rydif, r_p = y_r;
+      {
+        const int kn = (k + 1 < M) ? k + 1 : 0;
+        const int qx = kn * T + t, qy = (kn + 1 < M) ? (kn + 1) * T + t : t + 1;
+        x_arx = __ldg(P.arx + qx); x_rsx = __ldg(P.r_sx + qx); x_ycvr = __ldg(P.ycvr + qx); x_r = __ldg(P.r + qx);
+        y_fy = __ldg(P.fy + qy); y_rmn = __ldg(P.rmn + qy); y_rydif = __ldg(P.r_ydif + qy); y_r = __ldg(P.r + qy);
       }
-      if (k < M) {
-        const unsigned s = rs, ph = rph;
-        if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
-        mbar_wait(full0 + 8 * s, ph);
-        const double* sl = ring + (size_t)s * SW + tid;
-        u_n = sl[0];
-        vW_p = sl[TT];
-        vC_p = sl[2 * TT];
-        dW_p = sl[3 * TT];
-        dC_p = sl[4 * TT];
-        gW_p = sl[5 * TT];
-        gC_p = sl[6 * TT];
-        n_uW = sl[7 * TT];
-        n_uE = sl[8 * TT];
-        n_dWW = sl[9 * TT];
-        n_dE = sl[10 * TT];
-        n_pW = sl[11 * TT];
-        n_pC = sl[12 * TT];
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty0 + 8 * s);
-      } else {
-        u_n = ep_u; vW_p = ep_vW; vC_p = ep_vC; dW_p = ep_dW; dC_p = ep_dC; gW_p = ep_gW; gC_p = ep_gC;
+      const unsigned s = rs, ph = rph;
+      if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+      mbar_wait(full0 + 8 * s, ph);
+      const double* sl = ring + (size_t)s * SW + tid;
+      const double u_c = sl[0], dW_c = sl[TT], dC_c = sl[2 * TT], gW_c = sl[3 * TT], gC_c = sl[4 * TT];
+      const double u_w = sl[5 * TT], u_e = sl[6 * TT], den_ww = sl[7 * TT], den_e = sl[8 * TT];
+      const double p_w = sl[9 * TT], p_c = sl[10 * TT];
+      const bool north = k + 1 < M;          // the north copies of the last slice are not staged (stale values, unused)
+      const double s_uN = sl[11 * TT], vW_p = sl[12 * TT], vC_p = sl[13 * TT], dW_p = sl[14 * TT], dC_p = sl[15 * TT];
+      const double gW_p = sl[16 * TT], gC_p = sl[17 * TT];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      double u_n = em.uN, flowN = em.flowN, acofN = em.acofN;
+      if (north) {
+        u_n = s_uN;
+        flowN = 0.0;
+        acofN = 0.0;
+        if (j0 + 1 < nj)
+          gf_u_face_y(dC_c, dC_p, dW_c, dW_p, gC_c, gC_p, gW_c, gW_p, vC_p, vW_p, xcvi, xcvip, fy_p, rmn_p, rydif_p, r_c,
+                      r_p, j0 == 0, j0 + 1 == nj - 1, iadv, flowN, acofN);
       }
-      // face between the pending row (jh-1) and the arrived row jh
-      const int jh = j0base + k;
-      double flowN = 0.0, acofN = 0.0;
-      if (jh >= 1 && jh < nj)
-        gf_u_face_y(dC_c, dC_p, dW_c, dW_p, gC_c, gC_p, gW_c, gW_p, vC_p, vW_p, xcvi, xcvip, h_fy, h_rmn, h_rydif, r_c,
-                    r_p, jh == 1, jh == nj - 1, iadv, flowN, acofN);
-      if (k >= 1) {
-        const int kk = k - 1, j0 = jh - 1;
-        if (j0 >= P.jlo && j0 <= P.jhi) {
-          const int q = kk * T + t, cq = kk * P.L.cSK + t;
-          const double arx = g_arx, rsx = g_rsx;
-          const double F_c = u_c * gf_arim(dW_c, dC_c, fx_c);
-          double flow_w, diff_w, flow_e, diff_e;
-          if (west_b) {
-            flow_w = arx * o_uW * o_dWW;                          // u(2,j)*den(1,j), gam(1,j) (:135-142)
-            diff_w = arx * __ldg(P.gam + q) * (rsew_w * rsx);
-          } else {
-            flow_w = arx * 0.5 * (o_uW * gf_arim(o_dWW, dW_c, fx_w) + F_c);
-            diff_w = arx * gW_c * (rsew_w * rsx);
-          }
-          if (east_b) {
-            flow_e = arx * o_uE * o_dE;                           // u(ni,j)*den(ni,j)
-            diff_e = arx * __ldg(P.gam + (long long)(ni - 1) * LD + q) * (rsew_c * rsx);
-          } else {
-            flow_e = arx * 0.5 * (F_c + o_uE * gf_arim(dC_c, o_dE, fx_e));
-            diff_e = arx * gC_c * (rsew_c * rsx);
-          }
-          const double AW = gf_dapec(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
-          const double AE = (gf_dapec(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
-          const double AS = aS;
-          const double AN = (acofN + gf_max(0.0, flowN)) - flowN;
-          const double vol = g_ycvr * sewu_i;
-          const double DU = vol * rxdif_i * rsx;
-          double SU = DU * (o_pW - o_pC);
-          double AP = AE + AW + AN + AS;
-          const double reseq = AP * u_c - AE * o_uE - AW * o_uW - AN * u_n - AS * u_s - SU;
-          racc += fabs(reseq);
-          AP = AP * r_urf;
-          SU = fma(omu * AP, u_c, SU);
-          GT_STORE(AE, AW, AN, AS, SU, AP)
-          P.dout[out + q] = DU * rAP;
+      if (j0 >= P.jlo && j0 <= P.jhi) {
+        const int q = k * T + t, cq = k * P.L.cSK + t;
+        // x-faces: mass flux at the u nodes i-1, i, i+1
+        const double F_c = u_c * gf_arim(dW_c, dC_c, fx_c);
+        double flow_w, diff_w, flow_e, diff_e;
+        if (west_b) {
+          flow_w = arx * u_w * den_ww;                          // u(2,j)*den(1,j), gam(1,j) (:135-142)
+          diff_w = arx * __ldg(P.gam + q) * (rsew_w * rsx);
+        } else {
+          flow_w = arx * 0.5 * (u_w * gf_arim(den_ww, dW_c, fx_w) + F_c);
+          diff_w = arx * gW_c * (rsew_w * rsx);
         }
+        if (east_b) {
+          flow_e = arx * u_e * den_e;                           // u(ni,j)*den(ni,j)
+          diff_e = arx * __ldg(P.gam + (long long)(ni - 1) * LD + q) * (rsew_c * rsx);
+        } else {
+          flow_e = arx * 0.5 * (F_c + u_e * gf_arim(dC_c, den_e, fx_e));
+          diff_e = arx * gC_c * (rsew_c * rsx);
+        }
+        const double AW = gf_dapec(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
+        const double AE = (gf_dapec(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
+        const double AS = aS;
+        const double AN = (acofN + gf_max(0.0, flowN)) - flowN;
+        const double vol = ycvr * sewu_i;
+        const double DU = vol * rxdif_i * rsx;
+        double SU = DU * (p_w - p_c);
+        double AP = AE + AW + AN + AS;
+        const double reseq = AP * u_c - AE * u_e - AW * u_w - AN * u_n - AS * u_s - SU;
+        racc += fabs(reseq);
+        AP = AP * r_urf;
+        SU = fma(omu * AP, u_c, SU);
+        GT_STORE(AE, AW, AN, AS, SU, AP)
+        P.dout[out + q] = DU * rAP;
       }
-      // the arrived row becomes the pending one
       aS = acofN + gf_max(0.0, flowN);
-      u_s = u_c; u_c = u_n;
-      dW_c = dW_p; dC_c = dC_p; gW_c = gW_p; gC_c = gC_p; r_c = r_p;
-      o_uW = n_uW; o_uE = n_uE; o_dWW = n_dWW; o_dE = n_dE; o_pW = n_pW; o_pC = n_pC;
-      g_arx = ng_arx; g_rsx = ng_rsx; g_ycvr = ng_ycvr;
+      u_s = u_c;
     }
-    em_u = nm_u; em_dW = nm_dW; em_dC = nm_dC; em_gW = nm_gW; em_gC = nm_gC;
+    em = nm;
   }
   gt_consumer_sum(racc, red, TT, tid, P.partial + blockIdx.x);
 }
@@ -283,7 +281,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_v_tma(const GenFastPara
         for (int k = 0; k < M; ++k) {
           const unsigned s = rs, ph = rph;
           if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
-          mbar_wait(empty0 + 8 * s, ph ^ 1u);
+          mbar_wait_backoff(empty0 + 8 * s, ph ^ 1u);
           const unsigned fb = full0 + 8 * s;
           const unsigned dst = smem_u32(ring + (size_t)s * SW);
           const bool north = k + 1 < M;
@@ -456,6 +454,282 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_v_tma(const GenFastPara
   gt_consumer_sum(racc, red, TT, tid, P.partial + blockIdx.x);
 }
 
+// =====================================================================================================
+// Energy equation (buoyancy_cav.f90:373-428).
+// Stage layout: 0 dC 1 cC 2 gC 3 tC | 4 uC 5 uE 6 dW 7 cW 8 gW 9 gE 10 dE 11 cE 12 tW 13 tE |
+//   north copies 14 dN 15 cN 16 gN 17 tN 18 vN | optional 19 su_src 20 sp_src
+// =====================================================================================================
+#define GT_NT 21
+#define GT_NT_NORTH 0x7C000u
+struct GtTEdge { double aS, ts, flowN, acofN, tN; };
+
+// y-face between rows lo and hi of the scalar column: D = den*cp, g = gamt; v and the geometry belong to row hi
+__device__ __forceinline__ void gt_t_face(double D_lo, double D_hi, double g_lo, double g_hi, double v_hi, double sew_i,
+                                          double r_lo, double rmn_hi, double fy_hi, double rydif_hi, bool south_b,
+                                          bool north_b, int iadv, double& flow, double& acof) {
+  double diff;
+  if (south_b) {            // lo is the wall row 1 (:373-378)
+    const double areas = r_lo * sew_i;
+    flow = D_lo * v_hi * areas;
+    diff = g_lo * areas * rydif_hi;
+  } else {
+    const double arean = rmn_hi * sew_i;
+    if (north_b) {          // hi is the wall row nj
+      flow = D_hi * v_hi * arean;
+      diff = g_hi * arean * rydif_hi;
+    } else {
+      flow = gf_arim(D_lo, D_hi, fy_hi) * v_hi * arean;
+      diff = gf_harm(g_lo, g_hi, fy_hi) * arean * rydif_hi;
+    }
+  }
+  acof = gf_dapec(flow, diff, iadv);
+}
+
+__global__ void __launch_bounds__(384, 1) k_gen_assemble_t_tma(const GenFastParams P, const int S, const int NSPLIT) {
+  GT_RING_SETUP(GT_NT)
+  const bool has_src = P.su_src != nullptr;
+  GT_PRODUCE(GT_NT, GT_NT_NORTH, has_src ? 0u : 0x180000u,
+             const double* src[GT_NT] = {P.den + i0 * LD,       P.cp + i0 * LD,         P.gam + i0 * LD,
+                                         P.t + i0 * LD,         P.u + i0 * LD,          P.u + (i0 + 1) * LD,
+                                         P.den + (i0 - 1) * LD, P.cp + (i0 - 1) * LD,   P.gam + (i0 - 1) * LD,
+                                         P.gam + (i0 + 1) * LD, P.den + (i0 + 1) * LD,  P.cp + (i0 + 1) * LD,
+                                         P.t + (i0 - 1) * LD,   P.t + (i0 + 1) * LD,    P.den + i0 * LD + T,
+                                         P.cp + i0 * LD + T,    P.gam + i0 * LD + T,    P.t + i0 * LD + T,
+                                         P.v + i0 * LD + T,     has_src ? P.su_src + i0 * LD : nullptr,
+                                         has_src ? P.sp_src + i0 * LD : nullptr};)
+  // ---- consumers
+  const int t = toff + tid, lane = tid & 31;
+  const int j0base = t * M;
+  const bool hasprev = j0base >= 1 && j0base < nj, hasnext = j0base + M < nj;
+  const int qprev = (M - 1) * T + t - 1, qnext = t + 1, qlast = (M - 1) * T + t;
+  const int iadv = P.iadv;
+  const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
+  double racc = 0.0;
+  unsigned rs = 0, rph = 0;
+  auto load_edge = [&](long long i0) {
+    GtTEdge e{};
+    const double sew_i = __ldg(P.sew + i0);
+    const double *dC = P.den + i0 * LD, *cC = P.cp + i0 * LD, *gC = P.gam + i0 * LD, *vC = P.v + i0 * LD;
+    if (hasprev) {
+      double flow, acof;
+      gt_t_face(__ldg(dC + qprev) * __ldg(cC + qprev), __ldg(dC + t) * __ldg(cC + t), __ldg(gC + qprev), __ldg(gC + t),
+                __ldg(vC + t), sew_i, __ldg(P.r + qprev), __ldg(P.rmn + t), __ldg(P.fy + t), __ldg(P.r_ydif + t),
+                j0base == 1, j0base == nj - 1, iadv, flow, acof);
+      e.aS = acof + gf_max(0.0, flow);
+      e.ts = __ldg(P.t + i0 * LD + qprev);
+    }
+    if (hasnext) {
+      gt_t_face(__ldg(dC + qlast) * __ldg(cC + qlast), __ldg(dC + qnext) * __ldg(cC + qnext), __ldg(gC + qlast),
+                __ldg(gC + qnext), __ldg(vC + qnext), sew_i, __ldg(P.r + qlast), __ldg(P.rmn + qnext), __ldg(P.fy + qnext),
+                __ldg(P.r_ydif + qnext), j0base + M == 1, j0base + M == nj - 1, iadv, e.flowN, e.acofN);
+      e.tN = __ldg(P.t + i0 * LD + qnext);
+    }
+    return e;
+  };
+  GtTEdge em{};
+  if (bline < nlines) em = load_edge(P.ia + bline);
+  double x_arx = __ldg(P.arx + t), x_rsx = __ldg(P.r_sx + t), x_ycvr = __ldg(P.ycvr + t);
+  const int q1 = M > 1 ? T + t : t + 1;
+  double y_fy = __ldg(P.fy + q1), y_rmn = __ldg(P.rmn + q1), y_rydif = __ldg(P.r_ydif + q1);
+  for (int line = bline; line < nlines; line += lstride) {
+    const long long i0 = P.ia + line;
+    const int i = (int)i0 + 1 + P.goff;
+    const long long cout = i0 * P.L.cSL;
+    GtTEdge nm{};
+    if (line + lstride < nlines) nm = load_edge(i0 + lstride);
+    const double sew_i = __ldg(P.sew + i0), fx_c = __ldg(P.fx + i0), fx_e = __ldg(P.fx + i0 + 1);
+    const double rxdif_c = __ldg(P.r_xdif + i0), rxdif_e = __ldg(P.r_xdif + i0 + 1);
+    const bool west_b = (i == 2), east_b = (i == P.NI - 1);
+    double aS = em.aS, t_s = em.ts;
+    for (int k = 0; k < M; ++k) {
+      const int j0 = j0base + k;
+      const double arx = x_arx, rsx = x_rsx, ycvr = x_ycvr, fy_p = y_fy, rmn_p = y_rmn, rydif_p = y_rydif;
+      {
+        const int kn = (k + 1 < M) ? k + 1 : 0;
+        const int qx = kn * T + t, qy = (kn + 1 < M) ? (kn + 1) * T + t : t + 1;
+        x_arx = __ldg(P.arx + qx); x_rsx = __ldg(P.r_sx + qx); x_ycvr = __ldg(P.ycvr + qx);
+        y_fy = __ldg(P.fy + qy); y_rmn = __ldg(P.rmn + qy); y_rydif = __ldg(P.r_ydif + qy);
+      }
+      const unsigned s = rs, ph = rph;
+      if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+      mbar_wait(full0 + 8 * s, ph);
+      const double* sl = ring + (size_t)s * SW + tid;
+      const double D_c = sl[0] * sl[TT], g_c = sl[2 * TT], t_c = sl[3 * TT], u_c = sl[4 * TT], u_e = sl[5 * TT];
+      const double D_w = sl[6 * TT] * sl[7 * TT], g_w = sl[8 * TT], g_e = sl[9 * TT];
+      const double D_e = sl[10 * TT] * sl[11 * TT], t_w = sl[12 * TT], t_e = sl[13 * TT];
+      const double su_s = has_src ? sl[19 * TT] : 0.0, sp_s = has_src ? sl[20 * TT] : 0.0;
+      double t_n = em.tN, flowN = em.flowN, acofN = em.acofN;
+      const int q = k * T + t;
+      if (k + 1 < M) {
+        const double D_p = sl[14 * TT] * sl[15 * TT], g_p = sl[16 * TT], v_p = sl[18 * TT];
+        t_n = sl[17 * TT];
+        flowN = 0.0;
+        acofN = 0.0;
+        if (j0 + 1 < nj)
+          gt_t_face(D_c, D_p, g_c, g_p, v_p, sew_i, j0 == 0 ? __ldg(P.r + q) : 0.0, rmn_p, fy_p, rydif_p, j0 == 0,
+                    j0 + 1 == nj - 1, iadv, flowN, acofN);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      if (j0 >= P.jlo && j0 <= P.jhi) {
+        const int cq = k * P.L.cSK + t;
+        double flow_w, diff_w, flow_e, diff_e;
+        if (west_b) {
+          flow_w = D_w * u_c * arx;
+          diff_w = g_w * arx * (rxdif_c * rsx);
+        } else {
+          flow_w = gf_arim(D_w, D_c, fx_c) * u_c * arx;
+          diff_w = gf_harm(g_w, g_c, fx_c) * arx * (rxdif_c * rsx);
+        }
+        if (east_b) {                                            // quirk: den(nj,j) (:390)
+          const long long lq = (long long)(nj - 1 - P.goff) * LD + q;     // global line nj, held by the last slab
+          const double dq = __ldg(P.den + lq) * __ldg(P.cp + lq);
+          flow_e = dq * u_e * arx;
+          diff_e = g_e * arx * (rxdif_e * rsx);
+        } else {
+          flow_e = gf_arim(D_c, D_e, fx_e) * u_e * arx;
+          diff_e = gf_harm(g_c, g_e, fx_e) * arx * (rxdif_e * rsx);
+        }
+        const double AW = gf_dapec(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
+        const double AE = (gf_dapec(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
+        const double AS = aS;
+        const double AN = (acofN + gf_max(0.0, flowN)) - flowN;
+        const double vol = ycvr * sew_i;
+        const double SP = sp_s * vol;
+        double SU = su_s * vol;
+        double AP = AE + AW + AN + AS - SP;
+        const double reseq = AP * t_c - AE * t_e - AW * t_w - AN * t_n - AS * t_s - SU;
+        racc += fabs(reseq);
+        AP = AP * r_urf;
+        SU = fma(omu * AP, t_c, SU);
+        GT_STORE(AE, AW, AN, AS, SU, AP)
+      }
+      aS = acofN + gf_max(0.0, flowN);
+      t_s = t_c;
+    }
+    em = nm;
+  }
+  gt_consumer_sum(racc, red, TT, tid, P.partial + blockIdx.x);
+}
+
+// =====================================================================================================
+// Pressure correction (buoyancy_cav.f90:294-340).
+// Stage layout: 0 dC | 1 uC 2 uE 3 dW 4 dE 5 duC 6 duE | north copies 7 dN 8 vN 9 dvN
+// =====================================================================================================
+#define GT_NP 10
+#define GT_NP_NORTH 0x380u
+struct GtPEdge { double fS, aS, fN, aN; };
+
+// mass flux through and conductance of the y-face between rows lo and hi (v, dv and the geometry belong to row hi)
+__device__ __forceinline__ void gt_p_face(double d_lo, double d_hi, double v_hi, double dv_hi, double arean, double fy_hi,
+                                          bool south_b, bool north_b, double& f, double& a) {
+  if (north_b) {              // den(i,nj)*v(i,nj)
+    f = d_hi * v_hi * arean;
+    a = 0.0;
+  } else if (south_b) {       // (:301-306) den(i,1)*v(i,2)
+    f = d_lo * v_hi * arean;
+    a = 0.0;
+  } else {
+    const double denn = gf_arim(d_lo, d_hi, fy_hi);
+    f = denn * v_hi * arean;
+    a = denn * arean * dv_hi;
+  }
+}
+
+__global__ void __launch_bounds__(384, 1) k_gen_assemble_p_tma(const GenFastParams P, const int S, const int NSPLIT) {
+  GT_RING_SETUP(GT_NP)
+  GT_PRODUCE(GT_NP, GT_NP_NORTH, 0u,
+             const double* src[GT_NP] = {P.den + i0 * LD,       P.u + i0 * LD,         P.u + (i0 + 1) * LD,
+                                         P.den + (i0 - 1) * LD, P.den + (i0 + 1) * LD, P.du_in + i0 * LD,
+                                         P.du_in + (i0 + 1) * LD, P.den + i0 * LD + T, P.v + i0 * LD + T,
+                                         P.dv_in + i0 * LD + T};)
+  // ---- consumers
+  const int t = toff + tid, lane = tid & 31;
+  const int j0base = t * M;
+  const bool hasprev = j0base >= 1 && j0base < nj, hasnext = j0base + M < nj;
+  const int qprev = (M - 1) * T + t - 1, qnext = t + 1, qlast = (M - 1) * T + t;
+  double racc = 0.0;
+  unsigned rs = 0, rph = 0;
+  auto load_edge = [&](long long i0) {
+    GtPEdge e{};
+    const double sew_i = __ldg(P.sew + i0);
+    const double *dC = P.den + i0 * LD, *vC = P.v + i0 * LD, *dvC = P.dv_in + i0 * LD;
+    if (hasprev)
+      gt_p_face(__ldg(dC + qprev), __ldg(dC + t), __ldg(vC + t), __ldg(dvC + t), __ldg(P.rmn + t) * sew_i, __ldg(P.fy + t),
+                j0base == 1, j0base == nj - 1, e.fS, e.aS);
+    if (hasnext)
+      gt_p_face(__ldg(dC + qlast), __ldg(dC + qnext), __ldg(vC + qnext), __ldg(dvC + qnext), __ldg(P.rmn + qnext) * sew_i,
+                __ldg(P.fy + qnext), j0base + M == 1, j0base + M == nj - 1, e.fN, e.aN);
+    return e;
+  };
+  GtPEdge em{};
+  if (bline < nlines) em = load_edge(P.ia + bline);
+  double x_arx = __ldg(P.arx + t);
+  const int q1 = M > 1 ? T + t : t + 1;
+  double y_fy = __ldg(P.fy + q1), y_rmn = __ldg(P.rmn + q1);
+  for (int line = bline; line < nlines; line += lstride) {
+    const long long i0 = P.ia + line;
+    const int i = (int)i0 + 1 + P.goff;
+    const long long cout = i0 * P.L.cSL;
+    GtPEdge nm{};
+    if (line + lstride < nlines) nm = load_edge(i0 + lstride);
+    const double sew_i = __ldg(P.sew + i0), fx_c = __ldg(P.fx + i0), fx_e = __ldg(P.fx + i0 + 1);
+    const bool west_b = (i == 2), east_b = (i == P.NI - 1);
+    double fS = em.fS, aS = em.aS;
+    for (int k = 0; k < M; ++k) {
+      const int j0 = j0base + k;
+      const double arx = x_arx, fy_p = y_fy, rmn_p = y_rmn;
+      {
+        const int kn = (k + 1 < M) ? k + 1 : 0;
+        const int qx = kn * T + t, qy = (kn + 1 < M) ? (kn + 1) * T + t : t + 1;
+        x_arx = __ldg(P.arx + qx);
+        y_fy = __ldg(P.fy + qy); y_rmn = __ldg(P.rmn + qy);
+      }
+      const unsigned s = rs, ph = rph;
+      if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+      mbar_wait(full0 + 8 * s, ph);
+      const double* sl = ring + (size_t)s * SW + tid;
+      const double d_c = sl[0], u_c = sl[TT], u_e = sl[2 * TT], den_w = sl[3 * TT], den_e = sl[4 * TT];
+      const double du_c = sl[5 * TT], du_e = sl[6 * TT];
+      double fN = em.fN, aN = em.aN;
+      if (k + 1 < M) {
+        const double d_p = sl[7 * TT], v_p = sl[8 * TT], dv_p = sl[9 * TT];
+        fN = 0.0;
+        aN = 0.0;
+        if (j0 + 1 < nj) gt_p_face(d_c, d_p, v_p, dv_p, rmn_p * sew_i, fy_p, j0 == 0, j0 + 1 == nj - 1, fN, aN);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      if (j0 >= P.jlo && j0 <= P.jhi) {
+        const int cq = k * P.L.cSK + t;
+        double SU = fS, AW, AE;
+        if (west_b) {
+          SU = SU + den_w * u_c * arx;
+          AW = 0.0;
+        } else {
+          SU = SU + d_c * u_c * arx;                             // quirk: den(i+1,j) of the upstream cell's formula
+          AW = gf_arim(den_w, d_c, fx_c) * arx * du_c;
+        }
+        SU = SU - den_e * u_e * arx;
+        AE = east_b ? 0.0 : gf_arim(d_c, den_e, fx_e) * arx * du_e;
+        SU = SU - fN;
+        racc += fabs(SU);
+        const double APs = AE + AW + aN + aS;
+        const double rr = APs != 0.0 ? 1.0 / APs : 0.0;
+        P.ae[cout + cq] = AE * rr;
+        P.aw[cout + cq] = AW * rr;
+        P.an[cout + cq] = aN * rr;
+        P.as[cout + cq] = aS * rr;
+        P.su[cout + cq] = SU * rr;
+      }
+      fS = fN;
+      aS = aN;
+    }
+    em = nm;
+  }
+  gt_consumer_sum(racc, red, TT, tid, P.partial + blockIdx.x);
+}
+
 }  // namespace cfd
 
 using namespace cfd;
@@ -474,14 +748,14 @@ bool cfd_general_tma_eligible(const cfd_ctx* c, int which) {
     const char* e = getenv("CFD_B200_GEN_TMA");
     use_tma = e ? atoi(e) : 1;
   }
-  return use_tma && which <= 1 && gt_nsplit(c->L.T) > 0;
+  return use_tma && which <= 3 && gt_nsplit(c->L.T) > 0;
 }
 
-// which: 0 u, 1 v.  Returns the number of residual partials (grid size), or a negative status.
+// which: 0 u, 1 v, 2 p', 3 T.  Returns the number of residual partials (grid size), or a negative status.
 int cfd_launch_general_assemble_tma(cfd_ctx* c, int which, const GenFastParams& P) {
   static int num_sms = 0;
   if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device));
-  const int T = c->L.T, narr = which == 0 ? GT_NU : GT_NV, nsplit = gt_nsplit(T), TT = T / nsplit;
+  const int T = c->L.T, narr = which == 0 ? GT_NU : which == 1 ? GT_NV : which == 2 ? GT_NP : GT_NT, nsplit = gt_nsplit(T), TT = T / nsplit;
   const size_t stage = (size_t)narr * TT * sizeof(double);
   int S = 8;
   const char* es = getenv("CFD_B200_ASM_STAGES");
@@ -491,7 +765,8 @@ int cfd_launch_general_assemble_tma(cfd_ctx* c, int which, const GenFastParams& 
   const int nlines = P.ib - P.ia + 1;
   int nblocks = nlines * nsplit < num_sms ? nlines * nsplit : num_sms / nsplit * nsplit;
   const int nthreads = TT + 32 * GT_PRODUCER_WARPS;
-  void (*kernel)(const GenFastParams, const int, const int) = which == 0 ? k_gen_assemble_u_tma : k_gen_assemble_v_tma;
+  void (*kernel)(const GenFastParams, const int, const int) =
+      which == 0 ? k_gen_assemble_u_tma : which == 1 ? k_gen_assemble_v_tma : which == 2 ? k_gen_assemble_p_tma : k_gen_assemble_t_tma;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e == cudaSuccess) kernel<<<nblocks, nthreads, smem, c->stream>>>(P, S, nsplit);
   if (e != cudaSuccess) {

@@ -67,10 +67,10 @@ def test_local_jslabs_partitioned_thomas(cfd, world, shape):
     g.close()
 
 
-@pytest.mark.parametrize("world,n", [(2, 34), (3, 50), (4, 66)])
+@pytest.mark.parametrize("world,n", [(2, 34), (3, 50), (4, 66), (2, 2100)])
 def test_buoyancy_local_slabs_match_single_context(cfd, world, n):
     """General family (Boussinesq cavity with its temperature equation) cut into i-slabs: same bits as the single
-    red/black context."""
+    red/black context.  n = 2100 has lines long enough for the TMA-staged assembly kernels (general_tma_kernels.cu)."""
     from cfd_b200.dist import BuoyancySlab, LocalSlabCavity
     g = cfd.BuoyantCavity(n, n, order="redblack")
     s = LocalSlabCavity(n - 2, n - 2, world, slab_cls=BuoyancySlab)

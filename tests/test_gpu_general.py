@@ -190,6 +190,26 @@ def test_full_size_8194_buoyancy_properties(cfd):
     g.close(); h.close()
 
 
+def test_full_size_assembly_launches_are_reproducible(cfd):
+    """The TMA-staged assembly kernels at the BASELINE configs[3] size (lines split over two blocks, a last warp that
+    holds padding nodes): the same launch on the same rough fields must give the same bits every time.  A ring
+    slot read too early or too late shows here as a large difference in a few nodes of one line."""
+    n = 8194
+    g = cfd.BuoyantCavity(n, n, order="redblack")
+    rng = np.random.default_rng(5)
+    for name, scale, base in (("u", 2e-3, 0.0), ("v", 2e-3, 0.0), ("p", 1e-6, 0.0), ("t", 0.4, 0.5), ("den", 0.2, 1.0), ("cp", 0.2, 1.0)):
+        g.upload(name, np.asfortranarray(base + scale * (rng.random((n, n)) - 0.5)))
+    for name in ("u", "v", "p", "t"):
+        fn = getattr(g, "assemble_" + name)
+        fn()
+        ref = g.download("su")
+        assert np.isfinite(ref[2:-1, 2:-1]).all()
+        for rep in range(5):
+            fn()
+            assert np.array_equal(g.download("su"), ref), (name, rep)
+    g.close()
+
+
 def test_general_rejects_what_the_reference_cannot_do(cfd):
     with pytest.raises(cfd.CfdError, match="ni == nj"):
         cfd.GeneralFVM(40, 30, lsolve_flow=True)

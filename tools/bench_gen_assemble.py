@@ -11,7 +11,36 @@ import torch
 import cfd_b200
 
 
+def race_check(g, names, reps):
+    """Run-to-run determinism of each assembly launch on rough fields: a stale read shows as a large difference."""
+    for name in names:
+        fn = getattr(g, "assemble_" + name)
+        fn()
+        ref = {c: g.download(c) for c in ("su", "ae", "an")}
+        bad = 0
+        for r in range(reps):
+            fn()
+            for c, a in ref.items():
+                b = g.download(c)
+                d = np.argwhere(a != b)
+                if len(d):
+                    bad += 1
+                    print("RACE", name, c, "rep", r, "nodes", len(d), "first", d[:3].tolist(), "i", int(d[:, 0].min()),
+                          int(d[:, 0].max()), "j", int(d[:, 1].min()), int(d[:, 1].max()), "max abs", float(np.abs(a - b).max()))
+        print("race check", name, "reps", reps, "bad", bad, flush=True)
+
+
 def main():
+    if sys.argv[1] == "cavity":
+        n = int(sys.argv[2])
+        g = cfd_b200.CavityFVM(n, n, order="redblack")
+        g.init_lid_driven(reynolds=1000.0)
+        g.iterate(2)
+        rng = np.random.default_rng(5)
+        for name, scale in (("u", 2e-1), ("v", 2e-1), ("p", 1e-2)):
+            g.upload(name, np.asfortranarray(scale * (rng.random((n + 2, n + 2)) - 0.5)))
+        race_check(g, ("u", "v"), int(sys.argv[3]))
+        return
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 8194
     g = cfd_b200.BuoyantCavity(n, n, order="redblack")
     g.iterate(3)
@@ -32,6 +61,14 @@ def main():
         out[name + "_us"] = round(us, 1)
         out[name + "_B_per_cell_at_7TBs"] = round(us * 1e-6 * 7.0e12 / cells, 1)
     print(json.dumps(out))
+    if len(sys.argv) > 2 and sys.argv[2] == "race":
+        # run-to-run determinism of each assembly launch on rough (random) fields: a stale read shows as a large difference
+        rng = np.random.default_rng(5)
+        for name, scale, base in (("u", 2e-3, 0.0), ("v", 2e-3, 0.0), ("p", 1e-6, 0.0), ("t", 0.4, 0.5), ("den", 0.2, 1.0),
+                                  ("cp", 0.2, 1.0)):
+            g.upload(name, np.asfortranarray(base + scale * (rng.random((n, n)) - 0.5)))
+        race_check(g, tuple(sys.argv[4]) if len(sys.argv) > 4 else ("u", "v", "p", "t"), int(sys.argv[3]) if len(sys.argv) > 3 else 6)
+        return
     if len(sys.argv) > 2:
         g.close()
         g = cfd_b200.BuoyantCavity(n, n, order="redblack")
