@@ -473,11 +473,11 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
 #define LAUNCH_ASM(KERNEL)                                                                         \
   e = cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);        \
   if (e == cudaSuccess) KERNEL<<<nblocks, T + 32 * ASM_PRODUCER_WARPS, smem, c->stream>>>(P, G, S);
-  if (T + 32 * ASM_PRODUCER_WARPS <= 384) {
-    if (which == 0) { LAUNCH_ASM(k_assemble_u_tma<384>) } else { LAUNCH_ASM(k_assemble_v_tma<384>) }
-  } else {
-    if (which == 0) { LAUNCH_ASM(k_assemble_u_tma<768>) } else { LAUNCH_ASM(k_assemble_v_tma<768>) }
+  if (T + 32 * ASM_PRODUCER_WARPS > 384) {   // a 768-thread build spills (80 registers) and loses to the register-window kernels
+    cfd_set_error("k_assemble_*_tma: lines of %d layout threads do not fit the 384-thread build", T);
+    return CFD_ERR_INVALID;
   }
+  if (which == 0) { LAUNCH_ASM(k_assemble_u_tma<384>) } else { LAUNCH_ASM(k_assemble_v_tma<384>) }
 #undef LAUNCH_ASM
   if (e != cudaSuccess) {
     cfd_set_error("k_assemble_*_tma: %s", cudaGetErrorString(e));

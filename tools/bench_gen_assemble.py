@@ -31,6 +31,25 @@ def race_check(g, names, reps):
 
 
 def main():
+    if sys.argv[1] == "cavtime":       # cavity family: assembly launches and the whole iteration at n x n CV
+        n = int(sys.argv[2])
+        g = cfd_b200.CavityFVM(n, n, order="redblack")
+        g.init_lid_driven(reynolds=1000.0)
+        g.iterate(3)
+        out = {"cavity_n": n, "tma": os.environ.get("CFD_B200_ASM_TMA", "1")}
+        for name, fn in (("u", g.assemble_u), ("v", g.assemble_v), ("iteration", lambda: g.iterate(1))):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(10):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            out[name + "_us"] = round(a.elapsed_time(b) * 100.0, 1)
+        print(json.dumps(out))
+        return
     if sys.argv[1] == "cavity":
         n = int(sys.argv[2])
         g = cfd_b200.CavityFVM(n, n, order="redblack")
