@@ -31,7 +31,12 @@ __device__ __forceinline__ double gf_rcp(double x) {
   return r;
 }
 __device__ __forceinline__ double gf_arim(double a, double b, double w) { return fma(b - a, w, a); }
-__device__ __forceinline__ double gf_harm(double a, double b, double w) { return a * b * gf_rcp(fma(b - a, w, a)); }
+// HARMEAN (cylin_cond.f90:268-285).  Equal arguments (uniform properties, the usual case) return the argument: the
+// quotient a*a/a is the same number to rounding and the reciprocal with its Newton steps is a tenth of a kernel.
+__device__ __forceinline__ double gf_harm(double a, double b, double w) {
+  if (a == b) return a;
+  return a * b * gf_rcp(fma(b - a, w, a));
+}
 __device__ __forceinline__ double gf_dapec(double flow, double diff, int iadv) {
   if (flow == 0.0) return diff;
   switch (iadv) {
