@@ -37,6 +37,7 @@ __device__ __forceinline__ double gf_harm(double a, double b, double w) {
   if (a == b) return a;
   return a * b * gf_rcp(fma(b - a, w, a));
 }
+// DAPEC (cylin_cond.f90:245-266)
 __device__ __forceinline__ double gf_dapec(double flow, double diff, int iadv) {
   if (flow == 0.0) return diff;
   switch (iadv) {
@@ -51,9 +52,24 @@ __device__ __forceinline__ double gf_dapec(double flow, double diff, int iadv) {
     default: return diff;
   }
 }
+// The same without data-dependent branches: central / upwind / hybrid share one FMA and are told apart by selects on
+// the (launch-uniform) scheme number; only the power law keeps its own branch.  Same values; measured faster in
+// the TMA-staged u and T kernels (-3 %) and slower in the v kernel (+9 %, register pressure), which keeps gf_dapec.
+__device__ __forceinline__ double gf_dapec_sel(double flow, double diff, int iadv) {
+  if (iadv == 4) {
+    if (flow == 0.0) return diff;
+    const double q = 1.0 - 0.1 * fabs(flow / diff);
+    const double q2 = q * q;
+    return gf_max(0.0, q2 * q2 * q) * diff;
+  }
+  const double c = fma(-0.5, fabs(flow), diff);
+  const double r = iadv == 1 ? c : (iadv == 3 ? gf_max(0.0, c) : diff);
+  return flow == 0.0 ? diff : r;
+}
 
 // u-momentum (buoyancy_cav.f90:135-194):
 // y-face between rows lo (j) and hi (j+1) of the u-cell column i: flow and diffusion conductance
+template <bool SEL = false>
 __device__ __forceinline__ void gf_u_face_y(double Dc_lo, double Dc_hi, double Dw_lo, double Dw_hi, double Gc_lo, double Gc_hi,
                                             double Gw_lo, double Gw_hi, double Vc, double Vw, double xcvi, double xcvip,
                                             double fy_h, double rmn_h, double rydif_h, double r_lo, double r_hi,
@@ -75,7 +91,7 @@ __device__ __forceinline__ void gf_u_face_y(double Dc_lo, double Dc_hi, double D
     diff = rmn_h * (gf_harm(Gc_lo, Gc_hi, fy_h) * xcvi + gf_harm(Gw_lo, Gw_hi, fy_h) * xcvip) * rydif_h;
     flow = rmn_h * (fl + flm);
   }
-  acof = gf_dapec(flow, diff, iadv);
+  acof = SEL ? gf_dapec_sel(flow, diff, iadv) : gf_dapec(flow, diff, iadv);
 }
 
 }  // namespace cfd

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastPara
     const double *vW = P.v + (i0 - 1) * LD, *vC = P.v + i0 * LD;
     if (hasprev) {
       double flow, acof;
-      gf_u_face_y(__ldg(dC + qprev), __ldg(dC + t), __ldg(dW + qprev), __ldg(dW + t), __ldg(gC + qprev), __ldg(gC + t),
+      gf_u_face_y<true>(__ldg(dC + qprev), __ldg(dC + t), __ldg(dW + qprev), __ldg(dW + t), __ldg(gC + qprev), __ldg(gC + t),
                   __ldg(gW + qprev), __ldg(gW + t), __ldg(vC + t), __ldg(vW + t), xcvi, xcvip, __ldg(P.fy + t),
                   __ldg(P.rmn + t), __ldg(P.r_ydif + t), __ldg(P.r + qprev), __ldg(P.r + t), j0base == 1,
                   j0base == nj - 1, iadv, flow, acof);
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastPara
       e.us = __ldg(P.u + i0 * LD + qprev);
     }
     if (hasnext) {
-      gf_u_face_y(__ldg(dC + qlast), __ldg(dC + qnext), __ldg(dW + qlast), __ldg(dW + qnext), __ldg(gC + qlast),
+      gf_u_face_y<true>(__ldg(dC + qlast), __ldg(dC + qnext), __ldg(dW + qlast), __ldg(dW + qnext), __ldg(gC + qlast),
                   __ldg(gC + qnext), __ldg(gW + qlast), __ldg(gW + qnext), __ldg(vC + qnext), __ldg(vW + qnext), xcvi, xcvip,
                   __ldg(P.fy + qnext), __ldg(P.rmn + qnext), __ldg(P.r_ydif + qnext), __ldg(P.r + qlast), __ldg(P.r + qnext),
                   j0base + M == 1, j0base + M == nj - 1, iadv, e.flowN, e.acofN);
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastPara
         flowN = 0.0;
         acofN = 0.0;
         if (j0 + 1 < nj)
-          gf_u_face_y(dC_c, dC_p, dW_c, dW_p, gC_c, gC_p, gW_c, gW_p, vC_p, vW_p, xcvi, xcvip, fy_p, rmn_p, rydif_p, r_c,
+          gf_u_face_y<true>(dC_c, dC_p, dW_c, dW_p, gC_c, gC_p, gW_c, gW_p, vC_p, vW_p, xcvi, xcvip, fy_p, rmn_p, rydif_p, r_c,
                       r_p, j0 == 0, j0 + 1 == nj - 1, iadv, flowN, acofN);
       }
       if (j0 >= P.jlo && j0 <= P.jhi) {
@@ -230,8 +230,8 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastPara
           flow_e = arx * 0.5 * (F_c + u_e * gf_arim(dC_c, den_e, fx_e));
           diff_e = arx * gC_c * (rsew_c * rsx);
         }
-        const double AW = gf_dapec(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
-        const double AE = (gf_dapec(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
+        const double AW = gf_dapec_sel(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
+        const double AE = (gf_dapec_sel(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
         const double AS = aS;
         const double AN = (acofN + gf_max(0.0, flowN)) - flowN;
         const double vol = ycvr * sewu_i;
@@ -482,7 +482,7 @@ __device__ __forceinline__ void gt_t_face(double D_lo, double D_hi, double g_lo,
       diff = gf_harm(g_lo, g_hi, fy_hi) * arean * rydif_hi;
     }
   }
-  acof = gf_dapec(flow, diff, iadv);
+  acof = gf_dapec_sel(flow, diff, iadv);
 }
 
 __global__ void __launch_bounds__(384, 1) k_gen_assemble_t_tma(const GenFastParams P, const int S, const int NSPLIT) {
@@ -590,8 +590,8 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_t_tma(const GenFastPara
           flow_e = gf_arim(D_c, D_e, fx_e) * u_e * arx;
           diff_e = gf_harm(g_c, g_e, fx_e) * arx * (rxdif_e * rsx);
         }
-        const double AW = gf_dapec(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
-        const double AE = (gf_dapec(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
+        const double AW = gf_dapec_sel(flow_w, diff_w, iadv) + gf_max(0.0, flow_w);
+        const double AE = (gf_dapec_sel(flow_e, diff_e, iadv) + gf_max(0.0, flow_e)) - flow_e;
         const double AS = aS;
         const double AN = (acofN + gf_max(0.0, flowN)) - flowN;
         const double vol = ycvr * sew_i;
