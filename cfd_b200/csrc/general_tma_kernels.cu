@@ -19,7 +19,7 @@
 
 namespace cfd {
 
-#define GT_PRODUCER_WARPS 2   // bulk-copy issue is per-thread serial: 13 copies per slice need several issuers
+#define GT_PRODUCER_WARPS 2   // bulk-copy issue is per-thread serial: 10-21 copies per slice need several issuers
 
 // block reduction over the consumer threads only (named barrier 1), thread 0 writes *out
 __device__ __forceinline__ void gt_consumer_sum(double v, double* red, int T, int t, double* out) {
