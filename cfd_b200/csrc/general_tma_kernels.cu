@@ -97,13 +97,16 @@ __device__ __forceinline__ void gt_consumer_sum(double v, double* red, int T, in
     return;                                                                                            \
   }
 
+// The five arrays of a production (nc = 5) coefficient block sit T doubles apart in the order an, as, ae, aw, su
+// (api.cu: kCoefOrder5), so one base pointer serves the five stores.
 #define GT_STORE(AE, AW, AN, AS, SU, AP)   \
   const double rAP = gf_rcp(AP);           \
-  P.ae[cout + cq] = (AE) * rAP;            \
-  P.aw[cout + cq] = (AW) * rAP;            \
-  P.an[cout + cq] = (AN) * rAP;            \
-  P.as[cout + cq] = (AS) * rAP;            \
-  P.su[cout + cq] = (SU) * rAP;
+  double* cb__ = P.an + cout + cq;         \
+  cb__[0] = (AN) * rAP;                    \
+  cb__[T] = (AS) * rAP;                    \
+  cb__[2 * T] = (AE) * rAP;                \
+  cb__[3 * T] = (AW) * rAP;                \
+  cb__[4 * T] = (SU) * rAP;
 
 // =====================================================================================================
 // u-momentum (buoyancy_cav.f90:135-194).
@@ -119,6 +122,7 @@ __device__ __forceinline__ void gt_consumer_sum(double v, double* red, int T, in
 #define GT_NU_NORTH 0x3F800u
 struct GtUEdge { double aS, us, flowN, acofN, uN; };
 
+template <int IADV>   // scheme number known at compile time (3 = hybrid, the default of every shipped case), 0 = read it from P
 __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastParams P, const int S, const int NSPLIT) {
   GT_RING_SETUP(GT_NU)
   GT_PRODUCE(GT_NU, GT_NU_NORTH, 0u,
@@ -133,7 +137,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastPara
   const int j0base = t * M;
   const bool hasprev = j0base >= 1 && j0base < nj, hasnext = j0base + M < nj;
   const int qprev = (M - 1) * T + t - 1, qnext = t + 1, qlast = (M - 1) * T + t;
-  const int iadv = P.iadv, ni = P.L.ni;
+  const int iadv = IADV ? IADV : P.iadv, ni = P.L.ni;
   const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
   double racc = 0.0;
   unsigned rs = 0, rph = 0;
@@ -264,6 +268,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_u_tma(const GenFastPara
 #define GT_NV 15
 struct GtVEdge { double fw, fe, hw, he, dC, gC, v, p, t, G; };
 
+template <int IADV>   // scheme number known at compile time (3 = hybrid, the default of every shipped case), 0 = read it from P
 __global__ void __launch_bounds__(384, 1) k_gen_assemble_v_tma(const GenFastParams P, const int S, const int NSPLIT) {
   GT_RING_SETUP(GT_NV)
   const bool has_t = P.t != nullptr;
@@ -304,7 +309,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_v_tma(const GenFastPara
   const bool hasprev = j0base >= 1, hasnext = j0base + M < nj;
   const int qprev = (M - 1) * T + t - 1, qnext = t + 1;
   const int qprev2 = j0base >= 2 ? lpos(j0base - 2, M, T) : 0;
-  const int iadv = P.iadv;
+  const int iadv = IADV ? IADV : P.iadv;
   const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
   double racc = 0.0;
   unsigned rs = 0, rph = 0;
@@ -485,6 +490,7 @@ __device__ __forceinline__ void gt_t_face(double D_lo, double D_hi, double g_lo,
   acof = gf_dapec_sel(flow, diff, iadv);
 }
 
+template <int IADV>   // scheme number known at compile time (3 = hybrid, the default of every shipped case), 0 = read it from P
 __global__ void __launch_bounds__(384, 1) k_gen_assemble_t_tma(const GenFastParams P, const int S, const int NSPLIT) {
   GT_RING_SETUP(GT_NT)
   const bool has_src = P.su_src != nullptr;
@@ -502,7 +508,7 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_t_tma(const GenFastPara
   const int j0base = t * M;
   const bool hasprev = j0base >= 1 && j0base < nj, hasnext = j0base + M < nj;
   const int qprev = (M - 1) * T + t - 1, qnext = t + 1, qlast = (M - 1) * T + t;
-  const int iadv = P.iadv;
+  const int iadv = IADV ? IADV : P.iadv;
   const double r_urf = 1.0 / P.urf, omu = 1.0 - P.urf;
   double racc = 0.0;
   unsigned rs = 0, rph = 0;
@@ -716,11 +722,12 @@ __global__ void __launch_bounds__(384, 1) k_gen_assemble_p_tma(const GenFastPara
         racc += fabs(SU);
         const double APs = AE + AW + aN + aS;
         const double rr = APs != 0.0 ? 1.0 / APs : 0.0;
-        P.ae[cout + cq] = AE * rr;
-        P.aw[cout + cq] = AW * rr;
-        P.an[cout + cq] = aN * rr;
-        P.as[cout + cq] = aS * rr;
-        P.su[cout + cq] = SU * rr;
+        double* cb = P.an + cout + cq;
+        cb[0] = aN * rr;
+        cb[T] = aS * rr;
+        cb[2 * T] = AE * rr;
+        cb[3 * T] = AW * rr;
+        cb[4 * T] = SU * rr;
       }
       fS = fN;
       aS = aN;
@@ -765,8 +772,12 @@ int cfd_launch_general_assemble_tma(cfd_ctx* c, int which, const GenFastParams& 
   const int nlines = P.ib - P.ia + 1;
   int nblocks = nlines * nsplit < num_sms ? nlines * nsplit : num_sms / nsplit * nsplit;
   const int nthreads = TT + 32 * GT_PRODUCER_WARPS;
+  const bool hybrid = P.iadv == 3;
   void (*kernel)(const GenFastParams, const int, const int) =
-      which == 0 ? k_gen_assemble_u_tma : which == 1 ? k_gen_assemble_v_tma : which == 2 ? k_gen_assemble_p_tma : k_gen_assemble_t_tma;
+      which == 0   ? (hybrid ? k_gen_assemble_u_tma<3> : k_gen_assemble_u_tma<0>)
+      : which == 1 ? (hybrid ? k_gen_assemble_v_tma<3> : k_gen_assemble_v_tma<0>)
+      : which == 2 ? k_gen_assemble_p_tma
+                   : (hybrid ? k_gen_assemble_t_tma<3> : k_gen_assemble_t_tma<0>);
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e == cudaSuccess) kernel<<<nblocks, nthreads, smem, c->stream>>>(P, S, nsplit);
   if (e != cudaSuccess) {
