@@ -1,5 +1,10 @@
-"""Times the four production assembly launches of the general family alone (buoyancy cavity, n x n nodes) and checks
-that cfd_iterate and the subroutine path give the same bits.  Usage: python tools/bench_gen_assemble.py [n] [check]"""
+"""Assembly launches of the general family (buoyancy cavity, n x n nodes) timed alone, and reproducibility checks.
+  python tools/bench_gen_assemble.py 8194                 time assemble_u/v/p/t (10 launches each)
+  python tools/bench_gen_assemble.py 8194 check           cfd_iterate against the subroutine path, bit for bit, 4 iterations
+  python tools/bench_gen_assemble.py 8194 race 30 [uvpt]  the same launch 30 times on rough fields: identical bits every time?
+  python tools/bench_gen_assemble.py cavity 4096 30       the same for the cavity family's TMA-staged u and v kernels
+  python tools/bench_gen_assemble.py cavtime 8192         cavity family: assembly launches and one iteration
+CFD_B200_GEN_TMA=0 / CFD_B200_ASM_TMA=0 select the register-window kernels for comparison."""
 import json
 import os
 import sys
