@@ -231,3 +231,29 @@ def _jslab_worker(rank, world, port, ni, nj):
 @pytest.mark.parametrize("world", [2, 3])
 def test_jslab_rows_and_gathers_gloo(world):
     mp.spawn(_jslab_worker, args=(world, _free_port(), 9, 31), nprocs=world, join=True)
+
+
+def test_iteration_stage_list_orders_exchanges_and_sweeps():
+    """The stage list every slab driver walks (host logic only): halos before the u assembly, du exchanged before the
+    u sweeps, 2*nswp colour passes per equation with pp = 0 folded into the first pressure passes, the reference
+    pressure before the correction, and -- general family -- the temperature equation after the correction."""
+    from cfd_b200.dist import iteration_stages
+    nswp = (3, 2, 5, 4)
+    st = iteration_stages(nswp, solve_t=True)
+    kinds = [s[0] for s in st]
+    assert kinds[0] == "halos" and {f[0] for f in st[0][1]} == {"u", "v", "p"}
+    assert kinds[1] == "compute" and st[2][:2] == ("halo", "du")
+    sweeps = [s for s in st if s[0] == "sweep"]
+    for name, n in zip(("u", "v", "pp", "t"), nswp):
+        mine = [s for s in sweeps if s[1] == name]
+        assert len(mine) == 2 * n
+        assert [s[4] for s in mine] == [0, 1] * n                                   # red, black, red, black ...
+        assert [s[5] for s in mine] == ([True, True] + [False] * (2 * n - 2) if name == "pp" else [False] * (2 * n))
+    assert [s[2:4] for s in sweeps if s[1] == "u"][0] == (3, 2) and [s[2:4] for s in sweeps if s[1] == "v"][0] == (2, 3)
+    i_ppref = kinds.index("ppref")
+    assert kinds[i_ppref + 1] == "compute"                                          # the correction
+    assert max(i for i, s in enumerate(st) if s[0] == "sweep" and s[1] == "pp") < i_ppref
+    assert st[i_ppref + 2][0] == "halos" and {f[0] for f in st[i_ppref + 2][1]} == {"u", "t"}
+    assert min(i for i, s in enumerate(st) if s[0] == "sweep" and s[1] == "t") > i_ppref + 3
+    cav = iteration_stages(nswp[:3])
+    assert [s for s in cav if s[0] == "sweep" and s[1] == "t"] == [] and cav[-1][0] == "compute"
