@@ -102,11 +102,12 @@ def test_buoyancy_production_assembly_vs_oracle(cfd, oracle, n, iadv):
     check_production_assembly(cfd, oracle, n, iadv)
 
 
-@pytest.mark.parametrize("n,tdma_m", [(2100, 16), (5200, 13)])
+@pytest.mark.parametrize("n,tdma_m", [(2100, 16), (1790, 4), (5200, 13)])
 @pytest.mark.parametrize("iadv", [3, 4])
 def test_buoyancy_tma_assembly_vs_oracle(cfd, oracle, n, tdma_m, iadv):
-    """Long lines take the TMA-staged kernels of general_tma_kernels.cu (T = 160 consumer threads in the 384-thread
-    build, T = 416 in the 768-thread one): same check as above."""
+    """Long lines take the TMA-staged kernels of general_tma_kernels.cu: T = 160 layout threads (one block per line),
+    T = 448 (a line split over two blocks of 224 consumers, padding nodes in the last warp, as at 8192^2); T = 416 has
+    no aligned split and stays on the register-window kernels.  Same check as above."""
     check_production_assembly(cfd, oracle, n, iadv, tdma_m=tdma_m)
 
 
