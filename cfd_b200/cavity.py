@@ -150,10 +150,12 @@ class CavityFVM:
 
     def upload_noalloc(self, name: str, a: np.ndarray):
         """cfd_upload_noalloc: same effect as `upload`, staged in the library's built-in 32 MiB device buffer
-        (no cudaMalloc at run time); grids up to ni*nj = 4 194 304 nodes."""
-        a = np.asfortranarray(a, dtype=np.float64)
-        assert a.shape == (self.ni, self.nj), (a.shape, self.ni, self.nj)
-        check(self.lib.cfd_upload_noalloc(self._h, FIELD_ID[name], a.ctypes.data_as(C.c_void_p), a.shape[0]))
+        (no cudaMalloc at run time); grids up to ni*nj = 4 194 304 nodes.  `a` may be the leading (ni, nj) part of a
+        larger column-major array (leading dimension > ni), like the reference's (it, jt) arrays."""
+        assert a.dtype == np.float64 and a.shape == (self.ni, self.nj), (a.dtype, a.shape, self.ni, self.nj)
+        if not (a.strides[0] == 8 and a.strides[1] % 8 == 0 and a.strides[1] >= 8 * self.ni):
+            a = np.asfortranarray(a)
+        check(self.lib.cfd_upload_noalloc(self._h, FIELD_ID[name], a.ctypes.data_as(C.c_void_p), a.strides[1] // 8))
 
     def upload_ptr(self, name: str, ptr: int, ld: int):
         check(self.lib.cfd_upload(self._h, FIELD_ID[name], C.c_void_p(ptr), ld))

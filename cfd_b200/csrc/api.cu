@@ -131,6 +131,31 @@ static bool geom_is_j(int id) {
   }
 }
 
+// ---- upload for callers that must not allocate ----------------------------------------------------------
+// cfd_upload() stages the host image in a device buffer that it cudaMalloc's on its first call.  Some hosts of
+// this library cannot tolerate that: a driver that has already handed all free HBM to its own pool (an
+// OpenACC / CUDA-Fortran runtime arena, an MPS client at its memory limit) gets an out-of-memory error from any
+// later cudaMalloc, and a time-stepping loop that re-uploads boundary data every iteration (the `boundary()` /
+// `gamsor()` hooks of buoyancy_cav.f90) must not hit cudaMalloc's device-wide synchronisation in the middle of
+// the loop.  For them the staging area below is part of the library image itself.  With CUDA's lazy module loading
+// (the default) the array gets its device memory when this module is first touched on a GPU, so cfd_create --
+// which allocates anyway -- looks its address up on the context's device (cfd_noalloc_resolve); from then until
+// the process exits nothing is allocated or freed by cfd_upload_noalloc.
+#define CFD_NOALLOC_MAX_DOUBLES (4u * 1024u * 1024u) /* 32 MiB: grids up to ni*nj = 4 194 304 nodes (2048 x 2048) */
+static __device__ __align__(256) double g_noalloc_stage[CFD_NOALLOC_MAX_DOUBLES];
+// Device addresses of g_noalloc_stage, one per device ordinal.  In host code the symbol itself is only a
+// stand-in; the address a kernel or a memcpy may use comes from cudaGetSymbolAddress with that device current.
+static double* g_noalloc_addr[64] = {nullptr};
+
+// Look the staging area's address up on device `dev` (which must be the current device).  Called by cfd_create.
+static int cfd_noalloc_resolve(int dev) {
+  if (dev < 0 || dev >= 64 || g_noalloc_addr[dev]) return CFD_OK;   // ordinals >= 64: cfd_upload_noalloc refuses them
+  double* p = nullptr;
+  CFD_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_stage));
+  g_noalloc_addr[dev] = p;
+  return CFD_OK;
+}
+
 extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CFD_REQUIRE(out && cfg, "null argument");
   *out = nullptr;
@@ -186,6 +211,18 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->res_dev = nullptr;
   c->seq_scratch = nullptr;
   c->launches = 0;
+  // from here on every failure path releases what has been allocated so far
+#define CREATE_CUDA(call)                                                                       \
+  do {                                                                                          \
+    cudaError_t e__ = (call);                                                                   \
+    if (e__ != cudaSuccess) {                                                                   \
+      cfd_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));     \
+      cfd_destroy(c);                                                                           \
+      return e__ == cudaErrorMemoryAllocation ? CFD_ERR_NOMEM : CFD_ERR_CUDA;                   \
+    }                                                                                           \
+  } while (0)
+  CREATE_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, dev));
+  CREATE_CUDA(cudaDeviceGetAttribute(&c->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   for (auto& g : c->gfast) g = nullptr;
   for (auto& g : c->tfast) g = nullptr;
   c->spike_w = c->spike_z = c->spike_small = nullptr;
@@ -228,34 +265,44 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
       cfd_destroy(c);
       return CFD_ERR_NOMEM;
     }
-    CFD_CUDA(cudaMemset(c->field[f], 0, fbytes));
+    CREATE_CUDA(cudaMemset(c->field[f], 0, fbytes));
   }
   if (cudaMalloc(&c->coef, c->L.nc * fbytes) != cudaSuccess) {
     cfd_set_error("cudaMalloc of %zu bytes for the coefficient block failed", c->L.nc * fbytes);
     cfd_destroy(c);
     return CFD_ERR_NOMEM;
   }
-  CFD_CUDA(cudaMemset(c->coef, 0, c->L.nc * fbytes));
+  CREATE_CUDA(cudaMemset(c->coef, 0, c->L.nc * fbytes));
   for (int a = 0; a < c->L.nc; ++a)
     c->field[c->L.nc == 6 ? kCoefOrder6[a] : kCoefOrder5[a]] = c->coef + (size_t)a * c->L.T;
   for (int g = 0; g < CFD_GEOM_COUNT; ++g) {
     const size_t n = geom_is_j(g) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
     c->geom_host[g].assign(geom_is_j(g) ? c->L.nj : c->L.ni, 0.0);
-    CFD_CUDA(cudaMalloc(&c->geom[g], n * sizeof(double)));
-    CFD_CUDA(cudaMemset(c->geom[g], 0, n * sizeof(double)));
+    CREATE_CUDA(cudaMalloc(&c->geom[g], n * sizeof(double)));
+    CREATE_CUDA(cudaMemset(c->geom[g], 0, n * sizeof(double)));
     const size_t nn = (size_t)(geom_is_j(g) ? c->L.nj : c->L.ni) + 2;
-    CFD_CUDA(cudaMalloc(&c->geomn[g], nn * sizeof(double)));
-    CFD_CUDA(cudaMemset(c->geomn[g], 0, nn * sizeof(double)));
+    CREATE_CUDA(cudaMalloc(&c->geomn[g], nn * sizeof(double)));
+    CREATE_CUDA(cudaMemset(c->geomn[g], 0, nn * sizeof(double)));
   }
   for (int g = 0; g < 8; ++g) {
     const size_t n = (g >= 4) ? (size_t)c->L.LD : (size_t)c->L.ni + 2;
-    CFD_CUDA(cudaMalloc(&c->gfast[g], n * sizeof(double)));
-    CFD_CUDA(cudaMemset(c->gfast[g], 0, n * sizeof(double)));
+    CREATE_CUDA(cudaMalloc(&c->gfast[g], n * sizeof(double)));
+    CREATE_CUDA(cudaMemset(c->gfast[g], 0, n * sizeof(double)));
   }
   c->max_partials = ((c->L.T + 31) / 32) * ((c->L.ni + 3) / 4);
-  CFD_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
-  CFD_CUDA(cudaMalloc(&c->res_dev, 8 * sizeof(double)));
-  CFD_CUDA(cudaMemset(c->res_dev, 0, 8 * sizeof(double)));
+  CREATE_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
+  CREATE_CUDA(cudaMalloc(&c->res_dev, CFD_RES_SLOTS * sizeof(double)));
+  CREATE_CUDA(cudaMemset(c->res_dev, 0, CFD_RES_SLOTS * sizeof(double)));
+  {
+    // cfd_upload_noalloc's staging area: with lazy module loading the array is only materialised when something in
+    // this module is first touched, so touch it HERE, while allocating is still allowed (see cfd_upload_noalloc)
+    int rcn = cfd_noalloc_resolve(dev);
+    if (rcn) {
+      cfd_destroy(c);
+      return rcn;
+    }
+  }
+#undef CREATE_CUDA
   *out = c;
   return CFD_OK;
 }
@@ -293,6 +340,7 @@ extern "C" int cfd_set_stream(cfd_ctx* c, void* s) {
 
 extern "C" int cfd_synchronize(cfd_ctx* c) {
   CFD_REQUIRE(c, "null context");
+  CFD_CUDA(cudaSetDevice(c->device));
   CFD_CUDA(cudaStreamSynchronize(c->stream));
   return CFD_OK;
 }
@@ -386,20 +434,6 @@ extern "C" int cfd_upload(cfd_ctx* c, int field, const double* host, int ld) {
   return CFD_OK;
 }
 
-// ---- upload for callers that must not allocate ----------------------------------------------------------
-// cfd_upload() stages the host image in a device buffer that it cudaMalloc's on its first call.  Some hosts of
-// this library cannot tolerate that: a driver that has already handed all free HBM to its own pool (an
-// OpenACC / CUDA-Fortran runtime arena, an MPS client at its memory limit) gets an out-of-memory error from any
-// later cudaMalloc, and a time-stepping loop that re-uploads boundary data every iteration (the `boundary()` /
-// `gamsor()` hooks of buoyancy_cav.f90) must not hit cudaMalloc's device-wide synchronisation in the middle of
-// the loop.  For them the staging area below is part of the library image itself: it exists on every GPU that
-// loads libcfd_b200.so, from load until the process exits, and nothing is allocated or freed at run time.
-#define CFD_NOALLOC_MAX_DOUBLES (4u * 1024u * 1024u) /* 32 MiB: grids up to ni*nj = 4 194 304 nodes (2048 x 2048) */
-static __device__ __align__(256) double g_noalloc_stage[CFD_NOALLOC_MAX_DOUBLES];
-// Device addresses of g_noalloc_stage, one per device ordinal.  In host code the symbol itself is only a
-// stand-in; the address a kernel or a memcpy may use comes from cudaGetSymbolAddress with that device current.
-static double* g_noalloc_addr[64] = {nullptr};
-
 extern "C" int cfd_upload_noalloc(cfd_ctx* c, int field, const double* host, int ld) {
   CFD_REQUIRE(c && host, "null argument");
   int rc = check_field(c, field);
@@ -413,12 +447,8 @@ extern "C" int cfd_upload_noalloc(cfd_ctx* c, int field, const double* host, int
   }
   CFD_REQUIRE(c->device >= 0 && c->device < 64, "device ordinal outside the supported range 0..63");
   CFD_CUDA(cudaSetDevice(c->device));
-  if (!g_noalloc_addr[c->device]) {   // one-time set-up on this device (do it before any stream capture)
-    double* p = nullptr;
-    CFD_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_stage));
-    g_noalloc_addr[c->device] = p;
-  }
-  double* stage = g_noalloc_addr[c->device];
+  double* stage = g_noalloc_addr[c->device];   // looked up by cfd_create on this device
+  CFD_REQUIRE(stage, "the built-in staging area was not resolved on this device (cfd_create does it)");
   // the image is overwritten completely (ni*nj doubles), so nothing left by an earlier call is ever read
   CFD_CUDA(cudaMemcpy2DAsync(stage, (size_t)c->L.ni * sizeof(double), host, (size_t)ld * sizeof(double),
                              (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyHostToDevice, c->stream));
@@ -446,6 +476,7 @@ extern "C" int cfd_probe(cfd_ctx* c, int field, int i, int j, double* value) {
   int rc = check_field(c, field);
   if (rc) return rc;
   CFD_REQUIRE(i >= 1 && i <= c->L.ni && j >= 1 && j <= c->L.nj, "probe index out of range");
+  CFD_CUDA(cudaSetDevice(c->device));
   const double* src = c->field[field] + (size_t)(i - 1) * c->L.LD + lpos(j - 1, c->L.M, c->L.T);
   CFD_CUDA(cudaMemcpyAsync(value, src, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CFD_CUDA(cudaStreamSynchronize(c->stream));
@@ -492,11 +523,18 @@ static int asm_v(cfd_ctx* c) {
 static int asm_p(cfd_ctx* c) {
   return is_general(c) ? cfd_launch_general_assemble(c, 2) : is_teach(c) ? cfd_launch_teach_assemble(c, 2) : cfd_launch_assemble_p(c);
 }
-extern "C" int cfd_assemble_u(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_u(c); }
-extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_v(c); }
-extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_REQUIRE(c, "null context"); return asm_p(c); }
+// Every entry point that launches or copies makes the context's device current first: one process may hold
+// contexts on several GPUs and call them in any order.
+#define CFD_ENTER(c)                         \
+  do {                                       \
+    CFD_REQUIRE(c, "null context");          \
+    CFD_CUDA(cudaSetDevice((c)->device));    \
+  } while (0)
+extern "C" int cfd_assemble_u(cfd_ctx* c) { CFD_ENTER(c); return asm_u(c); }
+extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_ENTER(c); return asm_v(c); }
+extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_ENTER(c); return asm_p(c); }
 extern "C" int cfd_assemble_t(cfd_ctx* c) {
-  CFD_REQUIRE(c, "null context");
+  CFD_ENTER(c);
   CFD_REQUIRE(is_general(c), "cfd_assemble_t needs a CFD_FAMILY_GENERAL context");
   return cfd_launch_general_assemble(c, 3);
 }
@@ -516,10 +554,10 @@ extern "C" int cfd_set_hook(cfd_ctx* c, int eq, const cfd_hook_desc* d) {
   cfd_set_error("cfd_set_hook: hook kind %d is not defined for equation %d", d->kind, eq);
   return CFD_ERR_UNSUPPORTED;
 }
-extern "C" int cfd_correct(cfd_ctx* c, const double* ppref) { CFD_REQUIRE(c, "null context"); return cfd_launch_correct(c, ppref); }
+extern "C" int cfd_correct(cfd_ctx* c, const double* ppref) { CFD_ENTER(c); return cfd_launch_correct(c, ppref); }
 
 extern "C" int cfd_sweep(cfd_ctx* c, int istart, int jstart, int field, int colour, int first) {
-  CFD_REQUIRE(c, "null context");
+  CFD_ENTER(c);
   int rc = check_field(c, field);
   if (rc) return rc;
   CFD_REQUIRE(istart >= 2 && jstart >= 2 && jstart <= c->L.nj - 1, "istart/jstart out of range");
@@ -529,7 +567,7 @@ extern "C" int cfd_sweep(cfd_ctx* c, int istart, int jstart, int field, int colo
 }
 
 extern "C" int cfd_sweep_part(cfd_ctx* c, int istart, int jstart, int field, int colour, int first, int part) {
-  CFD_REQUIRE(c, "null context");
+  CFD_ENTER(c);
   int rc = check_field(c, field);
   if (rc) return rc;
   CFD_REQUIRE(istart >= 2 && jstart >= 2 && jstart <= c->L.nj - 1, "istart/jstart out of range");
@@ -676,10 +714,12 @@ extern "C" int cfd_wall_download(cfd_ctx* c, int which, double* host, int n) {
 }
 extern "C" int cfd_assemble_te(cfd_ctx* c) {
   CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  CFD_CUDA(cudaSetDevice(c->device));
   return cfd_launch_teach_scalar(c, CFD_EQ_TE);
 }
 extern "C" int cfd_assemble_ed(cfd_ctx* c) {
   CFD_REQUIRE(c && is_teach(c) && c->turbulent, "needs a TEACH context after cfd_set_turbulence");
+  CFD_CUDA(cudaSetDevice(c->device));
   return cfd_launch_teach_scalar(c, CFD_EQ_ED);
 }
 extern "C" int cfd_calcte(cfd_ctx* c, double* resork) {
@@ -754,6 +794,7 @@ extern "C" int cfd_iterate(cfd_ctx* c, int n, double res[8]) {
 
 extern "C" int cfd_residuals(cfd_ctx* c, double res[8]) {
   CFD_REQUIRE(c && res, "null argument");
+  CFD_CUDA(cudaSetDevice(c->device));
   CFD_CUDA(cudaMemcpyAsync(res, c->res_dev, 8 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CFD_CUDA(cudaStreamSynchronize(c->stream));
   return CFD_OK;

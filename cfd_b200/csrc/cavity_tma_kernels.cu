@@ -458,8 +458,7 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
   FastGeom G;
   G.rdxu = c->gfast[0]; G.rdx = c->gfast[1]; G.rsew = c->gfast[2]; G.rsewu = c->gfast[3];
   G.rdyL = c->gfast[4]; G.rdyvL = c->gfast[5]; G.rsnsL = c->gfast[6]; G.rsnsvL = c->gfast[7];
-  static int num_sms = 0;
-  if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device));
+  const int num_sms = c->num_sms;
   const int T = c->L.T, narr = which == 0 ? NU_ARR : NV_ARR;
   const size_t stage = (size_t)narr * T * sizeof(double);
   int S = 8;
@@ -471,7 +470,7 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
   const int nblocks = nlines < num_sms ? nlines : num_sms;
   cudaError_t e;
 #define LAUNCH_ASM(KERNEL)                                                                         \
-  e = cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);        \
+  e = cfd_raise_smem(c, KERNEL);                                                                   \
   if (e == cudaSuccess) KERNEL<<<nblocks, T + 32 * ASM_PRODUCER_WARPS, smem, c->stream>>>(P, G, S);
   if (T + 32 * ASM_PRODUCER_WARPS > 384) {   // a 768-thread build spills (80 registers) and loses to the register-window kernels
     cfd_set_error("k_assemble_*_tma: lines of %d layout threads do not fit the 384-thread build", T);

@@ -39,6 +39,8 @@ struct Layout {
 __host__ __device__ __forceinline__ int lpos(int j0, int M, int T) { return (j0 % M) * T + (j0 / M); }
 
 #define CFD_MAX_M 16
+// res_dev: the 8 residual sums cfd_residuals / cfd_iterate hand to the host, then TEACH's outlet increment uinc
+#define CFD_RES_SLOTS 9
 
 // Everything a cavity-family kernel needs, passed by value.
 struct CavParams {
@@ -141,7 +143,23 @@ struct cfd_ctx {
   bool tfast_ready;
   bool exact_assembly;              // bit-exact assembly kernels (sequential-order mode, or CFD_B200_EXACT_ASSEMBLY=1)
   long long launches;               // kernels launched by this context so far (cfd_launch_count)
+  int num_sms;                      // SM count of THIS context's device (persistent grids are sized from it)
+  int smem_optin;                   // largest dynamic shared memory a block may opt into on this device
+  std::vector<const void*> smem_raised;   // kernels whose dynamic shared-memory limit was raised for this context's device
 };
+
+// cudaFuncSetAttribute is per device and costs a driver call: raise a kernel's dynamic shared-memory limit to the
+// device's opt-in maximum the first time THIS context launches it (contexts on other devices do their own), never
+// on the per-launch path after that.
+template <class K>
+static inline cudaError_t cfd_raise_smem(cfd_ctx* c, K kernel) {
+  const void* f = reinterpret_cast<const void*>(kernel);
+  for (const void* g : c->smem_raised)
+    if (g == f) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem_optin);
+  if (e == cudaSuccess) c->smem_raised.push_back(f);
+  return e;
+}
 
 // kernels / launchers implemented across the .cu files (all asynchronous on ctx->stream)
 int cfd_launch_assemble_u(cfd_ctx* c);

@@ -760,8 +760,7 @@ bool cfd_general_tma_eligible(const cfd_ctx* c, int which) {
 
 // which: 0 u, 1 v, 2 p', 3 T.  Returns the number of residual partials (grid size), or a negative status.
 int cfd_launch_general_assemble_tma(cfd_ctx* c, int which, const GenFastParams& P) {
-  static int num_sms = 0;
-  if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device));
+  const int num_sms = c->num_sms;
   const int T = c->L.T, narr = which == 0 ? GT_NU : which == 1 ? GT_NV : which == 2 ? GT_NP : GT_NT, nsplit = gt_nsplit(T), TT = T / nsplit;
   const size_t stage = (size_t)narr * TT * sizeof(double);
   int S = 8;
@@ -778,7 +777,7 @@ int cfd_launch_general_assemble_tma(cfd_ctx* c, int which, const GenFastParams& 
       : which == 1 ? (hybrid ? k_gen_assemble_v_tma<3> : k_gen_assemble_v_tma<0>)
       : which == 2 ? k_gen_assemble_p_tma
                    : (hybrid ? k_gen_assemble_t_tma<3> : k_gen_assemble_t_tma<0>);
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cfd_raise_smem(c, kernel);
   if (e == cudaSuccess) kernel<<<nblocks, nthreads, smem, c->stream>>>(P, S, nsplit);
   if (e != cudaSuccess) {
     cfd_set_error("k_gen_assemble_*_tma: %s", cudaGetErrorString(e));

@@ -616,8 +616,8 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   // chunked production sweeps: warm-up length from the contraction rate of the recurrences (see k_lod_y_chunk)
   // `slots` = blocks of the sweep kernel resident on the GPU at once: every block lives as long as the kernel, so
   // the grid should fit in one wave (a second, partial wave would double the time)
-  static int num_sms = 0;
-  if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, h->device));
+  int num_sms = 0;   // of this handle's device; one attribute query per call, outside the step loop
+  CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, h->device));
   auto plan = [](int n, int nlines, int slots, double fo, LodChunk& c) {
     const double m = fo > 0 ? ((1.0 + 2.0 * fo) - sqrt(1.0 + 4.0 * fo)) / (2.0 * fo) : 0.0;
     int warm = (m > 0 && m < 1) ? (int)ceil(70.0 * log(2.0) / -log(m)) : 1;

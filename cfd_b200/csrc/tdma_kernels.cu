@@ -503,8 +503,8 @@ static int launch_tma_m(cfd_ctx* c, const SweepParams& P, int nblocks, int S, si
   cudaError_t e = cudaSuccess;
 #define LAUNCH_TDMA(BM, NCV)                                                                                   \
   {                                                                                                           \
-    e = cudaFuncSetAttribute(k_tdma_tma<M, BM, NCV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    k_tdma_tma<M, BM, NCV><<<nblocks, nthreads, smem, c->stream>>>(P, S);                                      \
+    e = cfd_raise_smem(c, k_tdma_tma<M, BM, NCV>);                                                            \
+    if (e == cudaSuccess) k_tdma_tma<M, BM, NCV><<<nblocks, nthreads, smem, c->stream>>>(P, S);                \
   }
   const bool five = P.L.nc == 5;
   if (nthreads <= 352) {
@@ -655,9 +655,8 @@ int cfd_launch_spike_basis(cfd_ctx* c, int istart, int jstart) {
 
 static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P) {
   const int T = c->L.T;
-  static int num_sms = 0;
-  if (!num_sms) CFD_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device));
-  static int use_tma = -1;
+  const int num_sms = c->num_sms;
+  static int use_tma = -1;   // environment switch, the same for every device
   if (use_tma < 0) {
     const char* e = getenv("CFD_B200_TDMA_TMA");
     use_tma = e ? atoi(e) : 1;
@@ -751,11 +750,7 @@ int cfd_launch_sweep_seq2(cfd_ctx* c, int istart, int jstart, double* phi, int f
     cfd_set_error("sequential-order debug sweep supports nj <= 5120 (got %d)", c->L.nj);
     return CFD_ERR_UNSUPPORTED;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    CFD_CUDA(cudaFuncSetAttribute(k_tdma_seq, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
-  }
+  CFD_CUDA(cfd_raise_smem(c, k_tdma_seq));
   k_tdma_seq<<<1, 1024, smem, c->stream>>>(P);
   ++c->launches;
   CFD_CUDA(cudaGetLastError());

@@ -334,7 +334,7 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which) {
   P.ae = c->field[CFD_AE]; P.aw = c->field[CFD_AW]; P.an = c->field[CFD_AN]; P.as = c->field[CFD_AS];
   P.ap = c->field[CFD_AP]; P.su = c->field[CFD_SU];
   P.ufield = c->field[CFD_U];
-  P.uinc = c->res_dev + 7;          // last slot of the packed scalar block
+  P.uinc = c->res_dev + 8;          // device scalar behind the 8 residual slots the host sees (CFD_RES_SLOTS)
   P.tmult_n = c->turbulent ? c->tmult_n : nullptr;
   P.tmult_w = c->turbulent ? c->tmult_w : nullptr;
   P.x = c->geomn[CFD_G_X]; P.y = c->geom[CFD_G_Y]; P.xu = c->geomn[CFD_G_XU]; P.yv = c->geom[CFD_G_YV];

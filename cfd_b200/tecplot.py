@@ -8,12 +8,22 @@ import numpy as np
 
 
 def es14_7(v: float) -> str:
-    """Fortran edit descriptor es14.7 (one leading digit, 7 decimals, two-digit exponent, width 14)."""
+    """Fortran edit descriptor es14.7 (one leading digit, 7 decimals, width 14).  Exponents of one or two digits
+    print as E+dd; a three-digit exponent drops the letter (`-1.2345678-100`), as the Fortran standard prescribes
+    for Ew.d output, so the field keeps its width."""
     s = f"{v:.7E}"                      # e.g. -1.5782975E-01
     mant, exp = s.split("E")
     e = int(exp)
-    out = f"{mant}E{'+' if e >= 0 else '-'}{abs(e):02d}"
+    sign = "+" if e >= 0 else "-"
+    out = f"{mant}E{sign}{abs(e):02d}" if abs(e) < 100 else f"{mant}{sign}{abs(e):03d}"
     return out.rjust(14)
+
+
+def i3(n: int) -> str:
+    """Fortran edit descriptor i3: a value that does not fit three characters prints as `***` (the reference's zone
+    header does exactly that beyond 999 nodes, cavity_fvm.f90:593; teach_tecprint below follows the same rule)."""
+    s = f"{n:3d}"
+    return s if len(s) <= 3 else "***"
 
 
 def corner_pressure(p: np.ndarray, ipref: int, jpref: int) -> np.ndarray:
@@ -34,7 +44,7 @@ def write_result_dat(path, x, y, uc, vc, p, title="Lid Driven Cavity Flow"):
     with open(path, "w") as f:
         f.write(f' title="{title}"\n')
         f.write(' variables="x", "y", "u", "v", "p"\n')
-        f.write(f"zone  i={ni:3d}  j={nj:3d}  f=point\n")
+        f.write(f"zone  i={i3(ni)}  j={i3(nj)}  f=point\n")
         for j in range(nj):
             for i in range(ni):
                 f.write("".join(" " + es14_7(v) for v in (x[i], y[j], uc[i, j], vc[i, j], p[i, j])) + "\n")

@@ -150,9 +150,11 @@ int cfd_download(cfd_ctx* ctx, int field, double* host, int ld);
  * device-wide synchronisation.)  Same arguments and result as cfd_upload, but the column-major image is staged
  * in a 32 MiB buffer that is part of the library image on every GPU that loads it, so it calls no cudaMalloc /
  * cudaFree.  Limit: ni*nj <= 4 194 304 nodes (e.g. 2048 x 2048); larger grids get CFD_ERR_INVALID with a
- * message -- use cfd_upload.  The first call on each device looks the buffer's device address up
- * (cudaGetSymbolAddress); make that first call before any stream capture.  All contexts on one GPU share
- * the buffer: calls that overlap on the GPU (different streams or host threads) race, so issue them one at a time.
+ * message -- use cfd_upload.  The buffer's device address is looked up (cudaGetSymbolAddress), and with CUDA's
+ * lazy module loading its memory is materialised, by cfd_create on the context's device -- the one call that
+ * allocates anyway -- so no call of cfd_upload_noalloc itself ever reserves memory (with CUDA_MODULE_LOADING=EAGER
+ * it exists from library load).  All contexts on one GPU share the buffer: calls that overlap on the GPU
+ * (different streams or host threads) race, so issue them one at a time.
  */
 int cfd_upload_noalloc(cfd_ctx* ctx, int field, const double* host, int ld);
 /* monitor-point read u(imon,jmon) etc. (cavity_fvm.f90:559-563); LOCAL 1-based indices */

@@ -10,7 +10,9 @@ def test_es14_7_matches_fortran_edit_descriptor():
     assert tecplot.es14_7(1.0) == " 1.0000000E+00"
     assert tecplot.es14_7(2793.942303605858) == " 2.7939423E+03"
     assert tecplot.es14_7(9.99999999e-11) == " 1.0000000E-10"
-    assert all(len(tecplot.es14_7(v)) == 14 for v in (1e-300, -3.5e7, 12345.678))
+    assert all(len(tecplot.es14_7(v)) == 14 for v in (1e-300, -1e-300, -3.5e7, 12345.678))
+    assert tecplot.es14_7(-1.2345678e-100) == "-1.2345678-100"      # three-digit exponent: the letter is dropped
+    assert tecplot.i3(12) == " 12" and tecplot.i3(999) == "999" and tecplot.i3(4098) == "***"
 
 
 def test_result_files_structure(tmp_path, oracle):

@@ -27,7 +27,40 @@ def test_noalloc_upload_matches_upload_on_two_calls_in_a_row(cfd):
         new.close()
 
 
-def test_noalloc_upload_honours_leading_dimension_and_feeds_the_solver(cfd):
+def test_noalloc_upload_honours_a_padded_leading_dimension(cfd):
+    """A host array whose leading dimension is larger than ni (the reference's (it, jt) storage, control.f90:22-25):
+    the pitch argument of the staged copy must skip the padding rows exactly as cfd_upload does."""
+    rng = np.random.default_rng(7)
+    ref, new = cfd.CavityFVM(61, 40), cfd.CavityFVM(61, 40)
+    big = np.asfortranarray(rng.standard_normal((ref.ni + 3, ref.nj)))       # ld = ni + 3
+    a = big[:ref.ni, :]
+    assert a.strides == (8, 8 * (ref.ni + 3))
+    ref.upload("v", np.asfortranarray(a))
+    new.upload_noalloc("v", a)
+    assert np.array_equal(new.download("v"), ref.download("v"))
+    assert np.array_equal(new.download("v"), a)
+    ref.close()
+    new.close()
+
+
+def test_noalloc_upload_allocates_no_device_memory(cfd):
+    """The defining property: once the context exists, free device memory is the same before and after the call
+    (the staging area was materialised by cfd_create, not by the upload)."""
+    import torch
+    g = cfd.CavityFVM(500, 300)
+    a = np.asfortranarray(np.random.default_rng(3).standard_normal((g.ni, g.nj)))
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    g.upload_noalloc("u", a)                                                  # first call of this context
+    g.upload_noalloc("p", a)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, (free0, free1)
+    assert np.array_equal(g.download("u"), a)
+    g.close()
+
+
+def test_noalloc_upload_feeds_the_solver(cfd):
     g = cfd.CavityFVM(10, 10, order="sequential")
     h = cfd.CavityFVM(10, 10, order="sequential")
     g.init_lid_driven(reynolds=100.0)
