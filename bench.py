@@ -42,7 +42,9 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock, power and throttle reasons of one GPU sampled WHILE the timed region runs.  NVML is polled from a
+    thread every ~5 ms (a 20-step run lasts ~50 ms: an nvidia-smi loop at 200 ms would see it once); if NVML is not
+    importable the nvidia-smi loop is the fallback."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -50,8 +52,30 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.proc, self.lines = index, None, []
+        self.nvml, self.handle, self.samples, self._stop = None, None, [], threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            try:
+                import torch
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                h = None
+            if h is None:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+                h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml, self.handle = pynvml, h
+        except Exception:
+            self.nvml = None
 
     def start(self):
+        if self.nvml is not None:
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "200"],
@@ -61,11 +85,39 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        n, h = self.nvml, self.handle
+        while not self._stop.is_set():
+            try:
+                sm = n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)
+                pw = n.nvmlDeviceGetPowerUsage(h) / 1000.0
+                rs = n.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else n.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((sm, mx, pw, rs))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     def _read(self):
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop.set()
+            self.th.join(timeout=2)
+            n = self.nvml
+            bits = {"hw_slowdown": getattr(n, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                    "hw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                    "sw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                    "sw_power_cap": getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+            sm = sorted(x[0] for x in self.samples)
+            reasons = sorted(k for k, b in bits.items() if any(x[3] & b for x in self.samples))
+            return {"sm_mhz": float(sm[len(sm) // 2]) if sm else None,
+                    "sm_max_mhz": float(max(x[1] for x in self.samples)) if sm else None,
+                    "power_w_max": max(x[2] for x in self.samples) if sm else None, "samples": len(sm),
+                    "reasons": reasons, "how": "NVML polled every ~5 ms during the timed region"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -88,7 +140,8 @@ class ClockSampler:
                     reasons.add(nm)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons),
+                "how": "nvidia-smi -lms 200"}
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -148,6 +201,67 @@ def run_reference(args):
     emit(out)
 
 
+
+# ----------------------------------------------------------------------------------------------------------
+def parity_check(kind, slabs="i", iters=6):
+    """N > 1 only, before the timed region: a small problem of the same family runs once slab-decomposed over all
+    ranks (the very driver, kernels and exchange the timed run uses) and once in a single context on rank 0; the
+    gathered u, v, p are compared.  i-slabs must agree BIT FOR BIT (red/black iterates do not depend on the partition);
+    j-slabs reorder the elimination (partition method) and must agree to 1e-10.  Returns the record for the JSON line;
+    a mismatch makes every rank exit non-zero.  Lines are long enough (>= 1026 nodes) for the production TMA-staged
+    kernels to be the ones that run."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import cfd_b200
+    from cfd_b200.dist import BuoyancySlab, JSlabCavity, SlabCavity, TeachSlab
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if kind == "buoyancy":
+        n = 1026
+        shape = (n, n)
+        s = SlabCavity(n - 2, n - 2, slab_cls=BuoyancySlab)
+        single = (lambda: cfd_b200.BuoyantCavity(n, n, order="redblack")) if rank == 0 else None
+    elif kind == "step":
+        shape = (64 * world + 2, 1026)
+        s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab, epsx=1.0)
+        single = (lambda: cfd_b200.TeachFVM(shape[0], shape[1], epsx=1.0, order="redblack")) if rank == 0 else None
+    else:
+        shape = (64 * world, 1024) if slabs == "i" else (96, 256 * world)
+        s = (SlabCavity if slabs == "i" else JSlabCavity)(*shape, reynolds=REYNOLDS)
+
+        def single():
+            g = cfd_b200.CavityFVM(*shape, order="redblack")
+            g.init_lid_driven(reynolds=REYNOLDS)
+            return g
+    s.iterate(iters)
+    names = ("u", "v", "p") + (("t",) if kind == "buoyancy" else ())
+    got = {n: s.gather_field(n) for n in names}
+    s.ctx.close()
+    rec = None
+    if rank == 0:
+        g = single()
+        g.iterate(iters)
+        max_abs, bitwise, scale = 0.0, True, 0.0
+        for n in names:
+            want = g.download(n)
+            bitwise = bitwise and bool(np.array_equal(got[n], want))
+            max_abs = max(max_abs, float(np.abs(got[n] - want).max()))
+            scale = max(scale, float(np.abs(want).max()))
+        g.close()
+        tol = 0.0 if slabs == "i" else 1e-10 * max(1.0, scale)
+        rec = {"world": world, "case": f"{kind} {shape[0]}x{shape[1]}, {iters} outer iterations, {slabs}-slabs vs one context",
+               "fields": list(names), "bitwise": bitwise, "max_abs": max_abs, "tolerance": tol,
+               "ok": bool(bitwise if slabs == "i" else max_abs <= tol)}
+    flag = torch.tensor([1 if (rec is None or rec["ok"]) else 0], device="cuda")
+    dist.broadcast(flag, 0)
+    if int(flag.item()) != 1:
+        if rank == 0:
+            sys.stderr.write("bench.py: multi-GPU parity check FAILED: %s\n" % json.dumps(rec))
+        dist.destroy_process_group()
+        raise SystemExit(3)
+    return rec
+
 # ----------------------------------------------------------------------------------------------------------
 def run_ours(args):
     import numpy as np
@@ -167,6 +281,7 @@ def run_ours(args):
     K, W = args.steps, args.warmup
     hbm_peak, peak_src = peaks()
     stream = torch.cuda.Stream()
+    parity = parity_check("cavity", args.slabs) if world > 1 else None
 
     if world == 1:
         solver = cfd_b200.CavityFVM(NICV, NJCV, order="redblack", device=local)
@@ -241,6 +356,8 @@ def run_ours(args):
                       "l2": "inputs larger than L2 (1.9 GB of live fields per GPU vs 126 MB L2); no explicit flush",
                       "line_layout": ctx0.layout},
            "residuals_last": list(res[:3]), "gpu_launches": int(launches)}
+    if parity is not None:
+        out["parity_check"] = parity
 
     # ---- roofline of the dominant kernel (the red/black line solver), timed live with CUDA events ---------
     ctxr = ctx0
@@ -263,7 +380,7 @@ def run_ours(args):
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("k_tdma_rb", {}).get("dram_bytes_per_launch")
+            traffic = json.load(open(tp)).get("k_tdma_tma", {}).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
     out["roofline"] = {"bound": "hbm", "kernel": "k_tdma_tma (one colour pass of a line sweep)",
@@ -456,8 +573,10 @@ def run_cavity16k(args):
     hbm_peak, peak_src = peaks()
     NG = 16384
     stream = torch.cuda.current_stream()
+    parity = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        parity = parity_check("cavity", "j")
         solver = JSlabCavity(NG, NG, reynolds=REYNOLDS)
         step, ctx0 = solver.iterate_async, solver.ctx
     else:
@@ -509,6 +628,8 @@ def run_cavity16k(args):
                         "peak_source": peak_src, "traffic": None,
                         "note": "algorithmic bytes of the single-context algorithm (928 B/cell); the partition method moves more"},
            "e2e": None, "clocks": clocks}
+    if parity is not None:
+        out["parity_check"] = parity
     if rank == 0:
         emit(out)
     if world > 1:
@@ -535,6 +656,7 @@ def run_step(args, kind="step"):
     hbm_peak, peak_src = peaks()
     NI, NJ = (16384, 4096) if kind == "step" else (8194, 8194)
     stream = torch.cuda.Stream()
+    parity = parity_check(kind) if world > 1 else None
     if world == 1:
         if kind == "step":
             solver = cfd_b200.TeachFVM(NI, NJ, epsx=1.0, order="redblack", device=local)
@@ -597,6 +719,8 @@ def run_step(args, kind="step"):
                         "unit": "GB/s", "frac": B * glups / world / hbm_peak, "peak_source": peak_src, "traffic": None,
                         "algorithmic_bytes_per_cell": B},
            "e2e": None, "clocks": clocks}
+    if parity is not None:
+        out["parity_check"] = parity
     if rank == 0:
         emit(out)
     if world > 1:
