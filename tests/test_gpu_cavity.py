@@ -313,3 +313,99 @@ def test_iterate_reports_divergence(cfd):
         g.iterate(1)
     g.iterate_async(1)          # without a residual read-back nothing is checked (and nothing blocks)
     g.close()
+
+
+# ---- converged-field parity above 64^2 ---------------------------------------------------------------
+def _kat():
+    import json
+    import os
+    return json.load(open(os.path.join(os.path.dirname(__file__), "golden", "cavity_kat.json")))
+
+
+def test_cv128_re1000_redblack_converges_to_the_known_answer(cfd):
+    """128^2 CV, Re=1000, literal stop rule max(res) < 1e-10 (cavity_fvm.f90:565): the independent transliteration
+    (tests/golden/cavity_kat.json, regenerated by tools/gen_kat.py) needs 22 887 iterations in the reference's
+    sequential order; red/black lines reach the same fixed point in about as many.  Monitor values to 1e-8."""
+    k = _kat()["cv128_re1000"]
+    g = cfd.CavityFVM(128, 128, order="redblack")
+    g.init_lid_driven(reynolds=1000.0)
+    n = g.run(maxit=60000)
+    assert abs(n - k["iters"]) <= 0.01 * k["iters"], n
+    u, v = g.probe("u", k["imon"], k["jmon"]), g.probe("v", k["imon"], k["jmon"])
+    assert abs(u - k["final_uv"][0]) <= 1e-8 * abs(k["final_uv"][0])
+    assert abs(v - k["final_uv"][1]) <= 1e-8 * abs(k["final_uv"][1])
+    uc = 0.5 * (u + g.probe("u", k["imon"] + 1, k["jmon"]))             # centred_vel, cavity_fvm.f90:424
+    assert abs(uc - k["uc_mon"]) <= 1e-8 * abs(k["uc_mon"])
+    g.close()
+
+
+def test_cv128_re1000_sequential_residuals_at_iteration_1000_match_the_known_answer(cfd):
+    """Same case in the reference's line order: the residual sums of iteration 1000 are in the known-answer table."""
+    k = _kat()["cv128_re1000"]
+    g = cfd.CavityFVM(128, 128, order="sequential")
+    g.init_lid_driven(reynolds=1000.0)
+    res = g.iterate(1000)
+    for a, b in zip(res, k["iter1000"]):
+        assert abs(a - b) <= 1e-9 * abs(b), (res, k["iter1000"])
+    g.close()
+
+
+@pytest.mark.slow
+def test_trajectory_1024_sequential_20_iterations_bitwise(cfd, oracle):
+    """20 outer iterations at 1024^2 in the reference's sequential order, every field bit for bit."""
+    o, g = make_pair(cfd, oracle, 1024, 1024, re=1000.0)
+    o.run(maxit=20, tol=0.0)
+    res = g.iterate(20)
+    for name in ("u", "v", "p", "pp"):
+        assert np.array_equal(g.download(name), getattr(o, name)), name
+    for a, b in zip(res, o.residuals):
+        assert abs(a - b) <= 1e-11 * abs(b)
+    g.close()
+
+
+@pytest.mark.slow
+@pytest.mark.parametrize("re", [100, 1000])
+def test_cv256_redblack_converges_to_the_reference_solution(cfd, re):
+    """256^2 CV to the literal stop rule.  The CPU oracle needs the better part of an hour for this, so its converged
+    answer is a committed fixture (tools/gen_cavity_converged.py wrote tests/golden/cavity_cv256_re*.npz from
+    oracle/cavity_oracle.c in the reference's sequential order): iteration count, monitor values, |.|-sums, the two
+    centre-line profiles the reference writes (uvel.txt / vvel.txt) and a strided sample of u, v, p -- all to 1e-8
+    relative L-inf, north_star's bar for converged fields."""
+    import os
+    path = os.path.join(os.path.dirname(__file__), "golden", f"cavity_cv256_re{re}.npz")
+    f = np.load(path)
+    g = cfd.CavityFVM(256, 256, order="redblack")
+    g.init_lid_driven(reynolds=float(re))
+    n = g.run(maxit=int(2 * f["iters"]), check_every=20)
+    assert abs(n - int(f["iters"])) <= 0.01 * int(f["iters"]) + 20, (n, int(f["iters"]))
+    u, v, p = g.download("u"), g.download("v"), g.download("p")
+    st, im, jm = int(f["stride"]), int(f["imon"]), int(f["jmon"])
+    for got, want, name in ((u[im - 1, :], f["u_centre"], "u centre line"), (v[:, jm - 1], f["v_centre"], "v centre line"),
+                            (p[im - 1, :], f["p_centre"], "p centre line"), (u[::st, ::st], f["u_s"], "u sample"),
+                            (v[::st, ::st], f["v_s"], "v sample"), (p[::st, ::st], f["p_s"], "p sample")):
+        assert linf_rel(got, want) < 1e-8, name
+    sums = np.array([np.abs(u).sum(), np.abs(v).sum(), np.abs(p).sum()])
+    assert np.all(np.abs(sums - f["sum_abs"]) <= 1e-8 * f["sum_abs"])
+    g.close()
+
+
+@pytest.mark.parametrize("istart,jstart,field", [(3, 2, "u"), (2, 3, "v"), (2, 2, "pp")])
+def test_lisolv_drop_in_on_host_assembled_coefficients(cfd, oracle, istart, jstart, field):
+    """What the Fortran shim's lisolv(istart,jstart,ni,nj,phi) does (fortran/cfd_b200_shim.f90, module linsolv_mod):
+    a private sequential-order context with raw coefficient storage, the six HOST coefficient arrays and phi uploaded,
+    one cfd_lisolv, phi downloaded -- bit-identical to the reference's lisolv (cavity_fvm.f90:49-82) on the same arrays."""
+    o = oracle.Cavity(40, 56, 100.0)
+    rng = np.random.default_rng(17)
+    for name, scale, base in (("u", 0.3, 0.0), ("v", 0.3, 0.0), ("p", 5.0, 0.0), ("den", 50.0, 1000.0), ("vis", 2.0, 10.0)):
+        getattr(o, name)[:, :] = base + scale * (rng.random((o.ni, o.nj)) - 0.5)
+    {"u": o.assemble_u, "v": o.assemble_v, "pp": o.assemble_p}[field]()      # host-assembled ae..su
+    phi = np.asfortranarray(rng.random((o.ni, o.nj)))
+    g = cfd.CavityFVM(40, 56, order="sequential", raw_coefficients=True)     # no geometry, no fields: solver only
+    for n, on in (("ap", "ap"), ("an", "an"), ("as", "as_"), ("ae", "ae"), ("aw", "aw"), ("su", "su")):
+        g.upload(n, getattr(o, on))
+    g.upload("pp", phi)
+    g.lisolv(istart, jstart, "pp")
+    want = phi.copy(order="F")
+    o.lisolv(istart, jstart, want)
+    assert np.array_equal(g.download("pp"), want)
+    g.close()
