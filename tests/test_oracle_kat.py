@@ -1,0 +1,149 @@
+"""oracle/*.c against the known-answer tables of tools/gen_kat.py -- a second, independently written restatement of the
+reference programs (whole-array numpy + numba recurrences, written from the .f90 sources, sharing no code with oracle/
+or cfd_b200/).  The reference ships no expected outputs and cannot be compiled here, so this is what stands between the
+C oracle and a transcription slip: every family's residual history, monitor values, field sums and iteration counts
+must come out the same from both restatements.  Tolerances: 1e-11 on residual sums (summation order differs), 1e-12 on
+field values, exact on iteration counts."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def kat(name):
+    return json.load(open(os.path.join(GOLD, name + "_kat.json")))
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
+
+
+# ---- cavity_fvm.f90: three-way (SURVEY table, regenerated table, C oracle) ------------------------------------------------
+def test_cavity_regenerated_table_agrees_with_the_survey_table():
+    a, b = kat("cavity_regen"), kat("cavity")
+    assert a["cv10_re100"]["iters"] == b["cv10_re100"]["iters"] == 232
+    for it, row in b["cv10_re100"]["history"].items():
+        if it not in a["cv10_re100"]["history"]:
+            continue
+        got = a["cv10_re100"]["history"][it]
+        for g, w in zip(got[:3], row[:3]):
+            assert rel(g, w) < (1e-11 if int(it) <= 10 else 1e-9)
+        for g, w in zip(got[3:], row[3:]):
+            assert rel(g, w) < 1e-12
+    assert rel(a["cv10_re100"]["uc_mon"], b["cv10_re100"]["uc_mon"]) < 1e-12
+    for k, j in (("sum_abs_u", 0), ("sum_abs_v", 1), ("sum_abs_p", 2)):
+        assert rel(a["cv10_re100"]["sum_abs"][j], b["cv10_re100"][k]) < 1e-12
+    assert a["cv32_re100"]["iters"] == b["cv32_re100"]["iters"] == 2093
+    assert rel(a["cv32_re100"]["min_centreline_uc"], b["cv32_re100"]["min_centreline_uc"]) < 1e-11
+    assert a["cv64_re100"]["iters"] == b["cv64_re100"]["iters"] == 8258
+    assert rel(a["cv64_re100"]["uc_mon"], b["cv64_re100"]["uc_mon"]) < 1e-11
+    assert a["cv128_re1000"]["iters"] == b["cv128_re1000"]["iters"] == 22887
+    for g, w in zip(a["cv128_re1000"]["iter1000"], b["cv128_re1000"]["iter1000"]):
+        assert rel(g, w) < 1e-9
+    for g, w in zip(a["cv128_re1000"]["final_uv"], b["cv128_re1000"]["final_uv"]):
+        assert rel(g, w) < 1e-10
+
+
+@pytest.mark.parametrize("iadv", [1, 2])
+def test_cavity_cds_and_uds_histories(oracle, iadv):
+    k = kat("cavity_regen")[f"cv10_re100_iadv{iadv}"]["history"]
+    c = oracle.Cavity(10, 10, 100.0, iadv=iadv)
+    n, h = c.run(maxit=20, tol=0.0, history=True)
+    for it, row in k.items():
+        got = h[int(it) - 1]
+        for g, w in zip(got[:3], row[:3]):
+            assert rel(g, w) < 1e-11, (iadv, it)
+        for g, w in zip(got[3:], row[3:]):
+            assert rel(g, w) < 1e-12, (iadv, it)
+
+
+def test_cylinder_regenerated_table_agrees_with_the_survey_table_and_the_oracle(oracle):
+    a, b = kat("cylinder_regen"), kat("cylinder")
+    for it, (tres, tmon) in b["history"].items():
+        assert rel(a["history"][it][0], tres) < (1e-6 if int(it) in (1000, 2000) else 1e-12)     # the survey rounded these two
+        assert rel(a["history"][it][1], tmon) < 1e-13
+    assert a["final_tres"] == b["final_tres"] and a["final_t_mon"] == b["final_t_mon"]         # bitwise-stationary floor
+    for key in ("qwall_west", "sum_abs_t", "t_max", "t_min"):
+        assert rel(a[key], b[key]) < 1e-13, key
+    g = oracle.General("cylinder")
+    n, h = g.run(max_iter=2000, tol=0.0, history=True)
+    for it in ("1", "2", "10", "100", "1000", "2000"):
+        assert rel(h[int(it) - 1][3], a["history"][it][0]) < 1e-9 and rel(h[int(it) - 1][4], a["history"][it][1]) < 1e-13
+
+
+# ---- buoyancy_cav.f90: calcu / calcv / calcp / calct with the authored Boussinesq user module ---------------------------
+@pytest.mark.parametrize("case", ["n34_iadv3", "n34_iadv4", "n34_iadv1", "n34_iadv2", "n66_iadv3"])
+def test_buoyancy_histories(oracle, case):
+    c = kat("buoyancy")[case]
+    g = oracle.General("buoyancy", ni=c["ni"], nj=c["nj"], iadv=c["iadv"])
+    last = max(int(i) for i in c["history"])
+    n, h = g.run(max_iter=last, tol=0.0, history=True)
+    assert n == last
+    for it, row in c["history"].items():
+        got = h[int(it) - 1]
+        for q in range(4):
+            assert rel(got[q], row["resor"][q]) < 1e-11 or abs(got[q] - row["resor"][q]) < 1e-25, (case, it, q)
+        assert rel(got[4], row["t_mon"]) < 1e-13
+    row = c["history"][str(last)]
+    for name, want in zip(("u", "v", "p"), row["sum_abs"]):
+        assert rel(np.abs(getattr(g, name)).sum(), want) < 1e-11, (case, name)
+    assert rel(np.abs(g.t[:, 1:-1]).sum(), row["sum_abs"][3]) < 1e-12        # adiabatic rows are filled on the last pass only
+    im, jm = c["imon"], c["jmon"]
+    assert rel(g.u[im - 1, jm - 1], row["u_mon"]) < 1e-11 and rel(g.v[im - 1, jm - 1], row["v_mon"]) < 1e-11
+    assert rel(g.p[im, jm + 1], row["p_mon"]) < 1e-10
+
+
+# ---- backward step (TEACH-T), laminar ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", ["ni40_nj30", "ni34_nj26_plane"])
+def test_teach_laminar_histories(oracle, case):
+    c = kat("teach")[case]
+    t = oracle.Teach(ni=c["ni"], nj=c["nj"], jstep=c["jstep"], epsx=c["epsx"], indcos=c["indcos"])
+    assert rel(t.s.flowin, c["flowin"]) < 1e-14
+    done, im, jm = 0, c["imon"], c["jmon"]
+    for it, row in sorted(c["history"].items(), key=lambda kv: int(kv[0])):
+        res = t.iterate(int(it) - done)
+        done = int(it)
+        for g, w in zip(res, row["res"]):
+            assert rel(g, w) < 1e-10, (case, it, res, row["res"])
+        assert rel(t.u[im - 1, jm - 1], row["u_mon"]) < 1e-11
+        assert rel(t.v[im - 1, jm - 1], row["v_mon"]) < 1e-10
+        assert rel(t.p[im - 1, jm - 1], row["p_mon"]) < 1e-10
+        assert rel(t.u[c["ni"] - 1, jm - 1], row["u_out"]) < 1e-11            # outlet mass balance of modu
+        for name, want in zip(("u", "v", "p"), row["sum_abs"]):
+            assert rel(np.abs(getattr(t, name)[:c["ni"], :c["nj"]]).sum(), want) < 1e-10, (case, it, name)
+
+
+# ---- explicit FD cavity with SIP ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", ["n33", "n21x13", "n11_default"])
+def test_fd_explicit_cavity_steps(oracle, case):
+    c = kat("fdcavity")[case]
+    o = oracle.FDCavity(ni=c["ni"], nj=c["nj"], re=c["re"], dt=c["dt"])
+    for n, st in enumerate(c["steps"]):
+        err = o.step()
+        assert o.s.sip_iters == st["sip_iters"], (case, n)
+        assert rel(err, st["error"]) < 1e-11, (case, n)
+        assert rel(o.u[c["ni"] // 2 - 1, c["nj"] // 2 - 1], st["u_mon"]) < 1e-11 or abs(st["u_mon"]) < 1e-300
+    ni, nj = c["ni"], c["nj"]
+    last = c["steps"][-1]["sum_abs"]
+    assert rel(np.abs(o.u[:ni, :nj + 1]).sum(), last[0]) < 1e-11
+    assert rel(np.abs(o.v[:ni + 1, :nj]).sum(), last[1]) < 1e-11
+    assert rel(np.abs(o.p[:ni + 1, :nj + 1]).sum(), last[2]) < 1e-11
+
+
+# ---- stagnation-point scalar transport, steady ---------------------------------------------------------------------------
+def test_stagnation_point_solver_loops(oracle):
+    k = kat("stagnation")
+    n = 0
+    for key, c in k.items():
+        if key.startswith("_"):
+            continue
+        o = oracle.StagPoint(c["ncv"], c["ncv"], isch=c["isch"], isol=c["isol"])
+        assert o.solve() == c["iters"], key
+        assert rel(o.rsm, c["rsm"]) < 1e-8, key
+        assert rel(o.finish(), c["fwall"]) < 1e-12, key
+        assert rel(np.abs(o.phi).sum(), c["sum_abs_phi"]) < 1e-12, key
+        n += 1
+    assert n == 8

@@ -1,0 +1,1129 @@
+#!/usr/bin/env python
+"""Known-answer tables for the CPU oracle, from a SECOND restatement of the reference programs.
+
+The reference (brli3/CFD, Fortran 90) ships no tests or expected outputs and the build image has no Fortran compiler, so
+oracle/*.c cannot be checked against the reference's own binaries.  To take the single-author failure mode out -- one
+transcription slip shared by oracle/*.c and the CUDA kernels would pass every GPU-vs-oracle test -- this file restates the
+programs once more, written from the .f90 sources (cited per function), NOT from oracle/*.c, and in a different form:
+whole-array numpy expressions over index windows instead of cell loops, 1-based arrays padded with an unused index 0,
+and numba only for the recurrences (Thomas / SIP), written in P-Q form rather than the reference's a/c form.  It shares no
+code with oracle/ or cfd_b200/.  tests/test_oracle_*.py assert the C oracle against the tables written here.
+
+    python tools/gen_kat.py [cavity] [cylinder] [teach] [fdcavity] [stagnation] [buoyancy]     (default: all)
+
+writes tests/golden/<family>_kat.json.  Floating-point sums are accumulated in a different order than the reference's
+loops (numpy pairwise sums), so the tables pin residual sums to ~1e-12 relative, fields and iteration counts exactly to the
+extent that the iteration is insensitive to that (the counts below are reproduced by the C oracle).
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import time
+
+import numba
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def W(lo, hi, d=0):
+    """Index window lo..hi (inclusive, 1-based) shifted by d: the numpy slice that addresses a(lo+d : hi+d)."""
+    return slice(lo + d, hi + d + 1)
+
+
+# =====================================================================================================================
+# Line solver shared by the SIMPLE programs: lisolv (lid-driven-cavity-2d/fvm-simple/cavity_fvm.f90:49-82),
+# lisolv (backward-step-flow-2d/general.f90:294-327), tdma (buoyancy-driven-cavity-2d/buoyancy_cav.f90:471-505).
+# W->E over lines i = istart..ni-1; each line is the tridiagonal system
+#     ap*phi(j) = an*phi(j+1) + as*phi(j-1) + [ae*phi(i+1,j) + aw*phi(i-1,j) + su]       j = jstart..nj-1
+# with phi(jstart-1), phi(nj) given.  Thomas in P-Q form: phi(j) = P(j)*phi(j+1) + Q(j).
+# =====================================================================================================================
+@numba.njit(cache=True)
+def line_sweep(istart, jstart, ni, nj, phi, ap, an, as_, ae, aw, su):
+    P = np.zeros(nj + 2)
+    Q = np.zeros(nj + 2)
+    for i in range(istart, ni):
+        P[jstart - 1] = 0.0
+        Q[jstart - 1] = phi[i, jstart - 1]
+        for j in range(jstart, nj):
+            rhs = ae[i, j] * phi[i + 1, j] + aw[i, j] * phi[i - 1, j] + su[i, j]
+            inv = 1.0 / (ap[i, j] - as_[i, j] * P[j - 1])
+            P[j] = an[i, j] * inv
+            Q[j] = (rhs + as_[i, j] * Q[j - 1]) * inv
+        for j in range(nj - 1, jstart - 1, -1):
+            phi[i, j] = P[j] * phi[i, j + 1] + Q[j]
+
+
+# =====================================================================================================================
+# 1. lid-driven-cavity-2d/fvm-simple/cavity_fvm.f90
+# =====================================================================================================================
+class CavityRef:
+    """program cavity_fvm (:509-566) with setgrid (:366-414), calcu (:92-192), calcv (:194-291), calcp (:293-355)."""
+
+    def __init__(self, nicv, njcv, reynolds, iadv=3, urf=(0.5, 0.5, 0.8), nswp=(3, 3, 3)):
+        ni, nj = nicv + 2, njcv + 2
+        self.ni, self.nj, self.iadv, self.urf, self.nswp = ni, nj, iadv, urf, nswp
+        z1 = lambda n: np.zeros(n + 2)
+        self.x, self.xu, self.sew, self.sewu = z1(ni), z1(ni), z1(ni), z1(ni)
+        self.y, self.yv, self.sns, self.snsv = z1(nj), z1(nj), z1(nj), z1(nj)
+        # setgrid (:366-414), xstart = ystart = 0, xend = yend = 1
+        dx, dy = 1.0 / nicv, 1.0 / njcv
+        self.xu[1] = self.xu[2] = 0.0
+        for i in range(3, ni + 1):
+            self.xu[i] = self.xu[i - 1] + dx
+        self.x[1] = self.xu[2]
+        self.x[W(2, ni - 1)] = 0.5 * (self.xu[W(2, ni - 1)] + self.xu[W(2, ni - 1, 1)])
+        self.sew[W(2, ni - 1)] = self.xu[W(2, ni - 1, 1)] - self.xu[W(2, ni - 1)]
+        self.x[ni] = self.xu[ni]
+        self.sewu[W(3, ni - 1)] = self.x[W(3, ni - 1)] - self.x[W(3, ni - 1, -1)]
+        self.yv[1] = self.yv[2] = 0.0
+        for j in range(3, nj + 1):
+            self.yv[j] = self.yv[j - 1] + dy
+        self.y[1] = self.yv[2]
+        self.y[W(2, nj - 1)] = 0.5 * (self.yv[W(2, nj - 1)] + self.yv[W(2, nj - 1, 1)])
+        self.sns[W(2, nj - 1)] = self.yv[W(2, nj - 1, 1)] - self.yv[W(2, nj - 1)]
+        self.y[nj] = self.yv[nj]
+        self.snsv[W(3, nj - 1)] = self.y[W(3, nj - 1)] - self.y[W(3, nj - 1, -1)]
+        z2 = lambda: np.zeros((ni + 2, nj + 2))
+        for n in ("u", "v", "p", "pp", "du", "dv", "ae", "aw", "an", "as_", "ap", "su"):
+            setattr(self, n, z2())
+        self.den = np.full((ni + 2, nj + 2), 1000.0)                       # :536
+        self.vis = self.den * 1.0 * 1.0 / reynolds                         # :537
+        self.u[2:ni + 1, nj] = 1.0                                         # :538  u(2:,nj) = utop
+        self.ipref, self.jpref = ni // 2, nj // 2                          # :549-552
+        self.imon, self.jmon = self.ipref, self.jpref
+        self.res = [0.0, 0.0, 0.0]
+
+    def _scheme(self, c_e, c_w, c_n, c_s, d_e, d_w, d_n, d_s):
+        if self.iadv == 1:                                                 # :141-145
+            return d_e - 0.5 * c_e, d_w + 0.5 * c_w, d_n - 0.5 * c_n, d_s + 0.5 * c_s
+        if self.iadv == 2:                                                 # :146-150
+            return (d_e + np.maximum(0.0, -c_e), d_w + np.maximum(0.0, c_w),
+                    d_n + np.maximum(0.0, -c_n), d_s + np.maximum(0.0, c_s))
+        return (np.maximum(np.abs(0.5 * c_e), d_e) - 0.5 * c_e, np.maximum(np.abs(0.5 * c_w), d_w) + 0.5 * c_w,
+                np.maximum(np.abs(0.5 * c_n), d_n) - 0.5 * c_n, np.maximum(np.abs(0.5 * c_s), d_s) + 0.5 * c_s)
+
+    def calcu(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, vis = self.u, self.v, self.p, self.den, self.vis
+        I = lambda d=0: W(3, nim1, d)
+        J = lambda d=0: W(2, njm1, d)
+        col = lambda a, d=0: a[I(d)][:, None]            # by-i geometry as a column
+        row = lambda a, d=0: a[J(d)][None, :]            # by-j geometry as a row
+        a_ns, a_ew = col(self.sewu), row(self.sns)       # arean = areas = sewu(i); areae = areaw = sns(j)   (:106-110)
+        vol = a_ns * a_ew
+        g_ee = 0.5 * (den[I(), J()] + den[I(1), J()]) * u[I(1), J()]                      # :112-118
+        g_ww = 0.5 * (den[I(-2), J()] + den[I(-1), J()]) * u[I(-1), J()]
+        g_ne = 0.5 * (den[I(), J()] + den[I(), J(1)]) * v[I(), J(1)]
+        g_nw = 0.5 * (den[I(-1), J()] + den[I(-1), J(1)]) * v[I(-1), J(1)]
+        g_se = 0.5 * (den[I(), J(-1)] + den[I(), J()]) * v[I(), J()]
+        g_sw = 0.5 * (den[I(-1), J(-1)] + den[I(-1), J()]) * v[I(-1), J()]
+        g_p = 0.5 * (den[I(-1), J()] + den[I(), J()]) * u[I(), J()]
+        c_e, c_w = 0.5 * (g_p + g_ee) * a_ew, 0.5 * (g_ww + g_p) * a_ew                   # :120-128
+        c_n, c_s = 0.5 * (g_nw + g_ne) * a_ns, 0.5 * (g_sw + g_se) * a_ns
+        smp = c_e - c_w + c_n - c_s
+        cp = np.maximum(smp, 0.0)
+        v_e, v_w = vis[I(), J()], vis[I(-1), J()]                                         # :131-135
+        v_n = 0.25 * (vis[I(-1), J()] + vis[I(-1), J(1)] + vis[I(), J(1)] + vis[I(), J()])
+        v_s = 0.25 * (vis[I(-1), J(-1)] + vis[I(-1), J()] + vis[I(), J()] + vis[I(), J(-1)])
+        d_e = v_e * a_ew / (col(self.xu, 1) - col(self.xu))                               # :137-140
+        d_w = v_w * a_ew / (col(self.xu) - col(self.xu, -1))
+        d_n = v_n * a_ns / (row(self.y, 1) - row(self.y))
+        d_s = v_s * a_ns / (row(self.y) - row(self.y, -1))
+        ae, aw, an, as_ = self._scheme(c_e, c_w, c_n, c_s, d_e, d_w, d_n, d_s)
+        su = (p[I(-1), J()] - p[I(), J()]) * 0.5 * (a_ew + a_ew)                          # :158
+        dudxe = (u[I(1), J()] - u[I(), J()]) / col(self.sew)                              # :160-163
+        dudxw = (u[I(), J()] - u[I(-1), J()]) / col(self.sew, -1)
+        dvdxn = (v[I(), J(1)] - v[I(-1), J(1)]) / a_ns
+        dvdxs = (v[I(), J()] - v[I(-1), J()]) / a_ns
+        su = su + ((v_e * dudxe - v_w * dudxw) / a_ns + (v_n * dvdxn - v_s * dvdxs) / a_ew) * vol
+        su = su + cp * u[I(), J()]
+        sp = -cp
+        # second loop (:174-187); du uses the scalars areae, areaw LEFT OVER from the first loop's last cell: sns(njm1)
+        ap = ae + aw + an + as_ - sp
+        r = ap * u[I(), J()] - ae * u[I(1), J()] - aw * u[I(-1), J()] - an * u[I(), J(1)] - as_ * u[I(), J(-1)] - su
+        self.res[0] = float(np.abs(r).sum())
+        ap = ap / self.urf[0]
+        su = su + (1 - self.urf[0]) * ap * u[I(), J()]
+        stale = self.sns[njm1]
+        self.du[I(), J()] = 0.5 * (stale + stale) / ap
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("ap", ap), ("su", su)):
+            getattr(self, name)[I(), J()] = val
+        for _ in range(self.nswp[0]):
+            line_sweep(3, 2, ni, nj, u, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    def calcv(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, vis = self.u, self.v, self.p, self.den, self.vis
+        I = lambda d=0: W(2, nim1, d)
+        J = lambda d=0: W(3, njm1, d)
+        col = lambda a, d=0: a[I(d)][:, None]
+        row = lambda a, d=0: a[J(d)][None, :]
+        a_ew, a_ns = row(self.snsv), col(self.sew)       # areae = areaw = snsv(j); arean = areas = sew(i)   (:207-211)
+        vol = a_ns * a_ew
+        g_ne = 0.5 * (den[I(), J()] + den[I(1), J()]) * u[I(1), J()]                      # :213-219
+        g_nw = 0.5 * (den[I(-1), J()] + den[I(), J()]) * u[I(), J()]
+        g_nn = 0.5 * (den[I(), J()] + den[I(), J(1)]) * v[I(), J(1)]
+        g_se = 0.5 * (den[I(), J(-1)] + den[I(1), J(-1)]) * u[I(1), J(-1)]
+        g_sw = 0.5 * (den[I(-1), J(-1)] + den[I(), J(-1)]) * u[I(), J(-1)]
+        g_ss = 0.5 * (den[I(), J(-2)] + den[I(), J(-1)]) * v[I(), J(-1)]
+        g_p = 0.5 * (den[I(), J(-1)] + den[I(), J()]) * v[I(), J()]
+        c_e, c_w = 0.5 * (g_ne + g_se) * a_ew, 0.5 * (g_nw + g_sw) * a_ew                 # :221-229
+        c_n, c_s = 0.5 * (g_p + g_nn) * a_ns, 0.5 * (g_ss + g_p) * a_ns
+        smp = c_e - c_w + c_n - c_s
+        cp = np.maximum(smp, 0.0)
+        v_e = 0.25 * (vis[I(), J(-1)] + vis[I(), J()] + vis[I(1), J()] + vis[I(1), J(-1)])   # :233-236
+        v_w = 0.25 * (vis[I(-1), J(-1)] + vis[I(-1), J()] + vis[I(), J()] + vis[I(), J(-1)])
+        v_n, v_s = vis[I(), J()], vis[I(), J(-1)]
+        d_e = v_e * a_ew / (col(self.x, 1) - col(self.x))                                 # :238-241
+        d_w = v_w * a_ew / (col(self.x) - col(self.x, -1))
+        d_n = v_n * a_ns / (row(self.yv, 1) - row(self.yv))
+        d_s = v_s * a_ns / (row(self.yv) - row(self.yv, -1))
+        ae, aw, an, as_ = self._scheme(c_e, c_w, c_n, c_s, d_e, d_w, d_n, d_s)
+        su = (p[I(), J(-1)] - p[I(), J()]) * 0.5 * (a_ns + a_ns)                          # :258
+        dudye = (u[I(1), J()] - u[I(1), J(-1)]) / a_ew                                    # :259-262
+        dudyw = (u[I(), J()] - u[I(), J(-1)]) / a_ew
+        dvdyn = (v[I(), J(1)] - v[I(), J()]) / row(self.sns)
+        dvdys = (v[I(), J()] - v[I(), J(-1)]) / row(self.sns, -1)
+        su = su + (v_e * dudye - v_w * dudyw) / a_ns * vol + (v_n * dvdyn - v_s * dvdys) / a_ew * vol   # :263-264
+        sp = -cp
+        su = su + cp * v[I(), J()]
+        ap = ae + aw + an + as_ - sp                                                      # :272-283
+        r = ap * v[I(), J()] - ae * v[I(1), J()] - aw * v[I(-1), J()] - an * v[I(), J(1)] - as_ * v[I(), J(-1)] - su
+        self.res[1] = float(np.abs(r).sum())
+        ap = ap / self.urf[1]
+        su = su + (1.0 - self.urf[1]) * ap * v[I(), J()]
+        stale = self.sew[nim1]                            # arean, areas left over from the first loop's last cell
+        self.dv[I(), J()] = 0.5 * (stale + stale) / ap
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("ap", ap), ("su", su)):
+            getattr(self, name)[I(), J()] = val
+        for _ in range(self.nswp[1]):
+            line_sweep(2, 3, ni, nj, v, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    def calcp(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, du, dv, pp = self.u, self.v, self.p, self.den, self.du, self.dv, self.pp
+        I = lambda d=0: W(2, nim1, d)
+        J = lambda d=0: W(2, njm1, d)
+        a_ew, a_ns = self.sns[J()][None, :], self.sew[I()][:, None]                        # :304-307
+        d_e = 0.5 * (den[I(), J()] + den[I(1), J()])                                       # :309-312
+        d_w = 0.5 * (den[I(-1), J()] + den[I(), J()])
+        d_n = 0.5 * (den[I(), J()] + den[I(), J(1)])
+        d_s = 0.5 * (den[I(), J(-1)] + den[I(), J()])
+        ae, aw = d_e * a_ew * du[I(1), J()], d_w * a_ew * du[I(), J()]                    # :313-316
+        an, as_ = d_n * a_ns * dv[I(), J(1)], d_s * a_ns * dv[I(), J()]
+        smp = (d_e * u[I(1), J()]) * a_ew - (d_w * u[I(), J()]) * a_ew + (d_n * v[I(), J(1)]) * a_ns \
+            - (d_s * v[I(), J()]) * a_ns                                                   # :317-325
+        self.res[2] = float(np.abs(smp).sum())
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("ap", ae + aw + an + as_ - 0.0), ("su", -smp)):
+            getattr(self, name)[I(), J()] = val
+        pp[:, :] = 0.0                                                                     # :342
+        for _ in range(self.nswp[2]):
+            line_sweep(2, 2, ni, nj, pp, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+        ppref = pp[self.ipref, self.jpref]                                                 # :346-354
+        p[I(), J()] += self.urf[2] * (pp[I(), J()] - ppref)
+        Iu = W(3, nim1)
+        u[Iu, J()] += du[Iu, J()] * (pp[W(3, nim1, -1), J()] - pp[Iu, J()])
+        Jv = W(3, njm1)
+        v[I(), Jv] += dv[I(), Jv] * (pp[I(), W(3, njm1, -1)] - pp[I(), Jv])
+
+    def run(self, maxit=90000, tol=1.0e-10, record=()):
+        hist = {}
+        for it in range(1, maxit + 1):
+            self.calcu()
+            self.calcv()
+            self.calcp()
+            if it in record:
+                hist[it] = {"res": list(self.res), "u_mon": float(self.u[self.imon, self.jmon]),
+                            "v_mon": float(self.v[self.imon, self.jmon])}
+            if max(self.res) < tol:                                                        # :565
+                break
+        return it, hist
+
+    def uc_mon(self):
+        return float(0.5 * (self.u[self.imon, self.jmon] + self.u[self.imon + 1, self.jmon]))   # centred_vel :428
+
+    def sums(self):
+        ni, nj = self.ni, self.nj
+        return [float(np.abs(a[1:ni + 1, 1:nj + 1]).sum()) for a in (self.u, self.v, self.p)]
+
+
+def gen_cavity():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of lid-driven-cavity-2d/fvm-simple/cavity_fvm.f90, "
+                      "independent of oracle/cavity_oracle.c); hybrid scheme, rho 1000, utop 1, urf .5/.5/.8, nswp 3/3/3, "
+                      "stop rule max(res) < 1e-10 (cavity_fvm.f90:565)",
+           "case": "SURVEY.md section 8c table"}
+    c = CavityRef(10, 10, 100.0)
+    n, hist = c.run(record=(1, 2, 3, 10, 100))
+    out["cv10_re100"] = {"iters": n, "imon": c.imon, "jmon": c.jmon,
+                         "history": {str(k): [*v["res"], v["u_mon"], v["v_mon"]] for k, v in hist.items()},
+                         "final_res": list(c.res), "final_uv": [float(c.u[c.imon, c.jmon]), float(c.v[c.imon, c.jmon])],
+                         "uc_mon": c.uc_mon(), "sum_abs": c.sums()}
+    for iadv in (1, 2):
+        c = CavityRef(10, 10, 100.0, iadv=iadv)
+        n, hist = c.run(maxit=20, tol=0.0, record=(1, 20))
+        out[f"cv10_re100_iadv{iadv}"] = {"history": {str(k): [*v["res"], v["u_mon"], v["v_mon"]] for k, v in hist.items()}}
+    c = CavityRef(32, 32, 100.0)
+    n, _ = c.run()
+    uc = 0.5 * (c.u[c.imon, 1:c.nj + 1] + c.u[c.imon + 1, 1:c.nj + 1])
+    out["cv32_re100"] = {"iters": n, "min_centreline_uc": float(uc.min()), "sum_abs": c.sums()}
+    c = CavityRef(64, 64, 100.0)
+    n, _ = c.run()
+    out["cv64_re100"] = {"iters": n, "imon": c.imon, "jmon": c.jmon, "final_res": list(c.res),
+                         "final_uv": [float(c.u[c.imon, c.jmon]), float(c.v[c.imon, c.jmon])], "uc_mon": c.uc_mon()}
+    c = CavityRef(128, 128, 1000.0)
+    n, hist = c.run(record=(1000,))
+    out["cv128_re1000"] = {"iters": n, "imon": c.imon, "jmon": c.jmon, "iter1000": hist[1000]["res"],
+                           "final_uv": [float(c.u[c.imon, c.jmon]), float(c.v[c.imon, c.jmon])], "uc_mon": c.uc_mon()}
+    return out
+
+
+
+# =====================================================================================================================
+# 2. the `vars` programs: cylinder-heat-conduction-2d/cylin_cond.f90 (complete, as shipped) and
+#    buoyancy-driven-cavity-2d/buoyancy_cav.f90 (grid, calcu, calcv, calcp, calct, tdma; its `user` module is missing
+#    from the reference -- the Boussinesq set-up below repeats the choices documented in DESIGN.md / SURVEY 8a).
+#    Face-based: every equation is assembled from whole arrays of east-face and north-face (flow, diff) pairs, the
+#    reference's scatter  aw(i+1,j) = acof + max(0,flow); ae(i,j) = aw(i+1,j) - flow  becoming array shifts.
+# =====================================================================================================================
+def dapec(flow, diff, iadv):
+    """DAPEC (cylin_cond.f90:245-269), elementwise."""
+    af = np.abs(flow)
+    if iadv == 1:
+        a = diff - 0.5 * af
+    elif iadv == 3:
+        a = np.maximum(0.0, diff - 0.5 * af)
+    elif iadv == 4:
+        with np.errstate(divide="ignore", invalid="ignore"):
+            a = np.maximum(0.0, (1.0 - 0.1 * np.abs(flow / diff)) ** 5) * diff
+    else:
+        a = diff + 0.0 * af
+    return np.where(flow == 0.0, diff, a)
+
+
+def arimean(a, b, w):           # cylin_cond.f90:271-277
+    return a * (1 - w) + b * w
+
+
+def harmean(a, b, w):           # cylin_cond.f90:279-285 (0/0 where both conductivities are zero: never used there)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        return a * b / (a * (1.0 - w) + b * w)
+
+
+class GeneralRef:
+    def __init__(self, ni, nj, icrd, iadv, lim, urf, nsweep):
+        self.ni, self.nj, self.icrd, self.iadv, self.urf, self.nsweep = ni, nj, icrd, iadv, urf, nsweep
+        xstart, xend, ystart, yend, rstart = lim
+        nim1, nim2, njm1, njm2 = ni - 1, ni - 2, nj - 1, nj - 2
+        zi, zj = (lambda: np.zeros(ni + 2)), (lambda: np.zeros(nj + 2))
+        x, xu, xdif, sew, sewu, xcvi, xcvip, fx, fxm = (zi() for _ in range(9))
+        (y, yv, ydif, sns, snsv, ycvr, ycvrs, arx, arxj, arxjp, r, rmn, sx, sxmn, fv, fvp, fy, fym) = (zj() for _ in range(18))
+        # grid (buoyancy_cav.f90:28-120)
+        dx = (xend - xstart) / (ni - 2)
+        xu[2] = xstart
+        for i in range(3, ni + 1):
+            xu[i] = xu[i - 1] + dx
+        sew[W(2, nim1)] = xu[W(3, ni)] - xu[W(2, nim1)]
+        x[1] = xu[2]
+        x[W(2, nim1)] = 0.5 * (xu[W(2, nim1)] + xu[W(3, ni)])
+        x[ni] = xu[ni]
+        xdif[W(2, ni)] = x[W(2, ni)] - x[W(1, nim1)]
+        sewu[W(3, nim1)] = xdif[W(3, nim1)]
+        sewu[3] += xdif[2]
+        sewu[nim1] += xdif[ni]
+        xcvi[W(3, nim2)] = 0.5 * sew[W(3, nim2)]
+        xcvip[W(3, nim2)] = xcvi[W(3, nim2)]
+        xcvip[2] = sew[2]
+        xcvi[nim1] = sew[nim1]
+        dy = (yend - ystart) / (nj - 2)
+        yv[2] = ystart
+        for j in range(3, nj + 1):
+            yv[j] = yv[j - 1] + dy
+        sns[W(2, njm1)] = yv[W(3, nj)] - yv[W(2, njm1)]
+        y[1] = yv[2]
+        y[W(2, njm1)] = 0.5 * (yv[W(2, njm1)] + yv[W(3, nj)])
+        y[nj] = yv[nj]
+        ydif[W(2, nj)] = y[W(2, nj)] - y[W(1, njm1)]
+        snsv[W(3, njm1)] = ydif[W(3, njm1)]
+        snsv[3] += ydif[2]
+        snsv[njm1] += ydif[nj]
+        r[1] = rstart
+        if icrd == 1:
+            rmn[1:nj + 1] = 1.0
+            r[1:nj + 1] = 1.0
+        else:
+            for j in range(2, nj + 1):
+                r[j] = r[j - 1] + ydif[j]
+            rmn[2] = r[1]
+            for j in range(3, nj + 1):
+                rmn[j] = rmn[j - 1] + sns[j - 1]
+        sx[1:nj + 1] = 1.0
+        sxmn[1:nj + 1] = 1.0
+        if icrd == 3:
+            sx[1:nj + 1] = r[1:nj + 1]
+            sxmn[2:nj + 1] = rmn[2:nj + 1]
+        ycvr[W(2, njm1)] = r[W(2, njm1)] * sns[W(2, njm1)]
+        arx[W(2, njm1)] = ycvr[W(2, njm1)]
+        if icrd == 3:
+            arx[1:nj + 1] = sns[1:nj + 1]
+        ycvrs[W(4, njm2)] = 0.5 * (r[W(4, njm2)] + r[W(3, njm2 - 1)]) * ydif[W(4, njm2)]
+        ycvrs[3] = 0.5 * (r[3] + r[1]) * snsv[3]
+        ycvrs[njm1] = 0.5 * (r[nj] + r[njm2]) * snsv[njm1]
+        if icrd == 2:
+            arxj[W(3, njm2)] = 0.25 * (1.0 + rmn[W(3, njm2)] / r[W(3, njm2)]) * arx[W(3, njm2)]
+            arxjp[W(3, njm2)] = arx[W(3, njm2)] - arxj[W(3, njm2)]
+        else:
+            arxj[W(3, njm2)] = 0.5 * arx[W(3, njm2)]
+            arxjp[W(3, njm2)] = arxj[W(3, njm2)]
+        arxjp[2] = arx[2]
+        arxj[njm1] = arx[njm1]
+        fv[W(3, njm2)] = arxjp[W(3, njm2)] / arx[W(3, njm2)]
+        fvp[W(3, njm2)] = 1.0 - fv[W(3, njm2)]
+        fx[W(2, ni)] = 0.5 * sew[W(1, nim1)] / xdif[W(2, ni)]
+        fxm[W(2, ni)] = 1.0 - fx[W(2, ni)]
+        fy[W(2, nj)] = 0.5 * sns[W(1, njm1)] / ydif[W(2, nj)]
+        fym[W(2, nj)] = 1.0 - fy[W(2, nj)]
+        for k, v in dict(x=x, xu=xu, xdif=xdif, sew=sew, sewu=sewu, xcvi=xcvi, xcvip=xcvip, fx=fx, y=y, yv=yv, ydif=ydif,
+                         sns=sns, snsv=snsv, ycvr=ycvr, ycvrs=ycvrs, arx=arx, arxj=arxj, arxjp=arxjp, r=r, rmn=rmn, sx=sx,
+                         sxmn=sxmn, fv=fv, fvp=fvp, fy=fy).items():
+            setattr(self, k, v)
+        z2 = lambda: np.zeros((ni + 2, nj + 2))
+        for n in ("u", "v", "p", "pp", "du", "dv", "t", "ae", "aw", "an", "as_", "ap", "su"):
+            setattr(self, n, z2())
+        self.den = np.ones((ni + 2, nj + 2))            # den_ini = cp_ini = 1 (cylin_cond.f90:118-119 in grid())
+        self.cp = np.ones((ni + 2, nj + 2))
+        self.resor = [0.0, 0.0, 0.0, 0.0]
+        self.ipref = self.jpref = 1
+
+    def _store(self, I, J, ae, aw, an, as_, ap, su):
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("ap", ap), ("su", su)):
+            getattr(self, name)[I, J] = val
+
+    # ---- calct (buoyancy_cav.f90:358-433) ---------------------------------------------------------------------------
+    def calct(self, gam, su_vol, sp_vol):
+        ni, nj, nim1, njm1, iadv = self.ni, self.nj, self.ni - 1, self.nj - 1, self.iadv
+        u, v, t = self.u, self.v, self.t
+        den = self.den * self.cp                                            # :372
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        arx_, sx_ = row(self.arx), row(self.sx)
+        # east faces of cells i = 2..nim1 (the last one is the boundary face, :388-391 with den(nj,j) as written)
+        fe = arimean(den[I(), J()], den[I(1), J()], col(self.fx, 1)) * u[I(1), J()] * arx_
+        de = harmean(gam[I(), J()], gam[I(1), J()], col(self.fx, 1)) * arx_ / (col(self.xdif, 1) * sx_)
+        fe[-1, :] = den[nj, J()] * u[ni, J()] * self.arx[J()]
+        de[-1, :] = gam[ni, J()] * self.arx[J()] / (self.xdif[ni] * self.sx[J()])
+        aw_next = dapec(fe, de, iadv) + np.maximum(0.0, fe)                 # aw(i+1,j)
+        ae = aw_next - fe
+        fw0 = den[1, J()] * u[2, J()] * self.arx[J()]                       # west boundary face (:381-385)
+        dw0 = gam[1, J()] * self.arx[J()] / (self.xdif[2] * self.sx[J()])
+        aw = np.vstack([(dapec(fw0, dw0, iadv) + np.maximum(0.0, fw0))[None, :], aw_next[:-1, :]])
+        # north faces of cells j = 2..njm1 (:400-412)
+        a_n = row(self.rmn, 1) * col(self.sew)
+        fn = arimean(den[I(), J()], den[I(), J(1)], row(self.fy, 1)) * v[I(), J(1)] * a_n
+        dn = harmean(gam[I(), J()], gam[I(), J(1)], row(self.fy, 1)) * a_n / row(self.ydif, 1)
+        fn[:, -1] = den[I(), nj] * v[I(), nj] * a_n[:, -1]
+        dn[:, -1] = gam[I(), nj] * a_n[:, -1] / self.ydif[nj]
+        as_next = dapec(fn, dn, iadv) + np.maximum(0.0, fn)
+        an = as_next - fn
+        a_s = self.r[1] * self.sew[I()]                                     # south boundary face (:373-379)
+        fs0 = den[I(), 1] * v[I(), 2] * a_s
+        ds0 = gam[I(), 1] * a_s / self.ydif[2]
+        as_ = np.hstack([(dapec(fs0, ds0, iadv) + np.maximum(0.0, fs0))[:, None], as_next[:, :-1]])
+        vol = row(self.ycvr) * col(self.sew)
+        sp, su = sp_vol[I(), J()] * vol, su_vol[I(), J()] * vol
+        ap = ae + aw + an + as_ - sp
+        rq = ap * t[I(), J()] - ae * t[I(1), J()] - aw * t[I(-1), J()] - an * t[I(), J(1)] - as_ * t[I(), J(-1)] - su
+        self.resor[3] = float(np.abs(rq).sum())
+        ap = ap / self.urf[3]
+        su = su + (1.0 - self.urf[3]) * ap * t[I(), J()]
+        self._store(I(), J(), ae, aw, an, as_, ap, su)
+        for _ in range(self.nsweep[3]):
+            line_sweep(2, 2, ni, nj, t, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    # ---- calcu (buoyancy_cav.f90:122-198); the i loops run to njm1 as written (ni == nj required) ---------------------
+    def calcu(self, gam):
+        ni, nj, nim1, njm1, iadv = self.ni, self.nj, self.ni - 1, self.nj - 1, self.iadv
+        u, v, p, den = self.u, self.v, self.p, self.den
+        I, J = (lambda d=0: W(3, njm1, d)), (lambda d=0: W(2, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        arx_, sx_ = row(self.arx), row(self.sx)
+        fl = u[I(), J()] * arimean(den[I(-1), J()], den[I(), J()], col(self.fx))            # :151-158
+        flp = u[I(1), J()] * arimean(den[I(), J()], den[I(1), J()], col(self.fx, 1))
+        fe = arx_ * 0.5 * (fl + flp)
+        de = arx_ * gam[I(), J()] / (col(self.sew) * sx_)
+        fe[-1, :] = self.arx[J()] * u[ni, J()] * den[ni, J()]
+        de[-1, :] = self.arx[J()] * gam[ni, J()] / (self.sew[nim1] * self.sx[J()])
+        aw_next = dapec(fe, de, iadv) + np.maximum(0.0, fe)
+        ae = aw_next - fe
+        fw0 = self.arx[J()] * u[2, J()] * den[1, J()]                                        # :146-149
+        dw0 = self.arx[J()] * gam[1, J()] / (self.sew[2] * self.sx[J()])
+        aw = np.vstack([(dapec(fw0, dw0, iadv) + np.maximum(0.0, fw0))[None, :], aw_next[:-1, :]])
+        xc, xcm = col(self.xcvi), col(self.xcvip, -1)
+        fn = row(self.rmn, 1) * (xc * v[I(), J(1)] * arimean(den[I(), J()], den[I(), J(1)], row(self.fy, 1))
+                                 + xcm * v[I(-1), J(1)] * arimean(den[I(-1), J()], den[I(-1), J(1)], row(self.fy, 1)))
+        dn = row(self.rmn, 1) * (harmean(gam[I(), J()], gam[I(), J(1)], row(self.fy, 1)) * xc
+                                 + harmean(gam[I(-1), J()], gam[I(-1), J(1)], row(self.fy, 1)) * xcm) / row(self.ydif, 1)
+        fn[:, -1] = self.rmn[nj] * (xc[:, 0] * v[I(), nj] * den[I(), nj] + xcm[:, 0] * v[I(-1), nj] * den[I(-1), nj])   # :163-166
+        dn[:, -1] = self.r[nj] * (xc[:, 0] * gam[I(), nj] + xcm[:, 0] * gam[I(-1), nj]) / self.ydif[nj]
+        as_next = dapec(fn, dn, iadv) + np.maximum(0.0, fn)
+        an = as_next - fn
+        fs0 = self.r[1] * (xc[:, 0] * v[I(), 2] * den[I(), 1] + xcm[:, 0] * v[I(-1), 2] * den[I(-1), 1])     # :135-142
+        ds0 = self.r[1] * (xc[:, 0] * gam[I(), 1] + xcm[:, 0] * gam[I(-1), 1]) / self.ydif[2]
+        as_ = np.hstack([(dapec(fs0, ds0, iadv) + np.maximum(0.0, fs0))[:, None], as_next[:, :-1]])
+        vol = row(self.ycvr) * col(self.sewu)
+        du = vol / (col(self.xdif) * sx_)
+        su = 0.0 * vol + du * (p[I(-1), J()] - p[I(), J()])                                   # no u sources in either user module
+        ap = ae + aw + an + as_
+        rq = ap * u[I(), J()] - ae * u[I(1), J()] - aw * u[I(-1), J()] - an * u[I(), J(1)] - as_ * u[I(), J(-1)] - su
+        self.resor[0] = float(np.abs(rq).sum())
+        ap = ap / self.urf[0]
+        su = su + (1 - self.urf[0]) * ap * u[I(), J()]
+        self.du[I(), J()] = du / ap
+        self._store(I(), J(), ae, aw, an, as_, ap, su)
+        for _ in range(self.nsweep[0]):
+            line_sweep(3, 2, ni, nj, u, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    # ---- calcv (buoyancy_cav.f90:200-277) -------------------------------------------------------------------------------
+    def calcv(self, gam, su_vol):
+        ni, nj, nim1, njm1, iadv = self.ni, self.nj, self.ni - 1, self.nj - 1, self.iadv
+        u, v, p, den = self.u, self.v, self.p, self.den
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(3, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        aj, ajm = row(self.arxj), row(self.arxjp, -1)
+        fe = aj * u[I(1), J()] * arimean(den[I(), J()], den[I(1), J()], col(self.fx, 1)) \
+            + ajm * u[I(1), J(-1)] * arimean(den[I(), J(-1)], den[I(1), J(-1)], col(self.fx, 1))      # :235-239
+        de = (harmean(gam[I(), J()], gam[I(1), J()], col(self.fx, 1)) * aj
+              + harmean(gam[I(), J(-1)], gam[I(1), J(-1)], col(self.fx, 1)) * ajm) / (col(self.xdif, 1) * row(self.sxmn))
+        fe[-1, :] = aj[0] * u[ni, J()] * den[ni, J()] + ajm[0] * u[ni, J(-1)] * den[ni, J(-1)]        # :231-233
+        de[-1, :] = (aj[0] * gam[ni, J()] + ajm[0] * gam[ni, J(-1)]) / (self.xdif[ni] * self.sxmn[J()])
+        aw_next = dapec(fe, de, iadv) + np.maximum(0.0, fe)
+        ae = aw_next - fe
+        fw0 = aj[0] * u[2, J()] * den[1, J()] + ajm[0] * u[2, J(-1)] * den[1, J(-1)]                  # :223-228
+        dw0 = (aj[0] * gam[1, J()] + ajm[0] * gam[1, J(-1)]) / (self.xdif[2] * self.sxmn[J()])
+        aw = np.vstack([(dapec(fw0, dw0, iadv) + np.maximum(0.0, fw0))[None, :], aw_next[:-1, :]])
+        sew_ = col(self.sew)
+        fl = v[I(), J()] * row(self.rmn) * sew_ * arimean(den[I(), J(-1)], den[I(), J()], row(self.fy))   # :250-254
+        flp = v[I(), J(1)] * row(self.rmn, 1) * sew_ * arimean(den[I(), J()], den[I(), J(1)], row(self.fy, 1))
+        fn = arimean(fl, flp, row(self.fvp))
+        dn = (row(self.r) * sew_) * gam[I(), J()] / row(self.sns)
+        a_top = self.r[nj] * self.sew[I()]                                                           # :245-248
+        fn[:, -1] = a_top * v[I(), nj] * den[I(), nj]
+        dn[:, -1] = a_top * gam[I(), nj] / self.sns[njm1]
+        as_next = dapec(fn, dn, iadv) + np.maximum(0.0, fn)
+        an = as_next - fn
+        a_bot = self.r[1] * self.sew[I()]                                                            # :212-219, `* sns(2)` as written
+        fs0 = a_bot * v[I(), 2] * den[I(), 1]
+        ds0 = a_bot * gam[I(), 1] * self.sns[2]
+        as_ = np.hstack([(dapec(fs0, ds0, iadv) + np.maximum(0.0, fs0))[:, None], as_next[:, :-1]])
+        vol = row(self.ycvrs) * sew_
+        su = su_vol[I(), J()] * vol
+        dv = vol / row(self.ydif)
+        su = su + dv * (p[I(), J(-1)] - p[I(), J()])
+        ap = ae + aw + an + as_
+        rq = ap * v[I(), J()] - ae * v[I(1), J()] - aw * v[I(-1), J()] - an * v[I(), J(1)] - as_ * v[I(), J(-1)] - su
+        self.resor[1] = float(np.abs(rq).sum())
+        ap = ap / self.urf[1]
+        su = su + (1.0 - self.urf[1]) * ap * v[I(), J()]
+        self.dv[I(), J()] = dv / ap
+        self._store(I(), J(), ae, aw, an, as_, ap, su)
+        for _ in range(self.nsweep[1]):
+            line_sweep(2, 3, ni, nj, v, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    # ---- calcp (buoyancy_cav.f90:279-356) -------------------------------------------------------------------------------
+    def calcp(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, du, dv, pp = self.u, self.v, self.p, self.den, self.du, self.dv, self.pp
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        arx_ = row(self.arx)
+        ce = den[I(1), J()] * u[I(1), J()] * arx_                           # east mass flow; den(i+1,j) as written (:319)
+        ae = arimean(den[I(), J()], den[I(1), J()], col(self.fx, 1)) * arx_ * du[I(1), J()]
+        ae[-1, :] = 0.0                                                     # :313-316
+        cw = np.vstack([(den[1, J()] * u[2, J()] * self.arx[J()])[None, :], ce[:-1, :]])        # :308-311 and the scatter :322
+        aw = np.vstack([np.zeros((1, njm1 - 1)), ae[:-1, :]])
+        a_n = row(self.rmn, 1) * col(self.sew)
+        dnn = arimean(den[I(), J()], den[I(), J(1)], row(self.fy, 1))
+        cn = dnn * v[I(), J(1)] * a_n
+        an = dnn * a_n * dv[I(), J(1)]
+        cn[:, -1] = den[I(), nj] * v[I(), nj] * a_n[:, -1]                  # :326-329
+        an[:, -1] = 0.0
+        cs = np.hstack([(den[I(), 1] * v[I(), 2] * (self.rmn[2] * self.sew[I()]))[:, None], cn[:, :-1]])   # :300-305, :335
+        as_ = np.hstack([np.zeros((nim1 - 1, 1)), an[:, :-1]])
+        su = ((0.0 + cs) + cw) - ce - cn
+        self.resor[2] = float(np.abs(su).sum())
+        self._store(I(), J(), ae, aw, an, as_, ae + aw + an + as_, su)
+        pp[I(), J()] = 0.0
+        for _ in range(self.nsweep[2]):
+            line_sweep(2, 2, ni, nj, pp, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+        ppref = pp[self.ipref, self.jpref]
+        p[I(), J()] += self.urf[2] * (pp[I(), J()] - ppref)
+        Iu, Jv = W(3, nim1), W(3, njm1)
+        u[Iu, J()] += du[Iu, J()] * (pp[W(3, nim1, -1), J()] - pp[Iu, J()])
+        v[I(), Jv] += dv[I(), Jv] * (pp[I(), W(3, njm1, -1)] - pp[I(), Jv])
+
+
+def gen_cylinder():
+    """cylin_cond.f90 exactly as shipped: control (:83-115), initial (:117-134), gamsor (:149-169), boundary (:140-147),
+    program main (:289-312), wall flux of output (:187-190)."""
+    ni = nj = 52
+    g = GeneralRef(ni, nj, 2, 1, (0.0, 2.0, 0.0, 1.0, 1.0), (0.3, 0.3, 0.9, 1.0), (3, 3, 3, 3))
+    nim1, njm1 = ni - 1, nj - 1
+    is1, is2, js2 = ni // 2 - 10, ni // 2 + 10, nj
+    js1 = js2 - 20
+    gam0, gam1, qin, htc, t0, tf = 3.0, 1.0, 50.0, 50.0, 20.0, 10.0
+    g.t[2:ni + 1, 1:nj + 1] = t0
+    g.t[1, 1:nj + 1] = t0 * (1.0 + g.y[1:nj + 1])
+    gam = np.full((ni + 2, nj + 2), gam0)
+    su, sp = np.zeros((ni + 2, nj + 2)), np.zeros((ni + 2, nj + 2))
+    gam[is1:is2 + 1, js1:js2 + 1] = gam1
+    su[is1:is2 + 1, js1:js2 + 1] = 200.0
+    sp[is1:is2 + 1, js1:js2 + 1] = -0.1
+    gam[2:nim1 + 1, nj] = 0.0
+    for i in range(2, nim1 + 1):
+        su[i, 2] += g.r[1] / g.arx[2] * tf / (g.ydif[2] / gam[i, 2] + 1.0 / htc)
+        sp[i, 2] -= g.r[1] / g.arx[2] / (g.ydif[2] / gam[i, 2] + 1.0 / htc)
+        gam[i, 1] = 0.0
+    su[nim1, 2:njm1 + 1] += qin / g.sew[nim1]
+    gam[ni, 2:njm1 + 1] = 0.0
+    imon = jmon = 26
+    hist, max_iter, llast, it = {}, 19999, False, 0
+    prev = None
+    for it in range(1, max_iter + 1):
+        if llast:                                       # boundary() acts on the last pass only (ibnd = 2)
+            g.t[2:nim1 + 1, nj] = g.t[2:nim1 + 1, njm1]
+            g.t[2:nim1 + 1, 1] = (gam0 * g.t[2:nim1 + 1, 2] + htc * g.ydif[2] * tf) / (gam0 + htc * g.ydif[2])
+            g.t[ni, 2:njm1 + 1] = g.t[nim1, 2:njm1 + 1] + qin * g.xdif[ni] / gam0
+        g.calct(gam, su, sp)
+        if it in (1, 2, 10, 100, 1000, 2000, 3000):
+            hist[str(it)] = [g.resor[3], float(g.t[imon, jmon])]
+        if llast:
+            break
+        if g.resor[3] < 1.0e-10 or it == max_iter - 1:
+            llast = True
+        # the iteration becomes bitwise stationary well before max_iter: stop restating once it has
+        cur = (g.resor[3], float(g.t[imon, jmon]))
+        if it > 3000 and cur == prev and not llast:
+            stationary_at = it
+            it = max_iter - 1                          # jump to the reference's last-but-one pass
+            llast = True
+            continue
+        prev = cur
+    qwall = sum(gam[1, j] * (g.y[j] - g.y[j - 1]) * (g.t[1, j] - g.t[2, j]) / (g.x[2] - g.x[1]) for j in range(2, njm1 + 1))
+    T = g.t[1:ni + 1, 1:nj + 1]
+    return {"_source": "tools/gen_kat.py (face-based numpy restatement of the complete program "
+                       "cylinder-heat-conduction-2d/cylin_cond.f90 as shipped; independent of oracle/general_oracle.c)",
+            "history": hist, "iterations": 19999, "final_tres": g.resor[3], "final_t_mon": float(g.t[imon, jmon]),
+            "qwall_west": float(qwall), "sum_abs_t": float(np.abs(T).sum()), "t_max": float(T.max()), "t_min": float(T.min())}
+
+
+def gen_buoyancy():
+    """buoyancy_cav.f90 (calcu, calcv, calcp, calct, tdma, grid) with the Boussinesq `user` module this build authored
+    (the reference's is missing): unit square, T = 1 / 0 on the west / east wall, adiabatic north / south, rho = cp = 1,
+    nu = Pr*alpha, rho*g*beta = Ra*nu*alpha, Tref = 0.5, Ra = 1e6, Pr = 0.71, alpha = 2.3e-5, urf .3/.3/.9/1, nsweep 3."""
+    out = {"_source": "tools/gen_kat.py (face-based numpy restatement of buoyancy-driven-cavity-2d/buoyancy_cav.f90 "
+                      "calcu/calcv/calcp/calct/tdma/grid; user module authored by this build, DESIGN.md section 7)"}
+    for n, iadv, its in ((34, 3, (1, 2, 10, 100)), (34, 4, (1, 5)), (34, 1, (1, 5)), (34, 2, (1, 5)), (66, 3, (1, 20))):
+        ra, pr, alpha = 1.0e6, 0.71, 2.3e-5
+        visc, cond, tref = pr * alpha, alpha, 0.5
+        rgbeta = ra * visc * alpha
+        g = GeneralRef(n, n, 1, iadv, (0.0, 1.0, 0.0, 1.0, 1.0), (0.3, 0.3, 0.9, 1.0), (3, 3, 3, 3))
+        g.ipref = g.jpref = n // 2
+        imon = jmon = n // 2
+        g.t[1:n + 1, 1:n + 1] = tref
+        g.t[1, 1:n + 1] = 1.0
+        g.t[n, 1:n + 1] = 0.0
+        gmom = np.full((n + 2, n + 2), visc)
+        gt = np.full((n + 2, n + 2), cond)
+        gt[2:n, n] = 0.0
+        gt[2:n, 1] = 0.0
+        zero = np.zeros((n + 2, n + 2))
+        hist = {}
+        for it in range(1, max(its) + 1):
+            g.calcu(gmom)
+            sv = np.zeros((n + 2, n + 2))
+            Iv, Jv = W(2, n - 1), W(3, n - 1)
+            sv[Iv, Jv] = rgbeta * (arimean(g.t[Iv, W(3, n - 1, -1)], g.t[Iv, Jv], g.fy[Jv][None, :]) - tref)
+            g.calcv(gmom, sv)
+            g.calcp()
+            g.calct(gt, zero, zero)
+            if it in its:
+                hist[str(it)] = {"resor": list(g.resor), "u_mon": float(g.u[imon, jmon]), "v_mon": float(g.v[imon, jmon]),
+                                 "p_mon": float(g.p[imon + 1, jmon + 2]), "t_mon": float(g.t[imon, jmon]),
+                                 # t without its adiabatic boundary rows: the program fills them on its last pass only
+                                 "sum_abs": [float(np.abs(a[1:n + 1, 1:n + 1]).sum()) for a in (g.u, g.v, g.p)]
+                                 + [float(np.abs(g.t[1:n + 1, 2:n]).sum())]}
+        out[f"n{n}_iadv{iadv}"] = {"ni": n, "nj": n, "iadv": iadv, "imon": imon, "jmon": jmon, "history": hist}
+    return out
+
+
+
+# =====================================================================================================================
+# 3. backward-step-flow-2d/ (TEACH-T), laminar subset: contro (control.f90:15-204), init (general.f90:69-161),
+#    calcu / calcv / calcp (calc.f90:20-305), modu / modv (promod.f90:26-133), lisolv (general.f90:294-327).
+#    Double precision (the reference is default REAL; the C oracle and the CUDA path are FP64).
+# =====================================================================================================================
+class TeachRef:
+    def __init__(self, ni, nj, jstep, epsx=1.05, indcos=2, rlarge=0.0124, uin=0.5, densit=1000.0, viscos=0.8e-3,
+                 urf=(0.5, 0.5, 1.0), nswp=(3, 3, 5)):
+        self.ni, self.nj, self.urf, self.nswp, self.viscos, self.indcos = ni, nj, urf, nswp, viscos, indcos
+        nim1, njm1 = ni - 1, nj - 1
+        self.istep, self.jstep, self.great = 2, jstep, 1.0e30
+        istp1, jstp1 = 3, jstep + 1
+        zi, zj = (lambda: np.zeros(ni + 2)), (lambda: np.zeros(nj + 2))
+        x, y = zi(), zj()
+        altot = 16.0 * rlarge                                              # control.f90:72-90
+        sumx = 0.5 * epsx ** (ni - 4) + (epsx ** (ni - 3) - 1.0) / (epsx - 1.0) + 0.5 if epsx != 1.0 else float(ni - 2)
+        dx = altot / sumx
+        x[1] = -0.5 * dx
+        x[2] = -x[1]
+        for i in range(3, nim1 + 1):
+            x[i] = x[i - 1] + dx
+            dx = epsx * dx
+        x[ni] = x[nim1] - x[ni - 2] + x[nim1]
+        dy = rlarge / float(nj - 2)
+        y[1] = -0.5 * dy
+        for j in range(2, nj + 1):
+            y[j] = y[j - 1] + dy
+        # init (general.f90:69-140)
+        r = y.copy() if indcos != 1 else np.concatenate(([0.0], np.ones(nj), [0.0]))
+        dxep, dxpw, dynp, dyps = zi(), zi(), zj(), zj()
+        dxep[W(1, nim1)] = x[W(2, ni)] - x[W(1, nim1)]
+        dxpw[W(2, ni)] = dxep[W(1, nim1)]
+        dynp[W(1, njm1)] = y[W(2, nj)] - y[W(1, njm1)]
+        dyps[W(2, nj)] = dynp[W(1, njm1)]
+        sew, sns = zi(), zj()
+        sew[W(2, nim1)] = 0.5 * (dxep[W(2, nim1)] + dxpw[W(2, nim1)])
+        sns[W(2, njm1)] = 0.5 * (dynp[W(2, njm1)] + dyps[W(2, njm1)])
+        xu = zi()
+        xu[W(2, ni)] = 0.5 * (x[W(2, ni)] + x[W(1, nim1)])
+        dxepu, dxpwu, sewu = zi(), zi(), zi()
+        dxepu[W(2, nim1)] = xu[W(3, ni)] - xu[W(2, nim1)]
+        dxpwu[W(3, ni)] = dxepu[W(2, nim1)]
+        sewu[W(3, nim1)] = 0.5 * (dxepu[W(3, nim1)] + dxpwu[W(3, nim1)])
+        rv, rcv, yv = zj(), zj(), zj()
+        rv[W(2, nj)] = 0.5 * (r[W(2, nj)] + r[W(1, njm1)])
+        for j in range(2, nj + 1):
+            rcv[j] = 0.5 * (rv[j] + rv[j - 1])
+        yv[W(2, nj)] = 0.5 * (y[W(2, nj)] + y[W(1, njm1)])
+        dynpv, dypsv, snsv = zj(), zj(), zj()
+        dynpv[W(2, njm1)] = yv[W(3, nj)] - yv[W(2, njm1)]
+        dypsv[W(3, nj)] = dynpv[W(2, njm1)]
+        snsv[W(3, njm1)] = 0.5 * (dynpv[W(3, njm1)] + dypsv[W(3, njm1)])
+        for k, v in dict(x=x, y=y, r=r, rv=rv, rcv=rcv, yv=yv, xu=xu, sew=sew, sns=sns, sewu=sewu, snsv=snsv, dxep=dxep,
+                         dxpw=dxpw, dynp=dynp, dyps=dyps, dxepu=dxepu, dxpwu=dxpwu, dynpv=dynpv, dypsv=dypsv).items():
+            setattr(self, k, v)
+        z2 = lambda: np.zeros((ni + 2, nj + 2))
+        for n in ("u", "v", "p", "pp", "du", "dv", "ae", "aw", "an", "as_", "ap", "su", "sp"):
+            setattr(self, n, z2())
+        self.den = np.full((ni + 2, nj + 2), densit)
+        self.vis = np.full((ni + 2, nj + 2), viscos)
+        u = self.u                                                         # control.f90:148-168
+        u[2, W(2, jstep)] = uin
+        jfin = jstp1
+        for i in range(2, ni + 1):
+            if i >= istp1:
+                jfin = nj
+            factor = (yv[jstp1] * rv[jstp1]) / (yv[jfin] * rv[jfin])
+            u[i, W(2, jfin - 1)] = uin * factor
+        J = W(2, njm1)                                                     # control.f90:197-203
+        arden = 0.5 * (self.den[1, J] + self.den[2, J]) * r[J] * sns[J]
+        self.flowin = float((arden * u[2, J]).sum())
+        self.xmonin = float((arden * u[2, J] * u[2, J]).sum())
+        self.res = [0.0, 0.0, 0.0]
+
+    @staticmethod
+    def _hybrid(c, d, sign):
+        return np.maximum(np.abs(0.5 * c), d) + sign * 0.5 * c
+
+    def calcu(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, vis = self.u, self.v, self.p, self.den, self.vis
+        I, J = (lambda d=0: W(3, nim1, d)), (lambda d=0: W(2, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        a_n, a_s = row(self.rv, 1) * col(self.sewu), row(self.rv) * col(self.sewu)            # calc.f90:32-35
+        a_ew = row(self.r) * row(self.sns)
+        vol = row(self.r) * col(self.sewu) * row(self.sns)
+        gn = 0.5 * (den[I(), J(1)] + den[I(), J()]) * v[I(), J(1)]                            # :39-46
+        gnw = 0.5 * (den[I(-1), J()] + den[I(-1), J(1)]) * v[I(-1), J(1)]
+        gs = 0.5 * (den[I(), J(-1)] + den[I(), J()]) * v[I(), J()]
+        gsw = 0.5 * (den[I(-1), J()] + den[I(-1), J(-1)]) * v[I(-1), J()]
+        ge = 0.5 * (den[I(1), J()] + den[I(), J()]) * u[I(1), J()]
+        gp = 0.5 * (den[I(), J()] + den[I(-1), J()]) * u[I(), J()]
+        gw = 0.5 * (den[I(-1), J()] + den[I(-2), J()]) * u[I(-1), J()]
+        cn, cs = 0.5 * (gn + gnw) * a_n, 0.5 * (gs + gsw) * a_s                               # :48-51
+        ce, cw = 0.5 * (ge + gp) * a_ew, 0.5 * (gp + gw) * a_ew
+        visn = 0.25 * (vis[I(), J()] + vis[I(), J(1)] + vis[I(-1), J()] + vis[I(-1), J(1)])   # :54-59
+        viss = 0.25 * (vis[I(), J()] + vis[I(), J(-1)] + vis[I(-1), J()] + vis[I(-1), J(-1)])
+        dn, ds = visn * a_n / row(self.dynp), viss * a_s / row(self.dyps)
+        de, dw = vis[I(), J()] * a_ew / col(self.dxepu), vis[I(-1), J()] * a_ew / col(self.dxpwu)
+        cp = np.maximum(0.0, cn - cs + ce - cw)                                               # :63-66
+        an, as_ = self._hybrid(cn, dn, -1), self._hybrid(cs, ds, +1)                          # :69-72
+        ae, aw = self._hybrid(ce, de, -1), self._hybrid(cw, dw, +1)
+        du = a_ew + 0.0 * vol
+        su = cp * u[I(), J()] + du * (p[I(-1), J()] - p[I(), J()])                            # :76
+        sp = -cp
+        dudxp = (u[I(1), J()] - u[I(), J()]) / col(self.sew)                                  # :81-84
+        dudxm = (u[I(), J()] - u[I(-1), J()]) / col(self.sew, -1)
+        su = (vis[I(), J()] * dudxp - vis[I(-1), J()] * dudxm) / col(self.sewu) * vol + su
+        dvdxp = row(self.rv, 1) * (v[I(), J(1)] - v[I(-1), J(1)]) / col(self.dxep)            # :86-94 (gamp = visn, gamm = viss)
+        dvdxm = row(self.rv) * (v[I(), J()] - v[I(-1), J()]) / col(self.dxep)
+        su = su + (visn * dvdxp - viss * dvdxm) / row(self.sns) / row(self.r) * vol
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("su", su), ("sp", sp), ("du", du)):
+            getattr(self, name)[I(), J()] = val
+        # modu (promod.f90:26-95), laminar branch of the wall law: yplusn = 11 <= 11.63  ->  tmult = viscos / yp
+        yp = self.yv[nj] - self.y[njm1]
+        tmult = self.viscos / yp
+        Iw = W(3, nim1)
+        self.sp[Iw, njm1] -= tmult * self.sewu[Iw] * self.rv[nj]
+        self.an[Iw, njm1] = 0.0
+        self.aw[3, W(self.jstep + 1, njm1)] = 0.0
+        u[1:ni + 1, 1] = u[1:ni + 1, 2]
+        self.as_[1:ni + 1, 2] = 0.0
+        Jo = W(2, njm1)
+        arden = 0.5 * (den[nim1, Jo] + den[nim1 - 1, Jo]) * self.r[Jo] * self.sns[Jo]
+        uinc = (self.flowin - float((arden * u[nim1, Jo]).sum())) / float(arden.sum())
+        u[ni, Jo] = u[nim1, Jo] + uinc
+        # chapter 3 (calc.f90:103-124)
+        ae, aw, an, as_, su, sp = (getattr(self, n)[I(), J()] for n in ("ae", "aw", "an", "as_", "su", "sp"))
+        ap = an + as_ + ae + aw - sp
+        du = self.du[I(), J()] / ap
+        rs = an * u[I(), J(1)] + as_ * u[I(), J(-1)] + ae * u[I(1), J()] + aw * u[I(-1), J()] - ap * u[I(), J()] + su
+        self.res[0] = float(np.abs(rs).sum())
+        ap = ap / self.urf[0]
+        self.su[I(), J()] = su + (1.0 - self.urf[0]) * ap * u[I(), J()]
+        self.ap[I(), J()] = ap
+        self.du[I(), J()] = du * self.urf[0]
+        for _ in range(self.nswp[0]):
+            line_sweep(3, 2, ni, nj, u, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    def calcv(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, vis = self.u, self.v, self.p, self.den, self.vis
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(3, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        a_n, a_s = row(self.rcv, 1) * col(self.sew), row(self.rcv) * col(self.sew)            # calc.f90:148-151
+        a_ew = row(self.rv) * row(self.snsv)
+        vol = row(self.rv) * col(self.sew) * row(self.snsv)
+        gn = 0.5 * (den[I(), J(1)] + den[I(), J()]) * v[I(), J(1)]                            # :153-159
+        gp = 0.5 * (den[I(), J()] + den[I(), J(-1)]) * v[I(), J()]
+        gs = 0.5 * (den[I(), J(-1)] + den[I(), J(-2)]) * v[I(), J(-1)]
+        ge = 0.5 * (den[I(1), J()] + den[I(), J()]) * u[I(1), J()]
+        gse = 0.5 * (den[I(), J(-1)] + den[I(1), J(-1)]) * u[I(1), J(-1)]
+        gw = 0.5 * (den[I(), J()] + den[I(-1), J()]) * u[I(), J()]
+        gsw = 0.5 * (den[I(), J(-1)] + den[I(-1), J(-1)]) * u[I(), J(-1)]
+        cn, cs = 0.5 * (gn + gp) * a_n, 0.5 * (gp + gs) * a_s
+        ce, cw = 0.5 * (ge + gse) * a_ew, 0.5 * (gw + gsw) * a_ew
+        vise = 0.25 * (vis[I(), J()] + vis[I(1), J()] + vis[I(), J(-1)] + vis[I(1), J(-1)])   # :165-170
+        visw = 0.25 * (vis[I(), J()] + vis[I(-1), J()] + vis[I(), J(-1)] + vis[I(-1), J(-1)])
+        dn, ds = vis[I(), J()] * a_n / row(self.dynpv), vis[I(), J(-1)] * a_s / row(self.dypsv)
+        de, dw = vise * a_ew / col(self.dxep), visw * a_ew / col(self.dxpw)
+        cp = np.maximum(0.0, cn - cs + ce - cw)
+        an, as_ = self._hybrid(cn, dn, -1), self._hybrid(cs, ds, +1)
+        ae, aw = self._hybrid(ce, de, -1), self._hybrid(cw, dw, +1)
+        dv = 0.5 * (a_n + a_s)
+        su = cp * v[I(), J()] + dv * (p[I(), J(-1)] - p[I(), J()])                            # :181
+        sp = -cp
+        if self.indcos == 2:                                                                  # :183-184: subtracted TWICE as written
+            sink = vis[I(), J()] * vol / row(self.rv) ** 2
+            sp = sp - sink
+            sp = sp - sink
+        dudyp = (u[I(1), J()] - u[I(1), J(-1)]) / row(self.dyps)                              # :185-189
+        dudym = (u[I(), J()] - u[I(), J(-1)]) / row(self.dyps)
+        su = su + (vise * dudyp - visw * dudym) / col(self.sew) * vol
+        dvdyp = (v[I(), J(1)] - v[I(), J()]) / row(self.sns)                                  # :190-194
+        dvdym = (v[I(), J()] - v[I(), J(-1)]) / row(self.sns, -1)
+        su = su + (vis[I(), J()] * row(self.r) * dvdyp - vis[I(), J(-1)] * row(self.r, -1) * dvdym) / (row(self.r) * row(self.sns)) * vol
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("su", su), ("sp", sp), ("dv", dv)):
+            getattr(self, name)[I(), J()] = val
+        # modv (promod.f90:99-133), laminar branch: xplusw = 11 (0 at jstep) <= 11.63  ->  tmult = viscos / xp
+        xp = self.x[self.istep] - self.xu[self.istep]
+        tmult = self.viscos / xp
+        Jw = W(self.jstep + 1, njm1)
+        self.sp[self.istep, Jw] -= tmult * self.snsv[Jw] * self.rv[Jw]
+        self.aw[self.istep, Jw] = 0.0
+        self.an[W(self.istep, nim1), njm1] = 0.0
+        self.as_[W(2, nim1), 3] = 0.0
+        ae, aw, an, as_, su, sp = (getattr(self, n)[I(), J()] for n in ("ae", "aw", "an", "as_", "su", "sp"))
+        ap = an + as_ + ae + aw - sp                                                          # :207-219
+        dv = self.dv[I(), J()] / ap
+        rs = an * v[I(), J(1)] + as_ * v[I(), J(-1)] + ae * v[I(1), J()] + aw * v[I(-1), J()] - ap * v[I(), J()] + su
+        self.res[1] = float(np.abs(rs).sum())
+        ap = ap / self.urf[1]
+        self.su[I(), J()] = su + (1.0 - self.urf[1]) * ap * v[I(), J()]
+        self.ap[I(), J()] = ap
+        self.dv[I(), J()] = dv * self.urf[1]
+        for _ in range(self.nswp[1]):
+            line_sweep(2, 3, ni, nj, v, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+
+    def calcp(self):
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        u, v, p, den, du, dv, pp = self.u, self.v, self.p, self.den, self.du, self.dv, self.pp
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        a_n, a_s = row(self.rv, 1) * col(self.sew), row(self.rv) * col(self.sew)              # calc.f90:245-247
+        a_ew = row(self.r) * row(self.sns) + 0.0 * a_n
+        dnn, dns = 0.5 * (den[I(), J()] + den[I(), J(1)]), 0.5 * (den[I(), J()] + den[I(), J(-1)])
+        dne, dnw = 0.5 * (den[I(), J()] + den[I(1), J()]), 0.5 * (den[I(), J()] + den[I(-1), J()])
+        an, as_ = dnn * a_n * dv[I(), J(1)], dns * a_s * dv[I(), J()]                         # :253-256
+        ae, aw = dne * a_ew * du[I(1), J()], dnw * a_ew * du[I(), J()]
+        smp = dnn * v[I(), J(1)] * a_n - dns * v[I(), J()] * a_s + dne * u[I(1), J()] * a_ew - dnw * u[I(), J()] * a_ew
+        self.res[2] = float(np.abs(smp).sum())
+        for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("ap", an + as_ + ae + aw), ("su", -smp)):
+            getattr(self, name)[I(), J()] = val
+        for _ in range(self.nswp[2]):
+            line_sweep(2, 2, ni, nj, pp, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+        Iu, Jv = W(3, nim1), W(3, njm1)                                                       # :290-304: velocities first
+        u[Iu, J()] += du[Iu, J()] * (pp[W(3, nim1, -1), J()] - pp[Iu, J()])
+        v[I(), Jv] += dv[I(), Jv] * (pp[I(), W(3, njm1, -1)] - pp[I(), Jv])
+        ppref = pp[2, 2]
+        p[I(), J()] += self.urf[2] * (pp[I(), J()] - ppref)
+        pp[I(), J()] = 0.0
+
+
+def gen_teach():
+    out = {"_source": "tools/gen_kat.py (numpy restatement of backward-step-flow-2d: control.f90, general.f90, calc.f90 "
+                      "calcu/calcv/calcp, promod.f90 modu/modv; laminar, FP64; independent of oracle/teach_body.inc)"}
+    for key, kw in (("ni40_nj30", dict(ni=40, nj=30, jstep=8, epsx=1.05, indcos=2)),
+                    ("ni34_nj26_plane", dict(ni=34, nj=26, jstep=6, epsx=1.0, indcos=1))):
+        t = TeachRef(**kw)
+        imon, jmon = 10, 10
+        hist = {}
+        for it in range(1, 101):
+            t.calcu()
+            t.calcv()
+            t.calcp()
+            if it in (1, 2, 10, 100):
+                ni, nj = t.ni, t.nj
+                hist[str(it)] = {"res": list(t.res), "u_mon": float(t.u[imon, jmon]), "v_mon": float(t.v[imon, jmon]),
+                                 "p_mon": float(t.p[imon, jmon]), "u_out": float(t.u[ni, jmon]),
+                                 "sum_abs": [float(np.abs(a[1:ni + 1, 1:nj + 1]).sum()) for a in (t.u, t.v, t.p)]}
+        out[key] = dict(kw, imon=imon, jmon=jmon, flowin=t.flowin, xmonin=t.xmonin, history=hist)
+    return out
+
+
+
+# =====================================================================================================================
+# 4. lid-driven-cavity-2d/fdm-explicit/fdm_explicit_cavity.f90: explicit-Euler predictor, p' by Stone's SIP (sipsol
+#    :24-87), correction, mirror-ghost boundary conditions, continuity norm (time loop :168-255).
+#    SIP works on the system  ap*phi + aw*phiW + ae*phiE + as*phiS + an*phiN = su  (the program passes -aw .. -an).
+# =====================================================================================================================
+@numba.njit(cache=True)
+def sip_solve(n1, n2, aw, ae, as_, an, ap, su, phi, alpha, tol, maxit):
+    """sipsol on the index box 1..n1 x 1..n2 (interior 2..n1-1 x 2..n2-1).  Returns the iterations used."""
+    lw = np.zeros((n1 + 2, n2 + 2)); ls = np.zeros((n1 + 2, n2 + 2)); lp = np.zeros((n1 + 2, n2 + 2))
+    un = np.zeros((n1 + 2, n2 + 2)); ue = np.zeros((n1 + 2, n2 + 2)); rs = np.zeros((n1 + 2, n2 + 2))
+    for j in range(2, n2):
+        for i in range(2, n1):
+            lw[i, j] = aw[i, j] / (1.0 + alpha * un[i - 1, j])
+            ls[i, j] = as_[i, j] / (1.0 + alpha * ue[i, j - 1])
+            p1 = alpha * lw[i, j] * un[i - 1, j]
+            p2 = alpha * ls[i, j] * ue[i, j - 1]
+            lp[i, j] = 1.0 / (ap[i, j] + p1 + p2 - lw[i, j] * ue[i - 1, j] - ls[i, j] * un[i, j - 1])
+            un[i, j] = (an[i, j] - p1) * lp[i, j]
+            ue[i, j] = (ae[i, j] - p2) * lp[i, j]
+    res1 = 0.0
+    used = 0
+    for it in range(1, maxit + 1):
+        used = it
+        resl = 0.0
+        for j in range(2, n2):
+            for i in range(2, n1):
+                r = su[i, j] - aw[i, j] * phi[i - 1, j] - ae[i, j] * phi[i + 1, j] - an[i, j] * phi[i, j + 1] \
+                    - as_[i, j] * phi[i, j - 1] - ap[i, j] * phi[i, j]
+                resl += abs(r)
+                rs[i, j] = (r - ls[i, j] * rs[i, j - 1] - lw[i, j] * rs[i - 1, j]) * lp[i, j]
+        if it == 1:
+            res1 = resl
+        rsm = resl / res1
+        for j in range(n2 - 1, 1, -1):
+            for i in range(n1 - 1, 1, -1):
+                rs[i, j] = rs[i, j] - un[i, j] * rs[i, j + 1] - ue[i, j] * rs[i + 1, j]
+                phi[i, j] += rs[i, j]
+        if rsm < tol:
+            break
+        if it == 1 and res1 < 1.0e-10:
+            break
+    return used
+
+
+def gen_fdcavity():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of lid-driven-cavity-2d/fdm-explicit/fdm_explicit_cavity.f90; "
+                      "independent of oracle/fdcavity_oracle.c)"}
+    for key, ni, nj, re, dt, nsteps in (("n33", 33, 33, 10.0, 1.0e-4, 5), ("n21x13", 21, 13, 10.0, 1.0e-4, 5),
+                                        ("n11_default", 11, 11, 10.0, 1.0e-4, 20)):
+        utop, urfp = 1.0, 0.8
+        dx, dy = 1.0 / (ni - 1), 1.0 / (nj - 1)
+        Z = lambda a, b: np.zeros((a + 2, b + 2))
+        u, v, p, pp = Z(ni, nj + 1), Z(ni + 1, nj), Z(ni + 1, nj + 1), Z(ni + 1, nj + 1)
+        uo, vo, po = Z(ni, nj + 1), Z(ni + 1, nj), Z(ni + 1, nj + 1)
+        uo[1:ni + 1, nj:nj + 2] = 1.0                                     # :162-165
+        po[1:ni + 1 + 1, 1:nj + 1 + 1] = 1.0
+        ae, aw, an, as_, ap, su = (Z(ni + 1, nj + 1) for _ in range(6))
+        steps = []
+        for itsp in range(1, nsteps + 1):
+            I, J = (lambda d=0: W(2, ni - 1, d)), (lambda d=0: W(2, nj, d))            # u momentum :170-180
+            t = -0.5 * (uo[I(1), J()] * uo[I(1), J()] - uo[I(-1), J()] * uo[I(-1), J()]) / dx \
+                - 0.25 * ((uo[I(), J()] + uo[I(), J(1)]) * (vo[I(), J()] + vo[I(1), J()])
+                          - (uo[I(), J()] + uo[I(), J(-1)]) * (vo[I(), J(-1)] + vo[I(1), J(-1)])) / dy \
+                - (po[I(1), J()] - po[I(), J()]) / dx \
+                + ((uo[I(-1), J()] - 2.0 * uo[I(), J()] + uo[I(1), J()]) / dx ** 2
+                   + (uo[I(), J(-1)] - 2.0 * uo[I(), J()] + uo[I(), J(1)]) / dy ** 2) / re
+            u[I(), J()] = uo[I(), J()] + dt * t
+            I, J = (lambda d=0: W(2, ni, d)), (lambda d=0: W(2, nj - 1, d))            # v momentum :182-192
+            t = -0.25 * ((uo[I(), J()] + uo[I(), J(1)]) * (vo[I(), J()] + vo[I(1), J()])
+                         - (uo[I(-1), J()] + uo[I(-1), J(1)]) * (vo[I(), J()] + vo[I(-1), J()])) / dx \
+                - 0.5 * (vo[I(), J(1)] * vo[I(), J(1)] - vo[I(), J(-1)] * vo[I(), J(-1)]) / dy \
+                - (po[I(), J(1)] - po[I(), J()]) / dy \
+                + ((vo[I(-1), J()] - 2.0 * vo[I(), J()] + vo[I(1), J()]) / dx ** 2
+                   + (vo[I(), J(-1)] - 2.0 * vo[I(), J()] + vo[I(), J(1)]) / dy ** 2) / re
+            v[I(), J()] = vo[I(), J()] + dt * t
+            pp[:, :] = 0.0                                                               # :194-205
+            I, J = (lambda d=0: W(2, ni, d)), (lambda d=0: W(2, nj, d))
+            ae[I(), J()] = aw[I(), J()] = dt / dx ** 2
+            an[I(), J()] = as_[I(), J()] = dt / dy ** 2
+            su[I(), J()] = -(u[I(), J()] - u[I(-1), J()]) / dx - (v[I(), J()] - v[I(), J(-1)]) / dy
+            ap[I(), J()] = 2 * (dt / dx ** 2 + dt / dy ** 2)
+            nit = sip_solve(ni + 1, nj + 1, -aw, -ae, -as_, -an, ap, su, pp, 0.88, 1.0e-5, 600)   # :206
+            p[I(), J()] += urfp * pp[I(), J()]                                           # :208-222
+            Iu = W(2, ni - 1)
+            u[Iu, J()] -= dt / dx * (pp[W(2, ni - 1, 1), J()] - pp[Iu, J()])
+            Jv = W(2, nj - 1)
+            v[I(), Jv] -= dt / dy * (pp[I(), W(2, nj - 1, 1)] - pp[I(), Jv])
+            u[1:ni + 1, 1] = -u[1:ni + 1, 2]                                             # :224-237
+            u[1:ni + 1, nj + 1] = 2.0 * utop - u[1:ni + 1, nj]
+            u[1, 2:nj + 1] = 0.0
+            u[ni, 2:nj + 1] = 0.0
+            v[1, 1:nj + 1] = -v[2, 1:nj + 1]
+            v[ni + 1, 1:nj + 1] = -v[ni, 1:nj + 1]
+            v[2:ni + 1, 1] = 0.0
+            v[2:ni + 1, nj] = 0.0
+            p[1, 1:ni + 2] = p[2, 1:ni + 2]                                              # extent ni+1 as written (:234)
+            p[ni + 1, 1:nj + 2] = p[ni, 1:nj + 2]
+            p[2:ni + 1, nj + 1] = p[2:ni + 1, nj]
+            p[2:ni + 1, 1] = p[2:ni + 1, 2]
+            I, J = (lambda d=0: W(2, ni, d)), (lambda d=0: W(2, nj, d))                  # :239-247
+            err = float(np.sqrt((((u[I(), J()] - u[I(-1), J()]) / dx + (v[I(), J()] - v[I(), J(-1)]) / dy) ** 2).sum()))
+            steps.append({"sip_iters": int(nit), "error": err, "u_mon": float(u[ni // 2, nj // 2]),
+                          "sum_abs": [float(np.abs(a[1:, 1:]).sum()) for a in (u[:ni + 1, :nj + 2], v[:ni + 2, :nj + 1], p[:ni + 2, :nj + 2])]})
+            uo[:, :], vo[:, :], po[:, :] = u, v, p                                       # :252-254
+        out[key] = {"ni": ni, "nj": nj, "re": re, "dt": dt, "steps": steps}
+    return out
+
+
+# =====================================================================================================================
+# 5. stagnation-point-flow-2d/steady/fvm2d_stag_point.f90: coefficients (:462-498), boundary edits (:500-515), the
+#    iterative line solvers tdma_we / tdma_sn (:82-160) with wesweep / snsweep / tdma (:162-260), wall flux (:528-533).
+# =====================================================================================================================
+@numba.njit(cache=True)
+def stag_sweep(direction, ni, nj, aw, ae, as_, an, ap, su, phi):
+    """direction 0: wesweep (lines along j, W->E); 1: snsweep (lines along i, S->N).  tdma :232-260: two divisions."""
+    n = nj if direction == 0 else ni
+    P = np.zeros(n + 2); Q = np.zeros(n + 2)
+    outer = ni if direction == 0 else nj
+    for o in range(2, outer):
+        P[1] = 0.0
+        Q[1] = phi[o, 1] if direction == 0 else phi[1, o]
+        for k in range(2, n):
+            if direction == 0:
+                a, b, c = ap[o, k], an[o, k], as_[o, k]
+                d = su[o, k] + aw[o, k] * phi[o - 1, k] + ae[o, k] * phi[o + 1, k]
+            else:
+                a, b, c = ap[k, o], ae[k, o], aw[k, o]
+                d = su[k, o] + as_[k, o] * phi[k, o - 1] + an[k, o] * phi[k, o + 1]
+            P[k] = b / (a - c * P[k - 1])
+            Q[k] = (d + c * Q[k - 1]) / (a - c * P[k - 1])
+        for k in range(n - 1, 1, -1):
+            if direction == 0:
+                phi[o, k] = P[k] * phi[o, k + 1] + Q[k]
+            else:
+                phi[k, o] = P[k] * phi[k + 1, o] + Q[k]
+
+
+def gen_stagnation():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of stagnation-point-flow-2d/steady/fvm2d_stag_point.f90; "
+                      "independent of oracle/lin_oracle.c); den 1.2, gam 0.1, uniform grid, stop rule rsm < 1e-4"}
+    for ncv in (20, 32):
+        for isch in (1, 2):
+            for isol in (1, 2):
+                ni = nj = ncv + 2
+                nim1, njm1 = ni - 1, nj - 1
+                den, gam = 1.2, 0.1
+                x, y, xc, yc, fx, fy = (np.zeros(ni + 2) for _ in range(6))
+                dx = 1.0 / ncv
+                x[1] = 0.0
+                for i in range(2, nim1 + 1):
+                    x[i] = x[i - 1] + dx
+                x[ni] = x[nim1]
+                xc[1] = x[1]
+                xc[W(2, nim1)] = 0.5 * (x[W(2, nim1)] + x[W(2, nim1, -1)])
+                xc[ni] = x[nim1]
+                y[:], yc[:] = x, xc                                          # same construction in y (ymin = 0, ymax = 1)
+                fx[W(2, nim1)] = (x[W(2, nim1)] - xc[W(2, nim1)]) / (xc[W(2, nim1, 1)] - xc[W(2, nim1)])
+                fy[:] = fx
+                u = np.repeat(x[:, None], nj + 2, axis=1)                   # u(i,j) = x(i), v(i,j) = -y(j)   (:443-448)
+                v = -np.repeat(y[None, :], ni + 2, axis=0)
+                phi = np.zeros((ni + 2, nj + 2))
+                phi[1, 1:njm1 + 1] = 1.0 - yc[1:njm1 + 1]                   # :452
+                I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+                hy = (y[J()] - y[J(-1)])[None, :]
+                hx = (x[I()] - x[I(-1)])[:, None]
+                de = -gam * hy / (xc[I(1)] - xc[I()])[:, None]              # :456-459
+                dw = -gam * hy / (xc[I()] - xc[I(-1)])[:, None]
+                dn = -gam * hx / (yc[J(1)] - yc[J()])[None, :]
+                ds = -gam * hx / (yc[J()] - yc[J(-1)])[None, :]
+                ge, gw = den * u[I(), J()] * hy, -den * u[I(-1), J()] * hy   # :466-469
+                gn, gs = den * v[I(), J()] * hx, -den * v[I(), J(-1)] * hx
+                if isch == 1:
+                    ce, cw, cn, cs = (np.minimum(g, 0.0) for g in (ge, gw, gn, gs))
+                else:
+                    ce, cw = ge * fx[I()][:, None], gw * (1.0 - fx[I(-1)])[:, None]
+                    cn, cs = gn * fy[J()][None, :], gs * (1.0 - fy[J(-1)])[None, :]
+                A = {k: np.zeros((ni + 2, nj + 2)) for k in ("ae", "aw", "an", "as", "ap", "su")}
+                A["ae"][I(), J()], A["aw"][I(), J()] = ce + de, cw + dw
+                A["an"][I(), J()], A["as"][I(), J()] = cn + dn, cs + ds
+                A["ap"][I(), J()] = A["ae"][I(), J()] + A["aw"][I(), J()] + A["an"][I(), J()] + A["as"][I(), J()]
+                A["ap"][nim1, J()] -= A["ae"][nim1, J()]                   # :505-507
+                A["ae"][nim1, J()] = 0.0
+                A["ap"][I(), 2] -= A["as"][I(), 2]                         # :512-514
+                A["as"][I(), 2] = 0.0
+                iters, res1, rsm = 0, 0.0, 0.0
+                for it in range(1, 1001):
+                    iters = it
+                    stag_sweep(isol - 1, ni, nj, A["aw"], A["ae"], A["as"], A["an"], A["ap"], A["su"], phi)
+                    r = A["ae"][I(), J()] * phi[I(1), J()] + A["aw"][I(), J()] * phi[I(-1), J()] + A["an"][I(), J()] * phi[I(), J(1)] \
+                        + A["as"][I(), J()] * phi[I(), J(-1)] + A["su"][I(), J()] - A["ap"][I(), J()] * phi[I(), J()]
+                    res = float(np.abs(r).sum())
+                    if it == 1:
+                        res1 = res
+                    rsm = res / res1
+                    if rsm < 1.0e-4 or (it == 1 and res1 < 1.0e-10):
+                        break
+                phi[W(2, nim1), 1] = phi[W(2, nim1), 2]                    # :524-525
+                phi[ni, 1:nj + 1] = phi[nim1, 1:nj + 1]
+                fwall = float((gam * (y[J()] - y[J(-1)]) * (phi[2, J()] - phi[1, J()]) / (xc[2] - xc[1])).sum())
+                out[f"cv{ncv}_isch{isch}_isol{isol}"] = {"ncv": ncv, "isch": isch, "isol": isol, "iters": iters, "rsm": rsm,
+                                                         "fwall": fwall, "phi_mid": float(phi[ni // 2, nj // 2]),
+                                                         "sum_abs_phi": float(np.abs(phi[1:ni + 1, 1:nj + 1]).sum())}
+    return out
+
+
+GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "fdcavity": gen_fdcavity, "stagnation": gen_stagnation}
+
+
+
+def main():
+    which = sys.argv[1:] or list(GENERATORS)
+    for name in which:
+        t0 = time.time()
+        data = GENERATORS[name]()
+        path = os.path.join(GOLD, f"{name}_kat.json")
+        with open(path, "w") as f:
+            json.dump(data, f, indent=1)
+        print(f"{path}: {time.time() - t0:.1f} s")
+
+
+if __name__ == "__main__":
+    main()
