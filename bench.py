@@ -309,8 +309,13 @@ def run_ours(args):
         sync_res = solver.residuals
         ctx0 = solver.ctx
         cells_total = NICV * world * NJCV
-        par = (f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals, "
-               + ("one CUDA graph per outer iteration" if graphed else "eager launches"))
+        if getattr(solver, "peer", False):
+            par = (f"i-slabs x{world}; halo lines over peer memory (NVLink): edge lines stored into the neighbour's halo from "
+                   "inside the flag-ordered sweep kernels, cfd_halo_push between stages; pp(ipref,jpref) broadcast and "
+                   "residual all-reduce over NCCL")
+        else:
+            par = (f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals, "
+                   + ("one CUDA graph per outer iteration" if graphed else "eager launches"))
         if args.slabs == "j":
             par = (f"j-slabs x{world}: lines cut across GPUs, partitioned Thomas (piece solves + spike vectors, "
                    "all-gathered reduced system per line), halo rows once per iteration, all-reduced residuals")
@@ -340,9 +345,11 @@ def run_ours(args):
         clocks = sampler.stop() if rank == 0 else None
         res = sync_res()
     if world > 1:
-        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        tms = torch.tensor([ms, 1.0 if ctx0.peer_status() else 0.0], device="cuda", dtype=torch.float64)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        ms = float(tms.item())
+        ms = float(tms[0].item())
+        if float(tms[1].item()) != 0.0:
+            raise SystemExit("bench.py: a wait on a neighbouring GPU timed out (peer halo path); the run is invalid")
     glups = cells_total * K / (ms * 1e-3) / 1e9
 
     out = {"metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K,

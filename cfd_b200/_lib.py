@@ -101,6 +101,14 @@ SYMBOLS = {
     "cfd_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cfd_sweep_part": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cfd_correct": (C.c_int, [_vp, _vp]),
+    "cfd_sweeps": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "cfd_ipc_export": (C.c_int, [_vp, C.c_int, _vp]),
+    "cfd_ipc_open": (C.c_int, [_vp, _vp, C.POINTER(_vp)]),
+    "cfd_peer_attach": (C.c_int, [_vp, C.c_int, C.c_int, _vp, C.c_int, C.c_int, C.c_int]),
+    "cfd_peer_detach": (C.c_int, [_vp]),
+    "cfd_halo_push": (C.c_int, [_vp, C.c_int, _ip, _ip, _ip]),
+    "cfd_peer_status": (C.c_int, [_vp, _ip]),
+    "cfd_sweeps_single_launch": (C.c_int, [_vp, _ip]),
     "cfd_set_turbulence": (C.c_int, [_vp, C.POINTER(CfdTurbulence)]),
     "cfd_wall_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_wall_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),

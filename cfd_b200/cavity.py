@@ -230,6 +230,50 @@ class CavityFVM:
     def sweep_part(self, istart, jstart, phi, colour, first=False, part=0):
         check(self.lib.cfd_sweep_part(self._h, istart, jstart, FIELD_ID[phi], colour, 1 if first else 0, part))
 
+    def sweeps(self, istart, jstart, phi, nsweeps, first=False):
+        """cfd_sweeps: the `do n = 1, nswp; call lisolv` loop, all colour passes in one flag-ordered launch."""
+        check(self.lib.cfd_sweeps(self._h, istart, jstart, FIELD_ID[phi], nsweeps, 1 if first else 0))
+
+    # -- i-slab neighbours over peer memory -------------------------------------------------------------------
+    IPC_FLAGS = -1
+
+    def ipc_export(self, what) -> bytes:
+        """64-byte CUDA IPC handle of a plain field's allocation (`what` = field name) or of the flag block ("flags")."""
+        buf = C.create_string_buffer(64)
+        check(self.lib.cfd_ipc_export(self._h, self.IPC_FLAGS if what == "flags" else FIELD_ID[what], buf))
+        return buf.raw
+
+    def ipc_open(self, handle: bytes) -> int:
+        p = C.c_void_p()
+        check(self.lib.cfd_ipc_open(self._h, C.create_string_buffer(handle, 64), C.byref(p)))
+        return p.value
+
+    def peer_attach(self, side: int, what, devptr: int, peer_ni: int, peer_hw: int, peer_he: int):
+        check(self.lib.cfd_peer_attach(self._h, side, self.IPC_FLAGS if what == "flags" else FIELD_ID[what],
+                                       C.c_void_p(devptr), peer_ni, peer_hw, peer_he))
+
+    def halo_push(self, spec):
+        """spec: sequence of (field name, w, e): my last w owned lines go to the east neighbour's west halo, my first e
+        owned lines to the west neighbour's east halo; returns when (on the stream) the neighbours' lines are here."""
+        n = len(spec)
+        arr = lambda vals: (C.c_int * n)(*vals)
+        check(self.lib.cfd_halo_push(self._h, n, arr([FIELD_ID[f] for f, _, _ in spec]), arr([w for _, w, _ in spec]),
+                                     arr([e for _, _, e in spec])))
+
+    def sweeps_single_launch(self) -> bool:
+        y = C.c_int()
+        check(self.lib.cfd_sweeps_single_launch(self._h, C.byref(y)))
+        return bool(y.value)
+
+    def peer_detach(self):
+        check(self.lib.cfd_peer_detach(self._h))
+
+    def peer_status(self) -> bool:
+        """True if a bounded wait on a neighbour ever timed out."""
+        a = C.c_int()
+        check(self.lib.cfd_peer_status(self._h, C.byref(a)))
+        return bool(a.value)
+
     def correct(self, ppref_device_ptr: int | None = None):
         check(self.lib.cfd_correct(self._h, C.c_void_p(ppref_device_ptr) if ppref_device_ptr else None))
 

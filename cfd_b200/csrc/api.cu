@@ -211,6 +211,15 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->res_dev = nullptr;
   c->seq_scratch = nullptr;
   c->launches = 0;
+  c->flags = nullptr;
+  c->epoch = 1;
+  c->xepoch = 0;
+  for (int sd = 0; sd < 2; ++sd) {
+    c->peer_attached[sd] = false;
+    c->peer_flags[sd] = nullptr;
+    c->peer_ni[sd] = c->peer_hw[sd] = c->peer_halo_line[sd] = 0;
+    for (auto& pf : c->peer_field[sd]) pf = nullptr;
+  }
   // from here on every failure path releases what has been allocated so far
 #define CREATE_CUDA(call)                                                                       \
   do {                                                                                          \
@@ -293,6 +302,8 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CREATE_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
   CREATE_CUDA(cudaMalloc(&c->res_dev, CFD_RES_SLOTS * sizeof(double)));
   CREATE_CUDA(cudaMemset(c->res_dev, 0, CFD_RES_SLOTS * sizeof(double)));
+  CREATE_CUDA(cudaMalloc(&c->flags, ((size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
+  CREATE_CUDA(cudaMemset(c->flags, 0, ((size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
   {
     // cfd_upload_noalloc's staging area: with lazy module loading the array is only materialised when something in
     // this module is first touched, so touch it HERE, while allocating is still allowed (see cfd_upload_noalloc)
@@ -327,6 +338,8 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   if (c->stage) cudaFree(c->stage);
   if (c->partial) cudaFree(c->partial);
   if (c->res_dev) cudaFree(c->res_dev);
+  for (void* m : c->ipc_opened) cudaIpcCloseMemHandle(m);
+  if (c->flags) cudaFree(c->flags);
   if (c->seq_scratch) cudaFree(c->seq_scratch);
   delete c;
   return CFD_OK;
@@ -583,6 +596,107 @@ static int full_sweep(cfd_ctx* c, int istart, int jstart, int field, int first) 
   return cfd_launch_sweep_rb(c, istart, jstart, c->field[field], 1, first);
 }
 
+// nsw sweeps of one equation: all colour passes in one flag-ordered launch where the layout allows it
+// (tdma_flow_kernels.cu), else one launch per colour pass
+static int sweeps(cfd_ctx* c, int istart, int jstart, int field, int nsw, int first) {
+  if (nsw > 0 && cfd_flow_eligible(c)) return cfd_launch_sweeps_flow(c, istart, jstart, field, nsw, first);
+  int rc;
+  for (int n = 0; n < nsw; ++n)
+    if ((rc = full_sweep(c, istart, jstart, field, first && n == 0))) return rc;
+  return CFD_OK;
+}
+
+extern "C" int cfd_sweeps(cfd_ctx* c, int istart, int jstart, int field, int nsweeps, int first) {
+  CFD_ENTER(c);
+  int rc = check_field(c, field);
+  if (rc) return rc;
+  CFD_REQUIRE(istart >= 2 && jstart >= 2 && jstart <= c->L.nj - 1 && nsweeps >= 0, "istart/jstart/nsweeps out of range");
+  return sweeps(c, istart, jstart, field, nsweeps, first);
+}
+
+// ---- i-slab neighbours over peer memory ---------------------------------------------------------------------------
+static void* ipc_target(cfd_ctx* c, int what) {
+  if (what == CFD_IPC_FLAGS) return c->flags;
+  if (what < 0 || what >= CFD_FIELD_COUNT || cfd_is_coef_field(what)) return nullptr;
+  return c->field[what];
+}
+extern "C" int cfd_ipc_export(cfd_ctx* c, int what, void* handle64) {
+  CFD_REQUIRE(c && handle64, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  void* p = ipc_target(c, what);
+  CFD_REQUIRE(p, "cfd_ipc_export: not a plain field of this context (or CFD_IPC_FLAGS)");
+  CFD_CUDA(cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  CFD_CUDA(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle64, &h, 64);
+  return CFD_OK;
+}
+extern "C" int cfd_ipc_open(cfd_ctx* c, const void* handle64, void** devptr) {
+  CFD_REQUIRE(c && handle64 && devptr, "null argument");
+  CFD_CUDA(cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  CFD_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  c->ipc_opened.push_back(p);
+  *devptr = p;
+  return CFD_OK;
+}
+extern "C" int cfd_peer_attach(cfd_ctx* c, int side, int what, void* devptr, int peer_ni, int peer_halo_w, int peer_halo_e) {
+  CFD_REQUIRE(c && devptr, "null argument");
+  CFD_REQUIRE(side == 0 || side == 1, "side must be 0 (west neighbour) or 1 (east neighbour)");
+  CFD_REQUIRE((side == 0 ? c->cfg.halo_w : c->cfg.halo_e) > 0, "this context has no halo (no neighbour) on that side");
+  CFD_REQUIRE(what == CFD_IPC_FLAGS || ipc_target(c, what), "not a plain field of this context (or CFD_IPC_FLAGS)");
+  CFD_REQUIRE(peer_ni > 0 && peer_halo_w >= 0 && peer_halo_e >= 0, "bad neighbour extents");
+  CFD_REQUIRE(side == 0 ? peer_halo_e >= 1 : peer_halo_w >= 1, "the neighbour has no halo line facing this context");
+  CFD_CUDA(cudaSetDevice(c->device));
+  cudaPointerAttributes at;
+  CFD_CUDA(cudaPointerGetAttributes(&at, devptr));
+  if (at.type == cudaMemoryTypeDevice && at.device != c->device) {   // same process, other GPU: map it
+    int can = 0;
+    CFD_CUDA(cudaDeviceCanAccessPeer(&can, c->device, at.device));
+    CFD_REQUIRE(can, "the neighbour's GPU is not peer-accessible from this one");
+    cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CFD_CUDA(e);
+    (void)cudaGetLastError();
+  }
+  c->peer_ni[side] = peer_ni;
+  c->peer_hw[side] = peer_halo_w;
+  // where my edge line lands in the neighbour's arrays: its first east halo line / its last west halo line
+  c->peer_halo_line[side] = side == 0 ? peer_ni - peer_halo_e : peer_halo_w - 1;
+  if (what == CFD_IPC_FLAGS) c->peer_flags[side] = (int*)devptr;
+  else c->peer_field[side][what] = (double*)devptr;
+  c->peer_attached[side] = c->peer_flags[side] != nullptr;
+  return CFD_OK;
+}
+extern "C" int cfd_peer_detach(cfd_ctx* c) {
+  CFD_REQUIRE(c, "null context");
+  for (int sd = 0; sd < 2; ++sd) {
+    c->peer_attached[sd] = false;
+    c->peer_flags[sd] = nullptr;
+    for (auto& pf : c->peer_field[sd]) pf = nullptr;
+  }
+  return CFD_OK;
+}
+extern "C" int cfd_halo_push(cfd_ctx* c, int nfields, const int* fields, const int* w, const int* e) {
+  CFD_ENTER(c);
+  CFD_REQUIRE(fields && w && e && nfields >= 1 && nfields <= 4, "cfd_halo_push: 1..4 fields");
+  if (!c->peer_attached[0] && !c->peer_attached[1]) return CFD_OK;
+  return cfd_launch_halo_push(c, nfields, fields, w, e);
+}
+extern "C" int cfd_sweeps_single_launch(cfd_ctx* c, int* yes) {
+  CFD_REQUIRE(c && yes, "null argument");
+  *yes = cfd_flow_eligible(c) ? 1 : 0;
+  return CFD_OK;
+}
+extern "C" int cfd_peer_status(cfd_ctx* c, int* aborted) {
+  CFD_REQUIRE(c && aborted, "null argument");
+  CFD_CUDA(cudaSetDevice(c->device));
+  CFD_CUDA(cudaMemcpyAsync(aborted, c->flags + c->L.ni + CFD_FLAG_ABORT, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CFD_CUDA(cudaStreamSynchronize(c->stream));
+  return CFD_OK;
+}
+
 extern "C" int cfd_lisolv(cfd_ctx* c, int istart, int jstart, int field) {
   CFD_REQUIRE(c, "null context");
   int rc = check_field(c, field);
@@ -604,16 +718,12 @@ static int read_res(cfd_ctx* c, int eq, double* out) {
 static int stage_u(cfd_ctx* c) {
   int rc;
   if ((rc = asm_u(c))) return rc;
-  for (int n = 0; n < c->cfg.nswp[CFD_EQ_U]; ++n)
-    if ((rc = full_sweep(c, 3, 2, CFD_U, 0))) return rc;
-  return CFD_OK;
+  return sweeps(c, 3, 2, CFD_U, c->cfg.nswp[CFD_EQ_U], 0);
 }
 static int stage_v(cfd_ctx* c) {
   int rc;
   if ((rc = asm_v(c))) return rc;
-  for (int n = 0; n < c->cfg.nswp[CFD_EQ_V]; ++n)
-    if ((rc = full_sweep(c, 2, 3, CFD_V, 0))) return rc;
-  return CFD_OK;
+  return sweeps(c, 2, 3, CFD_V, c->cfg.nswp[CFD_EQ_V], 0);
 }
 static int stage_p(cfd_ctx* c) {
   int rc;
@@ -621,26 +731,21 @@ static int stage_p(cfd_ctx* c) {
   if (c->cfg.nswp[CFD_EQ_P] == 0) {   // pp(:,:) = 0 with no sweep to fold it into
     CFD_CUDA(cudaMemsetAsync(c->field[CFD_PP], 0, (size_t)c->L.ni * c->L.LD * sizeof(double), c->stream));
   }
-  for (int n = 0; n < c->cfg.nswp[CFD_EQ_P]; ++n)
-    if ((rc = full_sweep(c, 2, 2, CFD_PP, n == 0))) return rc;
+  if ((rc = sweeps(c, 2, 2, CFD_PP, c->cfg.nswp[CFD_EQ_P], 1))) return rc;
   return cfd_launch_correct(c, nullptr);
 }
 
 static int stage_scalar_teach(cfd_ctx* c, int eq, int field, int nsw) {
   int rc;
   if ((rc = cfd_launch_teach_scalar(c, eq))) return rc;
-  for (int n = 0; n < nsw; ++n)
-    if ((rc = full_sweep(c, 2, 2, field, 0))) return rc;
-  return CFD_OK;
+  return sweeps(c, 2, 2, field, nsw, 0);
 }
 
 static int stage_t(cfd_ctx* c) {
   int rc;
   if (is_teach(c)) return stage_scalar_teach(c, CFD_EQ_T, CFD_T, c->turb.nswpt);
   if ((rc = cfd_launch_general_assemble(c, 3))) return rc;
-  for (int n = 0; n < c->cfg.nswp[CFD_EQ_T]; ++n)
-    if ((rc = full_sweep(c, 2, 2, CFD_T, 0))) return rc;
-  return CFD_OK;
+  return sweeps(c, 2, 2, CFD_T, c->cfg.nswp[CFD_EQ_T], 0);
 }
 extern "C" int cfd_calct(cfd_ctx* c, double* resort) {
   CFD_REQUIRE(c, "null context");

@@ -90,6 +90,50 @@ struct SweepParams {
   double* out;               // solution array (same layout as phi); phi itself unless a spike vector is built
 };
 
+// All colour passes of an equation's sweeps in one launch (tdma_flow_kernels.cu).
+struct FlowParams {
+  Layout L;
+  int npass;                 // colour passes in this launch; pass p has colour (colour0 + p) & 1 and epoch epoch0 + p
+  int colour0;
+  int i_first[2], nlines[2]; // per colour: first local line (0-based) and number of lines (every second line)
+  int jlo, jhi;              // unknowns along a line
+  int first;                 // pp = 0 folded into the first sweep: pass 0 takes both neighbours as zero, passes 0 and 1 the end values
+  const double* coef;        // interleaved coefficient block (array `an`)
+  double* phi;
+  int* flags;                // per local line: epoch of the last pass that finished it
+  int epoch0;
+  int wait_lo[2], wait_hi[2];   // per colour: local lines of that colour whose flag a later pass may wait for (owned lines and,
+                                // with a neighbouring GPU attached, the halo line that GPU rewrites)
+  int edge_line[2];          // first / last owned line if it is swept and a neighbour is attached on that side, else -1
+  double* peer_phi[2];       // that line's image in the neighbour's array (its halo line), peer memory
+  int* peer_flag[2];         // the neighbour's flag of that halo line
+  int* peer_ready[2];        // the neighbour's "ready" slot for this GPU (written once at kernel start)
+  const int* ready;          // my ready slots [from west, from east]
+  int halo_line[2];          // my west / east halo line that the neighbour rewrites during this launch (-1: none) ...
+  int halo_last[2];          // ... and the epoch of the last pass that does: the launch does not end before it has arrived
+  int* abort_flag;
+};
+
+struct HaloPush {
+  int nmsg;
+  const double* src[8];
+  double* dst[8];
+  long long count[8];        // doubles
+  int xe;                    // exchange epoch
+  int* peer_xready[2];       // neighbour's slots for this GPU
+  int* peer_xdata[2];
+  const int* xready;         // my slots [from west, from east]
+  const int* xdata;
+  int* abort_flag;
+};
+
+// slots behind the ni per-line flags of a context's flag block
+#define CFD_FLAG_XDATA 0         /* [2] halo-push data marks from the west / east neighbour */
+#define CFD_FLAG_XREADY 2        /* [2] halo-push ready marks */
+#define CFD_FLAG_SWEEP_READY 4   /* [2] sweep-kernel ready marks */
+#define CFD_FLAG_ABORT 6
+#define CFD_FLAG_SLOTS 8
+
 }  // namespace cfd
 
 // ---- error plumbing -----------------------------------------------------------------------------------
@@ -143,6 +187,15 @@ struct cfd_ctx {
   bool tfast_ready;
   bool exact_assembly;              // bit-exact assembly kernels (sequential-order mode, or CFD_B200_EXACT_ASSEMBLY=1)
   long long launches;               // kernels launched by this context so far (cfd_launch_count)
+  // sweeps ordered by per-line flags, i-slab neighbours over peer memory (tdma_flow_kernels.cu)
+  int* flags;                       // ni per-line epochs + CFD_FLAG_SLOTS handshake slots (its own cudaMalloc: exportable)
+  int epoch;                        // epoch of the next colour pass (the same on every rank of an SPMD run)
+  int xepoch;                       // halo-push counter
+  bool peer_attached[2];            // west / east neighbour's memory is mapped
+  double* peer_field[2][CFD_FIELD_COUNT];
+  int* peer_flags[2];
+  int peer_ni[2], peer_hw[2], peer_halo_line[2];
+  std::vector<void*> ipc_opened;    // mappings made by cfd_ipc_open (closed by cfd_destroy)
   int num_sms;                      // SM count of THIS context's device (persistent grids are sized from it)
   int smem_optin;                   // largest dynamic shared memory a block may opt into on this device
   std::vector<const void*> smem_raised;   // kernels whose dynamic shared-memory limit was raised for this context's device
@@ -187,4 +240,7 @@ int cfd_launch_teach_assemble(cfd_ctx* c, int which);
 int cfd_launch_teach_wall(cfd_ctx* c, int which);
 int cfd_launch_teach_scalar(cfd_ctx* c, int eq);
 int cfd_launch_teach_props(cfd_ctx* c);
+bool cfd_flow_eligible(const cfd_ctx* c);
+int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int nsweeps, int first);
+int cfd_launch_halo_push(cfd_ctx* c, int nfields, const int* fields, const int* w, const int* e);
 int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double* partial, const double* uinc);

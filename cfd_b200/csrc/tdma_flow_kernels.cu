@@ -1,0 +1,527 @@
+// tdma_flow_kernels.cu -- all colour passes of an equation's line sweeps in ONE persistent launch, ordered by per-line
+// flags instead of kernel boundaries, with the slab-edge lines handed to the neighbouring GPUs over peer memory.
+//
+// The reference runs `nswp` W->E sweeps of lisolv per equation (cavity_fvm.f90:189-191, 287-289, 343-345); with
+// red/black lines that is 2*nswp colour passes.  k_tdma_tma (tdma_kernels.cu) runs one pass per launch: 18 launches per
+// outer iteration, each starting with an empty ring and a cold HBM pipe, and -- on several GPUs -- each followed by a
+// host-issued halo exchange.  Here:
+//   * one launch walks through all passes; a line of pass p may start as soon as its two neighbour lines (other colour)
+//     have finished pass p-1.  Every finished line publishes `flags[line] = epoch of the pass` (release); the producer
+//     warp acquires the two neighbour flags before it streams the line's first slice.  No grid-wide barrier: blocks
+//     drift from pass to pass and the copy ring never drains.
+//   * i-slabs over several GPUs: the first / last owned line of a slab is also stored into the neighbour's halo line
+//     (plain global stores into peer-mapped memory over NVLink), followed by a system-scope release of the neighbour's
+//     flag for that halo line -- to the neighbour its halo line looks like any other line of the previous pass.  The edge
+//     lines are solved FIRST in every pass, so the transfer has a whole pass to arrive.  Every bulk copy (TMA) of this
+//     kernel reads this GPU's memory only; remote traffic is stores and flag polls.
+//   * a neighbour may only store into a halo line once this GPU has launched its own sweep kernel (everything that read
+//     the halo before is then complete in stream order): each launch first tells both neighbours "ready for epoch e0",
+//     and the first remote store of a launch waits for the neighbour's ready mark.
+// Same arithmetic as k_tdma_tma (same chunked elimination, same cyclic reduction): the two paths give identical bits.
+// All waits are bounded; a timeout raises the context's abort flag instead of hanging the GPU.
+#include "common.cuh"
+#include "tma.cuh"
+
+namespace cfd {
+
+__device__ __forceinline__ double rcp_nr(double x) {   // == rcp() of tdma_kernels.cu
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = fma(fma(-x, r, 1.0), r, r);
+  r = fma(fma(-x, r, 1.0), r, r);
+  return r;
+}
+
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Poll until *p >= want (wrap-safe) or about a second has passed; false = timed out (abort flag raised).
+__device__ __forceinline__ bool wait_flag(const int* p, int want, int* abort_flag) {
+  if (ld_acquire_sys(p) - want >= 0) return true;
+  const long long t0 = clock64();
+  for (;;) {
+    __nanosleep(40);
+    if (ld_acquire_sys(p) - want >= 0) return true;
+    if (clock64() - t0 > 4000000000LL || *(volatile int*)abort_flag) {   // ~2 s at 2 GHz
+      atomicExch(abort_flag, 1);
+      return false;
+    }
+  }
+}
+
+// position in the per-block work order -> line of the colour: slab-edge lines (first, last) come first
+__device__ __forceinline__ int flow_line(int idx, int n) { return idx == 0 ? 0 : (idx == 1 ? n - 1 : idx - 1); }
+
+template <int M, int BMAX, int NC>
+__global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const int S) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int T = P.L.T;
+  const long long LD = P.L.LD;
+  const int tid = threadIdx.x;
+  constexpr int nc = NC;
+  const int SW = (nc + 2) * T;
+  double* ring = reinterpret_cast<double*>(smem_raw);
+  double* bufA = ring + (size_t)S * SW;
+  double* bufB = bufA + 3 * T;
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(bufB + 3 * T);
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S);
+  const int ncw = T / 32;
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, ncw);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    // tell both neighbours that every earlier reader of this GPU's halo lines is done (stream order): they may store
+    if (blockIdx.x == 0) {
+      if (P.peer_ready[0]) st_release_sys(P.peer_ready[0], P.epoch0);
+      if (P.peer_ready[1]) st_release_sys(P.peer_ready[1], P.epoch0);
+    }
+  }
+  __syncthreads();
+
+  if (tid >= T) {
+    // ---------------- producer warp ---------------------------------------------------------------------
+    if (tid == T) {
+      const unsigned slice_bytes = (unsigned)(T * sizeof(double));
+      unsigned rs = 0, rph = 0;
+      for (int p = 0; p < P.npass; ++p) {
+        const int c = (P.colour0 + p) & 1, oc = c ^ 1;
+        const bool zeroEW = P.first && p == 0;
+        const unsigned tx = slice_bytes * ((unsigned)nc + (zeroEW ? 0u : 2u));
+        const int nl = P.nlines[c];
+        for (int idx = blockIdx.x; idx < nl; idx += gridDim.x) {
+          const int i0 = P.i_first[c] + 2 * flow_line(idx, nl);
+          if (p > 0) {
+            // the neighbour lines were rewritten by the previous pass: wait until both are complete
+            const int want = P.epoch0 + p - 1;
+            if (i0 - 1 >= P.wait_lo[oc] && i0 - 1 <= P.wait_hi[oc]) wait_flag(P.flags + (i0 - 1), want, P.abort_flag);
+            if (i0 + 1 >= P.wait_lo[oc] && i0 + 1 <= P.wait_hi[oc]) wait_flag(P.flags + (i0 + 1), want, P.abort_flag);
+            asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes (other SMs / peer GPU) -> bulk-copy reads
+          }
+          const double* csrc = P.coef + (long long)i0 * P.L.cSL;
+          const double* esrc = P.phi + (long long)(i0 + 1) * LD;
+          const double* wsrc = P.phi + (long long)(i0 - 1) * LD;
+          for (int k = 0; k < M; ++k) {
+            const unsigned s = rs, ph = rph;
+            if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+            mbar_wait(empty0 + 8 * s, ph ^ 1u);
+            const unsigned fb = full0 + 8 * s;
+            const unsigned dst = smem_u32(ring + (size_t)s * SW);
+            mbar_expect_tx(fb, tx);
+            tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, nc * slice_bytes, fb);
+            if (!zeroEW) {
+              tma_load_1d(dst + nc * slice_bytes, esrc + (size_t)k * T, slice_bytes, fb);
+              tma_load_1d(dst + (nc + 1) * slice_bytes, wsrc + (size_t)k * T, slice_bytes, fb);
+            }
+          }
+        }
+      }
+      // The neighbours' last stores into my halo lines must have landed before this launch ends (what follows on the
+      // stream reads them).  Their edge lines are solved first in every pass, so this is normally already true.
+      if (blockIdx.x == 0) {
+        for (int sd = 0; sd < 2; ++sd)
+          if (P.halo_line[sd] >= 0) wait_flag(P.flags + P.halo_line[sd], P.halo_last[sd], P.abort_flag);
+      }
+    }
+    return;
+  }
+
+  // ---------------- consumers ---------------------------------------------------------------------------
+  const int t = tid, lane = tid & 31;
+  const int j0base = t * M;
+  const unsigned T8 = (unsigned)T * 8u, stage_bytes = (unsigned)SW * 8u, ring32 = smem_u32(ring) + (unsigned)t * 8u;
+  const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.jhi + 1, M, T);
+  unsigned rs = 0, rph = 0;
+  bool peer_open[2] = {false, false};   // this launch has seen the neighbour's ready mark
+  for (int p = 0; p < P.npass; ++p) {
+    const int c = (P.colour0 + p) & 1;
+    const bool zeroEW = P.first && p == 0, zero_ends = P.first && p < 2;
+    const int nl = P.nlines[c];
+    const int epoch = P.epoch0 + p;
+    for (int idx = blockIdx.x; idx < nl; idx += gridDim.x) {
+      const int i0 = P.i_first[c] + 2 * flow_line(idx, nl);
+      double* phi = P.phi + (long long)i0 * LD;
+      // Dirichlet end values phi(i, jstart-1), phi(i, nj): never written by a sweep, so plain loads are safe at any time
+      double bS = 0.0, bN = 0.0;
+      if (!zero_ends) {
+        bS = __ldg(phi + q_s);
+        bN = __ldg(phi + q_n);
+      }
+      double ca[M], cc[M], cf[M];
+#pragma unroll
+      for (int k = 0; k < M; ++k) {
+        const unsigned s = rs, ph = rph;
+        if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+        mbar_wait(full0 + 8 * s, ph);
+        const unsigned sl = ring32 + s * stage_bytes;
+        double a = lds_f64(sl), b = lds_f64(sl + T8), d = 1.0;
+        unsigned sr = sl + 2 * T8;
+        if (nc == 6) {
+          d = lds_f64(sr);
+          sr += T8;
+        }
+        double cv = lds_f64(sr + 2 * T8);
+        if (!zeroEW) {
+          cv = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), cv);
+          cv = fma(lds_f64(sr), lds_f64(sr + 3 * T8), cv);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty0 + 8 * s);
+        const int j0 = j0base + k;
+        if (!(j0 >= P.jlo && j0 <= P.jhi)) {
+          a = 0.0;
+          b = 0.0;
+          d = 1.0;
+          cv = (j0 == P.jlo - 1) ? bS : ((j0 == P.jhi + 1) ? bN : 0.0);
+        }
+        if (k == 0) {
+          const double inv = rcp_nr(d);
+          ca[0] = a * inv;
+          cc[0] = cv * inv;
+          cf[0] = b * inv;
+        } else {
+          const double inv = rcp_nr(fma(-b, ca[k > 0 ? k - 1 : 0], d));
+          ca[k] = a * inv;
+          cc[k] = fma(b, cc[k > 0 ? k - 1 : 0], cv) * inv;
+          cf[k] = b * cf[k > 0 ? k - 1 : 0] * inv;
+        }
+      }
+#pragma unroll
+      for (int k = M - 3; k >= 0; --k) {
+        cc[k] = fma(ca[k], cc[k + 1], cc[k]);
+        cf[k] = fma(ca[k], cf[k + 1], cf[k]);
+        ca[k] = ca[k] * ca[k + 1];
+      }
+      double l, u, r;
+      if (M == 1) {
+        l = cf[0];
+        u = ca[0];
+        r = cc[0];
+      } else {
+        bufB[t] = cc[0];
+        bufB[T + t] = cf[0];
+        bufB[2 * T + t] = ca[0];
+        consumer_sync(T);
+        double ncc = 0.0, ncf = 0.0, ng = 0.0;
+        if (t + 1 < T) {
+          ncc = bufB[t + 1];
+          ncf = bufB[T + t + 1];
+          ng = bufB[2 * T + t + 1];
+        }
+        const double inv = rcp_nr(fma(-ca[M - 1], ncf, 1.0));
+        l = cf[M - 1] * inv;
+        u = ca[M - 1] * ng * inv;
+        r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
+      }
+      double* cur = bufA;
+      double* nxt = bufB;
+      cur[t] = l;
+      cur[T + t] = u;
+      cur[2 * T + t] = r;
+      consumer_sync(T);
+      for (int sft = 1; sft < T; sft <<= 1) {
+        double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
+        if (t - sft >= 0) {
+          lm = cur[t - sft];
+          um = cur[T + t - sft];
+          rm = cur[2 * T + t - sft];
+        }
+        if (t + sft < T) {
+          lp = cur[t + sft];
+          up = cur[T + t + sft];
+          rp = cur[2 * T + t + sft];
+        }
+        const double inv = rcp_nr(fma(-l, um, fma(-u, lp, 1.0)));
+        r = fma(l, rm, fma(u, rp, r)) * inv;
+        l = l * lm * inv;
+        u = u * up * inv;
+        nxt[t] = l;
+        nxt[T + t] = u;
+        nxt[2 * T + t] = r;
+        consumer_sync(T);
+        double* tmp = cur;
+        cur = nxt;
+        nxt = tmp;
+      }
+      const double xe = r;
+      const double xp = (t > 0) ? cur[2 * T + t - 1] : 0.0;
+      // a slab-edge line also goes into the neighbour's halo line (peer memory)
+      const int side = (i0 == P.edge_line[0]) ? 0 : ((i0 == P.edge_line[1]) ? 1 : -1);
+      double* rphi = nullptr;
+      if (side >= 0 && P.peer_phi[side]) {
+        if (!peer_open[side]) {
+          // the neighbour must have launched this same sweep kernel (its earlier readers of the halo are then done)
+          if (t == 0) wait_flag(P.ready + side, P.epoch0, P.abort_flag);
+          consumer_sync(T);
+          peer_open[side] = true;
+        }
+        rphi = P.peer_phi[side];
+      }
+#pragma unroll
+      for (int k = 0; k < M; ++k) {
+        const int j0 = j0base + k;
+        if (j0 >= P.jlo && j0 <= P.jhi) {
+          const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
+          phi[k * T + t] = xk;
+          if (rphi) rphi[k * T + t] = xk;
+        }
+      }
+      if (rphi) __threadfence_system(); else __threadfence();
+      consumer_sync(T);   // all stores of the line are ordered before the flag; the PCR buffers are free again
+      if (t == 0) {
+        st_release_sys(P.flags + i0, epoch);
+        if (rphi) st_release_sys(P.peer_flag[side], epoch);
+      }
+    }
+  }
+}
+
+// ---- halo push over peer memory: the lines a neighbour needs go straight into its halo lines --------------------------
+// Handshake per call (xe = the context's exchange counter, the same on both sides because both run the same call
+// sequence): (1) tell each neighbour "my earlier readers of the halo are done, you may write" (ready = xe), (2) wait
+// for the neighbour's ready, (3) store the lines, system fence, (4) release "data = xe" at the neighbour, (5) wait for
+// both neighbours' data marks.  One block.
+__global__ void __launch_bounds__(1024, 1) k_halo_push(const HaloPush H) {
+  __shared__ int ok;
+  if (threadIdx.x == 0) {
+    ok = 1;
+    for (int s = 0; s < 2; ++s)
+      if (H.peer_xready[s]) st_release_sys(H.peer_xready[s], H.xe);
+    for (int s = 0; s < 2; ++s)
+      if (H.peer_xready[s] && !wait_flag(H.xready + s, H.xe, H.abort_flag)) ok = 0;
+  }
+  __syncthreads();
+  if (ok) {
+    for (int m = 0; m < H.nmsg; ++m) {
+      const double* __restrict__ src = H.src[m];
+      double* __restrict__ dst = H.dst[m];
+      const long long n2 = H.count[m] >> 1;    // LD is even (T multiple of 32): whole double2 transfers
+      const double2* s2 = reinterpret_cast<const double2*>(src);
+      double2* d2 = reinterpret_cast<double2*>(dst);
+      for (long long q = threadIdx.x; q < n2; q += blockDim.x) d2[q] = s2[q];
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s)
+      if (H.peer_xdata[s]) st_release_sys(H.peer_xdata[s], H.xe);
+    for (int s = 0; s < 2; ++s)
+      if (H.peer_xdata[s]) wait_flag(H.xdata + s, H.xe, H.abort_flag);
+  }
+}
+
+// a slab that has no line to solve in this call still owes its neighbours the "ready" mark of the launch
+__global__ void k_flow_ready(int* r0, int* r1, int epoch0) {
+  if (r0) st_release_sys(r0, epoch0);
+  if (r1) st_release_sys(r1, epoch0);
+}
+
+template <int M>
+static cudaError_t launch_flow_m(cfd_ctx* c, const FlowParams& P, int nblocks, int S, size_t smem) {
+  const int nthreads = P.L.T + 32;
+  void* args[2] = {(void*)&P, (void*)&S};
+  cudaError_t e;
+  // cooperative launch: every block must be resident, since blocks wait for lines other blocks publish
+#define LAUNCH_FLOW(NCV)                                                                                        \
+  {                                                                                                             \
+    e = cfd_raise_smem(c, k_tdma_flow<M, 352, NCV>);                                                            \
+    if (e == cudaSuccess)                                                                                       \
+      e = cudaLaunchCooperativeKernel((const void*)k_tdma_flow<M, 352, NCV>, dim3(nblocks), dim3(nthreads), args, \
+                                      smem, c->stream);                                                         \
+  }
+  if (P.L.nc == 5) LAUNCH_FLOW(5) else LAUNCH_FLOW(6)
+#undef LAUNCH_FLOW
+  return e;
+}
+
+}  // namespace cfd
+
+using namespace cfd;
+
+// True when cfd_launch_sweeps_flow can take this context: red/black order, lines in one piece (no j-slab), a layout
+// that fits the 352-thread build of the TMA-staged solver.
+bool cfd_flow_eligible(const cfd_ctx* c) {
+  static int use = -1;
+  if (use < 0) {
+    const char* e = getenv("CFD_B200_FLOW");
+    use = e ? atoi(e) : 1;
+  }
+  const char* tma = getenv("CFD_B200_TDMA_TMA");
+  if (tma && atoi(tma) == 0) return false;
+  // an i-slab needs its neighbours attached: without them the halo lines change between passes by host-issued
+  // exchanges, which only the one-pass-per-launch path can interleave
+  const bool peers_ok = (c->cfg.halo_w == 0 || c->peer_attached[0]) && (c->cfg.halo_e == 0 || c->peer_attached[1]);
+  return use && c->cfg.order == CFD_ORDER_REDBLACK && c->cfg.halo_s == 0 && c->cfg.halo_n == 0 && c->cfg.joff == 0 &&
+         c->L.T >= 128 && c->L.T + 32 <= 352 && c->flags != nullptr && peers_ok;
+}
+
+// nsweeps red/black sweeps (2*nsweeps colour passes) of `phi` over the current coefficients, one launch.
+int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int nsweeps, int first) {
+  if (nsweeps <= 0) return CFD_OK;
+  const int epoch0 = c->epoch;
+  c->epoch += 2 * nsweeps;          // advanced on every rank alike, whether or not this slab has lines to solve
+  const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
+  const int own_lo = c->cfg.goff + c->cfg.halo_w + 1, own_hi = c->cfg.goff + c->L.ni - c->cfg.halo_e;   // global, 1-based
+  int glo = own_lo, ghi = own_hi;
+  if (glo < istart) glo = istart;
+  if (ghi > NI - 1) ghi = NI - 1;
+  FlowParams P{};
+  P.L = c->L;
+  P.npass = 2 * nsweeps;
+  P.colour0 = 0;
+  for (int col = 0; col < 2; ++col) {
+    const int g0 = glo + ((((glo - istart) & 1) != col) ? 1 : 0);
+    if (g0 > ghi) {
+      P.i_first[col] = 0;
+      P.nlines[col] = 0;
+    } else {
+      P.i_first[col] = g0 - 1 - c->cfg.goff;
+      P.nlines[col] = (ghi - g0) / 2 + 1;
+    }
+    // lines of this colour whose flag another pass may wait for: the owned ones, plus a halo line next to an owned
+    // line when the neighbouring slab updates it (it lies inside the global sweep range istart .. NI-1)
+    int lo = P.i_first[col], hi = P.i_first[col] + 2 * (P.nlines[col] - 1);
+    if (P.nlines[col] == 0) { lo = 1; hi = 0; }
+    const int gw = own_lo - 1, ge = own_hi + 1;                         // global numbers of the adjacent halo lines
+    if (c->cfg.halo_w > 0 && c->peer_attached[0] && gw >= istart && ((gw - istart) & 1) == col) {
+      const int l = gw - 1 - c->cfg.goff;
+      if (P.nlines[col] == 0) { lo = hi = l; } else if (l < lo) lo = l;
+    }
+    if (c->cfg.halo_e > 0 && c->peer_attached[1] && ge <= NI - 1 && ((ge - istart) & 1) == col) {
+      const int l = ge - 1 - c->cfg.goff;
+      if (hi < lo) { lo = hi = l; } else if (l > hi) hi = l;
+    }
+    P.wait_lo[col] = lo;
+    P.wait_hi[col] = hi;
+  }
+  int jlo, jhi;
+  const int NJ = c->L.nj;
+  cfd_local_j_range(c, jstart - 1, NJ - 2, &jlo, &jhi);
+  if (P.nlines[0] + P.nlines[1] == 0 || jhi < jlo) {
+    int* r[2] = {nullptr, nullptr};
+    for (int s = 0; s < 2; ++s)
+      if (c->peer_attached[s]) r[s] = c->peer_flags[s] + c->peer_ni[s] + CFD_FLAG_SWEEP_READY + (1 - s);
+    if (r[0] || r[1]) {
+      k_flow_ready<<<1, 1, 0, c->stream>>>(r[0], r[1], epoch0);
+      ++c->launches;
+      CFD_CUDA(cudaGetLastError());
+    }
+    return CFD_OK;
+  }
+  P.jlo = jlo;
+  P.jhi = jhi;
+  P.first = first ? 1 : 0;
+  P.coef = c->field[CFD_AN];
+  P.phi = c->field[field];
+  P.flags = c->flags;
+  P.epoch0 = epoch0;
+  P.abort_flag = c->flags + c->L.ni + CFD_FLAG_ABORT;
+  P.ready = c->flags + c->L.ni + CFD_FLAG_SWEEP_READY;
+  for (int s = 0; s < 2; ++s) {
+    P.halo_line[s] = -1;
+    const int gh = s == 0 ? own_lo - 1 : own_hi + 1;       // the halo line next to my owned lines, global number
+    if (c->peer_attached[s] && (s == 0 ? c->cfg.halo_w : c->cfg.halo_e) > 0 && gh >= istart && gh <= NI - 1) {
+      const int ch = (gh - istart) & 1;                     // its colour; passes of that colour: p with (p & 1) == ch
+      const int plast = ((P.npass - 1) & 1) == ch ? P.npass - 1 : P.npass - 2;
+      P.halo_line[s] = gh - 1 - c->cfg.goff;
+      P.halo_last[s] = epoch0 + plast;
+    }
+  }
+  for (int s = 0; s < 2; ++s) {
+    P.edge_line[s] = -1;
+    P.peer_phi[s] = nullptr;
+    P.peer_flag[s] = nullptr;
+    P.peer_ready[s] = nullptr;
+    if (!c->peer_attached[s] || !c->peer_field[s][field]) continue;
+    // my first (s = 0) / last (s = 1) owned line, if the sweep updates it
+    const int g = s == 0 ? own_lo : own_hi;
+    const int peer_line = s == 0 ? c->peer_halo_line[0] : c->peer_halo_line[1];
+    P.peer_ready[s] = c->peer_flags[s] + c->peer_ni[s] + CFD_FLAG_SWEEP_READY + (1 - s);   // I am its east (s=0) / west (s=1) neighbour
+    if (g < glo || g > ghi) continue;
+    P.edge_line[s] = g - 1 - c->cfg.goff;
+    P.peer_phi[s] = c->peer_field[s][field] + (long long)peer_line * c->L.LD;
+    P.peer_flag[s] = c->peer_flags[s] + peer_line;
+  }
+  const size_t stage = (size_t)(c->L.nc + 2) * c->L.T * sizeof(double), pcr = (size_t)6 * c->L.T * sizeof(double);
+  int S = 16;
+  const char* es = getenv("CFD_B200_TDMA_STAGES");
+  if (es && atoi(es) > 0) S = atoi(es);
+  while (S > 1 && S * stage + pcr + 2 * S * 8 > 220 * 1024) --S;
+  const size_t smem = S * stage + pcr + 2 * (size_t)S * 8;
+  int nmax = P.nlines[0] > P.nlines[1] ? P.nlines[0] : P.nlines[1];
+  const int nblocks = nmax < c->num_sms ? nmax : c->num_sms;
+  cudaError_t e = cudaSuccess;
+  switch (c->L.M) {
+#define CFD_CASE(m) \
+  case m:           \
+    e = launch_flow_m<m>(c, P, nblocks, S, smem); \
+    break;
+    CFD_CASE(1) CFD_CASE(2) CFD_CASE(3) CFD_CASE(4) CFD_CASE(5) CFD_CASE(6) CFD_CASE(7) CFD_CASE(8)
+    CFD_CASE(9) CFD_CASE(10) CFD_CASE(11) CFD_CASE(12) CFD_CASE(13) CFD_CASE(14) CFD_CASE(15) CFD_CASE(16)
+#undef CFD_CASE
+    default:
+      cfd_set_error("unsupported M=%d", c->L.M);
+      return CFD_ERR_INVALID;
+  }
+  if (e != cudaSuccess) {
+    cfd_set_error("k_tdma_flow: %s", cudaGetErrorString(e));
+    return CFD_ERR_CUDA;
+  }
+  ++c->launches;
+  return CFD_OK;
+}
+
+// Push halo lines of up to 4 fields to the neighbouring slabs: `w` lines to the east neighbour's west halo (my last
+// owned lines), `e` lines to the west neighbour's east halo (my first owned lines); both sides wait for what they receive.
+int cfd_launch_halo_push(cfd_ctx* c, int nfields, const int* fields, const int* w, const int* e) {
+  HaloPush H{};
+  const int ni = c->L.ni, hw = c->cfg.halo_w, he = c->cfg.halo_e, nown = ni - hw - he;
+  const long long LD = c->L.LD;
+  int* fl = c->flags + ni;
+  H.xe = ++c->xepoch;
+  H.abort_flag = fl + CFD_FLAG_ABORT;
+  H.xready = fl + CFD_FLAG_XREADY;
+  H.xdata = fl + CFD_FLAG_XDATA;
+  for (int s = 0; s < 2; ++s) {
+    if (!c->peer_attached[s]) continue;
+    int* pf = c->peer_flags[s] + c->peer_ni[s];
+    H.peer_xready[s] = pf + CFD_FLAG_XREADY + (1 - s);
+    H.peer_xdata[s] = pf + CFD_FLAG_XDATA + (1 - s);
+  }
+  for (int k = 0; k < nfields; ++k) {
+    const int f = fields[k];
+    if (f < 0 || f >= CFD_FIELD_COUNT || !c->field[f] || cfd_is_coef_field(f)) {
+      cfd_set_error("cfd_halo_push: field %d is not a plain field of this context", f);
+      return CFD_ERR_INVALID;
+    }
+    if (c->peer_attached[0] && e[k] > 0) {            // my first owned lines -> west neighbour's east halo
+      if (!c->peer_field[0][f]) { cfd_set_error("cfd_halo_push: field %d has no west peer mapping", f); return CFD_ERR_INVALID; }
+      const int n = e[k];
+      H.src[H.nmsg] = c->field[f] + (long long)hw * LD;
+      H.dst[H.nmsg] = c->peer_field[0][f] + (long long)c->peer_halo_line[0] * LD;
+      H.count[H.nmsg++] = n * LD;
+    }
+    if (c->peer_attached[1] && w[k] > 0) {            // my last owned lines -> east neighbour's west halo
+      if (!c->peer_field[1][f]) { cfd_set_error("cfd_halo_push: field %d has no east peer mapping", f); return CFD_ERR_INVALID; }
+      const int n = w[k] < c->peer_hw[1] ? w[k] : c->peer_hw[1];
+      if (n > 0) {
+        H.src[H.nmsg] = c->field[f] + (long long)(hw + nown - n) * LD;
+        H.dst[H.nmsg] = c->peer_field[1][f] + (long long)(c->peer_hw[1] - n) * LD;
+        H.count[H.nmsg++] = n * LD;
+      }
+    }
+  }
+  k_halo_push<<<1, 1024, 0, c->stream>>>(H);
+  ++c->launches;
+  CFD_CUDA(cudaGetLastError());
+  return CFD_OK;
+}

@@ -268,6 +268,31 @@ def iteration_stages(nswp, solve_t=False):
     return st
 
 
+def peer_stages(stages):
+    """The stage list of `iteration_stages` for slabs whose neighbours are attached over peer memory: grouped NCCL
+    send/recv stages become one cfd_halo_push each, and the colour passes of an equation (with the exchange after each)
+    become one cfd_sweeps launch that hands the edge lines over from inside the kernel."""
+    out, k = [], 0
+    while k < len(stages):
+        st = stages[k]
+        if st[0] == "sweep":
+            name, istart, jstart, _, first = st[1:]
+            n = 0
+            while k < len(stages) and stages[k][0] == "sweep" and stages[k][1] == name:
+                n += 1
+                k += 1
+            out.append(("sweeps", name, istart, jstart, n // 2, first))
+            continue
+        if st[0] == "halo":
+            out.append(("push", ((st[1], st[2], st[3]),)))
+        elif st[0] == "halos":
+            out.append(("push", tuple(st[1])))
+        else:
+            out.append(st)
+        k += 1
+    return out
+
+
 class _E2EMixin:
     def e2e(self, steps):
         """bench.py's end-to-end leg: per step upload u,v,p slabs from pinned host memory, one outer
@@ -327,6 +352,8 @@ class SlabCavity(_E2EMixin):
         if stream is not None:
             self.ctx.set_stream(stream.cuda_stream)
         self.stages = iteration_stages(self.slab.nswp, getattr(self.slab, "solve_t", False))
+        self.peer = self._attach_peers()
+        self.pstages = peer_stages(self.stages) if self.peer else None
         self.overlap = os.environ.get("CFD_B200_OVERLAP", "0") != "0"   # measured: no gain at N=2
         self._comm_stream = None
         self.pref_owner = [r for r, (lo, hi) in enumerate(partition(nicv + 2, self.world)) if lo <= self.slab.ipref <= hi][0]
@@ -337,6 +364,59 @@ class SlabCavity(_E2EMixin):
 
     def _global_cells(self):
         return (self.slab.ni_global - 2) * (self.slab.nj - 2)
+
+    def _attach_peers(self):
+        """Map the neighbouring slabs' fields and flag blocks into this process (CUDA IPC over NVLink peer access), so
+        that halo lines travel as plain stores from inside the kernels instead of NCCL messages issued by the host
+        between kernels.  All ranks decide together: if any mapping fails everywhere falls back to the NCCL stages.
+        CFD_B200_PEER=0 forces the NCCL path."""
+        torch, dist, s, ctx = self.torch, self.dist, self.slab, self.ctx
+        if self.world == 1:
+            return False
+        names = ("u", "v", "p", "pp", "du") + (("t",) if getattr(s, "solve_t", False) else ())
+        mine, ok = None, os.environ.get("CFD_B200_PEER", "1") != "0"
+        if ok:
+            try:
+                mine = {"ni": s.ni, "hw": s.hw, "he": s.he, "host": os.uname().nodename,
+                        "h": {n: ctx.ipc_export(n) for n in names + ("flags",)}}
+            except Exception as e:                          # noqa: BLE001
+                self.peer_error, ok = repr(e), False
+        every = [None] * self.world
+        dist.all_gather_object(every, mine if ok else None)
+        ok = ok and all(x is not None and x["host"] == every[0]["host"] for x in every)
+        if ok:
+            try:
+                for side, r in ((0, self.rank - 1), (1, self.rank + 1)):
+                    if 0 <= r < self.world:
+                        for n in names + ("flags",):
+                            ptr = ctx.ipc_open(every[r]["h"][n])
+                            ctx.peer_attach(side, n, ptr, every[r]["ni"], every[r]["hw"], every[r]["he"])
+                ok = ctx.sweeps_single_launch()             # short lines keep the pass-by-pass solver, which needs the NCCL stages
+            except Exception as e:                          # noqa: BLE001
+                self.peer_error, ok = repr(e), False
+        agree = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN)
+        if int(agree.item()) != 1:
+            ctx.peer_detach()
+            return False
+        torch.cuda.synchronize()
+        dist.barrier()                                      # nobody pushes before everybody has attached
+        return True
+
+    def _iterate_peer(self, n=1):
+        s = self.slab
+        for _ in range(n):
+            for st in self.pstages:
+                if st[0] == "compute":
+                    st[1](s)
+                elif st[0] == "sweeps":
+                    s.ctx.sweeps(st[2], st[3], st[1], st[4], first=st[5])
+                elif st[0] == "push":
+                    s.ctx.halo_push(st[1])
+                else:
+                    if s.owner_of_pref:
+                        s.ppref.copy_(s.ppref_element())
+                    self.comm.broadcast(s.ppref, self.pref_owner)
 
     def enable_graph(self, stream):
         """Capture one outer iteration (kernels + NCCL halo exchanges) into a CUDA graph and replay it from then
@@ -364,6 +444,8 @@ class SlabCavity(_E2EMixin):
         self._iterate_eager(n)
 
     def _iterate_eager(self, n=1):
+        if self.peer:
+            return self._iterate_peer(n)
         s = self.slab
         for _ in range(n):
             for st in self.stages:

@@ -200,6 +200,36 @@ int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int f
    driver send the edge lines while the interior is still being solved. */
 int cfd_sweep_part(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first, int part);
 int cfd_correct(cfd_ctx* ctx, const double* ppref_device); /* cavity_fvm.f90:346-354; NULL = pp(ipref,jpref) */
+/* the `do n = 1, nswp; call lisolv(...)` loop of calcu / calcv / calcp (cavity_fvm.f90:189-191, 287-289, 343-345):
+   nsweeps red/black sweeps of `field` over the current coefficients.  Where the layout allows it (lines of 128..320
+   layout threads, whole lines per context) all 2*nsweeps colour passes run in ONE persistent launch ordered by per-line
+   completion flags instead of kernel boundaries; an i-slab whose neighbours are attached (cfd_peer_attach) also stores
+   its edge lines into the neighbours' halo lines from inside that launch.  Same bits as nsweeps x cfd_sweep(0), cfd_sweep(1). */
+int cfd_sweeps(cfd_ctx* ctx, int istart, int jstart, int field, int nsweeps, int first);
+
+/* ---- i-slab neighbours over peer memory (multi-GPU; no counterpart in the reference, which is serial) -------------
+   Every slab context exports its plain fields and its flag block (cfd_ipc_export: a 64-byte CUDA IPC handle), the
+   neighbouring ranks open them (cfd_ipc_open -> a device pointer valid in this process) and attach them
+   (cfd_peer_attach: side 0 = west neighbour, 1 = east neighbour; `what` = a cfd_field or CFD_IPC_FLAGS; the neighbour's
+   local extents tell where this context's edge lines land in its arrays).  In one process with several GPUs the
+   neighbour's own device pointers (cfd_field_device_view) can be attached directly.  After that
+     cfd_halo_push   stores the first `e[k]` / last `w[k]` owned lines of up to 4 fields into the west / east neighbour's
+                     halo lines and waits for the lines the neighbours store here: one small kernel, remote STORES and
+                     flag polls only -- replaces a grouped NCCL send/recv on the stream
+     cfd_sweeps      hands the edge lines over from inside the sweep kernel (above)
+   All ranks must issue the same sequence of cfd_sweeps / cfd_halo_push calls (the handshakes count calls).  Waits are
+   bounded (about two seconds); cfd_peer_status reports whether one ever timed out.  Loads by bulk copy (TMA) in
+   these kernels touch this GPU's memory only. */
+#define CFD_IPC_FLAGS (-1)
+int cfd_ipc_export(cfd_ctx* ctx, int what, void* handle64);
+int cfd_ipc_open(cfd_ctx* ctx, const void* handle64, void** devptr);
+int cfd_peer_attach(cfd_ctx* ctx, int side, int what, void* devptr, int peer_ni, int peer_halo_w, int peer_halo_e);
+int cfd_peer_detach(cfd_ctx* ctx);
+int cfd_halo_push(cfd_ctx* ctx, int nfields, const int* fields, const int* w, const int* e);
+int cfd_peer_status(cfd_ctx* ctx, int* aborted);
+/* *yes = 1 when cfd_sweeps runs as the single flag-ordered launch in this context (with its neighbours attached as they
+   are now): an i-slab driver may only drop its per-pass halo exchanges in that case */
+int cfd_sweeps_single_launch(cfd_ctx* ctx, int* yes);
 
 /* ---- TEACH family: k-epsilon model, energy equation, wall functions -------------------------------
    cfd_set_turbulence allocates te, ed, t, gen, gamh and switches on the wall-function branches of modu / modv

@@ -409,3 +409,35 @@ def test_lisolv_drop_in_on_host_assembled_coefficients(cfd, oracle, istart, jsta
     o.lisolv(istart, jstart, want)
     assert np.array_equal(g.download("pp"), want)
     g.close()
+
+
+@pytest.mark.parametrize("shape", [(130, 1030), (64, 4096), (40, 300), (301, 2200)])
+def test_sweeps_in_one_launch_equal_the_colour_passes_bitwise(cfd, oracle, shape):
+    """cfd_sweeps runs all colour passes of the `do n = 1, nswp; call lisolv` loop in one flag-ordered launch
+    (tdma_flow_kernels.cu); it must give the bits of the pass-by-pass launches, for a plain field and for pp with the
+    pp = 0 fold of the first sweep (cavity_fvm.f90:342)."""
+    o, g = make_pair(cfd, oracle, *shape, order="redblack")
+    _, h = make_pair(cfd, oracle, *shape, order="redblack")
+    randomise(o, g, 5)
+    randomise(o, h, 5)
+    for q in (g, h):
+        q.assemble_u()
+    g.sweeps(3, 2, "u", 3)
+    for n in range(3):
+        h.sweep(3, 2, "u", 0)
+        h.sweep(3, 2, "u", 1)
+    assert np.array_equal(g.download("u"), h.download("u"))
+    junk = np.asfortranarray(np.random.default_rng(9).random((g.ni, g.nj)))
+    for q in (g, h):
+        q.assemble_v()
+        q.assemble_p()
+        q.upload("pp", junk)                       # pp(:,:) = 0 is folded into the first sweep: old contents must not matter
+    g.sweeps(2, 2, "pp", 2, first=True)
+    for n in range(2):
+        h.sweep(2, 2, "pp", 0, first=(n == 0))
+        h.sweep(2, 2, "pp", 1, first=(n == 0))
+    a, b = g.download("pp"), h.download("pp")
+    assert np.array_equal(a[1:-1, 1:-1], b[1:-1, 1:-1])
+    assert not g.peer_status()
+    g.close()
+    h.close()

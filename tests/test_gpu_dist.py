@@ -85,10 +85,10 @@ def test_buoyancy_local_slabs_match_single_context(cfd, world, n):
     g.close()
 
 
-def _nccl_worker(rank, world, port, shape, q, kind="i"):
+def _nccl_worker(rank, world, port, shape, q, kind="i", peer=True):
     import torch
     import torch.distributed as dist
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), CFD_B200_PEER="1" if peer else "0")
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
@@ -103,20 +103,26 @@ def _nccl_worker(rank, world, port, shape, q, kind="i"):
             s = SlabCavity(*shape, reynolds=100.0)
         res = s.iterate(6)
         out = {n: s.gather_field(n) for n in ("u", "v", "p")}
+        used_peer = bool(getattr(s, "peer", False))
+        timed_out = s.ctx.peer_status()
         if rank == 0:
-            q.put((res, out))
+            q.put((res, out, used_peer, timed_out))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kind", ["i", "j", "teach", "buoyancy"])
-def test_nccl_slabs_match_single_context(cfd, kind):
+@pytest.mark.parametrize("kind,peer,shape", [("i", False, (96, 130)), ("j", False, (96, 130)), ("teach", False, (96, 130)),
+                                             ("buoyancy", False, (98, 98)), ("i", True, (96, 1024)),
+                                             ("teach", True, (98, 1026)), ("buoyancy", True, (1026, 1026))])
+def test_nccl_slabs_match_single_context(cfd, kind, peer, shape):
+    """One process per GPU.  peer=True: halo lines over peer memory (stores from inside the flag-ordered sweep kernels
+    and cfd_halo_push) -- lines of 1026 nodes, long enough for the TMA-staged kernels that path lives in; peer=False:
+    the grouped NCCL send/recv stages."""
     import torch
     import torch.multiprocessing as mp
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("needs at least 2 GPUs (run under gpurun --gpus 2)")
-    shape = (96, 130) if kind != "buoyancy" else (98, 98)
     if kind == "buoyancy":
         g = cfd.BuoyantCavity(*shape, order="redblack")
     elif kind == "teach":
@@ -133,10 +139,13 @@ def test_nccl_slabs_match_single_context(cfd, kind):
     sk.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, shape, q, kind)) for r in range(world)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, shape, q, kind, peer)) for r in range(world)]
     for p in procs:
         p.start()
-    res, out = q.get(timeout=300)
+    res, out, used_peer, timed_out = q.get(timeout=300)
+    assert not timed_out
+    if peer and kind != "j":
+        assert used_peer, "the peer-memory path was asked for but the ranks fell back to NCCL"
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
