@@ -367,35 +367,45 @@ def run_ours(args):
         out["parity_check"] = parity
 
     # ---- roofline of the dominant kernel (the red/black line solver), timed live with CUDA events ---------
+    # the launch the step itself makes: all 2*nswp colour passes of one equation (cfd_sweeps)
     ctxr = ctx0
+    nsw = 3
+    one_launch = ctxr.sweeps_single_launch()
     with torch.cuda.stream(stream):
+        ctxr.assemble_u()
+        ctxr.sweeps(3, 2, "u", nsw)                       # untimed: first use of a kernel loads its module
+        if world > 1:
+            barrier()
         evs = []
-        for _ in range(3):
+        for _ in range(5):
             ctxr.assemble_u()
-            for sw in range(3):
-                for col in (0, 1):
-                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    a.record(stream)
-                    ctxr.sweep(3, 2, "u", col)
-                    b.record(stream)
-                    evs.append((a, b))
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            ctxr.sweeps(3, 2, "u", nsw)
+            b.record(stream)
+            evs.append((a, b))
         torch.cuda.synchronize()
     t_launch = sum(a.elapsed_time(b) for a, b in evs) / len(evs) * 1e-3
-    cells_launch = ((NICV - 1) if world == 1 else NICV) / 2.0 * NJCV   # u-lines i=3..ni-1, half per colour pass
+    cells_launch = ((NICV - 1) if world == 1 else NICV) * NJCV * nsw   # u-lines i=3..ni-1, both colours, nsw sweeps
     achieved = SWEEP_BYTES_PER_CELL * cells_launch / t_launch / 1e9
+    kname = "k_tdma_flow" if one_launch else "k_tdma_tma"
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("k_tdma_tma", {}).get("dram_bytes_per_launch")
+            traffic = json.load(open(tp)).get(kname, {}).get("dram_bytes_per_launch")
+            if traffic is not None and not one_launch:
+                traffic *= 2 * nsw                         # the file holds one colour pass of k_tdma_tma
         except Exception:
             traffic = None
-    out["roofline"] = {"bound": "hbm", "kernel": "k_tdma_tma (one colour pass of a line sweep)",
+    out["roofline"] = {"bound": "hbm",
+                       "kernel": (f"{kname} (the {2 * nsw} colour passes of one equation's line sweeps"
+                                  + (", one flag-ordered launch)" if one_launch else ", one launch per pass)")),
                        "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                        "peak_source": peak_src, "traffic": traffic, "launch_ms": t_launch * 1e3,
                        "algorithmic_bytes_per_launch": SWEEP_BYTES_PER_CELL * cells_launch,
-                       "note": "algorithmic = 8 doubles/cell (6 coefficients + phi read, phi written; SURVEY 8d); the kernel "
-                               "itself moves 7 (equations are stored divided by ap), so frac can exceed the copy peak",
+                       "note": "algorithmic = 8 doubles/cell and sweep (6 coefficients + phi read, phi written; SURVEY 8d); the "
+                               "kernel itself moves 7 (equations are stored divided by ap), so frac can exceed the copy peak",
                        "whole_iteration": {"algorithmic_bytes_per_cell": BYTES_PER_CELL_ITER,
                                            "achieved": BYTES_PER_CELL_ITER * glups / world,
                                            "frac": BYTES_PER_CELL_ITER * glups / world / hbm_peak,

@@ -84,6 +84,10 @@ SYMBOLS = {
     "cfd_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_upload_noalloc": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_probe": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _dp]),
+    "cfd_extract_line": (C.c_int, [_vp, C.c_int, C.c_int, _dp, C.c_int]),
+    "cfd_extract_row": (C.c_int, [_vp, C.c_int, C.c_int, _dp, C.c_int]),
+    "cfd_centreline": (C.c_int, [_vp, C.c_int, C.c_int, _dp, C.c_int]),
+    "cfd_reference_pressure": (C.c_int, [_vp]),
     "cfd_field_device_view": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
     "cfd_layout_info": (C.c_int, [_vp, _ip, _ip, _ip]),
     "cfd_launch_count": (C.c_longlong, [_vp]),
@@ -139,6 +143,10 @@ SYMBOLS = {
     "cfd_heat2d_step_exact": (C.c_int, [_vp, C.c_int]),
     "cfd_heat2d_implicit_step": (C.c_int, [_vp, C.c_int]),
     "cfd_heat2d_implicit_step_exact": (C.c_int, [_vp, C.c_int]),
+    "cfd_heat_set_operator": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
+    "cfd_heat2d_apply": (C.c_int, [_vp, _vp, C.c_int]),
+    "cfd_heat2d_step_var": (C.c_int, [_vp, C.c_int]),
+    "cfd_heat2d_steady_gs": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _ip, _dp]),
     "cfd_heat_device_view": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_longlong), _ip]),
     "cfd_heat_synchronize": (C.c_int, [_vp]),
     "cfd_fdcav_create": (C.c_int, [C.POINTER(_vp), C.POINTER(CfdFdcavConfig)]),

@@ -173,6 +173,35 @@ class CavityFVM:
         check(self.lib.cfd_probe(self._h, FIELD_ID[name], i, j, C.byref(v)))
         return v.value
 
+    # -- post-processing on the device fields (no whole-field download) -------------------------------------
+    def extract_line(self, name: str, i: int) -> np.ndarray:
+        """A(i, 1:nj), local 1-based i."""
+        out = np.zeros(self.nj)
+        check(self.lib.cfd_extract_line(self._h, FIELD_ID[name], i, out.ctypes.data_as(C.POINTER(C.c_double)), self.nj))
+        return out
+
+    def extract_row(self, name: str, j: int) -> np.ndarray:
+        """A(1:ni, j)."""
+        out = np.zeros(self.ni)
+        check(self.lib.cfd_extract_row(self._h, FIELD_ID[name], j, out.ctypes.data_as(C.POINTER(C.c_double)), self.ni))
+        return out
+
+    def centreline_uc(self, imon: int) -> np.ndarray:
+        """uc(imon, 1:nj) of centred_vel (cavity_fvm.f90:416-430): the third column of uvel.txt (:600-603)."""
+        out = np.zeros(self.nj)
+        check(self.lib.cfd_centreline(self._h, 0, imon, out.ctypes.data_as(C.POINTER(C.c_double)), self.nj))
+        return out
+
+    def centreline_vc(self, jmon: int) -> np.ndarray:
+        """vc(1:ni, jmon): the third column of vvel.txt (cavity_fvm.f90:604-607)."""
+        out = np.zeros(self.ni)
+        check(self.lib.cfd_centreline(self._h, 1, jmon, out.ctypes.data_as(C.POINTER(C.c_double)), self.ni))
+        return out
+
+    def reference_pressure(self):
+        """p = p - p(ipref,jpref) and the corner values (cavity_fvm.f90:568-573), on the device."""
+        check(self.lib.cfd_reference_pressure(self._h))
+
     def device_view(self, name: str):
         base, stride, n = C.c_void_p(), C.c_longlong(), C.c_int()
         check(self.lib.cfd_field_device_view(self._h, FIELD_ID[name], C.byref(base), C.byref(stride), C.byref(n)))

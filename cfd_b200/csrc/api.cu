@@ -212,6 +212,8 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->seq_scratch = nullptr;
   c->launches = 0;
   c->flags = nullptr;
+  c->post_buf = nullptr;
+  c->post_n = 0;
   c->epoch = 1;
   c->xepoch = 0;
   for (int sd = 0; sd < 2; ++sd) {
@@ -340,6 +342,7 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   if (c->res_dev) cudaFree(c->res_dev);
   for (void* m : c->ipc_opened) cudaIpcCloseMemHandle(m);
   if (c->flags) cudaFree(c->flags);
+  if (c->post_buf) cudaFree(c->post_buf);
   if (c->seq_scratch) cudaFree(c->seq_scratch);
   delete c;
   return CFD_OK;

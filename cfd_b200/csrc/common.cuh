@@ -196,6 +196,8 @@ struct cfd_ctx {
   int* peer_flags[2];
   int peer_ni[2], peer_hw[2], peer_halo_line[2];
   std::vector<void*> ipc_opened;    // mappings made by cfd_ipc_open (closed by cfd_destroy)
+  double* post_buf;                 // result vector of the post-processing kernels (post_kernels.cu), sized on first use
+  size_t post_n;
   int num_sms;                      // SM count of THIS context's device (persistent grids are sized from it)
   int smem_optin;                   // largest dynamic shared memory a block may opt into on this device
   std::vector<const void*> smem_raised;   // kernels whose dynamic shared-memory limit was raised for this context's device

@@ -19,6 +19,9 @@ struct cfd_heat {
   int cur;
   long long steps_done;
   double* thomas;      // implicit steps: e_x[nx], temp_x[nx], e_y[ny], temp_y[ny] of the forward sweep (constant)
+  double* op[5];       // variable-conductivity operator: aw, ae, as, an (fdm2d_steady_heat_cond.f90:176-179) and QDOT at the nodes
+  double* gs_partial;  // Gauss-Seidel: per-block partial sums of (x1-x2)**2, then the total
+  int gs_blocks;
 };
 
 namespace cfd {
@@ -442,6 +445,9 @@ extern "C" int cfd_heat_create(cfd_heat** out, const cfd_heat_config* cfg) {
   h->steps_done = 0;
   h->buf[0] = h->buf[1] = nullptr;
   h->thomas = nullptr;
+  for (auto& o : h->op) o = nullptr;
+  h->gs_partial = nullptr;
+  h->gs_blocks = 0;
   const size_t bytes = (size_t)cfg->nx * cfg->ny * sizeof(double);
   for (int b = 0; b < 2; ++b) {
     if (cudaMalloc(&h->buf[b], bytes) != cudaSuccess) {
@@ -461,6 +467,8 @@ extern "C" int cfd_heat_destroy(cfd_heat* h) {
   cudaDeviceSynchronize();
   for (int b = 0; b < 2; ++b) if (h->buf[b]) cudaFree(h->buf[b]);
   if (h->thomas) cudaFree(h->thomas);
+  for (auto& o : h->op) if (o) cudaFree(o);
+  if (h->gs_partial) cudaFree(h->gs_partial);
   delete h;
   return CFD_OK;
 }
@@ -664,3 +672,239 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
 
 extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) { return lod_steps(h, nsteps, false); }
 extern "C" int cfd_heat2d_implicit_step_exact(cfd_heat* h, int nsteps) { return lod_steps(h, nsteps, true); }
+
+
+// ---------------------------------------------------------------------------------------------------
+// Variable conductivity: the 5-point operator of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90:162-190 as it
+// stands -- four face coefficients per node, aw = LAMBDA(x-dx/2,y)/dx**2, ae, as = LAMBDA(x,y-dy/2)/dy**2, an
+// (:171-179), ap = -(aw+ae+as+an) (:180, formed on the fly), right-hand side -QDOT (:188).  Used three ways:
+//   k_heat_apply    the residual of the steady equations
+//   k_ftcs_var      the explicit update of fdm1d_explicit_heat_cond.f90:133-135 with this operator: 7 arrays streamed
+//                   per step (T, four coefficients, QDOT read; T written) = 56 B/cell against 16 B/cell of the
+//                   constant-conductivity kernel; same marching scheme (one thread per x-column, 3-row register window)
+//   k_heat_gs       the relaxed Gauss-Seidel of gauss_seidel (:248-287) without the dense (nx*ny)^2 matrix: the five
+//                   non-zeros of a row are the coefficient arrays, boundary rows are identity rows (:193-246); nodes in
+//                   two colours ((i+j) even, then odd) instead of the single lexicographic order -- same fixed point
+// All three use non-contracted IEEE operations in the restatement's order: bit-comparable with oracle/heat_oracle.c.
+// ---------------------------------------------------------------------------------------------------
+namespace cfd {
+struct VarParams {
+  int nx, ny;
+  const double *aw, *ae, *as, *an, *q;
+  double rho, cp, dt, rf;
+  double tleft, tright, tbottom, ttop;
+  const double* src;
+  double* dst;
+  double* partial;
+};
+
+__device__ __forceinline__ double var_operator(const VarParams& P, size_t k, double W, double E, double S, double N, double C) {
+  const double aw = __ldg(P.aw + k), ae = __ldg(P.ae + k), as = __ldg(P.as + k), an = __ldg(P.an + k);
+  const double ap = -__dadd_rn(__dadd_rn(__dadd_rn(aw, ae), as), an);
+  double r = __dadd_rn(__dmul_rn(aw, W), __dmul_rn(ae, E));
+  r = __dadd_rn(r, __dmul_rn(as, S));
+  r = __dadd_rn(r, __dmul_rn(an, N));
+  r = __dadd_rn(r, __dmul_rn(ap, C));
+  return __dadd_rn(r, __ldg(P.q + k));
+}
+
+// MODE 0: dst = operator(src) + q on interior nodes, 0 on the boundary; MODE 1: one explicit step src -> dst
+template <int MODE>
+__global__ void __launch_bounds__(128) k_heat_var(const VarParams P) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P.nx) return;
+  int j = blockIdx.y * HEAT_RY;
+  const int jend = min(j + HEAT_RY - 1, P.ny - 1);
+  const size_t nx = (size_t)P.nx;
+  const bool xedge = (i == 0) || (i == P.nx - 1);
+  const double* s = P.src + (size_t)j * nx + i;
+  double* d = P.dst + (size_t)j * nx + i;
+  double S = (j > 0) ? __ldg(s - nx) : 0.0;
+  double C = __ldg(s);
+  for (; j <= jend; ++j, s += nx, d += nx) {
+    const double N = (j + 1 < P.ny) ? __ldg(s + nx) : 0.0;
+    double out;
+    if (j == 0) {
+      out = MODE ? P.tbottom : 0.0;
+    } else if (j == P.ny - 1) {
+      out = MODE ? P.ttop : 0.0;
+    } else if (xedge) {
+      out = MODE ? (i == 0 ? P.tleft : P.tright) : 0.0;
+    } else {
+      const double op = var_operator(P, (size_t)j * nx + i, __ldg(s - 1), __ldg(s + 1), S, N, C);
+      out = MODE ? __dadd_rn(C, __dmul_rn(__ddiv_rn(__ddiv_rn(op, P.rho), P.cp), P.dt)) : op;
+    }
+    *d = out;
+    S = C;
+    C = N;
+  }
+}
+
+// one colour of a Gauss-Seidel pass, in place; each block leaves its sum of (x1-x2)**2 in partial[block]
+// (colour 1 adds to what colour 0 left)
+__global__ void __launch_bounds__(256) k_heat_gs(const VarParams P, const int colour) {
+  __shared__ double red[256];
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int ii = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = 2 * ii + ((j + colour) & 1);
+  double d2 = 0.0;
+  if (j < P.ny && i < P.nx) {
+    const size_t nx = (size_t)P.nx, k = (size_t)j * nx + i;
+    double* x = P.dst;
+    const double x1 = x[k];
+    double s, b, akk;
+    if (i == 0 || i == P.nx - 1 || j == 0 || j == P.ny - 1) {
+      s = 0.0;
+      akk = 1.0;
+      b = (j == 0) ? P.tbottom : (j == P.ny - 1) ? P.ttop : (i == 0) ? P.tleft : P.tright;
+    } else {
+      const double aw = __ldg(P.aw + k), ae = __ldg(P.ae + k), as = __ldg(P.as + k), an = __ldg(P.an + k);
+      s = __dadd_rn(__dmul_rn(as, x[k - nx]), __dmul_rn(aw, x[k - 1]));
+      s = __dadd_rn(s, __dmul_rn(ae, x[k + 1]));
+      s = __dadd_rn(s, __dmul_rn(an, x[k + nx]));
+      akk = -__dadd_rn(__dadd_rn(__dadd_rn(aw, ae), as), an);
+      b = -__ldg(P.q + k);
+    }
+    const double x2 = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn(b, s), P.rf), akk), __dmul_rn(__dsub_rn(1.0, P.rf), x1));
+    x[k] = x2;
+    const double df = __dsub_rn(x1, x2);
+    d2 = __dmul_rn(df, df);
+  }
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  red[tid] = d2;
+  __syncthreads();
+  for (int st = 128; st > 0; st >>= 1) {
+    if (tid < st) red[tid] += red[tid + st];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    double* p = P.partial + (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+    *p = colour ? *p + red[0] : red[0];
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_heat_gs_norm(const double* partial, int n, double* out) {
+  __shared__ double red[1024];
+  double a = 0.0;
+  for (int k = threadIdx.x; k < n; k += 1024) a += partial[k];
+  red[threadIdx.x] = a;
+  __syncthreads();
+  for (int st = 512; st > 0; st >>= 1) {
+    if ((int)threadIdx.x < st) red[threadIdx.x] += red[threadIdx.x + st];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = sqrt(red[0]);
+}
+}  // namespace cfd
+
+static int fill_var(cfd_heat* h, VarParams& P) {
+  CFD_REQUIRE(h->op[0], "set the operator first (cfd_heat_set_operator)");
+  const cfd_heat_config& g = h->cfg;
+  CFD_REQUIRE(g.halo_s == 0 && g.halo_n == 0 && (g.ny_global == 0 || g.ny_global == g.ny),
+              "the variable-conductivity path runs on whole grids (no row slabs)");
+  P.nx = g.nx; P.ny = g.ny;
+  P.aw = h->op[0]; P.ae = h->op[1]; P.as = h->op[2]; P.an = h->op[3]; P.q = h->op[4];
+  P.rho = g.rho; P.cp = g.cp; P.dt = g.dt; P.rf = 0.5;
+  P.tleft = g.tleft; P.tright = g.tright; P.tbottom = g.tbottom; P.ttop = g.ttop;
+  P.partial = nullptr;
+  return CFD_OK;
+}
+
+extern "C" int cfd_heat_set_operator(cfd_heat* h, const double* lamw, const double* lame, const double* lams,
+                                     const double* lamn, const double* qdot, int ld) {
+  CFD_REQUIRE(h && lamw && lame && lams && lamn && ld >= h->cfg.nx, "bad argument");
+  CFD_CUDA(cudaSetDevice(h->device));
+  const cfd_heat_config& g = h->cfg;
+  const int nx = g.nx, ny = g.ny;
+  const size_t n = (size_t)nx * ny;
+  const double dx = (g.xb - g.xa) / (double)(nx - 1), dy = (g.yb - g.ya) / (double)(ny - 1);
+  // interior() (:162-190): aw = cdw / dx**2 ... on the host, once (O(n), one division per coefficient)
+  std::vector<double> buf(n);
+  const double* src[5] = {lamw, lame, lams, lamn, qdot};
+  const double div[5] = {dx * dx, dx * dx, dy * dy, dy * dy, 1.0};
+  for (int a = 0; a < 5; ++a) {
+    if (!h->op[a]) {
+      if (cudaMalloc(&h->op[a], n * sizeof(double)) != cudaSuccess) {
+        cfd_set_error("cudaMalloc of %zu bytes failed", n * sizeof(double));
+        return CFD_ERR_NOMEM;
+      }
+    }
+    for (int j = 0; j < ny; ++j)
+      for (int i = 0; i < nx; ++i) {
+        const bool interior = i > 0 && i < nx - 1 && j > 0 && j < ny - 1;
+        const double v = (src[a] && interior) ? src[a][(size_t)j * ld + i] : 0.0;
+        buf[(size_t)j * nx + i] = a < 4 ? v / div[a] : v;
+      }
+    CFD_CUDA(cudaMemcpyAsync(h->op[a], buf.data(), n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CFD_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  return CFD_OK;
+}
+
+extern "C" int cfd_heat2d_apply(cfd_heat* h, double* host_r, int ld) {
+  CFD_REQUIRE(h && host_r && ld >= h->cfg.nx, "bad argument");
+  CFD_CUDA(cudaSetDevice(h->device));
+  VarParams P{};
+  int rc = fill_var(h, P);
+  if (rc) return rc;
+  P.src = h->buf[h->cur];
+  P.dst = h->buf[1 - h->cur];
+  dim3 grid((P.nx + 127) / 128, (P.ny + HEAT_RY - 1) / HEAT_RY);
+  k_heat_var<0><<<grid, 128, 0, h->stream>>>(P);
+  CFD_CUDA(cudaGetLastError());
+  const size_t w = (size_t)P.nx * sizeof(double);
+  CFD_CUDA(cudaMemcpy2DAsync(host_r, (size_t)ld * sizeof(double), P.dst, w, w, P.ny, cudaMemcpyDeviceToHost, h->stream));
+  CFD_CUDA(cudaStreamSynchronize(h->stream));
+  return CFD_OK;
+}
+
+extern "C" int cfd_heat2d_step_var(cfd_heat* h, int nsteps) {
+  CFD_REQUIRE(h && nsteps >= 0, "bad argument");
+  CFD_CUDA(cudaSetDevice(h->device));
+  VarParams P{};
+  int rc = fill_var(h, P);
+  if (rc) return rc;
+  dim3 grid((P.nx + 127) / 128, (P.ny + HEAT_RY - 1) / HEAT_RY);
+  for (int n = 0; n < nsteps; ++n) {
+    P.src = h->buf[h->cur];
+    P.dst = h->buf[1 - h->cur];
+    k_heat_var<1><<<grid, 128, 0, h->stream>>>(P);
+    h->cur = 1 - h->cur;
+    ++h->steps_done;
+  }
+  CFD_CUDA(cudaGetLastError());
+  return CFD_OK;
+}
+
+extern "C" int cfd_heat2d_steady_gs(cfd_heat* h, int maxit, double tol, double rf, int* iters, double* dx2) {
+  CFD_REQUIRE(h && maxit >= 1 && rf > 0.0, "bad argument");
+  CFD_CUDA(cudaSetDevice(h->device));
+  VarParams P{};
+  int rc = fill_var(h, P);
+  if (rc) return rc;
+  P.rf = rf;
+  P.dst = h->buf[h->cur];
+  dim3 block(32, 8), grid(((P.nx + 1) / 2 + 31) / 32, (P.ny + 7) / 8);
+  const int nb = grid.x * grid.y;
+  if (!h->gs_partial || h->gs_blocks < nb) {
+    if (h->gs_partial) cudaFree(h->gs_partial);
+    CFD_CUDA(cudaMalloc(&h->gs_partial, ((size_t)nb + 1) * sizeof(double)));
+    h->gs_blocks = nb;
+  }
+  P.partial = h->gs_partial;
+  double norm = 0.0;
+  int k = 0;
+  for (k = 1; k <= maxit; ++k) {                       // gauss_seidel :263-285
+    k_heat_gs<<<grid, block, 0, h->stream>>>(P, 0);
+    k_heat_gs<<<grid, block, 0, h->stream>>>(P, 1);
+    k_heat_gs_norm<<<1, 1024, 0, h->stream>>>(h->gs_partial, nb, h->gs_partial + nb);
+    CFD_CUDA(cudaMemcpyAsync(&norm, h->gs_partial + nb, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CFD_CUDA(cudaStreamSynchronize(h->stream));
+    if (norm < tol) break;
+  }
+  if (k > maxit) k = maxit;
+  if (iters) *iters = k;
+  if (dx2) *dx2 = norm;
+  CFD_CUDA(cudaGetLastError());
+  return CFD_OK;
+}

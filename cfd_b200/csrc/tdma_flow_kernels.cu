@@ -37,17 +37,27 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// Poll until *p >= want (wrap-safe) or about a second has passed; false = timed out (abort flag raised).
+// Poll until *p >= want (wrap-safe) or about two seconds have passed; false = timed out (abort flag raised).
+// SYS: the flag may be written by another GPU.
+template <bool SYS = true>
 __device__ __forceinline__ bool wait_flag(const int* p, int want, int* abort_flag) {
-  if (ld_acquire_sys(p) - want >= 0) return true;
+  if ((SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - want >= 0) return true;
   const long long t0 = clock64();
   for (;;) {
     __nanosleep(40);
-    if (ld_acquire_sys(p) - want >= 0) return true;
+    if ((SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - want >= 0) return true;
     if (clock64() - t0 > 4000000000LL || *(volatile int*)abort_flag) {   // ~2 s at 2 GHz
       atomicExch(abort_flag, 1);
       return false;
@@ -102,8 +112,11 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
           if (p > 0) {
             // the neighbour lines were rewritten by the previous pass: wait until both are complete
             const int want = P.epoch0 + p - 1;
-            if (i0 - 1 >= P.wait_lo[oc] && i0 - 1 <= P.wait_hi[oc]) wait_flag(P.flags + (i0 - 1), want, P.abort_flag);
-            if (i0 + 1 >= P.wait_lo[oc] && i0 + 1 <= P.wait_hi[oc]) wait_flag(P.flags + (i0 + 1), want, P.abort_flag);
+            for (int nb = i0 - 1; nb <= i0 + 1; nb += 2) {
+              if (nb < P.wait_lo[oc] || nb > P.wait_hi[oc]) continue;
+              if (nb == P.halo_line[0] || nb == P.halo_line[1]) wait_flag<true>(P.flags + nb, want, P.abort_flag);
+              else wait_flag<false>(P.flags + nb, want, P.abort_flag);
+            }
             asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes (other SMs / peer GPU) -> bulk-copy reads
           }
           const double* csrc = P.coef + (long long)i0 * P.L.cSL;
@@ -141,19 +154,43 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
   const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.jhi + 1, M, T);
   unsigned rs = 0, rph = 0;
   bool peer_open[2] = {false, false};   // this launch has seen the neighbour's ready mark
-  for (int p = 0; p < P.npass; ++p) {
+  // A finished line is published (flag = epoch) by ONE thread after a block barrier: the barrier orders every thread's
+  // stores before that thread's release, which is cumulative.  Releasing right after the stores would wait for them to
+  // drain (about a microsecond per line, with the whole block behind the next barrier); instead the release is issued
+  // one line later, after the first barrier of the next line's reduction, when those stores are long complete.  The
+  // last line a block solves in a pass is published at once: lines of the next pass wait for it.
+  int pend_line = -1, pend_epoch = 0;
+  // this block's work items in order: (pass, position); the Dirichlet end values of a line are fetched one item ahead
+  int p = 0, idx = blockIdx.x;
+  while (p < P.npass && idx >= P.nlines[(P.colour0 + p) & 1]) ++p;
+  double bS = 0.0, bN = 0.0;
+  if (p < P.npass && !(P.first && p < 2)) {
+    const double* ph = P.phi + (long long)(P.i_first[(P.colour0 + p) & 1] + 2 * flow_line(idx, P.nlines[(P.colour0 + p) & 1])) * LD;
+    bS = __ldg(ph + q_s);
+    bN = __ldg(ph + q_n);
+  }
+  while (p < P.npass) {
     const int c = (P.colour0 + p) & 1;
-    const bool zeroEW = P.first && p == 0, zero_ends = P.first && p < 2;
+    const bool zeroEW = P.first && p == 0;
     const int nl = P.nlines[c];
     const int epoch = P.epoch0 + p;
-    for (int idx = blockIdx.x; idx < nl; idx += gridDim.x) {
+    {
       const int i0 = P.i_first[c] + 2 * flow_line(idx, nl);
       double* phi = P.phi + (long long)i0 * LD;
-      // Dirichlet end values phi(i, jstart-1), phi(i, nj): never written by a sweep, so plain loads are safe at any time
-      double bS = 0.0, bN = 0.0;
-      if (!zero_ends) {
-        bS = __ldg(phi + q_s);
-        bN = __ldg(phi + q_n);
+      // next item of this block, and its end values phi(i, jstart-1), phi(i, nj) (never written by a sweep: safe to
+      // read at any time)
+      int np = p, nidx = idx + (int)gridDim.x;
+      if (nidx >= nl) {
+        nidx = blockIdx.x;
+        ++np;
+        while (np < P.npass && nidx >= P.nlines[(P.colour0 + np) & 1]) ++np;
+      }
+      double bS_next = 0.0, bN_next = 0.0;
+      if (np < P.npass && !(P.first && np < 2)) {
+        const int cn = (P.colour0 + np) & 1;
+        const double* ph = P.phi + (long long)(P.i_first[cn] + 2 * flow_line(nidx, P.nlines[cn])) * LD;
+        bS_next = __ldg(ph + q_s);
+        bN_next = __ldg(ph + q_n);
       }
       double ca[M], cc[M], cf[M];
 #pragma unroll
@@ -227,6 +264,10 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
       cur[T + t] = u;
       cur[2 * T + t] = r;
       consumer_sync(T);
+      if (pend_line >= 0) {                    // the previous line's stores were issued a whole line ago
+        if (t == 0) st_release_gpu(P.flags + pend_line, pend_epoch);
+        pend_line = -1;
+      }
       for (int sft = 1; sft < T; sft <<= 1) {
         double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
         if (t - sft >= 0) {
@@ -274,12 +315,26 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
           if (rphi) rphi[k * T + t] = xk;
         }
       }
-      if (rphi) __threadfence_system(); else __threadfence();
-      consumer_sync(T);   // all stores of the line are ordered before the flag; the PCR buffers are free again
-      if (t == 0) {
-        st_release_sys(P.flags + i0, epoch);
-        if (rphi) st_release_sys(P.peer_flag[side], epoch);
+      const bool last_of_pass = np != p;
+      if (rphi || last_of_pass) {
+        // a slab-edge line (the neighbouring GPU waits for it) or the block's last line of the pass: publish now
+        consumer_sync(T);   // every thread's stores precede thread 0's release; the PCR buffers are free again
+        if (t == 0) {
+          if (rphi) {
+            __threadfence_system();
+            st_release_sys(P.peer_flag[side], epoch);
+          }
+          st_release_gpu(P.flags + i0, epoch);
+        }
+      } else {
+        consumer_sync(T);   // the PCR buffers are reused by the next line
+        pend_line = i0;
+        pend_epoch = epoch;
       }
+      p = np;
+      idx = nidx;
+      bS = bS_next;
+      bN = bN_next;
     }
   }
 }

@@ -74,6 +74,50 @@ class Heat2D:
         fn = self.lib.cfd_heat2d_implicit_step_exact if exact else self.lib.cfd_heat2d_implicit_step
         check(fn(self._h, nsteps))
 
+    # -- variable conductivity: interior() / gauss_seidel of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90 ----
+    def face_points(self):
+        """The points interior() evaluates LAMBDA at (:171-174), as four pairs of (nx,ny) arrays: (x-dx/2, y),
+        (x+dx/2, y), (x, y-dy/2), (x, y+dy/2), plus the node coordinates; xymesh (:112-129) for x, y."""
+        g, nx, ny = self._cfg, self.nx, self.ny
+        dx, dy = (g.xb - g.xa) / (nx - 1), (g.yb - g.ya) / (ny - 1)
+        x, y = g.xa + np.arange(nx) * dx, g.ya + np.arange(ny) * dy
+        x[0], y[0] = g.xa, g.ya
+        X, Y = x[:, None] + 0.0 * y[None, :], 0.0 * x[:, None] + y[None, :]
+        xm, xp, ym, yp = (np.zeros_like(X) for _ in range(4))
+        xm[1:, :] = 0.5 * (x[1:] + x[:-1])[:, None]
+        xp[:-1, :] = 0.5 * (x[:-1] + x[1:])[:, None]
+        ym[:, 1:] = 0.5 * (y[1:] + y[:-1])[None, :]
+        yp[:, :-1] = 0.5 * (y[:-1] + y[1:])[None, :]
+        return (xm, Y), (xp, Y), (X, ym), (X, yp), (X, Y)
+
+    def set_operator(self, lam, qdot=None):
+        """`lam(x, y)`, `qdot(x, y)`: the program's functions LAMBDA and QDOT as vectorised callables (host logic,
+        evaluated once); or pass four ready-made face arrays as a tuple for `lam` and an array for `qdot`."""
+        f = lambda a: np.asfortranarray(np.broadcast_to(np.asarray(a, dtype=np.float64), (self.nx, self.ny)).copy())
+        if callable(lam):
+            w, e, s, n, c = self.face_points()
+            faces = [f(lam(*w)), f(lam(*e)), f(lam(*s)), f(lam(*n))]
+            q = f(qdot(*c)) if qdot is not None else None
+        else:
+            faces = [f(a) for a in lam]
+            q = f(qdot) if qdot is not None else None
+        ptr = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+        check(self.lib.cfd_heat_set_operator(self._h, *(ptr(a) for a in faces), ptr(q), self.nx))
+
+    def apply(self) -> np.ndarray:
+        r = np.zeros((self.nx, self.ny), order="F")
+        check(self.lib.cfd_heat2d_apply(self._h, r.ctypes.data_as(C.c_void_p), self.nx))
+        return r
+
+    def step_var(self, nsteps: int = 1):
+        check(self.lib.cfd_heat2d_step_var(self._h, nsteps))
+
+    def steady_gs(self, maxit=500, tol=1.0e-7, rf=0.5):
+        """gauss_seidel (:248-287), matrix-free, two colours; returns (passes, last |x1-x2|_2)."""
+        it, d = C.c_int(), C.c_double()
+        check(self.lib.cfd_heat2d_steady_gs(self._h, maxit, tol, rf, C.byref(it), C.byref(d)))
+        return it.value, d.value
+
     def synchronize(self):
         check(self.lib.cfd_heat_synchronize(self._h))
 

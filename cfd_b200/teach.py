@@ -235,8 +235,10 @@ class TeachFVM(CavityFVM):
         rsmall = rsmall if rsmall is not None else 0.5 * (self.y[self.jstep - 1] + self.y[self.jstep])   # control.f90:91
         ularge = uin * (rsmall / rlarge) ** 2
         taun, yplusn = self.wall_download("taun"), self.wall_download("yplusn")
-        te, t, den = self.download("te"), self.download("t"), self.download("den")
         j = nj - 1                                                          # njm1
+        # only the wall-adjacent row of the three fields is needed: fetched by the device (no whole-field download)
+        te, t, den = ({j - 1: self.extract_row(n, j)} for n in ("te", "t", "den"))
+        te, t, den = (_Row(a) for a in (te, t, den))
         xlref, tref, delt = rlarge - rsmall, tin, abs(tin - m.twalln)
         dyn = self.yv[nj - 1] - self.y[nj - 2]
         rows = []
@@ -258,6 +260,16 @@ class TeachFVM(CavityFVM):
         res = (C.c_double * 8)()
         check(self.lib.cfd_iterate(self._h, n, res))
         return res[0], res[1], res[2], res[3], res[4], res[5]
+
+
+class _Row:
+    """a[i, j] on a single extracted row j (wall_coefficients reads row njm1 only)."""
+
+    def __init__(self, rows):
+        self.rows = rows
+
+    def __getitem__(self, ij):
+        return self.rows[ij[1]][ij[0]]
 
 
 _BY_I = ("x", "xu", "sew", "sewu", "dxep", "dxpw", "dxepu", "dxpwu")

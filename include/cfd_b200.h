@@ -159,6 +159,16 @@ int cfd_download(cfd_ctx* ctx, int field, double* host, int ld);
 int cfd_upload_noalloc(cfd_ctx* ctx, int field, const double* host, int ld);
 /* monitor-point read u(imon,jmon) etc. (cavity_fvm.f90:559-563); LOCAL 1-based indices */
 int cfd_probe(cfd_ctx* ctx, int field, int i, int j, double* value);
+/* ---- post-processing on the device fields: result files and monitors without whole-field downloads --------------
+   cfd_extract_line / cfd_extract_row   A(i, 1:nj) / A(1:ni, j) of a plain field in natural order (n = nj / ni), LOCAL indices
+   cfd_centreline          which = 0: uc(index, 1:nj), which = 1: vc(1:ni, index) of centred_vel (cavity_fvm.f90:416-430;
+                           postproc buoyancy_cav.f90:441-449 has the same formulas) -- the columns of uvel.txt / vvel.txt
+                           (cavity_fvm.f90:600-607)
+   cfd_reference_pressure  p(:,:) = p(:,:) - p(ipref,jpref) and the four corner values (cavity_fvm.f90:568-573), in place */
+int cfd_extract_line(cfd_ctx* ctx, int field, int i, double* host, int n);
+int cfd_extract_row(cfd_ctx* ctx, int field, int j, double* host, int n);
+int cfd_centreline(cfd_ctx* ctx, int which, int index, double* host, int n);
+int cfd_reference_pressure(cfd_ctx* ctx);
 /* raw device view for peer/NCCL halo exchange: base pointer of `field`, doubles per line, number of lines.
    Line i (local, 1-based) is the contiguous range base[(i-1)*line_stride .. +line_stride). */
 int cfd_field_device_view(cfd_ctx* ctx, int field, void** base, long long* line_stride, int* nlines);
@@ -334,6 +344,24 @@ int cfd_heat2d_step_exact(cfd_heat* h, int nsteps);
 int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps);
 /* same, with IEEE divisions in the reference's operation order (bit-comparable with the oracle; slower) */
 int cfd_heat2d_implicit_step_exact(cfd_heat* h, int nsteps);
+/* ---- variable conductivity: the 5-point operator of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90:162-190 ----
+   lamw, lame, lams, lamn = LAMBDA at the four face mid-points of every node, (x-dx/2,y), (x+dx/2,y), (x,y-dy/2),
+   (x,y+dy/2) (:171-174), as (ld,ny) host arrays; qdot = QDOT at the nodes (:188; NULL = none).  The device keeps
+   aw = lamw/dx**2, ae, as = lams/dy**2, an (:176-179); ap = -(aw+ae+as+an) (:180) is formed on the fly.
+     cfd_heat2d_apply      r = aw*T(i-1,j) + ae*T(i+1,j) + as*T(i,j-1) + an*T(i,j+1) + ap*T(i,j) + qdot on the interior
+                           nodes, 0 on the boundary: the residual of the steady equations, to a host array
+     cfd_heat2d_step_var   nsteps of the explicit update (fdm1d_explicit_heat_cond.f90:133-135) with that operator,
+                           T += (operator/rho/cp)*dt, Dirichlet edges rewritten every step; 56 B/cell/step
+     cfd_heat2d_steady_gs  gauss_seidel (:248-287) on the rows interior() / boundary() define, matrix-free (the reference
+                           builds the dense (nx*ny)^2 matrix): x2 = (b - s)*rf/a_kk + (1-rf)*x1, stop when |x1-x2|_2 < tol
+                           or after maxit passes (reference: rf 0.5, tol 1e-7, 500).  Nodes are visited in two colours
+                           ((i+j) even, then odd) instead of one lexicographic order: same fixed point, different
+                           iterates.  Starts from the field in the handle (the reference starts from zero). */
+int cfd_heat_set_operator(cfd_heat* h, const double* lamw, const double* lame, const double* lams, const double* lamn,
+                          const double* qdot, int ld);
+int cfd_heat2d_apply(cfd_heat* h, double* host_r, int ld);
+int cfd_heat2d_step_var(cfd_heat* h, int nsteps);
+int cfd_heat2d_steady_gs(cfd_heat* h, int maxit, double tol, double rf, int* iters, double* dx2);
 int cfd_heat_device_view(cfd_heat* h, void** cur, long long* row_stride, int* nrows);
 int cfd_heat_synchronize(cfd_heat* h);
 

@@ -217,3 +217,102 @@ void orc_heat2d_lod(double k, double rho, double cp, double xa, double xb, doubl
   }
   free(a); free(b); free(c); free(r); free(s); free(x);
 }
+
+/* ---- variable conductivity: the operator of fdm2d_steady_heat_cond.f90:162-190 as it stands ------------------------
+   Coefficient arrays aw, ae, as, an come from orc_heat2d_coeffs (LAMBDA at the four face mid-points / dx**2, dy**2);
+   ap = -(aw + ae + as + an) (:180); rhs = -QDOT (:188).  q holds QDOT at the nodes. */
+
+/* residual of the steady equations on the interior nodes: aw*T(i-1,j) + ae*T(i+1,j) + as*T(i,j-1) + an*T(i,j+1) + ap*T + q
+   (the matrix row :182-186 applied to T minus the right-hand side); 0 on the boundary nodes */
+void orc_heat2d_apply(const double *aw, const double *ae, const double *as, const double *an, const double *q,
+                      const double *t, double *r, int nx, int ny) {
+  int i, j;
+  memset(r, 0, sizeof(double) * (size_t)nx * (size_t)ny);
+  for (j = 2; j <= ny - 1; ++j)
+    for (i = 2; i <= nx - 1; ++i) {
+      double ap = -(T2(aw, i, j) + T2(ae, i, j) + T2(as, i, j) + T2(an, i, j));
+      T2(r, i, j) = T2(aw, i, j) * T2(t, i - 1, j) + T2(ae, i, j) * T2(t, i + 1, j) + T2(as, i, j) * T2(t, i, j - 1) +
+                    T2(an, i, j) * T2(t, i, j + 1) + ap * T2(t, i, j) + T2(q, i, j);
+    }
+}
+
+/* the explicit update of fdm1d_explicit_heat_cond.f90:133-135 with that operator in place of k*(T(i+1)-2T(i)+T(i-1))/dx**2:
+   T = Tc + ((aw*Tw + ae*Te + as*Ts + an*Tn + ap*Tc + q)/rho/cp)*dt, Dirichlet edges rewritten every step (:131-132) */
+void orc_heat2d_ftcs_var(const double *aw, const double *ae, const double *as, const double *an, const double *q,
+                         double rho, double cp, double dt, double tleft, double tright, double tbottom, double ttop,
+                         double *tc, int nx, int ny, int nsteps) {
+  double *t = (double *)malloc(sizeof(double) * (size_t)nx * (size_t)ny);
+  int i, j, n;
+  for (n = 0; n < nsteps; ++n) {
+    for (j = 2; j <= ny - 1; ++j) {
+      T2(t, 1, j) = tleft;
+      T2(t, nx, j) = tright;
+    }
+    for (i = 1; i <= nx; ++i) {
+      T2(t, i, 1) = tbottom;
+      T2(t, i, ny) = ttop;
+    }
+    for (j = 2; j <= ny - 1; ++j)
+      for (i = 2; i <= nx - 1; ++i) {
+        double ap = -(T2(aw, i, j) + T2(ae, i, j) + T2(as, i, j) + T2(an, i, j));
+        double op = T2(aw, i, j) * T2(tc, i - 1, j) + T2(ae, i, j) * T2(tc, i + 1, j) + T2(as, i, j) * T2(tc, i, j - 1) +
+                    T2(an, i, j) * T2(tc, i, j + 1) + ap * T2(tc, i, j) + T2(q, i, j);
+        T2(t, i, j) = T2(tc, i, j) + (op / rho / cp) * dt;
+      }
+    memcpy(tc, t, sizeof(double) * (size_t)nx * (size_t)ny);
+  }
+  free(t);
+}
+
+/* gauss_seidel (fdm2d_steady_heat_cond.f90:248-287) on the matrix that interior() (:162-190) and boundary() (:193-246)
+   build, without forming it: row k = (j-1)*nx + i has a(k,k-nx) = as, a(k,k-1) = aw, a(k,k) = ap, a(k,k+1) = ae,
+   a(k,k+nx) = an and rhs -QDOT on interior nodes, a(k,k) = 1 and rhs = wall temperature on boundary nodes (bottom / top
+   rows include the corners).  The dense inner loop adds a(i,j)*x(j) in increasing j, zeros included: s = as*xS + aw*xW
+   + ae*xE + an*xN in that order, with the already updated x2 for j < i and x1 for j > i.  x2 = (b - s)*rf/a(k,k) +
+   (1-rf)*x1; stop when sqrt(sum (x1-x2)**2) < tol or after imax passes.  order 0: the reference's single lexicographic
+   pass; order 1: two colours, (i+j) even first (what the CUDA path does; same fixed point).  x holds the start vector
+   (the reference starts from 0) and receives the result.  Returns the number of passes; *dx2_out = the last norm. */
+int orc_heat2d_gs(const double *aw, const double *ae, const double *as, const double *an, const double *q,
+                  double tleft, double tright, double tbottom, double ttop, double rf, double tol, int imax, int order,
+                  double *x, int nx, int ny, double *dx2_out) {
+  size_t n = (size_t)nx * (size_t)ny;
+  double *x1 = (double *)malloc(sizeof(double) * n), *x2 = (double *)malloc(sizeof(double) * n);
+  double dx2 = 0.0;
+  int i, j, k, col, done = 0;
+  memcpy(x1, x, sizeof(double) * n);
+  memcpy(x2, x, sizeof(double) * n);
+  for (k = 1; k <= imax; ++k) {
+    for (col = 0; col < (order ? 2 : 1); ++col)
+      for (j = 1; j <= ny; ++j)
+        for (i = 1; i <= nx; ++i) {
+          double s, b, akk;
+          if (order && ((i + j) & 1) != col) continue;
+          if (i == 1 || i == nx || j == 1 || j == ny) {
+            s = 0.0;
+            akk = 1.0;
+            b = (j == 1) ? tbottom : (j == ny) ? ttop : (i == 1) ? tleft : tright;
+          } else {
+            /* in both orders the neighbours already visited in this pass hold x2, the others x1 */
+            double xs = order ? (col ? T2(x2, i, j - 1) : T2(x1, i, j - 1)) : T2(x2, i, j - 1);
+            double xw = order ? (col ? T2(x2, i - 1, j) : T2(x1, i - 1, j)) : T2(x2, i - 1, j);
+            double xe = order ? (col ? T2(x2, i + 1, j) : T2(x1, i + 1, j)) : T2(x1, i + 1, j);
+            double xn = order ? (col ? T2(x2, i, j + 1) : T2(x1, i, j + 1)) : T2(x1, i, j + 1);
+            s = T2(as, i, j) * xs + T2(aw, i, j) * xw + T2(ae, i, j) * xe + T2(an, i, j) * xn;
+            akk = -(T2(aw, i, j) + T2(ae, i, j) + T2(as, i, j) + T2(an, i, j));
+            b = -T2(q, i, j);
+          }
+          T2(x2, i, j) = (b - s) * rf / akk + (1 - rf) * T2(x1, i, j);
+        }
+    dx2 = 0.0;
+    for (i = 0; i < (int)n; ++i) dx2 = dx2 + (x1[i] - x2[i]) * (x1[i] - x2[i]);
+    dx2 = sqrt(dx2);
+    done = k;
+    if (dx2 < tol) break;
+    memcpy(x1, x2, sizeof(double) * n);
+  }
+  memcpy(x, x2, sizeof(double) * n);
+  if (dx2_out) *dx2_out = dx2;
+  free(x1);
+  free(x2);
+  return done;
+}

@@ -121,6 +121,12 @@ def lib(fast: bool = False) -> C.CDLL:
         L.orc_thomas.restype = None
         L.orc_heat2d_coeffs.argtypes = [_dp] * 4 + [C.c_double] * 2 + [_dp] * 5 + [C.c_int, C.c_int]
         L.orc_heat2d_coeffs.restype = None
+        L.orc_heat2d_apply.argtypes = [_dp] * 7 + [C.c_int, C.c_int]
+        L.orc_heat2d_apply.restype = None
+        L.orc_heat2d_ftcs_var.argtypes = [_dp] * 5 + [C.c_double] * 7 + [_dp, C.c_int, C.c_int, C.c_int]
+        L.orc_heat2d_ftcs_var.restype = None
+        L.orc_heat2d_gs.argtypes = [_dp] * 5 + [C.c_double] * 6 + [C.c_int, C.c_int, _dp, C.c_int, C.c_int, _dp]
+        L.orc_heat2d_gs.restype = C.c_int
         for n in ("orc_gen_grid", "orc_gen_boundary", "orc_gen_initial", "orc_gen_assemble_u", "orc_gen_assemble_v",
                   "orc_gen_assemble_p", "orc_gen_assemble_t", "orc_gen_correct", "orc_gen_calcu", "orc_gen_calcv",
                   "orc_gen_calcp", "orc_gen_calct"):
@@ -237,6 +243,57 @@ def heat2d_lod(tc, nsteps, k=5.0, rho=1.0, cp=1.0, lim=(0.0, 1.0, 0.0, 1.0), tbc
     lib(fast).orc_heat2d_lod(k, rho, cp, lim[0], lim[1], lim[2], lim[3], tbc[0], tbc[1], tbc[2], tbc[3],
                              dt, qthr, qval, _p(tc), nx, ny, nsteps)
     return tc
+
+
+class HeatVar:
+    """The variable-conductivity 5-point operator of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90:162-190:
+    `lam(x, y)` and `qdot(x, y)` are the program's functions LAMBDA and QDOT (vectorised callables); coefficient arrays
+    as interior() computes them."""
+
+    def __init__(self, nx, ny, lam, qdot, lim=(0.0, 0.03, 0.0, 0.02), fast=False):
+        self.L, self.nx, self.ny = lib(fast), nx, ny
+        self.dx, self.dy = (lim[1] - lim[0]) / (nx - 1), (lim[3] - lim[2]) / (ny - 1)
+        x = lim[0] + np.arange(nx) * self.dx                              # xymesh (:112-129)
+        y = lim[2] + np.arange(ny) * self.dy
+        x[0], y[0] = lim[0], lim[2]
+        self.x, self.y = x, y
+        X, Y = x[:, None] + 0.0 * y[None, :], 0.0 * x[:, None] + y[None, :]
+        xm, xp = np.zeros_like(X), np.zeros_like(X)
+        ym, yp = np.zeros_like(X), np.zeros_like(X)
+        xm[1:, :] = 0.5 * (x[1:] + x[:-1])[:, None]                        # :171-174: face mid-points
+        xp[:-1, :] = 0.5 * (x[:-1] + x[1:])[:, None]
+        ym[:, 1:] = 0.5 * (y[1:] + y[:-1])[None, :]
+        yp[:, :-1] = 0.5 * (y[:-1] + y[1:])[None, :]
+        f = lambda a: np.asfortranarray(np.broadcast_to(np.asarray(a, dtype=np.float64), X.shape).copy())
+        self.lamw, self.lame = f(lam(xm, Y)), f(lam(xp, Y))
+        self.lams, self.lamn = f(lam(X, ym)), f(lam(X, yp))
+        self.q = f(qdot(X, Y))
+        z = lambda: np.zeros((nx, ny), order="F")
+        self.aw, self.ae, self.as_, self.an, self.ap = z(), z(), z(), z(), z()
+        self.L.orc_heat2d_coeffs(_p(self.lamw), _p(self.lame), _p(self.lams), _p(self.lamn), self.dx, self.dy,
+                                 _p(self.aw), _p(self.ae), _p(self.as_), _p(self.an), _p(self.ap), nx, ny)
+
+    def _c(self):
+        return [_p(a) for a in (self.aw, self.ae, self.as_, self.an, self.q)]
+
+    def apply(self, t):
+        t = np.asfortranarray(t, dtype=np.float64)
+        r = np.zeros_like(t, order="F")
+        self.L.orc_heat2d_apply(*self._c(), _p(t), _p(r), self.nx, self.ny)
+        return r
+
+    def ftcs(self, t, nsteps, dt, rho=1.0, cp=1.0, tbc=(0.0, 0.0, 0.0, 0.0)):
+        t = np.array(t, dtype=np.float64, order="F", copy=True)
+        self.L.orc_heat2d_ftcs_var(*self._c(), rho, cp, dt, tbc[0], tbc[1], tbc[2], tbc[3], _p(t), self.nx, self.ny, nsteps)
+        return t
+
+    def gauss_seidel(self, x0=None, tbc=(300.0, 300.0, 300.0, 300.0), rf=0.5, tol=1.0e-7, imax=500, order=0):
+        """tbc = (tleft, tright, tbottom, ttop); returns (x, passes, last norm)."""
+        x = np.zeros((self.nx, self.ny), order="F") if x0 is None else np.array(x0, dtype=np.float64, order="F", copy=True)
+        d = C.c_double()
+        n = self.L.orc_heat2d_gs(*self._c(), tbc[0], tbc[1], tbc[2], tbc[3], rf, tol, imax, order, _p(x), self.nx, self.ny,
+                                 C.byref(d))
+        return x, n, d.value
 
 
 def thomas(a, b, c, d):

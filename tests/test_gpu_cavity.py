@@ -398,6 +398,9 @@ def test_lisolv_drop_in_on_host_assembled_coefficients(cfd, oracle, istart, jsta
     rng = np.random.default_rng(17)
     for name, scale, base in (("u", 0.3, 0.0), ("v", 0.3, 0.0), ("p", 5.0, 0.0), ("den", 50.0, 1000.0), ("vis", 2.0, 10.0)):
         getattr(o, name)[:, :] = base + scale * (rng.random((o.ni, o.nj)) - 0.5)
+    if field == "pp":                                                        # the p' coefficients are built from du, dv
+        o.assemble_u()
+        o.assemble_v()
     {"u": o.assemble_u, "v": o.assemble_v, "pp": o.assemble_p}[field]()      # host-assembled ae..su
     phi = np.asfortranarray(rng.random((o.ni, o.nj)))
     g = cfd.CavityFVM(40, 56, order="sequential", raw_coefficients=True)     # no geometry, no fields: solver only
@@ -441,3 +444,22 @@ def test_sweeps_in_one_launch_equal_the_colour_passes_bitwise(cfd, oracle, shape
     assert not g.peer_status()
     g.close()
     h.close()
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (33, 130), (300, 1030)])
+def test_device_side_postprocessing(cfd, oracle, shape):
+    """centred_vel on one line / row, line and row extraction, and the final pressure shift with its corner values
+    (cavity_fvm.f90:416-430, 567-573) computed on the device: the same bits as the oracle's routines on the whole fields."""
+    from cfd_b200 import tecplot
+    o, g = make_pair(cfd, oracle, *shape, order="redblack")
+    randomise(o, g, 21)
+    uc, vc = o.centred_vel()
+    for i in (1, 2, o.imon, o.ni - 1, o.ni):
+        assert np.array_equal(g.centreline_uc(i), uc[i - 1, :]), i
+        assert np.array_equal(g.extract_line("v", i), o.v[i - 1, :])
+    for j in (1, 2, o.jmon, o.nj - 1, o.nj):
+        assert np.array_equal(g.centreline_vc(j), vc[:, j - 1]), j
+        assert np.array_equal(g.extract_row("p", j), o.p[:, j - 1])
+    g.reference_pressure()
+    assert np.array_equal(g.download("p"), tecplot.corner_pressure(o.p, g.ipref, g.jpref))
+    g.close()

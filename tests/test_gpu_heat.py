@@ -129,3 +129,84 @@ def test_implicit_lod_large_time_step_is_stable(cfd):
     t = h.download()
     assert t.min() >= -1e-12 and t.max() <= 1.0 + 1e-12
     h.close()
+
+
+# ---- variable conductivity: the operator of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90:162-190 ---------------
+def _lam(x, y):
+    return 20.0 * (1.0 + 3.0 * x / 0.03 + 0.5 * np.sin(40.0 * y))
+
+
+def _qd(x, y):
+    return 5.0e7 * (1.0 + 10.0 * x) + 0.0 * y
+
+
+@pytest.mark.parametrize("shape", [(7, 5), (66, 34), (130, 257), (1030, 70)])
+def test_variable_conductivity_operator_and_explicit_steps_bitwise(cfd, oracle, shape):
+    """Four face conductivities per node (LAMBDA at the face mid-points, :171-174): the residual of the steady
+    equations and explicit steps with that operator, bit for bit against oracle/heat_oracle.c."""
+    nx, ny = shape
+    lim = (0.0, 0.03, 0.0, 0.02)
+    o = oracle.HeatVar(nx, ny, _lam, _qd, lim=lim)
+    dx, dy = o.dx, o.dy
+    dt = 0.2 * min(dx, dy) ** 2 / 80.0 * 7.8e3 * 460.0          # Fo = 0.2 at the largest conductivity
+    h = cfd.Heat2D(nx, ny, rho=7.8e3, cp=460.0, xa=lim[0], xb=lim[1], ya=lim[2], yb=lim[3], tleft=300.0, tright=310.0,
+                   tbottom=320.0, ttop=330.0, dt=dt)
+    h.set_operator(_lam, _qd)
+    t0 = np.asfortranarray(300.0 + 50.0 * np.random.default_rng(11).random((nx, ny)))
+    h.upload(t0)
+    assert np.array_equal(h.apply(), o.apply(t0))
+    h.step_var(5)
+    want = o.ftcs(t0, 5, dt, rho=7.8e3, cp=460.0, tbc=(300.0, 310.0, 320.0, 330.0))
+    assert np.array_equal(h.download(), want)
+    h.close()
+
+
+def test_matrix_free_gauss_seidel_reference_case(cfd, oracle):
+    """The program as shipped (7 x 5 nodes, LAMBDA = 20, QDOT = 5e7, walls at 300, rf 0.5, tol 1e-7, from zero): the
+    two-colour device passes against the same passes in the oracle bit for bit, and -- run to a tight tolerance --
+    against the reference's lexicographic order and a direct solve of the 35 x 35 system."""
+    nx, ny, lim = 7, 5, (0.0, 0.03, 0.0, 0.02)
+    lam, qd = (lambda x, y: 20.0 + 0.0 * x), (lambda x, y: 5.0e7 + 0.0 * x)
+    o = oracle.HeatVar(nx, ny, lam, qd, lim=lim)
+    h = cfd.Heat2D(nx, ny, xa=lim[0], xb=lim[1], ya=lim[2], yb=lim[3], tleft=300.0, tright=300.0, tbottom=300.0, ttop=300.0)
+    h.set_operator(lam, qd)
+    h.upload(np.zeros((nx, ny), order="F"))
+    n_g, d_g = h.steady_gs()
+    x_o, n_o, d_o = o.gauss_seidel(order=1)
+    assert n_g == n_o and abs(d_g - d_o) <= 1e-12 * d_o
+    assert np.array_equal(h.download(), x_o)
+    x_ref, n_ref, _ = o.gauss_seidel(order=0)                     # the reference's own order: 151 passes, same plate
+    assert abs(n_ref - n_g) <= 3 and np.abs(x_ref - x_o).max() < 1e-5
+    h.upload(np.zeros((nx, ny), order="F"))
+    h.steady_gs(maxit=5000, tol=1e-12)
+    x_seq, _, _ = o.gauss_seidel(order=0, tol=1e-12, imax=5000)
+    got = h.download()
+    assert np.abs(got - x_seq).max() <= 1e-8 * np.abs(x_seq).max()
+    # direct solve of the rows interior() / boundary() define
+    A, b = np.zeros((nx * ny, nx * ny)), np.zeros(nx * ny)
+    for j in range(ny):
+        for i in range(nx):
+            k = j * nx + i
+            if i in (0, nx - 1) or j in (0, ny - 1):
+                A[k, k], b[k] = 1.0, 300.0
+            else:
+                A[k, k - 1], A[k, k + 1], A[k, k - nx], A[k, k + nx] = o.aw[i, j], o.ae[i, j], o.as_[i, j], o.an[i, j]
+                A[k, k], b[k] = o.ap[i, j], -o.q[i, j]
+    exact = np.linalg.solve(A, b).reshape(ny, nx).T
+    assert np.abs(got - exact).max() <= 1e-8 * np.abs(exact).max()
+    assert abs(exact[3, 2] - 398.0) < 0.1                         # the plate's centre temperature
+    h.close()
+
+
+def test_matrix_free_gauss_seidel_variable_conductivity(cfd, oracle):
+    nx, ny, lim = 41, 29, (0.0, 0.03, 0.0, 0.02)
+    o = oracle.HeatVar(nx, ny, _lam, _qd, lim=lim)
+    h = cfd.Heat2D(nx, ny, xa=lim[0], xb=lim[1], ya=lim[2], yb=lim[3], tleft=300.0, tright=310.0, tbottom=320.0, ttop=330.0)
+    h.set_operator(_lam, _qd)
+    x0 = np.asfortranarray(300.0 + np.random.default_rng(2).random((nx, ny)))
+    h.upload(x0)
+    n_g, d_g = h.steady_gs(maxit=40, tol=0.0)
+    x_o, n_o, d_o = o.gauss_seidel(x0=x0, tbc=(300.0, 310.0, 320.0, 330.0), tol=0.0, imax=40, order=1)
+    assert n_g == n_o == 40 and abs(d_g - d_o) <= 1e-11 * d_o
+    assert np.array_equal(h.download(), x_o)
+    h.close()

@@ -157,12 +157,39 @@ def test_turbulent_stagewise_vs_oracle(cfd, oracle):
     g.close()
 
 
-def test_wall_coefficients_postprocessing(cfd):
-    """control.f90:243-272 on the device's wall arrays: finite, one row per wall node, Nusselt number positive."""
-    g = cfd.TeachFVM(40, 30, order="redblack", turbulent=True)
+@pytest.mark.parametrize("viscos", [0.8e-3, 2.0e-5])
+def test_wall_coefficients_postprocessing(cfd, oracle, viscos):
+    """Shear-stress coefficient and Nusselt number along the large-duct wall (control.f90:254-272) from the device's wall
+    arrays and the wall-adjacent row of te, t, den -- against the same formulas evaluated on the oracle's fields after the
+    same 30 passes.  viscos = 2e-5 takes the log-law branch (y+ > 11.63), 0.8e-3 the laminar one."""
+    ni, nj = 40, 30
+    o = oracle.TeachTurb(ni, nj, order=0, viscos=viscos)
+    g = cfd.TeachFVM(ni, nj, order="sequential", turbulent=True, viscos=viscos)
+    o.iterate_turb(30)
     g.iterate_turb(30)
-    rows = g.wall_coefficients()
-    assert len(rows) == 40 - 1 - g.istep + 1
-    a = np.array(rows)
-    assert np.isfinite(a).all() and (a[:, 3] > 0).all() and (np.diff(a[:, 4]) > 0).all()
+    rows = np.array(g.wall_coefficients())
+    assert len(rows) == ni - 1 - g.istep + 1
+    m = g.model
+    rlarge, uin, densit, tin, cpp, tk = 0.0124, 0.5, 1000.0, 0.0, 4.190e3, 6.0e-1
+    rsmall = 0.5 * (o.y[g.jstep - 1] + o.y[g.jstep])
+    ularge = uin * (rsmall / rlarge) ** 2
+    xlref, delt, dyn = rlarge - rsmall, abs(tin - m.twalln), o.yv[nj - 1] - o.y[nj - 2]
+    j = nj - 2                                                  # njm1, 0-based
+    branches = set()
+    for r in rows:
+        i = int(r[0])
+        ssc = o.taun[i - 1] / (densit * ularge * ularge)
+        if o.yplusn[i - 1] <= 11.63:
+            hf = tk * abs(m.twalln - o.t[i - 1, j]) / dyn
+            branches.add("laminar")
+        else:
+            uplusn = np.log(m.elog * o.yplusn[i - 1]) / m.cappa
+            hf = o.den[i - 1, j] * cpp * np.sqrt(o.te[i - 1, j]) * (tin - o.t[i - 1, j]) / m.prandt / (uplusn + m.pfun)
+            branches.add("log")
+        want = (i, o.xu[i - 1] / xlref, ssc, abs(hf) * xlref / (tk * delt), o.x[i - 1] / xlref)
+        for a, b in zip(r, want):
+            assert abs(a - b) <= 1e-9 * abs(b) + 1e-300, (i, r, want)
+    assert ("log" in branches) == (viscos < 1e-4)
+    # the extracted row itself is the downloaded field's row
+    assert np.array_equal(g.extract_row("t", nj - 1), g.download("t")[:, nj - 2])
     g.close()
