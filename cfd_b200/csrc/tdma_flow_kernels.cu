@@ -68,6 +68,52 @@ __device__ __forceinline__ bool wait_flag(const int* p, int want, int* abort_fla
 // position in the per-block work order -> line of the colour: slab-edge lines (first, last) come first
 __device__ __forceinline__ int flow_line(int idx, int n) { return idx == 0 ? 0 : (idx == 1 ? n - 1 : idx - 1); }
 
+// A block's work items in order: (pass, position in the pass).  Every role of the block walks the same sequence.
+struct FlowIter {
+  int p, idx;
+  __device__ __forceinline__ void skip(const FlowParams& P) {
+    while (p < P.npass && idx >= P.nlines[(P.colour0 + p) & 1]) ++p;
+  }
+  __device__ __forceinline__ void init(const FlowParams& P) {
+    p = 0;
+    idx = blockIdx.x;
+    skip(P);
+  }
+  __device__ __forceinline__ bool done(const FlowParams& P) const { return p >= P.npass; }
+  __device__ __forceinline__ int colour(const FlowParams& P) const { return (P.colour0 + p) & 1; }
+  __device__ __forceinline__ int line(const FlowParams& P) const {
+    const int c = (P.colour0 + p) & 1;
+    return P.i_first[c] + 2 * flow_line(idx, P.nlines[c]);
+  }
+  __device__ __forceinline__ void next(const FlowParams& P) {
+    idx += (int)gridDim.x;
+    if (idx >= P.nlines[(P.colour0 + p) & 1]) {
+      idx = blockIdx.x;
+      ++p;
+      skip(P);
+    }
+  }
+};
+
+__device__ __forceinline__ int lds_acquire(unsigned addr) {
+  int v;
+  asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_release(unsigned addr, int v) {
+  asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// Block = T consumer threads + a producer warp + a helper warp:
+//   consumers        eliminate / reduce / back-substitute the line whose slices the ring delivers (as k_tdma_tma)
+//   producer lane 0  issues the bulk copies (TMA) of the next slices as ring slots free up, across lines and passes
+//   helper lane 0    "acquirer": for each coming line waits (acquire) for the flags of its two neighbour lines from the
+//                    previous pass and tells the producer through a shared-memory counter -- the polls' latency stays
+//                    off the producer's issue loop
+//   helper lane 1    "publisher": once the consumers have stored a line (shared-memory counter, after a block barrier)
+//                    it releases the line's flag at GPU scope and, for a slab-edge line, the neighbouring GPU's flag at
+//                    system scope -- the fence that makes the stores visible costs about a microsecond, which nobody
+//                    on the critical path waits for
 template <int M, int BMAX, int NC>
 __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const int S) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -81,12 +127,16 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
   double* bufB = bufA + 3 * T;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(bufB + 3 * T);
   const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S);
+  int* counters = reinterpret_cast<int*>(bars + 2 * S);      // [0] lines acquired, [1] lines stored
+  const unsigned acq32 = smem_u32(counters), sto32 = smem_u32(counters + 1);
   const int ncw = T / 32;
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, ncw);
     }
+    counters[0] = 0;
+    counters[1] = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     // tell both neighbours that every earlier reader of this GPU's halo lines is done (stream order): they may store
@@ -97,43 +147,70 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
   }
   __syncthreads();
 
+  if (tid >= T + 32) {
+    // ---------------- helper warp ---------------------------------------------------------------------------
+    const int hl = tid - (T + 32);
+    if (hl == 0) {
+      // acquirer
+      FlowIter it;
+      int n = 0;
+      for (it.init(P); !it.done(P); it.next(P), ++n) {
+        if (it.p > 0) {
+          const int i0 = it.line(P), oc = it.colour(P) ^ 1, want = P.epoch0 + it.p - 1;
+          for (int nb = i0 - 1; nb <= i0 + 1; nb += 2) {
+            if (nb < P.wait_lo[oc] || nb > P.wait_hi[oc]) continue;
+            if (nb == P.halo_line[0] || nb == P.halo_line[1]) wait_flag<true>(P.flags + nb, want, P.abort_flag);
+            else wait_flag<false>(P.flags + nb, want, P.abort_flag);
+          }
+        }
+        sts_release(acq32, n + 1);
+      }
+    } else if (hl == 1) {
+      // publisher
+      FlowIter it;
+      int n = 0;
+      for (it.init(P); !it.done(P); it.next(P), ++n) {
+        while (lds_acquire(sto32) - (n + 1) < 0) __nanosleep(20);
+        const int i0 = it.line(P), epoch = P.epoch0 + it.p;
+        const int side = (i0 == P.edge_line[0]) ? 0 : ((i0 == P.edge_line[1]) ? 1 : -1);
+        if (side >= 0 && P.peer_phi[side]) {
+          __threadfence_system();
+          st_release_sys(P.peer_flag[side], epoch);
+        }
+        st_release_gpu(P.flags + i0, epoch);
+      }
+    }
+    return;
+  }
+
   if (tid >= T) {
     // ---------------- producer warp ---------------------------------------------------------------------
     if (tid == T) {
       const unsigned slice_bytes = (unsigned)(T * sizeof(double));
       unsigned rs = 0, rph = 0;
-      for (int p = 0; p < P.npass; ++p) {
-        const int c = (P.colour0 + p) & 1, oc = c ^ 1;
-        const bool zeroEW = P.first && p == 0;
+      FlowIter it;
+      int n = 0;
+      for (it.init(P); !it.done(P); it.next(P), ++n) {
+        const bool zeroEW = P.first && it.p == 0;
         const unsigned tx = slice_bytes * ((unsigned)nc + (zeroEW ? 0u : 2u));
-        const int nl = P.nlines[c];
-        for (int idx = blockIdx.x; idx < nl; idx += gridDim.x) {
-          const int i0 = P.i_first[c] + 2 * flow_line(idx, nl);
-          if (p > 0) {
-            // the neighbour lines were rewritten by the previous pass: wait until both are complete
-            const int want = P.epoch0 + p - 1;
-            for (int nb = i0 - 1; nb <= i0 + 1; nb += 2) {
-              if (nb < P.wait_lo[oc] || nb > P.wait_hi[oc]) continue;
-              if (nb == P.halo_line[0] || nb == P.halo_line[1]) wait_flag<true>(P.flags + nb, want, P.abort_flag);
-              else wait_flag<false>(P.flags + nb, want, P.abort_flag);
-            }
-            asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes (other SMs / peer GPU) -> bulk-copy reads
-          }
-          const double* csrc = P.coef + (long long)i0 * P.L.cSL;
-          const double* esrc = P.phi + (long long)(i0 + 1) * LD;
-          const double* wsrc = P.phi + (long long)(i0 - 1) * LD;
-          for (int k = 0; k < M; ++k) {
-            const unsigned s = rs, ph = rph;
-            if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
-            mbar_wait(empty0 + 8 * s, ph ^ 1u);
-            const unsigned fb = full0 + 8 * s;
-            const unsigned dst = smem_u32(ring + (size_t)s * SW);
-            mbar_expect_tx(fb, tx);
-            tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, nc * slice_bytes, fb);
-            if (!zeroEW) {
-              tma_load_1d(dst + nc * slice_bytes, esrc + (size_t)k * T, slice_bytes, fb);
-              tma_load_1d(dst + (nc + 1) * slice_bytes, wsrc + (size_t)k * T, slice_bytes, fb);
-            }
+        const int i0 = it.line(P);
+        // the neighbour lines were rewritten by the previous pass: the acquirer has seen both complete
+        while (lds_acquire(acq32) - (n + 1) < 0) __nanosleep(20);
+        if (it.p > 0) asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes (other SMs / peer GPU) -> bulk-copy reads
+        const double* csrc = P.coef + (long long)i0 * P.L.cSL;
+        const double* esrc = P.phi + (long long)(i0 + 1) * LD;
+        const double* wsrc = P.phi + (long long)(i0 - 1) * LD;
+        for (int k = 0; k < M; ++k) {
+          const unsigned s = rs, ph = rph;
+          if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+          mbar_wait(empty0 + 8 * s, ph ^ 1u);
+          const unsigned fb = full0 + 8 * s;
+          const unsigned dst = smem_u32(ring + (size_t)s * SW);
+          mbar_expect_tx(fb, tx);
+          tma_load_1d(dst, csrc + (size_t)k * P.L.cSK, nc * slice_bytes, fb);
+          if (!zeroEW) {
+            tma_load_1d(dst + nc * slice_bytes, esrc + (size_t)k * T, slice_bytes, fb);
+            tma_load_1d(dst + (nc + 1) * slice_bytes, wsrc + (size_t)k * T, slice_bytes, fb);
           }
         }
       }
@@ -154,188 +231,150 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
   const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.jhi + 1, M, T);
   unsigned rs = 0, rph = 0;
   bool peer_open[2] = {false, false};   // this launch has seen the neighbour's ready mark
-  // A finished line is published (flag = epoch) by ONE thread after a block barrier: the barrier orders every thread's
-  // stores before that thread's release, which is cumulative.  Releasing right after the stores would wait for them to
-  // drain (about a microsecond per line, with the whole block behind the next barrier); instead the release is issued
-  // one line later, after the first barrier of the next line's reduction, when those stores are long complete.  The
-  // last line a block solves in a pass is published at once: lines of the next pass wait for it.
-  int pend_line = -1, pend_epoch = 0;
-  // this block's work items in order: (pass, position); the Dirichlet end values of a line are fetched one item ahead
-  int p = 0, idx = blockIdx.x;
-  while (p < P.npass && idx >= P.nlines[(P.colour0 + p) & 1]) ++p;
+  FlowIter it;
+  it.init(P);
+  // Dirichlet end values phi(i, jstart-1), phi(i, nj) of a line are fetched one item ahead (never written by a sweep:
+  // safe to read at any time)
   double bS = 0.0, bN = 0.0;
-  if (p < P.npass && !(P.first && p < 2)) {
-    const double* ph = P.phi + (long long)(P.i_first[(P.colour0 + p) & 1] + 2 * flow_line(idx, P.nlines[(P.colour0 + p) & 1])) * LD;
+  if (!it.done(P) && !(P.first && it.p < 2)) {
+    const double* ph = P.phi + (long long)it.line(P) * LD;
     bS = __ldg(ph + q_s);
     bN = __ldg(ph + q_n);
   }
-  while (p < P.npass) {
-    const int c = (P.colour0 + p) & 1;
-    const bool zeroEW = P.first && p == 0;
-    const int nl = P.nlines[c];
-    const int epoch = P.epoch0 + p;
-    {
-      const int i0 = P.i_first[c] + 2 * flow_line(idx, nl);
-      double* phi = P.phi + (long long)i0 * LD;
-      // next item of this block, and its end values phi(i, jstart-1), phi(i, nj) (never written by a sweep: safe to
-      // read at any time)
-      int np = p, nidx = idx + (int)gridDim.x;
-      if (nidx >= nl) {
-        nidx = blockIdx.x;
-        ++np;
-        while (np < P.npass && nidx >= P.nlines[(P.colour0 + np) & 1]) ++np;
-      }
-      double bS_next = 0.0, bN_next = 0.0;
-      if (np < P.npass && !(P.first && np < 2)) {
-        const int cn = (P.colour0 + np) & 1;
-        const double* ph = P.phi + (long long)(P.i_first[cn] + 2 * flow_line(nidx, P.nlines[cn])) * LD;
-        bS_next = __ldg(ph + q_s);
-        bN_next = __ldg(ph + q_n);
-      }
-      double ca[M], cc[M], cf[M];
-#pragma unroll
-      for (int k = 0; k < M; ++k) {
-        const unsigned s = rs, ph = rph;
-        if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
-        mbar_wait(full0 + 8 * s, ph);
-        const unsigned sl = ring32 + s * stage_bytes;
-        double a = lds_f64(sl), b = lds_f64(sl + T8), d = 1.0;
-        unsigned sr = sl + 2 * T8;
-        if (nc == 6) {
-          d = lds_f64(sr);
-          sr += T8;
-        }
-        double cv = lds_f64(sr + 2 * T8);
-        if (!zeroEW) {
-          cv = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), cv);
-          cv = fma(lds_f64(sr), lds_f64(sr + 3 * T8), cv);
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty0 + 8 * s);
-        const int j0 = j0base + k;
-        if (!(j0 >= P.jlo && j0 <= P.jhi)) {
-          a = 0.0;
-          b = 0.0;
-          d = 1.0;
-          cv = (j0 == P.jlo - 1) ? bS : ((j0 == P.jhi + 1) ? bN : 0.0);
-        }
-        if (k == 0) {
-          const double inv = rcp_nr(d);
-          ca[0] = a * inv;
-          cc[0] = cv * inv;
-          cf[0] = b * inv;
-        } else {
-          const double inv = rcp_nr(fma(-b, ca[k > 0 ? k - 1 : 0], d));
-          ca[k] = a * inv;
-          cc[k] = fma(b, cc[k > 0 ? k - 1 : 0], cv) * inv;
-          cf[k] = b * cf[k > 0 ? k - 1 : 0] * inv;
-        }
-      }
-#pragma unroll
-      for (int k = M - 3; k >= 0; --k) {
-        cc[k] = fma(ca[k], cc[k + 1], cc[k]);
-        cf[k] = fma(ca[k], cf[k + 1], cf[k]);
-        ca[k] = ca[k] * ca[k + 1];
-      }
-      double l, u, r;
-      if (M == 1) {
-        l = cf[0];
-        u = ca[0];
-        r = cc[0];
-      } else {
-        bufB[t] = cc[0];
-        bufB[T + t] = cf[0];
-        bufB[2 * T + t] = ca[0];
-        consumer_sync(T);
-        double ncc = 0.0, ncf = 0.0, ng = 0.0;
-        if (t + 1 < T) {
-          ncc = bufB[t + 1];
-          ncf = bufB[T + t + 1];
-          ng = bufB[2 * T + t + 1];
-        }
-        const double inv = rcp_nr(fma(-ca[M - 1], ncf, 1.0));
-        l = cf[M - 1] * inv;
-        u = ca[M - 1] * ng * inv;
-        r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
-      }
-      double* cur = bufA;
-      double* nxt = bufB;
-      cur[t] = l;
-      cur[T + t] = u;
-      cur[2 * T + t] = r;
-      consumer_sync(T);
-      if (pend_line >= 0) {                    // the previous line's stores were issued a whole line ago
-        if (t == 0) st_release_gpu(P.flags + pend_line, pend_epoch);
-        pend_line = -1;
-      }
-      for (int sft = 1; sft < T; sft <<= 1) {
-        double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
-        if (t - sft >= 0) {
-          lm = cur[t - sft];
-          um = cur[T + t - sft];
-          rm = cur[2 * T + t - sft];
-        }
-        if (t + sft < T) {
-          lp = cur[t + sft];
-          up = cur[T + t + sft];
-          rp = cur[2 * T + t + sft];
-        }
-        const double inv = rcp_nr(fma(-l, um, fma(-u, lp, 1.0)));
-        r = fma(l, rm, fma(u, rp, r)) * inv;
-        l = l * lm * inv;
-        u = u * up * inv;
-        nxt[t] = l;
-        nxt[T + t] = u;
-        nxt[2 * T + t] = r;
-        consumer_sync(T);
-        double* tmp = cur;
-        cur = nxt;
-        nxt = tmp;
-      }
-      const double xe = r;
-      const double xp = (t > 0) ? cur[2 * T + t - 1] : 0.0;
-      // a slab-edge line also goes into the neighbour's halo line (peer memory)
-      const int side = (i0 == P.edge_line[0]) ? 0 : ((i0 == P.edge_line[1]) ? 1 : -1);
-      double* rphi = nullptr;
-      if (side >= 0 && P.peer_phi[side]) {
-        if (!peer_open[side]) {
-          // the neighbour must have launched this same sweep kernel (its earlier readers of the halo are then done)
-          if (t == 0) wait_flag(P.ready + side, P.epoch0, P.abort_flag);
-          consumer_sync(T);
-          peer_open[side] = true;
-        }
-        rphi = P.peer_phi[side];
-      }
-#pragma unroll
-      for (int k = 0; k < M; ++k) {
-        const int j0 = j0base + k;
-        if (j0 >= P.jlo && j0 <= P.jhi) {
-          const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
-          phi[k * T + t] = xk;
-          if (rphi) rphi[k * T + t] = xk;
-        }
-      }
-      const bool last_of_pass = np != p;
-      if (rphi || last_of_pass) {
-        // a slab-edge line (the neighbouring GPU waits for it) or the block's last line of the pass: publish now
-        consumer_sync(T);   // every thread's stores precede thread 0's release; the PCR buffers are free again
-        if (t == 0) {
-          if (rphi) {
-            __threadfence_system();
-            st_release_sys(P.peer_flag[side], epoch);
-          }
-          st_release_gpu(P.flags + i0, epoch);
-        }
-      } else {
-        consumer_sync(T);   // the PCR buffers are reused by the next line
-        pend_line = i0;
-        pend_epoch = epoch;
-      }
-      p = np;
-      idx = nidx;
-      bS = bS_next;
-      bN = bN_next;
+  for (int n = 0; !it.done(P); ++n) {
+    const bool zeroEW = P.first && it.p == 0;
+    const int i0 = it.line(P);
+    double* phi = P.phi + (long long)i0 * LD;
+    it.next(P);
+    double bS_next = 0.0, bN_next = 0.0;
+    if (!it.done(P) && !(P.first && it.p < 2)) {
+      const double* ph = P.phi + (long long)it.line(P) * LD;
+      bS_next = __ldg(ph + q_s);
+      bN_next = __ldg(ph + q_n);
     }
+    double ca[M], cc[M], cf[M];
+#pragma unroll
+    for (int k = 0; k < M; ++k) {
+      const unsigned s = rs, ph = rph;
+      if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+      mbar_wait(full0 + 8 * s, ph);
+      const unsigned sl = ring32 + s * stage_bytes;
+      double a = lds_f64(sl), b = lds_f64(sl + T8), d = 1.0;
+      unsigned sr = sl + 2 * T8;
+      if (nc == 6) {
+        d = lds_f64(sr);
+        sr += T8;
+      }
+      double cv = lds_f64(sr + 2 * T8);
+      if (!zeroEW) {
+        cv = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), cv);
+        cv = fma(lds_f64(sr), lds_f64(sr + 3 * T8), cv);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      const int j0 = j0base + k;
+      if (!(j0 >= P.jlo && j0 <= P.jhi)) {
+        a = 0.0;
+        b = 0.0;
+        d = 1.0;
+        cv = (j0 == P.jlo - 1) ? bS : ((j0 == P.jhi + 1) ? bN : 0.0);
+      }
+      if (k == 0) {
+        const double inv = rcp_nr(d);
+        ca[0] = a * inv;
+        cc[0] = cv * inv;
+        cf[0] = b * inv;
+      } else {
+        const double inv = rcp_nr(fma(-b, ca[k > 0 ? k - 1 : 0], d));
+        ca[k] = a * inv;
+        cc[k] = fma(b, cc[k > 0 ? k - 1 : 0], cv) * inv;
+        cf[k] = b * cf[k > 0 ? k - 1 : 0] * inv;
+      }
+    }
+#pragma unroll
+    for (int k = M - 3; k >= 0; --k) {
+      cc[k] = fma(ca[k], cc[k + 1], cc[k]);
+      cf[k] = fma(ca[k], cf[k + 1], cf[k]);
+      ca[k] = ca[k] * ca[k + 1];
+    }
+    double l, u, r;
+    if (M == 1) {
+      l = cf[0];
+      u = ca[0];
+      r = cc[0];
+    } else {
+      bufB[t] = cc[0];
+      bufB[T + t] = cf[0];
+      bufB[2 * T + t] = ca[0];
+      consumer_sync(T);
+      double ncc = 0.0, ncf = 0.0, ng = 0.0;
+      if (t + 1 < T) {
+        ncc = bufB[t + 1];
+        ncf = bufB[T + t + 1];
+        ng = bufB[2 * T + t + 1];
+      }
+      const double inv = rcp_nr(fma(-ca[M - 1], ncf, 1.0));
+      l = cf[M - 1] * inv;
+      u = ca[M - 1] * ng * inv;
+      r = fma(ca[M - 1], ncc, cc[M - 1]) * inv;
+    }
+    double* cur = bufA;
+    double* nxt = bufB;
+    cur[t] = l;
+    cur[T + t] = u;
+    cur[2 * T + t] = r;
+    consumer_sync(T);
+    for (int sft = 1; sft < T; sft <<= 1) {
+      double lm = 0.0, um = 0.0, rm = 0.0, lp = 0.0, up = 0.0, rp = 0.0;
+      if (t - sft >= 0) {
+        lm = cur[t - sft];
+        um = cur[T + t - sft];
+        rm = cur[2 * T + t - sft];
+      }
+      if (t + sft < T) {
+        lp = cur[t + sft];
+        up = cur[T + t + sft];
+        rp = cur[2 * T + t + sft];
+      }
+      const double inv = rcp_nr(fma(-l, um, fma(-u, lp, 1.0)));
+      r = fma(l, rm, fma(u, rp, r)) * inv;
+      l = l * lm * inv;
+      u = u * up * inv;
+      nxt[t] = l;
+      nxt[T + t] = u;
+      nxt[2 * T + t] = r;
+      consumer_sync(T);
+      double* tmp = cur;
+      cur = nxt;
+      nxt = tmp;
+    }
+    const double xe = r;
+    const double xp = (t > 0) ? cur[2 * T + t - 1] : 0.0;
+    // a slab-edge line also goes into the neighbour's halo line (peer memory)
+    const int side = (i0 == P.edge_line[0]) ? 0 : ((i0 == P.edge_line[1]) ? 1 : -1);
+    double* rphi = nullptr;
+    if (side >= 0 && P.peer_phi[side]) {
+      if (!peer_open[side]) {
+        // the neighbour must have launched this same sweep kernel (its earlier readers of the halo are then done)
+        if (t == 0) wait_flag(P.ready + side, P.epoch0, P.abort_flag);
+        consumer_sync(T);
+        peer_open[side] = true;
+      }
+      rphi = P.peer_phi[side];
+    }
+#pragma unroll
+    for (int k = 0; k < M; ++k) {
+      const int j0 = j0base + k;
+      if (j0 >= P.jlo && j0 <= P.jhi) {
+        const double xk = (k == M - 1) ? xe : fma(cf[k], xp, fma(ca[k], xe, cc[k]));
+        phi[k * T + t] = xk;
+        if (rphi) rphi[k * T + t] = xk;
+      }
+    }
+    consumer_sync(T);   // every thread's stores precede the publisher's release; the PCR buffers are free again
+    if (t == 0) sts_release(sto32, n + 1);
+    bS = bS_next;
+    bN = bN_next;
   }
 }
 
@@ -382,15 +421,15 @@ __global__ void k_flow_ready(int* r0, int* r1, int epoch0) {
 
 template <int M>
 static cudaError_t launch_flow_m(cfd_ctx* c, const FlowParams& P, int nblocks, int S, size_t smem) {
-  const int nthreads = P.L.T + 32;
+  const int nthreads = P.L.T + 64;   // consumers + producer warp + helper warp
   void* args[2] = {(void*)&P, (void*)&S};
   cudaError_t e;
   // cooperative launch: every block must be resident, since blocks wait for lines other blocks publish
 #define LAUNCH_FLOW(NCV)                                                                                        \
   {                                                                                                             \
-    e = cfd_raise_smem(c, k_tdma_flow<M, 352, NCV>);                                                            \
+    e = cfd_raise_smem(c, k_tdma_flow<M, 384, NCV>);                                                            \
     if (e == cudaSuccess)                                                                                       \
-      e = cudaLaunchCooperativeKernel((const void*)k_tdma_flow<M, 352, NCV>, dim3(nblocks), dim3(nthreads), args, \
+      e = cudaLaunchCooperativeKernel((const void*)k_tdma_flow<M, 384, NCV>, dim3(nblocks), dim3(nthreads), args, \
                                       smem, c->stream);                                                         \
   }
   if (P.L.nc == 5) LAUNCH_FLOW(5) else LAUNCH_FLOW(6)
@@ -510,8 +549,8 @@ int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int ns
   int S = 16;
   const char* es = getenv("CFD_B200_TDMA_STAGES");
   if (es && atoi(es) > 0) S = atoi(es);
-  while (S > 1 && S * stage + pcr + 2 * S * 8 > 220 * 1024) --S;
-  const size_t smem = S * stage + pcr + 2 * (size_t)S * 8;
+  while (S > 1 && S * stage + pcr + 2 * S * 8 + 16 > 220 * 1024) --S;
+  const size_t smem = S * stage + pcr + 2 * (size_t)S * 8 + 16;
   int nmax = P.nlines[0] > P.nlines[1] ? P.nlines[0] : P.nlines[1];
   const int nblocks = nmax < c->num_sms ? nmax : c->num_sms;
   cudaError_t e = cudaSuccess;

@@ -463,3 +463,36 @@ def test_device_side_postprocessing(cfd, oracle, shape):
     g.reference_pressure()
     assert np.array_equal(g.download("p"), tecplot.corner_pressure(o.p, g.ipref, g.jpref))
     g.close()
+
+
+def test_scaled_and_stationary_stop_rules(cfd, oracle):
+    """The literal rule max(res) < 1e-10 (cavity_fvm.f90:565) is an un-normalised sum over all cells; the scaled rule
+    divides by cells x per-cell flux and the stationary rule waits for the floating-point fixed point.  All three
+    must stop on the reference's converged solution; the scaled residual at the literal stopping point must not
+    depend on the grid size by more than the problem's own conditioning (here: within a factor 30 from 10^2 to 64^2)."""
+    o = oracle.Cavity(32, 32, 100.0)
+    o.run()
+    scaled_at_literal_stop = {}
+    for cv in (10, 32, 64):
+        g = cfd.CavityFVM(cv, cv, order="redblack")
+        g.init_lid_driven(reynolds=100.0)
+        g.run(check_every=2)
+        ru, rv, rm = g.iterate(1)
+        scaled_at_literal_stop[cv] = max(ru, rv, rm) / (cv * cv * 1000.0 / cv)
+        g.close()
+    v = list(scaled_at_literal_stop.values())
+    assert max(v) / min(v) < 30.0 and max(v) < 1e-12, scaled_at_literal_stop
+    g = cfd.CavityFVM(32, 32, order="redblack")
+    g.init_lid_driven(reynolds=100.0)
+    n_scaled = g.run(rule="scaled", tol=3.0e-14, check_every=2)
+    assert 1500 < n_scaled < 2600
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-8, name
+    n_more = g.run(rule="stationary", check_every=50, maxit=20000)
+    if n_more < 20000:                                   # it stopped: the monitor node no longer moves at all
+        a = tuple(g.probe(f, g.imon, g.jmon) for f in ("u", "v", "p"))
+        g.iterate(50)
+        assert a == tuple(g.probe(f, g.imon, g.jmon) for f in ("u", "v", "p"))
+    for name in ("u", "v", "p"):
+        assert linf_rel(g.download(name), getattr(o, name)) < 1e-8, name
+    g.close()
