@@ -217,17 +217,19 @@ def parity_check(kind, slabs="i", iters=6):
     import cfd_b200
     from cfd_b200.dist import BuoyancySlab, JSlabCavity, SlabCavity, TeachSlab
     world, rank = dist.get_world_size(), dist.get_rank()
+    # lines of 2050 nodes: a layout (160 threads x 13 nodes) the flag-ordered sweep kernel takes, so that the check runs
+    # over the same halo path (peer memory or NCCL) as the timed run
     if kind == "buoyancy":
-        n = 1026
+        n = 2050
         shape = (n, n)
         s = SlabCavity(n - 2, n - 2, slab_cls=BuoyancySlab)
         single = (lambda: cfd_b200.BuoyantCavity(n, n, order="redblack")) if rank == 0 else None
     elif kind == "step":
-        shape = (64 * world + 2, 1026)
+        shape = (64 * world + 2, 2050)
         s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab, epsx=1.0)
         single = (lambda: cfd_b200.TeachFVM(shape[0], shape[1], epsx=1.0, order="redblack")) if rank == 0 else None
     else:
-        shape = (64 * world, 1024) if slabs == "i" else (96, 256 * world)
+        shape = (64 * world, 2048) if slabs == "i" else (96, 256 * world)
         s = (SlabCavity if slabs == "i" else JSlabCavity)(*shape, reynolds=REYNOLDS)
 
         def single():
@@ -235,6 +237,7 @@ def parity_check(kind, slabs="i", iters=6):
             g.init_lid_driven(reynolds=REYNOLDS)
             return g
     s.iterate(iters)
+    halo_path = "peer memory" if getattr(s, "peer", False) else "NCCL"
     names = ("u", "v", "p") + (("t",) if kind == "buoyancy" else ())
     got = {n: s.gather_field(n) for n in names}
     s.ctx.close()
@@ -251,7 +254,7 @@ def parity_check(kind, slabs="i", iters=6):
         g.close()
         tol = 0.0 if slabs == "i" else 1e-10 * max(1.0, scale)
         rec = {"world": world, "case": f"{kind} {shape[0]}x{shape[1]}, {iters} outer iterations, {slabs}-slabs vs one context",
-               "fields": list(names), "bitwise": bitwise, "max_abs": max_abs, "tolerance": tol,
+               "halo_path": halo_path, "fields": list(names), "bitwise": bitwise, "max_abs": max_abs, "tolerance": tol,
                "ok": bool(bitwise if slabs == "i" else max_abs <= tol)}
     flag = torch.tensor([1 if (rec is None or rec["ok"]) else 0], device="cuda")
     dist.broadcast(flag, 0)

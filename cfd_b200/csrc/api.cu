@@ -211,6 +211,12 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->res_dev = nullptr;
   c->seq_scratch = nullptr;
   c->launches = 0;
+  c->uni_den = c->uni_vis = false;
+  c->den0 = c->vis0 = 0.0;
+  {
+    const char* e = getenv("CFD_B200_UNIFORM");      // read per context: tests switch it between contexts
+    c->allow_uniform = !(e && atoi(e) == 0);
+  }
   c->flags = nullptr;
   c->post_buf = nullptr;
   c->post_n = 0;
@@ -428,6 +434,22 @@ static int ensure_stage(cfd_ctx* c) {
   return CFD_OK;
 }
 
+// cavity family: remember whether an uploaded den / vis image holds a single value (then the production assembly
+// kernels read it as a scalar, cavity_tma_kernels.cu).  The reference's driver fills both by whole-array assignment
+// (cavity_fvm.f90:536-537), so this is the usual case; any non-uniform upload switches the field path back on.
+static void note_uniform(cfd_ctx* c, int field, const double* host, int ld) {
+  if (c->cfg.family != CFD_FAMILY_CAVITY || (field != CFD_DEN && field != CFD_VIS)) return;
+  const double v0 = host[0];
+  bool uni = c->allow_uniform;
+  for (int j = 0; j < c->L.nj && uni; ++j) {
+    const double* row = host + (size_t)j * ld;
+    for (int i = 0; i < c->L.ni; ++i)
+      if (row[i] != v0) { uni = false; break; }
+  }
+  if (field == CFD_DEN) { c->uni_den = uni; c->den0 = v0; }
+  else { c->uni_vis = uni; c->vis0 = v0; }
+}
+
 static int check_field(const cfd_ctx* c, int field) {
   if (field < 0 || field >= CFD_FIELD_COUNT || !c->field[field]) {
     cfd_set_error("field id %d is not allocated in this context", field);
@@ -445,6 +467,7 @@ extern "C" int cfd_upload(cfd_ctx* c, int field, const double* host, int ld) {
   if ((rc = ensure_stage(c))) return rc;
   CFD_CUDA(cudaMemcpy2DAsync(c->stage, (size_t)c->L.ni * sizeof(double), host, (size_t)ld * sizeof(double),
                              (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyHostToDevice, c->stream));
+  note_uniform(c, field, host, ld);      // scans the host image while the copy is in flight
   if ((rc = cfd_launch_to_line_layout(c, c->stage, c->field[field], field))) return rc;
   CFD_CUDA(cudaStreamSynchronize(c->stream));
   return CFD_OK;
@@ -468,6 +491,7 @@ extern "C" int cfd_upload_noalloc(cfd_ctx* c, int field, const double* host, int
   // the image is overwritten completely (ni*nj doubles), so nothing left by an earlier call is ever read
   CFD_CUDA(cudaMemcpy2DAsync(stage, (size_t)c->L.ni * sizeof(double), host, (size_t)ld * sizeof(double),
                              (size_t)c->L.ni * sizeof(double), c->L.nj, cudaMemcpyHostToDevice, c->stream));
+  note_uniform(c, field, host, ld);
   if ((rc = cfd_launch_to_line_layout(c, stage, c->field[field], field))) return rc;
   CFD_CUDA(cudaStreamSynchronize(c->stream));
   return CFD_OK;

@@ -329,6 +329,7 @@ __global__ void __launch_bounds__(256) k_assemble_v(const CavParams P) {
 // ---------------------------------------------------------------------------------------------------
 // p' equation: cavity_fvm.f90:301-340 (pp = 0 of line 342 is folded into the first sweep)
 // ---------------------------------------------------------------------------------------------------
+template <bool UNI>
 __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
   const int M = P.L.M, T = P.L.T, nj = P.L.nj;
   const long long LD = P.L.LD;
@@ -349,18 +350,18 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
         const long long cout = (long long)i0 * P.L.cSL;
     const double sew_i = __ldg(P.sew + i0);
     Win3 wd, wv, wdv;
-    lc.init(wd, dC);
+    if (UNI) wd.m = wd.c = wd.p = P.den0; else lc.init(wd, dC);
     lc.init(wv, vC);
     lc.init(wdv, dvC);
     for (int k = 0; k < M; ++k) {
       const int j0 = lc.j0base + k;
-      lc.fetch(wd, dC, k);
+      if (!UNI) lc.fetch(wd, dC, k);
       lc.fetch(wv, vC, k);
       lc.fetch(wdv, dvC, k);
       if (j0 >= P.jlo && j0 <= P.jhi) {
         const int q = lc.pos(k);
         const int cq = k * P.L.cSK + t;
-        const double den_w = __ldg(dW + q), den_e = __ldg(dE + q);
+        const double den_w = UNI ? P.den0 : __ldg(dW + q), den_e = UNI ? P.den0 : __ldg(dE + q);
         const double u_c = __ldg(uC + q), u_e = __ldg(uE + q);
         const double du_c = __ldg(duC + q), du_e = __ldg(duE + q);
         const double sns_j = __ldg(P.snsL + q);
@@ -394,7 +395,7 @@ __global__ void __launch_bounds__(256) k_assemble_p(const CavParams P) {
           P.su[cout + cq] = -smp * r;
         }
       }
-      LineCursor::shift(wd);
+      if (!UNI) LineCursor::shift(wd);
       LineCursor::shift(wv);
       LineCursor::shift(wdv);
     }
@@ -478,6 +479,10 @@ static void fill_common(const cfd_ctx* c, CavParams& P) {
   P.p = c->field[CFD_P];
   P.den = c->field[CFD_DEN];
   P.vis = c->field[CFD_VIS];
+  // production kernels only: both property fields hold one value each (cfd_upload saw it)
+  P.uniform = (!c->exact_assembly && c->uni_den && c->uni_vis) ? 1 : 0;
+  P.den0 = c->den0;
+  P.vis0 = c->vis0;
   P.du_in = c->field[CFD_DU];
   P.dv_in = c->field[CFD_DV];
   P.ae = c->field[CFD_AE];
@@ -541,7 +546,8 @@ static int launch_assemble(cfd_ctx* c, int which, CavParams& P, int eq) {
     } else if (which == 1) {
       k_assemble_v<<<grid, block, 0, c->stream>>>(P);
     } else {
-      k_assemble_p<<<grid, block, 0, c->stream>>>(P);
+      if (P.uniform) k_assemble_p<true><<<grid, block, 0, c->stream>>>(P);
+      else k_assemble_p<false><<<grid, block, 0, c->stream>>>(P);
     }
     ++c->launches;
     CFD_CUDA(cudaGetLastError());

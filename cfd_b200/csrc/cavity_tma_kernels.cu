@@ -61,13 +61,21 @@ __device__ __forceinline__ void consumer_sum_to(double v, double* red, int T, in
 // =====================================================================================================
 #define NU_ARR 13
 #define ASM_PRODUCER_WARPS 2   // bulk-copy issue is per-thread serial: 12-13 copies per slice need several issuers
-template <int BMAX>
+// UNI: den and vis are one value each in this context (CavParams::uniform): their six slices are not staged at all, the
+// stage holds the other seven arrays back to back, and every den / vis operand below is the scalar.
+__host__ __device__ constexpr bool u_is_prop(int a) { return (a >= 3 && a <= 6) || a == 9 || a == 10; }
+__host__ __device__ constexpr int u_slot(int a, bool uni) {
+  return !uni ? a : (a <= 2 ? a : (a == 7 ? 3 : (a == 8 ? 4 : (a == 11 ? 5 : (a == 12 ? 6 : -1)))));
+}
+template <int BMAX, bool UNI>
 __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, const FastGeom G, const int S) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int T = P.L.T, M = P.L.M, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int tid = threadIdx.x;
-  const int SW = NU_ARR * T;
+  constexpr int NA = UNI ? 7 : NU_ARR;
+  const int SW = NA * T;
+  const double den0 = UNI ? P.den0 : 0.0, vis0 = UNI ? P.vis0 : 0.0;
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* red = ring + (size_t)S * SW;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(red + 32);
@@ -101,10 +109,13 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
           mbar_wait(empty0 + 8 * s, ph ^ 1u);
           const unsigned fb = full0 + 8 * s;
           const unsigned dst = smem_u32(ring + (size_t)s * SW);
-          if (pw == 0) mbar_expect_tx(fb, NU_ARR * sb);
+          if (pw == 0) mbar_expect_tx(fb, NA * sb);
 #pragma unroll
-          for (int a = 0; a < NU_ARR; ++a)
-            if ((a % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + a * sb, src[a] + (size_t)k * T, sb, fb);
+          for (int a = 0; a < NU_ARR; ++a) {
+            if (UNI && u_is_prop(a)) continue;
+            const int sl = u_slot(a, UNI);
+            if ((sl % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + sl * sb, src[a] + (size_t)k * T, sb, fb);
+          }
         }
       }
     }
@@ -125,9 +136,9 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
   if ((int)blockIdx.x < nlines && hasprev) {
     const long long i0 = P.ia + blockIdx.x;
     em_u = __ldg(P.u + i0 * LD + qprev);
-    em_dW = __ldg(P.den + (i0 - 1) * LD + qprev);
-    em_dC = __ldg(P.den + i0 * LD + qprev);
-    em_A = __ldg(P.vis + (i0 - 1) * LD + qprev) + __ldg(P.vis + i0 * LD + qprev);
+    em_dW = UNI ? den0 : __ldg(P.den + (i0 - 1) * LD + qprev);
+    em_dC = UNI ? den0 : __ldg(P.den + i0 * LD + qprev);
+    em_A = UNI ? vis0 + vis0 : __ldg(P.vis + (i0 - 1) * LD + qprev) + __ldg(P.vis + i0 * LD + qprev);
     em_rdy = __ldg(G.rdyL + qprev);
   }
   for (int line = blockIdx.x; line < nlines; line += gridDim.x) {
@@ -137,10 +148,10 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
     double ep_u = 0, ep_dW = 0, ep_dC = 0, ep_sW = 0, ep_sC = 0, ep_vW = 0, ep_vC = 0;
     if (hasnext) {
       ep_u = __ldg(P.u + i0 * LD + qnext);
-      ep_dW = __ldg(P.den + (i0 - 1) * LD + qnext);
-      ep_dC = __ldg(P.den + i0 * LD + qnext);
-      ep_sW = __ldg(P.vis + (i0 - 1) * LD + qnext);
-      ep_sC = __ldg(P.vis + i0 * LD + qnext);
+      ep_dW = UNI ? den0 : __ldg(P.den + (i0 - 1) * LD + qnext);
+      ep_dC = UNI ? den0 : __ldg(P.den + i0 * LD + qnext);
+      ep_sW = UNI ? vis0 : __ldg(P.vis + (i0 - 1) * LD + qnext);
+      ep_sC = UNI ? vis0 : __ldg(P.vis + i0 * LD + qnext);
       ep_vW = __ldg(P.v + (i0 - 1) * LD + qnext);
       ep_vC = __ldg(P.v + i0 * LD + qnext);
     }
@@ -148,9 +159,9 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
     if (line + (int)gridDim.x < nlines && hasprev) {
       const long long n0 = i0 + gridDim.x;
       nm_u = __ldg(P.u + n0 * LD + qprev);
-      nm_dW = __ldg(P.den + (n0 - 1) * LD + qprev);
-      nm_dC = __ldg(P.den + n0 * LD + qprev);
-      nm_A = __ldg(P.vis + (n0 - 1) * LD + qprev) + __ldg(P.vis + n0 * LD + qprev);
+      nm_dW = UNI ? den0 : __ldg(P.den + (n0 - 1) * LD + qprev);
+      nm_dC = UNI ? den0 : __ldg(P.den + n0 * LD + qprev);
+      nm_A = UNI ? vis0 + vis0 : __ldg(P.vis + (n0 - 1) * LD + qprev) + __ldg(P.vis + n0 * LD + qprev);
     }
     const double sewu_i = __ldg(P.sewu + i0), r_sewu_i = __ldg(G.rsewu + i0);
     const double r_dxe = __ldg(G.rdxu + i0), r_dxw = __ldg(G.rdxu + i0 - 1);
@@ -171,16 +182,16 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
         u_n = sl[0];
         vW_p = sl[T];
         vC_p = sl[2 * T];
-        dW_p = sl[3 * T];
-        dC_p = sl[4 * T];
-        sW_p = sl[5 * T];
-        sC_p = sl[6 * T];
-        n_uW = sl[7 * T];
-        n_uE = sl[8 * T];
-        n_dWW = sl[9 * T];
-        n_dE = sl[10 * T];
-        n_pW = sl[11 * T];
-        n_pC = sl[12 * T];
+        dW_p = UNI ? den0 : sl[3 * T];
+        dC_p = UNI ? den0 : sl[4 * T];
+        sW_p = UNI ? vis0 : sl[5 * T];
+        sC_p = UNI ? vis0 : sl[6 * T];
+        n_uW = sl[u_slot(7, UNI) * T];
+        n_uE = sl[u_slot(8, UNI) * T];
+        n_dWW = UNI ? den0 : sl[9 * T];
+        n_dE = UNI ? den0 : sl[10 * T];
+        n_pW = sl[u_slot(11, UNI) * T];
+        n_pC = sl[u_slot(12, UNI) * T];
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * s);
         const int q = k * T + t;
@@ -255,13 +266,19 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
 //   vC and dC need the node ahead (j+1): evaluated with one slice of lag; everything else looks back only.
 // =====================================================================================================
 #define NV_ARR 12
-template <int BMAX>
+__host__ __device__ constexpr bool v_is_prop(int a) { return a == 1 || (a >= 4 && a <= 8); }
+__host__ __device__ constexpr int v_slot(int a, bool uni) {
+  return !uni ? a : (a == 0 ? 0 : (a == 2 ? 1 : (a == 3 ? 2 : (a == 9 ? 3 : (a == 10 ? 4 : (a == 11 ? 5 : -1))))));
+}
+template <int BMAX, bool UNI>
 __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, const FastGeom G, const int S) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int T = P.L.T, M = P.L.M, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int tid = threadIdx.x;
-  const int SW = NV_ARR * T;
+  constexpr int NA = UNI ? 6 : NV_ARR;
+  const int SW = NA * T;
+  const double den0 = UNI ? P.den0 : 0.0, vis0 = UNI ? P.vis0 : 0.0;
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* red = ring + (size_t)S * SW;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(red + 32);
@@ -294,10 +311,13 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
           mbar_wait(empty0 + 8 * s, ph ^ 1u);
           const unsigned fb = full0 + 8 * s;
           const unsigned dst = smem_u32(ring + (size_t)s * SW);
-          if (pw == 0) mbar_expect_tx(fb, NV_ARR * sb);
+          if (pw == 0) mbar_expect_tx(fb, NA * sb);
 #pragma unroll
-          for (int a = 0; a < NV_ARR; ++a)
-            if ((a % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + a * sb, src[a] + (size_t)k * T, sb, fb);
+          for (int a = 0; a < NV_ARR; ++a) {
+            if (UNI && v_is_prop(a)) continue;
+            const int sl = v_slot(a, UNI);
+            if ((sl % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + sl * sb, src[a] + (size_t)k * T, sb, fb);
+          }
         }
       }
     }
@@ -321,15 +341,15 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
     Edge e{};
     if (hasprev) {
       e.v = __ldg(P.v + i0 * LD + qprev);
-      e.dC = __ldg(P.den + i0 * LD + qprev);
-      e.dCmm = (j0base >= 2) ? __ldg(P.den + i0 * LD + qprev2) : 0.0;
+      e.dC = UNI ? den0 : __ldg(P.den + i0 * LD + qprev);
+      e.dCmm = (j0base >= 2) ? (UNI ? den0 : __ldg(P.den + i0 * LD + qprev2)) : 0.0;
       e.uC = __ldg(P.u + i0 * LD + qprev);
       e.uE = __ldg(P.u + (i0 + 1) * LD + qprev);
-      e.dW = __ldg(P.den + (i0 - 1) * LD + qprev);
-      e.dE = __ldg(P.den + (i0 + 1) * LD + qprev);
-      e.sW = __ldg(P.vis + (i0 - 1) * LD + qprev);
-      e.sC = __ldg(P.vis + i0 * LD + qprev);
-      e.sE = __ldg(P.vis + (i0 + 1) * LD + qprev);
+      e.dW = UNI ? den0 : __ldg(P.den + (i0 - 1) * LD + qprev);
+      e.dE = UNI ? den0 : __ldg(P.den + (i0 + 1) * LD + qprev);
+      e.sW = UNI ? vis0 : __ldg(P.vis + (i0 - 1) * LD + qprev);
+      e.sC = UNI ? vis0 : __ldg(P.vis + i0 * LD + qprev);
+      e.sE = UNI ? vis0 : __ldg(P.vis + (i0 + 1) * LD + qprev);
       e.p = __ldg(P.p + i0 * LD + qprev);
     }
     return e;
@@ -343,7 +363,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
     double ep_v = 0, ep_dC = 0;
     if (hasnext) {
       ep_v = __ldg(P.v + i0 * LD + qnext);
-      ep_dC = __ldg(P.den + i0 * LD + qnext);
+      ep_dC = UNI ? den0 : __ldg(P.den + i0 * LD + qnext);
     }
     Edge nm{};
     if (line + (int)gridDim.x < nlines) nm = load_edge(i0 + gridDim.x);
@@ -366,17 +386,17 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
         mbar_wait(full0 + 8 * s, ph);
         const double* sl = ring + (size_t)s * SW + t;
         v_n = sl[0];
-        dC_p = sl[T];
-        n_uC = sl[2 * T];
-        n_uE = sl[3 * T];
-        n_dW = sl[4 * T];
-        n_dE = sl[5 * T];
-        n_sW = sl[6 * T];
-        n_sC = sl[7 * T];
-        n_sE = sl[8 * T];
-        n_p = sl[9 * T];
-        n_vW = sl[10 * T];
-        n_vE = sl[11 * T];
+        dC_p = UNI ? den0 : sl[T];
+        n_uC = sl[v_slot(2, UNI) * T];
+        n_uE = sl[v_slot(3, UNI) * T];
+        n_dW = UNI ? den0 : sl[4 * T];
+        n_dE = UNI ? den0 : sl[5 * T];
+        n_sW = UNI ? vis0 : sl[6 * T];
+        n_sC = UNI ? vis0 : sl[7 * T];
+        n_sE = UNI ? vis0 : sl[8 * T];
+        n_p = sl[v_slot(9, UNI) * T];
+        n_vW = sl[v_slot(10, UNI) * T];
+        n_vE = sl[v_slot(11, UNI) * T];
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * s);
         const int q = k * T + t;
@@ -459,9 +479,10 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
   G.rdxu = c->gfast[0]; G.rdx = c->gfast[1]; G.rsew = c->gfast[2]; G.rsewu = c->gfast[3];
   G.rdyL = c->gfast[4]; G.rdyvL = c->gfast[5]; G.rsnsL = c->gfast[6]; G.rsnsvL = c->gfast[7];
   const int num_sms = c->num_sms;
-  const int T = c->L.T, narr = which == 0 ? NU_ARR : NV_ARR;
+  const bool uni = P.uniform != 0;
+  const int T = c->L.T, narr = uni ? (which == 0 ? 7 : 6) : (which == 0 ? NU_ARR : NV_ARR);
   const size_t stage = (size_t)narr * T * sizeof(double);
-  int S = 8;
+  int S = uni ? 10 : 8;      // the uniform-property stage is about half as large: a deeper ring fits
   const char* es = getenv("CFD_B200_ASM_STAGES");
   if (es && atoi(es) > 0) S = atoi(es);
   while (S > 2 && S * stage + 32 * 8 + 2 * S * 8 > 200 * 1024) --S;
@@ -476,7 +497,11 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
     cfd_set_error("k_assemble_*_tma: lines of %d layout threads do not fit the 384-thread build", T);
     return CFD_ERR_INVALID;
   }
-  if (which == 0) { LAUNCH_ASM(k_assemble_u_tma<384>) } else { LAUNCH_ASM(k_assemble_v_tma<384>) }
+  if (which == 0) {
+    if (uni) { LAUNCH_ASM((k_assemble_u_tma<384, true>)) } else { LAUNCH_ASM((k_assemble_u_tma<384, false>)) }
+  } else {
+    if (uni) { LAUNCH_ASM((k_assemble_v_tma<384, true>)) } else { LAUNCH_ASM((k_assemble_v_tma<384, false>)) }
+  }
 #undef LAUNCH_ASM
   if (e != cudaSuccess) {
     cfd_set_error("k_assemble_*_tma: %s", cudaGetErrorString(e));

@@ -56,6 +56,10 @@ struct CavParams {
   const double *x, *xu, *sew, *sewu;
   const double *yL, *yvL, *snsL, *snsvL;
   double* partial;       // one residual partial per block
+  // uniform-property form (production kernels): den and vis hold one value each in every node of this context, so the
+  // kernels take them as scalars instead of streaming the two fields (same arithmetic on the same values: same bits)
+  int uniform;
+  double den0, vis0;
 };
 
 // Reciprocals of the 1-D geometry for the production assembly kernels (cavity_fast_kernels.cu); 0 where the
@@ -196,6 +200,9 @@ struct cfd_ctx {
   int* peer_flags[2];
   int peer_ni[2], peer_hw[2], peer_halo_line[2];
   std::vector<void*> ipc_opened;    // mappings made by cfd_ipc_open (closed by cfd_destroy)
+  // cavity family: value of den / vis if the last upload of the field was uniform over the whole local array
+  bool uni_den, uni_vis, allow_uniform;
+  double den0, vis0;
   double* post_buf;                 // result vector of the post-processing kernels (post_kernels.cu), sized on first use
   size_t post_n;
   int num_sms;                      // SM count of THIS context's device (persistent grids are sized from it)

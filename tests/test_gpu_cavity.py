@@ -496,3 +496,29 @@ def test_scaled_and_stationary_stop_rules(cfd, oracle):
     for name in ("u", "v", "p"):
         assert linf_rel(g.download(name), getattr(o, name)) < 1e-8, name
     g.close()
+
+
+@pytest.mark.parametrize("shape", [(64, 4096), (130, 2048), (40, 40)])
+def test_uniform_property_kernels_give_the_same_bits(cfd, shape, monkeypatch):
+    """The reference fills den and vis by whole-array assignment (cavity_fvm.f90:536-537).  When an uploaded den / vis
+    image holds one value, the production assembly kernels take it as a scalar instead of streaming the field
+    (cavity_tma_kernels.cu).  Same arithmetic on the same values: the iterates must be bit-identical to the field path."""
+    monkeypatch.setenv("CFD_B200_UNIFORM", "0")
+    a = cfd.CavityFVM(*shape, order="redblack")
+    monkeypatch.setenv("CFD_B200_UNIFORM", "1")
+    b = cfd.CavityFVM(*shape, order="redblack")
+    for g in (a, b):
+        g.init_lid_driven(reynolds=1000.0)
+    ra, rb = a.iterate(4), b.iterate(4)
+    assert ra == rb
+    for name in ("u", "v", "p", "pp", "du", "dv"):
+        assert np.array_equal(a.download(name), b.download(name)), name
+    # a non-uniform upload switches the field path back on
+    den = b.download("den")
+    den[3, 5] *= 1.5
+    a.upload("den", den)
+    b.upload("den", den)
+    assert a.iterate(2) == b.iterate(2)
+    assert np.array_equal(a.download("u"), b.download("u"))
+    a.close()
+    b.close()

@@ -112,11 +112,12 @@ def _nccl_worker(rank, world, port, shape, q, kind="i", peer=True):
 
 
 @pytest.mark.parametrize("kind,peer,shape", [("i", False, (96, 130)), ("j", False, (96, 130)), ("teach", False, (96, 130)),
-                                             ("buoyancy", False, (98, 98)), ("i", True, (96, 1024)),
-                                             ("teach", True, (98, 1026)), ("buoyancy", True, (1026, 1026))])
+                                             ("buoyancy", False, (98, 98)), ("i", True, (96, 2048)),
+                                             ("teach", True, (98, 2050)), ("buoyancy", True, (2050, 2050))])
 def test_nccl_slabs_match_single_context(cfd, kind, peer, shape):
     """One process per GPU.  peer=True: halo lines over peer memory (stores from inside the flag-ordered sweep kernels
-    and cfd_halo_push) -- lines of 1026 nodes, long enough for the TMA-staged kernels that path lives in; peer=False:
+    and cfd_halo_push) -- lines of 2050 nodes (160 layout threads x 13 nodes), long enough for the TMA-staged kernels that path
+    lives in; peer=False:
     the grouped NCCL send/recv stages."""
     import torch
     import torch.multiprocessing as mp
