@@ -576,13 +576,15 @@ def run_heat(args):
 
 
 def run_cavity16k(args):
-    """--workload cavity16k: north_star's "8 GPUs on 16384^2" case, STRONG scaling.  A line of 16386 nodes does not fit
-    one thread block's registers, so the lines are cut along j and solved with the partition method (j-slabs): N ranks
-    each hold 16384/N rows of every line.  N = 1 runs the same algorithm with two slabs on the one GPU."""
+    """--workload cavity16k: north_star's "8 GPUs on 16384^2" case, STRONG scaling (the global grid is fixed).  Default:
+    i-slabs -- every GPU owns 16384/N whole lines of 16386 nodes, solved by clusters of four thread blocks
+    (tdma_cluster_kernels.cu), halo lines over peer memory.  --slabs j: the lines themselves are cut across the GPUs and
+    solved with the partition method (N = 1 then runs two slabs on the one GPU)."""
     import torch
     import torch.distributed as dist
 
-    from cfd_b200.dist import JSlabCavity, LocalJSlabCavity
+    import cfd_b200
+    from cfd_b200.dist import JSlabCavity, LocalJSlabCavity, SlabCavity
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -593,15 +595,19 @@ def run_cavity16k(args):
     hbm_peak, peak_src = peaks()
     NG = 16384
     stream = torch.cuda.current_stream()
-    parity = None
+    parity, jcut = None, args.slabs == "j"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        parity = parity_check("cavity", "j")
-        solver = JSlabCavity(NG, NG, reynolds=REYNOLDS)
+        parity = parity_check("cavity", "j" if jcut else "i")
+        solver = JSlabCavity(NG, NG, reynolds=REYNOLDS) if jcut else SlabCavity(NG, NG, reynolds=REYNOLDS)
         step, ctx0 = solver.iterate_async, solver.ctx
-    else:
+    elif jcut:
         solver = LocalJSlabCavity(NG, NG, 2, reynolds=REYNOLDS)
         step, ctx0 = (lambda n: [solver._iterate_once() for _ in range(n)]), solver.slabs[0].ctx
+    else:
+        solver = cfd_b200.CavityFVM(NG, NG, order="redblack", device=local)
+        solver.init_lid_driven(reynolds=REYNOLDS)
+        step, ctx0 = solver.iterate_async, solver
 
     def barrier():
         torch.cuda.synchronize()
@@ -623,30 +629,40 @@ def run_cavity16k(args):
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
-    launches = (ctx0.launches - l0) * (2 if world == 1 else 1)
+    launches = (ctx0.launches - l0) * (2 if (world == 1 and jcut) else 1)
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
-        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        tms = torch.tensor([ms, 1.0 if ctx0.peer_status() else 0.0], device="cuda", dtype=torch.float64)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        ms = float(tms.item())
+        ms = float(tms[0].item())
+        if float(tms[1].item()) != 0.0:
+            raise SystemExit("bench.py: a wait on a neighbouring GPU timed out (peer halo path); the run is invalid")
         res = solver.residuals()
-    else:
+    elif jcut:
         res = tuple(sum(s.res.clone() for s in solver.slabs).cpu().tolist())
+    else:
+        res = solver.residuals()
     glups = NG * NG * K / (ms * 1e-3) / 1e9
+    if jcut:
+        par = (f"j-slabs x{world}: piece solves + spike vectors, all-gathered reduced system per line (NCCL), halo rows once "
+               "per iteration" if world > 1 else "single GPU, two j-slabs in one process (same algorithm, copies instead of messages)")
+    elif world > 1:
+        par = (f"i-slabs x{world}: {NG // world} whole lines of {NG + 2} nodes per GPU, each line solved by a cluster of thread "
+               "blocks; halo lines " + ("over peer memory (stores from inside the sweep kernels, cfd_halo_push)"
+                                        if getattr(solver, "peer", False) else "by NCCL send/recv"))
+    else:
+        par = "single GPU, whole lines solved by clusters of thread blocks"
     out = {"metric": "simple_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K,
            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic", "iters_per_s": K / (ms * 1e-3),
            "config": {"workload": f"lid-driven cavity FVM SIMPLE Re=1000, {NG}x{NG} CV in total, hybrid scheme, urf .5/.5/.8, "
-                                  "nswp 3/3/3, red/black lines cut along j (partitioned Thomas)",
-                      "parallelism": (f"j-slabs x{world}: piece solves + spike vectors, all-gathered reduced system per line "
-                                      "(NCCL), halo rows once per iteration" if world > 1 else
-                                      "single GPU, two j-slabs in one process (same algorithm, copies instead of messages)"),
-                      "l2": "inputs larger than L2; no explicit flush", "line_layout": ctx0.layout},
+                                  "nswp 3/3/3, red/black lines",
+                      "parallelism": par, "l2": "inputs larger than L2; no explicit flush", "line_layout": ctx0.layout},
            "residuals_last": [float(x) for x in res[:3]], "gpu_launches": int(launches),
            "roofline": {"bound": "hbm", "kernel": "whole outer iteration", "achieved": BYTES_PER_CELL_ITER * glups / world,
                         "peak": hbm_peak, "unit": "GB/s", "frac": BYTES_PER_CELL_ITER * glups / world / hbm_peak,
                         "peak_source": peak_src, "traffic": None,
-                        "note": "algorithmic bytes of the single-context algorithm (928 B/cell); the partition method moves more"},
+                        "note": "algorithmic bytes of the stored-coefficient algorithm (928 B/cell, SURVEY 8d)"},
            "e2e": None, "clocks": clocks}
     if parity is not None:
         out["parity_check"] = parity

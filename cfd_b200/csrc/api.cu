@@ -84,7 +84,8 @@ int cfd_launch_from_line_layout(cfd_ctx* c, const double* src, double* colmajor,
 // T threads per line (multiple of 32, <= 1024), M nodes per thread (<= CFD_MAX_M), T*M >= nj.  Among the
 // (M,T) pairs whose line-solver instantiation keeps its chunk in registers (ptxas: no spills) take the least
 // padding, ties to the larger M (less parallel-cyclic-reduction work per node); if none fits, least padding.
-static bool fits_registers(int m, int t) { return t <= 384 || (t <= 640 && m <= 9) || m <= 5; }
+// a layout whose lines split evenly over a cluster of blocks of <= 320 threads also fits (tdma_cluster_kernels.cu)
+static bool fits_registers(int m, int t) { return t <= 384 || (cfd_cluster_size(t) > 0 && m >= 4) || (t <= 640 && m <= 9) || m <= 5; }
 
 static int choose_layout(int ni, int nj, int want_m, Layout* L) {
   long best = -1;
@@ -93,8 +94,19 @@ static int choose_layout(int ni, int nj, int want_m, Layout* L) {
     for (int m = CFD_MAX_M; m >= 1; --m) {
       if (want_m > 0 && m != want_m) continue;
       int t = ((nj + m - 1) / m + 31) / 32 * 32;
-      if (t > 1024) continue;
-      if (pass == 0 && !fits_registers(m, t)) continue;
+      if (t > 1024) {
+        // longer than any single-block solver: the line is split over a cluster of 4 or 8 blocks of <= 320 threads
+        // (tdma_cluster_kernels.cu), so T must be a multiple of 32 * cluster size
+        if (m < 4) continue;
+        int tt = 0;
+        for (int cs = 4; cs <= 8 && !tt; cs *= 2) {
+          const int r = (t + 32 * cs - 1) / (32 * cs) * (32 * cs);
+          if (r / cs <= 320) tt = r;
+        }
+        if (!tt) continue;
+        t = tt;
+      }
+      if (pass == 0 && t <= 1024 && !fits_registers(m, t)) continue;
       long ld = (long)t * m;
       if (best < 0 || ld < best) {
         best = ld;
@@ -254,7 +266,7 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   }
   if (choose_layout(cfg->ni, cfg->nj, want_m, &c->L) != CFD_OK) {
     delete c;
-    cfd_set_error("nj=%d too long for the line layout (max %d)", cfg->nj, 1024 * CFD_MAX_M);
+    cfd_set_error("nj=%d too long for the line layout (max %d)", cfg->nj, 2560 * CFD_MAX_M);
     return CFD_ERR_UNSUPPORTED;
   }
   {
@@ -310,8 +322,9 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CREATE_CUDA(cudaMalloc(&c->partial, (size_t)CFD_EQ_COUNT * c->max_partials * sizeof(double)));
   CREATE_CUDA(cudaMalloc(&c->res_dev, CFD_RES_SLOTS * sizeof(double)));
   CREATE_CUDA(cudaMemset(c->res_dev, 0, CFD_RES_SLOTS * sizeof(double)));
-  CREATE_CUDA(cudaMalloc(&c->flags, ((size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
-  CREATE_CUDA(cudaMemset(c->flags, 0, ((size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
+  // per-line epochs, handshake slots, per-line arrival counters (lines split over a cluster of blocks)
+  CREATE_CUDA(cudaMalloc(&c->flags, (2 * (size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
+  CREATE_CUDA(cudaMemset(c->flags, 0, (2 * (size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
   {
     // cfd_upload_noalloc's staging area: with lazy module loading the array is only materialised when something in
     // this module is first touched, so touch it HERE, while allocating is still allowed (see cfd_upload_noalloc)

@@ -209,20 +209,21 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
           const int q = kk * T + t, cq = kk * P.L.cSK + t;
           const double sns_j = g_sns, rsns_j = g_rsns;
           const double vol = sewu_i * sns_j;
-          const double gee = 0.5 * (dC_c + o_dE) * o_uE;
-          const double gww = 0.5 * (o_dWW + dW_c) * o_uW;
-          const double gne = 0.5 * (dC_c + dC_p) * vC_p;
-          const double gnw = 0.5 * (dW_c + dW_p) * vW_p;
-          const double gse = 0.5 * (dC_m + dC_c) * vC_c;
-          const double gsw = 0.5 * (dW_m + dW_c) * vW_c;
-          const double gp = 0.5 * (dW_c + dC_c) * u_c;
+          // UNI: 0.5*(den0 + den0) is den0 exactly and 0.25*(4 vis0) is vis0 exactly, so the means drop out bit for bit
+          const double gee = UNI ? den0 * o_uE : 0.5 * (dC_c + o_dE) * o_uE;
+          const double gww = UNI ? den0 * o_uW : 0.5 * (o_dWW + dW_c) * o_uW;
+          const double gne = UNI ? den0 * vC_p : 0.5 * (dC_c + dC_p) * vC_p;
+          const double gnw = UNI ? den0 * vW_p : 0.5 * (dW_c + dW_p) * vW_p;
+          const double gse = UNI ? den0 * vC_c : 0.5 * (dC_m + dC_c) * vC_c;
+          const double gsw = UNI ? den0 * vW_c : 0.5 * (dW_m + dW_c) * vW_c;
+          const double gp = UNI ? den0 * u_c : 0.5 * (dW_c + dC_c) * u_c;
           const double ce = 0.5 * (gp + gee) * sns_j, cw = 0.5 * (gww + gp) * sns_j;
           const double cn = 0.5 * (gnw + gne) * sewu_i, cs = 0.5 * (gsw + gse) * sewu_i;
           const double smp = ce - cw + cn - cs;
           const double cp = tmax2(smp, 0.0);
-          const double vise = sC_c, visw = sW_c;
-          const double visn = 0.25 * (A_c + (sW_p + sC_p));
-          const double viss = 0.25 * (A_m + A_c);
+          const double vise = UNI ? vis0 : sC_c, visw = UNI ? vis0 : sW_c;
+          const double visn = UNI ? vis0 : 0.25 * (A_c + (sW_p + sC_p));
+          const double viss = UNI ? vis0 : 0.25 * (A_m + A_c);
           const double de = vise * sns_j * r_dxe;
           const double dw = visw * sns_j * r_dxw;
           const double dn = visn * sewu_i * rdy_c;
@@ -415,20 +416,20 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
           const int q = kk * T + t, cq = kk * P.L.cSK + t;
           const double snsv_j = c_snsv, rsnsv_j = c_rsnsv;
           const double vol = sew_i * snsv_j;
-          const double gne = 0.5 * (dC_c + c_dE) * c_uE;
-          const double gnw = 0.5 * (c_dW + dC_c) * c_uC;
-          const double gnn = 0.5 * (dC_c + dC_p) * v_n;
-          const double gse = 0.5 * (dC_m + dE_m) * uE_m;
-          const double gsw = 0.5 * (dW_m + dC_m) * uC_m;
-          const double gss = 0.5 * (dC_mm + dC_m) * v_s;
-          const double gp = 0.5 * (dC_m + dC_c) * v_c;
+          const double gne = UNI ? den0 * c_uE : 0.5 * (dC_c + c_dE) * c_uE;
+          const double gnw = UNI ? den0 * c_uC : 0.5 * (c_dW + dC_c) * c_uC;
+          const double gnn = UNI ? den0 * v_n : 0.5 * (dC_c + dC_p) * v_n;
+          const double gse = UNI ? den0 * uE_m : 0.5 * (dC_m + dE_m) * uE_m;
+          const double gsw = UNI ? den0 * uC_m : 0.5 * (dW_m + dC_m) * uC_m;
+          const double gss = UNI ? den0 * v_s : 0.5 * (dC_mm + dC_m) * v_s;
+          const double gp = UNI ? den0 * v_c : 0.5 * (dC_m + dC_c) * v_c;
           const double ce = 0.5 * (gne + gse) * snsv_j, cw = 0.5 * (gnw + gsw) * snsv_j;
           const double cn = 0.5 * (gp + gnn) * sew_i, cs = 0.5 * (gss + gp) * sew_i;
           const double smp = ce - cw + cn - cs;
           const double cp = tmax2(smp, 0.0);
-          const double vise = 0.25 * (SE_m + SE_c);
-          const double visw = 0.25 * (SW_m + SW_c);
-          const double visn = c_sC, viss = sC_m;
+          const double vise = UNI ? vis0 : 0.25 * (SE_m + SE_c);
+          const double visw = UNI ? vis0 : 0.25 * (SW_m + SW_c);
+          const double visn = UNI ? vis0 : c_sC, viss = UNI ? vis0 : sC_m;
           const double de = vise * snsv_j * r_dxe;
           const double dw = visw * snsv_j * r_dxw;
           const double dn = visn * sew_i * c_rdyv;

@@ -101,7 +101,8 @@ struct FlowParams {
   int colour0;
   int i_first[2], nlines[2]; // per colour: first local line (0-based) and number of lines (every second line)
   int jlo, jhi;              // unknowns along a line
-  int first;                 // pp = 0 folded into the first sweep: pass 0 takes both neighbours as zero, passes 0 and 1 the end values
+  int n_zero_ew;             // pp = 0 folded into the first sweep: the first n_zero_ew passes take both neighbour lines as zero,
+  int n_zero_ends;           // the first n_zero_ends passes the Dirichlet end values (full sweeps: 1 and 2)
   const double* coef;        // interleaved coefficient block (array `an`)
   double* phi;
   int* flags;                // per local line: epoch of the last pass that finished it
@@ -116,6 +117,7 @@ struct FlowParams {
   int halo_line[2];          // my west / east halo line that the neighbour rewrites during this launch (-1: none) ...
   int halo_last[2];          // ... and the epoch of the last pass that does: the launch does not end before it has arrived
   int* abort_flag;
+  int* arrive;               // lines split over a cluster: per-line count of the blocks that have stored their part
 };
 
 struct HaloPush {
@@ -250,6 +252,9 @@ int cfd_launch_teach_wall(cfd_ctx* c, int which);
 int cfd_launch_teach_scalar(cfd_ctx* c, int eq);
 int cfd_launch_teach_props(cfd_ctx* c);
 bool cfd_flow_eligible(const cfd_ctx* c);
+int cfd_cluster_size(int T);
+int cfd_launch_flow_cluster(cfd_ctx* c, cfd::FlowParams& P);
+int cfd_launch_flow_from_sweep(cfd_ctx* c, const cfd::SweepParams& Q, int field_unused);
 int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int nsweeps, int first);
 int cfd_launch_halo_push(cfd_ctx* c, int nfields, const int* fields, const int* w, const int* e);
 int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double* partial, const double* uinc);

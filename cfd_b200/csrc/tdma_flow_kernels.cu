@@ -19,90 +19,9 @@
 //     and the first remote store of a launch waits for the neighbour's ready mark.
 // Same arithmetic as k_tdma_tma (same chunked elimination, same cyclic reduction): the two paths give identical bits.
 // All waits are bounded; a timeout raises the context's abort flag instead of hanging the GPU.
-#include "common.cuh"
-#include "tma.cuh"
+#include "flow.cuh"
 
 namespace cfd {
-
-__device__ __forceinline__ double rcp_nr(double x) {   // == rcp() of tdma_kernels.cu
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-  r = fma(fma(-x, r, 1.0), r, r);
-  r = fma(fma(-x, r, 1.0), r, r);
-  return r;
-}
-
-__device__ __forceinline__ int ld_acquire_sys(const int* p) {
-  int v;
-  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu(int* p, int v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void st_release_sys(int* p, int v) {
-  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Poll until *p >= want (wrap-safe) or about two seconds have passed; false = timed out (abort flag raised).
-// SYS: the flag may be written by another GPU.
-template <bool SYS = true>
-__device__ __forceinline__ bool wait_flag(const int* p, int want, int* abort_flag) {
-  if ((SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - want >= 0) return true;
-  const long long t0 = clock64();
-  for (;;) {
-    __nanosleep(40);
-    if ((SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - want >= 0) return true;
-    if (clock64() - t0 > 4000000000LL || *(volatile int*)abort_flag) {   // ~2 s at 2 GHz
-      atomicExch(abort_flag, 1);
-      return false;
-    }
-  }
-}
-
-// position in the per-block work order -> line of the colour: slab-edge lines (first, last) come first
-__device__ __forceinline__ int flow_line(int idx, int n) { return idx == 0 ? 0 : (idx == 1 ? n - 1 : idx - 1); }
-
-// A block's work items in order: (pass, position in the pass).  Every role of the block walks the same sequence.
-struct FlowIter {
-  int p, idx;
-  __device__ __forceinline__ void skip(const FlowParams& P) {
-    while (p < P.npass && idx >= P.nlines[(P.colour0 + p) & 1]) ++p;
-  }
-  __device__ __forceinline__ void init(const FlowParams& P) {
-    p = 0;
-    idx = blockIdx.x;
-    skip(P);
-  }
-  __device__ __forceinline__ bool done(const FlowParams& P) const { return p >= P.npass; }
-  __device__ __forceinline__ int colour(const FlowParams& P) const { return (P.colour0 + p) & 1; }
-  __device__ __forceinline__ int line(const FlowParams& P) const {
-    const int c = (P.colour0 + p) & 1;
-    return P.i_first[c] + 2 * flow_line(idx, P.nlines[c]);
-  }
-  __device__ __forceinline__ void next(const FlowParams& P) {
-    idx += (int)gridDim.x;
-    if (idx >= P.nlines[(P.colour0 + p) & 1]) {
-      idx = blockIdx.x;
-      ++p;
-      skip(P);
-    }
-  }
-};
-
-__device__ __forceinline__ int lds_acquire(unsigned addr) {
-  int v;
-  asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ void sts_release(unsigned addr, int v) {
-  asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
 
 // Block = T consumer threads + a producer warp + a helper warp:
 //   consumers        eliminate / reduce / back-substitute the line whose slices the ring delivers (as k_tdma_tma)
@@ -191,7 +110,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
       FlowIter it;
       int n = 0;
       for (it.init(P); !it.done(P); it.next(P), ++n) {
-        const bool zeroEW = P.first && it.p == 0;
+        const bool zeroEW = it.p < P.n_zero_ew;
         const unsigned tx = slice_bytes * ((unsigned)nc + (zeroEW ? 0u : 2u));
         const int i0 = it.line(P);
         // the neighbour lines were rewritten by the previous pass: the acquirer has seen both complete
@@ -236,18 +155,18 @@ __global__ void __launch_bounds__(BMAX, 1) k_tdma_flow(const FlowParams P, const
   // Dirichlet end values phi(i, jstart-1), phi(i, nj) of a line are fetched one item ahead (never written by a sweep:
   // safe to read at any time)
   double bS = 0.0, bN = 0.0;
-  if (!it.done(P) && !(P.first && it.p < 2)) {
+  if (!it.done(P) && !(it.p < P.n_zero_ends)) {
     const double* ph = P.phi + (long long)it.line(P) * LD;
     bS = __ldg(ph + q_s);
     bN = __ldg(ph + q_n);
   }
   for (int n = 0; !it.done(P); ++n) {
-    const bool zeroEW = P.first && it.p == 0;
+    const bool zeroEW = it.p < P.n_zero_ew;
     const int i0 = it.line(P);
     double* phi = P.phi + (long long)i0 * LD;
     it.next(P);
     double bS_next = 0.0, bN_next = 0.0;
-    if (!it.done(P) && !(P.first && it.p < 2)) {
+    if (!it.done(P) && !(it.p < P.n_zero_ends)) {
       const double* ph = P.phi + (long long)it.line(P) * LD;
       bS_next = __ldg(ph + q_s);
       bN_next = __ldg(ph + q_n);
@@ -454,15 +373,27 @@ bool cfd_flow_eligible(const cfd_ctx* c) {
   // an i-slab needs its neighbours attached: without them the halo lines change between passes by host-issued
   // exchanges, which only the one-pass-per-launch path can interleave
   const bool peers_ok = (c->cfg.halo_w == 0 || c->peer_attached[0]) && (c->cfg.halo_e == 0 || c->peer_attached[1]);
+  const bool layout_ok = (c->L.T >= 128 && c->L.T <= 320) || (cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4);
   return use && c->cfg.order == CFD_ORDER_REDBLACK && c->cfg.halo_s == 0 && c->cfg.halo_n == 0 && c->cfg.joff == 0 &&
-         c->L.T >= 128 && c->L.T + 32 <= 352 && c->flags != nullptr && peers_ok;
+         layout_ok && c->flags != nullptr && peers_ok;
 }
+
+static int flow_launch(cfd_ctx* c, int istart, int jstart, int field, int npass, int colour0, int n_zero_ew, int n_zero_ends);
 
 // nsweeps red/black sweeps (2*nsweeps colour passes) of `phi` over the current coefficients, one launch.
 int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int nsweeps, int first) {
   if (nsweeps <= 0) return CFD_OK;
+  return flow_launch(c, istart, jstart, field, 2 * nsweeps, 0, first ? 1 : 0, first ? 2 : 0);
+}
+
+// one colour pass through the same kernels (lines longer than one block have no other solver)
+int cfd_launch_sweep_flow_pass(cfd_ctx* c, int istart, int jstart, int field, int colour, int first) {
+  return flow_launch(c, istart, jstart, field, 1, colour, (first && colour == 0) ? 1 : 0, first ? 1 : 0);
+}
+
+static int flow_launch(cfd_ctx* c, int istart, int jstart, int field, int npass, int colour0, int n_zero_ew, int n_zero_ends) {
   const int epoch0 = c->epoch;
-  c->epoch += 2 * nsweeps;          // advanced on every rank alike, whether or not this slab has lines to solve
+  c->epoch += npass;                // advanced on every rank alike, whether or not this slab has lines to solve
   const int NI = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
   const int own_lo = c->cfg.goff + c->cfg.halo_w + 1, own_hi = c->cfg.goff + c->L.ni - c->cfg.halo_e;   // global, 1-based
   int glo = own_lo, ghi = own_hi;
@@ -470,8 +401,8 @@ int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int ns
   if (ghi > NI - 1) ghi = NI - 1;
   FlowParams P{};
   P.L = c->L;
-  P.npass = 2 * nsweeps;
-  P.colour0 = 0;
+  P.npass = npass;
+  P.colour0 = colour0;
   for (int col = 0; col < 2; ++col) {
     const int g0 = glo + ((((glo - istart) & 1) != col) ? 1 : 0);
     if (g0 > ghi) {
@@ -513,7 +444,8 @@ int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int ns
   }
   P.jlo = jlo;
   P.jhi = jhi;
-  P.first = first ? 1 : 0;
+  P.n_zero_ew = n_zero_ew;
+  P.n_zero_ends = n_zero_ends;
   P.coef = c->field[CFD_AN];
   P.phi = c->field[field];
   P.flags = c->flags;
@@ -545,6 +477,7 @@ int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int ns
     P.peer_phi[s] = c->peer_field[s][field] + (long long)peer_line * c->L.LD;
     P.peer_flag[s] = c->peer_flags[s] + peer_line;
   }
+  if (cfd_cluster_size(c->L.T) > 0) return cfd_launch_flow_cluster(c, P);    // a line split over a cluster of blocks
   const size_t stage = (size_t)(c->L.nc + 2) * c->L.T * sizeof(double), pcr = (size_t)6 * c->L.T * sizeof(double);
   int S = 16;
   const char* es = getenv("CFD_B200_TDMA_STAGES");
@@ -618,4 +551,41 @@ int cfd_launch_halo_push(cfd_ctx* c, int nfields, const int* fields, const int* 
   ++c->launches;
   CFD_CUDA(cudaGetLastError());
   return CFD_OK;
+}
+
+// One colour pass described by SweepParams (cfd_sweep / cfd_sweep_part) through the flag-ordered kernels: what
+// launch_sweep (tdma_kernels.cu) falls back to when the lines are longer than any single-block solver takes.
+int cfd_launch_flow_from_sweep(cfd_ctx* c, const cfd::SweepParams& Q, int field_unused) {
+  (void)field_unused;
+  if (Q.basis || Q.end_s_const || Q.end_n_const || Q.i_step != 2 || Q.out != Q.phi) {
+    cfd_set_error("lines of %d layout threads: only plain colour passes are available (no j-slab pieces)", c->L.T);
+    return CFD_ERR_UNSUPPORTED;
+  }
+  FlowParams P{};
+  P.L = c->L;
+  P.npass = 1;
+  P.colour0 = 0;
+  P.i_first[0] = Q.i_first;
+  P.nlines[0] = Q.nlines;
+  P.i_first[1] = 0;
+  P.nlines[1] = 0;
+  P.wait_lo[0] = P.wait_lo[1] = 1;
+  P.wait_hi[0] = P.wait_hi[1] = 0;
+  P.jlo = Q.jlo;
+  P.jhi = Q.jhi;
+  P.n_zero_ew = (Q.first && Q.first_colour == 0) ? 1 : 0;
+  P.n_zero_ends = Q.first ? 1 : 0;
+  P.coef = Q.an;
+  P.phi = Q.phi;
+  P.flags = c->flags;
+  P.epoch0 = c->epoch;
+  c->epoch += 1;
+  P.abort_flag = c->flags + c->L.ni + CFD_FLAG_ABORT;
+  P.ready = c->flags + c->L.ni + CFD_FLAG_SWEEP_READY;
+  for (int s = 0; s < 2; ++s) {
+    P.edge_line[s] = -1;
+    P.halo_line[s] = -1;
+  }
+  if (Q.nlines <= 0) return CFD_OK;
+  return cfd_launch_flow_cluster(c, P);
 }

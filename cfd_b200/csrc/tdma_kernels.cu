@@ -655,6 +655,9 @@ int cfd_launch_spike_basis(cfd_ctx* c, int istart, int jstart) {
 
 static int launch_sweep(cfd_ctx* c, cfd::SweepParams& P) {
   const int T = c->L.T;
+  // lines longer than one block's solver takes are split over a cluster of blocks (tdma_cluster_kernels.cu)
+  if (T + 32 > 1024 || (T > 640 && cfd_cluster_size(T) > 0 && c->L.M >= 4 && !P.basis && !P.end_s_const && !P.end_n_const))
+    return cfd_launch_flow_from_sweep(c, P, 0);
   const int num_sms = c->num_sms;
   static int use_tma = -1;   // environment switch, the same for every device
   if (use_tma < 0) {

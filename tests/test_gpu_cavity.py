@@ -522,3 +522,37 @@ def test_uniform_property_kernels_give_the_same_bits(cfd, shape, monkeypatch):
     assert np.array_equal(a.download("u"), b.download("u"))
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("shape,cs", [((20, 8192), 2), ((12, 16384), 4), ((8, 20000), 4), ((6, 40000), 8), ((40, 6000), 2)])
+def test_lines_split_over_a_cluster_of_blocks(cfd, oracle, shape, cs):
+    """Lines longer than one thread block takes (more than 320 layout threads) are solved by a cluster of 2 / 4 / 8 blocks
+    that exchange their interface relations through distributed shared memory (tdma_cluster_kernels.cu): two full
+    sweeps in one launch and a single colour pass, against the oracle's red/black lisolv (cavity_fvm.f90:49-82)."""
+    o, g = make_pair(cfd, oracle, *shape, order="redblack")
+    L = g.layout
+    assert L["T"] > 320 and L["T"] % (32 * cs) == 0 and L["T"] // cs <= 320, L
+    assert g.sweeps_single_launch()
+    randomise(o, g, 5)
+    o.assemble_u()
+    g.assemble_u()
+    for _ in range(2):
+        o.lisolv(3, 2, o.u)
+    g.sweeps(3, 2, "u", 2)
+    assert linf_rel(g.download("u"), o.u) < 1e-10
+    o.assemble_v()
+    g.assemble_v()
+    o.lisolv(2, 3, o.v)
+    g.lisolv(2, 3, "v")                      # one pass per launch (the cluster kernel again beyond 1024 threads)
+    assert linf_rel(g.download("v"), o.v) < 1e-10
+    o.assemble_p()
+    g.assemble_p()
+    o.pp[:, :] = 0.0
+    for _ in range(3):
+        o.lisolv(2, 2, o.pp)
+    g.upload("pp", np.asfortranarray(np.random.default_rng(1).random((g.ni, g.nj))))    # pp = 0 is folded in
+    g.sweeps(2, 2, "pp", 3, first=True)
+    a, b = g.download("pp"), o.pp
+    assert np.abs(a[1:-1, 1:-1] - b[1:-1, 1:-1]).max() <= 1e-10 * np.abs(b).max()
+    assert not g.peer_status()
+    g.close()
