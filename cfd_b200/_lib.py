@@ -113,6 +113,7 @@ SYMBOLS = {
     "cfd_halo_push": (C.c_int, [_vp, C.c_int, _ip, _ip, _ip]),
     "cfd_peer_status": (C.c_int, [_vp, _ip]),
     "cfd_sweeps_single_launch": (C.c_int, [_vp, _ip]),
+    "cfd_debug_flow_timing": (C.c_int, [_vp, _dp]),
     "cfd_set_turbulence": (C.c_int, [_vp, C.POINTER(CfdTurbulence)]),
     "cfd_wall_upload": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "cfd_wall_download": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),

@@ -230,6 +230,7 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
     c->allow_uniform = !(e && atoi(e) == 0);
   }
   c->flags = nullptr;
+  c->dbg = nullptr;
   c->post_buf = nullptr;
   c->post_n = 0;
   c->epoch = 1;
@@ -362,6 +363,7 @@ extern "C" int cfd_destroy(cfd_ctx* c) {
   for (void* m : c->ipc_opened) cudaIpcCloseMemHandle(m);
   if (c->flags) cudaFree(c->flags);
   if (c->post_buf) cudaFree(c->post_buf);
+  if (c->dbg) cudaFree(c->dbg);
   if (c->seq_scratch) cudaFree(c->seq_scratch);
   delete c;
   return CFD_OK;
@@ -723,6 +725,19 @@ extern "C" int cfd_halo_push(cfd_ctx* c, int nfields, const int* fields, const i
   CFD_REQUIRE(fields && w && e && nfields >= 1 && nfields <= 4, "cfd_halo_push: 1..4 fields");
   if (!c->peer_attached[0] && !c->peer_attached[1]) return CFD_OK;
   return cfd_launch_halo_push(c, nfields, fields, w, e);
+}
+// diagnostic: clock64 sums of the consumer phases of the flag-ordered sweep kernels since the last call
+// (out[0] = lines, out[1..6] = cycles in: slices, backward, reduction, exchange, stores, end barrier), block 0 only
+extern "C" int cfd_debug_flow_timing(cfd_ctx* c, double out[8]) {
+  CFD_REQUIRE(c && out, "null argument");
+  for (int k = 0; k < 8; ++k) out[k] = 0.0;
+  if (!c->dbg) return CFD_OK;
+  CFD_CUDA(cudaSetDevice(c->device));
+  unsigned long long h[8];
+  CFD_CUDA(cudaMemcpy(h, c->dbg, sizeof(h), cudaMemcpyDeviceToHost));
+  CFD_CUDA(cudaMemset(c->dbg, 0, sizeof(h)));
+  for (int k = 0; k < 8; ++k) out[k] = (double)h[k];
+  return CFD_OK;
 }
 extern "C" int cfd_sweeps_single_launch(cfd_ctx* c, int* yes) {
   CFD_REQUIRE(c && yes, "null argument");

@@ -118,6 +118,7 @@ struct FlowParams {
   int halo_last[2];          // ... and the epoch of the last pass that does: the launch does not end before it has arrived
   int* abort_flag;
   int* arrive;               // lines split over a cluster: per-line count of the blocks that have stored their part
+  unsigned long long* dbg;   // optional (CFD_B200_FLOW_TIMING=1): clock64 sums of the consumer phases, per kernel
 };
 
 struct HaloPush {
@@ -205,6 +206,7 @@ struct cfd_ctx {
   // cavity family: value of den / vis if the last upload of the field was uniform over the whole local array
   bool uni_den, uni_vis, allow_uniform;
   double den0, vis0;
+  unsigned long long* dbg;          // phase timing of the flag-ordered sweeps (diagnostic, CFD_B200_FLOW_TIMING=1)
   double* post_buf;                 // result vector of the post-processing kernels (post_kernels.cu), sized on first use
   size_t post_n;
   int num_sms;                      // SM count of THIS context's device (persistent grids are sized from it)

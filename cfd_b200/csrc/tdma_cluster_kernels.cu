@@ -66,6 +66,13 @@ __device__ __forceinline__ int atom_add_acq_rel_gpu(int* p, int v) {
   return old;
 }
 
+// asynchronous store of one double into another block's shared memory; completes `bytes` on that block's mbarrier
+__device__ __forceinline__ void st_async_f64(unsigned raddr, double v, unsigned rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(raddr),
+               "l"(__double_as_longlong(v)), "r"(rbar)
+               : "memory");
+}
+
 #define XCH_N 9   // per block and line: E = (r, pL, pR) of chunk-end 0, A = (r, pL, pR) of chunk-end Tc-1, first node (cc0, cf0, ca0)
 
 template <int M, int NC, int CS>
@@ -80,11 +87,10 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* bufA = ring + (size_t)S * SW;          // PCR: two buffers of 5*Tc
   double* bufB = bufA + 5 * Tc;
-  double* xch = bufB + 5 * Tc;                   // [2][XCH_N] interface numbers of this block, by line parity
-  double* xlr = xch + 2 * XCH_N;                 // [2] XL, XR of the current line
-  unsigned long long* bars = reinterpret_cast<unsigned long long*>(xlr + 2);
-  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S), xbar = smem_u32(bars + 2 * S);
-  int* counters = reinterpret_cast<int*>(bars + 2 * S + 1);
+  double* xin = bufB + 5 * Tc;                   // [2][CS][XCH_N] interface numbers of every block of the cluster, by line parity
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(xin + 2 * CS * XCH_N);
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S), xbar0 = smem_u32(bars + 2 * S);   // xbar[2]
+  int* counters = reinterpret_cast<int*>(bars + 2 * S + 2);
   const unsigned acq32 = smem_u32(counters), sto32 = smem_u32(counters + 1);
   const int ncw = Tc / 32;
   if (tid == 0) {
@@ -92,7 +98,8 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, ncw);
     }
-    mbar_init(xbar, CS);
+    mbar_init(xbar0, 1);
+    mbar_init(xbar0 + 8, 1);
     counters[0] = 0;
     counters[1] = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -142,8 +149,11 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
       }
     }
   } else if (tid >= Tc) {
-    // ---------------- producer warp ---------------------------------------------------------------------
-    if (tid == Tc) {
+    // ---------------- producer warp: lane a issues the copy of array a (nc coefficient parts, phi east, phi west) --------
+    // (a block's part of a slice is nc+2 separate pieces of Tc doubles; issued one after the other by a single thread
+    // the copies, not HBM, set the pace)
+    {
+      const int la = tid - Tc;
       const unsigned part_bytes = (unsigned)(Tc * sizeof(double));
       unsigned rs = 0, rph = 0;
       FlowIter it;
@@ -152,27 +162,29 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
         const bool zeroEW = it.p < P.n_zero_ew;
         const unsigned tx = part_bytes * ((unsigned)nc + (zeroEW ? 0u : 2u));
         const int i0 = it.line(P);
-        while (lds_acquire(acq32) - (n + 1) < 0) __nanosleep(20);
-        if (it.p > 0) asm volatile("fence.proxy.async;" ::: "memory");
-        const double* csrc = P.coef + (long long)i0 * P.L.cSL + crank * Tc;
-        const double* esrc = P.phi + (long long)(i0 + 1) * LD + crank * Tc;
-        const double* wsrc = P.phi + (long long)(i0 - 1) * LD + crank * Tc;
+        if (la == 0) {
+          while (lds_acquire(acq32) - (n + 1) < 0) __nanosleep(20);
+          if (it.p > 0) asm volatile("fence.proxy.async;" ::: "memory");
+        }
+        __syncwarp();
+        // source of this lane's array for node slice 0
+        const double* src = la < nc ? P.coef + (long long)i0 * P.L.cSL + (size_t)la * T + crank * Tc
+                                    : P.phi + (long long)(la == nc ? i0 + 1 : i0 - 1) * LD + crank * Tc;
+        const size_t kstride = la < nc ? (size_t)P.L.cSK : (size_t)T;
+        const bool mine = la < nc || (la < nc + 2 && !zeroEW);
         for (int k = 0; k < M; ++k) {
           const unsigned s = rs, ph = rph;
           if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
-          mbar_wait(empty0 + 8 * s, ph ^ 1u);
           const unsigned fb = full0 + 8 * s;
-          const unsigned dst = smem_u32(ring + (size_t)s * SW);
-          mbar_expect_tx(fb, tx);
-#pragma unroll
-          for (int a = 0; a < nc; ++a) tma_load_1d(dst + a * part_bytes, csrc + (size_t)k * P.L.cSK + (size_t)a * T, part_bytes, fb);
-          if (!zeroEW) {
-            tma_load_1d(dst + nc * part_bytes, esrc + (size_t)k * T, part_bytes, fb);
-            tma_load_1d(dst + (nc + 1) * part_bytes, wsrc + (size_t)k * T, part_bytes, fb);
+          if (la == 0) {
+            mbar_wait(empty0 + 8 * s, ph ^ 1u);
+            mbar_expect_tx(fb, tx);
           }
+          __syncwarp();
+          if (mine) tma_load_1d(smem_u32(ring + (size_t)s * SW) + la * part_bytes, src + (size_t)k * kstride, part_bytes, fb);
         }
       }
-      if (blockIdx.x == 0) {
+      if (la == 0 && blockIdx.x == 0) {
         for (int sd = 0; sd < 2; ++sd)
           if (P.halo_line[sd] >= 0) wait_flag(P.flags + P.halo_line[sd], P.halo_last[sd], P.abort_flag);
       }
@@ -184,7 +196,7 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
     const int j0base = tg * M;
     const unsigned T8 = (unsigned)Tc * 8u, stage_bytes = (unsigned)SW * 8u, ring32 = smem_u32(ring) + (unsigned)t * 8u;
     const int q_s = lpos(P.jlo - 1, M, T), q_n = lpos(P.jhi + 1, M, T);
-    unsigned rs = 0, rph = 0, xph = 0;
+    unsigned rs = 0, rph = 0;
     bool peer_open[2] = {false, false};
     FlowIter it;
     it.init(P, cid, ncl);
@@ -194,7 +206,16 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
       bS = __ldg(ph + q_s);
       bN = __ldg(ph + q_n);
     }
+    const bool tm = P.dbg != nullptr && blockIdx.x == 0 && t == 0;
+    unsigned long long tacc[6] = {0, 0, 0, 0, 0, 0}, nl_done = 0;
     for (int n = 0; !it.done(P); ++n) {
+      long long c0 = tm ? clock64() : 0, c1;
+#define STAMP(k)                \
+  if (tm) {                     \
+    c1 = clock64();             \
+    tacc[k] += (unsigned long long)(c1 - c0); \
+    c0 = c1;                    \
+  }
       const bool zeroEW = it.p < P.n_zero_ew;
       const int i0 = it.line(P);
       double* phi = P.phi + (long long)i0 * LD;
@@ -244,15 +265,20 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
           cf[k] = b * cf[k > 0 ? k - 1 : 0] * inv;
         }
       }
+      STAMP(0)
 #pragma unroll
       for (int k = M - 3; k >= 0; --k) {
         cc[k] = fma(ca[k], cc[k + 1], cc[k]);
         cf[k] = fma(ca[k], cf[k + 1], cf[k]);
         ca[k] = ca[k] * ca[k + 1];
       }
+      STAMP(1)
       // ---- chunk-end relations  x_t = l*x_{t-1} + u*x_{t+1} + r + pL*XL + pR*XR
-      double* xc = xch + (n & 1) * XCH_N;
+      const int q = n & 1;
+      double* xq = xin + (size_t)q * CS * XCH_N;                 // this line's table [CS][9]
+      const unsigned xb = xbar0 + 8u * (unsigned)q;
       double l, u, r, pL = 0.0, pR = 0.0;
+      double f0c = 0.0, f0f = 0.0, f0a = 1.0;                    // first node of the block (thread 0): x_first = f0c + f0f*XL + f0a*x_end(0)
       if (M == 1) {
         l = cf[0];
         u = ca[0];
@@ -278,85 +304,96 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
           r = cc[M - 1];
           pR = ca[M - 1];
         }
+        f0c = cc[0];
+        f0f = cf[0];
+        f0a = ca[0];
       }
       if (t == 0) {                       // first chunk of the block: its x_{t-1} is XL
         pL = l;
         l = 0.0;
-        // first node of the block: x_first = cc0 + cf0*XL + ca0*x_end(0); with one node per chunk it IS x_end(0)
-        xc[6] = (M == 1) ? 0.0 : cc[0];
-        xc[7] = (M == 1) ? 0.0 : cf[0];
-        xc[8] = (M == 1) ? 1.0 : ca[0];
       }
-      double* cur = bufA;
-      double* nxt = bufB;
-      cur[t] = l;
-      cur[Tc + t] = u;
-      cur[2 * Tc + t] = r;
-      cur[3 * Tc + t] = pL;
-      cur[4 * Tc + t] = pR;
+      // cyclic reduction with three right-hand sides; (l,u) and (r,pL) travel as 16-byte pairs
+      double2* LU = reinterpret_cast<double2*>(bufA);            // two buffers of [Tc] double2 + [Tc] double2 + [Tc] double
+      double2* RP = LU + Tc;
+      double* QR = reinterpret_cast<double*>(RP + Tc);
+      double2* LU2 = reinterpret_cast<double2*>(bufB);
+      double2* RP2 = LU2 + Tc;
+      double* QR2 = reinterpret_cast<double*>(RP2 + Tc);
+      LU[t] = make_double2(l, u);
+      RP[t] = make_double2(r, pL);
+      QR[t] = pR;
       consumer_sync(Tc);
       for (int sft = 1; sft < Tc; sft <<= 1) {
-        double lm = 0.0, um = 0.0, rm = 0.0, am = 0.0, bm = 0.0, lp = 0.0, up = 0.0, rp = 0.0, ap = 0.0, bp = 0.0;
+        double2 lum = make_double2(0.0, 0.0), rpm = lum, lup = lum, rpp = lum;
+        double qm = 0.0, qp = 0.0;
         if (t - sft >= 0) {
-          lm = cur[t - sft];
-          um = cur[Tc + t - sft];
-          rm = cur[2 * Tc + t - sft];
-          am = cur[3 * Tc + t - sft];
-          bm = cur[4 * Tc + t - sft];
+          lum = LU[t - sft];
+          rpm = RP[t - sft];
+          qm = QR[t - sft];
         }
         if (t + sft < Tc) {
-          lp = cur[t + sft];
-          up = cur[Tc + t + sft];
-          rp = cur[2 * Tc + t + sft];
-          ap = cur[3 * Tc + t + sft];
-          bp = cur[4 * Tc + t + sft];
+          lup = LU[t + sft];
+          rpp = RP[t + sft];
+          qp = QR[t + sft];
         }
-        const double inv = rcp_nr(fma(-l, um, fma(-u, lp, 1.0)));
-        r = fma(l, rm, fma(u, rp, r)) * inv;
-        pL = fma(l, am, fma(u, ap, pL)) * inv;
-        pR = fma(l, bm, fma(u, bp, pR)) * inv;
-        l = l * lm * inv;
-        u = u * up * inv;
-        nxt[t] = l;
-        nxt[Tc + t] = u;
-        nxt[2 * Tc + t] = r;
-        nxt[3 * Tc + t] = pL;
-        nxt[4 * Tc + t] = pR;
+        const double inv = rcp_nr(fma(-l, lum.y, fma(-u, lup.x, 1.0)));
+        r = fma(l, rpm.x, fma(u, rpp.x, r)) * inv;
+        pL = fma(l, rpm.y, fma(u, rpp.y, pL)) * inv;
+        pR = fma(l, qm, fma(u, qp, pR)) * inv;
+        l = l * lum.x * inv;
+        u = u * lup.y * inv;
+        LU2[t] = make_double2(l, u);
+        RP2[t] = make_double2(r, pL);
+        QR2[t] = pR;
         consumer_sync(Tc);
-        double* tmp = cur;
-        cur = nxt;
-        nxt = tmp;
+        double2* t2 = LU; LU = LU2; LU2 = t2;
+        t2 = RP; RP = RP2; RP2 = t2;
+        double* t1 = QR; QR = QR2; QR2 = t1;
       }
-      // ---- the one exchange of the line: interface relations of every block, then XL / XR of this block
-      if (t == 0) {
-        xc[0] = r;
-        xc[1] = pL;
-        xc[2] = pR;
-      }
-      if (t == Tc - 1) {
-        xc[3] = r;
-        xc[4] = pL;
-        xc[5] = pR;
-      }
-      consumer_sync(Tc);
-      if (t == 0) {
+      STAMP(2)
+      // ---- the one exchange of the line.  Thread 0 holds E = (r,pL,pR) of chunk-end 0 and the first-node relation,
+      // thread Tc-1 holds A = (r,pL,pR) of the last chunk-end: both write them into this block's row of the table and send
+      // them to the same row in every other block with asynchronous shared-memory stores that complete on that block's
+      // barrier -- no fence, no flag; each block expects (CS-1)*9 doubles per line.
+      if (t == 0 || t == Tc - 1) {
+        double* mine = xq + crank * XCH_N;
+        const unsigned m32 = smem_u32(mine);
+        if (t == 0) {
+          mbar_expect_tx(xb, (unsigned)((CS - 1) * XCH_N * sizeof(double)));
+          mine[0] = r; mine[1] = pL; mine[2] = pR; mine[6] = f0c; mine[7] = f0f; mine[8] = f0a;
 #pragma unroll
-        for (int b = 0; b < CS; ++b) mbar_arrive_cluster(map_shared(xbar, (unsigned)b));
+          for (int b = 0; b < CS; ++b) {
+            if (b == crank) continue;
+            const unsigned ra = map_shared(m32, (unsigned)b), rb = map_shared(xb, (unsigned)b);
+            st_async_f64(ra, r, rb); st_async_f64(ra + 8, pL, rb); st_async_f64(ra + 16, pR, rb);
+            st_async_f64(ra + 48, f0c, rb); st_async_f64(ra + 56, f0f, rb); st_async_f64(ra + 64, f0a, rb);
+          }
+        }
+        if (t == Tc - 1) {
+          mine[3] = r; mine[4] = pL; mine[5] = pR;
+#pragma unroll
+          for (int b = 0; b < CS; ++b) {
+            if (b == crank) continue;
+            const unsigned ra = map_shared(m32, (unsigned)b), rb = map_shared(xb, (unsigned)b);
+            st_async_f64(ra + 24, r, rb); st_async_f64(ra + 32, pL, rb); st_async_f64(ra + 40, pR, rb);
+          }
+        }
       }
-      mbar_wait_cluster(xbar, xph);
-      xph ^= 1u;
-      if (t == 0) {
+      consumer_sync(Tc);                           // this block's own row is complete
+      mbar_wait(xb, (unsigned)((n >> 1) & 1));     // ... and the other blocks' rows have arrived
+      double XL = 0.0, XR = 0.0;
+      {
+        // every thread solves the interface unknowns itself (a short recurrence on the 9*CS numbers, broadcast reads):
         // E_c = RE + LE*A_{c-1} + UE*F_{c+1};  A_c = RA + LA*A_{c-1} + UA*F_{c+1};  F_c = cc0 + cf0*A_{c-1} + ca0*E_c
         double RA[CS], LA[CS], UA[CS], PF[CS], QF[CS], SF[CS];
-        const unsigned xc32 = smem_u32(xc);
 #pragma unroll
         for (int b = 0; b < CS; ++b) {
-          const unsigned ra = map_shared(xc32, (unsigned)b);
-          const double RE = ld_dsmem(ra), LE = ld_dsmem(ra + 8), UE = ld_dsmem(ra + 16);
-          RA[b] = ld_dsmem(ra + 24);
-          LA[b] = ld_dsmem(ra + 32);
-          UA[b] = ld_dsmem(ra + 40);
-          const double c0 = ld_dsmem(ra + 48), f0 = ld_dsmem(ra + 56), a0 = ld_dsmem(ra + 64);
+          const double* row = xq + b * XCH_N;
+          const double RE = row[0], LE = row[1], UE = row[2];
+          RA[b] = row[3];
+          LA[b] = row[4];
+          UA[b] = row[5];
+          const double c0 = row[6], f0 = row[7], a0 = row[8];
           PF[b] = fma(a0, RE, c0);
           QF[b] = fma(a0, LE, f0);
           SF[b] = a0 * UE;
@@ -369,11 +406,9 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
         de[0] = 0.0;
 #pragma unroll
         for (int b = 1; b < CS; ++b) {
-          // F_b = PF + QF*A_{b-1} + SF*F_{b+1},  A_{b-1} = al + be*F_b
           const double inv = rcp_nr(fma(-QF[b], be[b - 1], 1.0));
           ga[b] = fma(QF[b], al[b - 1], PF[b]) * inv;
           de[b] = SF[b] * inv;
-          // A_b = RA + LA*A_{b-1} + UA*F_{b+1},  A_{b-1} = al + be*(ga + de*F_{b+1})
           al[b] = fma(LA[b], fma(be[b - 1], ga[b], al[b - 1]), RA[b]);
           be[b] = fma(LA[b] * be[b - 1], de[b], UA[b]);
         }
@@ -383,7 +418,6 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
         for (int b = CS - 1; b >= 1; --b) F[b] = fma(de[b], F[b + 1], ga[b]);
 #pragma unroll
         for (int b = 0; b < CS; ++b) A[b] = fma(be[b], F[b + 1], al[b]);
-        double XL = 0.0, XR = 0.0;
 #pragma unroll
         for (int b = 0; b < CS; ++b) {
           if (b == crank) {
@@ -391,15 +425,16 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
             XR = F[b + 1];
           }
         }
-        xlr[0] = XL;
-        xlr[1] = XR;
       }
-      consumer_sync(Tc);
-      const double XL = xlr[0], XR = xlr[1];
+      STAMP(3)
       const double xe = fma(pL, XL, fma(pR, XR, r));
       double xp;
-      if (t > 0) xp = fma(cur[3 * Tc + t - 1], XL, fma(cur[4 * Tc + t - 1], XR, cur[2 * Tc + t - 1]));
-      else xp = XL;
+      if (t > 0) {
+        const double2 rpn = RP[t - 1];
+        xp = fma(rpn.y, XL, fma(QR[t - 1], XR, rpn.x));
+      } else {
+        xp = XL;
+      }
       const int side = (i0 == P.edge_line[0]) ? 0 : ((i0 == P.edge_line[1]) ? 1 : -1);
       double* rphi = nullptr;
       if (side >= 0 && P.peer_phi[side]) {
@@ -419,10 +454,18 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
           if (rphi) rphi[k * T + tg] = xk;
         }
       }
+      STAMP(4)
       consumer_sync(Tc);
+      STAMP(5)
+      ++nl_done;
       if (t == 0) sts_release(sto32, n + 1);
       bS = bS_next;
       bN = bN_next;
+    }
+#undef STAMP
+    if (tm) {
+      atomicAdd(P.dbg, nl_done);
+      for (int k = 0; k < 6; ++k) atomicAdd(P.dbg + 1 + k, tacc[k]);
     }
   }
   __syncwarp();
@@ -502,7 +545,7 @@ int cfd_launch_flow_cluster(cfd_ctx* c, FlowParams& P) {
   const int Tc = c->L.T / cs;
   P.arrive = c->flags + c->L.ni + CFD_FLAG_SLOTS;
   const size_t stage = (size_t)(c->L.nc + 2) * Tc * sizeof(double);
-  const size_t fixed = (size_t)10 * Tc * sizeof(double) + (2 * XCH_N + 2) * sizeof(double) + 8 + 16;
+  const size_t fixed = (size_t)10 * Tc * sizeof(double) + (size_t)2 * cs * XCH_N * sizeof(double) + 16 + 16;
   int S = 16;
   const char* es = getenv("CFD_B200_TDMA_STAGES");
   if (es && atoi(es) > 0) S = atoi(es);

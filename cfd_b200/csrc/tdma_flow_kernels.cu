@@ -373,7 +373,16 @@ bool cfd_flow_eligible(const cfd_ctx* c) {
   // an i-slab needs its neighbours attached: without them the halo lines change between passes by host-issued
   // exchanges, which only the one-pass-per-launch path can interleave
   const bool peers_ok = (c->cfg.halo_w == 0 || c->peer_attached[0]) && (c->cfg.halo_e == 0 || c->peer_attached[1]);
-  const bool layout_ok = (c->L.T >= 128 && c->L.T <= 320) || (cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4);
+  // Lines of 321 .. 992 layout threads have two solvers: one block per line (k_tdma_tma's 672 / 1024-thread builds, one
+  // launch per colour pass) and a cluster of blocks per line (k_tdma_flowc).  Measured at 8192^2 (T = 640): three sweeps
+  // 2.18 ms against 2.55 ms -- the cluster kernel's three-column reduction costs more than the single block's short
+  // ring -- so a lone GPU keeps the first; with neighbouring GPUs attached the cluster kernel wins, because only it
+  // hands the halo lines over from inside the launch.  Beyond 992 threads the cluster kernel is the only solver.
+  const char* fce = getenv("CFD_B200_CLUSTER");          // read per call: tests switch it
+  const bool force_cluster = fce && atoi(fce) != 0;
+  const bool has_peer = c->peer_attached[0] || c->peer_attached[1];
+  const bool cluster_ok = cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4 && (c->L.T + 32 > 1024 || has_peer || force_cluster);
+  const bool layout_ok = (c->L.T >= 128 && c->L.T <= 320) || cluster_ok;
   return use && c->cfg.order == CFD_ORDER_REDBLACK && c->cfg.halo_s == 0 && c->cfg.halo_n == 0 && c->cfg.joff == 0 &&
          layout_ok && c->flags != nullptr && peers_ok;
 }
@@ -476,6 +485,18 @@ static int flow_launch(cfd_ctx* c, int istart, int jstart, int field, int npass,
     P.edge_line[s] = g - 1 - c->cfg.goff;
     P.peer_phi[s] = c->peer_field[s][field] + (long long)peer_line * c->L.LD;
     P.peer_flag[s] = c->peer_flags[s] + peer_line;
+  }
+  {
+    static int timing = -1;
+    if (timing < 0) {
+      const char* e = getenv("CFD_B200_FLOW_TIMING");
+      timing = e ? atoi(e) : 0;
+    }
+    if (timing && !c->dbg) {
+      CFD_CUDA(cudaMalloc(&c->dbg, 8 * sizeof(unsigned long long)));
+      CFD_CUDA(cudaMemset(c->dbg, 0, 8 * sizeof(unsigned long long)));
+    }
+    P.dbg = c->dbg;
   }
   if (cfd_cluster_size(c->L.T) > 0) return cfd_launch_flow_cluster(c, P);    // a line split over a cluster of blocks
   const size_t stage = (size_t)(c->L.nc + 2) * c->L.T * sizeof(double), pcr = (size_t)6 * c->L.T * sizeof(double);

@@ -240,6 +240,10 @@ int cfd_peer_status(cfd_ctx* ctx, int* aborted);
 /* *yes = 1 when cfd_sweeps runs as the single flag-ordered launch in this context (with its neighbours attached as they
    are now): an i-slab driver may only drop its per-pass halo exchanges in that case */
 int cfd_sweeps_single_launch(cfd_ctx* ctx, int* yes);
+/* diagnostic (environment CFD_B200_FLOW_TIMING=1): clock64 sums of the consumer phases of the cluster sweep kernel since
+   the last call -- out[0] = lines solved by block 0, out[1..6] = cycles waiting for / eliminating the slices, in the
+   backward elimination, the cyclic reduction, the cluster exchange, the stores, the end-of-line barrier */
+int cfd_debug_flow_timing(cfd_ctx* ctx, double out[8]);
 
 /* ---- TEACH family: k-epsilon model, energy equation, wall functions -------------------------------
    cfd_set_turbulence allocates te, ed, t, gen, gamh and switches on the wall-function branches of modu / modv

@@ -525,10 +525,11 @@ def test_uniform_property_kernels_give_the_same_bits(cfd, shape, monkeypatch):
 
 
 @pytest.mark.parametrize("shape,cs", [((20, 8192), 2), ((12, 16384), 4), ((8, 20000), 4), ((6, 40000), 8), ((40, 6000), 2)])
-def test_lines_split_over_a_cluster_of_blocks(cfd, oracle, shape, cs):
+def test_lines_split_over_a_cluster_of_blocks(cfd, oracle, shape, cs, monkeypatch):
     """Lines longer than one thread block takes (more than 320 layout threads) are solved by a cluster of 2 / 4 / 8 blocks
     that exchange their interface relations through distributed shared memory (tdma_cluster_kernels.cu): two full
     sweeps in one launch and a single colour pass, against the oracle's red/black lisolv (cavity_fvm.f90:49-82)."""
+    monkeypatch.setenv("CFD_B200_CLUSTER", "1")      # up to 992 layout threads a lone GPU would keep the one-block solver
     o, g = make_pair(cfd, oracle, *shape, order="redblack")
     L = g.layout
     assert L["T"] > 320 and L["T"] % (32 * cs) == 0 and L["T"] // cs <= 320, L

@@ -42,3 +42,13 @@ for name, fn in (("per-pass", per_pass), ("one launch", lambda: g.sweeps(3, 2, "
     t = min(timed(fn, 8))
     print("%-10s best %.3f ms = %.0f GB/s on 64 B/cell" % (name, t, 64 * cells / t / 1e6))
 print("timed out:", g.peer_status())
+if os.environ.get("CFD_B200_FLOW_TIMING"):
+    import ctypes as C
+    out = (C.c_double * 8)()
+    g.lib.cfd_debug_flow_timing(g._h, out)
+    g.sweeps(3, 2, "u", nsw)
+    torch.cuda.synchronize()
+    g.lib.cfd_debug_flow_timing(g._h, out)
+    nl = max(out[0], 1.0)
+    names = ("slices", "backward", "reduction", "exchange", "stores", "end barrier")
+    print("block 0: %d lines; cycles per line: " % nl + ", ".join("%s %.0f" % (k, out[1 + i] / nl) for i, k in enumerate(names)))
