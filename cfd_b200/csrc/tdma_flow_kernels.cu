@@ -375,13 +375,13 @@ bool cfd_flow_eligible(const cfd_ctx* c) {
   const bool peers_ok = (c->cfg.halo_w == 0 || c->peer_attached[0]) && (c->cfg.halo_e == 0 || c->peer_attached[1]);
   // Lines of 321 .. 992 layout threads have two solvers: one block per line (k_tdma_tma's 672 / 1024-thread builds, one
   // launch per colour pass) and a cluster of blocks per line (k_tdma_flowc).  Measured at 8192^2 (T = 640): three sweeps
-  // 2.18 ms against 2.55 ms -- the cluster kernel's three-column reduction costs more than the single block's short
-  // ring -- so a lone GPU keeps the first; with neighbouring GPUs attached the cluster kernel wins, because only it
-  // hands the halo lines over from inside the launch.  Beyond 992 threads the cluster kernel is the only solver.
+  // 2.18 ms against 2.55 ms on one GPU, and the buoyancy iteration over two GPUs 8.07 ms (one block per line, NCCL halo
+  // lines) against 8.32 ms (clusters, halo lines over peer memory): the cluster kernel's three-column reduction costs
+  // more than it saves there, so those layouts keep the first solver.  Beyond 992 threads the cluster kernel is the
+  // only one.  CFD_B200_CLUSTER=1 forces it (tests).
   const char* fce = getenv("CFD_B200_CLUSTER");          // read per call: tests switch it
   const bool force_cluster = fce && atoi(fce) != 0;
-  const bool has_peer = c->peer_attached[0] || c->peer_attached[1];
-  const bool cluster_ok = cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4 && (c->L.T + 32 > 1024 || has_peer || force_cluster);
+  const bool cluster_ok = cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4 && (c->L.T + 32 > 1024 || force_cluster);
   const bool layout_ok = (c->L.T >= 128 && c->L.T <= 320) || cluster_ok;
   return use && c->cfg.order == CFD_ORDER_REDBLACK && c->cfg.halo_s == 0 && c->cfg.halo_n == 0 && c->cfg.joff == 0 &&
          layout_ok && c->flags != nullptr && peers_ok;
