@@ -314,8 +314,8 @@ def run_ours(args):
         cells_total = NICV * world * NJCV
         if getattr(solver, "peer", False):
             par = (f"i-slabs x{world}; halo lines over peer memory (NVLink): edge lines stored into the neighbour's halo from "
-                   "inside the flag-ordered sweep kernels, cfd_halo_push between stages; pp(ipref,jpref) broadcast and "
-                   "residual all-reduce over NCCL")
+                   "inside the flag-ordered sweep kernels, cfd_halo_push between stages, pp(ipref,jpref) by peer stores from "
+                   "its owner; residual all-reduce over NCCL when the host asks")
         else:
             par = (f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals, "
                    + ("one CUDA graph per outer iteration" if graphed else "eager launches"))
@@ -746,8 +746,10 @@ def run_step(args, kind="step"):
            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic", "iters_per_s": K / (ms * 1e-3),
            "config": {"workload": wl,
-                      "parallelism": "single GPU" if world == 1 else f"i-slabs x{world}, 1-line halo exchange (NCCL "
-                                     "send/recv), all-reduced residuals",
+                      "parallelism": "single GPU" if world == 1 else (
+                          f"i-slabs x{world}; halo lines and pp(ipref,jpref) over peer memory (NVLink), all-reduced residuals"
+                          if getattr(solver, "peer", False) else
+                          f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals"),
                       "l2": "inputs larger than L2 (several GB of live fields); no explicit flush",
                       "line_layout": ctx0.layout},
            "residuals_last": [float(x) for x in res[:3]], "gpu_launches": int(launches),

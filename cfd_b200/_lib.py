@@ -112,6 +112,8 @@ SYMBOLS = {
     "cfd_peer_detach": (C.c_int, [_vp]),
     "cfd_halo_push": (C.c_int, [_vp, C.c_int, _ip, _ip, _ip]),
     "cfd_peer_status": (C.c_int, [_vp, _ip]),
+    "cfd_bcast_attach": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "cfd_scalar_bcast": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
     "cfd_sweeps_single_launch": (C.c_int, [_vp, _ip]),
     "cfd_debug_flow_timing": (C.c_int, [_vp, _dp]),
     "cfd_set_turbulence": (C.c_int, [_vp, C.POINTER(CfdTurbulence)]),

@@ -297,6 +297,15 @@ class CavityFVM:
     def peer_detach(self):
         check(self.lib.cfd_peer_detach(self._h))
 
+    def bcast_attach(self, rank: int, flag_block_ptr, rank_ni: int):
+        check(self.lib.cfd_bcast_attach(self._h, rank, C.c_void_p(flag_block_ptr) if flag_block_ptr else None, rank_ni))
+
+    def scalar_bcast(self, owner: bool, name: str, i: int, j: int) -> int:
+        """All ranks call it; returns the device address where the owner's A(i,j) arrives (peer-memory broadcast)."""
+        p = C.c_void_p()
+        check(self.lib.cfd_scalar_bcast(self._h, 1 if owner else 0, FIELD_ID[name], i, j, C.byref(p)))
+        return p.value
+
     def peer_status(self) -> bool:
         """True if a bounded wait on a neighbour ever timed out."""
         a = C.c_int()

@@ -235,6 +235,9 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   c->post_n = 0;
   c->epoch = 1;
   c->xepoch = 0;
+  c->bcast_n = 0;
+  c->bepoch = 0;
+  for (auto& bf : c->bcast_flags) bf = nullptr;
   for (int sd = 0; sd < 2; ++sd) {
     c->peer_attached[sd] = false;
     c->peer_flags[sd] = nullptr;
@@ -324,8 +327,8 @@ extern "C" int cfd_create(cfd_ctx** out, const cfd_config* cfg) {
   CREATE_CUDA(cudaMalloc(&c->res_dev, CFD_RES_SLOTS * sizeof(double)));
   CREATE_CUDA(cudaMemset(c->res_dev, 0, CFD_RES_SLOTS * sizeof(double)));
   // per-line epochs, handshake slots, per-line arrival counters (lines split over a cluster of blocks)
-  CREATE_CUDA(cudaMalloc(&c->flags, (2 * (size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
-  CREATE_CUDA(cudaMemset(c->flags, 0, (2 * (size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int)));
+  CREATE_CUDA(cudaMalloc(&c->flags, (2 * (size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int) + CFD_MAILBOX_DOUBLES * sizeof(double)));
+  CREATE_CUDA(cudaMemset(c->flags, 0, (2 * (size_t)c->L.ni + CFD_FLAG_SLOTS) * sizeof(int) + CFD_MAILBOX_DOUBLES * sizeof(double)));
   {
     // cfd_upload_noalloc's staging area: with lazy module loading the array is only materialised when something in
     // this module is first touched, so touch it HERE, while allocating is still allowed (see cfd_upload_noalloc)
@@ -711,8 +714,22 @@ extern "C" int cfd_peer_attach(cfd_ctx* c, int side, int what, void* devptr, int
   c->peer_attached[side] = c->peer_flags[side] != nullptr;
   return CFD_OK;
 }
+extern "C" int cfd_bcast_attach(cfd_ctx* c, int rank, void* flag_block, int rank_ni) {
+  CFD_REQUIRE(c, "null context");
+  CFD_REQUIRE(rank >= 0 && rank < CFD_BCAST_MAX && rank_ni > 0, "cfd_bcast_attach: bad rank / extent");
+  c->bcast_flags[rank] = flag_block ? (int*)flag_block : c->flags;     // NULL = this context itself
+  c->bcast_ni[rank] = rank_ni;
+  if (rank + 1 > c->bcast_n) c->bcast_n = rank + 1;
+  return CFD_OK;
+}
+extern "C" int cfd_scalar_bcast(cfd_ctx* c, int owner, int field, int i, int j, void** value_dev) {
+  CFD_ENTER(c);
+  CFD_REQUIRE(value_dev, "null argument");
+  return cfd_launch_scalar_bcast(c, owner, field, i, j, (double**)value_dev);
+}
 extern "C" int cfd_peer_detach(cfd_ctx* c) {
   CFD_REQUIRE(c, "null context");
+  c->bcast_n = 0;
   for (int sd = 0; sd < 2; ++sd) {
     c->peer_attached[sd] = false;
     c->peer_flags[sd] = nullptr;

@@ -139,7 +139,10 @@ struct HaloPush {
 #define CFD_FLAG_XREADY 2        /* [2] halo-push ready marks */
 #define CFD_FLAG_SWEEP_READY 4   /* [2] sweep-kernel ready marks */
 #define CFD_FLAG_ABORT 6
+#define CFD_FLAG_BCAST 7         /* epoch of the last scalar broadcast that has arrived (cfd_scalar_bcast) */
 #define CFD_FLAG_SLOTS 8
+#define CFD_MAILBOX_DOUBLES 8    /* behind the flag block: 4 slots of received scalars (by epoch & 3), rest reserved */
+#define CFD_BCAST_MAX 64
 
 }  // namespace cfd
 
@@ -202,6 +205,11 @@ struct cfd_ctx {
   double* peer_field[2][CFD_FIELD_COUNT];
   int* peer_flags[2];
   int peer_ni[2], peer_hw[2], peer_halo_line[2];
+  // one-to-all broadcast of a scalar (pp(ipref,jpref)) over peer memory: the owner holds every rank's flag block
+  int bcast_n;                       // ranks attached (owner only), 0 = none
+  int* bcast_flags[CFD_BCAST_MAX];   // flag block of rank r (its mailbox lies behind it)
+  int bcast_ni[CFD_BCAST_MAX];
+  int bepoch;
   std::vector<void*> ipc_opened;    // mappings made by cfd_ipc_open (closed by cfd_destroy)
   // cavity family: value of den / vis if the last upload of the field was uniform over the whole local array
   bool uni_den, uni_vis, allow_uniform;
@@ -258,5 +266,6 @@ int cfd_cluster_size(int T);
 int cfd_launch_flow_cluster(cfd_ctx* c, cfd::FlowParams& P);
 int cfd_launch_flow_from_sweep(cfd_ctx* c, const cfd::SweepParams& Q, int field_unused);
 int cfd_launch_sweeps_flow(cfd_ctx* c, int istart, int jstart, int field, int nsweeps, int first);
+int cfd_launch_scalar_bcast(cfd_ctx* c, int owner, int field, int i, int j, double** value_dev);
 int cfd_launch_halo_push(cfd_ctx* c, int nfields, const int* fields, const int* w, const int* e);
 int cfd_launch_teach_assemble_fast(cfd_ctx* c, int which, int ia, int ib, double* partial, const double* uinc);

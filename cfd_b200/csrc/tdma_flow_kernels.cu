@@ -338,6 +338,26 @@ __global__ void k_flow_ready(int* r0, int* r1, int epoch0) {
   if (r1) st_release_sys(r1, epoch0);
 }
 
+// ---- one-to-all broadcast of a scalar over peer memory --------------------------------------------------------------
+// The rank that owns pp(ipref,jpref) stores the value into slot (epoch & 3) of every rank's mailbox and releases the
+// rank's broadcast flag; every rank (the owner too) waits for its own flag before the correction kernel reads the slot.
+// Four slots: a rank can be at most a few exchange stages behind the owner, never four broadcasts.
+struct BcastParams {
+  int n;
+  const double* src;
+  int* flags[CFD_BCAST_MAX];
+  double* mail[CFD_BCAST_MAX];
+  int epoch;
+};
+__global__ void k_scalar_send(const BcastParams B) {
+  const int r = threadIdx.x;
+  if (r >= B.n) return;
+  B.mail[r][B.epoch & 3] = *B.src;
+  __threadfence_system();
+  st_release_sys(B.flags[r], B.epoch);
+}
+__global__ void k_scalar_wait(const int* flag, int epoch, int* abort_flag) { wait_flag<true>(flag, epoch, abort_flag); }
+
 template <int M>
 static cudaError_t launch_flow_m(cfd_ctx* c, const FlowParams& P, int nblocks, int S, size_t smem) {
   const int nthreads = P.L.T + 64;   // consumers + producer warp + helper warp
@@ -609,4 +629,41 @@ int cfd_launch_flow_from_sweep(cfd_ctx* c, const cfd::SweepParams& Q, int field_
   }
   if (Q.nlines <= 0) return CFD_OK;
   return cfd_launch_flow_cluster(c, P);
+}
+
+// owner != 0: this context holds element (i,j) (local, 1-based) of `field` and every rank's flag block is attached
+// (cfd_bcast_attach).  *value_dev = device address of the received value, valid until three more broadcasts.
+int cfd_launch_scalar_bcast(cfd_ctx* c, int owner, int field, int i, int j, double** value_dev) {
+  const int epoch = ++c->bepoch;
+  int* myflags = c->flags + c->L.ni;
+  double* mymail = reinterpret_cast<double*>(c->flags + 2 * (size_t)c->L.ni + CFD_FLAG_SLOTS);
+  if (owner) {
+    if (c->bcast_n < 1) {
+      cfd_set_error("cfd_scalar_bcast: the owner has no ranks attached (cfd_bcast_attach)");
+      return CFD_ERR_INVALID;
+    }
+    if (field < 0 || field >= CFD_FIELD_COUNT || !c->field[field] || i < 1 || i > c->L.ni || j < 1 || j > c->L.nj) {
+      cfd_set_error("cfd_scalar_bcast: bad field / index");
+      return CFD_ERR_INVALID;
+    }
+    BcastParams B{};
+    B.n = c->bcast_n;
+    B.src = c->field[field] + (size_t)(i - 1) * c->L.LD + lpos(j - 1, c->L.M, c->L.T);
+    B.epoch = epoch;
+    for (int r = 0; r < c->bcast_n; ++r) {
+      if (!c->bcast_flags[r]) {
+        cfd_set_error("cfd_scalar_bcast: rank %d is not attached", r);
+        return CFD_ERR_INVALID;
+      }
+      B.flags[r] = c->bcast_flags[r] + c->bcast_ni[r] + CFD_FLAG_BCAST;
+      B.mail[r] = reinterpret_cast<double*>(c->bcast_flags[r] + 2 * (size_t)c->bcast_ni[r] + CFD_FLAG_SLOTS);
+    }
+    k_scalar_send<<<1, CFD_BCAST_MAX, 0, c->stream>>>(B);
+    ++c->launches;
+  }
+  k_scalar_wait<<<1, 1, 0, c->stream>>>(myflags + CFD_FLAG_BCAST, epoch, myflags + CFD_FLAG_ABORT);
+  ++c->launches;
+  CFD_CUDA(cudaGetLastError());
+  *value_dev = mymail + (epoch & 3);
+  return CFD_OK;
 }

@@ -283,6 +283,11 @@ def peer_stages(stages):
                 k += 1
             out.append(("sweeps", name, istart, jstart, n // 2, first))
             continue
+        if st[0] == "ppref":
+            out.append(st)
+            out.append(("correct",))                     # the correction reads the broadcast value from the mailbox
+            k += 2                                       # (skips the NCCL path's correct stage that follows)
+            continue
         if st[0] == "halo":
             out.append(("push", ((st[1], st[2], st[3]),)))
         elif st[0] == "halos":
@@ -386,12 +391,21 @@ class SlabCavity(_E2EMixin):
         ok = ok and all(x is not None and x["host"] == every[0]["host"] for x in every)
         if ok:
             try:
+                opened = {}                                 # (rank, what) -> device pointer: every handle is opened once
+
+                def peer_ptr(r, n):
+                    if (r, n) not in opened:
+                        opened[(r, n)] = ctx.ipc_open(every[r]["h"][n])
+                    return opened[(r, n)]
+
                 for side, r in ((0, self.rank - 1), (1, self.rank + 1)):
                     if 0 <= r < self.world:
                         for n in names + ("flags",):
-                            ptr = ctx.ipc_open(every[r]["h"][n])
-                            ctx.peer_attach(side, n, ptr, every[r]["ni"], every[r]["hw"], every[r]["he"])
+                            ctx.peer_attach(side, n, peer_ptr(r, n), every[r]["ni"], every[r]["hw"], every[r]["he"])
                 ok = ctx.sweeps_single_launch()             # short lines keep the pass-by-pass solver, which needs the NCCL stages
+                if ok and s.owner_of_pref:                  # the owner of pp(ipref,jpref) reaches every rank's mailbox
+                    for r in range(self.world):
+                        ctx.bcast_attach(r, None if r == self.rank else peer_ptr(r, "flags"), every[r]["ni"])
             except Exception as e:                          # noqa: BLE001
                 self.peer_error, ok = repr(e), False
         agree = torch.tensor([1 if ok else 0], device="cuda")
@@ -407,16 +421,19 @@ class SlabCavity(_E2EMixin):
         s = self.slab
         for _ in range(n):
             for st in self.pstages:
-                if st[0] == "compute":
+                if st[0] == "correct":
+                    s.ctx.correct(self._ppref_dev)
+                elif st[0] == "compute":
                     st[1](s)
                 elif st[0] == "sweeps":
                     s.ctx.sweeps(st[2], st[3], st[1], st[4], first=st[5])
                 elif st[0] == "push":
                     s.ctx.halo_push(st[1])
+                elif st[0] == "ppref":
+                    # pp(ipref,jpref) from its owner into every rank's mailbox (peer stores), then the correction
+                    self._ppref_dev = s.ctx.scalar_bcast(s.owner_of_pref, "pp", s.ipref - s.goff, s.jpref)
                 else:
-                    if s.owner_of_pref:
-                        s.ppref.copy_(s.ppref_element())
-                    self.comm.broadcast(s.ppref, self.pref_owner)
+                    raise ValueError(st[0])
 
     def enable_graph(self, stream):
         """Capture one outer iteration (kernels + NCCL halo exchanges) into a CUDA graph and replay it from then

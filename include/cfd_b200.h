@@ -237,6 +237,13 @@ int cfd_peer_attach(cfd_ctx* ctx, int side, int what, void* devptr, int peer_ni,
 int cfd_peer_detach(cfd_ctx* ctx);
 int cfd_halo_push(cfd_ctx* ctx, int nfields, const int* fields, const int* w, const int* e);
 int cfd_peer_status(cfd_ctx* ctx, int* aborted);
+/* pp(ipref,jpref) to every rank without a collective: the rank that owns the cell attaches every rank's flag block
+   (cfd_bcast_attach(ctx, rank, ptr, that rank's ni); ptr = NULL for itself); cfd_scalar_bcast(ctx, owner, field, i, j, &v)
+   -- called by ALL ranks, owner != 0 on the owning one -- stores the value into every rank's mailbox (peer stores), and
+   returns in v the device address where this rank will find it; the wait for its arrival is queued on the stream.
+   Pass v to cfd_correct. */
+int cfd_bcast_attach(cfd_ctx* ctx, int rank, void* flag_block, int rank_ni);
+int cfd_scalar_bcast(cfd_ctx* ctx, int owner, int field, int i, int j, void** value_dev);
 /* *yes = 1 when cfd_sweeps runs as the single flag-ordered launch in this context (with its neighbours attached as they
    are now): an i-slab driver may only drop its per-pass halo exchanges in that case */
 int cfd_sweeps_single_launch(cfd_ctx* ctx, int* yes);
