@@ -517,10 +517,10 @@ static int launch_assemble(cfd_ctx* c, int which, CavParams& P, int eq) {
     use_tma = e ? atoi(e) : 1;
   }
   const bool jslab = c->cfg.halo_s > 0 || c->cfg.halo_n > 0;
-  // TMA-staged persistent kernels for lines of 128..320 layout threads (the 384-thread build: 168 registers, no
-  // spills).  Longer lines would need the 768-thread build, which spills and measured 17.1 ms per iteration at
-  // 8192^2 against 11.2 ms with the register-window kernels below, so those keep the register-window path.
-  if (fast && use_tma && !jslab && c->L.T >= 128 && c->L.T + 64 <= 384) {
+  // TMA-staged persistent kernels (the 384-thread build: 168 registers, no spills): lines of 128..320 layout threads in
+  // one block, longer lines split over 2 / 4 / 8 blocks of that size (a 768-thread build spilt and measured 17.1 ms per
+  // iteration at 8192^2 against 11.2 ms with the register-window kernels, which remain the fallback).
+  if (fast && use_tma && !jslab && cfd_assemble_tma_split(c->L.T) > 0) {
     P.partial = c->partial + (size_t)eq * c->max_partials;
     const int nb = cfd_launch_assemble_tma(c, which, P);
     if (nb < 0) return nb;

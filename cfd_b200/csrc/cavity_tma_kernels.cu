@@ -68,19 +68,23 @@ __host__ __device__ constexpr int u_slot(int a, bool uni) {
   return !uni ? a : (a <= 2 ? a : (a == 7 ? 3 : (a == 8 ? 4 : (a == 11 ? 5 : (a == 12 ? 6 : -1)))));
 }
 template <int BMAX, bool UNI>
-__global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, const FastGeom G, const int S) {
+__global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, const FastGeom G, const int S, const int NSPLIT) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int T = P.L.T, M = P.L.M, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int tid = threadIdx.x;
+  // a line of more than 320 layout threads is split over NSPLIT blocks of TT = T / NSPLIT consumers each: block part
+  // stages and evaluates chunks toff .. toff+TT-1 of the line (the chunk-edge neighbours come from global memory anyway)
+  const int TT = T / NSPLIT, toff = ((int)blockIdx.x % NSPLIT) * TT;
+  const int bline = (int)blockIdx.x / NSPLIT, lstride = (int)gridDim.x / NSPLIT;
   constexpr int NA = UNI ? 7 : NU_ARR;
-  const int SW = NA * T;
+  const int SW = NA * TT;
   const double den0 = UNI ? P.den0 : 0.0, vis0 = UNI ? P.vis0 : 0.0;
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* red = ring + (size_t)S * SW;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(red + 32);
   const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S);
-  const int ncw = T / 32;
+  const int ncw = TT / 32;
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
       mbar_init(full0 + 8 * s, 1);
@@ -92,12 +96,12 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
   __syncthreads();
   const int nlines = P.ib - P.ia + 1;
 
-  if (tid >= T) {
-    if (((tid - T) & 31) == 0) {   // ---- producers: one elected lane per producer warp, arrays dealt round-robin
-      const int pw = (tid - T) >> 5;
-      const unsigned sb = (unsigned)(T * sizeof(double));
+  if (tid >= TT) {
+    if (((tid - TT) & 31) == 0) {   // ---- producers: one elected lane per producer warp, arrays dealt round-robin
+      const int pw = (tid - TT) >> 5;
+      const unsigned sb = (unsigned)(TT * sizeof(double));
       unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
-      for (int line = blockIdx.x; line < nlines; line += gridDim.x) {
+      for (int line = bline; line < nlines; line += lstride) {
         const long long i0 = P.ia + line;
         const double* src[NU_ARR] = {P.u + i0 * LD,         P.v + (i0 - 1) * LD,   P.v + i0 * LD,       P.den + (i0 - 1) * LD,
                                      P.den + i0 * LD,       P.vis + (i0 - 1) * LD, P.vis + i0 * LD,     P.u + (i0 - 1) * LD,
@@ -114,7 +118,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
           for (int a = 0; a < NU_ARR; ++a) {
             if (UNI && u_is_prop(a)) continue;
             const int sl = u_slot(a, UNI);
-            if ((sl % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + sl * sb, src[a] + (size_t)k * T, sb, fb);
+            if ((sl % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + sl * sb, src[a] + (size_t)k * T + toff, sb, fb);
           }
         }
       }
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
   }
 
   // ---- consumers
-  const int t = tid, lane = tid & 31;
+  const int t = toff + tid, lane = tid & 31;
   const int j0base = t * M;
   const bool hasprev = j0base >= 1, hasnext = j0base + M < nj;
   const int qprev = (M - 1) * T + t - 1, qnext = t + 1;
@@ -133,15 +137,15 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
   unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
   // chunk-edge neighbours (node j0base-1) of the first line, fetched ahead
   double em_u = 0, em_dW = 0, em_dC = 0, em_A = 0, em_rdy = 0;
-  if ((int)blockIdx.x < nlines && hasprev) {
-    const long long i0 = P.ia + blockIdx.x;
+  if (bline < nlines && hasprev) {
+    const long long i0 = P.ia + bline;
     em_u = __ldg(P.u + i0 * LD + qprev);
     em_dW = UNI ? den0 : __ldg(P.den + (i0 - 1) * LD + qprev);
     em_dC = UNI ? den0 : __ldg(P.den + i0 * LD + qprev);
     em_A = UNI ? vis0 + vis0 : __ldg(P.vis + (i0 - 1) * LD + qprev) + __ldg(P.vis + i0 * LD + qprev);
     em_rdy = __ldg(G.rdyL + qprev);
   }
-  for (int line = blockIdx.x; line < nlines; line += gridDim.x) {
+  for (int line = bline; line < nlines; line += lstride) {
     const long long i0 = P.ia + line;
     const long long out = i0 * LD, cout = i0 * P.L.cSL;
     // node j0base+M of this line (used after the last slice) and node j0base-1 of the next line
@@ -156,8 +160,8 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
       ep_vC = __ldg(P.v + i0 * LD + qnext);
     }
     double nm_u = 0, nm_dW = 0, nm_dC = 0, nm_A = 0;
-    if (line + (int)gridDim.x < nlines && hasprev) {
-      const long long n0 = i0 + gridDim.x;
+    if (line + lstride < nlines && hasprev) {
+      const long long n0 = i0 + lstride;
       nm_u = __ldg(P.u + n0 * LD + qprev);
       nm_dW = UNI ? den0 : __ldg(P.den + (n0 - 1) * LD + qprev);
       nm_dC = UNI ? den0 : __ldg(P.den + n0 * LD + qprev);
@@ -178,20 +182,20 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
         const unsigned s = rs, ph = rph;
         if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
         mbar_wait(full0 + 8 * s, ph);
-        const double* sl = ring + (size_t)s * SW + t;
+        const double* sl = ring + (size_t)s * SW + tid;
         u_n = sl[0];
-        vW_p = sl[T];
-        vC_p = sl[2 * T];
-        dW_p = UNI ? den0 : sl[3 * T];
-        dC_p = UNI ? den0 : sl[4 * T];
-        sW_p = UNI ? vis0 : sl[5 * T];
-        sC_p = UNI ? vis0 : sl[6 * T];
-        n_uW = sl[u_slot(7, UNI) * T];
-        n_uE = sl[u_slot(8, UNI) * T];
-        n_dWW = UNI ? den0 : sl[9 * T];
-        n_dE = UNI ? den0 : sl[10 * T];
-        n_pW = sl[u_slot(11, UNI) * T];
-        n_pC = sl[u_slot(12, UNI) * T];
+        vW_p = sl[TT];
+        vC_p = sl[2 * TT];
+        dW_p = UNI ? den0 : sl[3 * TT];
+        dC_p = UNI ? den0 : sl[4 * TT];
+        sW_p = UNI ? vis0 : sl[5 * TT];
+        sC_p = UNI ? vis0 : sl[6 * TT];
+        n_uW = sl[u_slot(7, UNI) * TT];
+        n_uE = sl[u_slot(8, UNI) * TT];
+        n_dWW = UNI ? den0 : sl[9 * TT];
+        n_dE = UNI ? den0 : sl[10 * TT];
+        n_pW = sl[u_slot(11, UNI) * TT];
+        n_pC = sl[u_slot(12, UNI) * TT];
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * s);
         const int q = k * T + t;
@@ -259,7 +263,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_u_tma(const CavParams P, c
     }
     em_u = nm_u; em_dW = nm_dW; em_dC = nm_dC; em_A = nm_A;
   }
-  consumer_sum_to(racc, red, T, t, P.partial + blockIdx.x);
+  consumer_sum_to(racc, red, TT, tid, P.partial + blockIdx.x);
 }
 
 // =====================================================================================================
@@ -272,19 +276,23 @@ __host__ __device__ constexpr int v_slot(int a, bool uni) {
   return !uni ? a : (a == 0 ? 0 : (a == 2 ? 1 : (a == 3 ? 2 : (a == 9 ? 3 : (a == 10 ? 4 : (a == 11 ? 5 : -1))))));
 }
 template <int BMAX, bool UNI>
-__global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, const FastGeom G, const int S) {
+__global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, const FastGeom G, const int S, const int NSPLIT) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int T = P.L.T, M = P.L.M, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int tid = threadIdx.x;
+  // a line of more than 320 layout threads is split over NSPLIT blocks of TT = T / NSPLIT consumers each: block part
+  // stages and evaluates chunks toff .. toff+TT-1 of the line (the chunk-edge neighbours come from global memory anyway)
+  const int TT = T / NSPLIT, toff = ((int)blockIdx.x % NSPLIT) * TT;
+  const int bline = (int)blockIdx.x / NSPLIT, lstride = (int)gridDim.x / NSPLIT;
   constexpr int NA = UNI ? 6 : NV_ARR;
-  const int SW = NA * T;
+  const int SW = NA * TT;
   const double den0 = UNI ? P.den0 : 0.0, vis0 = UNI ? P.vis0 : 0.0;
   double* ring = reinterpret_cast<double*>(smem_raw);
   double* red = ring + (size_t)S * SW;
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(red + 32);
   const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + S);
-  const int ncw = T / 32;
+  const int ncw = TT / 32;
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
       mbar_init(full0 + 8 * s, 1);
@@ -296,12 +304,12 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
   __syncthreads();
   const int nlines = P.ib - P.ia + 1;
 
-  if (tid >= T) {
-    if (((tid - T) & 31) == 0) {
-      const int pw = (tid - T) >> 5;
-      const unsigned sb = (unsigned)(T * sizeof(double));
+  if (tid >= TT) {
+    if (((tid - TT) & 31) == 0) {
+      const int pw = (tid - TT) >> 5;
+      const unsigned sb = (unsigned)(TT * sizeof(double));
       unsigned rs = 0, rph = 0;   // ring slot and its phase bit, advanced together (no div/mod per slice)
-      for (int line = blockIdx.x; line < nlines; line += gridDim.x) {
+      for (int line = bline; line < nlines; line += lstride) {
         const long long i0 = P.ia + line;
         const double* src[NV_ARR] = {P.v + i0 * LD,         P.den + i0 * LD,       P.u + i0 * LD,         P.u + (i0 + 1) * LD,
                                      P.den + (i0 - 1) * LD, P.den + (i0 + 1) * LD, P.vis + (i0 - 1) * LD, P.vis + i0 * LD,
@@ -317,7 +325,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
           for (int a = 0; a < NV_ARR; ++a) {
             if (UNI && v_is_prop(a)) continue;
             const int sl = v_slot(a, UNI);
-            if ((sl % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + sl * sb, src[a] + (size_t)k * T, sb, fb);
+            if ((sl % ASM_PRODUCER_WARPS) == pw) tma_load_1d(dst + sl * sb, src[a] + (size_t)k * T + toff, sb, fb);
           }
         }
       }
@@ -325,7 +333,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
     return;
   }
 
-  const int t = tid, lane = tid & 31;
+  const int t = toff + tid, lane = tid & 31;
   const int j0base = t * M;
   const bool hasprev = j0base >= 1, hasnext = j0base + M < nj;
   const int qprev = (M - 1) * T + t - 1, qnext = t + 1;
@@ -356,9 +364,9 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
     return e;
   };
   Edge em{};
-  if ((int)blockIdx.x < nlines) em = load_edge(P.ia + blockIdx.x);
+  if (bline < nlines) em = load_edge(P.ia + bline);
   const double g_rdyv_prev0 = hasprev ? __ldg(G.rdyvL + qprev) : 0.0, g_rsns_prev0 = hasprev ? __ldg(G.rsnsL + qprev) : 0.0;
-  for (int line = blockIdx.x; line < nlines; line += gridDim.x) {
+  for (int line = bline; line < nlines; line += lstride) {
     const long long i0 = P.ia + line;
     const long long out = i0 * LD, cout = i0 * P.L.cSL;
     double ep_v = 0, ep_dC = 0;
@@ -367,7 +375,7 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
       ep_dC = UNI ? den0 : __ldg(P.den + i0 * LD + qnext);
     }
     Edge nm{};
-    if (line + (int)gridDim.x < nlines) nm = load_edge(i0 + gridDim.x);
+    if (line + lstride < nlines) nm = load_edge(i0 + lstride);
     const double sew_i = __ldg(P.sew + i0), r_sew_i = __ldg(G.rsew + i0);
     const double r_dxe = __ldg(G.rdx + i0), r_dxw = __ldg(G.rdx + i0 - 1);
     // state "at node kk-1" (m) and "at node kk" (c); vC / dC also one node ahead (n / p)
@@ -385,19 +393,19 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
         const unsigned s = rs, ph = rph;
         if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
         mbar_wait(full0 + 8 * s, ph);
-        const double* sl = ring + (size_t)s * SW + t;
+        const double* sl = ring + (size_t)s * SW + tid;
         v_n = sl[0];
-        dC_p = UNI ? den0 : sl[T];
-        n_uC = sl[v_slot(2, UNI) * T];
-        n_uE = sl[v_slot(3, UNI) * T];
-        n_dW = UNI ? den0 : sl[4 * T];
-        n_dE = UNI ? den0 : sl[5 * T];
-        n_sW = UNI ? vis0 : sl[6 * T];
-        n_sC = UNI ? vis0 : sl[7 * T];
-        n_sE = UNI ? vis0 : sl[8 * T];
-        n_p = sl[v_slot(9, UNI) * T];
-        n_vW = sl[v_slot(10, UNI) * T];
-        n_vE = sl[v_slot(11, UNI) * T];
+        dC_p = UNI ? den0 : sl[TT];
+        n_uC = sl[v_slot(2, UNI) * TT];
+        n_uE = sl[v_slot(3, UNI) * TT];
+        n_dW = UNI ? den0 : sl[4 * TT];
+        n_dE = UNI ? den0 : sl[5 * TT];
+        n_sW = UNI ? vis0 : sl[6 * TT];
+        n_sC = UNI ? vis0 : sl[7 * TT];
+        n_sE = UNI ? vis0 : sl[8 * TT];
+        n_p = sl[v_slot(9, UNI) * TT];
+        n_vW = sl[v_slot(10, UNI) * TT];
+        n_vE = sl[v_slot(11, UNI) * TT];
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * s);
         const int q = k * T + t;
@@ -467,12 +475,20 @@ __global__ void __launch_bounds__(BMAX, 1) k_assemble_v_tma(const CavParams P, c
     }
     em = nm;
   }
-  consumer_sum_to(racc, red, T, t, P.partial + blockIdx.x);
+  consumer_sum_to(racc, red, TT, tid, P.partial + blockIdx.x);
 }
 
 }  // namespace cfd
 
 using namespace cfd;
+
+// blocks per line for the TMA-staged assembly: the smallest split whose consumer count fits the 384-thread build
+// (168 registers, no spills); 0 = the layout does not split that way
+int cfd_assemble_tma_split(int T) {
+  for (int n = 1; n <= 8; ++n)
+    if (T % (32 * n) == 0 && T / n >= 128 && T / n + 32 * ASM_PRODUCER_WARPS <= 384) return n;
+  return 0;
+}
 
 // returns the number of partial sums written (grid size), or a negative status
 int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
@@ -482,22 +498,24 @@ int cfd_launch_assemble_tma(cfd_ctx* c, int which, CavParams& P) {
   const int num_sms = c->num_sms;
   const bool uni = P.uniform != 0;
   const int T = c->L.T, narr = uni ? (which == 0 ? 7 : 6) : (which == 0 ? NU_ARR : NV_ARR);
-  const size_t stage = (size_t)narr * T * sizeof(double);
+  const int nsplit = cfd_assemble_tma_split(T);
+  if (!nsplit) {
+    cfd_set_error("k_assemble_*_tma: lines of %d layout threads do not split into blocks of 128..320 consumers", T);
+    return CFD_ERR_INVALID;
+  }
+  const int TT = T / nsplit;
+  const size_t stage = (size_t)narr * TT * sizeof(double);
   int S = uni ? 10 : 8;      // the uniform-property stage is about half as large: a deeper ring fits
   const char* es = getenv("CFD_B200_ASM_STAGES");
   if (es && atoi(es) > 0) S = atoi(es);
   while (S > 2 && S * stage + 32 * 8 + 2 * S * 8 > 200 * 1024) --S;
   const size_t smem = S * stage + 32 * 8 + 2 * (size_t)S * 8;
   const int nlines = P.ib - P.ia + 1;
-  const int nblocks = nlines < num_sms ? nlines : num_sms;
+  const int nblocks = nlines * nsplit < num_sms ? nlines * nsplit : num_sms / nsplit * nsplit;
   cudaError_t e;
 #define LAUNCH_ASM(KERNEL)                                                                         \
   e = cfd_raise_smem(c, KERNEL);                                                                   \
-  if (e == cudaSuccess) KERNEL<<<nblocks, T + 32 * ASM_PRODUCER_WARPS, smem, c->stream>>>(P, G, S);
-  if (T + 32 * ASM_PRODUCER_WARPS > 384) {   // a 768-thread build spills (80 registers) and loses to the register-window kernels
-    cfd_set_error("k_assemble_*_tma: lines of %d layout threads do not fit the 384-thread build", T);
-    return CFD_ERR_INVALID;
-  }
+  if (e == cudaSuccess) KERNEL<<<nblocks, TT + 32 * ASM_PRODUCER_WARPS, smem, c->stream>>>(P, G, S, nsplit);
   if (which == 0) {
     if (uni) { LAUNCH_ASM((k_assemble_u_tma<384, true>)) } else { LAUNCH_ASM((k_assemble_u_tma<384, false>)) }
   } else {

@@ -255,6 +255,7 @@ int cfd_launch_reduce_partials(cfd_ctx* c, int eq, int nblocks);
 int cfd_launch_assemble_fast(cfd_ctx* c, int which, cfd::CavParams& P, dim3 grid, dim3 block);
 int cfd_update_fast_geometry(cfd_ctx* c);
 int cfd_launch_assemble_tma(cfd_ctx* c, int which, cfd::CavParams& P);
+int cfd_assemble_tma_split(int T);
 int cfd_launch_general_assemble(cfd_ctx* c, int which);
 int cfd_launch_general_assemble_fast(cfd_ctx* c, int which, double* partial);
 int cfd_launch_teach_assemble(cfd_ctx* c, int which);

@@ -227,25 +227,33 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
         bN_next = __ldg(ph + q_n);
       }
       double ca[M], cc[M], cf[M];
+      // The elimination is a dependent chain per thread (reciprocal of the pivot, then the row): with lines this long
+      // the consumers, not HBM, set the pace, so the pivot operands `as` (and `ap`) of slice k+1 are fetched -- and its
+      // barrier waited for -- while slice k is still in the chain.
+      unsigned s_cur = rs, ph_cur = rph;
+      if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+      mbar_wait(full0 + 8 * s_cur, ph_cur);
+      double b_nx = lds_f64(ring32 + s_cur * stage_bytes + T8), d_nx = (nc == 6) ? lds_f64(ring32 + s_cur * stage_bytes + 2 * T8) : 1.0;
 #pragma unroll
       for (int k = 0; k < M; ++k) {
-        const unsigned s = rs, ph = rph;
-        if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
-        mbar_wait(full0 + 8 * s, ph);
-        const unsigned sl = ring32 + s * stage_bytes;
-        double a = lds_f64(sl), b = lds_f64(sl + T8), d = 1.0;
-        unsigned sr = sl + 2 * T8;
-        if (nc == 6) {
-          d = lds_f64(sr);
-          sr += T8;
-        }
+        const unsigned sl = ring32 + s_cur * stage_bytes;
+        double a = lds_f64(sl), b = b_nx, d = d_nx;
+        const unsigned sr = sl + (nc == 6 ? 3u : 2u) * T8;
         double cv = lds_f64(sr + 2 * T8);
         if (!zeroEW) {
           cv = fma(lds_f64(sr + T8), lds_f64(sr + 4 * T8), cv);
           cv = fma(lds_f64(sr), lds_f64(sr + 3 * T8), cv);
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(empty0 + 8 * s);
+        if (lane == 0) mbar_arrive(empty0 + 8 * s_cur);
+        if (k + 1 < M) {
+          s_cur = rs;
+          ph_cur = rph;
+          if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
+          mbar_wait(full0 + 8 * s_cur, ph_cur);
+          b_nx = lds_f64(ring32 + s_cur * stage_bytes + T8);
+          if (nc == 6) d_nx = lds_f64(ring32 + s_cur * stage_bytes + 2 * T8);
+        }
         const int j0 = j0base + k;
         if (!(j0 >= P.jlo && j0 <= P.jhi)) {
           a = 0.0;
