@@ -15,6 +15,7 @@
 //     unknowns redundantly by a short recurrence; then back-substitution and stores as in k_tdma_flow.
 //   * a line is published (flag = epoch) by whichever block's helper lane arrives last at the line's arrival counter.
 // Producer / helper roles, flags, peer halos and the work order are those of k_tdma_flow (flow.cuh).
+#include <cuda.h>
 #include "flow.cuh"
 
 namespace cfd {
@@ -73,10 +74,23 @@ __device__ __forceinline__ void st_async_f64(unsigned raddr, double v, unsigned 
                : "memory");
 }
 
+// one tiled bulk copy (TMA) of a 3-D box out of this GPU's memory: [c2 rows][c1 segments][segment] -> dense shared memory
+__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* tm, int c0, int c1, int c2, unsigned bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+      "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+      : "memory");
+}
+
 #define XCH_N 9   // per block and line: E = (r, pL, pR) of chunk-end 0, A = (r, pL, pR) of chunk-end Tc-1, first node (cc0, cf0, ca0)
 
+// TM: the nc coefficient parts of a slice arrive as ONE tiled copy through a tensor map of the coefficient block (rows of T
+// doubles: row (i0*M + k)*nc + a; the block's Tc columns as Tc/SEG segments of SEG <= 256 doubles) instead of nc 1-D
+// copies of Tc doubles.  Measured need: with seven copies of 2.5 KB per slice the copy engine, not HBM, set the pace
+// (about 85 ns per copy).
 template <int M, int NC, int CS>
-__global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const int S) {
+__global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const int S, const int SEG,
+                                                       const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int T = P.L.T, Tc = T / CS;
   const long long LD = P.L.LD;
@@ -167,21 +181,25 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
           if (it.p > 0) asm volatile("fence.proxy.async;" ::: "memory");
         }
         __syncwarp();
-        // source of this lane's array for node slice 0
+        const bool tm = SEG > 0;
+        // lane's source for node slice 0: with the tensor map lane 0 takes all nc coefficient parts in one tiled copy
         const double* src = la < nc ? P.coef + (long long)i0 * P.L.cSL + (size_t)la * T + crank * Tc
                                     : P.phi + (long long)(la == nc ? i0 + 1 : i0 - 1) * LD + crank * Tc;
         const size_t kstride = la < nc ? (size_t)P.L.cSK : (size_t)T;
-        const bool mine = la < nc || (la < nc + 2 && !zeroEW);
+        const bool mine = la < nc ? !tm : (la < nc + 2 && !zeroEW);
+        const int row0 = i0 * M * nc, seg0 = tm ? crank * (Tc / SEG) : 0;
         for (int k = 0; k < M; ++k) {
           const unsigned s = rs, ph = rph;
           if (++rs == (unsigned)S) { rs = 0; rph ^= 1u; }
           const unsigned fb = full0 + 8 * s;
+          const unsigned dst = smem_u32(ring + (size_t)s * SW);
           if (la == 0) {
             mbar_wait(empty0 + 8 * s, ph ^ 1u);
             mbar_expect_tx(fb, tx);
+            if (tm) tma_load_3d(dst, &tmap, 0, seg0, row0 + k * nc, fb);
           }
           __syncwarp();
-          if (mine) tma_load_1d(smem_u32(ring + (size_t)s * SW) + la * part_bytes, src + (size_t)k * kstride, part_bytes, fb);
+          if (mine) tma_load_1d(dst + la * part_bytes, src + (size_t)k * kstride, part_bytes, fb);
         }
       }
       if (la == 0 && blockIdx.x == 0) {
@@ -480,9 +498,44 @@ __global__ void __launch_bounds__(384, 1) k_tdma_flowc(const FlowParams P, const
   cluster_sync_all();   // no block leaves while another may still read its shared memory or signal its barrier
 }
 
+// Tensor map of a context's coefficient block, for the tiled copies of k_tdma_flowc: 3-D view (SEG, T/SEG, ni*M*nc rows) of
+// doubles, box (SEG, Tc/SEG, nc).  Returns the segment length, 0 if the driver entry point is not available (the kernel
+// then uses 1-D copies).
+static int coef_tensor_map(cfd_ctx* c, int Tc, CUtensorMap* tm) {
+  typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static encode_fn enc = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* fp = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    const char* e = getenv("CFD_B200_TDMA_TENSORMAP");
+    if (!(e && atoi(e) == 0) && cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess)
+      enc = (encode_fn)fp;
+    (void)cudaGetLastError();
+  }
+  if (!enc) return 0;
+  const int T = c->L.T, nc = c->L.nc;
+  const int seg = Tc <= 256 ? Tc : Tc / 2;
+  if (Tc % seg != 0 || seg > 256 || (seg * 8) % 16 != 0) return 0;
+  const cuuint64_t gdim[3] = {(cuuint64_t)seg, (cuuint64_t)(T / seg), (cuuint64_t)c->L.ni * c->L.M * nc};
+  const cuuint64_t gstr[2] = {(cuuint64_t)seg * 8, (cuuint64_t)T * 8};
+  const cuuint32_t box[3] = {(cuuint32_t)seg, (cuuint32_t)(Tc / seg), (cuuint32_t)nc};
+  const cuuint32_t est[3] = {1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void*)c->coef, gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? seg : 0;
+}
+
 template <int M, int NC, int CS>
 static cudaError_t launch_flowc_cs(cfd_ctx* c, const FlowParams& P, int S, size_t smem, int nmax) {
   const int Tc = P.L.T / CS;
+  CUtensorMap tmap;
+  memset(&tmap, 0, sizeof(tmap));
+  const int SEG = coef_tensor_map(c, Tc, &tmap);
   auto kern = k_tdma_flowc<M, NC, CS>;
   cudaError_t e = cfd_raise_smem(c, kern);
   if (e != cudaSuccess) return e;
@@ -512,11 +565,11 @@ static cudaError_t launch_flowc_cs(cfd_ctx* c, const FlowParams& P, int S, size_
   if (ncl > nmax) ncl = nmax;
   cfg.gridDim = dim3(ncl * CS);
   cfg.numAttrs = 2;
-  e = cudaLaunchKernelEx(&cfg, kern, P, S);
+  e = cudaLaunchKernelEx(&cfg, kern, P, S, SEG, tmap);
   if (e != cudaSuccess) {           // cooperative + cluster not accepted: the occupancy bound above still holds on an idle GPU
     (void)cudaGetLastError();
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, kern, P, S);
+    e = cudaLaunchKernelEx(&cfg, kern, P, S, SEG, tmap);
   }
   return e;
 }
