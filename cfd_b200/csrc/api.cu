@@ -593,8 +593,9 @@ extern "C" int cfd_assemble_v(cfd_ctx* c) { CFD_ENTER(c); return asm_v(c); }
 extern "C" int cfd_assemble_p(cfd_ctx* c) { CFD_ENTER(c); return asm_p(c); }
 extern "C" int cfd_assemble_t(cfd_ctx* c) {
   CFD_ENTER(c);
-  CFD_REQUIRE(is_general(c), "cfd_assemble_t needs a CFD_FAMILY_GENERAL context");
-  return cfd_launch_general_assemble(c, 3);
+  CFD_REQUIRE(is_general(c) || (is_teach(c) && c->turbulent),
+              "cfd_assemble_t needs a CFD_FAMILY_GENERAL context, or a TEACH context after cfd_set_turbulence");
+  return is_general(c) ? cfd_launch_general_assemble(c, 3) : cfd_launch_teach_scalar(c, CFD_EQ_T);
 }
 extern "C" int cfd_set_hook(cfd_ctx* c, int eq, const cfd_hook_desc* d) {
   CFD_REQUIRE(c && d, "null argument");
@@ -832,7 +833,6 @@ extern "C" int cfd_calct(cfd_ctx* c, double* resort) {
 extern "C" int cfd_set_turbulence(cfd_ctx* c, const cfd_turbulence* m) {
   CFD_REQUIRE(c && m, "null argument");
   CFD_REQUIRE(is_teach(c), "cfd_set_turbulence needs a CFD_FAMILY_TEACH context");
-  CFD_REQUIRE(c->cfg.goff == 0 && c->cfg.halo_w == 0 && c->cfg.halo_e == 0, "turbulent TEACH contexts do not shard yet");
   CFD_REQUIRE(m->urfk > 0 && m->urfe > 0 && m->urft > 0 && m->nswpk >= 0 && m->nswpd >= 0 && m->nswpt >= 0, "bad model values");
   CFD_CUDA(cudaSetDevice(c->device));
   const size_t fbytes = (size_t)c->L.ni * c->L.LD * sizeof(double);

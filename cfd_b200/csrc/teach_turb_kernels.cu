@@ -19,6 +19,9 @@ namespace cfd {
 struct TurbParams {
   Layout L;
   int indcos, istep, jstep;
+  int goff, ni_global;       // global 1-based i of local line i0 is i0 + 1 + goff (i-slab contexts)
+  int il_lo, il_hi;          // owned interior lines (local, 0-based, inclusive)
+  int halo_w, halo_e;
   double viscos, great, urf, rurf;
   cfd_turbulence m;
   const double *u, *v, *den;
@@ -64,14 +67,16 @@ __device__ __forceinline__ void tq_block_sum(double v, double* partial) {
 
 // ---- wall-function pre-pass of modu (which = 0, threads over i) / modv (which = 1, threads over j) ----------------
 __global__ void k_teach_wall(const TurbParams P, int which) {
-  const int ni = P.L.ni, nj = P.L.nj, nim1 = ni - 1, njm1 = nj - 1, M = P.L.M, T = P.L.T;
+  const int ni = P.L.ni, nj = P.L.nj, njm1 = nj - 1, M = P.L.M, T = P.L.T;
   const long long LD = P.L.LD;
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   auto F = [&](const double* f, int i, int j) { return f[(long long)(i - 1) * LD + lpos(j - 1, M, T)]; };
   const double cdterm = pow(P.m.cmu, 0.25);
   if (which == 0) {
-    const int i = n;
-    if (i < 3 || i > nim1) return;
+    // local 1-based line i; taun(i) needs the lines i-1, i, so it exists for every owned line and for the east halo
+    // line next to the slab (calcte reads taun(i+1)); global tests through ig
+    const int i = n, ig = n + P.goff, NI = P.ni_global;
+    if (ig < 3 || ig > NI - 1 || i < 2 || i - 1 < P.il_lo || i - 1 > P.il_hi + (P.halo_e ? 1 : 0)) return;
     const int j = njm1;
     const double yp = P.yvn[nj - 1] - P.yn[njm1 - 1];
     const double sqrtk = sqrt(0.5 * (F(P.te, i, j) + F(P.te, i - 1, j)));
@@ -86,12 +91,13 @@ __global__ void k_teach_wall(const TurbParams P, int which) {
     const double tau = -tmult * F(P.u, i, j);
     P.tmult_n[i - 1] = tmult;
     P.taun[i - 1] = tau;
-    if (i == 3) P.taun[1] = tau;          // taun(2) = taun(3)
-    if (i == nim1) P.taun[ni - 1] = tau;  // taun(ni) = taun(nim1)
+    if (ig == 3 && i >= 2) P.taun[i - 2] = tau;          // taun(2) = taun(3)
+    if (ig == NI - 1 && i < ni) P.taun[i] = tau;         // taun(ni) = taun(nim1)
   } else {
-    const int j = n, i = P.istep, jstp1 = P.jstep + 1;
+    const int j = n, i = P.istep - P.goff, jstp1 = P.jstep + 1;      // the slab that owns line istep
+    if (i - 1 < P.il_lo || i - 1 > P.il_hi) return;
     if (j < jstp1 || j > njm1) return;
-    const double xp = P.x[i - 1] - P.xu[i - 1];
+    const double xp = P.x[i - 1] - P.xu[i - 1];                         // by-i geometry is the slab's slice
     const double sqrtk = sqrt(0.5 * (F(P.te, i, j) + F(P.te, i, j - 1)));
     const double denv = 0.5 * (F(P.den, i, j) + F(P.den, i, j - 1));
     const double xplusa = 0.5 * (P.xplusw[j - 1] + P.xplusw[j - 2]);
@@ -111,11 +117,11 @@ __global__ void k_teach_wall(const TurbParams P, int which) {
 
 // ---- props: general.f90:165-190 -------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_teach_props(const TurbParams P) {
-  const int M = P.L.M, T = P.L.T, ni = P.L.ni, nj = P.L.nj;
+  const int M = P.L.M, T = P.L.T, nj = P.L.nj;
   const long long LD = P.L.LD;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i0 = 1 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (t >= T || i0 > ni - 2) return;
+  const int i0 = P.il_lo + blockIdx.y * blockDim.y + threadIdx.y;
+  if (t >= T || i0 > P.il_hi) return;
   const long long o = (long long)i0 * LD;
   for (int k = 0; k < M; ++k) {
     const int j0 = t * M + k, q = k * T + t;
@@ -151,13 +157,14 @@ __device__ __forceinline__ double tq_rcp(double x) {
 #define TQ_DIV(a, b) (FAST ? (a) * tq_rcp(b) : (a) / (b))
 template <int EQ, bool FAST>
 __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
-  const int M = P.L.M, T = P.L.T, ni = P.L.ni, nj = P.L.nj, njm1 = nj - 1;
+  const int M = P.L.M, T = P.L.T, nj = P.L.nj, njm1 = nj - 1;
   const long long LD = P.L.LD;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i0 = 1 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int i0 = P.il_lo + blockIdx.y * blockDim.y + threadIdx.y;
   double racc = 0.0;
-  if (t < T && i0 <= ni - 2) {
-    const int i = i0 + 1, jstp1 = P.jstep + 1, istep = P.istep;
+  if (t < T && i0 <= P.il_hi) {
+    // i: local 1-based line (geometry, wall arrays); ig: global (the tests against istep and the inlet plane)
+    const int i = i0 + 1, ig = i + P.goff, jstp1 = P.jstep + 1, istep = P.istep;
     double* phi_w = EQ == CFD_EQ_TE ? P.te : (EQ == CFD_EQ_ED ? P.ed : P.t);
     const long long oline = (long long)i0 * LD;
     const double pr = EQ == CFD_EQ_TE ? P.m.prte : P.m.pred;
@@ -239,6 +246,10 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
           const double gencou = 0.5 * (fabs(P.taun[i] * U.at<1, 0>()) + fabs(P.taun[i - 1] * U.at<0, 0>())) / yp;
           const double yplus = den_c * sqrtk * cdterm * yp / P.viscos;
           P.yplusn[i - 1] = yplus;
+          // i-slabs: the wall law of the next iteration reads yplusn of the halo line beside the slab; its owner
+          // computes it from these same operands, so the neighbour restates it here instead of exchanging it
+          if (P.halo_w && i0 == P.il_lo) P.yplusn[i - 2] = D.at<-1, 0>() * sqrt(PHI.at<-1, 0>()) * cdterm * yp / P.viscos;
+          if (P.halo_e && i0 == P.il_hi) P.yplusn[i] = D.at<1, 0>() * sqrt(PHI.at<1, 0>()) * cdterm * yp / P.viscos;
           const double genres = gen - vis_c * (dudy * dudy);
           gen = genres + gencou;
           double diterm;
@@ -251,8 +262,8 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
           SP = -diterm * vol + spkd;
           AN = 0.0;
         }
-        if (i == istep && j >= jstp1) {
-          const double xp = P.x[istep - 1] - P.xu[istep - 1];
+        if (ig == istep && j >= jstp1) {
+          const double xp = P.x[i - 1] - P.xu[i - 1];
           const double sqrtk = sqrt(phi_c);
           const double xplus = den_c * sqrtk * cdterm * xp / P.viscos;
           P.xplusw[j - 1] = xplus;
@@ -288,8 +299,8 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
           SU = P.great * term * pow(te_c, 1.5);
           SP = -P.great;
         }
-        if (i == istep && j >= jstp1 && j <= nj - 2) {
-          const double xp = P.x[istep - 1] - P.xu[istep - 1];
+        if (ig == istep && j >= jstp1 && j <= nj - 2) {
+          const double xp = P.x[i - 1] - P.xu[i - 1];
           const double term = cmu75 / (P.m.cappa * xp);
           SU = P.great * term * pow(te_c, 1.5);
           SP = -P.great;
@@ -313,7 +324,7 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
           SU = SU + term * P.m.twalln;
           SP = SP - term;
         }
-        if (i == 2 && j >= jstp1) AW = 0.0;
+        if (ig == 2 && j >= jstp1) AW = 0.0;
         if (j == 2) AS = 0.0;
       }
       // ---- chapter 3
@@ -349,6 +360,12 @@ static void fill_turb(const cfd_ctx* c, TurbParams& P) {
   P.L = c->L;
   P.indcos = c->cfg.indcos; P.istep = c->cfg.istep; P.jstep = c->cfg.jstep;
   P.viscos = c->cfg.viscos; P.great = c->cfg.great;
+  P.goff = c->cfg.goff;
+  P.ni_global = c->cfg.ni_global ? c->cfg.ni_global : c->L.ni;
+  P.halo_w = c->cfg.halo_w; P.halo_e = c->cfg.halo_e;
+  // owned lines without the two global boundary lines
+  P.il_lo = c->cfg.halo_w > 0 ? c->cfg.halo_w : (c->cfg.goff == 0 ? 1 : 0);
+  P.il_hi = c->L.ni - 1 - c->cfg.halo_e - ((c->cfg.goff + c->L.ni == P.ni_global) ? 1 : 0);
   P.m = c->turb;
   P.u = c->field[CFD_U]; P.v = c->field[CFD_V]; P.den = c->field[CFD_DEN];
   P.vis = c->field[CFD_VIS]; P.te = c->field[CFD_TE]; P.ed = c->field[CFD_ED]; P.t = c->field[CFD_T];
@@ -379,7 +396,7 @@ int cfd_launch_teach_wall(cfd_ctx* c, int which) {
 int cfd_launch_teach_props(cfd_ctx* c) {
   TurbParams P{};
   fill_turb(c, P);
-  dim3 block(32, 8), grid((c->L.T + 31) / 32, (c->L.ni - 2 + 7) / 8);
+  dim3 block(32, 8), grid((c->L.T + 31) / 32, (P.il_hi - P.il_lo + 1 + 7) / 8);
   k_teach_props<<<grid, block, 0, c->stream>>>(P);
   ++c->launches;
   CFD_CUDA(cudaGetLastError());
@@ -393,7 +410,7 @@ int cfd_launch_teach_scalar(cfd_ctx* c, int eq) {
   P.urf = eq == CFD_EQ_TE ? c->turb.urfk : (eq == CFD_EQ_ED ? c->turb.urfe : c->turb.urft);
   P.rurf = 1.0 / P.urf;
   const bool fast = !c->exact_assembly;     // red/black contexts: reciprocal form of the same formulas
-  dim3 block(32, 8), grid((c->L.T + 31) / 32, (c->L.ni - 2 + 7) / 8);
+  dim3 block(32, 8), grid((c->L.T + 31) / 32, (P.il_hi - P.il_lo + 1 + 7) / 8);
   const int nblocks = grid.x * grid.y;
   if (nblocks > c->max_partials) {
     cfd_set_error("residual partial buffer too small (%d > %d)", nblocks, c->max_partials);

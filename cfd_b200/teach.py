@@ -151,8 +151,6 @@ class TeachFVM(CavityFVM):
         self.resoru = self.resorv = self.resorm = 0.0
         self.turbulent = False
         if turbulent:
-            if ni_local is not None:
-                raise ValueError("turbulent TEACH contexts do not shard yet")
             self._init_turbulence(uin, rlarge, urf_turb, nswp_turb, tin, turbin, alamda, twalln, prandl)
 
     # -- k-epsilon / energy (control.f90:105-179): constants, initial k, eps, T, wall y+, first props ------------
@@ -173,18 +171,24 @@ class TeachFVM(CavityFVM):
         self.turbulent = True
         tein = turbin * (uin * uin)
         edin = tein ** 1.5 / (alamda * rlarge)
+        # local lines of an i-slab: il = 0 .. ni-1 is the global 1-based line il + 1 + goff
+        goff, NI = self.goff, self.ni_global
         te, ed, t = (np.zeros((ni, nj), order="F") for _ in range(3))
-        te[0, 1:js] = tein
-        ed[0, 1:js] = edin
-        t[0, 1:js] = tin
-        for i in range(2, ni + 1):
-            jfin = nj if i >= self.istep + 1 else js + 1
-            te[i - 1, 1:jfin - 1] = tein
-            ed[i - 1, 1:jfin - 1] = edin
-        t[1:ni - 1, nj - 1] = twalln
-        t[0, js - 1:nj] = tin
         yplusn, xplusw = np.zeros(ni), np.zeros(nj)
-        yplusn[1:ni - 1] = 11.0
+        for il in range(ni):
+            i = il + 1 + goff
+            if i == 1:
+                te[il, 1:js] = tein
+                ed[il, 1:js] = edin
+                t[il, 1:js] = tin
+                t[il, js - 1:nj] = tin
+            else:
+                jfin = nj if i >= self.istep + 1 else js + 1
+                te[il, 1:jfin - 1] = tein
+                ed[il, 1:jfin - 1] = edin
+            if 2 <= i <= NI - 1:
+                t[il, nj - 1] = twalln
+                yplusn[il] = 11.0
         xplusw[js - 1:nj] = 11.0
         xplusw[js - 1] = 0.0
         self.upload("te", te)
@@ -192,7 +196,7 @@ class TeachFVM(CavityFVM):
         self.upload("t", t)
         self.wall_upload("yplusn", yplusn)
         self.wall_upload("xplusw", xplusw)
-        self.props()
+        self.props()      # i-slabs: the halo lines of vis, gamh follow by the driver's first exchange (dist.py)
 
     def wall_upload(self, name, a):
         a = np.ascontiguousarray(a, dtype=np.float64)

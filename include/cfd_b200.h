@@ -201,7 +201,8 @@ int cfd_iterate(cfd_ctx* ctx, int n, double res[8]);
 int cfd_assemble_u(cfd_ctx* ctx);                       /* cavity_fvm.f90:104-187 */
 int cfd_assemble_v(cfd_ctx* ctx);                       /* cavity_fvm.f90:205-285 */
 int cfd_assemble_p(cfd_ctx* ctx);                       /* cavity_fvm.f90:301-342 */
-int cfd_assemble_t(cfd_ctx* ctx);                       /* buoyancy_cav.f90:371-428 (general family) */
+int cfd_assemble_t(cfd_ctx* ctx);                       /* buoyancy_cav.f90:371-428 (general family); TEACH after
+                                                           cfd_set_turbulence: calct chapters 1-3, calc.f90:309-385 */
 /* half sweep over the lines of one colour (0/1), or a full sequential sweep if colour < 0;
    first != 0 treats phi as zero where the reference has just executed pp(:,:)=0 (cavity_fvm.f90:342) */
 int cfd_sweep(cfd_ctx* ctx, int istart, int jstart, int field, int colour, int first);
