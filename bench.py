@@ -203,7 +203,7 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------------------------------------
-def parity_check(kind, slabs="i", iters=6):
+def parity_check(kind, slabs="i", iters=6, turbulent=False):
     """N > 1 only, before the timed region: a small problem of the same family runs once slab-decomposed over all
     ranks (the very driver, kernels and exchange the timed run uses) and once in a single context on rank 0; the
     gathered u, v, p are compared.  i-slabs must agree BIT FOR BIT (red/black iterates do not depend on the partition);
@@ -226,8 +226,8 @@ def parity_check(kind, slabs="i", iters=6):
         single = (lambda: cfd_b200.BuoyantCavity(n, n, order="redblack")) if rank == 0 else None
     elif kind == "step":
         shape = (64 * world + 2, 2050)
-        s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab, epsx=1.0)
-        single = (lambda: cfd_b200.TeachFVM(shape[0], shape[1], epsx=1.0, order="redblack")) if rank == 0 else None
+        s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab, epsx=1.0, turbulent=turbulent)
+        single = (lambda: cfd_b200.TeachFVM(shape[0], shape[1], epsx=1.0, order="redblack", turbulent=turbulent)) if rank == 0 else None
     else:
         shape = (64 * world, 2048) if slabs == "i" else (96, 256 * world)
         s = (SlabCavity if slabs == "i" else JSlabCavity)(*shape, reynolds=REYNOLDS)
@@ -238,7 +238,7 @@ def parity_check(kind, slabs="i", iters=6):
             return g
     s.iterate(iters)
     halo_path = "peer memory" if getattr(s, "peer", False) else "NCCL"
-    names = ("u", "v", "p") + (("t",) if kind == "buoyancy" else ())
+    names = ("u", "v", "p") + (("t",) if kind == "buoyancy" else ()) + (("te", "ed", "t", "vis") if turbulent else ())
     got = {n: s.gather_field(n) for n in names}
     s.ctx.close()
     rec = None
@@ -253,7 +253,8 @@ def parity_check(kind, slabs="i", iters=6):
             scale = max(scale, float(np.abs(want).max()))
         g.close()
         tol = 0.0 if slabs == "i" else 1e-10 * max(1.0, scale)
-        rec = {"world": world, "case": f"{kind} {shape[0]}x{shape[1]}, {iters} outer iterations, {slabs}-slabs vs one context",
+        rec = {"world": world, "case": f"{kind}{' (k-epsilon + energy)' if turbulent else ''} {shape[0]}x{shape[1]}, {iters} outer "
+                                       f"iterations, {slabs}-slabs vs one context",
                "halo_path": halo_path, "fields": list(names), "bitwise": bitwise, "max_abs": max_abs, "tolerance": tol,
                "ok": bool(bitwise if slabs == "i" else max_abs <= tol)}
     flag = torch.tensor([1 if (rec is None or rec["ok"]) else 0], device="cuda")
@@ -692,16 +693,17 @@ def run_step(args, kind="step"):
     hbm_peak, peak_src = peaks()
     NI, NJ = (16384, 4096) if kind == "step" else (8194, 8194)
     stream = torch.cuda.Stream()
-    parity = parity_check(kind) if world > 1 else None
+    turb = bool(getattr(args, "turbulent", False)) and kind == "step"
+    parity = parity_check(kind, turbulent=turb) if world > 1 else None
     if world == 1:
         if kind == "step":
-            solver = cfd_b200.TeachFVM(NI, NJ, epsx=1.0, order="redblack", device=local)
+            solver = cfd_b200.TeachFVM(NI, NJ, epsx=1.0, order="redblack", device=local, turbulent=turb)
         else:
             solver = cfd_b200.BuoyantCavity(NI, NJ, order="redblack", device=local)
         solver.set_stream(stream.cuda_stream)
         step, ctx0 = solver.iterate_async, solver
     elif kind == "step":
-        solver = SlabCavity(NI - 2, NJ - 2, stream=stream, slab_cls=TeachSlab, epsx=1.0)
+        solver = SlabCavity(NI - 2, NJ - 2, stream=stream, slab_cls=TeachSlab, epsx=1.0, turbulent=turb)
         step, ctx0 = solver.iterate_async, solver.ctx
     else:
         solver = SlabCavity(NI - 2, NJ - 2, stream=stream, slab_cls=BuoyancySlab)
@@ -737,8 +739,10 @@ def run_step(args, kind="step"):
         ms = float(tms.item())
     cells = (NI - 2) * (NJ - 2)
     glups = cells * K / (ms * 1e-3) / 1e9
-    B = 1056 if kind == "step" else 1224                      # 132 / 153 doubles per cell and outer iteration
-    wl = (f"backward-facing step FVM SIMPLE (TEACH family, laminar, axisymmetric, hybrid scheme, urf .5/.5/1, nswp 3/3/5) "
+    B = (1992 if turb else 1056) if kind == "step" else 1224   # 132 (249 as shipped) / 153 doubles per cell and outer iteration
+    wl = (f"backward-facing step FVM SIMPLE (TEACH family, "
+          f"{'as shipped: k-epsilon + energy + props, control.f90:210-217' if turb else 'laminar'}, axisymmetric, hybrid scheme, "
+          f"urf .5/.5/1, nswp 3/3/5{' + 3/3/3' if turb else ''}) "
           f"on {NI}x{NJ}, red/black line TDMA (BASELINE.json configs[4])") if kind == "step" else (
           f"buoyancy-driven cavity Ra=1e6 (Boussinesq, coupled T equation) SIMPLE on {NI - 2}^2 CV, hybrid scheme, urf "
           ".3/.3/.9/1, nsweep 3/3/3/3, red/black line TDMA (BASELINE.json configs[3])")
@@ -752,7 +756,7 @@ def run_step(args, kind="step"):
                           f"i-slabs x{world}, 1-line halo exchange (NCCL send/recv), all-reduced residuals"),
                       "l2": "inputs larger than L2 (several GB of live fields); no explicit flush",
                       "line_layout": ctx0.layout},
-           "residuals_last": [float(x) for x in res[:3]], "gpu_launches": int(launches),
+           "residuals_last": [float(x) for x in res[:6 if turb else 3]], "gpu_launches": int(launches),
            "roofline": {"bound": "hbm", "kernel": "whole outer iteration", "achieved": B * glups / world, "peak": hbm_peak,
                         "unit": "GB/s", "frac": B * glups / world / hbm_peak, "peak_source": peak_src, "traffic": None,
                         "algorithmic_bytes_per_cell": B},
@@ -795,6 +799,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step", "cavity16k", "buoyancy"])
     ap.add_argument("--slabs", default="i", choices=["i", "j"], help="N>1 cavity: cut along i (whole lines per GPU) or j")
+    ap.add_argument("--turbulent", action="store_true", help="--workload step: the case as shipped (k-epsilon + energy)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()

@@ -211,7 +211,7 @@ class TeachSlab(Slab):
     (promod.f90:79-94) lives entirely on the last rank (it owns the lines ni-2 .. ni), the inlet flow is a host
     constant, so the stage list is the cavity's: no extra exchange."""
 
-    def __init__(self, nicv, njcv, rank, world, *, device=-1, nswp=(3, 3, 5), **kw):
+    def __init__(self, nicv, njcv, rank, world, *, device=-1, nswp=(3, 3, 5), turbulent=False, **kw):
         from .teach import TeachFVM
         self.rank, self.world = rank, world
         ni_g, nj = nicv + 2, njcv + 2
@@ -222,8 +222,16 @@ class TeachSlab(Slab):
         if world > 1 and rank == world - 1 and self.nown < 3:
             raise ValueError("the last TEACH slab must own the lines ni-2 .. ni (outlet mass balance)")
         self.ctx = TeachFVM(ni_g, nj, order="redblack", device=device, nswp=nswp, ni_local=self.ni, goff=self.goff,
-                            halo_w=self.hw, halo_e=self.he, **kw)
+                            halo_w=self.hw, halo_e=self.he, turbulent=turbulent, **kw)
+        # k-epsilon + energy as shipped (control.f90:210-217): the wall arrays taun, yplusn are per line and stay with
+        # the slab (the entry beside the slab is restated by the neighbour, teach_turb_kernels.cu), tauw, xplusw live
+        # with the slab that owns line istep; vis and gamh are fields now and get a halo exchange after props
+        self.turb = self.ctx.model if turbulent else None
         self._finish(nswp)
+
+    def wall_owned(self, name):
+        """Owned part of a per-line wall array (taun, yplusn)."""
+        return self.ctx.wall_download(name)[self.hw:self.hw + self.nown]
 
 
 class BuoyancySlab(Slab):
@@ -247,7 +255,7 @@ class BuoyancySlab(Slab):
 
 # stages of one outer iteration: ("compute", fn(slab)), ("halo", field, w, e, colour filter), ("halos", ...),
 # ("sweep", field, istart, jstart, colour, first) = colour pass + halo exchange of that colour's edge lines, ("ppref",)
-def iteration_stages(nswp, solve_t=False):
+def iteration_stages(nswp, solve_t=False, turb=None):
     st = [("halos", (("u", 1, 1), ("v", 1, 1), ("p", 1, 0))),
           ("compute", lambda s: s.ctx.assemble_u()), ("halo", "du", 0, 1, None)]
     for name, istart, jstart, n, first in (("u", 3, 2, nswp[0], False), ("v", 2, 3, nswp[1], False), ("pp", 2, 2, nswp[2], True)):
@@ -265,6 +273,19 @@ def iteration_stages(nswp, solve_t=False):
         for k in range(nswp[3]):
             for colour in (0, 1):
                 st.append(("sweep", "t", 2, 2, colour, False))
+    if turb is not None:   # control.f90:213-217: calcte, calced, calct, props after calcp (TEACH, k-epsilon + energy)
+        # the scalar equations read the corrected u(i+1), v(i-1), v(i+1); te, ed, t halos follow their own sweeps
+        st.append(("halos", (("u", 0, 1), ("v", 1, 1))))
+        for on, fn, name, n in ((turb.incalk, lambda s: s.ctx.assemble_te(), "te", turb.nswpk),
+                                (turb.incald, lambda s: s.ctx.assemble_ed(), "ed", turb.nswpd),
+                                (turb.incalt, lambda s: s.ctx.assemble_t(), "t", turb.nswpt)):
+            if on:
+                st.append(("compute", fn))
+                for k in range(n):
+                    for colour in (0, 1):
+                        st.append(("sweep", name, 2, 2, colour, False))
+        if turb.inpro:
+            st += [("compute", lambda s: s.ctx.props()), ("halos", (("vis", 1, 1), ("gamh", 1, 1)))]
     return st
 
 
@@ -356,7 +377,7 @@ class SlabCavity(_E2EMixin):
         self.ctx = self.slab.ctx
         if stream is not None:
             self.ctx.set_stream(stream.cuda_stream)
-        self.stages = iteration_stages(self.slab.nswp, getattr(self.slab, "solve_t", False))
+        self.stages = iteration_stages(self.slab.nswp, getattr(self.slab, "solve_t", False), getattr(self.slab, "turb", None))
         self.peer = self._attach_peers()
         self.pstages = peer_stages(self.stages) if self.peer else None
         self.overlap = os.environ.get("CFD_B200_OVERLAP", "0") != "0"   # measured: no gain at N=2
@@ -366,6 +387,8 @@ class SlabCavity(_E2EMixin):
         s = self.slab
         self.comm.exchange(halo_ops(s.lines("den"), s.rank, s.world, s.hw, s.he, s.nown, HALO_W, HALO_E))
         self.comm.exchange(halo_ops(s.lines("vis"), s.rank, s.world, s.hw, s.he, s.nown, 1, 1))
+        if getattr(s, "turb", None) is not None:        # the first props ran on the owned lines only
+            self.comm.exchange(halo_ops(s.lines("gamh"), s.rank, s.world, s.hw, s.he, s.nown, 1, 1))
 
     def _global_cells(self):
         return (self.slab.ni_global - 2) * (self.slab.nj - 2)
@@ -379,6 +402,8 @@ class SlabCavity(_E2EMixin):
         if self.world == 1:
             return False
         names = ("u", "v", "p", "pp", "du") + (("t",) if getattr(s, "solve_t", False) else ())
+        if getattr(s, "turb", None) is not None:
+            names += ("te", "ed", "t", "vis", "gamh")
         mine, ok = None, os.environ.get("CFD_B200_PEER", "1") != "0"
         if ok:
             try:
@@ -521,6 +546,12 @@ class SlabCavity(_E2EMixin):
         self.iterate_async(n)
         return self.residuals()[:3]
 
+    def gather_wall(self, name):
+        """taun / yplusn along the top wall on rank 0 (None elsewhere): owned entries of every slab in line order."""
+        out = [None] * self.world if self.rank == 0 else None
+        self.dist.gather_object(self.slab.wall_owned(name), out, dst=0)
+        return np.concatenate(out) if self.rank == 0 else None
+
     def gather_field(self, name):
         """Global (ni,nj) array on rank 0 (None elsewhere): owned lines of every slab, in order."""
         a = np.ascontiguousarray(self.slab.owned(self.ctx.download(name)))
@@ -535,9 +566,12 @@ class LocalSlabCavity:
         self.world = world
         self.slabs = [(slab_cls or Slab)(nicv, njcv, r, world, **kw) for r in range(world)]
         self.comm = LocalComm(world)
-        self.stages = iteration_stages(self.slabs[0].nswp, getattr(self.slabs[0], "solve_t", False))
+        self.stages = iteration_stages(self.slabs[0].nswp, getattr(self.slabs[0], "solve_t", False),
+                                       getattr(self.slabs[0], "turb", None))
         self.comm.exchange_all(self.slabs, "den", HALO_W, HALO_E)
         self.comm.exchange_all(self.slabs, "vis", 1, 1)
+        if getattr(self.slabs[0], "turb", None) is not None:
+            self.comm.exchange_all(self.slabs, "gamh", 1, 1)
 
     def iterate(self, n=1):
         import torch
@@ -568,6 +602,15 @@ class LocalSlabCavity:
 
     def gather_field(self, name):
         return np.asfortranarray(np.concatenate([s.owned(s.ctx.download(name)) for s in self.slabs], axis=0))
+
+    def residuals(self):
+        """All residual slots (resoru, resorv, resorm, resort, resork, resore, ...), summed over the slabs."""
+        res = sum(s.res.clone() for s in self.slabs)
+        return tuple(res.cpu().tolist())
+
+    def gather_wall(self, name):
+        """taun / yplusn along the top wall: owned entries of every slab in line order."""
+        return np.concatenate([s.wall_owned(name) for s in self.slabs])
 
     def close(self):
         for s in self.slabs:

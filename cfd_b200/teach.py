@@ -216,6 +216,10 @@ class TeachFVM(CavityFVM):
     def assemble_ed(self):
         check(self.lib.cfd_assemble_ed(self._h))
 
+    def assemble_t(self):
+        """calct chapters 1-3 (calc.f90:309-385) + modt, without the sweeps (the slab driver interleaves the exchange)."""
+        check(self.lib.cfd_assemble_t(self._h))
+
     def calcte(self):
         r = C.c_double()
         check(self.lib.cfd_calcte(self._h, C.byref(r)))

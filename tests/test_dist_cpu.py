@@ -257,3 +257,29 @@ def test_iteration_stage_list_orders_exchanges_and_sweeps():
     assert min(i for i, s in enumerate(st) if s[0] == "sweep" and s[1] == "t") > i_ppref + 3
     cav = iteration_stages(nswp[:3])
     assert [s for s in cav if s[0] == "sweep" and s[1] == "t"] == [] and cav[-1][0] == "compute"
+
+
+def test_turbulent_stage_list():
+    """TEACH with k-epsilon + energy (control.f90:210-217): after the correction the corrected velocities beside the
+    slab are exchanged once, then calcte, calced, calct each assemble and sweep (the switched-off ones vanish), then
+    props and the exchange of the two property fields it rewrites; the peer-memory form keeps the same order."""
+    from types import SimpleNamespace
+    from cfd_b200.dist import iteration_stages, peer_stages
+    turb = SimpleNamespace(incalk=1, incald=1, incalt=0, inpro=1, nswpk=3, nswpd=2, nswpt=4)
+    st = iteration_stages((3, 3, 5), turb=turb)
+    kinds = [s[0] for s in st]
+    i_ppref = kinds.index("ppref")
+    tail = st[i_ppref + 2:]
+    assert tail[0][0] == "halos" and {f for f in tail[0][1]} == {("u", 0, 1), ("v", 1, 1)}
+    names = [s[1] for s in tail if s[0] == "sweep"]
+    assert names == ["te"] * 6 + ["ed"] * 4                      # incalt = 0: no temperature passes
+    assert [s[2:4] for s in tail if s[0] == "sweep"][0] == (2, 2)
+    assert tail[-2][0] == "compute" and tail[-1] == ("halos", (("vis", 1, 1), ("gamh", 1, 1)))
+    assert sum(1 for s in tail if s[0] == "compute") == 3         # assemble_te, assemble_ed, props
+    ps = peer_stages(st)
+    assert [s[1] for s in ps if s[0] == "sweeps"] == ["u", "v", "pp", "te", "ed"]
+    assert [s[4] for s in ps if s[0] == "sweeps"] == [3, 3, 5, 3, 2]
+    assert ps[-1] == ("push", (("vis", 1, 1), ("gamh", 1, 1)))
+    turb.incalt, turb.inpro = 1, 0
+    st = iteration_stages((3, 3, 5), turb=turb)
+    assert [s[1] for s in st if s[0] == "sweep"][-8:] == ["t"] * 8 and st[-1][0] == "sweep"

@@ -47,6 +47,33 @@ def test_teach_local_slabs_match_single_context(cfd, world, shape):
     g.close()
 
 
+@pytest.mark.parametrize("world,shape", [(2, (40, 34)), (3, (47, 66)), (4, (64, 130)), (5, (98, 2050))])
+def test_turbulent_teach_local_slabs_match_single_context(cfd, world, shape):
+    """The backward step as shipped (k-epsilon + energy + props, control.f90:210-217) cut into i-slabs: every field,
+    the wall arrays along the top wall and the six residuals agree with the single red/black context -- fields and
+    wall arrays bit for bit (per-cell arithmetic does not depend on the partition; yplusn beside a slab is restated
+    by the neighbour from the owner's operands), residuals up to the order of the sums."""
+    from cfd_b200.dist import LocalSlabCavity, TeachSlab
+    ni, nj = shape
+    g = cfd.TeachFVM(ni, nj, order="redblack", turbulent=True)
+    s = LocalSlabCavity(ni - 2, nj - 2, world, slab_cls=TeachSlab, turbulent=True)
+    for _ in range(3):
+        r1 = g.iterate_turb(2)
+        s.iterate(2)
+        r2 = s.residuals()[:6]
+        for a, b in zip(r1, r2):
+            assert abs(a - b) <= 1e-11 * abs(a), (r1, r2)
+    for name in ("u", "v", "p", "pp", "te", "ed", "t", "vis", "gamh"):
+        assert np.array_equal(s.gather_field(name), g.download(name)), name
+    for name in ("taun", "yplusn"):
+        assert np.array_equal(s.gather_wall(name), g.wall_download(name)), name
+    owner = [x for x in s.slabs if x.lo <= g.istep <= x.hi][0]
+    for name in ("tauw", "xplusw"):
+        assert np.array_equal(owner.ctx.wall_download(name), g.wall_download(name)), name
+    s.close()
+    g.close()
+
+
 @pytest.mark.parametrize("world,shape", [(2, (30, 34)), (3, (40, 66)), (4, (64, 130)), (8, (34, 96))])
 def test_local_jslabs_partitioned_thomas(cfd, world, shape):
     """Lines cut ACROSS contexts (j-slabs): piece solves + spike vectors + reduced system reproduce the single
@@ -99,10 +126,16 @@ def _nccl_worker(rank, world, port, shape, q, kind="i", peer=True):
             s = JSlabCavity(*shape, reynolds=100.0)
         elif kind == "teach":
             s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab)
+        elif kind == "turb":
+            s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab, turbulent=True)
         else:
             s = SlabCavity(*shape, reynolds=100.0)
         res = s.iterate(6)
-        out = {n: s.gather_field(n) for n in ("u", "v", "p")}
+        if kind == "turb":
+            res = s.residuals()[:6]
+        out = {n: s.gather_field(n) for n in (("u", "v", "p", "te", "ed", "t", "vis") if kind == "turb" else ("u", "v", "p"))}
+        if kind == "turb":
+            out["taun"] = s.gather_wall("taun")
         used_peer = bool(getattr(s, "peer", False))
         timed_out = s.ctx.peer_status()
         if rank == 0:
@@ -113,7 +146,8 @@ def _nccl_worker(rank, world, port, shape, q, kind="i", peer=True):
 
 @pytest.mark.parametrize("kind,peer,shape", [("i", False, (96, 130)), ("j", False, (96, 130)), ("teach", False, (96, 130)),
                                              ("buoyancy", False, (98, 98)), ("i", True, (96, 2048)),
-                                             ("teach", True, (98, 2050)), ("buoyancy", True, (2050, 2050))])
+                                             ("teach", True, (98, 2050)), ("buoyancy", True, (2050, 2050)),
+                                             ("turb", False, (96, 130)), ("turb", True, (98, 2050))])
 def test_nccl_slabs_match_single_context(cfd, kind, peer, shape):
     """One process per GPU.  peer=True: halo lines over peer memory (stores from inside the flag-ordered sweep kernels
     and cfd_halo_push) -- lines of 2050 nodes (160 layout threads x 13 nodes), long enough for the TMA-staged kernels that path
@@ -128,11 +162,18 @@ def test_nccl_slabs_match_single_context(cfd, kind, peer, shape):
         g = cfd.BuoyantCavity(*shape, order="redblack")
     elif kind == "teach":
         g = cfd.TeachFVM(*shape, order="redblack")
+    elif kind == "turb":
+        g = cfd.TeachFVM(*shape, order="redblack", turbulent=True)
     else:
         g = cfd.CavityFVM(*shape, order="redblack")
         g.init_lid_driven(reynolds=100.0)
-    want_res = g.iterate(6)
-    want = {n: g.download(n) for n in ("u", "v", "p")}
+    if kind == "turb":
+        want_res = g.iterate_turb(6)
+        want = {n: g.download(n) for n in ("u", "v", "p", "te", "ed", "t", "vis")}
+        want["taun"] = g.wall_download("taun")
+    else:
+        want_res = g.iterate(6)
+        want = {n: g.download(n) for n in ("u", "v", "p")}
     g.close()
     sk = socket.socket()
     sk.bind(("127.0.0.1", 0))
