@@ -21,6 +21,7 @@ struct cfd_fdcav {
   int* sip_info;
   double* sip_rsm;
 };
+size_t cfd_sip_sync_bytes(int ld, int nrows);
 int cfd_launch_sip(int device, cudaStream_t stream, int ld, int nrows, int imax, int jmax, const double* c,
                    const double* const* coef, double alpha, double tol, int maxit, const double* su, double* phi, double* work,
                    unsigned long long* prog, double* partial, int* info, double* rsm_out, int max_partials);
@@ -340,7 +341,7 @@ static int sip_alloc(cfd_fdcav* h) {
   const size_t n = (size_t)(h->cfg.ni + 1) * (h->cfg.nj + 1);
   if (!h->sip_work) {
     CFD_CUDA(cudaMalloc(&h->sip_work, 6 * n * sizeof(double)));
-    CFD_CUDA(cudaMalloc(&h->sip_prog, (size_t)((h->cfg.nj + 31) / 32 + 2) * sizeof(unsigned long long)));
+    CFD_CUDA(cudaMalloc(&h->sip_prog, cfd_sip_sync_bytes(h->cfg.ni + 1, h->cfg.nj + 1)));
     CFD_CUDA(cudaMalloc(&h->sip_partial, 1024 * sizeof(double)));
     CFD_CUDA(cudaMalloc(&h->sip_info, 2 * sizeof(int)));
     CFD_CUDA(cudaMalloc(&h->sip_rsm, sizeof(double)));
