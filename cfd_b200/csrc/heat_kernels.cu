@@ -100,6 +100,8 @@ __global__ void __launch_bounds__(128) k_ftcs(const HeatParams P) {
 // ---------------------------------------------------------------------------------------------------
 struct LodParams {
   int nx, ny;
+  int wall_s, wall_n;        // the local row 0 / ny-1 is a physical (Dirichlet) boundary row; 0 in a row slab whose first /
+                             // last rows are halo rows (there the recurrences just start, see k_lod_y_chunk)
   double fox, foy, dt, rho, cp, xa, dx, qthr, qval, qdt;
   double tleft, tright, tbottom, ttop;
   const double *ex, *tx, *ey, *ty;
@@ -110,13 +112,13 @@ struct LodParams {
 __global__ void k_lod_bc(const LodParams P) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   const size_t nx = (size_t)P.nx;
-  if (n >= 1 && n <= P.ny - 2) {
+  if (n >= (P.wall_s ? 1 : 0) && n <= P.ny - (P.wall_n ? 2 : 1)) {
     P.t[(size_t)n * nx] = P.tleft;
     P.t[(size_t)n * nx + nx - 1] = P.tright;
   }
   if (n < P.nx) {
-    P.t[n] = P.tbottom;
-    P.t[(size_t)(P.ny - 1) * nx + n] = P.ttop;
+    if (P.wall_s) P.t[n] = P.tbottom;
+    if (P.wall_n) P.t[(size_t)(P.ny - 1) * nx + n] = P.ttop;
   }
 }
 
@@ -310,7 +312,7 @@ __global__ void __launch_bounds__(128, 8) k_lod_y_chunk(const LodParams P, const
       for (int r = 0; r < U; ++r) {
         const int j = j0 + r;
         if (j < r1) {
-          const double f = (ident || j == 0 || j == ny - 1) ? v[r] : fma(P.foy, fprev, v[r]) * __ldg(P.ty + j);
+          const double f = (ident || (j == 0 && P.wall_s) || (j == ny - 1 && P.wall_n)) ? v[r] : fma(P.foy, fprev, v[r]) * __ldg(P.ty + j);
           if (j >= r0) d[(size_t)j * nx] = f;
           fprev = f;
         }
@@ -327,7 +329,7 @@ __global__ void __launch_bounds__(128, 8) k_lod_y_chunk(const LodParams P, const
       for (int r = 0; r < U; ++r) {
         const int j = j0 - r;
         if (j >= r0) {
-          const double x = (ident || j == ny - 1) ? v[r] : fma(-__ldg(P.ey + j), xnext, v[r]);
+          const double x = (ident || (j == ny - 1 && P.wall_n)) ? v[r] : fma(-__ldg(P.ey + j), xnext, v[r]);
           if (j < r1) d[(size_t)j * nx] = x;
           xnext = x;
         }
@@ -349,7 +351,7 @@ __global__ void __launch_bounds__(128) k_lod_x_chunk(const LodParams P, const Lo
   if (c_lo >= nx) return;
   const int myrow = row0 + lane;
   const bool rowin = myrow < P.ny;
-  const bool solve = rowin && myrow >= 1 && myrow <= P.ny - 2;      // interior row: recurrence; boundary row: copy
+  const bool solve = rowin && myrow >= (P.wall_s ? 1 : 0) && myrow <= P.ny - (P.wall_n ? 2 : 1);   // boundary row: copy
   double (*tl)[33] = tile[w];
   double nxt[32];
   auto fetch = [&](int c0) {
@@ -583,16 +585,23 @@ static void thomas_constants(int n, double fo, std::vector<double>& e, std::vect
 static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   CFD_REQUIRE(h && nsteps >= 0, "bad argument");
   const cfd_heat_config& g = h->cfg;
-  if (g.ny_global && g.ny_global != g.ny) {
-    cfd_set_error("cfd_heat2d_implicit_step: the y-lines would cross slabs; implicit steps run on whole grids only");
+  // Row slab of a larger grid: the y-lines cross the slabs.  Both Thomas recurrences forget their start at the rate m per
+  // node (see k_lod_y_chunk), so a slab whose halo is `warm` rows deep on each inner side solves its owned rows to the
+  // last bit from halo rows the caller refreshed before the step (cfd_heat_implicit_halo says how deep); the exact mode
+  // needs whole lines.
+  const bool slab = g.ny_global && g.ny_global != g.ny;
+  if (slab && exact) {
+    cfd_set_error("cfd_heat2d_implicit_step_exact: the y-lines would cross slabs; the exact mode runs on whole grids only");
     return CFD_ERR_UNSUPPORTED;
   }
   CFD_CUDA(cudaSetDevice(h->device));
-  const int nx = g.nx, ny = g.ny;
-  const double dx = (g.xb - g.xa) / (double)(nx - 1), dy = (g.yb - g.ya) / (double)(ny - 1);
+  const int nx = g.nx, ny = g.ny, nyg = slab ? g.ny_global : g.ny;
+  const double dx = (g.xb - g.xa) / (double)(nx - 1), dy = (g.yb - g.ya) / (double)(nyg - 1);
   LodParams P{};
   P.nx = nx;
   P.ny = ny;
+  P.wall_s = !slab || g.j_goff == 0;
+  P.wall_n = !slab || g.j_goff + ny == nyg;
   P.fox = g.k * g.dt / g.rho / g.cp / (dx * dx);
   P.foy = g.k * g.dt / g.rho / g.cp / (dy * dy);
   P.dt = g.dt; P.rho = g.rho; P.cp = g.cp; P.xa = g.xa; P.dx = dx; P.qthr = g.qthr; P.qval = g.qval;
@@ -600,7 +609,7 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   if (!h->thomas) {
     std::vector<double> ex, tx, ey, ty, all;
     thomas_constants(nx, P.fox, ex, tx);
-    thomas_constants(ny, P.foy, ey, ty);
+    thomas_constants(nyg, P.foy, ey, ty);      // by GLOBAL row: the pivots depend on the distance from the wall
     all.insert(all.end(), ex.begin(), ex.end());
     all.insert(all.end(), tx.begin(), tx.end());
     all.insert(all.end(), ey.begin(), ey.end());
@@ -613,11 +622,14 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   P.ex = h->thomas;
   P.tx = h->thomas + nx;
   P.ey = h->thomas + 2 * (size_t)nx;
-  P.ty = h->thomas + 2 * (size_t)nx + ny;
+  P.ty = h->thomas + 2 * (size_t)nx + nyg;
   if (!exact) {
-    P.tx = h->thomas + 2 * (size_t)nx + 2 * (size_t)ny;
+    P.tx = h->thomas + 2 * (size_t)nx + 2 * (size_t)nyg;
     P.ty = P.tx + nx;
   }
+  const int joff = slab ? g.j_goff : 0;        // the kernels index the by-row constants with the local row
+  P.ey += joff;
+  P.ty += joff;
   P.qdt = g.dt * g.qval / g.rho / g.cp;
   P.t = h->buf[h->cur];
   const int nmax = nx > ny ? nx : ny;
@@ -641,7 +653,15 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
   };
   LodChunk cx{}, cy{};
   const int ncx = plan(nx, ny, num_sms * 4, P.fox, cx), ncy = plan(ny, nx, num_sms * 8, P.foy, cy);
-  const bool chunked = !exact && (ncx > 1 || ncy > 1);
+  const bool chunked = !exact && (ncx > 1 || ncy > 1 || slab);      // the chunk kernels are the ones that can start mid-line
+  if (slab) {
+    const int hs = g.j_goff == 0 ? 0 : cy.warm, hn = (g.j_goff + ny == nyg) ? 0 : cy.warm;
+    if (g.halo_s < hs || g.halo_n < hn) {
+      cfd_set_error("cfd_heat2d_implicit_step: a row slab needs %d halo rows towards each neighbour at this Fourier number "
+                    "(has %d / %d): see cfd_heat_implicit_halo", cy.warm, g.halo_s, g.halo_n);
+      return CFD_ERR_INVALID;
+    }
+  }
   for (int n = 0; n < nsteps; ++n) {
     k_lod_bc<<<(nmax + 127) / 128, 128, 0, h->stream>>>(P);
     if (exact) {
@@ -671,6 +691,15 @@ static int lod_steps(cfd_heat* h, int nsteps, bool exact) {
 }
 
 extern "C" int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps) { return lod_steps(h, nsteps, false); }
+// halo depth (rows towards each neighbour) a row slab needs for implicit steps at Fourier number fo_y = k dt / (rho cp dy^2):
+// the warm-up length of the chunked sweeps, m^W < 2^-70
+extern "C" int cfd_heat_implicit_halo(double fo_y, int* rows) {
+  CFD_REQUIRE(rows && fo_y > 0, "bad argument");
+  const double m = ((1.0 + 2.0 * fo_y) - sqrt(1.0 + 4.0 * fo_y)) / (2.0 * fo_y);
+  int warm = (m > 0 && m < 1) ? (int)ceil(70.0 * log(2.0) / -log(m)) : 1;
+  *rows = ((warm + 31) / 32) * 32;
+  return CFD_OK;
+}
 extern "C" int cfd_heat2d_implicit_step_exact(cfd_heat* h, int nsteps) { return lod_steps(h, nsteps, true); }
 
 

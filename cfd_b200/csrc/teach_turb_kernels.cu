@@ -12,6 +12,7 @@
 // value).  Compiled with -fmad=false and the reference's operation order; log / pow / sqrt come from the CUDA math
 // library, so agreement with oracle/teach_turb.inc is to rounding, not bitwise.  Works for both coefficient
 // storages (nc = 6 raw, nc = 5 divided by ap).
+#include <cmath>
 #include "common.cuh"
 
 namespace cfd {
@@ -23,6 +24,7 @@ struct TurbParams {
   int il_lo, il_hi;          // owned interior lines (local, 0-based, inclusive)
   int halo_w, halo_e;
   double viscos, great, urf, rurf;
+  double cdterm, cmu75;      // cmu^0.25, cmu^0.75 (the reference evaluates them per cell; constants of the model)
   cfd_turbulence m;
   const double *u, *v, *den;
   double *vis, *te, *ed, *t, *gen, *gamh;
@@ -71,7 +73,7 @@ __global__ void k_teach_wall(const TurbParams P, int which) {
   const long long LD = P.L.LD;
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   auto F = [&](const double* f, int i, int j) { return f[(long long)(i - 1) * LD + lpos(j - 1, M, T)]; };
-  const double cdterm = pow(P.m.cmu, 0.25);
+  const double cdterm = P.cdterm;
   if (which == 0) {
     // local 1-based line i; taun(i) needs the lines i-1, i, so it exists for every owned line and for the east halo
     // line next to the slab (calcte reads taun(i+1)); global tests through ig
@@ -169,7 +171,7 @@ __global__ void __launch_bounds__(256) k_teach_scalar(const TurbParams P) {
     const long long oline = (long long)i0 * LD;
     const double pr = EQ == CFD_EQ_TE ? P.m.prte : P.m.pred;
     const double rpr = 1.0 / pr;
-    const double cdterm = pow(P.m.cmu, 0.25), cmu75 = pow(P.m.cmu, .75);
+    const double cdterm = P.cdterm, cmu75 = P.cmu75;
     for (int k = 0; k < M; ++k) {
       const int j0 = t * M + k, j = j0 + 1;
       if (j0 < 1 || j0 > nj - 2) continue;
@@ -367,6 +369,8 @@ static void fill_turb(const cfd_ctx* c, TurbParams& P) {
   P.il_lo = c->cfg.halo_w > 0 ? c->cfg.halo_w : (c->cfg.goff == 0 ? 1 : 0);
   P.il_hi = c->L.ni - 1 - c->cfg.halo_e - ((c->cfg.goff + c->L.ni == P.ni_global) ? 1 : 0);
   P.m = c->turb;
+  P.cdterm = std::pow(c->turb.cmu, 0.25);
+  P.cmu75 = std::pow(c->turb.cmu, .75);
   P.u = c->field[CFD_U]; P.v = c->field[CFD_V]; P.den = c->field[CFD_DEN];
   P.vis = c->field[CFD_VIS]; P.te = c->field[CFD_TE]; P.ed = c->field[CFD_ED]; P.t = c->field[CFD_T];
   P.gen = c->field[CFD_GEN]; P.gamh = c->field[CFD_GAMH];

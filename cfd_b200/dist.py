@@ -621,19 +621,39 @@ class LocalSlabCavity:
 # 2-D FTCS heat conduction: j-slabs (rows are contiguous in the column-major layout), one halo row per side
 # and step.  The update loop is fdm1d_explicit_heat_cond.f90:130-139 in 2-D.
 # ----------------------------------------------------------------------------------------------------------
-def heat_slab_extent(ny_global: int, world: int, rank: int):
-    """(j_goff, ny_local, halo_s, halo_n): owned rows plus one halo row towards each neighbour."""
+def heat_slab_extent(ny_global: int, world: int, rank: int, halo: int = 1):
+    """(j_goff, ny_local, halo_s, halo_n): owned rows plus `halo` rows towards each neighbour (1 for the explicit scheme;
+    the implicit one needs cfd_heat_implicit_halo rows)."""
     lo, hi = partition(ny_global, world)[rank]
-    hs = 1 if rank > 0 else 0
-    hn = 1 if rank < world - 1 else 0
+    if world > 1 and hi - lo + 1 < halo:
+        raise ValueError(f"slab of rank {rank} owns {hi - lo + 1} rows; the halo is {halo} rows deep")
+    hs = halo if rank > 0 else 0
+    hn = halo if rank < world - 1 else 0
     return lo - 1 - hs, (hi - lo + 1) + hs + hn, hs, hn
 
 
+def implicit_halo_rows(nx, ny_global, **kw):
+    """Halo depth of a row slab for implicit (LOD) steps of this problem: cfd_heat_implicit_halo at its Fo_y."""
+    import ctypes as C
+    from . import _lib
+    dx = (kw.get("xb", 1.0) - kw.get("xa", 0.0)) / (nx - 1)
+    dy = (kw.get("yb", 1.0) - kw.get("ya", 0.0)) / (ny_global - 1)
+    k, rho, cp = kw.get("k", 5.0), kw.get("rho", 1.0), kw.get("cp", 1.0)
+    dt = kw.get("dt")
+    if dt is None:
+        dt = kw.get("fo", 0.2) * dx * dx / (k / rho / cp)
+    rows = C.c_int()
+    rc = _lib.load().cfd_heat_implicit_halo(k * dt / rho / cp / (dy * dy), C.byref(rows))
+    if rc:
+        raise RuntimeError("cfd_heat_implicit_halo failed")
+    return rows.value
+
+
 class HeatSlab:
-    def __init__(self, nx, ny_global, rank, world, device=-1, t0=None, **kw):
+    def __init__(self, nx, ny_global, rank, world, device=-1, t0=None, halo=1, **kw):
         from .heat import Heat2D
         self.rank, self.world, self.nx, self.ny_global = rank, world, nx, ny_global
-        self.j_goff, self.ny, self.hs, self.hn = heat_slab_extent(ny_global, world, rank)
+        self.j_goff, self.ny, self.hs, self.hn = heat_slab_extent(ny_global, world, rank, halo)
         self.nown = self.ny - self.hs - self.hn
         dx = (kw.get("xb", 1.0) - kw.get("xa", 0.0)) / (nx - 1)
         k, rho, cp = kw.get("k", 5.0), kw.get("rho", 1.0), kw.get("cp", 1.0)
@@ -650,12 +670,15 @@ class HeatSlab:
         return device_tensor(base, (n, stride))
 
     def halo_ops(self):
+        """Every halo row from the neighbour's owned rows (one row for the explicit scheme, the whole warm-up depth for
+        the implicit one)."""
         r, ops = self.rows(), []
         first, last = self.hs, self.hs + self.nown - 1
         if self.rank > 0:
-            ops += [("recv", r[first - 1:first], self.rank - 1), ("send", r[first:first + 1], self.rank - 1)]
+            ops += [("recv", r[first - self.hs:first], self.rank - 1), ("send", r[first:first + self.hs], self.rank - 1)]
         if self.rank < self.world - 1:
-            ops += [("recv", r[last + 1:last + 2], self.rank + 1), ("send", r[last:last + 1], self.rank + 1)]
+            ops += [("recv", r[last + 1:last + 1 + self.hn], self.rank + 1),
+                    ("send", r[last + 1 - self.hn:last + 1], self.rank + 1)]
         return ops
 
     def owned(self, a):
@@ -678,12 +701,33 @@ class SlabHeat:
             self.slab.h.step(1)
             self.comm.exchange(self.slab.halo_ops())
 
+    def implicit_step(self, n=1):
+        """Implicit (LOD) steps; the slabs must have been built with halo=implicit_halo_rows(...).  Per step: the x- and
+        y-sweeps on the local rows, then the refresh of the halo rows (whose results the sweeps leave inexact)."""
+        for _ in range(n):
+            self.slab.h.implicit_step(1)
+            self.comm.exchange(self.slab.halo_ops())
+
 
 class LocalSlabHeat:
     """All slabs in one process on one GPU (tests)."""
 
     def __init__(self, nx, ny_global, world, t0, **kw):
         self.slabs = [HeatSlab(nx, ny_global, r, world, t0=t0, **dict(kw)) for r in range(world)]
+
+    def implicit_step(self, n=1):
+        for _ in range(n):
+            for s in self.slabs:
+                s.h.implicit_step(1)
+            self._exchange()
+
+    def _exchange(self):
+        rows = [s.rows() for s in self.slabs]
+        for r in range(len(self.slabs) - 1):
+            a, b = self.slabs[r], self.slabs[r + 1]
+            a_last = a.hs + a.nown - 1
+            rows[r + 1][b.hs - b.hs:b.hs].copy_(rows[r][a_last + 1 - b.hs:a_last + 1])
+            rows[r][a_last + 1:a_last + 1 + a.hn].copy_(rows[r + 1][b.hs:b.hs + a.hn])
 
     def step(self, n=1):
         for _ in range(n):

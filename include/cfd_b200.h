@@ -356,6 +356,11 @@ int cfd_heat2d_step_exact(cfd_heat* h, int nsteps);
 int cfd_heat2d_implicit_step(cfd_heat* h, int nsteps);
 /* same, with IEEE divisions in the reference's operation order (bit-comparable with the oracle; slower) */
 int cfd_heat2d_implicit_step_exact(cfd_heat* h, int nsteps);
+/* Row slabs (cfd_heat_config.j_goff / ny_global) and implicit steps: the y-lines cross the slabs, but both recurrences of
+   `thomas` forget their start at a fixed rate per node, so a slab with `rows` halo rows towards each neighbour -- refreshed
+   from the neighbours' owned rows before every step -- reproduces the whole-grid result to the last bit or two.  `rows`
+   depends on Fo_y = k dt / (rho cp dy^2) only (e.g. 128 at Fo = 5); cfd_heat2d_implicit_step refuses slabs with less. */
+int cfd_heat_implicit_halo(double fo_y, int* rows);
 /* ---- variable conductivity: the 5-point operator of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90:162-190 ----
    lamw, lame, lams, lamn = LAMBDA at the four face mid-points of every node, (x-dx/2,y), (x+dx/2,y), (x,y-dy/2),
    (x,y+dy/2) (:171-174), as (ld,ny) host arrays; qdot = QDOT at the nodes (:188; NULL = none).  The device keeps

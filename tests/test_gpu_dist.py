@@ -213,3 +213,94 @@ def test_heat_row_slabs_match_single_grid(cfd, world):
     assert np.array_equal(s.gather(), h.download())
     s.close()
     h.close()
+
+
+@pytest.mark.parametrize("world,fo", [(2, 5.0), (3, 1.0), (4, 0.4)])
+def test_implicit_heat_row_slabs_match_single_grid(cfd, world, fo):
+    """Implicit (LOD) steps on row slabs: the y-lines cross the slabs, each slab carries cfd_heat_implicit_halo rows of
+    halo (the distance over which the Thomas recurrences forget their start: m^W < 2^-70) refreshed before every step.
+    Equal to the whole-grid production step to rounding (north_star: 1e-12 relative per step), and to the exact
+    (one thread per line, reference operation order) mode likewise."""
+    from cfd_b200.dist import LocalSlabHeat, implicit_halo_rows
+    nx, ny = 1024, 1024
+    kw = dict(fo=fo, tleft=1.0, ttop=2.0, tbottom=0.5)
+    t0 = np.asfortranarray(np.random.default_rng(5).random((nx, ny)))
+    halo = implicit_halo_rows(nx, ny, **kw)
+    assert 32 <= halo <= ny // world
+    h = cfd.Heat2D(nx, ny, **kw)
+    h.upload(t0)
+    hx = cfd.Heat2D(nx, ny, **kw)
+    hx.upload(t0)
+    s = LocalSlabHeat(nx, ny, world, t0, halo=halo, **kw)
+    for _ in range(3):
+        h.implicit_step(2)
+        hx.implicit_step(2, exact=True)
+        s.implicit_step(2)
+        want, got = h.download(), s.gather()
+        scale = np.abs(want).max()
+        assert np.abs(got - want).max() <= 1e-12 * scale
+        assert np.abs(got - hx.download()).max() <= 1e-12 * scale
+    s.close()
+    h.close()
+    hx.close()
+
+
+def test_implicit_heat_slab_refuses_a_shallow_halo(cfd):
+    from cfd_b200.dist import HeatSlab
+    s = HeatSlab(512, 512, 1, 2, halo=1, fo=5.0)
+    with pytest.raises(Exception):
+        s.h.implicit_step(1)
+    s.h.close()
+
+
+def _heat_lod_worker(rank, world, port, q):
+    import os
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from cfd_b200.dist import SlabHeat, implicit_halo_rows
+        nx = ny = 1024
+        kw = dict(fo=2.0, tleft=1.0, ttop=2.0)
+        t0 = np.asfortranarray(np.random.default_rng(9).random((nx, ny)))
+        s = SlabHeat(nx, ny, t0=t0, halo=implicit_halo_rows(nx, ny, **kw), **kw)
+        s.implicit_step(4)
+        torch.cuda.synchronize()
+        part = np.ascontiguousarray(s.slab.owned(s.slab.h.download()))
+        out = [None] * world if rank == 0 else None
+        dist.gather_object(part, out, dst=0)
+        if rank == 0:
+            q.put(np.asfortranarray(np.concatenate(out, axis=1)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_implicit_heat_row_slabs_over_nccl(cfd):
+    """One process per GPU: implicit (LOD) steps on row slabs with the deep halo exchanged over NCCL."""
+    import torch
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs (run under gpurun --gpus 2)")
+    nx = ny = 1024
+    h = cfd.Heat2D(nx, ny, fo=2.0, tleft=1.0, ttop=2.0)
+    h.upload(np.asfortranarray(np.random.default_rng(9).random((nx, ny))))
+    h.implicit_step(4)
+    want = h.download()
+    h.close()
+    sk = socket.socket()
+    sk.bind(("127.0.0.1", 0))
+    port = sk.getsockname()[1]
+    sk.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_heat_lod_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
