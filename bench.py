@@ -484,10 +484,16 @@ def run_heat(args):
     stream = torch.cuda.Stream()
     if world > 1:
         # weak scaling: 16384 x 16384 rows per GPU, row slabs with one halo row per side and step (NCCL send/recv)
-        from cfd_b200.dist import SlabHeat
+        from cfd_b200.dist import SlabHeat, implicit_halo_rows
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        sh = SlabHeat(n, n * world, stream=stream)
-        step = sh.step
+        implicit = bool(getattr(args, "implicit", False))
+        if implicit:      # Fo = 5 (25x the explicit limit): 128 halo rows per inner side, refreshed every step
+            halo = implicit_halo_rows(n, n * world, fo=5.0, yb=float(world))
+            sh = SlabHeat(n, n * world, stream=stream, halo=halo, fo=5.0, yb=float(world))
+            step = sh.implicit_step
+        else:
+            sh = SlabHeat(n, n * world, stream=stream)
+            step = sh.step
         with torch.cuda.stream(stream):
             step(W)
             torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
@@ -505,16 +511,22 @@ def run_heat(args):
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         ms = float(tms.item())
         glups = n * n * world * K / (ms * 1e-3) / 1e9
-        out = {"metric": "ftcs_cell_updates_per_s", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": K, "warmup": W,
+        bpc = 64 if implicit else HEAT_BYTES_PER_CELL        # LOD: four passes x (read + write)
+        out = {"metric": "lod_cell_updates_per_s" if implicit else "ftcs_cell_updates_per_s", "value": glups, "unit": "GLUPS",
+               "n_gpus": world, "steps": K, "warmup": W,
                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                "data": "synthetic", "steps_per_s": K / (ms * 1e-3),
-               "config": {"workload": f"2-D FTCS heat conduction, {n}x{n} nodes per GPU, FP64, Fo=0.2 (BASELINE.json configs[1])",
+               "config": {"workload": (f"2-D implicit (LOD) heat conduction, {n}x{n} nodes per GPU, FP64, Fo=5" if implicit else
+                                       f"2-D FTCS heat conduction, {n}x{n} nodes per GPU, FP64, Fo=0.2 (BASELINE.json configs[1])"),
                           "global_grid": f"{n}x{n * world}",
-                          "parallelism": f"row slabs x{world}, one halo row per side and step (NCCL send/recv)",
+                          "parallelism": (f"row slabs x{world}, {sh.slab.hs or sh.slab.hn} halo rows per inner side refreshed every step "
+                                          "(NCCL send/recv)" if implicit else
+                                          f"row slabs x{world}, one halo row per side and step (NCCL send/recv)"),
                           "l2": "field (2.1 GB per GPU) larger than L2; ping-pong buffers"},
-               "gpu_launches": K,
-               "roofline": {"bound": "hbm", "kernel": "k_ftcs<false>", "achieved": HEAT_BYTES_PER_CELL * glups / world,
-                            "peak": hbm_peak, "unit": "GB/s", "frac": HEAT_BYTES_PER_CELL * glups / world / hbm_peak,
+               "gpu_launches": K * (5 if implicit else 1),
+               "roofline": {"bound": "hbm", "kernel": "k_lod_x/y_chunk (four sweeps)" if implicit else "k_ftcs<false>",
+                            "achieved": bpc * glups / world,
+                            "peak": hbm_peak, "unit": "GB/s", "frac": bpc * glups / world / hbm_peak,
                             "peak_source": peak_src, "traffic": None},
                "e2e": None, "clocks": clocks}
         if rank == 0:
@@ -882,6 +894,7 @@ def main():
     ap.add_argument("--workload", default="cavity", choices=["cavity", "heat", "step", "cavity16k", "buoyancy", "fdcavity"])
     ap.add_argument("--slabs", default="i", choices=["i", "j"], help="N>1 cavity: cut along i (whole lines per GPU) or j")
     ap.add_argument("--turbulent", action="store_true", help="--workload step: the case as shipped (k-epsilon + energy)")
+    ap.add_argument("--implicit", action="store_true", help="--workload heat at N > 1: implicit (LOD) steps on row slabs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()

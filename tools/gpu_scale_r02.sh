@@ -25,4 +25,6 @@ run c16k_n8 8 --workload cavity16k --steps 30 --warmup 5 --no-cpu-baseline
 run step_n8 8 --workload step --steps 30 --warmup 5
 run stepturb_n8 8 --workload step --turbulent --steps 30 --warmup 5
 run buoy_n8 8 --workload buoyancy --steps 30 --warmup 5
+run heatlod_n8 8 --workload heat --implicit --steps 20 --warmup 3
+run heat_n8 8 --workload heat --steps 100 --warmup 5
 ls -la gpurun_out/r02s_* | head -20
