@@ -283,3 +283,37 @@ def test_turbulent_stage_list():
     turb.incalt, turb.inpro = 1, 0
     st = iteration_stages((3, 3, 5), turb=turb)
     assert [s[1] for s in st if s[0] == "sweep"][-8:] == ["t"] * 8 and st[-1][0] == "sweep"
+
+
+def _heat_halo_worker(rank, world, port, ny, nx, halo):
+    """HeatSlab.halo_ops with a deep halo (implicit steps) over gloo: host tensors stand in for the device rows."""
+    from cfd_b200.dist import HeatSlab, heat_slab_extent
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        comm = TorchDistComm()
+        glob = torch.from_numpy(np.random.default_rng(11).random((ny, nx)))
+        s = HeatSlab.__new__(HeatSlab)                              # bookkeeping only: no GPU context
+        s.rank, s.world = rank, world
+        s.j_goff, s.ny, s.hs, s.hn = heat_slab_extent(ny, world, rank, halo)
+        s.nown = s.ny - s.hs - s.hn
+        loc = torch.full((s.ny, nx), -1.0, dtype=torch.float64)
+        loc[s.hs:s.hs + s.nown] = glob[s.j_goff + s.hs:s.j_goff + s.hs + s.nown]
+        s.rows = lambda: loc
+        comm.exchange(s.halo_ops())
+        assert torch.equal(loc, glob[s.j_goff:s.j_goff + s.ny]), rank     # every halo row filled from its owner
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,halo", [(2, 1), (2, 32), (3, 17)])
+def test_heat_deep_halo_exchange_gloo(world, halo):
+    mp.spawn(_heat_halo_worker, args=(world, _free_port(), 160, 12, halo), nprocs=world, join=True)
+
+
+def test_heat_slab_extent_deep_halo():
+    from cfd_b200.dist import heat_slab_extent
+    assert heat_slab_extent(400, 2, 0, 128) == (0, 328, 0, 128)
+    assert heat_slab_extent(400, 2, 1, 128) == (72, 328, 128, 0)
+    with pytest.raises(ValueError):
+        heat_slab_extent(100, 4, 1, 64)                             # a slab must own at least the halo depth
