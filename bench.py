@@ -203,7 +203,7 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------------------------------------
-def parity_check(kind, slabs="i", iters=6, turbulent=False):
+def parity_check(kind, slabs="i", iters=6, turbulent=False, cluster=False):
     """N > 1 only, before the timed region: a small problem of the same family runs once slab-decomposed over all
     ranks (the very driver, kernels and exchange the timed run uses) and once in a single context on rank 0; the
     gathered u, v, p are compared.  i-slabs must agree BIT FOR BIT (red/black iterates do not depend on the partition);
@@ -219,6 +219,11 @@ def parity_check(kind, slabs="i", iters=6, turbulent=False):
     world, rank = dist.get_world_size(), dist.get_rank()
     # lines of 2050 nodes: a layout (160 threads x 13 nodes) the flag-ordered sweep kernel takes, so that the check runs
     # over the same halo path (peer memory or NCCL) as the timed run
+    # cluster=True: the timed run solves its lines with clusters of thread blocks (k_tdma_flowc); the check then uses lines
+    # of 8194 nodes (640 layout threads, two blocks per line) and forces that solver in BOTH runs -- its three-column
+    # reduction rounds differently from the one-block solver, the partition must not matter
+    if cluster:
+        os.environ["CFD_B200_CLUSTER"] = "1"
     if kind == "buoyancy":
         n = 2050
         shape = (n, n)
@@ -229,7 +234,7 @@ def parity_check(kind, slabs="i", iters=6, turbulent=False):
         s = SlabCavity(shape[0] - 2, shape[1] - 2, slab_cls=TeachSlab, epsx=1.0, turbulent=turbulent)
         single = (lambda: cfd_b200.TeachFVM(shape[0], shape[1], epsx=1.0, order="redblack", turbulent=turbulent)) if rank == 0 else None
     else:
-        shape = (64 * world, 2048) if slabs == "i" else (96, 256 * world)
+        shape = ((64 * world, 2048) if not cluster else (64 * world, 8192)) if slabs == "i" else (96, 256 * world)
         s = (SlabCavity if slabs == "i" else JSlabCavity)(*shape, reynolds=REYNOLDS)
 
         def single():
@@ -257,6 +262,10 @@ def parity_check(kind, slabs="i", iters=6, turbulent=False):
                                        f"iterations, {slabs}-slabs vs one context",
                "halo_path": halo_path, "fields": list(names), "bitwise": bitwise, "max_abs": max_abs, "tolerance": tol,
                "ok": bool(bitwise if slabs == "i" else max_abs <= tol)}
+    if cluster:
+        os.environ.pop("CFD_B200_CLUSTER", None)
+        if rec is not None:
+            rec["line_solver"] = "clusters of thread blocks (k_tdma_flowc), forced in both runs"
     flag = torch.tensor([1 if (rec is None or rec["ok"]) else 0], device="cuda")
     dist.broadcast(flag, 0)
     if int(flag.item()) != 1:
@@ -693,7 +702,7 @@ def run_cavity16k(args):
     parity, jcut = None, args.slabs == "j"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        parity = parity_check("cavity", "j" if jcut else "i")
+        parity = parity_check("cavity", "j" if jcut else "i", cluster=not jcut)
         solver = JSlabCavity(NG, NG, reynolds=REYNOLDS) if jcut else SlabCavity(NG, NG, reynolds=REYNOLDS)
         step, ctx0 = solver.iterate_async, solver.ctx
     elif jcut:
@@ -788,6 +797,9 @@ def run_step(args, kind="step"):
     NI, NJ = (16384, 4096) if kind == "step" else (8194, 8194)
     stream = torch.cuda.Stream()
     turb = bool(getattr(args, "turbulent", False)) and kind == "step"
+    # (buoyancy 8192^2 on >= 3 GPUs: slabs of <= 3072 lines take the cluster line solver, tdma_flow_kernels.cu:
+    # cfd_flow_eligible; the general family needs square grids, so its small parity case cannot have 8194-node lines --
+    # the cluster solver over peer memory is checked by --workload cavity16k's parity case and tests/test_gpu_dist.py)
     parity = parity_check(kind, turbulent=turb) if world > 1 else None
     if world == 1:
         if kind == "step":

@@ -398,10 +398,14 @@ bool cfd_flow_eligible(const cfd_ctx* c) {
   // 2.18 ms against 2.55 ms on one GPU, and the buoyancy iteration over two GPUs 8.07 ms (one block per line, NCCL halo
   // lines) against 8.32 ms (clusters, halo lines over peer memory): the cluster kernel's three-column reduction costs
   // more than it saves there, so those layouts keep the first solver.  Beyond 992 threads the cluster kernel is the
-  // only one.  CFD_B200_CLUSTER=1 forces it (tests).
+  // only one.  Narrow i-slabs turn the balance: with 2048 lines per GPU (8192^2 over 4) the same iteration takes 3.99 ms
+  // with clusters and peer-memory halos against 4.48 ms with NCCL stages, with 1024 lines (over 8) 2.17 against 2.81 ms --
+  // every colour pass of the one-block solver ends in a partial wave and in a host-issued exchange.  Slabs of at most 3072
+  // local lines therefore take the cluster solver.  CFD_B200_CLUSTER=1 forces it everywhere (tests), =0 never prefers it.
   const char* fce = getenv("CFD_B200_CLUSTER");          // read per call: tests switch it
   const bool force_cluster = fce && atoi(fce) != 0;
-  const bool cluster_ok = cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4 && (c->L.T + 32 > 1024 || force_cluster);
+  const bool narrow_slab = (c->cfg.halo_w > 0 || c->cfg.halo_e > 0) && c->L.ni <= 3072 && !(fce && atoi(fce) == 0);
+  const bool cluster_ok = cfd_cluster_size(c->L.T) > 0 && c->L.M >= 4 && (c->L.T + 32 > 1024 || force_cluster || narrow_slab);
   const bool layout_ok = (c->L.T >= 128 && c->L.T <= 320) || cluster_ok;
   return use && c->cfg.order == CFD_ORDER_REDBLACK && c->cfg.halo_s == 0 && c->cfg.halo_n == 0 && c->cfg.joff == 0 &&
          layout_ok && c->flags != nullptr && peers_ok;

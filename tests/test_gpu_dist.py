@@ -147,8 +147,9 @@ def _nccl_worker(rank, world, port, shape, q, kind="i", peer=True):
 @pytest.mark.parametrize("kind,peer,shape", [("i", False, (96, 130)), ("j", False, (96, 130)), ("teach", False, (96, 130)),
                                              ("buoyancy", False, (98, 98)), ("i", True, (96, 2048)),
                                              ("teach", True, (98, 2050)), ("buoyancy", True, (2050, 2050)),
-                                             ("turb", False, (96, 130)), ("turb", True, (98, 2050))])
-def test_nccl_slabs_match_single_context(cfd, kind, peer, shape):
+                                             ("turb", False, (96, 130)), ("turb", True, (98, 2050)),
+                                             ("icluster", True, (96, 8192))])
+def test_nccl_slabs_match_single_context(cfd, kind, peer, shape, monkeypatch):
     """One process per GPU.  peer=True: halo lines over peer memory (stores from inside the flag-ordered sweep kernels
     and cfd_halo_push) -- lines of 2050 nodes (160 layout threads x 13 nodes), long enough for the TMA-staged kernels that path
     lives in; peer=False:
@@ -158,6 +159,9 @@ def test_nccl_slabs_match_single_context(cfd, kind, peer, shape):
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("needs at least 2 GPUs (run under gpurun --gpus 2)")
+    if kind == "icluster":      # lines of 8194 nodes solved by clusters of two thread blocks, in the slabs AND in the single context
+        monkeypatch.setenv("CFD_B200_CLUSTER", "1")       # (the spawned ranks inherit it)
+        kind = "i"
     if kind == "buoyancy":
         g = cfd.BuoyantCavity(*shape, order="redblack")
     elif kind == "teach":
