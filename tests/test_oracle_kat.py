@@ -116,6 +116,35 @@ def test_teach_laminar_histories(oracle, case):
             assert rel(np.abs(getattr(t, name)[:c["ni"], :c["nj"]]).sum(), want) < 1e-10, (case, it, name)
 
 
+# ---- backward step as shipped: k-epsilon + energy + props + wall functions -------------------------------------------------
+@pytest.mark.parametrize("case", ["ni40_nj30", "ni34_nj26_plane"])
+def test_teach_turbulent_histories(oracle, case):
+    """oracle/teach_turb.inc against the numpy restatement of calcte / calced / calct / props / modte / moded / modt and the
+    wall law of modu / modv: six residual sums, monitor values of seven fields, field sums and the four wall arrays after
+    1, 2, 10, 30 and 60 passes of control.f90:210-217.  Both log-law branches occur (max yplusn 13-15 on the first pass,
+    below 11.63 later).  log / pow / sqrt come from two math libraries, so agreement is to rounding, not bitwise."""
+    c = kat("teach_turb")[case]
+    t = oracle.TeachTurb(ni=c["ni"], nj=c["nj"], jstep=c["jstep"], epsx=c["epsx"], indcos=c["indcos"])
+    ni, nj, im, jm = c["ni"], c["nj"], c["imon"], c["jmon"]
+    done = 0
+    for it, row in sorted(c["history"].items(), key=lambda kv: int(kv[0])):
+        res = t.iterate_turb(int(it) - done)
+        done = int(it)
+        tol = 1e-10                                               # observed: <= 2e-12 after 60 passes
+        for g, w in zip(res, row["res"]):
+            assert rel(g, w) < tol, (case, it, res, row["res"])
+        for name, want in row["mon"].items():
+            assert rel(getattr(t, name)[im - 1, jm - 1], want) < tol, (case, it, name)
+        for name, want in row["sum_abs"].items():
+            assert rel(np.abs(getattr(t, name)[:ni, :nj]).sum(), want) < tol, (case, it, name)
+        assert rel(np.abs(t.taun[:ni]).sum(), row["taun_sum"]) < tol
+        assert rel(t.yplusn[:ni].sum(), row["yplusn_sum"]) < tol
+        assert rel(np.abs(t.tauw[:nj]).sum(), row["tauw_sum"]) < tol
+        assert rel(t.xplusw[:nj].sum(), row["xplusw_sum"]) < tol
+    first = c["history"]["1"]
+    assert first["yplusn_max"] > 11.63                            # the log-law branch was taken
+
+
 # ---- explicit FD cavity with SIP ----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("case", ["n33", "n21x13", "n11_default"])
 def test_fd_explicit_cavity_steps(oracle, case):

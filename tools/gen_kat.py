@@ -738,6 +738,12 @@ class TeachRef:
     def _hybrid(c, d, sign):
         return np.maximum(np.abs(0.5 * c), d) + sign * 0.5 * c
 
+    def _tmult_n(self):
+        return self.viscos / (self.yv[self.nj] - self.y[self.nj - 1])
+
+    def _tmult_w(self):
+        return self.viscos / (self.x[self.istep] - self.xu[self.istep])
+
     def calcu(self):
         ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
         u, v, p, den, vis = self.u, self.v, self.p, self.den, self.vis
@@ -773,10 +779,9 @@ class TeachRef:
         su = su + (visn * dvdxp - viss * dvdxm) / row(self.sns) / row(self.r) * vol
         for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("su", su), ("sp", sp), ("du", du)):
             getattr(self, name)[I(), J()] = val
-        # modu (promod.f90:26-95), laminar branch of the wall law: yplusn = 11 <= 11.63  ->  tmult = viscos / yp
-        yp = self.yv[nj] - self.y[njm1]
-        tmult = self.viscos / yp
+        # modu (promod.f90:26-95); laminar runs: yplusn = 11 <= 11.63  ->  tmult = viscos / yp (TurbTeachRef: wall law)
         Iw = W(3, nim1)
+        tmult = self._tmult_n()
         self.sp[Iw, njm1] -= tmult * self.sewu[Iw] * self.rv[nj]
         self.an[Iw, njm1] = 0.0
         self.aw[3, W(self.jstep + 1, njm1)] = 0.0
@@ -838,10 +843,9 @@ class TeachRef:
         su = su + (vis[I(), J()] * row(self.r) * dvdyp - vis[I(), J(-1)] * row(self.r, -1) * dvdym) / (row(self.r) * row(self.sns)) * vol
         for name, val in (("ae", ae), ("aw", aw), ("an", an), ("as_", as_), ("su", su), ("sp", sp), ("dv", dv)):
             getattr(self, name)[I(), J()] = val
-        # modv (promod.f90:99-133), laminar branch: xplusw = 11 (0 at jstep) <= 11.63  ->  tmult = viscos / xp
-        xp = self.x[self.istep] - self.xu[self.istep]
-        tmult = self.viscos / xp
+        # modv (promod.f90:99-133); laminar runs: xplusw = 11 (0 at jstep) <= 11.63  ->  tmult = viscos / xp
         Jw = W(self.jstep + 1, njm1)
+        tmult = self._tmult_w()
         self.sp[self.istep, Jw] -= tmult * self.snsv[Jw] * self.rv[Jw]
         self.aw[self.istep, Jw] = 0.0
         self.an[W(self.istep, nim1), njm1] = 0.0
@@ -881,6 +885,265 @@ class TeachRef:
         ppref = pp[2, 2]
         p[I(), J()] += self.urf[2] * (pp[I(), J()] - ppref)
         pp[I(), J()] = 0.0
+
+
+class TurbTeachRef(TeachRef):
+    """The program as shipped: k-epsilon + energy + props on top of the laminar core.  control.f90:95-179 (constants,
+    initial fields), calc.f90:309-577 (calct, calcte, calced), promod.f90:36-60, 105-121 (wall law in modu / modv),
+    :146-296 (modt, modte, moded), general.f90:165-190 (props); loop order control.f90:210-217."""
+
+    def __init__(self, ni, nj, jstep, tin=0.0, twalln=100.0, turbin=0.03, alamda=0.005, prandl=7.0,
+                 urf_turb=(0.7, 0.7, 1.0, 0.7), nswp_turb=(3, 3, 3), uin=0.5, rlarge=0.0124, **kw):
+        super().__init__(ni, nj, jstep, uin=uin, rlarge=rlarge, **kw)
+        nim1, njm1, jstp1 = ni - 1, nj - 1, jstep + 1
+        self.cmu, self.cd, self.c1, self.c2, self.cappa, self.elog = 0.09, 1.00, 1.44, 1.92, .4187, 9.793
+        self.pred = self.cappa * self.cappa / (self.c2 - self.c1) / (self.cmu ** .5)
+        self.prte, self.prandt, self.prandl, self.twalln = 1.0, 0.9, prandl, twalln
+        pf = prandl / self.prandt
+        self.pfun = 9.24 * (pf ** 0.75 - 1.0) * (1.0 + 0.28 * np.exp(-0.007 * pf))
+        self.urfk, self.urfe, self.urft, self.urfvis = urf_turb
+        self.nswpk, self.nswpd, self.nswpt = nswp_turb
+        z2 = lambda: np.zeros((ni + 2, nj + 2))
+        for n in ("te", "ed", "t", "gen", "gamh", "sukd", "spkd"):
+            setattr(self, n, z2())
+        self.taun, self.yplusn = np.zeros(ni + 2), np.zeros(ni + 2)
+        self.tauw, self.xplusw = np.zeros(nj + 2), np.zeros(nj + 2)
+        tein = turbin * uin ** 2
+        edin = tein ** 1.5 / (alamda * rlarge)
+        self.t[1, W(2, jstep)] = tin                                       # control.f90:148-179
+        self.te[1, W(2, jstep)] = tein
+        self.ed[1, W(2, jstep)] = edin
+        self.te[2, W(2, jstep)] = tein                                     # i = 2 < istp1: jfin = jstp1
+        self.ed[2, W(2, jstep)] = edin
+        self.te[W(3, ni), W(2, njm1)] = tein
+        self.ed[W(3, ni), W(2, njm1)] = edin
+        self.t[W(2, nim1), nj] = twalln
+        self.yplusn[W(2, nim1)] = 11.0
+        self.t[1, W(jstep, nj)] = tin
+        self.xplusw[W(jstep, nj)] = 11.0
+        self.xplusw[jstep] = 0.0
+        self.res = [0.0] * 6
+        self.props()
+
+    # ---- wall law of modu / modv (promod.f90:36-60, 105-121)
+    def _tmult_n(self):
+        ni, nj = self.ni, self.nj
+        I, j = W(3, ni - 1), nj - 1
+        Im = W(3, ni - 1, -1)
+        yp = self.yv[nj] - self.y[j]
+        sqrtk = np.sqrt(0.5 * (self.te[I, j] + self.te[Im, j]))
+        denu = 0.5 * (self.den[I, j] + self.den[Im, j])
+        ypa = 0.5 * (self.yplusn[I] + self.yplusn[Im])
+        with np.errstate(divide="ignore", invalid="ignore"):
+            tm = np.where(ypa <= 11.63, self.viscos / yp, denu * self.cmu ** 0.25 * sqrtk * self.cappa / np.log(self.elog * ypa))
+        self.taun[I] = -tm * self.u[I, j]
+        self.taun[2], self.taun[ni] = self.taun[3], self.taun[ni - 1]
+        return tm
+
+    def _tmult_w(self):
+        nj, i = self.nj, self.istep
+        J, Jm = W(self.jstep + 1, nj - 1), W(self.jstep + 1, nj - 1, -1)
+        xp = self.x[i] - self.xu[i]
+        sqrtk = np.sqrt(0.5 * (self.te[i, J] + self.te[i, Jm]))
+        denv = 0.5 * (self.den[i, J] + self.den[i, Jm])
+        xpa = 0.5 * (self.xplusw[J] + self.xplusw[Jm])
+        with np.errstate(divide="ignore", invalid="ignore"):
+            tm = np.where(xpa <= 11.63, self.viscos / xp, denv * self.cmu ** 0.25 * sqrtk * self.cappa / np.log(self.elog * xpa))
+        self.tauw[J] = -tm * self.v[i, J]
+        self.tauw[self.jstep], self.tauw[nj] = self.tauw[self.jstep + 1], self.tauw[nj - 1]
+        return tm
+
+    # ---- chapter 1 shared by the three scalar equations: convection + diffusion with exchange coefficient `gam`
+    def _scalar_coefficients(self, gam):
+        nim1, njm1 = self.ni - 1, self.nj - 1
+        u, v, den = self.u, self.v, self.den
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+        col, row = (lambda a, d=0: a[I(d)][:, None]), (lambda a, d=0: a[J(d)][None, :])
+        a_n, a_s = row(self.rv, 1) * col(self.sew), row(self.rv) * col(self.sew)
+        a_ew = row(self.r) * row(self.sns) + 0.0 * a_n
+        vol = row(self.r) * row(self.sns) * col(self.sew)
+        cn = 0.5 * (den[I(), J()] + den[I(), J(1)]) * v[I(), J(1)] * a_n
+        cs = 0.5 * (den[I(), J()] + den[I(), J(-1)]) * v[I(), J()] * a_s
+        ce = 0.5 * (den[I(), J()] + den[I(1), J()]) * u[I(1), J()] * a_ew
+        cw = 0.5 * (den[I(), J()] + den[I(-1), J()]) * u[I(), J()] * a_ew
+        dn = 0.5 * (gam[I(), J()] + gam[I(), J(1)]) * a_n / row(self.dynp)
+        ds = 0.5 * (gam[I(), J()] + gam[I(), J(-1)]) * a_s / row(self.dyps)
+        de = 0.5 * (gam[I(), J()] + gam[I(1), J()]) * a_ew / col(self.dxep)
+        dw = 0.5 * (gam[I(), J()] + gam[I(-1), J()]) * a_ew / col(self.dxpw)
+        cp = np.maximum(0.0, cn - cs + ce - cw)
+        self.an[I(), J()], self.as_[I(), J()] = self._hybrid(cn, dn, -1), self._hybrid(cs, ds, +1)
+        self.ae[I(), J()], self.aw[I(), J()] = self._hybrid(ce, de, -1), self._hybrid(cw, dw, +1)
+        return I, J, col, row, vol, cp
+
+    def _finish(self, phi, urf, nswp):
+        """chapter 3 + 4 of calct / calcte / calced: ap, residual (normalised where sp holds a `great` source), relaxation."""
+        ni, nj, nim1, njm1 = self.ni, self.nj, self.ni - 1, self.nj - 1
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+        an, as_, ae, aw, su, sp = (getattr(self, n)[I(), J()] for n in ("an", "as_", "ae", "aw", "su", "sp"))
+        ap = an + as_ + ae + aw - sp
+        rs = an * phi[I(), J(1)] + as_ * phi[I(), J(-1)] + ae * phi[I(1), J()] + aw * phi[I(-1), J()] - ap * phi[I(), J()] + su
+        sorvol = self.great * (self.r[J()][None, :] * self.sew[I()][:, None] * self.sns[J()][None, :])
+        rs = np.where(-sp > 0.5 * sorvol, rs / sorvol, rs)
+        ap = ap / urf
+        self.su[I(), J()] = su + (1.0 - urf) * ap * phi[I(), J()]
+        self.ap[I(), J()] = ap
+        for _ in range(nswp):
+            line_sweep(2, 2, ni, nj, phi, self.ap, self.an, self.as_, self.ae, self.aw, self.su)
+        return float(np.abs(rs).sum())
+
+    def _dudy(self, i, j):           # cell-centre du/dy of promod.f90 / calc.f90 (i, j may be windows)
+        u = self.u
+        ip = slice(i.start + 1, i.stop + 1) if isinstance(i, slice) else i + 1
+        jp = slice(j.start + 1, j.stop + 1) if isinstance(j, slice) else j + 1
+        jm = slice(j.start - 1, j.stop - 1) if isinstance(j, slice) else j - 1
+        return (u[i, j] + u[ip, j] + u[i, jp] + u[ip, jp]) / 4. - (u[i, j] + u[ip, j] + u[i, jm] + u[ip, jm]) / 4.
+
+    def _dvdx(self, i, j):
+        v = self.v
+        ip = slice(i.start + 1, i.stop + 1) if isinstance(i, slice) else i + 1
+        im = slice(i.start - 1, i.stop - 1) if isinstance(i, slice) else i - 1
+        jp = slice(j.start + 1, j.stop + 1) if isinstance(j, slice) else j + 1
+        return (v[i, j] + v[i, jp] + v[ip, j] + v[ip, jp]) / 4. - (v[i, j] + v[i, jp] + v[im, j] + v[im, jp]) / 4.
+
+    def calcte(self):
+        ni, nj, nim1, njm1, jstp1, istep = self.ni, self.nj, self.ni - 1, self.nj - 1, self.jstep + 1, self.istep
+        u, v, den, vis, te, gen = self.u, self.v, self.den, self.vis, self.te, self.gen
+        I, J, col, row, vol, cp = self._scalar_coefficients(vis / self.prte)
+        dudx = (u[I(1), J()] - u[I(), J()]) / col(self.sew)                                    # calc.f90:430-436
+        dvdy = (v[I(), J(1)] - v[I(), J()]) / row(self.sns)
+        dudy = self._dudy(I(), J()) / row(self.sns)
+        dvdx = self._dvdx(I(), J()) / col(self.sew)
+        g = (2. * (dudx ** 2 + dvdy ** 2) + (dudy + dvdx) ** 2) * vis[I(), J()]
+        if self.indcos == 2:                                                                   # :438-441
+            with np.errstate(divide="ignore", invalid="ignore"):
+                vdr = v[I(), J()] / row(self.rv)                                               # rv(2) = 0 on the axis ...
+            vdr[:, 0] = 0.0                                                                    # ... j == 2: vdr = 0
+            g = g + vis[I(), J()] * 0.5 * (vdr + v[I(), J(1)] / row(self.rv, 1)) ** 2
+        gen[I(), J()] = g
+        self.sukd[I(), J()] = cp * te[I(), J()]
+        self.su[I(), J()] = self.sukd[I(), J()] + g * vol
+        self.spkd[I(), J()] = -cp
+        self.sp[I(), J()] = -cp - self.cd * self.cmu * den[I(), J()] ** 2 * te[I(), J()] * vol / vis[I(), J()]
+        # ---- modte (promod.f90:182-256): top wall, side wall, symmetry axis -- in this order (they share corner cells)
+        cdterm, cmu75 = self.cmu ** 0.25, self.cmu ** .75
+        j, Iw = njm1, W(2, nim1)
+        yp = self.yv[nj] - self.y[njm1]
+        sqrtk = np.sqrt(te[Iw, j])
+        vol_w = self.r[j] * self.sns[j] * self.sew[Iw]
+        gencou = 0.5 * (np.abs(self.taun[W(2, nim1, 1)] * u[W(2, nim1, 1), j]) + np.abs(self.taun[Iw] * u[Iw, j])) / yp
+        self.yplusn[Iw] = den[Iw, j] * sqrtk * cdterm * yp / self.viscos
+        dudy_w = self._dudy(Iw, j) / self.sns[j]
+        gen[Iw, j] = (gen[Iw, j] - vis[Iw, j] * dudy_w ** 2) + gencou
+        ypl = self.yplusn[Iw]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            diterm = np.where(ypl <= 11.63, den[Iw, j] * cmu75 * sqrtk * ypl / yp,
+                              den[Iw, j] * cmu75 * sqrtk * np.log(self.elog * ypl) / (self.cappa * yp))
+        self.su[Iw, j] = gen[Iw, j] * vol_w + self.sukd[Iw, j]
+        self.sp[Iw, j] = -diterm * vol_w + self.spkd[Iw, j]
+        self.an[Iw, j] = 0.0
+        i, Jw = istep, W(jstp1, njm1)
+        xp = self.x[istep] - self.xu[istep]
+        sqrtk = np.sqrt(te[i, Jw])
+        vol_s = self.r[Jw] * self.sns[Jw] * self.sew[i]
+        self.xplusw[Jw] = den[i, Jw] * sqrtk * cdterm * xp / self.viscos
+        gencou = 0.5 * (np.abs(self.tauw[W(jstp1, njm1, 1)] * v[i, W(jstp1, njm1, 1)]) + np.abs(self.tauw[Jw] * v[i, Jw])) / xp
+        dvdx_s = self._dvdx(i, Jw) / self.sew[i]
+        gen[i, Jw] = (gen[i, Jw] - vis[i, Jw] * dvdx_s ** 2) + gencou
+        xpl = self.xplusw[Jw]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            diterm = np.where(xpl <= 11.63, den[i, Jw] * cmu75 * sqrtk * xpl / xp,
+                              den[i, Jw] * cmu75 * sqrtk * np.log(self.elog * xpl) / (self.cappa * xp))
+        self.su[i, Jw] = self.sukd[i, Jw] + gen[i, Jw] * vol_s
+        self.sp[i, Jw] = self.spkd[i, Jw] - diterm * vol_s
+        self.aw[i, Jw] = 0.0
+        j = 2
+        te[Iw, 1] = te[Iw, 2]
+        dudy_a = self._dudy(Iw, j) / self.sns[j]
+        gen[Iw, j] = gen[Iw, j] - vis[Iw, j] * dudy_a ** 2
+        self.su[Iw, j] = self.sukd[Iw, j] + gen[Iw, j] * (self.r[j] * self.sns[j] * self.sew[Iw])
+        self.as_[Iw, 2] = 0.0
+        self.res[4] = self._finish(te, self.urfk, self.nswpk)
+
+    def calced(self):
+        nj, nim1, njm1, jstp1, istep = self.nj, self.ni - 1, self.nj - 1, self.jstep + 1, self.istep
+        den, vis, te, ed = self.den, self.vis, self.te, self.ed
+        I, J, col, row, vol, cp = self._scalar_coefficients(vis / self.pred)
+        self.su[I(), J()] = cp * ed[I(), J()] + self.c1 * self.cmu * self.gen[I(), J()] * vol * den[I(), J()] * te[I(), J()] / vis[I(), J()]
+        with np.errstate(divide="ignore", invalid="ignore"):      # 0/0 behind the step (te = ed = 0): moded overwrites those cells
+            self.sp[I(), J()] = -cp - self.c2 * den[I(), J()] * ed[I(), J()] * vol / te[I(), J()]
+        cmu75, Iw = self.cmu ** .75, W(2, nim1)                                               # moded (promod.f90:260-296)
+        term = cmu75 / (self.cappa * (self.yv[nj] - self.y[njm1]))
+        self.su[Iw, njm1] = self.great * term * te[Iw, njm1] ** 1.5
+        self.sp[Iw, njm1] = -self.great
+        term = cmu75 / (self.cappa * (self.x[istep] - self.xu[istep]))
+        Jw = W(jstp1, nj - 2)
+        self.su[istep, Jw] = self.great * term * te[istep, Jw] ** 1.5
+        self.sp[istep, Jw] = -self.great
+        self.as_[Iw, 2] = 0.0
+        self.res[5] = self._finish(ed, self.urfe, self.nswpd)
+
+    def calct(self):
+        nj, nim1, njm1, jstp1 = self.nj, self.ni - 1, self.nj - 1, self.jstep + 1
+        I, J, col, row, vol, cp = self._scalar_coefficients(self.gamh)
+        self.su[I(), J()] = cp * self.t[I(), J()]
+        self.sp[I(), J()] = -cp
+        j, Iw = njm1, W(2, nim1)                                                               # modt (promod.f90:146-178)
+        dyn = self.yv[nj] - self.y[njm1]
+        self.an[Iw, j] = 0.0
+        area = self.rv[j + 1] * self.sew[Iw]
+        ypl = self.yplusn[Iw]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            uplus = np.log(self.elog * ypl) / self.cappa
+            gt = np.where(ypl <= 11.63, self.viscos / (self.prandl * dyn),
+                          self.den[Iw, j] * self.cmu ** 0.25 * np.sqrt(self.te[Iw, j]) / (self.prandt * (uplus + self.pfun)))
+        term = gt * area
+        self.su[Iw, j] += term * self.twalln
+        self.sp[Iw, j] -= term
+        self.aw[2, W(jstp1, njm1)] = 0.0
+        self.as_[Iw, 2] = 0.0
+        self.res[3] = self._finish(self.t, self.urft, self.nswpt)
+
+    def props(self):                                                                           # general.f90:165-190
+        nim1, njm1 = self.ni - 1, self.nj - 1
+        I, J = W(2, nim1), W(2, njm1)
+        vis, te, ed = self.vis, self.te, self.ed
+        vis[I, 1] = vis[I, 2]
+        old = vis[I, J].copy()
+        with np.errstate(divide="ignore", invalid="ignore"):
+            new = np.where(ed[I, J] == 0., self.viscos, self.den[I, J] * te[I, J] ** 2 * self.cmu / ed[I, J] + self.viscos)
+        vis[I, J] = self.urfvis * new + (1. - self.urfvis) * old
+        self.gamh[I, J] = self.viscos / self.prandl + (vis[I, J] - self.viscos) / self.prandt
+
+    def iterate(self):                                  # control.f90:210-217
+        self.calcu()
+        self.calcv()
+        self.calcp()
+        self.calcte()
+        self.calced()
+        self.calct()
+        self.props()
+
+
+def gen_teach_turb():
+    out = {"_source": "tools/gen_kat.py (numpy restatement of backward-step-flow-2d as shipped: k-epsilon + energy + props + wall "
+                      "functions; FP64; independent of oracle/teach_turb.inc)"}
+    for key, kw in (("ni40_nj30", dict(ni=40, nj=30, jstep=8, epsx=1.05, indcos=2)),
+                    ("ni34_nj26_plane", dict(ni=34, nj=26, jstep=6, epsx=1.0, indcos=1))):
+        t = TurbTeachRef(**kw)
+        imon, jmon = 10, 10
+        hist = {}
+        for it in range(1, 61):
+            t.iterate()
+            if it in (1, 2, 10, 30, 60):
+                ni, nj = t.ni, t.nj
+                hist[str(it)] = {"res": list(t.res),
+                                 "mon": {n: float(getattr(t, n)[imon, jmon]) for n in ("u", "v", "p", "te", "ed", "t", "vis")},
+                                 "sum_abs": {n: float(np.abs(getattr(t, n)[1:ni + 1, 1:nj + 1]).sum()) for n in ("u", "v", "p", "te", "ed", "t", "vis", "gamh")},
+                                 "taun_sum": float(np.abs(t.taun[1:ni + 1]).sum()), "yplusn_sum": float(t.yplusn[1:ni + 1].sum()),
+                                 "tauw_sum": float(np.abs(t.tauw[1:nj + 1]).sum()), "xplusw_sum": float(t.xplusw[1:nj + 1].sum()),
+                                 "yplusn_max": float(t.yplusn.max())}
+        out[key] = dict(kw, imon=imon, jmon=jmon, history=hist)
+    return out
 
 
 def gen_teach():
@@ -1110,7 +1373,7 @@ def gen_stagnation():
     return out
 
 
-GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "fdcavity": gen_fdcavity, "stagnation": gen_stagnation}
+GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "stagnation": gen_stagnation}
 
 
 
