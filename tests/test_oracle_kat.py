@@ -162,6 +162,24 @@ def test_fd_explicit_cavity_steps(oracle, case):
     assert rel(np.abs(o.p[:ni + 1, :nj + 1]).sum(), last[2]) < 1e-11
 
 
+# ---- implicit-Euler / steady FD cavity with three SIP solves per step ------------------------------------------------------
+@pytest.mark.parametrize("case", ["n11_default", "n25x17_relaxed", "n17_steady"])
+def test_fd_implicit_cavity_steps(oracle, case):
+    """oracle/fdcavity_oracle.c (orc_fdci_*) against the numpy restatement of fdm_implicit_cavity.f90:174-288: the SIP
+    iteration counts of the u, v and p' solves of every step, the continuity norm, the monitor value and the field sums --
+    default case, an under-relaxed non-square case and the steady form."""
+    c = kat("fdcavity_implicit")[case]
+    o = oracle.FDCavityImplicit(ni=c["ni"], nj=c["nj"], re=c["re"], dt=c["dt"], urf=tuple(c["urf"]), steady=c["steady"])
+    ni, nj = c["ni"], c["nj"]
+    for n, st in enumerate(c["steps"]):
+        err = o.step()
+        assert list(o.s.sip_iters) == st["sip_iters"], (case, n)
+        assert rel(err, st["error"]) < 1e-11, (case, n)
+        assert rel(o.u[ni // 2 - 1, nj // 2 - 1], st["u_mon"]) < 1e-11 or abs(st["u_mon"]) < 1e-300
+        for a, want in zip((o.u, o.v, o.p), st["sum_abs"]):
+            assert rel(np.abs(a).sum(), want) < 1e-11, (case, n)
+
+
 # ---- stagnation-point scalar transport, steady ---------------------------------------------------------------------------
 def test_stagnation_point_solver_loops(oracle):
     k = kat("stagnation")

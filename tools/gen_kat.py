@@ -1173,7 +1173,7 @@ def gen_teach():
 #    :24-87), correction, mirror-ghost boundary conditions, continuity norm (time loop :168-255).
 #    SIP works on the system  ap*phi + aw*phiW + ae*phiE + as*phiS + an*phiN = su  (the program passes -aw .. -an).
 # =====================================================================================================================
-@numba.njit(cache=True)
+@numba.njit(cache=True, error_model="numpy")      # 0/0 -> NaN as in the Fortran program (a zero first residual)
 def sip_solve(n1, n2, aw, ae, as_, an, ap, su, phi, alpha, tol, maxit):
     """sipsol on the index box 1..n1 x 1..n2 (interior 2..n1-1 x 2..n2-1).  Returns the iterations used."""
     lw = np.zeros((n1 + 2, n2 + 2)); ls = np.zeros((n1 + 2, n2 + 2)); lp = np.zeros((n1 + 2, n2 + 2))
@@ -1277,6 +1277,81 @@ def gen_fdcavity():
 
 
 # =====================================================================================================================
+# 4b. lid-driven-cavity-2d/fdm-implicit/fdm_implicit_cavity.f90: implicit-Euler (or steady) momentum equations linearised
+#     about the previous velocities, each solved by SIP (sipsol :29-92: alpha 0.80, tol 1e-6, maxit 3000), p' from
+#     continuity, correction, mirror-ghost boundary values, continuity norm (time loop :174-288).
+# =====================================================================================================================
+def gen_fdcavity_implicit():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of lid-driven-cavity-2d/fdm-implicit/fdm_implicit_cavity.f90; "
+                      "independent of oracle/fdcavity_oracle.c)"}
+    for key, ni, nj, re, dt, urf, steady, nsteps in (("n11_default", 11, 11, 10.0, 1.0e-4, (1.0, 1.0, 0.5), False, 12),
+                                                     ("n25x17_relaxed", 25, 17, 100.0, 2.0e-3, (0.8, 0.7, 0.5), False, 8),
+                                                     ("n17_steady", 17, 17, 10.0, 1.0e-4, (0.7, 0.7, 0.3), True, 8)):
+        utop = 1.0
+        urfu, urfv, urfp = urf
+        dx, dy = 1.0 / (ni - 1), 1.0 / (nj - 1)
+        Z = lambda: np.zeros((ni + 3, nj + 3))                     # every array (1:ni+1, 1:nj+1) as in the program (:128-133)
+        u, v, p, pp, ae, aw, an, as_, ap, su = (Z() for _ in range(10))
+        u[1:ni + 1, nj:nj + 2] = 1.0                                # :166-169
+        rex, rey = 1.0 / re / dx ** 2, 1.0 / re / dy ** 2
+        pterm = 1.0 / dt + 2.0 * (rex + rey)
+        steps = []
+        for itsp in range(1, nsteps + 1):
+            I, J = (lambda d=0: W(2, ni - 1, d)), (lambda d=0: W(2, nj, d))             # u momentum :177-197
+            vel1, vel2 = 0.5 * (v[I(), J()] + v[I(1), J()]), 0.5 * (v[I(), J(-1)] + v[I(1), J(-1)])
+            ae[I(), J()] = -0.5 * u[I(1), J()] / dx + rex
+            aw[I(), J()] = 0.5 * u[I(-1), J()] / dx + rex
+            an[I(), J()] = -0.5 * vel1 / dy + rey
+            as_[I(), J()] = 0.5 * vel2 / dy + rey
+            gradp = (p[I(), J()] - p[I(1), J()]) / dx
+            s0, a0 = (gradp, 2.0 * (rex + rey) + 0.0 * gradp) if steady else (u[I(), J()] / dt + gradp, pterm + 0.0 * gradp)
+            su[I(), J()] = s0 + (1 - urfu) * a0 / urfu * u[I(), J()]
+            ap[I(), J()] = a0 / urfu
+            it_u = sip_solve(ni, nj + 1, -aw, -ae, -as_, -an, ap, su, u, 0.80, 1.0e-6, 3000)   # :198
+            I, J = (lambda d=0: W(2, ni, d)), (lambda d=0: W(2, nj - 1, d))             # v momentum :200-219
+            vel1, vel2 = 0.5 * (u[I(), J()] + u[I(), J(1)]), 0.5 * (u[I(-1), J()] + u[I(-1), J(1)])
+            ae[I(), J()] = -0.5 * vel1 / dx + rex
+            aw[I(), J()] = 0.5 * vel2 / dx + rex
+            an[I(), J()] = -0.5 * v[I(), J(1)] / dy + rey
+            as_[I(), J()] = -0.5 * v[I(), J(-1)] / dy + rey                              # the sign the source has (:208)
+            gradp = (p[I(), J()] - p[I(), J(1)]) / dy
+            s0, a0 = (gradp, 2.0 * (rex + rey) + 0.0 * gradp) if steady else (v[I(), J()] / dt + gradp, pterm + 0.0 * gradp)
+            su[I(), J()] = s0 + (1 - urfv) * a0 / urfv * v[I(), J()]
+            ap[I(), J()] = a0 / urfv
+            it_v = sip_solve(ni + 1, nj, -aw, -ae, -as_, -an, ap, su, v, 0.80, 1.0e-6, 3000)   # :220
+            pp[:, :] = 0.0                                                                # p' :222-240
+            I, J = (lambda d=0: W(2, ni, d)), (lambda d=0: W(2, nj, d))
+            den = 2.0 * (rex + rey) if steady else pterm
+            ae[I(), J()] = aw[I(), J()] = 1.0 / den / dx ** 2
+            an[I(), J()] = as_[I(), J()] = 1.0 / den / dy ** 2
+            ap[I(), J()] = ae[I(), J()] + aw[I(), J()] + an[I(), J()] + as_[I(), J()]
+            su[I(), J()] = (u[I(-1), J()] - u[I(), J()]) / dx + (v[I(), J(-1)] - v[I(), J()]) / dy
+            it_p = sip_solve(ni + 1, nj + 1, -aw, -ae, -as_, -an, ap, su, pp, 0.80, 1.0e-6, 3000)
+            p[I(), J()] += urfp * pp[I(), J()]                                            # :242-258 (pterm in both modes, as written)
+            Iu, Jv = W(2, ni - 1), W(2, nj - 1)
+            u[Iu, J()] -= (pp[W(2, ni - 1, 1), J()] - pp[Iu, J()]) / pterm / dx
+            v[I(), Jv] -= (pp[I(), W(2, nj - 1, 1)] - pp[I(), Jv]) / pterm / dy
+            u[1:ni + 1, 1] = -u[1:ni + 1, 2]                                              # :260-273
+            u[1:ni + 1, nj + 1] = 2.0 * utop - u[1:ni + 1, nj]
+            u[1, 2:nj + 1] = 0.0
+            u[ni, 2:nj + 1] = 0.0
+            v[1, 1:nj + 1] = -v[2, 1:nj + 1]
+            v[ni + 1, 1:nj + 1] = -v[ni, 1:nj + 1]
+            v[2:ni + 1, 1] = 0.0
+            v[2:ni + 1, nj] = 0.0
+            m = min(ni + 1, nj + 1)                                                       # `p(1,1:ni+1)` (:270): ni where nj is meant
+            p[1, 1:m + 1] = p[2, 1:m + 1]
+            p[ni + 1, 1:nj + 2] = p[ni, 1:nj + 2]
+            p[2:ni + 1, nj + 1] = p[2:ni + 1, nj]
+            p[2:ni + 1, 1] = p[2:ni + 1, 2]
+            err = float(np.sqrt((((u[I(), J()] - u[I(-1), J()]) / dx + (v[I(), J()] - v[I(), J(-1)]) / dy) ** 2).sum()))
+            steps.append({"sip_iters": [int(it_u), int(it_v), int(it_p)], "error": err, "u_mon": float(u[ni // 2, nj // 2]),
+                          "sum_abs": [float(np.abs(a[1:ni + 2, 1:nj + 2]).sum()) for a in (u, v, p)]})
+        out[key] = {"ni": ni, "nj": nj, "re": re, "dt": dt, "urf": list(urf), "steady": steady, "steps": steps}
+    return out
+
+
+# =====================================================================================================================
 # 5. stagnation-point-flow-2d/steady/fvm2d_stag_point.f90: coefficients (:462-498), boundary edits (:500-515), the
 #    iterative line solvers tdma_we / tdma_sn (:82-160) with wesweep / snsweep / tdma (:162-260), wall flux (:528-533).
 # =====================================================================================================================
@@ -1373,7 +1448,7 @@ def gen_stagnation():
     return out
 
 
-GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "stagnation": gen_stagnation}
+GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation}
 
 
 
