@@ -194,3 +194,44 @@ def test_stagnation_point_solver_loops(oracle):
         assert rel(np.abs(o.phi).sum(), c["sum_abs_phi"]) < 1e-12, key
         n += 1
     assert n == 8
+
+
+# ---- unsteady stagnation-point transport and oblique convection (scalar demos) ----------------------------------
+def test_unsteady_stagnation_point_steps(oracle):
+    """oracle/lin_oracle.c (time terms + the unsteady file's own solver copies) against the numpy restatement of
+    stag_point_unsteady.f90:583-700: 24 combinations of grid, convection scheme (UDS / CDS), time scheme (explicit Euler,
+    implicit Euler, Crank-Nicolson) and sweep direction; per step the solver's iteration count, rsm, the mid value and the
+    field sum; the wall flux after eight steps."""
+    table = kat("stag_unsteady")
+    n = 0
+    for key, c in table.items():
+        if key.startswith("_"):
+            continue
+        o = oracle.StagPoint(c["ncv"], c["ncv"], isch=c["isch"], isol=c["isol"])
+        ni = nj = c["ncv"] + 2
+        for k, st in enumerate(c["steps"]):
+            it = o.step(c["itsch"], dt=1.0e-3)
+            assert it == st["iters"], (key, k)
+            assert rel(o.rsm, st["rsm"]) < 1e-6 or (o.rsm < 1e-12 and st["rsm"] < 1e-12), (key, k, o.rsm, st["rsm"])
+            assert rel(o.phi[ni // 2 - 1, nj // 2 - 1], st["phi_mid"]) < 1e-11, (key, k)
+            assert rel(np.abs(o.phi).sum(), st["sum_abs_phi"]) < 1e-11, (key, k)
+        j = np.arange(1, nj - 1)
+        fwall = float((0.1 * (o.y[j] - o.y[j - 1]) * (o.phi[1, j] - o.phi[0, j]) / (o.xc[1] - o.xc[0])).sum())
+        assert rel(fwall, c["fwall"]) < 1e-11, key
+        n += 1
+    assert n == 24
+
+
+@pytest.mark.parametrize("case", ["cv20x20_bc1", "cv20x20_bc2", "cv32x24_bc1", "cv24x32_bc2"])
+def test_oblique_convection(oracle, case):
+    """oracle/lin_oracle.c against the numpy restatement of fvm2d_oblique_conv.f90: upwind convection of a step profile oblique
+    to the grid, outflow and prescribed east / north boundaries; iteration count of tdma_solver, the mid row of phi, the sum."""
+    c = kat("oblique")[case]
+    o = oracle.Oblique(c["nicv"], c["njcv"], vel=c["vel"], east_north_bc=c["bc"])
+    it = o.solve()
+    assert it == c["iters"]
+    phi = o.finish()
+    ni, nj = c["nicv"] + 2, c["njcv"] + 2
+    assert np.abs(phi[:, nj // 2 - 1] - np.array(c["phi_row"])).max() < 1e-13
+    assert rel(np.abs(phi).sum(), c["sum_abs_phi"]) < 1e-12
+    assert rel(phi[ni // 2 - 1, nj // 2 - 1], c["phi_mid"]) < 1e-12

@@ -1448,7 +1448,201 @@ def gen_stagnation():
     return out
 
 
-GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation}
+# =====================================================================================================================
+# 5b. stagnation-point-flow-2d/unsteady/stag_point_unsteady.f90: the same transport problem marched in time (explicit
+#     Euler, implicit Euler, Crank-Nicolson :634-688) with its own solver copies, which keep every term on the LEFT:
+#     a x(k-1) + b x(k) + c x(k+1) = d  (tdma :232-261: x(k) = q(k) - p(k) x(k+1)),  residual ae*phiE + ... + ap*phi - su.
+# 5c. diagonal-convection-2d/fvm2d_oblique_conv.f90: pure upwind convection of a step profile oblique to the grid,
+#     the same left-hand-side convention, a tdma that starts from p(2) = c(2)/b(2) (boundary terms already in su) :346-387.
+# =====================================================================================================================
+@numba.njit(cache=True, error_model="numpy")
+def lhs_sweep(direction, first_from_boundary, ni, nj, aw, ae, as_, an, ap, su, phi):
+    """One wesweep (direction 0) / snsweep (1) with all neighbour terms on the left.  first_from_boundary: the recurrence starts
+    from the boundary value x(1) (stag_point_unsteady.f90:245-249) or from the first interior equation alone (oblique :371-372)."""
+    n = nj if direction == 0 else ni
+    outer = ni if direction == 0 else nj
+    p = np.zeros(n + 2); q = np.zeros(n + 2)
+    for o in range(2, outer):
+        p[1] = 0.0
+        q[1] = (phi[o, 1] if direction == 0 else phi[1, o]) if first_from_boundary else 0.0
+        for k in range(2, n):
+            if direction == 0:
+                a, b, c = as_[o, k], ap[o, k], an[o, k]
+                d = su[o, k] - aw[o, k] * phi[o - 1, k] - ae[o, k] * phi[o + 1, k]
+            else:
+                a, b, c = aw[k, o], ap[k, o], ae[k, o]
+                d = su[k, o] - as_[k, o] * phi[k, o - 1] - an[k, o] * phi[k, o + 1]
+            if first_from_boundary or k > 2:
+                den = b - a * p[k - 1]
+                p[k] = c / den
+                q[k] = (d - a * q[k - 1]) / den
+            else:
+                p[k] = c / b
+                q[k] = d / b
+        last = (phi[o, n] if direction == 0 else phi[n, o]) if first_from_boundary else 0.0
+        x_next = last
+        for k in range(n - 1, 1, -1):
+            x = q[k] - p[k] * x_next if (first_from_boundary or k < n - 1) else q[k]
+            if direction == 0:
+                phi[o, k] = x
+            else:
+                phi[k, o] = x
+            x_next = x
+
+
+def lhs_residual(ni, nj, aw, ae, as_, an, ap, su, phi):
+    I, J = (lambda d=0: W(2, ni - 1, d)), (lambda d=0: W(2, nj - 1, d))
+    return float(np.abs(ae[I(), J()] * phi[I(1), J()] + aw[I(), J()] * phi[I(-1), J()] + an[I(), J()] * phi[I(), J(1)]
+                        + as_[I(), J()] * phi[I(), J(-1)] + ap[I(), J()] * phi[I(), J()] - su[I(), J()]).sum())
+
+
+def uniform_grid(ncv):
+    """Faces x(1..ni) and centres xc of the demos' uniform unit grid, interpolation factors fx (:522-566)."""
+    ni = ncv + 2
+    nim1 = ni - 1
+    x, xc, fx = (np.zeros(ni + 2) for _ in range(3))
+    dx = 1.0 / ncv
+    for i in range(2, nim1 + 1):
+        x[i] = x[i - 1] + dx
+    x[ni] = x[nim1]
+    xc[W(2, nim1)] = 0.5 * (x[W(2, nim1)] + x[W(2, nim1, -1)])
+    xc[1], xc[ni] = x[1], x[nim1]
+    fx[W(2, nim1)] = (x[W(2, nim1)] - xc[W(2, nim1)]) / (xc[W(2, nim1, 1)] - xc[W(2, nim1)])
+    return x, xc, fx
+
+
+def gen_stag_unsteady():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of stagnation-point-flow-2d/unsteady/stag_point_unsteady.f90 "
+                      ":583-700; independent of oracle/lin_oracle.c); den 1.2, gam 0.1, dt 1e-3, uniform 20 x 20 and 28 x 28 grids"}
+    for ncv in (20, 28):
+        for isch in (1, 2):
+            for itsch in (1, 2, 3):
+                for isol in (1, 2):
+                    ni = nj = ncv + 2
+                    nim1, njm1 = ni - 1, nj - 1
+                    den, gam, dt = 1.2, 0.1, 1.0e-3
+                    x, xc, fx = uniform_grid(ncv)
+                    y, yc, fy = x, xc, fx
+                    u = np.repeat(x[:, None], nj + 2, axis=1)
+                    v = -np.repeat(y[None, :], ni + 2, axis=0)
+                    phi = np.zeros((ni + 2, nj + 2))
+                    phi[1, 1:njm1 + 1] = 1.0 - yc[1:njm1 + 1]
+                    I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+                    hy, hx = (y[J()] - y[J(-1)])[None, :], (x[I()] - x[I(-1)])[:, None]
+                    Z = lambda: np.zeros((ni + 2, nj + 2))
+                    steps = []
+                    for it in range(1, 9):
+                        phio = phi.copy()
+                        phi[1, 1:njm1 + 1] = 1.0 - yc[1:njm1 + 1]
+                        ge, gw = den * u[I(), J()] * hy, -den * u[I(-1), J()] * hy
+                        gn, gs = den * v[I(), J()] * hx, -den * v[I(), J(-1)] * hx
+                        de = -gam * hy / (xc[I(1)] - xc[I()])[:, None]
+                        dw = -gam * hy / (xc[I()] - xc[I(-1)])[:, None]
+                        dn = -gam * hx / (yc[J(1)] - yc[J()])[None, :]
+                        ds = -gam * hx / (yc[J()] - yc[J(-1)])[None, :]
+                        if isch == 1:
+                            ce, cw, cn, cs = (np.minimum(g, 0.0) for g in (ge, gw, gn, gs))
+                        else:
+                            ce, cw = ge * fx[I()][:, None], gw * (1.0 - fx[I(-1)])[:, None]
+                            cn, cs = gn * fy[J()][None, :], gs * (1.0 - fy[J(-1)])[None, :]
+                        ae, aw, an, as_, ap, su = (Z() for _ in range(6))
+                        ae[I(), J()], aw[I(), J()], an[I(), J()], as_[I(), J()] = ce + de, cw + dw, cn + dn, cs + ds
+                        ae[nim1, J()] = 0.0                                  # outflow (:624)
+                        as_[I(), 2] = 0.0                                    # symmetry (:626)
+                        ct = den / dt * hx * hy
+                        nb = lambda: (ae[I(), J()] * phio[I(1), J()] + aw[I(), J()] * phio[I(-1), J()]
+                                      + an[I(), J()] * phio[I(), J(1)] + as_[I(), J()] * phio[I(), J(-1)])
+                        tot = lambda: ae[I(), J()] + aw[I(), J()] + an[I(), J()] + as_[I(), J()]
+                        if itsch == 1:                                       # :634-651
+                            su[I(), J()] = ct * phio[I(), J()] - nb() + tot() * phio[I(), J()]
+                            ap[I(), J()] = ct + 0.0 * ge
+                            for a in (ae, aw, an, as_):
+                                a[I(), J()] = 0.0
+                        elif itsch == 2:                                     # :653-662
+                            su[I(), J()] = ct * phio[I(), J()]
+                            ap[I(), J()] = ct - tot()
+                        else:                                                # :664-682
+                            for a in (ae, aw, an, as_):
+                                a[I(), J()] = 0.5 * a[I(), J()]
+                            su[I(), J()] = ct * phio[I(), J()] - nb() + tot() * phio[I(), J()]
+                            ap[I(), J()] = ct - tot()
+                        iters, res1, rsm = 0, 0.0, 0.0
+                        for k in range(1, 1001):                             # tdma_we / tdma_sn :79-160
+                            iters = k
+                            lhs_sweep(isol - 1, True, ni, nj, aw, ae, as_, an, ap, su, phi)
+                            res = lhs_residual(ni, nj, aw, ae, as_, an, ap, su, phi)
+                            if k == 1:
+                                res1 = res
+                            with np.errstate(divide="ignore", invalid="ignore"):
+                                rsm = float(np.float64(res) / np.float64(res1))
+                            if rsm < 1.0e-4 or (k == 1 and res1 < 1.0e-10):
+                                break
+                        steps.append({"iters": iters, "rsm": rsm, "phi_mid": float(phi[ni // 2, nj // 2]),
+                                      "sum_abs_phi": float(np.abs(phi[1:ni + 1, 1:nj + 1]).sum())})
+                    fwall = float((gam * (y[J()] - y[J(-1)]) * (phi[2, J()] - phi[1, J()]) / (xc[2] - xc[1])).sum())
+                    out[f"cv{ncv}_isch{isch}_itsch{itsch}_isol{isol}"] = {"ncv": ncv, "isch": isch, "itsch": itsch, "isol": isol,
+                                                                          "steps": steps, "fwall": fwall}
+    return out
+
+
+def gen_oblique():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of diagonal-convection-2d/fvm2d_oblique_conv.f90; independent of "
+                      "oracle/lin_oracle.c); UDS, uniform grids, tol 1e-4, maxit 100"}
+    for nicv, njcv, vel, bc in ((20, 20, 2.0, 1), (20, 20, 2.0, 2), (32, 24, 1.5, 1), (24, 32, 0.7, 2)):
+        ni, nj = nicv + 2, njcv + 2
+        nim1, njm1 = ni - 1, nj - 1
+        x, _, _ = uniform_grid(nicv)
+        y, _, _ = uniform_grid(njcv)
+        phi = np.zeros((ni + 2, nj + 2))
+        phi[1, W(2, njm1)] = 1.0                                            # :168-177
+        phi[1, 1] = 0.5
+        if bc == 2:
+            phi[W(1, nim1), nj] = 1.0
+            phi[ni, W(1, njm1)] = 0.0
+            phi[ni, nj] = 0.5
+        I, J = (lambda d=0: W(2, nim1, d)), (lambda d=0: W(2, njm1, d))
+        hy, hx = (y[J()] - y[J(-1)])[None, :], (x[I()] - x[I(-1)])[:, None]
+        Z = lambda: np.zeros((ni + 2, nj + 2))
+        ae, aw, an, as_, ap, su = (Z() for _ in range(6))
+        ae[I(), J()] = np.minimum(vel * hy + 0.0 * hx, 0.0)                  # :180-201
+        aw[I(), J()] = np.minimum(-vel * hy + 0.0 * hx, 0.0)
+        an[I(), J()] = np.minimum(vel * hx + 0.0 * hy, 0.0)
+        as_[I(), J()] = np.minimum(-vel * hx + 0.0 * hy, 0.0)
+        ap[I(), J()] = -(ae[I(), J()] + aw[I(), J()] + an[I(), J()] + as_[I(), J()])
+        su[2, J()] -= aw[2, J()] * phi[1, J()]                              # west, Dirichlet :203-208
+        aw[2, J()] = 0.0
+        if bc == 1:                                                         # east :210-219
+            ap[nim1, J()] = ae[nim1, J()] + ap[nim1, J()]
+        else:
+            su[nim1, J()] -= ae[nim1, J()] * phi[ni, J()]
+        ae[nim1, J()] = 0.0
+        if bc == 1:                                                         # north :221-230
+            ap[I(), njm1] = an[I(), njm1] + ap[I(), njm1]
+        else:
+            su[I(), njm1] -= an[I(), njm1] * phi[I(), nj]
+        an[I(), njm1] = 0.0
+        su[I(), 2] -= as_[I(), 2] * phi[I(), 1]                             # south, Dirichlet :232-237
+        as_[I(), 2] = 0.0
+        iters, res1, rsm = 0, 0.0, 0.0
+        for k in range(1, 101):                                             # tdma_solver :284-315
+            iters = k
+            lhs_sweep(0, False, ni, nj, aw, ae, as_, an, ap, su, phi)
+            res = lhs_residual(ni, nj, aw, ae, as_, an, ap, su, phi)
+            if k == 1:
+                res1 = res
+            rsm = res / res1
+            if res < 1.0e-10 or rsm < 1.0e-4:
+                break
+        if bc == 1:
+            phi[ni, 1:nj + 1] = phi[nim1, 1:nj + 1]
+            phi[1:ni + 1, nj] = phi[1:ni + 1, njm1]
+        out[f"cv{nicv}x{njcv}_bc{bc}"] = {"nicv": nicv, "njcv": njcv, "vel": vel, "bc": bc, "iters": iters, "rsm": rsm,
+                                         "phi_mid": float(phi[ni // 2, nj // 2]), "phi_row": [float(z) for z in phi[1:ni + 1, nj // 2]],
+                                         "sum_abs_phi": float(np.abs(phi[1:ni + 1, 1:nj + 1]).sum())}
+    return out
+
+
+GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation, "stag_unsteady": gen_stag_unsteady, "oblique": gen_oblique}
 
 
 
