@@ -483,3 +483,163 @@ subroutine lisolv(istart, jstart, ni, nj, it, jt, phi)
   rc = cfd_download(ctx_ls, CFD_PP, d, ni); phi(1:ni,1:nj) = real(d)
 end subroutine
 #endif
+
+! ======================================================================================================================
+! Heat-conduction programs (finite-difference-method/heat-conduction/): build with -DCFD_B200_HEAT.
+!   module cfd_b200_heat_c     bind(c) type + interfaces of the cfd_heat_* part of the C ABI
+!   fdm2d_steady_heat_cond(xmin,xmax,ymin,ymax,tleft,tright,ttop,tbottom,t,nx,ny)
+!                              steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90:68-105 with the same dummy list: the
+!                              dense (nx*ny)^2 matrix of interior()/boundary() is never built; LAMBDA and QDOT are still
+!                              the program's own functions, evaluated at the points interior() evaluates them (:171-188)
+!   heat2d_explicit_steps(...) the update loop of transient-conduction-1d/explicit-time/fdm1d_explicit_heat_cond.f90:
+!                              130-139 on a 2-D plate (the 5-point operator of the steady program, constant conductivity)
+!   heat2d_implicit_steps(...) the same plate with the implicit 1-D assembly + thomas of .../implicit-time/
+!                              fdm1d_explicit_heat_cond.f90:122-184 applied along x, then along y
+! ======================================================================================================================
+#ifdef CFD_B200_HEAT
+module cfd_b200_heat_c
+  use iso_c_binding
+  implicit none
+  type, bind(c) :: cfd_heat_config
+    integer(c_int) :: nx = 0
+    integer(c_int) :: ny = 0
+    real(c_double) :: k = 0.0_c_double
+    real(c_double) :: rho = 0.0_c_double
+    real(c_double) :: cp = 0.0_c_double
+    real(c_double) :: xa = 0.0_c_double
+    real(c_double) :: xb = 0.0_c_double
+    real(c_double) :: ya = 0.0_c_double
+    real(c_double) :: yb = 0.0_c_double
+    real(c_double) :: tleft = 0.0_c_double
+    real(c_double) :: tright = 0.0_c_double
+    real(c_double) :: tbottom = 0.0_c_double
+    real(c_double) :: ttop = 0.0_c_double
+    real(c_double) :: dt = 0.0_c_double
+    real(c_double) :: qthr = 0.0_c_double
+    real(c_double) :: qval = 0.0_c_double
+    integer(c_int) :: device = -1
+    integer(c_int) :: j_goff = 0
+    integer(c_int) :: ny_global = 0
+    integer(c_int) :: halo_s = 0
+    integer(c_int) :: halo_n = 0
+  end type
+  interface
+    integer(c_int) function cfd_heat_create(h, cfg) bind(c, name='cfd_heat_create')
+      import; type(c_ptr) :: h; type(cfd_heat_config) :: cfg
+    end function
+    integer(c_int) function cfd_heat_destroy(h) bind(c, name='cfd_heat_destroy')
+      import; type(c_ptr), value :: h
+    end function
+    integer(c_int) function cfd_heat_upload(h, t, ld) bind(c, name='cfd_heat_upload')
+      import; type(c_ptr), value :: h; integer(c_int), value :: ld; real(c_double) :: t(ld,*)
+    end function
+    integer(c_int) function cfd_heat_download(h, t, ld) bind(c, name='cfd_heat_download')
+      import; type(c_ptr), value :: h; integer(c_int), value :: ld; real(c_double) :: t(ld,*)
+    end function
+    integer(c_int) function cfd_heat2d_step(h, nsteps) bind(c, name='cfd_heat2d_step')
+      import; type(c_ptr), value :: h; integer(c_int), value :: nsteps
+    end function
+    integer(c_int) function cfd_heat2d_implicit_step(h, nsteps) bind(c, name='cfd_heat2d_implicit_step')
+      import; type(c_ptr), value :: h; integer(c_int), value :: nsteps
+    end function
+    integer(c_int) function cfd_heat_implicit_halo(fo_y, rows) bind(c, name='cfd_heat_implicit_halo')
+      import; real(c_double), value :: fo_y; integer(c_int) :: rows
+    end function
+    integer(c_int) function cfd_heat_set_operator(h, lamw, lame, lams, lamn, qdot, ld) bind(c, name='cfd_heat_set_operator')
+      import; type(c_ptr), value :: h; integer(c_int), value :: ld
+      real(c_double) :: lamw(ld,*), lame(ld,*), lams(ld,*), lamn(ld,*), qdot(ld,*)
+    end function
+    integer(c_int) function cfd_heat2d_apply(h, r, ld) bind(c, name='cfd_heat2d_apply')
+      import; type(c_ptr), value :: h; integer(c_int), value :: ld; real(c_double) :: r(ld,*)
+    end function
+    integer(c_int) function cfd_heat2d_step_var(h, nsteps) bind(c, name='cfd_heat2d_step_var')
+      import; type(c_ptr), value :: h; integer(c_int), value :: nsteps
+    end function
+    integer(c_int) function cfd_heat2d_steady_gs(h, maxit, tol, rf, iters, dx2) bind(c, name='cfd_heat2d_steady_gs')
+      import; type(c_ptr), value :: h; integer(c_int), value :: maxit; real(c_double), value :: tol, rf
+      integer(c_int) :: iters; real(c_double) :: dx2
+    end function
+    integer(c_int) function cfd_heat_synchronize(h) bind(c, name='cfd_heat_synchronize')
+      import; type(c_ptr), value :: h
+    end function
+  end interface
+end module
+
+! The reference's driver routine, same dummy list (fdm2d_steady_heat_cond.f90:68-105).  t(nx*ny) is numbered
+! k = (j-1)*nx + i as in the reference (:70-79), i.e. it is the column-major plate T(nx,ny).
+subroutine fdm2d_steady_heat_cond(xmin, xmax, ymin, ymax, tleft, tright, ttop, tbottom, t, nx, ny)
+  use cfd_b200_heat_c
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  integer, intent(in) :: nx, ny
+  real(dp), intent(in) :: xmin, xmax, ymin, ymax, tleft, tright, ttop, tbottom
+  real(dp), intent(out) :: t(nx*ny)
+  real(dp), external :: LAMBDA, QDOT
+  real(c_double), allocatable :: lw(:,:), le(:,:), ls(:,:), ln(:,:), q(:,:), t2(:,:)
+  real(dp) :: x(nx), y(ny), dx, dy
+  type(cfd_heat_config) :: cfg
+  type(c_ptr) :: h
+  integer(c_int) :: rc, iters
+  real(c_double) :: dx2
+  integer :: i, j
+  call xymesh(xmin, xmax, ymin, ymax, x, y, nx, ny)          ! the program's own mesh routine (:107-129)
+  dx = x(2) - x(1); dy = y(2) - y(1)
+  allocate(lw(nx,ny), le(nx,ny), ls(nx,ny), ln(nx,ny), q(nx,ny), t2(nx,ny))
+  lw = 0; le = 0; ls = 0; ln = 0; q = 0; t2 = 0
+  do j = 2, ny-1
+    do i = 2, nx-1
+      lw(i,j) = LAMBDA(x(i)-0.5_dp*dx, y(j)); le(i,j) = LAMBDA(x(i)+0.5_dp*dx, y(j))      ! :171-172
+      ls(i,j) = LAMBDA(x(i), y(j)-0.5_dp*dy); ln(i,j) = LAMBDA(x(i), y(j)+0.5_dp*dy)      ! :173-174
+      q(i,j) = QDOT(x(i), y(j))                                                            ! :188
+    end do
+  end do
+  cfg = cfd_heat_config(nx=nx, ny=ny, k=1.0_c_double, rho=1.0_c_double, cp=1.0_c_double, xa=xmin, xb=xmax, ya=ymin, yb=ymax, &
+                        tleft=tleft, tright=tright, tbottom=tbottom, ttop=ttop, dt=1.0_c_double)
+  rc = cfd_heat_create(h, cfg)
+  rc = cfd_heat_upload(h, t2, nx)                             ! gauss_seidel starts from t0 = 0 (:95)
+  rc = cfd_heat_set_operator(h, lw, le, ls, ln, q, nx)
+  rc = cfd_heat2d_steady_gs(h, 500, 1.0e-7_c_double, 0.5_c_double, iters, dx2)           ! maxit, tol, rf of :248-287
+  rc = cfd_heat_download(h, t2, nx)
+  t = reshape(t2, (/ nx*ny /))
+  rc = cfd_heat_destroy(h)
+end subroutine
+
+! nsteps explicit / implicit steps of a plate T(nx,ny) held by the caller (uploaded, advanced, downloaded)
+subroutine heat2d_explicit_steps(k, rho, cp, xa, xb, ya, yb, tleft, tright, tbottom, ttop, dt, t, nx, ny, nsteps)
+  use cfd_b200_heat_c
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  integer, intent(in) :: nx, ny, nsteps
+  real(dp), intent(in) :: k, rho, cp, xa, xb, ya, yb, tleft, tright, tbottom, ttop, dt
+  real(dp), intent(inout) :: t(nx,ny)
+  type(cfd_heat_config) :: cfg
+  type(c_ptr) :: h
+  integer(c_int) :: rc
+  cfg = cfd_heat_config(nx=nx, ny=ny, k=k, rho=rho, cp=cp, xa=xa, xb=xb, ya=ya, yb=yb, tleft=tleft, tright=tright, &
+                        tbottom=tbottom, ttop=ttop, dt=dt)
+  rc = cfd_heat_create(h, cfg)
+  rc = cfd_heat_upload(h, t, nx)
+  rc = cfd_heat2d_step(h, nsteps)
+  rc = cfd_heat_download(h, t, nx)
+  rc = cfd_heat_destroy(h)
+end subroutine
+
+subroutine heat2d_implicit_steps(k, rho, cp, xa, xb, ya, yb, tleft, tright, tbottom, ttop, dt, t, nx, ny, nsteps)
+  use cfd_b200_heat_c
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  integer, intent(in) :: nx, ny, nsteps
+  real(dp), intent(in) :: k, rho, cp, xa, xb, ya, yb, tleft, tright, tbottom, ttop, dt
+  real(dp), intent(inout) :: t(nx,ny)
+  type(cfd_heat_config) :: cfg
+  type(c_ptr) :: h
+  integer(c_int) :: rc
+  cfg = cfd_heat_config(nx=nx, ny=ny, k=k, rho=rho, cp=cp, xa=xa, xb=xb, ya=ya, yb=yb, tleft=tleft, tright=tright, &
+                        tbottom=tbottom, ttop=ttop, dt=dt)
+  rc = cfd_heat_create(h, cfg)
+  rc = cfd_heat_upload(h, t, nx)
+  rc = cfd_heat2d_implicit_step(h, nsteps)
+  rc = cfd_heat_download(h, t, nx)
+  rc = cfd_heat_destroy(h)
+end subroutine
+#endif

@@ -118,7 +118,7 @@ def test_bind_c_types_match_the_c_structs():
     shim, hdr = _load()
     cs, ft = c_structs(hdr), f_types(shim)
     enums = c_enums(hdr)
-    assert {"cfd_config", "cfd_turbulence", "cfd_hook_desc"} <= set(ft)
+    assert {"cfd_config", "cfd_turbulence", "cfd_hook_desc", "cfd_heat_config"} <= set(ft)
     for name, fcomps in ft.items():
         ccomps = cs[name]
         assert [c[0] for c in fcomps] == [c[0] for c in ccomps], f"{name}: component names / order differ"
@@ -185,22 +185,27 @@ def test_interfaces_exist_in_the_header_with_the_same_arity_and_value_passing():
         assert fname == cname and cname in cf, cname
         cparams = cf[cname]
         assert len(fargs) == len(cparams), (cname, fargs, cparams)
-        by_value = set()
+        by_value, handles = set(), set()
         for decl in re.split(r"[;\n]", body):
+            if "::" not in decl:
+                continue
+            names = {re.sub(r"\(.*", "", x).strip() for x in re.split(r",(?![^()]*\))", decl.split("::")[1])}
             if re.search(r",\s*value\s*::", decl):
-                by_value |= {x.strip() for x in decl.split("::")[1].split(",")}
+                by_value |= names
+            if re.match(r"\s*type\(c_ptr\)", decl):
+                handles |= names
         for fa, cp in zip(fargs, cparams):
             c_is_pointer = "*" in cp or "[" in cp
-            if fa == "ctx" and cname != "cfd_create":
-                assert "ctx" in by_value
-                continue
-            if fa == "ctx":
-                assert "**" in cp
+            if fa in handles:
+                # an opaque handle: `cfd_ctx* ctx` <-> type(c_ptr), value; `cfd_ctx** out` <-> type(c_ptr) by reference
+                assert (fa in by_value) == ("**" not in cp), (cname, fa, cp)
+                assert "*" in cp, (cname, fa, cp)
                 continue
             assert (fa in by_value) == (not c_is_pointer), (cname, fa, cp)
         seen += 1
-    assert seen >= 21
-    for need in ("cfd_lisolv", "cfd_calct", "cfd_upload_noalloc", "cfd_set_hook", "cfd_calcte", "cfd_calced", "cfd_props"):
+    assert seen >= 33
+    for need in ("cfd_lisolv", "cfd_calct", "cfd_upload_noalloc", "cfd_set_hook", "cfd_calcte", "cfd_calced", "cfd_props",
+                 "cfd_heat_create", "cfd_heat_set_operator", "cfd_heat2d_steady_gs", "cfd_heat2d_implicit_step"):
         assert re.search(r"name='%s'" % need, shim), need
 
 
@@ -213,6 +218,8 @@ def test_reference_subroutine_names_and_dummy_lists_are_kept():
     # general family: external subroutines + tdma (buoyancy_cav.f90:122-433, 471-505)
     for s in ("subroutine calct()", "subroutine tdma(istart, jstart, ni, nj, phi)"):
         assert s in raw, s
+    # heat programs: the steady 2-D driver routine with the reference's dummy list (fdm2d_steady_heat_cond.f90:68-69)
+    assert "subroutine fdm2d_steady_heat_cond(xmin, xmax, ymin, ymax, tleft, tright, ttop, tbottom, t, nx, ny)" in raw
     # TEACH: module calc (calc.f90:6) + lisolv with leading dimensions (general.f90:294)
     for s in ("module calc ", "subroutine calcte()", "subroutine calced()",
               "subroutine lisolv(istart, jstart, ni, nj, it, jt, phi)"):
