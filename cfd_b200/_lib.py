@@ -147,6 +147,8 @@ SYMBOLS = {
     "cfd_heat2d_implicit_step": (C.c_int, [_vp, C.c_int]),
     "cfd_heat2d_implicit_step_exact": (C.c_int, [_vp, C.c_int]),
     "cfd_heat_implicit_halo": (C.c_int, [C.c_double, C.POINTER(C.c_int)]),
+    "cfd_sipsol": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int] + [_vp] * 7 + [C.c_int, C.c_double, C.c_double, C.c_int,
+                             C.POINTER(C.c_int), C.POINTER(C.c_double)]),
     "cfd_heat_set_operator": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "cfd_heat2d_apply": (C.c_int, [_vp, _vp, C.c_int]),
     "cfd_heat2d_step_var": (C.c_int, [_vp, C.c_int]),

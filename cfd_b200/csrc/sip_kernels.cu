@@ -604,14 +604,25 @@ size_t cfd_sip_sync_bytes(int ld, int nrows) {
 
 // Launch one SIP solve.  coef != nullptr: five coefficient arrays {aw, ae, as, an, ap} (the four neighbour arrays are
 // negated, as the callers pass `-aw, -ae, -as, -an`); otherwise the constants c[5].  Work arrays are the caller's.
+static int sip_launch(int device, cudaStream_t stream, int ld, int nrows, int imax, int jmax, const double* c,
+                      const double* const* coef, double sign, double alpha, double tol, int maxit, const double* su, double* phi,
+                      double* work, unsigned long long* prog, double* partial, int* info, double* rsm_out, int max_partials);
+
 int cfd_launch_sip(int device, cudaStream_t stream, int ld, int nrows, int imax, int jmax, const double* c,
                    const double* const* coef, double alpha, double tol, int maxit, const double* su, double* phi, double* work,
                    unsigned long long* prog, double* partial, int* info, double* rsm_out, int max_partials) {
+  return sip_launch(device, stream, ld, nrows, imax, jmax, c, coef, -1.0, alpha, tol, maxit, su, phi, work, prog, partial, info,
+                    rsm_out, max_partials);
+}
+
+static int sip_launch(int device, cudaStream_t stream, int ld, int nrows, int imax, int jmax, const double* c,
+                      const double* const* coef, double sign, double alpha, double tol, int maxit, const double* su, double* phi,
+                      double* work, unsigned long long* prog, double* partial, int* info, double* rsm_out, int max_partials) {
   SipParams P{};
   P.imax = imax; P.jmax = jmax; P.ld = ld;
   if (coef) {
     P.awp = coef[0]; P.aep = coef[1]; P.asp = coef[2]; P.anp = coef[3]; P.app = coef[4];
-    P.sign = -1.0;
+    P.sign = sign;
   } else {
     P.aw = c[0]; P.ae = c[1]; P.as = c[2]; P.an = c[3]; P.ap = c[4];
   }
@@ -645,5 +656,65 @@ int cfd_launch_sip(int device, cudaStream_t stream, int ld, int nrows, int imax,
   CFD_CUDA(cudaMemsetAsync(info, 0, 2 * sizeof(int), stream));
   void* args[] = {(void*)&P};
   CFD_CUDA(cudaLaunchCooperativeKernel((void*)k_sip_solve, dim3(grid), dim3(32 * SIP_WARPS), args, smem, stream));
+  return CFD_OK;
+}
+
+
+// ---- sipsol as a drop-in on HOST arrays (include/cfd_b200.h: cfd_sipsol) ------------------------------------------------
+// One call = one `call sipsol(i1, i2, j1, j2, aw, ae, as, an, ap, su, phi)` of fdm_implicit_cavity.f90:29-92 /
+// fdm_explicit_cavity.f90:24-87 with i1 = j1 = 1: the six coefficient arrays and phi are uploaded, the whole solve (incomplete
+// factorisation + up to maxit iterations) runs in one kernel, phi comes back.  Work space is allocated and freed per call:
+// a convenience for hosts that keep their own time loop; the cfd_fdcav_* entry points keep everything resident.
+extern "C" int cfd_sipsol(int device, int i2, int j2, int ld, const double* aw, const double* ae, const double* as_,
+                          const double* an, const double* ap, const double* su, double* phi, int negate, double alpha,
+                          double tol, int maxit, int* iters, double* rsm) {
+  CFD_REQUIRE(i2 >= 3 && j2 >= 3 && ld >= i2 && aw && ae && as_ && an && ap && su && phi, "bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cfd_set_error("no CUDA device");
+    return CFD_ERR_NO_DEVICE;
+  }
+  if (device < 0) CFD_CUDA(cudaGetDevice(&device));
+  CFD_CUDA(cudaSetDevice(device));
+  const size_t n = (size_t)ld * j2, bytes = n * sizeof(double);
+  double* dev = nullptr;                       // 7 uploaded arrays + 6 work arrays + partials + rsm
+  unsigned long long* sync = nullptr;
+  int* info = nullptr;
+  const size_t tail = 1024 + 8;
+  if (cudaMalloc(&dev, 13 * bytes + tail * sizeof(double)) != cudaSuccess || cudaMalloc(&sync, cfd_sip_sync_bytes(ld, j2)) != cudaSuccess ||
+      cudaMalloc(&info, 2 * sizeof(int)) != cudaSuccess) {
+    if (dev) cudaFree(dev);
+    if (sync) cudaFree(sync);
+    if (info) cudaFree(info);
+    cfd_set_error("cfd_sipsol: cudaMalloc of %zu bytes failed", 13 * bytes);
+    return CFD_ERR_NOMEM;
+  }
+  const double* host[7] = {aw, ae, as_, an, ap, su, phi};
+  int rc = CFD_OK;
+  for (int k = 0; k < 7 && rc == CFD_OK; ++k)
+    if (cudaMemcpy(dev + k * n, host[k], bytes, cudaMemcpyHostToDevice) != cudaSuccess) rc = CFD_ERR_CUDA;
+  if (rc == CFD_OK) {
+    const double* coef[5] = {dev, dev + n, dev + 2 * n, dev + 3 * n, dev + 4 * n};
+    double* partial = dev + 13 * n;
+    rc = sip_launch(device, 0, ld, j2, i2 - 2, j2 - 2, nullptr, coef, negate ? -1.0 : 1.0, alpha, tol, maxit, dev + 5 * n, dev + 6 * n,
+                    dev + 7 * n, sync, partial, info, partial + 1024, 1024);
+  }
+  int hinfo[2] = {0, 0};
+  if (rc == CFD_OK && (cudaMemcpy(phi, dev + 6 * n, bytes, cudaMemcpyDeviceToHost) != cudaSuccess ||
+                       cudaMemcpy(hinfo, info, sizeof(hinfo), cudaMemcpyDeviceToHost) != cudaSuccess ||
+                       (rsm && cudaMemcpy(rsm, dev + 13 * n + 1024, sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess)))
+    rc = CFD_ERR_CUDA;
+  cudaFree(dev);
+  cudaFree(sync);
+  cudaFree(info);
+  if (rc != CFD_OK) {
+    if (rc == CFD_ERR_CUDA) cfd_set_error("cfd_sipsol: %s", cudaGetErrorString(cudaGetLastError()));
+    return rc;
+  }
+  if (hinfo[1]) {
+    cfd_set_error("SIP: wavefront wait abandoned (pipeline stalled)");
+    return CFD_ERR_CUDA;
+  }
+  if (iters) *iters = hinfo[0];
   return CFD_OK;
 }

@@ -94,3 +94,19 @@ class FDCavity:
         check(self.lib.cfd_fdcav_implicit_step(self._h, C.byref(e), it))
         self.sip_iters = list(it)
         return e.value
+
+
+def sipsol(aw, ae, as_, an, ap, su, phi, *, i2=None, j2=None, negate=True, alpha=0.80, tol=1.0e-6, maxit=3000, device=-1):
+    """`call sipsol(1, i2, 1, j2, -aw, -ae, -as, -an, ap, su, phi)` (fdm_implicit_cavity.f90:29-92; negate=False: the arrays as
+    given) on host arrays of one common shape (ld, ncols), Fortran order; phi is updated in place.  Returns (iterations, rsm)."""
+    lib = _lib.load()
+    arrs = [np.asfortranarray(a, dtype=np.float64) for a in (aw, ae, as_, an, ap, su)]
+    if not (phi.flags.f_contiguous and phi.dtype == np.float64):
+        raise ValueError("phi must be a Fortran-ordered float64 array (it is updated in place)")
+    ld, ncols = phi.shape
+    i2 = ld if i2 is None else i2
+    j2 = ncols if j2 is None else j2
+    it, rsm = C.c_int(), C.c_double()
+    check(lib.cfd_sipsol(device, i2, j2, ld, *(a.ctypes.data_as(C.c_void_p) for a in arrs), phi.ctypes.data_as(C.c_void_p),
+                         1 if negate else 0, alpha, tol, maxit, C.byref(it), C.byref(rsm)))
+    return it.value, rsm.value

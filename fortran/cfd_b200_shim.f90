@@ -643,3 +643,50 @@ subroutine heat2d_implicit_steps(k, rho, cp, xa, xb, ya, yb, tleft, tright, tbot
   rc = cfd_heat_destroy(h)
 end subroutine
 #endif
+
+! ======================================================================================================================
+! Finite-difference cavity programs (lid-driven-cavity-2d/fdm-explicit, fdm-implicit): build with -DCFD_B200_FDCAVITY
+! (add -DCFD_B200_SIP_EXPLICIT for the explicit program's solver constants).  Replaces `module cavity_mod`:
+!   sipsol(i1, i2, j1, j2, aw, ae, as, an, ap, su, phi)      fdm_implicit_cavity.f90:29-92 / fdm_explicit_cavity.f90:24-87,
+!                              same dummy list; the arrays arrive already negated (`call sipsol(1, ni, 1, nj+1, -aw, ...)`),
+!                              so the library is told to use them as they are (negate = 0)
+! ======================================================================================================================
+#ifdef CFD_B200_FDCAVITY
+module cavity_mod
+  use iso_c_binding
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  interface
+    integer(c_int) function cfd_sipsol(device, i2, j2, ld, aw, ae, as, an, ap, su, phi, negate, alpha, tol, maxit, iters, rsm) &
+        bind(c, name='cfd_sipsol')
+      import; integer(c_int), value :: device, i2, j2, ld, negate, maxit; real(c_double), value :: alpha, tol
+      real(c_double) :: aw(ld,*), ae(ld,*), as(ld,*), an(ld,*), ap(ld,*), su(ld,*), phi(ld,*)
+      integer(c_int) :: iters; real(c_double) :: rsm
+    end function
+  end interface
+contains
+  subroutine sipsol(i1, i2, j1, j2, aw, ae, as, an, ap, su, phi)
+    integer, intent(in) :: i1, i2, j1, j2
+    real(dp), dimension(:,:), intent(in) :: aw, ae, as, an, ap, su
+    real(dp), dimension(:,:), intent(out) :: phi            ! in/out in fact: the iteration starts from it (:66-68)
+#ifdef CFD_B200_SIP_EXPLICIT
+    integer, parameter :: maxit = 600                       ! fdm_explicit_cavity.f90:29-31
+    real(dp), parameter :: alpha = 0.88_dp, tol = 1.0e-5_dp
+#else
+    integer, parameter :: maxit = 3000                      ! fdm_implicit_cavity.f90:34-36
+    real(dp), parameter :: alpha = 0.80_dp, tol = 1.0e-6_dp
+#endif
+    real(c_double), allocatable :: c(:,:,:), x(:,:)
+    integer(c_int) :: rc, iters
+    real(c_double) :: rsm
+    integer :: ld, nc
+    ! every caller passes whole arrays with i1 = j1 = 1 (:198, :220, :241 / :206); sections would be copied here anyway
+    ld = size(phi, 1); nc = size(phi, 2)
+    allocate(c(ld,nc,6), x(ld,nc))
+    c(:,:,1) = aw; c(:,:,2) = ae; c(:,:,3) = as; c(:,:,4) = an; c(:,:,5) = ap; c(:,:,6) = su
+    x = phi
+    rc = cfd_sipsol(-1, i2, j2, ld, c(:,:,1), c(:,:,2), c(:,:,3), c(:,:,4), c(:,:,5), c(:,:,6), x, 0, alpha, tol, maxit, iters, rsm)
+    phi = x
+  end subroutine
+end module
+#endif

@@ -420,6 +420,15 @@ int cfd_fdcav_implicit_assemble(cfd_fdcav* h, int which);
 int cfd_fdcav_implicit_solve(cfd_fdcav* h, int which, int* iters);
 int cfd_fdcav_implicit_correct(cfd_fdcav* h, double* error);
 int cfd_fdcav_implicit_step(cfd_fdcav* h, double* error, int iters[3]);
+/* sipsol itself as a drop-in on host arrays: `call sipsol(1, i2, 1, j2, aw, ae, as, an, ap, su, phi)` of
+   fdm_implicit_cavity.f90:29-92 (alpha 0.80, tol 1e-6, maxit 3000) and fdm_explicit_cavity.f90:24-87 (0.88, 1e-5, 600).  All
+   arrays are (ld, j2) column-major, the unknowns are the interior 2..i2-1 x 2..j2-1, phi is in/out.  negate != 0: the four
+   neighbour arrays are the program's own and the solver uses their negatives, as in `call sipsol(.., -aw, -ae, -as, -an, ..)`
+   (no negated copies on the host).  Uploads, solves in one kernel, downloads phi; work space is allocated per call
+   (device < 0: the current device).  iters / rsm (may be NULL) return the iterations used and the last residual ratio. */
+int cfd_sipsol(int device, int i2, int j2, int ld, const double* aw, const double* ae, const double* as, const double* an,
+               const double* ap, const double* su, double* phi, int negate, double alpha, double tol, int maxit, int* iters,
+               double* rsm);
 
 /* library/build identification */
 const char* cfd_version(void);

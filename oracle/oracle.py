@@ -546,6 +546,18 @@ class FDCavityImplicit:
         return self.L.orc_fdci_step(C.byref(self.s))
 
 
+def sipsol_arr(aw, ae, as_, an, ap, su, phi, i2=None, j2=None, maxit=3000, alpha=0.80, tol=1.0e-6, fast=False):
+    """orc_sipsol_arr: sipsol of fdm_implicit_cavity.f90:29-92 on array coefficients (the four neighbour arrays are negated
+    inside, as the program's call does); phi (Fortran order) updated in place; returns the iterations used."""
+    L = lib(fast)
+    L.orc_sipsol_arr.restype = C.c_int
+    L.orc_sipsol_arr.argtypes = [C.c_int] * 4 + [_dp] * 7 + [C.c_int, C.c_double, C.c_double]
+    ld, nrow = phi.shape
+    arrs = [np.asfortranarray(a, dtype=np.float64) for a in (aw, ae, as_, an, ap, su)]
+    return L.orc_sipsol_arr(ld, nrow, ld if i2 is None else i2, nrow if j2 is None else j2, *(_p(a) for a in arrs), _p(phi),
+                            maxit, alpha, tol)
+
+
 # ---- scalar-transport demos (oracle/lin_oracle.c) ------------------------------------------------------------------
 class _LinBase:
     COEF = ("aw", "ae", "as_", "an", "ap", "su")

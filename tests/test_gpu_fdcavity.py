@@ -115,3 +115,28 @@ def test_implicit_steady_divergence_is_reproduced_too(cfd, oracle):
         g.implicit_step()
     assert np.array_equal(g.download("v"), o.v, equal_nan=True) and np.isnan(o.v).any()
     g.close()
+
+
+@pytest.mark.parametrize("shape,negate", [((40, 56), True), ((130, 97), True), ((65, 300), False)])
+def test_sipsol_drop_in_on_host_arrays(cfd, oracle, shape, negate):
+    """cfd_sipsol = `call sipsol(1, i2, 1, j2, -aw, -ae, -as, -an, ap, su, phi)` on host arrays (what the Fortran shim's
+    sipsol forwards to): same iteration count and the same bits as the restated sipsol on a random diagonally dominant
+    system, with the program's arrays (negated inside) and with arrays passed as they are."""
+    from cfd_b200.fdcavity import sipsol
+    ld, ncols = shape
+    rng = np.random.default_rng(ld * 1000 + ncols)
+    aw, ae, as_, an = (np.asfortranarray(0.1 + rng.random(shape)) for _ in range(4))
+    ap = np.asfortranarray(aw + ae + as_ + an + 0.05 + 0.5 * rng.random(shape))
+    su = np.asfortranarray(rng.random(shape) - 0.5)
+    phi0 = np.asfortranarray(rng.random(shape))
+    want = phi0.copy(order="F")
+    it_want = oracle.sipsol_arr(aw, ae, as_, an, ap, su, want)
+    got = phi0.copy(order="F")
+    if negate:
+        it, rsm = sipsol(aw, ae, as_, an, ap, su, got)
+    else:
+        it, rsm = sipsol(-aw, -ae, -as_, -an, ap, su, got, negate=False)
+    assert it == it_want and 0 < it < 3000
+    assert rsm < 1.0e-6
+    assert np.array_equal(got, want)
+    assert np.array_equal(got[0, :], phi0[0, :]) and np.array_equal(got[:, -1], phi0[:, -1])     # boundary values untouched
