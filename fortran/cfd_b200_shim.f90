@@ -133,6 +133,10 @@ module cfd_b200_c
     integer(c_int) function cfd_lisolv(ctx, istart, jstart, field) bind(c, name='cfd_lisolv')
       import; type(c_ptr), value :: ctx; integer(c_int), value :: istart, jstart, field
     end function
+    integer(c_int) function cfd_lin_solve(ctx, field, dir, variant, maxit, tol, iters, rsm) bind(c, name='cfd_lin_solve')
+      import; type(c_ptr), value :: ctx; integer(c_int), value :: field, dir, variant, maxit; real(c_double), value :: tol
+      integer(c_int) :: iters; real(c_double) :: rsm
+    end function
     integer(c_int) function cfd_iterate(ctx, n, res) bind(c, name='cfd_iterate')
       import; type(c_ptr), value :: ctx; integer(c_int), value :: n; real(c_double) :: res(8)
     end function
@@ -689,4 +693,91 @@ contains
     phi = x
   end subroutine
 end module
+#endif
+
+
+! ======================================================================================================================
+! Scalar-transport demos (stagnation-point-flow-2d/steady and /unsteady, diagonal-convection-2d): build with
+! -DCFD_B200_SCALAR.  The iterative line-by-line solvers keep their names and dummy lists:
+!   tdma_we / tdma_sn (aw, ae, as, an, ap, su, phi)     fvm2d_stag_point.f90:82-160 (neighbour terms on the right) and, with
+!                              -DCFD_B200_SCALAR_LHS, the unsteady program's copies stag_point_unsteady.f90:79-160, which
+!                              keep every term on the left: the neighbour arrays are uploaded negated (exact sign flips)
+!   tdma_solver(aw, ae, as, an, ap, su, phi, ni, nj)    fvm2d_oblique_conv.f90:284-318 (all terms on the left, its own stop
+!                              rule: variant 1 of cfd_lin_solve)
+! ======================================================================================================================
+#ifdef CFD_B200_SCALAR
+module cfd_b200_scalar
+  use cfd_b200_c
+  implicit none
+  integer, parameter, private :: dp = selected_real_kind(15)
+  type(c_ptr), private, save :: ctx_lin = c_null_ptr
+  integer, private, save :: lin_ni = 0, lin_nj = 0
+contains
+  ! dir 0: W->E sweeps of S-N lines, 1: S->N sweeps of W-E lines; sgn -1: the caller keeps the neighbour terms on the left
+  subroutine lin_solve(aw, ae, as, an, ap, su, phi, dir, variant, maxit, sgn)
+    real(dp), dimension(:,:), intent(in) :: aw, ae, as, an, ap, su
+    real(dp), dimension(:,:), intent(inout) :: phi
+    integer, intent(in) :: dir, variant, maxit
+    real(dp), intent(in) :: sgn
+    type(cfd_config) :: cfg
+    real(c_double), allocatable :: d(:,:)
+    integer(c_int) :: rc, iters
+    real(c_double) :: rsm
+    integer :: ni, nj
+    ni = size(phi, 1); nj = size(phi, 2)
+    if (.not. c_associated(ctx_lin) .or. ni /= lin_ni .or. nj /= lin_nj) then
+      if (c_associated(ctx_lin)) rc = cfd_destroy(ctx_lin)
+      cfg = cfd_config(family=CFD_FAMILY_CAVITY, ni=ni, nj=nj, order=CFD_ORDER_SEQUENTIAL, raw_coefficients=1)
+      rc = cfd_create(ctx_lin, cfg)
+      lin_ni = ni; lin_nj = nj
+    end if
+    allocate(d(ni,nj))
+    d = sgn*ae; rc = cfd_upload(ctx_lin, CFD_AE, d, ni)
+    d = sgn*aw; rc = cfd_upload(ctx_lin, CFD_AW, d, ni)
+    d = sgn*an; rc = cfd_upload(ctx_lin, CFD_AN, d, ni)
+    d = sgn*as; rc = cfd_upload(ctx_lin, CFD_AS, d, ni)
+    d = ap;     rc = cfd_upload(ctx_lin, CFD_AP, d, ni)
+    d = su;     rc = cfd_upload(ctx_lin, CFD_SU, d, ni)
+    d = phi;    rc = cfd_upload(ctx_lin, CFD_PP, d, ni)
+    rc = cfd_lin_solve(ctx_lin, CFD_PP, dir, variant, maxit, 1.0e-4_c_double, iters, rsm)
+    rc = cfd_download(ctx_lin, CFD_PP, d, ni)
+    phi = d
+  end subroutine
+end module
+
+subroutine tdma_we(aw, ae, as, an, ap, su, phi)
+  use cfd_b200_scalar
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  real(dp), dimension(:,:), intent(in) :: aw, ae, as, an, ap, su
+  real(dp), dimension(:,:), intent(out) :: phi
+#ifdef CFD_B200_SCALAR_LHS
+  call lin_solve(aw, ae, as, an, ap, su, phi, 0, 0, 1000, -1.0_dp)
+#else
+  call lin_solve(aw, ae, as, an, ap, su, phi, 0, 0, 1000, 1.0_dp)
+#endif
+end subroutine
+
+subroutine tdma_sn(aw, ae, as, an, ap, su, phi)
+  use cfd_b200_scalar
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  real(dp), dimension(:,:), intent(in) :: aw, ae, as, an, ap, su
+  real(dp), dimension(:,:), intent(out) :: phi
+#ifdef CFD_B200_SCALAR_LHS
+  call lin_solve(aw, ae, as, an, ap, su, phi, 1, 0, 1000, -1.0_dp)
+#else
+  call lin_solve(aw, ae, as, an, ap, su, phi, 1, 0, 1000, 1.0_dp)
+#endif
+end subroutine
+
+subroutine tdma_solver(aw, ae, as, an, ap, su, phi, ni, nj)
+  use cfd_b200_scalar
+  implicit none
+  integer, parameter :: dp = selected_real_kind(15)
+  integer, intent(in) :: ni, nj
+  real(dp), dimension(1:ni,1:nj), intent(in) :: aw, ae, as, an, ap, su
+  real(dp), dimension(1:ni,1:nj), intent(inout) :: phi
+  call lin_solve(aw, ae, as, an, ap, su, phi, 0, 1, 100, -1.0_dp)
+end subroutine
 #endif

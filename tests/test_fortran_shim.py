@@ -203,9 +203,9 @@ def test_interfaces_exist_in_the_header_with_the_same_arity_and_value_passing():
                 continue
             assert (fa in by_value) == (not c_is_pointer), (cname, fa, cp)
         seen += 1
-    assert seen >= 34
+    assert seen >= 35
     for need in ("cfd_lisolv", "cfd_calct", "cfd_upload_noalloc", "cfd_set_hook", "cfd_calcte", "cfd_calced", "cfd_props",
-                 "cfd_heat_create", "cfd_heat_set_operator", "cfd_heat2d_steady_gs", "cfd_heat2d_implicit_step", "cfd_sipsol"):
+                 "cfd_heat_create", "cfd_heat_set_operator", "cfd_heat2d_steady_gs", "cfd_heat2d_implicit_step", "cfd_sipsol", "cfd_lin_solve"):
         assert re.search(r"name='%s'" % need, shim), need
 
 
@@ -220,6 +220,10 @@ def test_reference_subroutine_names_and_dummy_lists_are_kept():
         assert s in raw, s
     # heat programs: the steady 2-D driver routine with the reference's dummy list (fdm2d_steady_heat_cond.f90:68-69)
     assert "subroutine fdm2d_steady_heat_cond(xmin, xmax, ymin, ymax, tleft, tright, ttop, tbottom, t, nx, ny)" in raw
+    # scalar-transport demos: the iterative line solvers (fvm2d_stag_point.f90:82,122; fvm2d_oblique_conv.f90:284)
+    for s in ("subroutine tdma_we(aw, ae, as, an, ap, su, phi)", "subroutine tdma_sn(aw, ae, as, an, ap, su, phi)",
+              "subroutine tdma_solver(aw, ae, as, an, ap, su, phi, ni, nj)"):
+        assert s in raw, s
     # FD cavity programs: module cavity_mod with sipsol's dummy list (fdm_implicit_cavity.f90:29, fdm_explicit_cavity.f90:24)
     for s in ("module cavity_mod", "subroutine sipsol(i1, i2, j1, j2, aw, ae, as, an, ap, su, phi)"):
         assert s in raw, s
