@@ -11,8 +11,12 @@
 !   lisolv(istart,jstart,ni,nj,it,jt,phi)   of backward-step-flow-2d/general.f90:294-327  (build with
 !                              -DCFD_B200_TEACH, because it has the cavity routine's name)
 !
+!   module cfd_b200_heat_c, fdm2d_steady_heat_cond(...), heat2d_explicit_steps / heat2d_implicit_steps   (heat programs)
+!   module cavity_mod          sipsol(i1,i2,j1,j2,aw,ae,as,an,ap,su,phi) of the two FD cavity programs
+!   tdma_we, tdma_sn, tdma_solver   the line solvers of the scalar-transport demos
+!
 ! Each reference program is built with the part of this file it needs (pre-processor symbols CFD_B200_CAVITY,
-! CFD_B200_GENERAL, CFD_B200_TEACH; gfortran -cpp).  Not compiled in this repository's build image (no Fortran
+! CFD_B200_GENERAL, CFD_B200_TEACH, CFD_B200_HEAT, CFD_B200_FDCAVITY, CFD_B200_SCALAR; gfortran -cpp).  Not compiled in this repository's build image (no Fortran
 ! compiler there); tests/test_fortran_shim.py checks the types, constants, constructors and interfaces against
 ! include/cfd_b200.h.  Every component of the bind(c) types is default-initialised and every structure constructor
 ! uses keywords, so a field added to the C struct cannot silently break a constructor.
