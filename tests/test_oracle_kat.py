@@ -235,3 +235,25 @@ def test_oblique_convection(oracle, case):
     assert np.abs(phi[:, nj // 2 - 1] - np.array(c["phi_row"])).max() < 1e-13
     assert rel(np.abs(phi).sum(), c["sum_abs_phi"]) < 1e-12
     assert rel(phi[ni // 2 - 1, nj // 2 - 1], c["phi_mid"]) < 1e-12
+
+
+# ---- the two transient 1-D heat programs (rows a9 / a11 of SURVEY section 8) --------------------------------------------------
+@pytest.mark.parametrize("case", ["shipped", "nx41_short", "nx33_t1"])
+def test_heat1d_programs(oracle, case):
+    """orc_heat1d_explicit / orc_heat1d_implicit (oracle/heat_oracle.c) against the numpy restatement of the two programs: the
+    step count of the `do while (time <= endtime)` loop and the final temperature profile -- as shipped (40 001 explicit and
+    50 001 implicit steps to t = 10) and two shorter variants."""
+    import ctypes as C
+    c = kat("heat1d")[case]
+    L = oracle.lib()
+    nx = c["nx"]
+    t0, x, t = np.zeros(nx), np.zeros(nx), np.zeros(nx)
+    dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+    n = L.orc_heat1d_explicit(5.0, 1.0, 1.0, 0.0, 1.0, 0.0, 0.0, dp(t0), c["endtime"], c["dt_explicit"], 0.1, 1.0e3, dp(x), dp(t),
+                              nx, 10 ** 7)
+    assert n == c["steps_explicit"]
+    assert np.abs(t - np.array(c["t_explicit"])).max() <= 1e-12 * max(1.0, np.abs(t).max())
+    n = L.orc_heat1d_implicit(5.0, 1.0, 1.0, 0.0, 1.0, 0.0, 0.0, dp(t0), c["endtime"], c["dt_implicit"], 0.1, 1.0e3, dp(x), dp(t),
+                              nx, 10 ** 7)
+    assert n == c["steps_implicit"]
+    assert np.abs(t - np.array(c["t_implicit"])).max() <= 1e-12 * max(1.0, np.abs(t).max())

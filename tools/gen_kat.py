@@ -1642,7 +1642,71 @@ def gen_oblique():
     return out
 
 
-GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation, "stag_unsteady": gen_stag_unsteady, "oblique": gen_oblique}
+# =====================================================================================================================
+# 6. finite-difference-method/heat-conduction/transient-conduction-1d: the explicit (explicit-time/
+#    fdm1d_explicit_heat_cond.f90:88-141) and implicit (implicit-time/fdm1d_explicit_heat_cond.f90:76-184) programs as
+#    shipped -- nx = 21, k = 5, rho = cp = 1, QDOT = 1e3 where x < 0.1, endtime = 10 -- and two shorter variants.  The time
+#    loop `do while (time <= endtime)` counts with a floating-point sum, so the step count is part of the answer.
+# =====================================================================================================================
+@numba.njit(cache=True)
+def thomas_pq(a, b, c, d, x):
+    """thomas (:147-184) for a(i) x(i-1) + b(i) x(i) + c(i) x(i+1) = d(i), i = 1..n (0-based here), in P-Q form:
+    x(i) = P(i) x(i+1) + Q(i).  The reference eliminates with e = c/temp, f = (d - a f_prev)/temp: the same numbers."""
+    n = len(b)
+    P = np.zeros(n); Q = np.zeros(n)
+    P[0] = -c[0] / b[0]
+    Q[0] = d[0] / b[0]
+    for i in range(1, n):
+        den = b[i] + a[i] * P[i - 1]
+        P[i] = -c[i] / den
+        Q[i] = (d[i] - a[i] * Q[i - 1]) / den
+    x[n - 1] = Q[n - 1]
+    for i in range(n - 2, -1, -1):
+        x[i] = P[i] * x[i + 1] + Q[i]
+
+
+def gen_heat1d():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of the two transient-conduction-1d programs; independent of "
+                      "oracle/heat_oracle.c)"}
+    for key, nx, endtime, cfl, dt_imp in (("shipped", 21, 10.0, 0.5, 2.0e-4), ("nx41_short", 41, 0.05, 0.4, 1.0e-4),
+                                          ("nx33_t1", 33, 1.0, 0.25, 5.0e-4)):
+        k, rho, cp, xa, xb, ta, tb = 5.0, 1.0, 1.0, 0.0, 1.0, 0.0, 0.0
+        dx = (xb - xa) / float(nx - 1)
+        x = xa + np.arange(nx) * dx
+        q = np.where(x < 0.1, 1.0e3, 0.0)
+        # ---- explicit: t(i) = tcopy(i) + (k/rho/cp*(tcopy(i+1) - 2 tcopy(i) + tcopy(i-1))/dx**2 + QDOT/rho/cp)*dt  (:130-139)
+        dt = cfl * dx ** 2 / (k / rho / cp)
+        tc = np.zeros(nx)
+        t = tc.copy()
+        time_, n_exp = 0.0, 0
+        while time_ <= endtime:
+            t[0], t[-1] = ta, tb
+            t[1:-1] = tc[1:-1] + (k / rho / cp * (tc[2:] - 2 * tc[1:-1] + tc[:-2]) / dx ** 2 + q[1:-1] / rho / cp) * dt
+            tc[:] = t
+            time_ += dt
+            n_exp += 1
+        t_exp = t.copy()
+        # ---- implicit: (1 + 2 fo) t(i) - fo t(i-1) - fo t(i+1) = tcopy(i) + dt QDOT/rho/cp, Dirichlet rows  (:118-141)
+        fo = k * dt_imp / rho / cp / dx ** 2
+        a = np.full(nx, -fo); b = np.full(nx, 1.0 + 2.0 * fo); c = np.full(nx, -fo)
+        a[0] = c[0] = a[-1] = c[-1] = 0.0
+        b[0] = b[-1] = 1.0
+        tc = np.zeros(nx)
+        t = tc.copy()
+        time_, n_imp = 0.0, 0
+        while time_ <= endtime:
+            rhs = tc + dt_imp * q / rho / cp
+            rhs[0], rhs[-1] = ta, tb
+            thomas_pq(a, b, c, rhs, t)
+            tc[:] = t
+            time_ += dt_imp
+            n_imp += 1
+        out[key] = {"nx": nx, "endtime": endtime, "dt_explicit": dt, "dt_implicit": dt_imp, "steps_explicit": n_exp,
+                    "steps_implicit": n_imp, "t_explicit": [float(z) for z in t_exp], "t_implicit": [float(z) for z in t]}
+    return out
+
+
+GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation, "stag_unsteady": gen_stag_unsteady, "oblique": gen_oblique, "heat1d": gen_heat1d}
 
 
 
