@@ -257,3 +257,22 @@ def test_heat1d_programs(oracle, case):
                               nx, 10 ** 7)
     assert n == c["steps_implicit"]
     assert np.abs(t - np.array(c["t_implicit"])).max() <= 1e-12 * max(1.0, np.abs(t).max())
+
+
+@pytest.mark.parametrize("case", ["shipped_7x5", "variable_13x9", "variable_21x17"])
+def test_steady_heat_program_with_its_dense_matrix(oracle, case):
+    """orc_heat2d_coeffs + orc_heat2d_gs (matrix-free, lexicographic order) against the restatement that builds the program's
+    dense (nx*ny)^2 matrix and runs gauss_seidel over full rows: same number of passes, same last norm, same temperatures --
+    the shipped 7 x 5 plate (LAMBDA = 20, QDOT = 5e7, walls at 300 K) and two variable-conductivity cases."""
+    c = kat("heat2d_steady")[case]
+    if c["kind"] == "const":
+        lam, qd = (lambda x, y: 20.0 + 0.0 * x), (lambda x, y: 5.0e7 + 0.0 * x)
+    else:
+        lam, qd = (lambda x, y: 20.0 * (1.0 + 10.0 * x + 5.0 * y)), (lambda x, y: 5.0e7 * (1.0 + 20.0 * x) + 0.0 * y)
+    h = oracle.HeatVar(c["nx"], c["ny"], lam, qd)
+    tl, tr, tb, tt = c["tbc"]
+    x, passes, dx2 = h.gauss_seidel(tbc=(tl, tr, tb, tt), order=0)
+    assert passes == c["passes"]
+    want = np.array(c["t"]).reshape((c["nx"], c["ny"]), order="F")
+    assert np.abs(x - want).max() <= 1e-12 * np.abs(want).max()
+    assert rel(dx2, c["dx2"]) < 1e-6

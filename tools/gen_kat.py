@@ -1706,7 +1706,83 @@ def gen_heat1d():
     return out
 
 
-GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation, "stag_unsteady": gen_stag_unsteady, "oblique": gen_oblique, "heat1d": gen_heat1d}
+# =====================================================================================================================
+# 7. finite-difference-method/heat-conduction/steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90 as written: the DENSE
+#    (nx*ny)^2 matrix of interior() (:131-191) and boundary() (:193-246), then gauss_seidel (:248-287) over full rows,
+#    zeros included.  The oracle and the device never build the matrix; this restatement does, exactly as the program.
+# =====================================================================================================================
+@numba.njit(cache=True)
+def dense_gauss_seidel(a, b, x0, imax, tol, rf):
+    n = len(b)
+    x1 = x0.copy()
+    x2 = x1.copy()
+    passes = 0
+    dx2 = 0.0
+    for k in range(1, imax + 1):
+        passes = k
+        for i in range(n):
+            s = 0.0
+            for j in range(n):
+                if j < i:
+                    s = s + a[i, j] * x2[j]
+                elif j > i:
+                    s = s + a[i, j] * x1[j]
+            x2[i] = (b[i] - s) * rf / a[i, i] + (1 - rf) * x1[i]
+        dx2 = 0.0
+        for i in range(n):
+            dx2 = dx2 + (x1[i] - x2[i]) ** 2
+        dx2 = np.sqrt(dx2)
+        if dx2 < tol:
+            break
+        x1[:] = x2
+    return x2, passes, dx2
+
+
+def gen_heat2d_steady():
+    out = {"_source": "tools/gen_kat.py (numpy/numba restatement of steady-heat-conduction-2d/fdm2d_steady_heat_cond.f90 with "
+                      "its dense matrix; independent of oracle/heat_oracle.c)"}
+    cases = (("shipped_7x5", 7, 5, "const"), ("variable_13x9", 13, 9, "var"), ("variable_21x17", 21, 17, "var"))
+    for key, nx, ny, kind in cases:
+        xmin, xmax, ymin, ymax = 0.0, 0.03, 0.0, 0.02
+        tleft, tright, tbottom, ttop = (300.0, 300.0, 300.0, 300.0) if kind == "const" else (300.0, 320.0, 310.0, 290.0)
+        lam = (lambda x, y: 20.0) if kind == "const" else (lambda x, y: 20.0 * (1.0 + 10.0 * x + 5.0 * y))
+        qd = (lambda x, y: 5.0e7) if kind == "const" else (lambda x, y: 5.0e7 * (1.0 + 20.0 * x))
+        dx, dy = (xmax - xmin) / (nx - 1), (ymax - ymin) / (ny - 1)            # xymesh :107-129
+        x = np.zeros(nx + 1); y = np.zeros(ny + 1)
+        x[1] = xmin
+        for i in range(2, nx + 1):
+            x[i] = x[1] + (i - 1) * dx
+        y[1] = ymin
+        for j in range(2, ny + 1):
+            y[j] = y[1] + (j - 1) * dy
+        n = nx * ny
+        a = np.zeros((n + 1, n + 1)); rhs = np.zeros(n + 1)
+        ddx, ddy = x[2] - x[1], y[2] - y[1]
+        for i in range(2, nx):
+            for j in range(2, ny):
+                k = (j - 1) * nx + i
+                aw = lam(0.5 * (x[i] + x[i - 1]), y[j]) / ddx ** 2
+                ae = lam(0.5 * (x[i] + x[i + 1]), y[j]) / ddx ** 2
+                as_ = lam(x[i], 0.5 * (y[j] + y[j - 1])) / ddy ** 2
+                an = lam(x[i], 0.5 * (y[j] + y[j + 1])) / ddy ** 2
+                a[k, k - 1], a[k, k + 1], a[k, k - nx], a[k, k + nx] = aw, ae, as_, an
+                a[k, k] = -(aw + ae + as_ + an)
+                rhs[k] = -qd(x[i], y[j])
+        for j in range(2, ny):                                                  # boundary :209-222
+            for i, tv in ((1, tleft), (nx, tright)):
+                k = (j - 1) * nx + i
+                a[k, k], rhs[k] = 1.0, tv
+        for j, tv in ((1, tbottom), (ny, ttop)):                                # :224-237 (rows include the corners)
+            for i in range(1, nx + 1):
+                k = (j - 1) * nx + i
+                a[k, k], rhs[k] = 1.0, tv
+        t, passes, dx2 = dense_gauss_seidel(a[1:, 1:].copy(), rhs[1:].copy(), np.zeros(n), 500, 1.0e-7, 0.5)
+        out[key] = {"nx": nx, "ny": ny, "kind": kind, "tbc": [tleft, tright, tbottom, ttop], "passes": int(passes), "dx2": float(dx2),
+                    "t": [float(z) for z in t], "t_centre": float(t[(ny // 2) * nx + nx // 2])}
+    return out
+
+
+GENERATORS = {"cavity_regen": gen_cavity, "cylinder_regen": gen_cylinder, "buoyancy": gen_buoyancy, "teach": gen_teach, "teach_turb": gen_teach_turb, "fdcavity": gen_fdcavity, "fdcavity_implicit": gen_fdcavity_implicit, "stagnation": gen_stagnation, "stag_unsteady": gen_stag_unsteady, "oblique": gen_oblique, "heat1d": gen_heat1d, "heat2d_steady": gen_heat2d_steady}
 
 
 
