@@ -276,3 +276,21 @@ def test_steady_heat_program_with_its_dense_matrix(oracle, case):
     want = np.array(c["t"]).reshape((c["nx"], c["ny"]), order="F")
     assert np.abs(x - want).max() <= 1e-12 * np.abs(want).max()
     assert rel(dx2, c["dx2"]) < 1e-6
+
+
+@pytest.mark.parametrize("re", [100, 1000])
+def test_cv256_fixtures_agree_with_the_second_restatement(re):
+    """The converged 256^2 fixtures the GPU tests use were written by the C oracle (tools/gen_cavity_converged.py); the second
+    restatement ran the same cases to the literal stop rule on its own (tools/gen_cavity_cv256_regen.py, ~1.5 h of CPU each):
+    same iteration count (133 440 / 88 876), monitor values and centre-line profiles to 1e-9, field sums to 1e-9."""
+    path = os.path.join(GOLD, f"cavity_cv256_re{re}_regen.json")
+    if not os.path.exists(path):
+        pytest.skip("regenerated table not present (tools/gen_cavity_cv256_regen.py)")
+    r = json.load(open(path))
+    f = np.load(os.path.join(GOLD, f"cavity_cv256_re{re}.npz"))
+    assert r["iters"] == int(f["iters"])
+    assert rel(r["u_mon"], float(f["u_mon"])) < 1e-9 and rel(r["v_mon"], float(f["v_mon"])) < 1e-9
+    for a, b in zip(r["sum_abs"], f["sum_abs"]):
+        assert rel(a, float(b)) < 1e-9
+    assert np.abs(np.array(r["u_centre"]) - f["u_centre"]).max() < 1e-9 * np.abs(f["u_centre"]).max()
+    assert np.abs(np.array(r["v_centre"]) - f["v_centre"]).max() < 1e-9 * np.abs(f["v_centre"]).max()
